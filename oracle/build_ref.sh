@@ -1,0 +1,34 @@
+#!/usr/bin/env bash
+# build_ref.sh <reference_root> <out_dir>      TEST INFRASTRUCTURE ONLY.
+#
+# Compiles the REFERENCE's own sources (from a headless-patched scratch copy under /tmp, see patch_ref.py;
+# the reference's CMake build is not used and no reference source enters the repo) into
+#   <out_dir>/libtitan_ref_host.so   host-callable reference code + oracle/ref_host_shim.cu   (CPU, runs here)
+#   <out_dir>/titan_ref_cuda         the reference's CUDA engine + oracle/ref_cuda_dump.cu     (needs a GPU)
+# Flags follow the reference's CMakeLists.txt: C++14, separable compilation, -DCONSTRAINTS, no GRAPHICS.
+set -euo pipefail
+REF="${1:-/root/reference}"
+OUT="${2:-$(dirname "$0")/_ref}"
+HERE="$(cd "$(dirname "$0")" && pwd)"
+if [ ! -d "$REF/src" ]; then echo "build_ref: no reference at $REF (skipped)"; exit 0; fi
+mkdir -p "$OUT"
+SCRATCH="$(mktemp -d /tmp/titan_ref_build.XXXXXX)"
+trap 'rm -rf "$SCRATCH"' EXIT
+python3 "$HERE/patch_ref.py" "$REF" "$SCRATCH/ref"
+S="$SCRATCH/ref"
+# the distro g++ as host compiler (the exported CXX=/opt/gcc/bin/g++ lacks pieces, see oracle/Makefile)
+NVFLAGS="-std=c++14 -O3 -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a -rdc=true -DCONSTRAINTS \
+  -Xcompiler -fPIC -Xcompiler -ffp-contract=off -I$S/include -I$S/include/Titan -w"
+for f in vec mass spring object sim; do
+  nvcc $NVFLAGS -c "$S/src/$f.cu" -o "$SCRATCH/$f.o" &
+done
+nvcc $NVFLAGS -c "$HERE/ref_host_shim.cu" -o "$SCRATCH/shim.o" &
+nvcc $NVFLAGS -c "$HERE/ref_cuda_dump.cu" -o "$SCRATCH/dump.o" &
+wait
+nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a -shared -Xcompiler -fPIC \
+  "$SCRATCH/vec.o" "$SCRATCH/mass.o" "$SCRATCH/spring.o" "$SCRATCH/object.o" "$SCRATCH/shim.o" \
+  -o "$OUT/libtitan_ref_host.so" -lcudart
+nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a \
+  "$SCRATCH/vec.o" "$SCRATCH/mass.o" "$SCRATCH/spring.o" "$SCRATCH/object.o" "$SCRATCH/sim.o" "$SCRATCH/dump.o" \
+  -o "$OUT/titan_ref_cuda" -lcudart
+echo "build_ref: built $OUT/libtitan_ref_host.so and $OUT/titan_ref_cuda"

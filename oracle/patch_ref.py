@@ -1,0 +1,67 @@
+#!/usr/bin/env python3
+"""Make a headless-buildable COPY of the reference under a scratch directory.  TEST INFRASTRUCTURE ONLY.
+
+usage: patch_ref.py /root/reference /tmp/scratch_dir
+
+The reference does not compile without a GL stack as shipped.  This script copies
+src/ and include/ to the scratch directory (never into the repo) and applies the six guards listed
+there.  No arithmetic on the step path is touched: every edit is an #ifdef GRAPHICS guard, a missing
+#include, or mapping atomicDoubleAdd to the native fp64 atomicAdd on sm_60+.
+"""
+import os
+import shutil
+import sys
+
+
+def sub_once(text, old, new, what):
+    if text.count(old) < 1:
+        raise SystemExit("patch_ref: anchor not found: " + what)
+    return text.replace(old, new, 1)
+
+
+def main(ref, out):
+    if os.path.exists(out):
+        shutil.rmtree(out)
+    os.makedirs(out)
+    shutil.copytree(os.path.join(ref, "src"), os.path.join(out, "src"))
+    shutil.copytree(os.path.join(ref, "include"), os.path.join(out, "include"))
+
+    def edit(rel, fn):
+        p = os.path.join(out, rel)
+        with open(p) as f:
+            t = f.read()
+        t = fn(t)
+        with open(p, "w") as f:
+            f.write(t)
+
+    # 1. src/vec.cu:13-31 -- atomicDoubleAdd only exists for __CUDA_ARCH__ < 600
+    edit("src/vec.cu", lambda t: sub_once(
+        t, "    return __longlong_as_double(old);\n}\n#endif",
+        "    return __longlong_as_double(old);\n}\n#else\n#define atomicDoubleAdd atomicAdd\n#endif",
+        "vec.cu atomicDoubleAdd"))
+
+    # 2. src/object.cu:456-459 -- Mass::color exists only under GRAPHICS
+    edit("src/object.cu", lambda t: sub_once(
+        t, "        ml->color = c;\n        mr->color = c;",
+        "#ifdef GRAPHICS\n        ml->color = c;\n        mr->color = c;\n#endif", "object.cu setColor"))
+
+    def sim(t):
+        # 3. DBL_MIN in stlparser.h needs <cfloat>
+        t = sub_once(t, '#include "sim.h"\n', '#include "sim.h"\n#include <cfloat>\n', "sim.cu cfloat")
+        # 4. cuda_gl_interop.h needs GL/gl.h
+        t = sub_once(t, "#include <cuda_gl_interop.h>\n",
+                     "#ifdef GRAPHICS\n#include <cuda_gl_interop.h>\n#endif\n", "sim.cu gl interop")
+        # 5. Simulation::fps() is declared only under GRAPHICS
+        t = sub_once(t, "double Simulation::fps(){", "#ifdef GRAPHICS\ndouble Simulation::fps(){", "sim.cu fps open")
+        t = sub_once(t, "        return -1.0;\n    }\n}\n", "        return -1.0;\n    }\n}\n#endif\n", "sim.cu fps close")
+        # 6. t_fps_now exists only under GRAPHICS
+        t = sub_once(t, "    t_fps_now = std::chrono::system_clock::now(); // set initial before times\n",
+                     "#ifdef GRAPHICS\n    t_fps_now = std::chrono::system_clock::now();\n#endif\n", "sim.cu t_fps_now")
+        return t
+
+    edit("src/sim.cu", sim)
+    print("patch_ref: patched copy in", out)
+
+
+if __name__ == "__main__":
+    main(sys.argv[1], sys.argv[2])
