@@ -1,0 +1,151 @@
+/*
+ * titan_b200.h -- C ABI of the B200-native mass-spring step engine (libtitan_b200.so).
+ *
+ * The reference (GitWyd/Titan) has no FFI layer: its boundary is the C++ class titan::Simulation
+ * (include/Titan/sim.h:38-129).  This ABI is the "thin C-ABI layer" the host C++ facade
+ * (the headers in include/Titan + titan_b200/host/) calls; each entry point names the reference code it replaces
+ * (paths relative to the reference root).  Plain pointers and sizes only; no C++ or torch types.
+ *
+ * Conventions
+ *  - every function returns 0 on success, else a tb_status / cudaError_t-derived code; the message is in
+ *    tb_last_error(e).  Nothing throws across this boundary.
+ *  - pointers are HOST pointers to caller-owned plain arrays unless the name ends in _dev.
+ *  - xyz arrays are [count][3] row-major doubles (the layout of titan::Vec, include/Titan/vec.h:165).
+ *  - optional array arguments may be NULL (= leave that field unchanged; at first upload = default).
+ *  - one engine owns one CUDA device + one stream; calls on one engine are not re-entrant.  The facade's
+ *    GPU thread calls tb_run_async/tb_sync, the user thread calls upload/download only while paused,
+ *    exactly the discipline of the reference (docs/README.md:440-443).
+ *  - there is NO CPU fallback: without a CUDA device tb_create fails with TB_ERR_NO_DEVICE.
+ */
+#ifndef TITAN_B200_H
+#define TITAN_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TB_ABI_VERSION 1
+
+#if defined(__GNUC__)
+#define TB_API __attribute__((visibility("default")))
+#else
+#define TB_API
+#endif
+
+typedef struct tb_engine tb_engine;
+
+typedef enum {
+    TB_OK = 0,
+    TB_ERR_INVALID = 1,     /* bad argument / call order */
+    TB_ERR_NO_DEVICE = 2,   /* no CUDA device: there is no CPU path */
+    TB_ERR_CUDA = 3,        /* a CUDA call failed; see tb_last_error */
+    TB_ERR_UNSUPPORTED = 4, /* feature outside the built scope (e.g. magnetic masses) */
+    TB_ERR_OOM = 5
+} tb_status;
+
+/* tb_create flags */
+#define TB_MATH_FAST 0u      /* default: fp64 with FMA contraction and one reciprocal per spring;  */
+                             /* <= 1e-12 relative per step against the oracle (tests state it)      */
+#define TB_MATH_STRICT 1u    /* unfused IEEE ops in the reference's operation order: bit-identical  */
+                             /* to oracle/titan_oracle.c (passive springs; sin() may differ by 1ulp) */
+#define TB_NO_GRAPH 2u       /* launch every step individually instead of CUDA-Graph batches         */
+#define TB_KERNEL_CSR 4u     /* force the generic CSR-gather step kernel (disable the tiled one)     */
+
+/* SpringType, include/Titan/spring.h:17-18 */
+enum { TB_PASSIVE_SOFT = 0, TB_PASSIVE_STIFF = 1, TB_ACTIVE_CONTRACT_THEN_EXPAND = 2,
+       TB_ACTIVE_EXPAND_THEN_CONTRACT = 3, TB_ACTUATED_EXPAND = 4, TB_ACTUATED_CONTRACT = 5 };
+/* CONSTRAINT_TYPE, include/Titan/object.h:225-227 */
+enum { TB_CONSTRAINT_PLANE = 0, TB_CONTACT_PLANE = 1, TB_BALL = 2, TB_DIRECTION = 3 };
+
+/* CudaContactPlane (include/Titan/object.h:138-149); normal already normalised by the caller, as the
+ * ContactPlane constructor does (object.h:101-109). */
+typedef struct { double normal[3]; double offset; double friction_k; double friction_s; } tb_plane;
+/* CudaBall (include/Titan/object.h:90-99) */
+typedef struct { double center[3]; double radius; } tb_ball;
+/* one record of a mass's LOCAL_CONSTRAINTS (include/Titan/object.h:181-220; Mass::addConstraint,
+ * src/mass.cu:104-122): vec = normalised normal / tangent, or ball center; num = friction / offset / radius */
+typedef struct { int32_t kind; int32_t pad; double vec[3]; double num; } tb_local;
+
+/* ---- lifetime ------------------------------------------------------------------------------------------- */
+TB_API int tb_abi_version(void);
+TB_API int tb_device_count(void);
+/* replaces the implicit device-0 context of the reference (no cudaSetDevice anywhere in src/sim.cu) */
+TB_API int tb_create(int device, uint32_t flags, tb_engine **out);
+TB_API void tb_destroy(tb_engine *e);                 /* Simulation::freeGPU, src/sim.cu:131-182 */
+TB_API const char *tb_last_error(const tb_engine *e); /* replaces gpuErrchk's fprintf, src/sim.cu:60-75 */
+
+/* ---- topology: replaces massToArray/springToArray pointer tables, src/sim.cu:940-1025 ------------------ */
+/* Declares nm masses and ns springs; left/right are mass indices, -1 = nullptr endpoint (spring skipped,
+ * src/sim.cu:1163).  The engine derives the CSR incidence (ascending spring index per mass) on upload.
+ * State and parameters are reset to defaults (m=0.1, k=10000, valid, not fixed, PASSIVE_SOFT, ...). */
+TB_API int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, const int32_t *right);
+
+/* ---- mass state: CUDA_MASS(Mass&) src/mass.cu:74-100, Simulation::set/setAll src/sim.cu:603-765 -------- */
+/* idx == NULL: masses [first, first+count); otherwise the `count` masses listed in idx (container upload). */
+TB_API int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t *idx,
+                      const double *pos, const double *vel, const double *m, const double *T,
+                      const double *extern_force, const uint8_t *fixed, const int32_t *drag,
+                      const uint8_t *valid);
+/* rad, stiffness, max_mag_force, mag_scale_factor (include/Titan/mass.h:97-100).  Any non-zero rad or
+ * max_mag_force makes tb_run_async fail with TB_ERR_UNSUPPORTED (magnet pass). */
+TB_API int tb_set_mass_magnet(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, const double *rad,
+                       const double *stiffness, const double *max_mag_force, const double *mag_scale);
+/* Mass::operator=(CUDA_MASS&) src/mass.cu:21-49, Simulation::get/getAll src/sim.cu:589-654,1051-1116 */
+TB_API int tb_get_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t *idx,
+                      double *pos, double *vel, double *acc, double *T, double *extern_force);
+
+/* ---- spring parameters: CUDA_SPRING(const Spring&) src/spring.cu:37-63 --------------------------------- */
+TB_API int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32_t *idx,
+                         const double *k, const double *rest, const double *damping, const int32_t *type,
+                         const double *omega, const double *l_max, const double *l_min, const double *rate);
+/* Spring::update copies back only _rest (src/spring.cu:12-14) */
+TB_API int tb_get_spring_rest(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, double *rest);
+
+/* ---- constraints ---------------------------------------------------------------------------------------- */
+/* createPlane/createBall, src/sim.cu:2251-2288; applied in array order, planes before balls (:1303-1309) */
+TB_API int tb_set_planes(tb_engine *e, int32_t n, const tb_plane *planes);
+TB_API int tb_set_balls(tb_engine *e, int32_t n, const tb_ball *balls);
+/* per-mass local constraints as CSR over all nm masses (row_ptr[nm+1]); NULL/empty clears them.
+ * Evaluation order per mass is the reference's: contact planes, balls, constraint planes, directions,
+ * each kind in record order (src/sim.cu:1312-1326). */
+TB_API int tb_set_local_constraints(tb_engine *e, const int64_t *row_ptr, const tb_local *records);
+
+/* setGlobalAcceleration src/sim.cu:2334-2340, setTimeStep :798-808 */
+TB_API int tb_set_globals(tb_engine *e, const double g[3], double dt);
+
+/* ---- stepping: Simulation::execute, src/sim.cu:1704-1841 (Euler branch :1800-1811) -------------------- */
+/* Enqueue nsteps steps on the engine stream and return.  t0 is the host Simulation::T at the first of
+ * them; step j uses t = t0 (+ dt) j times, accumulated in fp64 exactly like `T += dt` (:1811). */
+TB_API int tb_run_async(tb_engine *e, int64_t nsteps, double t0);
+TB_API int tb_sync(tb_engine *e);                                  /* cudaDeviceSynchronize at a breakpoint, :1708 */
+TB_API int tb_steps_done(tb_engine *e, int64_t *steps);            /* total steps enqueued so far */
+/* device time in ms of the most recent tb_run_async (CUDA events on the engine stream); call after tb_sync */
+TB_API int tb_last_run_ms(tb_engine *e, double *ms);
+
+/* ---- introspection used by tests / bench ---------------------------------------------------------------- */
+typedef struct {
+    int64_t nm, ns;
+    int32_t kernel;              /* 0 = CSR gather, 1 = tiled */
+    int32_t n_tiles;
+    int64_t launches;            /* kernel launches (graph nodes included) since creation */
+    int64_t device_bytes;        /* bytes of device memory held */
+    double algorithmic_bytes_per_step; /* nm*104 + ns*B_s */
+    int32_t sm_count;
+    int32_t graph_steps;         /* steps per CUDA-Graph launch (0 = no graph) */
+} tb_info;
+TB_API int tb_get_info(tb_engine *e, tb_info *info);
+/* headless position export, fp64 -> packed fp32 xyz (updateVertices, src/sim.cu:1944-1952); out is a
+ * DEVICE pointer to nm*3 floats owned by the engine, valid until the next call. */
+TB_API int tb_export_positions_f32_dev(tb_engine *e, const float **out_dev);
+
+/* page-locked host memory for upload/download buffers (the reference stages through pageable `new[]`
+ * arrays, src/sim.cu:948-962,1099-1101); owned by the engine, released by tb_destroy */
+TB_API int tb_alloc_host(tb_engine *e, size_t bytes, void **out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TITAN_B200_H */

@@ -1,0 +1,214 @@
+"""GPU parity tests proper: the CUDA engine, driven through the C ABI, against the CPU oracle on the same inputs.
+
+Tolerances (BASELINE.json north_star: <= 1e-9 relative per step in fp64; indexing bit-exact):
+  * TB_MATH_STRICT: bit-identical to the oracle for every scenario without sin() actuation; with actuation the
+    device sin() may differ from glibc's by 1 ulp, so <= 1e-13 relative after the test's step count.
+  * TB_MATH_FAST (what bench.py times): <= 1e-12 relative after 1 step, <= 1e-9 after 100 steps.
+Relative error is max|a-b| / max(1, max|b|) per field.
+"""
+import numpy as np
+import pytest
+
+import scenes
+import titan_b200 as tb
+
+pytestmark = pytest.mark.gpu
+
+FIELDS = ("pos", "vel", "acc")
+
+
+def rel(a, b):
+    return float(np.max(np.abs(a - b)) / max(1.0, float(np.max(np.abs(b)))))
+
+
+def same_bits(a, b):
+    return bool((np.ascontiguousarray(a).view(np.uint64) == np.ascontiguousarray(b).view(np.uint64)).all())
+
+
+def run_engine(sc, nsteps, flags, chunks=1):
+    eng = tb.Engine(0, flags)
+    scenes.upload(eng, sc)
+    t = sc.T_sim
+    per = nsteps // chunks
+    done = 0
+    for c in range(chunks):
+        n = per if c < chunks - 1 else nsteps - done
+        eng.run(n, t)
+        for _ in range(n):
+            t += sc.dt
+        done += n
+    st = eng.get_mass_state()
+    st["rest"] = eng.get_spring_rest() if sc.ns else np.zeros(0)
+    st["info"] = eng.info()
+    eng.close()
+    return st
+
+
+def oracle_after(sc, nsteps):
+    o = sc.copy()
+    o.step(nsteps)
+    return o
+
+
+@pytest.mark.parametrize("name", ["c1_readme", "contact_friction", "local_constraints", "cube_beam"])
+@pytest.mark.parametrize("nsteps", [1, 10, 137])
+def test_strict_is_bit_identical(name, nsteps):
+    sc = scenes.SCENARIOS[name]()
+    o = oracle_after(sc, nsteps)
+    g = run_engine(sc, nsteps, tb.MATH_STRICT)
+    for f in FIELDS:
+        assert rel(g[f], getattr(o, f)) == 0.0, (name, f, rel(g[f], getattr(o, f)))
+        assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (name, f)  # "+ 0.0" folds -0 into +0
+    assert same_bits(g["T"], o.T)
+    assert same_bits(g["rest"], o.rest)
+    assert same_bits(g["extern_force"] + 0.0, o.ext + 0.0)
+
+
+@pytest.mark.parametrize("nsteps", [1, 10, 137])
+def test_strict_actuated(nsteps):
+    sc = scenes.actuated()
+    o = oracle_after(sc, nsteps)
+    g = run_engine(sc, nsteps, tb.MATH_STRICT)
+    for f in FIELDS:
+        assert rel(g[f], getattr(o, f)) <= 1e-13, (f, rel(g[f], getattr(o, f)))
+    assert same_bits(g["rest"], o.rest)  # the _rest mutation of ACTUATED_* springs involves no sin()
+
+
+@pytest.mark.parametrize("name", sorted(scenes.SCENARIOS))
+def test_fast_within_tolerance(name):
+    sc = scenes.SCENARIOS[name]()
+    for nsteps, tol in ((1, 1e-12), (100, 1e-9)):
+        o = oracle_after(sc, nsteps)
+        g = run_engine(sc, nsteps, tb.MATH_FAST)
+        for f in FIELDS:
+            assert rel(g[f], getattr(o, f)) <= tol, (name, nsteps, f, rel(g[f], getattr(o, f)))
+        assert same_bits(g["T"], o.T)
+
+
+@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.NO_GRAPH, tb.MATH_STRICT | tb.KERNEL_CSR])
+def test_graph_batches_and_chunking_do_not_change_results(flags):
+    sc = scenes.contact_friction()
+    ref = run_engine(sc, 237, tb.MATH_STRICT | tb.NO_GRAPH | tb.KERNEL_CSR)
+    for chunks in (1, 3):
+        g = run_engine(sc, 237, flags, chunks=chunks)
+        for f in ("pos", "vel"):
+            assert same_bits(g[f], ref[f]), (flags, chunks, f)
+
+
+def test_pause_step_count_matches_reference_loop():
+    # Simulation::execute runs while !(bp <= T): pause(1.0) at dt=1e-4 is 10,001 steps
+    sc = scenes.c1_readme()
+    o = sc.copy()
+    n = o.run_until(1.0)
+    assert n == 10001
+    g = run_engine(sc, n, tb.MATH_STRICT)
+    for f in FIELDS:
+        assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), f
+    assert same_bits(g["T"], o.T)
+
+
+def test_external_force_acts_for_one_step_only():
+    sc = scenes.lattice_scene((0, 0, 5), (1, 1, 1), 3)
+    sc.ext[:] = (1.0, 2.0, 3.0)
+    sc.fixed[4] = 1
+    o = oracle_after(sc, 5)
+    g = run_engine(sc, 5, tb.MATH_STRICT)
+    assert same_bits(g["pos"], o.pos) and same_bits(g["vel"], o.vel)
+    assert same_bits(g["extern_force"] + 0.0, o.ext + 0.0)
+    assert (g["extern_force"][4] == (1.0, 2.0, 3.0)).all()          # fixed masses keep theirs (sim.cu:1294)
+    assert (np.delete(g["extern_force"], 4, axis=0) == 0).all()
+
+
+def test_partial_upload_download_by_index():
+    sc = scenes.c1_readme()
+    eng = tb.Engine(0, tb.MATH_STRICT)
+    scenes.upload(eng, sc)
+    eng.run(7, 0.0)
+    o = oracle_after(sc, 7)
+    idx = np.array([3, 100, 17, 64], dtype=np.int32)
+    part = eng.get_mass_state(idx=idx)
+    assert same_bits(part["pos"], o.pos[idx]) and same_bits(part["vel"], o.vel[idx])
+    # container-style set: move four masses, zero their velocity, advance both sides
+    newpos = o.pos[idx] + 0.125
+    o.pos[idx] = newpos
+    o.vel[idx] = 0.0
+    eng.set_mass_state(idx=idx, pos=newpos, vel=np.zeros((4, 3)))
+    eng.run(9, o.T_sim)
+    o.step(9)
+    st = eng.get_mass_state()
+    assert same_bits(st["pos"], o.pos) and same_bits(st["vel"], o.vel)
+    # spring parameter edit by index
+    sidx = np.array([0, 500, 1035], dtype=np.int32)
+    o.k[sidx] = (123.0, 4567.0, 8.5)
+    eng.set_spring_params(idx=sidx, k=o.k[sidx])
+    eng.run(4, o.T_sim)
+    o.step(4)
+    st = eng.get_mass_state()
+    assert same_bits(st["pos"], o.pos) and same_bits(st["vel"], o.vel)
+    eng.close()
+
+
+def test_invalid_masses_and_null_springs_are_skipped():
+    sc = scenes.lattice_scene((0, 0, 3), (1, 1, 1), 4)
+    sc.valid[5] = 0
+    sc.left[10] = -1
+    sc.right[77] = -1
+    sc.vel[:, 0] = 0.1
+    o = oracle_after(sc, 20)
+    g = run_engine(sc, 20, tb.MATH_STRICT)
+    assert same_bits(g["pos"], o.pos) and same_bits(g["vel"], o.vel)
+
+
+def test_time_step_change_and_per_mass_T():
+    sc = scenes.c1_readme()
+    eng = tb.Engine(0, tb.MATH_STRICT)
+    scenes.upload(eng, sc)
+    o = sc.copy()
+    eng.run(11, o.T_sim); o.step(11)
+    eng.set_globals(None, 2.5e-4); o.dt = 2.5e-4
+    eng.run(13, o.T_sim); o.step(13)
+    st = eng.get_mass_state()
+    assert same_bits(st["T"], o.T) and same_bits(st["pos"], o.pos)
+    eng.close()
+
+
+def test_more_global_constraints_than_fit_inline():
+    sc = scenes.lattice_scene((0, 0, 0.3), (0.5, 0.5, 0.5), 3)
+    import oracle
+    for j in range(7):
+        sc.planes.append(oracle.make_plane((0.1 * j, 0.05 * j, 1), 0.05 * j, 0.1 * j, 0.2))
+        sc.balls.append(oracle.make_ball((0.3 * j - 1, 0, 0), 0.4))
+    o = oracle_after(sc, 15)
+    g = run_engine(sc, 15, tb.MATH_STRICT)
+    assert same_bits(g["pos"], o.pos) and same_bits(g["vel"], o.vel)
+
+
+def test_full_size_c2_two_steps_against_oracle():
+    # BASELINE config C2 (100^3, 1M masses, 12.7M springs) at full size: the oracle needs ~1 s per step
+    sc = scenes.c2_lattice(100)
+    assert sc.nm == 1000000 and sc.ns == 12731796
+    o = oracle_after(sc, 2)
+    g = run_engine(sc, 2, tb.MATH_STRICT)
+    assert same_bits(g["pos"], o.pos) and same_bits(g["vel"] + 0.0, o.vel + 0.0)
+    f = run_engine(sc, 2, tb.MATH_FAST)
+    assert rel(f["pos"], o.pos) <= 1e-12 and rel(f["vel"], o.vel) <= 1e-12
+    assert f["info"]["algorithmic_bytes_per_step"] == 409563104.0
+
+
+def test_determinism_run_to_run():
+    sc = scenes.c2_lattice(40)
+    a = run_engine(sc, 120, tb.MATH_FAST)
+    b = run_engine(sc, 120, tb.MATH_FAST)
+    assert same_bits(a["pos"], b["pos"]) and same_bits(a["vel"], b["vel"])
+
+
+def test_magnetic_masses_fail_loudly():
+    sc = scenes.lattice_scene((0, 0, 3), (1, 1, 1), 2)
+    sc.rad[:] = 0.015
+    sc.max_mag[:] = 10.0
+    eng = tb.Engine(0)
+    scenes.upload(eng, sc)
+    with pytest.raises(tb.TitanError) as ei:
+        eng.run(1, 0.0)
+    assert ei.value.status == 4
+    eng.close()

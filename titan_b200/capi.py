@@ -1,0 +1,252 @@
+"""ctypes binding of the C ABI in include/titan_b200.h (libtitan_b200.so).
+
+Thin by design: every method maps onto one tb_* entry point with numpy arrays as the plain host buffers.
+There is no CPU path: if the library is missing, or no CUDA device is present, creating an Engine raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "libtitan_b200.so")
+
+MATH_FAST, MATH_STRICT, NO_GRAPH, KERNEL_CSR = 0, 1, 2, 4
+PASSIVE_SOFT, PASSIVE_STIFF, ACTIVE_CONTRACT_THEN_EXPAND, ACTIVE_EXPAND_THEN_CONTRACT, ACTUATED_EXPAND, \
+    ACTUATED_CONTRACT = range(6)
+CONSTRAINT_PLANE, CONTACT_PLANE, BALL, DIRECTION = range(4)
+
+EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_last_error", "tb_set_topology",
+           "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
+           "tb_get_spring_rest", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
+           "tb_run_async", "tb_sync", "tb_steps_done", "tb_last_run_ms", "tb_get_info",
+           "tb_export_positions_f32_dev", "tb_alloc_host"]
+
+
+class Plane(C.Structure):
+    _fields_ = [("normal", C.c_double * 3), ("offset", C.c_double), ("friction_k", C.c_double),
+                ("friction_s", C.c_double)]
+
+
+class Ball(C.Structure):
+    _fields_ = [("center", C.c_double * 3), ("radius", C.c_double)]
+
+
+class Local(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("pad", C.c_int32), ("vec", C.c_double * 3), ("num", C.c_double)]
+
+
+class Info(C.Structure):
+    _fields_ = [("nm", C.c_int64), ("ns", C.c_int64), ("kernel", C.c_int32), ("n_tiles", C.c_int32),
+                ("launches", C.c_int64), ("device_bytes", C.c_int64), ("algorithmic_bytes_per_step", C.c_double),
+                ("sm_count", C.c_int32), ("graph_steps", C.c_int32)]
+
+
+class TitanError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__("titan_b200 error %d: %s" % (status, message))
+        self.status = status
+
+
+_lib = None
+_vp = C.c_void_p
+
+
+def lib():
+    """Load libtitan_b200.so.  Raises (never falls back) when the CUDA extension has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("titan_b200: %s is missing -- build it with `python -c 'import __graft_entry__ as g; "
+                              "g.build()'` (there is no CPU fallback)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.tb_last_error.restype = C.c_char_p
+        L.tb_last_error.argtypes = [_vp]
+        L.tb_create.argtypes = [C.c_int, C.c_uint32, C.POINTER(_vp)]
+        L.tb_destroy.argtypes = [_vp]
+        L.tb_destroy.restype = None
+        L.tb_set_topology.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp]
+        L.tb_set_mass_state.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 9
+        L.tb_set_mass_magnet.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 5
+        L.tb_get_mass_state.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 6
+        L.tb_set_spring_params.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 9
+        L.tb_get_spring_rest.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp]
+        L.tb_set_planes.argtypes = [_vp, C.c_int32, _vp]
+        L.tb_set_balls.argtypes = [_vp, C.c_int32, _vp]
+        L.tb_set_local_constraints.argtypes = [_vp, _vp, _vp]
+        L.tb_set_globals.argtypes = [_vp, _vp, C.c_double]
+        L.tb_run_async.argtypes = [_vp, C.c_int64, C.c_double]
+        L.tb_sync.argtypes = [_vp]
+        L.tb_steps_done.argtypes = [_vp, C.POINTER(C.c_int64)]
+        L.tb_last_run_ms.argtypes = [_vp, C.POINTER(C.c_double)]
+        L.tb_get_info.argtypes = [_vp, C.POINTER(Info)]
+        L.tb_export_positions_f32_dev.argtypes = [_vp, C.POINTER(_vp)]
+        L.tb_alloc_host.argtypes = [_vp, C.c_size_t, C.POINTER(_vp)]
+        _lib = L
+    return _lib
+
+
+def device_count():
+    return int(lib().tb_device_count())
+
+
+def _arr(a, dtype, shape=None):
+    if a is None:
+        return None, None
+    x = np.ascontiguousarray(a, dtype=dtype)
+    if shape is not None:
+        x = x.reshape(shape)
+    return x, x.ctypes.data_as(_vp)
+
+
+class Engine:
+    """One tb_engine: one CUDA device, one stream."""
+
+    def __init__(self, device=0, flags=MATH_FAST):
+        self._L = lib()
+        h = _vp()
+        rc = self._L.tb_create(int(device), int(flags), C.byref(h))
+        if rc != 0:
+            raise TitanError(rc, self._L.tb_last_error(None).decode())
+        self._h = h
+        self.nm = self.ns = 0
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.tb_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise TitanError(rc, self._L.tb_last_error(self._h).decode())
+
+    # ---- uploads ---------------------------------------------------------------------------------------
+    def set_topology(self, nm, left, right):
+        l, lp = _arr(left, np.int32)
+        r, rp = _arr(right, np.int32)
+        ns = 0 if l is None else l.shape[0]
+        self._ck(self._L.tb_set_topology(self._h, int(nm), int(ns), lp, rp))
+        self.nm, self.ns = int(nm), int(ns)
+
+    def _sel(self, n_total, first, count, idx):
+        if idx is not None:
+            i, ip = _arr(idx, np.int32)
+            return 0, i.shape[0], i, ip
+        if count is None:
+            count = n_total - first
+        return first, count, None, None
+
+    def set_mass_state(self, first=0, count=None, idx=None, pos=None, vel=None, m=None, T=None, extern_force=None,
+                       fixed=None, drag=None, valid=None):
+        first, count, keep, ip = self._sel(self.nm, first, count, idx)
+        a = [_arr(pos, np.float64, (count, 3)), _arr(vel, np.float64, (count, 3)), _arr(m, np.float64, (count,)),
+             _arr(T, np.float64, (count,)), _arr(extern_force, np.float64, (count, 3)),
+             _arr(fixed, np.uint8, (count,)), _arr(drag, np.int32, (count,)), _arr(valid, np.uint8, (count,))]
+        self._ck(self._L.tb_set_mass_state(self._h, first, count, ip, *[p for _, p in a]))
+
+    def set_mass_magnet(self, first=0, count=None, idx=None, rad=None, stiffness=None, max_mag_force=None,
+                        mag_scale=None):
+        first, count, keep, ip = self._sel(self.nm, first, count, idx)
+        a = [_arr(x, np.float64, (count,)) for x in (rad, stiffness, max_mag_force, mag_scale)]
+        self._ck(self._L.tb_set_mass_magnet(self._h, first, count, ip, *[p for _, p in a]))
+
+    def set_spring_params(self, first=0, count=None, idx=None, k=None, rest=None, damping=None, type=None,
+                          omega=None, l_max=None, l_min=None, rate=None):
+        first, count, keep, ip = self._sel(self.ns, first, count, idx)
+        d = lambda x: _arr(x, np.float64, (count,))  # noqa: E731
+        a = [d(k), d(rest), d(damping), _arr(type, np.int32, (count,)), d(omega), d(l_max), d(l_min), d(rate)]
+        self._ck(self._L.tb_set_spring_params(self._h, first, count, ip, *[p for _, p in a]))
+
+    def set_planes(self, planes):
+        arr = (Plane * max(1, len(planes)))(*planes)
+        self._ck(self._L.tb_set_planes(self._h, len(planes), C.cast(arr, _vp)))
+
+    def set_balls(self, balls):
+        arr = (Ball * max(1, len(balls)))(*balls)
+        self._ck(self._L.tb_set_balls(self._h, len(balls), C.cast(arr, _vp)))
+
+    def set_local_constraints(self, per_mass):
+        """per_mass: list (len nm) of lists of Local records, or None to clear."""
+        if not per_mass or not any(per_mass):
+            self._ck(self._L.tb_set_local_constraints(self._h, None, None))
+            return
+        ptr = np.zeros(self.nm + 1, dtype=np.int64)
+        ptr[1:] = np.cumsum([len(x) for x in per_mass])
+        flat = [r for rows in per_mass for r in rows]
+        recs = (Local * len(flat))(*flat)
+        self._ck(self._L.tb_set_local_constraints(self._h, ptr.ctypes.data_as(_vp), C.cast(recs, _vp)))
+
+    def set_globals(self, g=None, dt=1e-4):
+        gp = None if g is None else (C.c_double * 3)(*[float(x) for x in g])
+        self._ck(self._L.tb_set_globals(self._h, None if gp is None else C.cast(gp, _vp), float(dt)))
+
+    # ---- stepping --------------------------------------------------------------------------------------
+    def run_async(self, nsteps, t0=0.0):
+        self._ck(self._L.tb_run_async(self._h, int(nsteps), float(t0)))
+
+    def sync(self):
+        self._ck(self._L.tb_sync(self._h))
+
+    def run(self, nsteps, t0=0.0):
+        self.run_async(nsteps, t0)
+        self.sync()
+
+    def steps_done(self):
+        n = C.c_int64()
+        self._ck(self._L.tb_steps_done(self._h, C.byref(n)))
+        return n.value
+
+    def last_run_ms(self):
+        ms = C.c_double()
+        self._ck(self._L.tb_last_run_ms(self._h, C.byref(ms)))
+        return ms.value
+
+    def info(self):
+        i = Info()
+        self._ck(self._L.tb_get_info(self._h, C.byref(i)))
+        return {f: getattr(i, f) for f, _ in Info._fields_}
+
+    # ---- downloads -------------------------------------------------------------------------------------
+    def get_mass_state(self, first=0, count=None, idx=None, fields=("pos", "vel", "acc", "T", "extern_force"),
+                       out=None):
+        """Download the selected fields; `out` may hold preallocated (e.g. pinned) float64 arrays to fill."""
+        first, count, keep, ip = self._sel(self.nm, first, count, idx)
+        out = dict(out or {})
+        ptrs = []
+        for name in ("pos", "vel", "acc", "T", "extern_force"):
+            if name in fields:
+                shape = (count,) if name == "T" else (count, 3)
+                if name not in out:
+                    out[name] = np.zeros(shape)
+                a = out[name]
+                assert a.dtype == np.float64 and a.flags["C_CONTIGUOUS"] and a.size == int(np.prod(shape)), name
+                ptrs.append(out[name].ctypes.data_as(_vp))
+            else:
+                ptrs.append(None)
+        self._ck(self._L.tb_get_mass_state(self._h, first, count, ip, *ptrs))
+        return out
+
+    def get_spring_rest(self, first=0, count=None, idx=None):
+        first, count, keep, ip = self._sel(self.ns, first, count, idx)
+        out = np.zeros(count)
+        self._ck(self._L.tb_get_spring_rest(self._h, first, count, ip, out.ctypes.data_as(_vp)))
+        return out
+
+    def alloc_pinned(self, shape, dtype=np.float64):
+        """A numpy array over page-locked host memory (tb_alloc_host); freed with the engine."""
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = _vp()
+        self._ck(self._L.tb_alloc_host(self._h, C.c_size_t(n), C.byref(p)))
+        buf = (C.c_char * n).from_address(p.value)
+        return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    def export_positions_f32_dev(self):
+        p = _vp()
+        self._ck(self._L.tb_export_positions_f32_dev(self._h, C.byref(p)))
+        return p.value

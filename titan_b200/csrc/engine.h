@@ -1,0 +1,113 @@
+// engine.h -- internal state of one tb_engine (one CUDA device, one stream).
+//
+// Data layout in HBM ("canonical" state, API mass/spring order), all fp64 structure-of-arrays:
+//   pos[2], vel[2]   : ping-pong buffers, each 3 planes of nm doubles (x[], y[], z[])
+//   acc              : 3 planes, written by the last step of every run
+//   ext              : 3 planes, allocated only once a non-zero external force is uploaded
+//   m, flags, drag   : per-mass scalars (flags: bit0 fixed, bit1 valid, bit2 has local constraints)
+//   left,right,k,rest,damping,type,omega,l_max,l_min,rate : per-spring arrays
+//   row_ptr, adj     : CSR incidence; adj = 2*spring + (1 if this mass is the spring's right endpoint),
+//                      rows in ascending spring order, right entry before left entry for self-loops
+// This replaces the reference's one-cudaMalloc-per-object AoS + pointer tables
+// (include/Titan/mass.h:89-126, spring.h:77-97, src/sim.cu:940-1025).
+#pragma once
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "physics.cuh"
+
+namespace tb {
+
+enum : uint8_t { F_FIXED = 1, F_VALID = 2, F_LOCAL = 4 };
+
+struct DtSegment { int64_t first_step; double dt; };
+
+struct TiledState;  // tiled.cu
+
+struct Engine {
+    int device = 0;
+    uint32_t flags = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string err;
+    int sm_count = 0;
+
+    int64_t nm = 0, ns = 0;
+    // device state
+    double *pos[2] = {nullptr, nullptr}, *vel[2] = {nullptr, nullptr};
+    double *acc = nullptr, *ext = nullptr, *m = nullptr;
+    uint8_t *mflags = nullptr;
+    int32_t *drag = nullptr;
+    int32_t *left = nullptr, *right = nullptr, *type = nullptr;
+    double *k = nullptr, *rest = nullptr, *damping = nullptr, *omega = nullptr, *l_max = nullptr,
+           *l_min = nullptr, *rate = nullptr;
+    int32_t *row_ptr = nullptr, *adj = nullptr;
+    int32_t *lc_ptr = nullptr;
+    tb_local *lc = nullptr;
+    tb_plane *more_planes = nullptr;
+    tb_ball *more_balls = nullptr;
+    double *t_dev = nullptr;       // [2] simulation time, ping-pong with the step parity
+    float *export_f32 = nullptr;
+    int cur = 0;                   // which pos/vel buffer holds the current state
+
+    // host-side knowledge
+    Globals G{};
+    std::vector<tb_plane> planes;
+    std::vector<tb_ball> balls;
+    std::vector<uint8_t> h_flags;  // mirror of mflags
+    std::vector<double> h_T0;      // per-mass T at its last upload
+    std::vector<int64_t> h_n0;     // steps_done at that upload
+    std::vector<DtSegment> dt_log;
+    int64_t steps_done = 0;
+    bool ext_pending = false;      // a non-zero extern force waits for the next step
+    bool any_damping = false, any_active = false, any_actuated = false, any_local = false, any_magnet = false;
+    bool any_fixed_or_invalid = false;
+    double last_run_ms = 0.0;
+    int64_t launches = 0;
+    int64_t device_bytes = 0;
+
+    // CUDA-graph cache for multi-step batches (one per parity)
+    cudaGraphExec_t graph[2] = {nullptr, nullptr};
+    int graph_steps = 0;
+    bool graph_dirty = true;
+
+    // staging
+    void *stage_dev = nullptr; size_t stage_dev_bytes = 0;
+    void *stage_host = nullptr; size_t stage_host_bytes = 0;   // pinned
+
+    std::vector<void *> pinned;    // tb_alloc_host allocations
+
+    TiledState *tiled = nullptr;
+    bool tiled_stale = true;       // tiled layout must be rebuilt from canonical state
+    bool canon_stale = false;      // canonical pos/vel must be refreshed from the tiled layout
+};
+
+// error plumbing: store message, return status
+int fail(Engine *e, int status, const char *fmt, ...);
+#define TB_CUDA(e, call)                                                                         \
+    do {                                                                                         \
+        cudaError_t _err = (call);                                                               \
+        if (_err != cudaSuccess)                                                                 \
+            return tb::fail((e), TB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_err), \
+                            __FILE__, __LINE__);                                                 \
+    } while (0)
+
+template <class T> int dev_alloc(Engine *e, T **p, size_t count);
+void dev_free(Engine *e, void *p, size_t bytes);
+
+// csr_step.cu
+int launch_csr_step(Engine *e, bool use_ext, bool write_acc);
+// tiled.cu
+int tiled_prepare(Engine *e);                    // (re)build tiles if stale
+int launch_tiled_step(Engine *e, bool use_ext, bool write_acc);
+int tiled_to_canonical(Engine *e);               // refresh canonical pos/vel from tiles
+void tiled_destroy(Engine *e);
+bool tiled_supported(const Engine *e);
+
+}  // namespace tb
+
+struct tb_engine : tb::Engine {};

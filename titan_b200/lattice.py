@@ -1,0 +1,85 @@
+"""Direct-to-array lattice builder (no per-object host handles).
+
+Emits masses and springs in exactly the order of the reference's `Lattice::Lattice`
+(src/object.cu:235-296): mass index k + j*nz + i*ny*nz with i outermost; per cell (i, j, k) the seven
+(l, m, n) != 0 neighbours in l, m, n order, then the yz / xz anti-diagonals, the three remaining body
+diagonals, and finally the xy anti-diagonal; rest length = initial distance (:293-295).  Used by bench.py and
+the multi-GPU partitioner, where 27 M `Mass` objects on the host would cost ~40 GB (SURVEY.md hard parts).
+tests/test_lattice_builder.py checks it bit for bit against the oracle and the reference's own builder.
+"""
+import numpy as np
+
+# (left offset, right offset) in (i, j, k); a spring exists when both endpoints are inside the grid
+_SLOTS = [((0, 0, 0), (0, 0, 1)), ((0, 0, 0), (0, 1, 0)), ((0, 0, 0), (0, 1, 1)), ((0, 0, 0), (1, 0, 0)),
+          ((0, 0, 0), (1, 0, 1)), ((0, 0, 0), (1, 1, 0)), ((0, 0, 0), (1, 1, 1)),
+          ((0, 0, 1), (0, 1, 0)), ((0, 0, 1), (1, 0, 0)), ((0, 0, 1), (1, 1, 0)),
+          ((1, 0, 1), (0, 1, 0)), ((0, 1, 1), (1, 0, 0)), ((0, 1, 0), (1, 0, 0))]
+
+
+def lattice_counts(nx, ny, nz):
+    a, b, c = int(nx), int(ny), int(nz)
+    nm = a * b * c
+    ns = ((a - 1) * b * c + a * (b - 1) * c + a * b * (c - 1)
+          + 2 * ((a - 1) * (b - 1) * c + (a - 1) * b * (c - 1) + a * (b - 1) * (c - 1))
+          + 4 * (a - 1) * (b - 1) * (c - 1))
+    return nm, ns
+
+
+def lattice_positions(center, dims, nx, ny, nz):
+    def axis(n, d, c):
+        u = (np.arange(n, dtype=np.float64) / (n - 1.0) - 0.5) if n > 1 else np.zeros(1)
+        return u * d + c
+    x, y, z = (axis(n, float(d), float(c)) for n, d, c in zip((nx, ny, nz), dims, center))
+    pos = np.empty((nx, ny, nz, 3))
+    pos[..., 0] = x[:, None, None]
+    pos[..., 1] = y[None, :, None]
+    pos[..., 2] = z[None, None, :]
+    return pos.reshape(-1, 3)
+
+
+def lattice_springs(nx, ny, nz, i_planes_per_chunk=8):
+    """left[ns], right[ns] (int32) in reference emission order."""
+    nm, ns = lattice_counts(nx, ny, nz)
+    left = np.empty(ns, dtype=np.int32)
+    right = np.empty(ns, dtype=np.int32)
+    out = 0
+    dims = np.array([nx, ny, nz])
+    stride = np.array([ny * nz, nz, 1], dtype=np.int64)
+    for i0 in range(0, nx, i_planes_per_chunk):
+        i1 = min(nx, i0 + i_planes_per_chunk)
+        ii, jj, kk = np.meshgrid(np.arange(i0, i1), np.arange(ny), np.arange(nz), indexing="ij")
+        cell = np.stack([ii.ravel(), jj.ravel(), kk.ravel()], axis=1).astype(np.int64)
+        ncell = cell.shape[0]
+        L = np.empty((ncell, 13), dtype=np.int32)
+        R = np.empty((ncell, 13), dtype=np.int32)
+        ok = np.empty((ncell, 13), dtype=bool)
+        for s, (lo, ro) in enumerate(_SLOTS):
+            a = cell + np.array(lo)
+            b = cell + np.array(ro)
+            ok[:, s] = ((a < dims).all(axis=1)) & ((b < dims).all(axis=1))
+            L[:, s] = (a @ stride).astype(np.int32)
+            R[:, s] = (b @ stride).astype(np.int32)
+        n = int(ok.sum())
+        left[out:out + n] = L[ok]
+        right[out:out + n] = R[ok]
+        out += n
+    assert out == ns
+    return left, right
+
+
+def rest_lengths(pos, left, right):
+    """Vec::norm of (right.pos - left.pos): sqrt((dx*dx + dy*dy) + dz*dz), include/Titan/vec.h:149-151."""
+    d = pos[right] - pos[left]
+    return np.sqrt((d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1]) + d[:, 2] * d[:, 2])
+
+
+def build_lattice(center, dims, nx, ny, nz):
+    pos = lattice_positions(center, dims, nx, ny, nz)
+    left, right = lattice_springs(nx, ny, nz)
+    if left.size <= 50_000_000:
+        rest = rest_lengths(pos, left, right)
+    else:
+        rest = np.empty(left.size)
+        for a in range(0, left.size, 20_000_000):
+            rest[a:a + 20_000_000] = rest_lengths(pos, left[a:a + 20_000_000], right[a:a + 20_000_000])
+    return dict(pos=pos, left=left, right=right, rest=rest)
