@@ -3,7 +3,7 @@
 Tolerances (BASELINE.json north_star: <= 1e-9 relative per step in fp64; indexing bit-exact):
   * TB_MATH_STRICT: bit-identical to the oracle for every scenario without sin() actuation; with actuation the
     device sin() may differ from glibc's by 1 ulp, so <= 1e-13 relative after the test's step count.
-  * TB_MATH_FAST (what bench.py times): <= 1e-12 relative after 1 step, <= 1e-9 after 100 steps.
+  * TB_MATH_FAST (what bench.py times): pos/vel <= 1e-12 relative after 1 step, <= 1e-9 after 100 steps.
 Relative error is max|a-b| / max(1, max|b|) per field.
 """
 import numpy as np
