@@ -317,13 +317,16 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
     }
     // CSR incidence: ascending spring index per mass; right entry before left entry (the reference adds to
     // the right endpoint first, src/sim.cu:1187-1193)
-    std::vector<int32_t> ptr((size_t)nm + 1, 0);
+    e->h_left.assign(left, left + ns); e->h_right.assign(right, right + ns);
+    std::vector<int32_t> &ptr = e->h_row_ptr;
+    ptr.assign((size_t)nm + 1, 0);
     for (int64_t s = 0; s < ns; s++) {
         if (left[s] < 0 || right[s] < 0) continue;
         ptr[(size_t)right[s] + 1]++; ptr[(size_t)left[s] + 1]++;
     }
     for (int64_t i = 0; i < nm; i++) ptr[(size_t)i + 1] += ptr[(size_t)i];
-    std::vector<int32_t> adj((size_t)std::max<int64_t>(1, ptr[(size_t)nm]));
+    std::vector<int32_t> &adj = e->h_adj;
+    adj.assign((size_t)std::max<int64_t>(1, ptr[(size_t)nm]), 0);
     {
         std::vector<int32_t> cursor(ptr.begin(), ptr.end() - 1);
         for (int64_t s = 0; s < ns; s++) {
@@ -341,7 +344,8 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
     e->cur = 0;
     e->ext_pending = false;
     e->any_damping = e->any_active = e->any_actuated = e->any_local = e->any_magnet = e->any_fixed_or_invalid = false;
-    e->graph_dirty = true; e->tiled_stale = true; e->canon_stale = false;
+    e->graph_dirty = true; e->tiled_stale = 0xf; e->canon_stale = false; e->tile_hint.clear();
+    e->h_type.assign((size_t)ns, 0);
     return TB_OK;
 }
 
@@ -377,13 +381,13 @@ int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
         }
         if (e->drag) TB_TRY(up_scalar<int32_t>(e, e->drag, drag, idx, first, count));
     }
-    bool flags_changed = false;
+    bool flags_changed = false, valid_changed = false;
     for (int64_t j = 0; j < count; j++) {
         int64_t i = idx ? idx[j] : first + j;
         uint8_t f = e->h_flags[(size_t)i], nf = f;
         if (fixed) nf = (uint8_t)((nf & ~F_FIXED) | (fixed[j] ? F_FIXED : 0));
         if (valid) nf = (uint8_t)((nf & ~F_VALID) | (valid[j] ? F_VALID : 0));
-        if (nf != f) { e->h_flags[(size_t)i] = nf; flags_changed = true; }
+        if (nf != f) { e->h_flags[(size_t)i] = nf; flags_changed = true; valid_changed |= ((nf ^ f) & F_VALID) != 0; }
         if (T) { e->h_T0[(size_t)i] = T[j]; e->h_n0[(size_t)i] = e->steps_done; }
         else if (nf != f) {
             // fixed/valid status changes: freeze the T accumulated so far (under the OLD flags) and restart
@@ -397,7 +401,9 @@ int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
         e->any_fixed_or_invalid = false;
         for (uint8_t f : e->h_flags) if ((f & F_FIXED) || !(f & F_VALID)) { e->any_fixed_or_invalid = true; break; }
     }
-    e->tiled_stale = true;
+    if (pos || vel || m) e->tiled_stale |= TS_STATE;
+    if (flags_changed) e->tiled_stale |= TS_FLAGS | (valid_changed ? TS_STRUCT : 0u);
+    if (flags_changed || drag) e->graph_dirty = true;
     return TB_OK;
 }
 
@@ -467,9 +473,11 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
         for (int64_t j = 0; j < count; j++) {
             if (type[j] < 0 || type[j] > 5) return fail(e, TB_ERR_INVALID, "tb_set_spring_params: bad SpringType %d", type[j]);
             nonpassive |= type[j] >= 2;
-            if (type[j] == 2 || type[j] == 3) e->any_active = true;
-            if (type[j] >= 4) e->any_actuated = true;
         }
+        if (e->h_type.size() != (size_t)e->ns) e->h_type.assign((size_t)e->ns, 0);
+        for (int64_t j = 0; j < count; j++) e->h_type[(size_t)(idx ? idx[j] : first + j)] = (uint8_t)type[j];
+        e->any_active = e->any_actuated = false;
+        for (uint8_t ty : e->h_type) { if (ty == 2 || ty == 3) e->any_active = true; if (ty >= 4) e->any_actuated = true; }
         if (e->type || nonpassive) {
             TB_TRY(ensure_spring_array<int32_t>(e, &e->type, 0));
             TB_TRY(up_scalar<int32_t>(e, e->type, type, idx, first, count));
@@ -482,7 +490,8 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
         TB_TRY(ensure_spring_array<double>(e, o.dst, 0.0));
         TB_TRY(up_scalar<double>(e, *o.dst, o.src, idx, first, count));
     }
-    e->tiled_stale = true;
+    e->tiled_stale |= TS_PARAMS | (type ? TS_STRUCT : 0u);
+    e->graph_dirty = true;
     return TB_OK;
 }
 
@@ -561,7 +570,7 @@ int tb_set_local_constraints(tb_engine *e, const int64_t *row_ptr, const tb_loca
         if (nf != f) { e->h_flags[(size_t)i] = nf; changed = true; }
     }
     if (changed) TB_CUDA(e, cudaMemcpy(e->mflags, e->h_flags.data(), (size_t)e->nm, cudaMemcpyHostToDevice));
-    e->graph_dirty = true; e->tiled_stale = true;
+    e->graph_dirty = true; e->tiled_stale |= TS_FLAGS;
     return TB_OK;
 }
 
@@ -652,7 +661,8 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     if (nsteps < 0) return fail(e, TB_ERR_INVALID, "tb_run_async: negative step count");
     if (e->any_magnet) return fail(e, TB_ERR_UNSUPPORTED, "magnetic masses (rad > 0 or max_mag_force != 0) need the occupancy-grid pass, which is not built (SURVEY.md row N2)");
     if (nsteps == 0) return TB_OK;
-    if (use_tiled(e)) TB_TRY(tiled_prepare(e));
+    if (use_tiled(e)) TB_TRY(tiled_prepare(e));       // may discover that the graph does not fit the tiled format
+    if (!use_tiled(e) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
     TB_CUDA(e, cudaEventRecord(e->ev0, e->stream));
     set_t_kernel<<<1, 1, 0, e->stream>>>(e->t_dev + e->cur, t0);
     int64_t left_steps = nsteps;
@@ -711,6 +721,7 @@ int tb_get_info(tb_engine *e, tb_info *info) {
     memset(info, 0, sizeof *info);
     info->nm = e->nm; info->ns = e->ns;
     info->kernel = use_tiled(e) ? 1 : 0;
+    tiled_info(e, &info->n_tiles);
     info->launches = e->launches;
     info->device_bytes = e->device_bytes;
     // 104 B per mass (read pos,vel,m; write pos,vel) + per spring 24 B (+8 damping, +12 actuated)

@@ -23,6 +23,8 @@
 namespace tb {
 
 enum : uint8_t { F_FIXED = 1, F_VALID = 2, F_LOCAL = 4 };
+// what a setter invalidated in the tiled layout: structure (tiles/ELL), spring parameters, mass state, mass flags
+enum : uint32_t { TS_STRUCT = 1, TS_PARAMS = 2, TS_STATE = 4, TS_FLAGS = 8 };
 
 struct DtSegment { int64_t first_step; double dt; };
 
@@ -59,6 +61,8 @@ struct Engine {
     std::vector<tb_plane> planes;
     std::vector<tb_ball> balls;
     std::vector<uint8_t> h_flags;  // mirror of mflags
+    std::vector<uint8_t> h_type;   // mirror of the spring types
+    std::vector<int32_t> h_left, h_right, h_row_ptr, h_adj;  // host copy of the topology + CSR (tile builder)
     std::vector<double> h_T0;      // per-mass T at its last upload
     std::vector<int64_t> h_n0;     // steps_done at that upload
     std::vector<DtSegment> dt_log;
@@ -82,8 +86,9 @@ struct Engine {
     std::vector<void *> pinned;    // tb_alloc_host allocations
 
     TiledState *tiled = nullptr;
-    bool tiled_stale = true;       // tiled layout must be rebuilt from canonical state
+    uint32_t tiled_stale = 0xf;    // TS_* bits: which parts of the tiled layout must be refreshed
     bool canon_stale = false;      // canonical pos/vel must be refreshed from the tiled layout
+    std::vector<int32_t> tile_hint; // optional caller-supplied tile id per mass (tb_set_tile_hint)
 };
 
 // error plumbing: store message, return status
@@ -107,6 +112,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc);
 int tiled_to_canonical(Engine *e);               // refresh canonical pos/vel from tiles
 void tiled_destroy(Engine *e);
 bool tiled_supported(const Engine *e);
+int tiled_info(const Engine *e, int32_t *n_tiles);
 
 }  // namespace tb
 
