@@ -47,6 +47,7 @@ def workload_c2(n=100):
     side = 0.1 * (n - 1)
     L = lattice.build_lattice((0.0, 0.0, side / 2 - 0.001), (side, side, side), n, n, n)
     L["plane"] = ((0.0, 0.0, 1.0), 0.0, 0.5, 0.6)
+    L["tile_hint"] = lattice.brick_hint(n, n, n)
     L["name"] = "C2: %d^3 lattice on frictional plane (k=1e4, m=0.1, dt=1e-4, g=-9.81)" % n
     return L
 
@@ -165,6 +166,7 @@ def main():
     ap.add_argument("--csr", action="store_true", help="force the generic CSR kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-hint", action="store_true", help="let the engine bisect positions instead of lattice bricks")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -200,6 +202,8 @@ def main():
     flags = (tb.MATH_STRICT if args.strict else tb.MATH_FAST) | (tb.KERNEL_CSR if args.csr else 0)
     eng = tb.Engine(local_rank, flags)
     eng.set_topology(nm, W["left"], W["right"])
+    if not args.no_hint:
+        eng.set_tile_hint(W["tile_hint"])     # what Lattice builders pass: bricks of lattice cells
     eng.set_mass_state(pos=W["pos"])
     eng.set_spring_params(rest=W["rest"])
     n, off, fk, fs = W["plane"]
@@ -279,7 +283,9 @@ def main():
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": W["name"], "masses": nm, "springs": ns, "sim_steps_per_bench_step": inner,
-                           "math": "strict" if args.strict else "fast", "per_rank": "independent copy of the workload",
+                           "math": "strict" if args.strict else "fast",
+                           "tiling": {k: info[k] for k in ("n_tiles", "threads_per_mass", "grid", "smem_bytes",
+                                                           "ell_unique_tiles", "tiled_bytes_per_step")}, "per_rank": "independent copy of the workload",
                            "l2": "working set per step (%.0f MB) exceeds the 126 MB L2" % (info["algorithmic_bytes_per_step"] / 1e6),
                            "timing": "CUDA events on the engine stream, max over ranks", "wall_ms": wall * 1e3},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),

@@ -82,6 +82,12 @@ TB_API const char *tb_last_error(const tb_engine *e); /* replaces gpuErrchk's fp
  * src/sim.cu:1163).  The engine derives the CSR incidence (ascending spring index per mass) on upload.
  * State and parameters are reset to defaults (m=0.1, k=10000, valid, not fixed, PASSIVE_SOFT, ...). */
 TB_API int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, const int32_t *right);
+/* Optional: tile id per mass (nm entries; NULL clears).  Masses sharing an id are kept together in one tile
+ * of the step kernel (split when more than 128 share one); ids order the tiles.  Builders that know the geometry
+ * (Lattice::Lattice, src/object.cu:235-296 -> bricks of lattice cells) pass it so that congruent bricks share
+ * their incidence tables; without a hint the engine bisects the current positions.  Results do not depend on it
+ * beyond the summation order of TB_MATH_FAST (TB_MATH_STRICT is bit-identical for any tiling). */
+TB_API int tb_set_tile_hint(tb_engine *e, const int32_t *tile_of_mass);
 
 /* ---- mass state: CUDA_MASS(Mass&) src/mass.cu:74-100, Simulation::set/setAll src/sim.cu:603-765 -------- */
 /* idx == NULL: masses [first, first+count); otherwise the `count` masses listed in idx (container upload). */
@@ -135,6 +141,11 @@ typedef struct {
     double algorithmic_bytes_per_step; /* nm*104 + ns*B_s */
     int32_t sm_count;
     int32_t graph_steps;         /* steps per CUDA-Graph launch (0 = no graph) */
+    int32_t threads_per_mass;    /* tiled kernel: threads sharing one mass's incident springs */
+    int32_t grid;                /* tiled kernel: persistent CTAs of the last launch */
+    int32_t smem_bytes;          /* tiled kernel: dynamic shared memory per CTA */
+    int32_t ell_unique_tiles;    /* tiled kernel: distinct incidence (ELL) blocks after content dedupe */
+    int64_t tiled_bytes_per_step;/* tiled kernel: bytes one step streams from its tables (blob+state+halo+ELL+meta) */
 } tb_info;
 TB_API int tb_get_info(tb_engine *e, tb_info *info);
 /* headless position export, fp64 -> packed fp32 xyz (updateVertices, src/sim.cu:1944-1952); out is a

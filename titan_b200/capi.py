@@ -16,7 +16,7 @@ PASSIVE_SOFT, PASSIVE_STIFF, ACTIVE_CONTRACT_THEN_EXPAND, ACTIVE_EXPAND_THEN_CON
     ACTUATED_CONTRACT = range(6)
 CONSTRAINT_PLANE, CONTACT_PLANE, BALL, DIRECTION = range(4)
 
-EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_last_error", "tb_set_topology",
+EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_last_error", "tb_set_topology", "tb_set_tile_hint",
            "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
            "tb_get_spring_rest", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
            "tb_run_async", "tb_sync", "tb_steps_done", "tb_last_run_ms", "tb_get_info",
@@ -39,7 +39,9 @@ class Local(C.Structure):
 class Info(C.Structure):
     _fields_ = [("nm", C.c_int64), ("ns", C.c_int64), ("kernel", C.c_int32), ("n_tiles", C.c_int32),
                 ("launches", C.c_int64), ("device_bytes", C.c_int64), ("algorithmic_bytes_per_step", C.c_double),
-                ("sm_count", C.c_int32), ("graph_steps", C.c_int32)]
+                ("sm_count", C.c_int32), ("graph_steps", C.c_int32), ("threads_per_mass", C.c_int32),
+                ("grid", C.c_int32), ("smem_bytes", C.c_int32), ("ell_unique_tiles", C.c_int32),
+                ("tiled_bytes_per_step", C.c_int64)]
 
 
 class TitanError(RuntimeError):
@@ -66,6 +68,7 @@ def lib():
         L.tb_destroy.argtypes = [_vp]
         L.tb_destroy.restype = None
         L.tb_set_topology.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp]
+        L.tb_set_tile_hint.argtypes = [_vp, _vp]
         L.tb_set_mass_state.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 9
         L.tb_set_mass_magnet.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 5
         L.tb_get_mass_state.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 6
@@ -133,6 +136,13 @@ class Engine:
         ns = 0 if l is None else l.shape[0]
         self._ck(self._L.tb_set_topology(self._h, int(nm), int(ns), lp, rp))
         self.nm, self.ns = int(nm), int(ns)
+
+    def set_tile_hint(self, tile_of_mass):
+        if tile_of_mass is None:
+            self._ck(self._L.tb_set_tile_hint(self._h, None))
+            return
+        a, ap = _arr(tile_of_mass, np.int32, (self.nm,))
+        self._ck(self._L.tb_set_tile_hint(self._h, ap))
 
     def _sel(self, n_total, first, count, idx):
         if idx is not None:

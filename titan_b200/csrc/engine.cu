@@ -349,6 +349,17 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
     return TB_OK;
 }
 
+int tb_set_tile_hint(tb_engine *e, const int32_t *tile_of_mass) {
+    E_CHECK(e);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_set_tile_hint before tb_set_topology");
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (tile_of_mass) e->tile_hint.assign(tile_of_mass, tile_of_mass + e->nm);
+    else e->tile_hint.clear();
+    e->tiled_stale |= TS_STRUCT;
+    e->graph_dirty = true;
+    return TB_OK;
+}
+
 static bool any_nonzero(const double *a, int64_t n) { for (int64_t i = 0; i < n; i++) if (a[i] != 0.0) return true; return false; }
 
 int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, const double *pos,
@@ -721,7 +732,6 @@ int tb_get_info(tb_engine *e, tb_info *info) {
     memset(info, 0, sizeof *info);
     info->nm = e->nm; info->ns = e->ns;
     info->kernel = use_tiled(e) ? 1 : 0;
-    tiled_info(e, &info->n_tiles);
     info->launches = e->launches;
     info->device_bytes = e->device_bytes;
     // 104 B per mass (read pos,vel,m; write pos,vel) + per spring 24 B (+8 damping, +12 actuated)
@@ -729,6 +739,7 @@ int tb_get_info(tb_engine *e, tb_info *info) {
     info->algorithmic_bytes_per_step = 104.0 * (double)e->nm + bs * (double)e->ns;
     info->sm_count = e->sm_count;
     info->graph_steps = (e->flags & TB_NO_GRAPH) ? 0 : GRAPH_STEPS;
+    tiled_info(e, info);
     return TB_OK;
 }
 

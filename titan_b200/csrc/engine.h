@@ -112,7 +112,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc);
 int tiled_to_canonical(Engine *e);               // refresh canonical pos/vel from tiles
 void tiled_destroy(Engine *e);
 bool tiled_supported(const Engine *e);
-int tiled_info(const Engine *e, int32_t *n_tiles);
+int tiled_info(const Engine *e, tb_info *info);
 
 }  // namespace tb
 

@@ -1,65 +1,111 @@
-// tiled.cu -- the fast-path step kernel: one CTA per TILE of masses, everything a tile needs staged in
-// shared memory, forces gathered per mass in ascending spring order in registers (deterministic), the
-// whole mass update fused behind it.  One launch == one time step (Jacobi ping-pong, as csr_step.cu).
+// tiled.cu -- the fast-path step kernel: PERSISTENT CTAs stream TILES of masses through a double-buffered
+// shared-memory pipeline fed by bulk async copies (cp.async.bulk + mbarrier, SASS UBLKCP) and per-element
+// cp.async gathers (LDGSTS) for the halo, so the next tile's bytes are in flight while this tile computes.
+// One launch == one time step (Jacobi ping-pong between two state buffers, like csr_step.cu), many launches
+// per CUDA graph.  Replaces computeSpringForces + massForcesAndUpdate, src/sim.cu:1157-1200,1285-1367.
 //
-// Layout in HBM (built once per topology by the host tile builder below, refreshed by small gather kernels
-// when only parameters / state change):
-//   masses are re-ordered tile-major: slot = tile*TM + t.  Tiles come from a recursive coordinate bisection of
-//   the current positions (bricks for lattices), or from a caller hint (tb_set_tile_hint).
-//   pos[2], vel[2] : 3 planes of n_slots doubles, ping-pong           m, flags : per slot
-//   per tile:  halo[]  : slots of the foreign masses its springs reach (gathered into smem every step)
-//              prm[]   : (k, rest) pairs of every spring touching the tile, one record per spring and tile,
-//                        contiguous -> streamed into smem with one bulk copy; [dmp[], omg[] when present]
-//              ell[]   : per own mass, one u32 per incident spring in ascending spring order (ELL, TM-strided
-//                        so a warp reads consecutive words): neighbour's local index | record slot | side | type
-// Per spring this reads 16 B of parameters (+ a second copy for springs cut by a tile face) and 2 x 4 B of
-// ELL entries, against the algorithmic 24 B; endpoint gathers hit shared memory.
-// Replaces computeSpringForces + massForcesAndUpdate, src/sim.cu:1157-1200,1285-1367.
+// Layout in HBM (built per topology by the host tile builder below; refreshed by small kernels when only
+// parameters / state / flags change):
+//   masses are re-ordered tile-major: slot = tile*TM + t.  Tiles come from the caller's hint (lattice bricks,
+//   tb_set_tile_hint) or from a recursive coordinate bisection of the current positions.
+//   state[2]  : per tile one contiguous block [px py pz vx vy vz][TM] of doubles, ping-pong
+//   blob      : per tile one contiguous block  header | flags[TM] | m[TM] | (k,rest)[n_rec] | dmp[] | omg[]
+//               -- one record per spring touching the tile -- fetched with ONE bulk copy
+//   halo      : per tile the state indices of the foreign masses its springs reach (bulk-copied two tiles
+//               ahead, then used as the address list of the cp.async position gather one tile ahead)
+//   ell       : per tile, per own mass, one u32 per incident spring in ascending spring order (ELL, TM-strided
+//               so a warp reads consecutive words): neighbour's local index | record slot | side | type.
+//               Identical blocks are stored once (content dedupe): congruent lattice bricks share their ELL
+//               block, which then stays L2-resident instead of costing 8 B per spring of HBM traffic.
+//   meta      : 32 B per tile (offsets and counts), prefetched through a small shared-memory ring
+// Forces are gathered per mass in registers; with TPM threads per mass each thread takes every TPM-th ELL row
+// and the partial sums are combined in a fixed order (deterministic).  TPM == 1 reproduces the oracle's
+// ascending-spring-index summation exactly (TB_MATH_STRICT).
 #include "engine.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
+#include <map>
 #include <numeric>
 
 namespace tb {
 
 #define TB_TRY(x) do { int _rc = (x); if (_rc != TB_OK) return _rc; } while (0)
 
-constexpr int TM = 128;                 // masses (threads) per tile
-constexpr int ELL_NB_BITS = 11;         // neighbour local index  (own: 0..TM-1, halo: TM..)
-constexpr int ELL_REC_BITS = 15;        // record slot in the tile's parameter arrays
-constexpr uint32_t ELL_SIDE = 1u << 26; // this mass is the spring's RIGHT endpoint
-constexpr int ELL_TYPE_SHIFT = 27;      // 0 passive, 1 contract-then-expand, 2 expand-then-contract
-constexpr uint32_t ELL_VALID = 1u << 31;
+constexpr int TM = 128;                 // masses per tile
+// ELL word: bits 3..11 neighbour local index (so `word & 0xff8` is its byte offset in a position array; own
+// masses 0..TM-1, halo TM..), bits 16..27 record slot (`(word >> 12) & 0xfff0` = byte offset of the (k,rest)
+// record), bits 28..29 actuation (0 passive, 1 contract-then-expand, 2 expand-then-contract), bit 30 this mass
+// is the spring's RIGHT endpoint, bit 31 valid.
+constexpr int ELL_NB_SHIFT = 3, ELL_REC_SHIFT = 16, ELL_TYPE_SHIFT = 28;
+constexpr uint32_t ELL_SIDE = 1u << 30, ELL_VALID = 1u << 31;
 constexpr int MAX_DEG = 32;             // ELL rows are held in registers; more incident springs -> CSR kernel
-constexpr int MAX_LOCAL = 1 << ELL_NB_BITS;
-constexpr int MAX_REC = 1 << ELL_REC_BITS;
-constexpr size_t SMEM_BUDGET = 100 * 1024;
+constexpr int MAX_LOCAL = 512;
+constexpr int MAX_REC = 4096;
+constexpr int ELL_CHUNK = 4;            // springs evaluated together, branch-free, by one thread (ILP)
 
-struct TileMeta {
-    int32_t ell_off;    // first ELL word of this tile (deg * TM words follow)
-    int32_t deg;        // ELL rows
-    int32_t halo_off, n_halo;
-    int32_t rec_off, n_rec;   // rec_off is a multiple of 8 records (128 B)
+// Which of a mass's TPM threads takes which ELL rows, in chunks of ELL_CHUNK rows (blocks are padded with zero
+// rows to a whole number of chunks).  Thread 0 also runs the mass update (worth about MASS_UPDATE_ROWS springs),
+// so it takes fewer chunks: chunks [0, c0) go to thread 0, the rest in equal contiguous runs to threads 1..TPM-1.
+constexpr int MASS_UPDATE_ROWS = 5;
+__host__ __device__ constexpr int ell_chunks(int deg) { return (deg + ELL_CHUNK - 1) / ELL_CHUNK; }
+__host__ __device__ constexpr int ell_chunks0(int n, int tpm) {          // chunks of thread 0 out of n
+    if (tpm == 1) return n;
+    int r0 = (n * ELL_CHUNK + MASS_UPDATE_ROWS) / tpm - MASS_UPDATE_ROWS;
+    int c0 = r0 > 0 ? (r0 + ELL_CHUNK / 2) / ELL_CHUNK : 0;
+    return c0 < n ? c0 : n;
+}
+__host__ __device__ constexpr int ell_chunks_q(int n, int tpm) {         // chunks per thread 1..TPM-1
+    return tpm == 1 ? 0 : (n - ell_chunks0(n, tpm) + tpm - 2) / (tpm - 1);
+}
+__host__ __device__ constexpr int ell_words_per_thread(int tpm) {
+    int m = 0;
+    for (int n = 0; n <= ell_chunks(MAX_DEG); n++) {
+        int a = ell_chunks0(n, tpm), b = ell_chunks_q(n, tpm);
+        if (a > m) m = a;
+        if (b > m) m = b;
+    }
+    return m * ELL_CHUNK;
+}
+constexpr size_t SMEM_LIMIT = 227 * 1024;
+constexpr int HALO_RING = 3;
+constexpr int BLOB_HDR = 16, BLOB_FLAGS = BLOB_HDR, BLOB_M = BLOB_FLAGS + TM, BLOB_REC = BLOB_M + TM * 8;
+constexpr int STATE_BLOCK = 6 * TM;     // doubles per tile in a state buffer
+
+struct __align__(16) TileMeta {
+    uint32_t blob_off16;  // blob offset in 16-byte units
+    uint32_t blob_bytes;  // multiple of 16
+    uint32_t halo_off;    // first halo entry (multiple of 4 entries)
+    uint32_t n_halo;
+    uint32_t ell_off;     // first ELL word (deg rounded up to ELL_CHUNK rows, TM words each)
+    uint32_t deg;         // ELL rows
+    uint32_t n_rec;       // spring records in the blob
+    uint32_t rec_off;     // first entry of rec_spring (refresh kernels only)
 };
+static_assert(sizeof(TileMeta) == 32, "TileMeta is copied as two 16-byte words");
 
 struct TiledState {
     int64_t n_tiles = 0, n_slots = 0, n_rec = 0, n_ell = 0, n_halo = 0;
-    int max_halo = 0, max_rec = 0, max_deg = 0;
+    size_t blob_bytes = 0;
+    int max_halo = 0, max_rec = 0, max_deg = 0, max_blob = 0;
+    int64_t ell_unique_tiles = 0;
+    bool has_damping = false, has_active = false, stage_vel = false;
+    int tpm = 4, grid = 0;
     size_t smem_bytes = 0;
-    bool has_damping = false, has_active = false;
     // device
-    double *pos[2] = {nullptr, nullptr}, *vel[2] = {nullptr, nullptr}, *m = nullptr;
-    uint8_t *flags = nullptr;
+    double *st[2] = {nullptr, nullptr};   // tile-blocked state, ping-pong
+    uint8_t *blob = nullptr;
     int32_t *slot_to_api = nullptr, *halo = nullptr, *rec_spring = nullptr;
     uint32_t *ell = nullptr;
-    double *prm = nullptr, *dmp = nullptr, *omg = nullptr;   // prm: 2 doubles per record
     TileMeta *meta = nullptr;
     // host
     std::vector<int32_t> h_slot_to_api, h_api_to_slot;
-    bool supported_checked = false, supported = false;
+    bool supported = false;
     std::string why_not;
 };
+
+static inline size_t up16(size_t x) { return (x + 15) & ~(size_t)15; }
 
 // ---------------------------------------------------------------- tile assignment (host) -----------------
 // Recursive coordinate bisection: split the mass set at a multiple of TM along its longest axis until one
@@ -86,8 +132,8 @@ static void rcb(std::vector<int32_t> &order, const double *pos, int64_t nm, int6
     rcb(order, pos, nm, mid, hi, tiles - left_tiles);
 }
 
-// Fills slot_to_api (n_tiles*TM entries, -1 = padding slot) from an RCB of the current positions (SoA, 3 planes
-// of nm) or from the caller's hint.  Inside a tile masses are sorted by API index.
+// Fills slot_to_api (n_tiles*TM entries, -1 = padding slot) from the caller's hint or from an RCB of the
+// current positions (SoA, 3 planes of nm).  Inside a tile masses are sorted by API index.
 static void assign_tiles(Engine *e, const std::vector<double> &pos_soa, std::vector<int32_t> &slot_to_api) {
     int64_t nm = e->nm;
     std::vector<int32_t> order((size_t)nm);
@@ -113,6 +159,33 @@ static void assign_tiles(Engine *e, const std::vector<double> &pos_soa, std::vec
     slot_to_api.resize((size_t)(tiles * TM), -1);
 }
 
+// ---------------------------------------------------------------- shared-memory plan -----------------------
+struct SmemPlan {            // byte offsets inside the dynamic shared memory of one CTA
+    int32_t cs;              // stride of one position component: TM own masses + halo, even
+    int32_t vs;              // stride of one velocity component (cs when halo velocities are staged, else TM)
+    int32_t hring_stride;    // bytes of one halo-index ring entry
+    int32_t off_ctrl, off_hring, off_part, part_bytes, off_stage, stage_bytes;
+    int32_t st_pos, st_vel;  // offsets inside a stage (the blob sits at 0)
+    int32_t total;
+};
+// mbarriers at offset 0: full[2], empty[2], hfull[HALO_RING]
+static SmemPlan plan_smem(int max_halo, int max_blob, bool stage_vel, int tpm) {
+    SmemPlan p;
+    int hp = (max_halo + 3) & ~3;
+    p.cs = TM + hp;
+    p.vs = stage_vel ? p.cs : TM;
+    p.hring_stride = (int32_t)up16((size_t)hp * 4 + 16);
+    p.off_ctrl = 64;
+    p.off_hring = 128;
+    p.off_part = p.off_hring + HALO_RING * p.hring_stride;
+    p.part_bytes = (tpm - 1) * 3 * TM * 8;
+    p.off_stage = p.off_part + 2 * p.part_bytes;
+    p.st_pos = (int32_t)up16((size_t)max_blob);
+    p.st_vel = p.st_pos + 3 * p.cs * 8;
+    p.stage_bytes = p.st_vel + 3 * p.vs * 8;
+    p.total = p.off_stage + 2 * p.stage_bytes;
+    return p;
+}
 
 // ---------------------------------------------------------------- structure build (host) -----------------
 template <class T> static int upload_vec(Engine *e, T **dst, const std::vector<T> &src) {
@@ -123,21 +196,25 @@ template <class T> static int upload_vec(Engine *e, T **dst, const std::vector<T
 template <class T> static void release(Engine *e, T *&p, size_t count) { dev_free(e, (void *)p, count * sizeof(T)); p = nullptr; }
 
 static void free_structure(Engine *e, TiledState *S) {
-    for (int p = 0; p < 2; p++) { release(e, S->pos[p], (size_t)S->n_slots * 3); release(e, S->vel[p], (size_t)S->n_slots * 3); }
-    release(e, S->m, (size_t)S->n_slots); release(e, S->flags, (size_t)S->n_slots);
+    for (int p = 0; p < 2; p++) release(e, S->st[p], (size_t)S->n_tiles * STATE_BLOCK);
+    release(e, S->blob, S->blob_bytes);
     release(e, S->slot_to_api, (size_t)S->n_slots); release(e, S->halo, (size_t)S->n_halo);
     release(e, S->rec_spring, (size_t)S->n_rec); release(e, S->ell, (size_t)S->n_ell);
-    release(e, S->prm, (size_t)S->n_rec * 2); release(e, S->dmp, (size_t)S->n_rec); release(e, S->omg, (size_t)S->n_rec);
     if (S->meta) { cudaFree(S->meta); S->meta = nullptr; }
     S->n_tiles = S->n_slots = S->n_rec = S->n_ell = S->n_halo = 0;
+    S->blob_bytes = 0;
 }
 
-static size_t smem_need(int max_halo, int max_rec, bool damping, bool active) {
-    size_t nl = (size_t)((TM + max_halo + 1) & ~1);
-    size_t b = nl * 24 * (damping ? 2 : 1) + (size_t)max_rec * 16;
-    if (damping) b += (size_t)max_rec * 8;
-    if (active) b += (size_t)max_rec * 8;
-    return b + 16;
+static size_t blob_size(int n_rec, bool damping, bool active) {
+    size_t np = (size_t)((n_rec + 1) & ~1);
+    return up16((size_t)BLOB_REC + (size_t)n_rec * 16) + (damping ? np * 8 : 0) + (active ? np * 8 : 0);
+}
+
+static int choose_tpm(const Engine *e) {
+    if (e->flags & TB_MATH_STRICT) return 1;   // one thread per mass: the oracle's summation order
+    int tpm = 4;
+    if (const char *s = getenv("TB_TPM")) { int v = atoi(s); if (v == 1 || v == 2 || v == 4) tpm = v; }
+    return tpm;
 }
 
 // Builds tiles, ELL rows, halo lists and record tables on the host and uploads them.  Returns TB_OK with
@@ -146,23 +223,33 @@ static int build_structure(Engine *e, TiledState *S) {
     free_structure(e, S);
     S->supported = false;
     const int64_t nm = e->nm;
-    // current positions (SoA) drive the bisection
-    std::vector<double> pos((size_t)nm * 3);
-    TB_CUDA(e, cudaMemcpy(pos.data(), e->pos[e->cur], (size_t)nm * 24, cudaMemcpyDeviceToHost));
+    std::vector<double> pos;
+    if (e->tile_hint.empty()) {     // current positions (SoA) drive the bisection
+        pos.resize((size_t)nm * 3);
+        TB_CUDA(e, cudaMemcpy(pos.data(), e->pos[e->cur], (size_t)nm * 24, cudaMemcpyDeviceToHost));
+    }
     assign_tiles(e, pos, S->h_slot_to_api);
     std::vector<double>().swap(pos);
     const int64_t n_slots = (int64_t)S->h_slot_to_api.size(), n_tiles = n_slots / TM;
+    if (n_tiles * (int64_t)STATE_BLOCK >= ((int64_t)1 << 31)) { S->why_not = "state exceeds int32 halo indices"; return TB_OK; }
     S->h_api_to_slot.assign((size_t)nm, -1);
     for (int64_t s = 0; s < n_slots; s++) if (S->h_slot_to_api[(size_t)s] >= 0) S->h_api_to_slot[(size_t)S->h_slot_to_api[(size_t)s]] = (int32_t)s;
 
+    S->has_damping = e->any_damping; S->has_active = e->any_active;
+    S->stage_vel = S->has_damping || (e->flags & TB_MATH_STRICT);
+    S->tpm = choose_tpm(e);
+
     std::vector<TileMeta> meta((size_t)n_tiles);
-    std::vector<uint32_t> ell;
+    std::vector<uint32_t> ell, block;
+    std::map<uint64_t, std::vector<uint32_t>> ell_index;   // content hash -> offsets of stored blocks
     std::vector<int32_t> halo, rec_spring;
     std::vector<int32_t> halo_stamp((size_t)nm, -1), halo_local((size_t)nm, 0);
     std::vector<int32_t> rec_stamp((size_t)e->ns, -1), rec_local((size_t)e->ns, 0);
     struct Half { int32_t s; int32_t o; uint8_t side; };
     std::vector<std::vector<Half>> rows(TM);
     int max_halo = 0, max_rec = 0, max_deg = 0;
+    size_t blob_total = 0, max_blob = 0;
+    int64_t unique_blocks = 0;
     const std::vector<int32_t> &rp = e->h_row_ptr, &adj = e->h_adj;
     for (int64_t T = 0; T < n_tiles; T++) {
         int deg = 0;
@@ -181,14 +268,11 @@ static int build_structure(Engine *e, TiledState *S) {
         }
         if (deg > MAX_DEG) { S->why_not = "a mass has more incident springs than the ELL format holds"; return TB_OK; }
         TileMeta &M = meta[(size_t)T];
-        M.ell_off = (int32_t)ell.size(); M.deg = deg;
-        M.halo_off = (int32_t)halo.size();
-        while (rec_spring.size() % 8) rec_spring.push_back(-1);   // 128-byte aligned record blocks
-        M.rec_off = (int32_t)rec_spring.size();
-        if ((int64_t)ell.size() + (int64_t)deg * TM >= ((int64_t)1 << 31) || rec_spring.size() >= ((size_t)1 << 31) - MAX_REC) {
-            S->why_not = "tiled tables exceed int32 offsets"; return TB_OK;
-        }
-        ell.resize(ell.size() + (size_t)deg * TM, 0u);
+        M.deg = (uint32_t)deg;
+        while (halo.size() % 4) halo.push_back(0);               // 16-byte aligned halo lists (bulk copy)
+        M.halo_off = (uint32_t)halo.size();
+        M.rec_off = (uint32_t)rec_spring.size();
+        block.assign((size_t)ell_chunks(deg) * ELL_CHUNK * TM, 0u);   // zero rows pad the last chunk
         int n_halo = 0, n_rec = 0;
         for (int j = 0; j < deg; j++) for (int t = 0; t < TM; t++) {   // j-major walk: record slots of one row are consecutive
             if (j >= (int)rows[t].size()) continue;
@@ -197,7 +281,10 @@ static int build_structure(Engine *e, TiledState *S) {
             int nb;
             if (oslot / TM == T) nb = oslot % TM;
             else {
-                if (halo_stamp[(size_t)h.o] != (int32_t)T) { halo_stamp[(size_t)h.o] = (int32_t)T; halo_local[(size_t)h.o] = n_halo++; halo.push_back(oslot); }
+                if (halo_stamp[(size_t)h.o] != (int32_t)T) {
+                    halo_stamp[(size_t)h.o] = (int32_t)T; halo_local[(size_t)h.o] = n_halo++;
+                    halo.push_back((int32_t)((int64_t)(oslot / TM) * STATE_BLOCK + oslot % TM));
+                }
                 nb = TM + halo_local[(size_t)h.o];
             }
             if (rec_stamp[(size_t)h.s] != (int32_t)T) { rec_stamp[(size_t)h.s] = (int32_t)T; rec_local[(size_t)h.s] = n_rec++; rec_spring.push_back(h.s); }
@@ -205,28 +292,48 @@ static int build_structure(Engine *e, TiledState *S) {
             if (nb >= MAX_LOCAL || rec >= MAX_REC) { S->why_not = "a tile reaches too many foreign masses or springs"; return TB_OK; }
             uint32_t ty = 0;
             if (!e->h_type.empty()) { uint8_t x = e->h_type[(size_t)h.s]; ty = (x == 2) ? 1u : (x == 3) ? 2u : 0u; }
-            ell[(size_t)M.ell_off + (size_t)j * TM + (size_t)t] =
-                (uint32_t)nb | ((uint32_t)rec << ELL_NB_BITS) | (h.side ? ELL_SIDE : 0u) | (ty << ELL_TYPE_SHIFT) | ELL_VALID;
+            block[(size_t)j * TM + (size_t)t] =
+                ((uint32_t)nb << ELL_NB_SHIFT) | ((uint32_t)rec << ELL_REC_SHIFT) | (h.side ? ELL_SIDE : 0u) | (ty << ELL_TYPE_SHIFT) | ELL_VALID;
         }
-        M.n_halo = n_halo; M.n_rec = n_rec;
+        // content dedupe of the ELL block (FNV-1a over the words, verified by comparison)
+        uint64_t hsh = 1469598103934665603ull ^ (uint64_t)deg;
+        for (uint32_t w : block) { hsh ^= w; hsh *= 1099511628211ull; }
+        bool found = false;
+        std::vector<uint32_t> &cands = ell_index[hsh];
+        for (uint32_t off : cands)
+            if (off + block.size() <= ell.size() && std::equal(block.begin(), block.end(), ell.begin() + off)) { M.ell_off = off; found = true; break; }
+        if (!found) {
+            if (ell.size() + block.size() >= ((size_t)1 << 31)) { S->why_not = "ELL table exceeds int32 offsets"; return TB_OK; }
+            M.ell_off = (uint32_t)ell.size();
+            cands.push_back(M.ell_off);
+            ell.insert(ell.end(), block.begin(), block.end());
+            unique_blocks++;
+        }
+        M.n_halo = (uint32_t)n_halo; M.n_rec = (uint32_t)n_rec;
+        size_t bb = blob_size(n_rec, S->has_damping, S->has_active);
+        if (blob_total / 16 >= ((size_t)1 << 32)) { S->why_not = "blob exceeds 64 GB"; return TB_OK; }
+        M.blob_off16 = (uint32_t)(blob_total / 16); M.blob_bytes = (uint32_t)bb;
+        blob_total += bb;
+        max_blob = std::max(max_blob, bb);
         max_halo = std::max(max_halo, n_halo); max_rec = std::max(max_rec, n_rec); max_deg = std::max(max_deg, deg);
     }
-    while (rec_spring.size() % 8) rec_spring.push_back(-1);
-    S->has_damping = e->any_damping; S->has_active = e->any_active;
-    S->smem_bytes = smem_need(max_halo, max_rec, S->has_damping || (e->flags & TB_MATH_STRICT), S->has_active);
-    if (S->smem_bytes > SMEM_BUDGET) { S->why_not = "a tile's working set exceeds the shared-memory budget"; return TB_OK; }
-    // padding: the ELL rows of all tiles together must not dwarf the real incidence (skewed degree distributions)
-    if ((double)ell.size() > 1.6 * (double)std::max<int64_t>(1, rp[(size_t)nm]) + 64.0 * TM) { S->why_not = "ELL padding too large for this degree distribution"; return TB_OK; }
+    while (halo.size() % 4) halo.push_back(0);
+    halo.resize(halo.size() + 4, 0);   // the last list may be copied rounded up to 16 bytes
+    SmemPlan plan = plan_smem(max_halo, (int)max_blob, S->stage_vel, S->tpm);
+    if ((size_t)plan.total > SMEM_LIMIT) { S->why_not = "a tile's working set exceeds the shared-memory budget"; return TB_OK; }
+    S->smem_bytes = (size_t)plan.total;
 
     S->n_tiles = n_tiles; S->n_slots = n_slots; S->n_rec = (int64_t)rec_spring.size(); S->n_ell = (int64_t)ell.size();
     S->n_halo = (int64_t)halo.size(); S->max_halo = max_halo; S->max_rec = max_rec; S->max_deg = max_deg;
-    for (int p = 0; p < 2; p++) { TB_TRY(dev_alloc(e, &S->pos[p], (size_t)n_slots * 3)); TB_TRY(dev_alloc(e, &S->vel[p], (size_t)n_slots * 3)); }
-    TB_TRY(dev_alloc(e, &S->m, (size_t)n_slots)); TB_TRY(dev_alloc(e, &S->flags, (size_t)n_slots));
+    S->max_blob = (int)max_blob; S->blob_bytes = blob_total; S->ell_unique_tiles = unique_blocks;
+    for (int p = 0; p < 2; p++) {
+        TB_TRY(dev_alloc(e, &S->st[p], (size_t)n_tiles * STATE_BLOCK));
+        TB_CUDA(e, cudaMemset(S->st[p], 0, (size_t)n_tiles * STATE_BLOCK * 8));
+    }
+    TB_TRY(dev_alloc(e, &S->blob, blob_total));
+    TB_CUDA(e, cudaMemset(S->blob, 0, blob_total));
     TB_TRY(upload_vec(e, &S->slot_to_api, S->h_slot_to_api));
     TB_TRY(upload_vec(e, &S->halo, halo)); TB_TRY(upload_vec(e, &S->rec_spring, rec_spring)); TB_TRY(upload_vec(e, &S->ell, ell));
-    TB_TRY(dev_alloc(e, &S->prm, (size_t)S->n_rec * 2));
-    if (S->has_damping) TB_TRY(dev_alloc(e, &S->dmp, (size_t)S->n_rec));
-    if (S->has_active) TB_TRY(dev_alloc(e, &S->omg, (size_t)S->n_rec));
     TB_CUDA(e, cudaMalloc((void **)&S->meta, (size_t)n_tiles * sizeof(TileMeta)));
     TB_CUDA(e, cudaMemcpy(S->meta, meta.data(), (size_t)n_tiles * sizeof(TileMeta), cudaMemcpyHostToDevice));
     S->supported = true;
@@ -234,171 +341,389 @@ static int build_structure(Engine *e, TiledState *S) {
 }
 
 // ---------------------------------------------------------------- refresh kernels -------------------------
-__global__ void tiled_gather_state(double *pos_t, double *vel_t, double *m_t, const double *pos_c, const double *vel_c,
-                                   const double *m_c, const int32_t *slot_to_api, int64_t n_slots, int64_t nm) {
+// canonical (API order, 3 planes of stride nm) <-> tile-blocked state
+__global__ void tiled_gather_state(double *st, const double *pos_c, const double *vel_c, const int32_t *slot_to_api,
+                                   int64_t n_slots, int64_t nm) {
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_slots) return;
     int32_t i = slot_to_api[s];
+    double *b = st + (s / TM) * STATE_BLOCK + (s % TM);
     for (int c = 0; c < 3; c++) {
-        pos_t[c * n_slots + s] = i >= 0 ? pos_c[c * nm + i] : 0.0;
-        vel_t[c * n_slots + s] = i >= 0 ? vel_c[c * nm + i] : 0.0;
+        b[c * TM] = i >= 0 ? pos_c[c * nm + i] : 0.0;
+        b[(3 + c) * TM] = i >= 0 ? vel_c[c * nm + i] : 0.0;
     }
-    m_t[s] = i >= 0 ? m_c[i] : 1.0;
 }
-__global__ void tiled_scatter_state(double *pos_c, double *vel_c, const double *pos_t, const double *vel_t,
-                                    const int32_t *slot_to_api, int64_t n_slots, int64_t nm) {
+__global__ void tiled_scatter_state(double *pos_c, double *vel_c, const double *st, const int32_t *slot_to_api,
+                                    int64_t n_slots, int64_t nm) {
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_slots) return;
     int32_t i = slot_to_api[s];
     if (i < 0) return;
-    for (int c = 0; c < 3; c++) { pos_c[c * nm + i] = pos_t[c * n_slots + s]; vel_c[c * nm + i] = vel_t[c * n_slots + s]; }
+    const double *b = st + (s / TM) * STATE_BLOCK + (s % TM);
+    for (int c = 0; c < 3; c++) { pos_c[c * nm + i] = b[c * TM]; vel_c[c * nm + i] = b[(3 + c) * TM]; }
 }
-__global__ void tiled_gather_flags(uint8_t *flags_t, const uint8_t *flags_c, const int32_t *slot_to_api, int64_t n_slots) {
-    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= n_slots) return;
-    int32_t i = slot_to_api[s];
-    flags_t[s] = i >= 0 ? flags_c[i] : (uint8_t)0;
+// one CTA of TM threads per tile: header, flags and masses of the tile's blob
+__global__ void tiled_refresh_mass(uint8_t *blob, const TileMeta *meta, const int32_t *slot_to_api, const double *m_c,
+                                   const uint8_t *flags_c) {
+    const TileMeta M = meta[blockIdx.x];
+    uint8_t *b = blob + (size_t)M.blob_off16 * 16;
+    int t = threadIdx.x;
+    int32_t i = slot_to_api[(int64_t)blockIdx.x * TM + t];
+    if (t == 0) { int32_t *h = (int32_t *)b; h[0] = (int32_t)M.deg; h[1] = (int32_t)M.n_halo; h[2] = (int32_t)M.n_rec; h[3] = 0; }
+    b[BLOB_FLAGS + t] = i >= 0 ? flags_c[i] : (uint8_t)0;
+    ((double *)(b + BLOB_M))[t] = i >= 0 ? m_c[i] : 1.0;
 }
-__global__ void tiled_gather_params(double *prm, double *dmp, double *omg, const int32_t *rec_spring, const double *k,
-                                    const double *rest, const double *damping, const double *omega, int64_t n_rec) {
-    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n_rec) return;
-    int32_t s = rec_spring[r];
-    prm[2 * r] = s >= 0 ? k[s] : 0.0;
-    prm[2 * r + 1] = s >= 0 ? rest[s] : 0.0;
-    if (dmp) dmp[r] = (s >= 0 && damping) ? damping[s] : 0.0;
-    if (omg) omg[r] = (s >= 0 && omega) ? omega[s] : 0.0;
+// one CTA per tile: the spring records of the tile's blob
+__global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const int32_t *rec_spring, const double *k,
+                                     const double *rest, const double *damping, const double *omega, int has_damping,
+                                     int has_active) {
+    const TileMeta M = meta[blockIdx.x];
+    uint8_t *b = blob + (size_t)M.blob_off16 * 16;
+    double2 *rec = (double2 *)(b + BLOB_REC);
+    double *dmp = (double *)(b + ((BLOB_REC + (size_t)M.n_rec * 16 + 15) & ~(size_t)15));
+    double *omg = dmp + (has_damping ? ((M.n_rec + 1) & ~1u) : 0);
+    for (uint32_t r = threadIdx.x; r < M.n_rec; r += blockDim.x) {
+        int32_t s = rec_spring[M.rec_off + r];
+        rec[r] = make_double2(k[s], rest[s]);
+        if (has_damping) dmp[r] = damping ? damping[s] : 0.0;
+        if (has_active) omg[r] = omega ? omega[s] : 0.0;
+    }
 }
 
+// ---------------------------------------------------------------- PTX helpers ------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+// global -> shared bulk copy completing on an mbarrier (SASS UBLKCP); 16-byte aligned, size multiple of 16
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// 1/sqrt(x): MUFU.RSQ64H seed (about 2^-22 relative) + one cubically convergent correction; no special-case
+// branch (x == 0 gives NaN exactly like the reference's temp / temp.norm(), include/Titan/vec.h:133-151)
+__device__ __forceinline__ double rsqrt_fast(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double e = fma(-(x * y), y, 1.0);
+    const double p = fma(0.375, e, 0.5) * e;
+    return fma(y, p, y);
+}
+__device__ __forceinline__ void cp_async8(uint32_t dst, const void *src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void *src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+// this thread's earlier cp.async copies arrive on the mbarrier when they have landed (count pre-charged at init)
+__device__ __forceinline__ void cp_async_arrive_noinc(uint32_t bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void named_bar_sync(int id, int count) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void named_bar_arrive(int id, int count) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(count) : "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // ---------------------------------------------------------------- the step kernel -------------------------
 struct TiledArgs {
-    int64_t n_slots;
-    int32_t nl;                      // smem stride of one coordinate plane (TM + max_halo, even)
-    int32_t max_rec;
-    const double *pos_in, *vel_in;
-    double *pos_out, *vel_out;
-    const double *m;
-    const uint8_t *flags;
+    int32_t n_tiles;
+    int32_t write_acc;
+    SmemPlan sp;
+    const double *st_in;
+    double *st_out;
+    const uint8_t *blob;
     const int32_t *slot_to_api, *halo;
     const uint32_t *ell;
-    const double *prm, *dmp, *omg;
     const TileMeta *meta;
     double *acc;                     // canonical (API-ordered) acceleration, stride X.nm
     const double *t_in;
     double *t_out;
 };
 
-template <class P, bool DAMPING, bool ACTIVE, bool WRITE_ACC>
-__global__ void __launch_bounds__(TM) tiled_step_kernel(TiledArgs A, Globals G, MassExtras X) {
-    extern __shared__ __align__(16) double smem[];
-    const int nl = A.nl;
-    double *px = smem, *py = px + nl, *pz = py + nl;
-    double *vx = pz + nl, *vy = vx + nl, *vz = vy + nl;               // only when staging velocities
+struct TileCtrl { uint32_t next_ell_off, next_deg, has_next, pad; };   // producer -> consumers, one per stage
+
+// Warp roles: warps 0 .. TM*TPM/32-1 are CONSUMERS (thread = (mass t, share q)); the last warp is the PRODUCER
+// that keeps the two stages filled.  Synchronisation is mbarrier-only between the roles:
+//   full[s]  : 1 expect_tx arrival (bulk copies: blob + own state) + 32 cp.async arrivals (halo gather)
+//   empty[s] : one arrival per consumer warp when it has finished reading stage s
+//   hfull[r] : bulk copy of a halo index list (producer-internal)
+// plus one named barrier per 32-mass column and tile parity for handing the partial sums to thread q == 0.
+template <class P, bool DAMPING, bool ACTIVE, int TPM>
+__global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_kernel(const __grid_constant__ TiledArgs A,
+                                                                   const __grid_constant__ Globals G,
+                                                                   const __grid_constant__ MassExtras X) {
+    extern __shared__ __align__(128) unsigned char smem[];
     constexpr bool STAGE_VEL = DAMPING || P::strict;
-    double2 *prm = reinterpret_cast<double2 *>(STAGE_VEL ? vz + nl : pz + nl);
-    double *dmp = reinterpret_cast<double *>(prm + A.max_rec);
-    double *omg = DAMPING ? dmp + A.max_rec : dmp;
+    constexpr int NT = TM * TPM;                       // consumer threads
+    constexpr int NCW = NT / 32;                       // consumer warps
+    constexpr int EPT = ell_words_per_thread(TPM);     // ELL words per thread
+    const SmemPlan &sp = A.sp;
+    const int tid = threadIdx.x;
+    const uint32_t smem_base = smem_u32(smem);
+    const int n_my = (A.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+    auto tile_of = [&](int i) { return (int64_t)blockIdx.x + (int64_t)i * gridDim.x; };
+    auto bar_full = [&](int s) { return smem_base + 8u * (uint32_t)s; };
+    auto bar_empty = [&](int s) { return smem_base + 8u * (uint32_t)(2 + s); };
+    auto bar_halo = [&](int r) { return smem_base + 8u * (uint32_t)(4 + r); };
 
-    const TileMeta M = A.meta[blockIdx.x];
-    const int t = threadIdx.x;
-    const int64_t n = A.n_slots, slot = (int64_t)blockIdx.x * TM + t;
-    const double t_sim = *A.t_in;
-    if (blockIdx.x == 0 && t == 0) *A.t_out = __dadd_rn(t_sim, G.dt);   // T += dt, src/sim.cu:1811
-
-    // ---- phase A: everything the tile needs, all loads in flight together ------------------------------
-    uint32_t ent[MAX_DEG];
-#pragma unroll
-    for (int j = 0; j < MAX_DEG; j++) ent[j] = (j < M.deg) ? A.ell[(size_t)M.ell_off + (size_t)j * TM + t] : 0u;
-    {
-        const double2 *src = reinterpret_cast<const double2 *>(A.prm) + M.rec_off;
-        for (int r = t; r < M.n_rec; r += TM) prm[r] = src[r];
-        if (DAMPING) for (int r = t; r < M.n_rec; r += TM) dmp[r] = A.dmp[M.rec_off + r];
-        if (ACTIVE) for (int r = t; r < M.n_rec; r += TM) omg[r] = A.omg[M.rec_off + r];
-    }
-    V3 pos = {A.pos_in[slot], A.pos_in[n + slot], A.pos_in[2 * n + slot]};
-    V3 vel = {A.vel_in[slot], A.vel_in[n + slot], A.vel_in[2 * n + slot]};
-    const uint8_t fl = A.flags[slot];
-    const double mass = A.m[slot];
-    px[t] = pos.x; py[t] = pos.y; pz[t] = pos.z;
-    if (STAGE_VEL) { vx[t] = vel.x; vy[t] = vel.y; vz[t] = vel.z; }
-    for (int h = t; h < M.n_halo; h += TM) {
-        int64_t o = A.halo[M.halo_off + h];
-        px[TM + h] = A.pos_in[o]; py[TM + h] = A.pos_in[n + o]; pz[TM + h] = A.pos_in[2 * n + o];
-        if (STAGE_VEL) { vx[TM + h] = A.vel_in[o]; vy[TM + h] = A.vel_in[n + o]; vz[TM + h] = A.vel_in[2 * n + o]; }
+    if (tid == 0) {
+        for (int s = 0; s < 2; s++) { mbar_init(bar_full(s), 33); mbar_init(bar_empty(s), NCW); }
+        for (int r = 0; r < HALO_RING; r++) mbar_init(bar_halo(r), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
     __syncthreads();
 
-    if (!(fl & F_VALID) || (fl & F_FIXED)) {      // padding / deleted / fixed: frozen (src/sim.cu:1292-1295)
-        A.pos_out[slot] = pos.x; A.pos_out[n + slot] = pos.y; A.pos_out[2 * n + slot] = pos.z;
-        A.vel_out[slot] = vel.x; A.vel_out[n + slot] = vel.y; A.vel_out[2 * n + slot] = vel.z;
+    if (tid >= NT) {
+        // =========================================== PRODUCER warp ===========================================
+        const int lane = tid - NT;
+        if (blockIdx.x == 0 && lane == 0) *A.t_out = __dadd_rn(*A.t_in, G.dt);   // T += dt, src/sim.cu:1811
+        const int4 *mg = reinterpret_cast<const int4 *>(A.meta);
+        auto load_meta = [&](int i, int4 &a, int4 &b) {
+            if (i < n_my) { a = __ldg(mg + 2 * tile_of(i)); b = __ldg(mg + 2 * tile_of(i) + 1); }
+            else { a = make_int4(0, 0, 0, 0); b = a; }
+        };
+        // a = {blob_off16, blob_bytes, halo_off, n_halo}, b = {ell_off, deg, n_rec, rec_off}
+        auto issue_hidx = [&](int i, const int4 &a) {     // lane 0
+            uint32_t bytes = ((uint32_t)a.w * 4u + 15u) & ~15u;
+            if (bytes < 16u) bytes = 16u;
+            const int r = i % HALO_RING;
+            mbar_expect_tx(bar_halo(r), bytes);
+            bulk_g2s(smem_base + (uint32_t)(sp.off_hring + r * sp.hring_stride), A.halo + (uint32_t)a.z, bytes, bar_halo(r));
+        };
+        int4 m0a, m0b, m1a, m1b, m2a, m2b, m3a, m3b;
+        load_meta(0, m0a, m0b); load_meta(1, m1a, m1b); load_meta(2, m2a, m2b);
+        if (lane == 0) { issue_hidx(0, m0a); if (n_my > 1) issue_hidx(1, m1a); }
+        for (int k = 0; k < n_my; k++) {
+            const int s = k & 1;
+            __syncwarp();
+            load_meta(k + 3, m3a, m3b);
+            mbar_wait(bar_empty(s), (uint32_t)(((k >> 1) & 1) ^ 1));    // consumers are done with tile k-2
+            const uint32_t stage = smem_base + (uint32_t)(sp.off_stage + s * sp.stage_bytes);
+            if (lane == 0) {
+                TileCtrl *c = reinterpret_cast<TileCtrl *>(smem + sp.off_ctrl) + s;
+                c->next_ell_off = (uint32_t)m1b.x; c->next_deg = (uint32_t)m1b.y; c->has_next = (k + 1 < n_my) ? 1u : 0u; c->pad = 0;
+                mbar_expect_tx(bar_full(s), (uint32_t)m0a.y + (uint32_t)(STATE_BLOCK * 8));
+                bulk_g2s(stage, A.blob + (size_t)(uint32_t)m0a.x * 16, (uint32_t)m0a.y, bar_full(s));
+                const double *sb = A.st_in + tile_of(k) * STATE_BLOCK;
+#pragma unroll
+                for (int c3 = 0; c3 < 3; c3++) {
+                    bulk_g2s(stage + (uint32_t)(sp.st_pos + c3 * sp.cs * 8), sb + c3 * TM, TM * 8, bar_full(s));
+                    bulk_g2s(stage + (uint32_t)(sp.st_vel + c3 * sp.vs * 8), sb + (3 + c3) * TM, TM * 8, bar_full(s));
+                }
+                if (k + 2 < n_my) issue_hidx(k + 2, m2a);
+            }
+            // halo gather of tile k: the index list was bulk-copied two tiles ago
+            mbar_wait(bar_halo(k % HALO_RING), (uint32_t)((k / HALO_RING) & 1));
+            const int n_halo = m0a.w;
+            const int32_t *hl = reinterpret_cast<const int32_t *>(smem + sp.off_hring + (k % HALO_RING) * sp.hring_stride);
+            for (int h = lane; h < n_halo; h += 32) {
+                const double *src = A.st_in + hl[h];
+                const uint32_t d = stage + (uint32_t)(sp.st_pos + (TM + h) * 8);
+                cp_async8(d, src); cp_async8(d + (uint32_t)(sp.cs * 8), src + TM); cp_async8(d + (uint32_t)(2 * sp.cs * 8), src + 2 * TM);
+                if (STAGE_VEL) {
+                    const uint32_t dv = stage + (uint32_t)(sp.st_vel + (TM + h) * 8);
+                    cp_async8(dv, src + 3 * TM); cp_async8(dv + (uint32_t)(sp.vs * 8), src + 4 * TM); cp_async8(dv + (uint32_t)(2 * sp.vs * 8), src + 5 * TM);
+                }
+            }
+            cp_async_arrive_noinc(bar_full(s));
+            m0a = m1a; m0b = m1b; m1a = m2a; m1b = m2b; m2a = m3a; m2b = m3b;
+        }
         return;
     }
 
-    // ---- phase B: gather the incident springs in ascending spring order, registers only -----------------
-    V3 force = {0.0, 0.0, 0.0};
+    // ============================================= CONSUMER warps ============================================
+    const int t = tid % TM, q = tid / TM;
+    const double t_sim = *A.t_in;
+    // this thread's ELL words: chunks [cb, cb + nch) of the tile's block, rows of TM words
+    auto my_chunks = [&](int deg, int &cb, int &nch) {
+        const int n = ell_chunks(deg), c0 = ell_chunks0(n, TPM);
+        if (q == 0) { cb = 0; nch = c0; }
+        else {
+            const int cq = ell_chunks_q(n, TPM);
+            cb = c0 + (q - 1) * cq;
+            nch = n - cb < cq ? n - cb : cq;
+            if (nch < 0) nch = 0;
+        }
+    };
+    auto load_ell = [&](uint32_t ell_off, int deg, uint32_t (&dst)[EPT]) {
+        int cb, nch;
+        my_chunks(deg, cb, nch);
+        const uint32_t *src = A.ell + ell_off + (size_t)cb * ELL_CHUNK * TM + t;
 #pragma unroll
-    for (int j = 0; j < MAX_DEG; j++) {
-        if (j < M.deg) {
-            const uint32_t en = ent[j];
-            if (en & ELL_VALID) {
-                const int nb = en & (MAX_LOCAL - 1), rec = (en >> ELL_NB_BITS) & (MAX_REC - 1);
-                const V3 po = {px[nb], py[nb], pz[nb]};
-                const double2 kr = prm[rec];
-                SpringArgs sp;
-                sp.k = kr.x;
-                sp.rest_scaled = kr.y;
-                sp.damping = DAMPING ? dmp[rec] : 0.0;
-                if (ACTIVE) {
-                    const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                    if (ty) sp.rest_scaled = P::mul(kr.y, actuation_scale<P>(ty + 1, omg[rec], t_sim));
+        for (int g = 0; g < EPT / ELL_CHUNK; g++)
+            if (g < nch) {
+#pragma unroll
+                for (int u = 0; u < ELL_CHUNK; u++) dst[g * ELL_CHUNK + u] = __ldg(src + (g * ELL_CHUNK + u) * TM);
+            }
+    };
+    uint32_t ell_cur[EPT], ell_nxt[EPT];
+#pragma unroll
+    for (int jj = 0; jj < EPT; jj++) { ell_cur[jj] = 0u; ell_nxt[jj] = 0u; }
+    {
+        const TileMeta *m0 = A.meta + tile_of(0);
+        load_ell(__ldg(&m0->ell_off), (int)__ldg(&m0->deg), ell_cur);
+    }
+
+    for (int i = 0; i < n_my; i++) {
+        const int s = i & 1;
+        mbar_wait(bar_full(s), (uint32_t)((i >> 1) & 1));     // blob, own state and halo of tile i have landed
+        const unsigned char *stage = smem + sp.off_stage + s * sp.stage_bytes;
+        const TileCtrl ctrl = reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl)[s];
+        if (ctrl.has_next) load_ell(ctrl.next_ell_off, (int)ctrl.next_deg, ell_nxt);   // next tile's words -> registers
+        const int deg = reinterpret_cast<const int32_t *>(stage)[0], n_rec = reinterpret_cast<const int32_t *>(stage)[2];
+        const uint8_t fl = stage[BLOB_FLAGS + t];
+        const char *prb = reinterpret_cast<const char *>(stage + BLOB_REC);
+        const char *dmb = prb + (size_t)n_rec * 16;
+        const char *omb = dmb + (DAMPING ? ((n_rec + 1) & ~1) * 8 : 0);
+        const char *pbx = reinterpret_cast<const char *>(stage + sp.st_pos), *pby = pbx + sp.cs * 8, *pbz = pby + sp.cs * 8;
+        const char *vbx = reinterpret_cast<const char *>(stage + sp.st_vel), *vby = vbx + sp.vs * 8, *vbz = vby + sp.vs * 8;
+        V3 pos = {reinterpret_cast<const double *>(pbx)[t], reinterpret_cast<const double *>(pby)[t], reinterpret_cast<const double *>(pbz)[t]};
+        V3 vel = {0.0, 0.0, 0.0};
+        if (STAGE_VEL || q == 0) vel = V3{reinterpret_cast<const double *>(vbx)[t], reinterpret_cast<const double *>(vby)[t], reinterpret_cast<const double *>(vbz)[t]};
+        const bool live = (fl & F_VALID) && !(fl & F_FIXED);   // else padding / deleted / fixed: frozen (src/sim.cu:1292-1295)
+
+        // ---- gather this thread's share of the incident springs, ascending row order ------------------------
+        V3 force = {0.0, 0.0, 0.0};
+        int cb, nch;
+        my_chunks(deg, cb, nch);
+        if (P::strict) {
+            if (live) {
+#pragma unroll
+                for (int jj = 0; jj < EPT; jj++) {
+                    const uint32_t en = (jj < nch * ELL_CHUNK) ? ell_cur[jj] : 0u;
+                    if (en & ELL_VALID) {
+                        const uint32_t nbo = en & 0xff8u, rco = (en >> 12) & 0xfff0u;
+                        const V3 po = {*(const double *)(pbx + nbo), *(const double *)(pby + nbo), *(const double *)(pbz + nbo)};
+                        const V3 vo = {*(const double *)(vbx + nbo), *(const double *)(vby + nbo), *(const double *)(vbz + nbo)};
+                        const double2 kr = *(const double2 *)(prb + rco);
+                        SpringArgs spr;
+                        spr.k = kr.x;
+                        spr.rest_scaled = kr.y;
+                        spr.damping = DAMPING ? *(const double *)(dmb + (rco >> 1)) : 0.0;
+                        if (ACTIVE) {
+                            const int ty = (en >> ELL_TYPE_SHIFT) & 3;
+                            if (ty) spr.rest_scaled = P::mul(kr.y, actuation_scale<P>(ty + 1, *(const double *)(omb + (rco >> 1)), t_sim));
+                        }
+                        if (en & ELL_SIDE) acc3<P>(force, spring_force<P, DAMPING>(po, pos, vo, vel, spr));
+                        else { V3 f = spring_force<P, DAMPING>(pos, po, vel, vo, spr); acc3<P>(force, V3{-f.x, -f.y, -f.z}); }
+                    }
                 }
-                if (P::strict) {
-                    const V3 vo = {vx[nb], vy[nb], vz[nb]};
-                    if (en & ELL_SIDE) acc3<P>(force, spring_force<P, DAMPING>(po, pos, vo, vel, sp));
-                    else { V3 f = spring_force<P, DAMPING>(pos, po, vel, vo, sp); acc3<P>(force, V3{-f.x, -f.y, -f.z}); }
-                } else {
-                    // force on this mass = (p_me - p_other) * coef whichever endpoint it is (see physics.cuh)
-                    V3 vo = {0.0, 0.0, 0.0};
-                    if (DAMPING) vo = V3{vx[nb], vy[nb], vz[nb]};
-                    acc3<P>(force, spring_force<P, DAMPING>(po, pos, vo, vel, sp));
+            }
+        } else {
+            // ELL_CHUNK springs at a time without branches (invalid words evaluate a dummy spring whose
+            // coefficient is then forced to zero), so their loads and fp64 chains interleave.
+            // force on this mass = (p_me - p_other) * coef whichever endpoint it is (see physics.cuh)
+#pragma unroll
+            for (int g = 0; g < EPT / ELL_CHUNK; g++) {
+                if (g < nch) {
+#pragma unroll
+                    for (int u = 0; u < ELL_CHUNK; u++) {
+                        const uint32_t en = ell_cur[g * ELL_CHUNK + u];
+                        const uint32_t nbo = en & 0xff8u, rco = (en >> 12) & 0xfff0u;
+                        const double dx = pos.x - *(const double *)(pbx + nbo);
+                        const double dy = pos.y - *(const double *)(pby + nbo);
+                        const double dz = pos.z - *(const double *)(pbz + nbo);
+                        const double2 kr = *(const double2 *)(prb + rco);
+                        double rest = kr.y;
+                        if (ACTIVE) {
+                            const int ty = (en >> ELL_TYPE_SHIFT) & 3;
+                            if (ty) rest = kr.y * actuation_scale<P>(ty + 1, *(const double *)(omb + (rco >> 1)), t_sim);
+                        }
+                        const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
+                        const double inv = rsqrt_fast(L2);
+                        const double L = L2 * inv;
+                        double coef = kr.x * (rest - L);
+                        if (DAMPING) {   // dot(v_left - v_right, dir) * damping along dir; symmetric in the endpoints
+                            const double dvx = *(const double *)(vbx + nbo) - vel.x, dvy = *(const double *)(vby + nbo) - vel.y,
+                                         dvz = *(const double *)(vbz + nbo) - vel.z;
+                            coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * inv, *(const double *)(dmb + (rco >> 1)), coef);
+                        }
+                        coef *= inv;
+                        coef = (en & ELL_VALID) ? coef : 0.0;
+                        force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
+                    }
                 }
             }
         }
-    }
+        if (TPM > 1) {   // hand the partial sums to thread q == 0 of the mass, which adds them in a fixed order
+            double *part = reinterpret_cast<double *>(smem + sp.off_part + s * sp.part_bytes);
+            const int bar_id = 1 + (t >> 5) + (TM / 32) * s;
+            if (q > 0) {
+                part[((q - 1) * 3 + 0) * TM + t] = force.x; part[((q - 1) * 3 + 1) * TM + t] = force.y; part[((q - 1) * 3 + 2) * TM + t] = force.z;
+                named_bar_arrive(bar_id, 32 * TPM);
+            } else {
+                named_bar_sync(bar_id, 32 * TPM);
+#pragma unroll
+                for (int qq = 1; qq < TPM; qq++) {
+                    force.x = P::add(force.x, part[((qq - 1) * 3 + 0) * TM + t]);
+                    force.y = P::add(force.y, part[((qq - 1) * 3 + 1) * TM + t]);
+                    force.z = P::add(force.z, part[((qq - 1) * 3 + 2) * TM + t]);
+                }
+            }
+        }
 
-    // ---- phase C: mass update ----------------------------------------------------------------------------
-    const bool extras = X.ext || X.drag || (fl & F_LOCAL) || WRITE_ACC;
-    const int64_t i_api = extras ? A.slot_to_api[slot] : 0;
-    V3 acc;
-    mass_update<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force, acc);
-    A.pos_out[slot] = pos.x; A.pos_out[n + slot] = pos.y; A.pos_out[2 * n + slot] = pos.z;
-    A.vel_out[slot] = vel.x; A.vel_out[n + slot] = vel.y; A.vel_out[2 * n + slot] = vel.z;
-    if (WRITE_ACC) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
+        // ---- mass update (one thread per mass) ---------------------------------------------------------------
+        if (q == 0) {
+            const int64_t tile = tile_of(i);
+            double *ob = A.st_out + tile * STATE_BLOCK + t;
+            if (live) {
+                const double mass = reinterpret_cast<const double *>(stage + BLOB_M)[t];
+                const bool extras = X.ext || X.drag || (fl & F_LOCAL) || A.write_acc;
+                const int64_t i_api = extras ? A.slot_to_api[tile * TM + t] : 0;
+                V3 acc;
+                mass_update<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force, acc);
+                if (A.write_acc) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
+            }
+            ob[0] = pos.x; ob[TM] = pos.y; ob[2 * TM] = pos.z;
+            ob[3 * TM] = vel.x; ob[4 * TM] = vel.y; ob[5 * TM] = vel.z;
+        }
+        __syncwarp();
+        if ((tid & 31) == 0) mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
+#pragma unroll
+        for (int jj = 0; jj < EPT; jj++) ell_cur[jj] = ell_nxt[jj];
+    }
 }
 
 // ---------------------------------------------------------------- glue ------------------------------------
-template <class P, bool D, bool AC, bool W>
-static int launch_v(Engine *e, const TiledArgs &A, const MassExtras &X, size_t smem, unsigned grid) {
-    static bool configured = false;     // per template instantiation
-    if (!configured) {
-        TB_CUDA(e, cudaFuncSetAttribute(tiled_step_kernel<P, D, AC, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BUDGET));
-        configured = true;
+template <class P, bool D, bool AC, int TPM>
+static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
+    static size_t configured_smem = 0;     // per template instantiation
+    static int blocks_per_sm = 0;
+    auto kern = tiled_step_kernel<P, D, AC, TPM>;
+    if (configured_smem != S->smem_bytes) {
+        TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S->smem_bytes));
+        TB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, TM * TPM + 32, S->smem_bytes));
+        if (blocks_per_sm < 1) return fail(e, TB_ERR_CUDA, "tiled step kernel does not fit on an SM (%zu bytes of shared memory)", S->smem_bytes);
+        configured_smem = S->smem_bytes;
     }
-    tiled_step_kernel<P, D, AC, W><<<grid, TM, smem, e->stream>>>(A, e->G, X);
+    int64_t grid = std::min<int64_t>(S->n_tiles, (int64_t)e->sm_count * blocks_per_sm);
+    if (const char *g = getenv("TB_GRID")) { int v = atoi(g); if (v > 0) grid = std::min<int64_t>(S->n_tiles, v); }
+    S->grid = (int)grid;
+    kern<<<(unsigned)grid, TM * TPM + 32, S->smem_bytes, e->stream>>>(A, e->G, X);
     return TB_OK;
 }
-template <class P, bool D, bool AC>
-static int launch_w(Engine *e, const TiledArgs &A, const MassExtras &X, size_t smem, unsigned grid, bool w) {
-    return w ? launch_v<P, D, AC, true>(e, A, X, smem, grid) : launch_v<P, D, AC, false>(e, A, X, smem, grid);
-}
-template <class P> static int launch_p(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X, unsigned grid, bool w) {
+template <class P, int TPM> static int launch_f(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     bool d = S->has_damping, a = S->has_active;
-    size_t smem = S->smem_bytes;
-    if (d && a) return launch_w<P, true, true>(e, A, X, smem, grid, w);
-    if (d) return launch_w<P, true, false>(e, A, X, smem, grid, w);
-    if (a) return launch_w<P, false, true>(e, A, X, smem, grid, w);
-    return launch_w<P, false, false>(e, A, X, smem, grid, w);
+    if (d && a) return launch_v<P, true, true, TPM>(e, S, A, X);
+    if (d) return launch_v<P, true, false, TPM>(e, S, A, X);
+    if (a) return launch_v<P, false, true, TPM>(e, S, A, X);
+    return launch_v<P, false, false, TPM>(e, S, A, X);
 }
 
 bool tiled_supported(const Engine *e) {
@@ -424,15 +749,16 @@ int tiled_prepare(Engine *e) {
         stale |= TS_PARAMS | TS_STATE | TS_FLAGS;
     }
     if (!S->supported) return TB_OK;
-    unsigned gs = (unsigned)((S->n_slots + 255) / 256), gr = (unsigned)((S->n_rec + 255) / 256);
+    unsigned gs = (unsigned)((S->n_slots + 255) / 256);
     if (stale & TS_STATE) {
         if (e->canon_stale && !(stale & TS_STRUCT)) TB_TRY(tiled_to_canonical(e));  // partial upload landed in canonical
-        tiled_gather_state<<<gs, 256, 0, e->stream>>>(S->pos[e->cur], S->vel[e->cur], S->m, e->pos[e->cur], e->vel[e->cur], e->m,
-                                                       S->slot_to_api, S->n_slots, e->nm);
+        tiled_gather_state<<<gs, 256, 0, e->stream>>>(S->st[e->cur], e->pos[e->cur], e->vel[e->cur], S->slot_to_api, S->n_slots, e->nm);
     }
-    if (stale & TS_FLAGS) tiled_gather_flags<<<gs, 256, 0, e->stream>>>(S->flags, e->mflags, S->slot_to_api, S->n_slots);
+    if (stale & (TS_FLAGS | TS_STATE))
+        tiled_refresh_mass<<<(unsigned)S->n_tiles, TM, 0, e->stream>>>(S->blob, S->meta, S->slot_to_api, e->m, e->mflags);
     if (stale & TS_PARAMS)
-        tiled_gather_params<<<gr, 256, 0, e->stream>>>(S->prm, S->dmp, S->omg, S->rec_spring, e->k, e->rest, e->damping, e->omega, S->n_rec);
+        tiled_refresh_params<<<(unsigned)S->n_tiles, 128, 0, e->stream>>>(S->blob, S->meta, S->rec_spring, e->k, e->rest, e->damping,
+                                                                          e->omega, S->has_damping ? 1 : 0, S->has_active ? 1 : 0);
     TB_CUDA(e, cudaGetLastError());
     e->tiled_stale = 0;
     return TB_OK;
@@ -442,13 +768,12 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     TiledState *S = e->tiled;
     if (!S || !S->supported) return fail(e, TB_ERR_INVALID, "tiled step requested without a tiled layout");
     TiledArgs A;
-    A.n_slots = S->n_slots;
-    A.nl = (TM + S->max_halo + 1) & ~1;
-    A.max_rec = S->max_rec;
-    A.pos_in = S->pos[e->cur]; A.vel_in = S->vel[e->cur];
-    A.pos_out = S->pos[e->cur ^ 1]; A.vel_out = S->vel[e->cur ^ 1];
-    A.m = S->m; A.flags = S->flags; A.slot_to_api = S->slot_to_api; A.halo = S->halo; A.ell = S->ell;
-    A.prm = S->prm; A.dmp = S->dmp; A.omg = S->omg; A.meta = S->meta; A.acc = e->acc;
+    A.n_tiles = (int32_t)S->n_tiles;
+    A.write_acc = write_acc ? 1 : 0;
+    A.sp = plan_smem(S->max_halo, S->max_blob, S->stage_vel, S->tpm);
+    A.st_in = S->st[e->cur]; A.st_out = S->st[e->cur ^ 1];
+    A.blob = S->blob; A.slot_to_api = S->slot_to_api; A.halo = S->halo; A.ell = S->ell; A.meta = S->meta;
+    A.acc = e->acc;
     A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + (e->cur ^ 1);
     MassExtras X;
     X.ext = (use_ext && e->ext) ? e->ext : nullptr;
@@ -456,8 +781,11 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     X.lc_ptr = e->any_local ? e->lc_ptr : nullptr;
     X.lc = e->lc;
     X.nm = e->nm;
-    unsigned grid = (unsigned)S->n_tiles;
-    int rc = (e->flags & TB_MATH_STRICT) ? launch_p<Strict>(e, S, A, X, grid, write_acc) : launch_p<Fast>(e, S, A, X, grid, write_acc);
+    int rc;
+    if (e->flags & TB_MATH_STRICT) rc = launch_f<Strict, 1>(e, S, A, X);
+    else if (S->tpm == 4) rc = launch_f<Fast, 4>(e, S, A, X);
+    else if (S->tpm == 2) rc = launch_f<Fast, 2>(e, S, A, X);
+    else rc = launch_f<Fast, 1>(e, S, A, X);
     if (rc != TB_OK) return rc;
     TB_CUDA(e, cudaGetLastError());
     return TB_OK;
@@ -467,7 +795,7 @@ int tiled_to_canonical(Engine *e) {
     TiledState *S = e->tiled;
     if (S && S->supported && S->n_slots > 0 && e->canon_stale) {
         tiled_scatter_state<<<(unsigned)((S->n_slots + 255) / 256), 256, 0, e->stream>>>(
-            e->pos[e->cur], e->vel[e->cur], S->pos[e->cur], S->vel[e->cur], S->slot_to_api, S->n_slots, e->nm);
+            e->pos[e->cur], e->vel[e->cur], S->st[e->cur], S->slot_to_api, S->n_slots, e->nm);
         TB_CUDA(e, cudaGetLastError());
         TB_CUDA(e, cudaStreamSynchronize(e->stream));
     }
@@ -482,8 +810,17 @@ void tiled_destroy(Engine *e) {
     e->tiled = nullptr;
 }
 
-int tiled_info(const Engine *e, int32_t *n_tiles) {
-    *n_tiles = (e->tiled && e->tiled->supported) ? (int32_t)e->tiled->n_tiles : 0;
+int tiled_info(const Engine *e, tb_info *info) {
+    const TiledState *S = e->tiled;
+    if (!S || !S->supported) return TB_OK;
+    info->n_tiles = (int32_t)S->n_tiles;
+    info->threads_per_mass = S->tpm;
+    info->grid = S->grid;
+    info->smem_bytes = (int32_t)S->smem_bytes;
+    info->ell_unique_tiles = (int32_t)S->ell_unique_tiles;
+    // read: blob + own state + halo gathers + halo lists + ELL words + meta; written: own state
+    info->tiled_bytes_per_step = (int64_t)S->blob_bytes + 2 * S->n_tiles * STATE_BLOCK * 8 + S->n_halo * (4 + (S->stage_vel ? 48 : 24)) +
+                                 S->n_tiles * (int64_t)sizeof(TileMeta) + S->n_ell * 4;
     return TB_OK;
 }
 

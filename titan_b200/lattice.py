@@ -83,3 +83,36 @@ def build_lattice(center, dims, nx, ny, nz):
         for a in range(0, left.size, 20_000_000):
             rest[a:a + 20_000_000] = rest_lengths(pos, left[a:a + 20_000_000], right[a:a + 20_000_000])
     return dict(pos=pos, left=left, right=right, rest=rest)
+
+
+def brick_dims(nx, ny, nz, tile=128):
+    """Brick edge lengths (bx, by, bz), bx*by*bz <= tile, for tiling an nx x ny x nz lattice, minimising the
+    modelled bytes per step: every tile streams `tile` mass slots (padding included), one record per spring
+    touching it (cut springs are stored by both bricks) and its halo positions."""
+    best = None
+    for bx in range(1, min(nx, tile) + 1):
+        for by in range(1, min(ny, tile // bx) + 1):
+            bz = min(nz, tile // (bx * by))
+            if bz < 1:
+                continue
+            tiles = -(-nx // bx) * -(-ny // by) * -(-nz // bz)
+            a, b, c = bx - 1, by - 1, bz - 1
+            inner = (a * by * bz + bx * b * bz + bx * by * c) + 2 * (a * b * bz + a * by * c + bx * b * c) + 4 * a * b * c
+            recs = 26 * bx * by * bz - inner
+            halo = (bx + 2) * (by + 2) * (bz + 2) - bx * by * bz
+            cost = tiles * (tile * 104 + 16 * recs + 24 * halo)
+            key = (cost, bx, by, -bz)
+            if best is None or key < best[0]:
+                best = (key, (bx, by, bz))
+    return best[1]
+
+
+def brick_hint(nx, ny, nz, tile=128, base=0):
+    """Tile id per mass (reference mass order, i outermost) for tb_set_tile_hint: bricks of lattice cells."""
+    bx, by, bz = brick_dims(nx, ny, nz, tile)
+    ti = np.arange(nx, dtype=np.int64) // bx
+    tj = np.arange(ny, dtype=np.int64) // by
+    tk = np.arange(nz, dtype=np.int64) // bz
+    ntj, ntk = -(-ny // by), -(-nz // bz)
+    ids = (ti[:, None, None] * ntj + tj[None, :, None]) * ntk + tk[None, None, :]
+    return (ids.reshape(-1) + base).astype(np.int32)
