@@ -47,7 +47,7 @@ def workload_c2(n=100):
     side = 0.1 * (n - 1)
     L = lattice.build_lattice((0.0, 0.0, side / 2 - 0.001), (side, side, side), n, n, n)
     L["plane"] = ((0.0, 0.0, 1.0), 0.0, 0.5, 0.6)
-    L["tile_hint"] = lattice.brick_hint(n, n, n)
+    L["tile_hint"] = lattice.brick_hint(n, n, n, tile=int(os.environ.get("TB_TILE", "128")))
     L["name"] = "C2: %d^3 lattice on frictional plane (k=1e4, m=0.1, dt=1e-4, g=-9.81)" % n
     return L
 

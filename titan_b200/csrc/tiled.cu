@@ -24,6 +24,7 @@
 #include "engine.h"
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <map>
@@ -43,6 +44,7 @@ constexpr uint32_t ELL_SIDE = 1u << 30, ELL_VALID = 1u << 31;
 constexpr int MAX_DEG = 32;             // ELL rows are held in registers; more incident springs -> CSR kernel
 constexpr int MAX_LOCAL = 512;
 constexpr int MAX_REC = 4096;
+constexpr int CS_SMALL = 384, CS_BIG = MAX_LOCAL;   // shared-memory stride of one position component (see plan_smem)
 constexpr int ELL_CHUNK = 4;            // springs evaluated together, branch-free, by one thread (ILP)
 
 // Which of a mass's TPM threads takes which ELL rows, in chunks of ELL_CHUNK rows (blocks are padded with zero
@@ -91,7 +93,7 @@ struct TiledState {
     int max_halo = 0, max_rec = 0, max_deg = 0, max_blob = 0;
     int64_t ell_unique_tiles = 0;
     bool has_damping = false, has_active = false, stage_vel = false;
-    int tpm = 4, grid = 0;
+    int tpm = 4, grid = 0, cs = CS_BIG;
     size_t smem_bytes = 0;
     // device
     double *st[2] = {nullptr, nullptr};   // tile-blocked state, ping-pong
@@ -169,10 +171,14 @@ struct SmemPlan {            // byte offsets inside the dynamic shared memory of
     int32_t total;
 };
 // mbarriers at offset 0: full[2], empty[2], hfull[HALO_RING]
-static SmemPlan plan_smem(int max_halo, int max_blob, bool stage_vel, int tpm) {
+// Position component stride is a compile-time constant of the kernel (CS_SMALL or CS_BIG doubles) so that the
+// y and z reads are immediate offsets from the x address.  Local index cs-1 is the DUMMY mass (far away, never
+// written by a copy): padding ELL words point at it and at record 0 (k = 0), and so contribute exactly zero.
+static int choose_cs(int max_halo, bool strict) { return (!strict && TM + max_halo + 1 <= CS_SMALL) ? CS_SMALL : CS_BIG; }
+static SmemPlan plan_smem(int cs, int max_halo, int max_blob, bool stage_vel, int tpm) {
     SmemPlan p;
     int hp = (max_halo + 3) & ~3;
-    p.cs = TM + hp;
+    p.cs = cs;
     p.vs = stage_vel ? p.cs : TM;
     p.hring_stride = (int32_t)up16((size_t)hp * 4 + 16);
     p.off_ctrl = 64;
@@ -210,9 +216,12 @@ static size_t blob_size(int n_rec, bool damping, bool active) {
     return up16((size_t)BLOB_REC + (size_t)n_rec * 16) + (damping ? np * 8 : 0) + (active ? np * 8 : 0);
 }
 
-static int choose_tpm(const Engine *e) {
-    if (e->flags & TB_MATH_STRICT) return 1;   // one thread per mass: the oracle's summation order
-    int tpm = 4;
+// Threads per mass.  Strict arithmetic needs the oracle's summation order (1).  Otherwise: big problems keep
+// every SM busy with one thread per mass (fewest instructions and hand-offs; measured best on C2), small ones
+// (fewer tiles than resident CTAs) are latency bound and split each mass's springs over 4 threads.
+static int choose_tpm(const Engine *e, int64_t n_tiles) {
+    if (e->flags & TB_MATH_STRICT) return 1;
+    int tpm = n_tiles >= 2 * (int64_t)e->sm_count ? 1 : 4;
     if (const char *s = getenv("TB_TPM")) { int v = atoi(s); if (v == 1 || v == 2 || v == 4) tpm = v; }
     return tpm;
 }
@@ -237,7 +246,7 @@ static int build_structure(Engine *e, TiledState *S) {
 
     S->has_damping = e->any_damping; S->has_active = e->any_active;
     S->stage_vel = S->has_damping || (e->flags & TB_MATH_STRICT);
-    S->tpm = choose_tpm(e);
+    S->tpm = choose_tpm(e, n_tiles);
 
     std::vector<TileMeta> meta((size_t)n_tiles);
     std::vector<uint32_t> ell, block;
@@ -247,6 +256,7 @@ static int build_structure(Engine *e, TiledState *S) {
     std::vector<int32_t> rec_stamp((size_t)e->ns, -1), rec_local((size_t)e->ns, 0);
     struct Half { int32_t s; int32_t o; uint8_t side; };
     std::vector<std::vector<Half>> rows(TM);
+    std::vector<int32_t> th;   // halo list of the tile being built (-1 = hole)
     int max_halo = 0, max_rec = 0, max_deg = 0;
     size_t blob_total = 0, max_blob = 0;
     int64_t unique_blocks = 0;
@@ -273,23 +283,64 @@ static int build_structure(Engine *e, TiledState *S) {
         M.halo_off = (uint32_t)halo.size();
         M.rec_off = (uint32_t)rec_spring.size();
         block.assign((size_t)ell_chunks(deg) * ELL_CHUNK * TM, 0u);   // zero rows pad the last chunk
-        int n_halo = 0, n_rec = 0;
+        int n_rec = 1;
+        rec_spring.push_back(-1);                                 // record 0: k = 0, read by padding ELL words
+        // Halo slots are chosen so that the 16 lanes of a half-warp reading row j hit 16 different shared-memory
+        // bank pairs (an LDS.64 conflict costs a replay).  Own neighbours sit at local index t + c_j (c_j = the
+        // row's dominant offset), so a foreign mass met by lane t in row j wants a slot = t + c_j (mod 16): on a
+        // lattice brick every row that reaches the mass asks for the same residue (the brick's linear index
+        // extended over its shell), which makes every row conflict-free.  Other graphs fall back to the lowest
+        // free slot whose residue no lane of the half-warp uses.  Unused slots (holes) are not gathered.
+        th.clear();
+        for (int j = 0; j < deg; j++) {
+            int votes[16] = {0}, cj = -1, best = 0;
+            for (int t = 0; t < TM; t++) {
+                if (j >= (int)rows[t].size()) continue;
+                int32_t oslot = S->h_api_to_slot[(size_t)rows[t][(size_t)j].o];
+                if (oslot / TM == T) votes[((oslot % TM) - t) & 15]++;
+            }
+            for (int r = 0; r < 16; r++) if (votes[r] > best) { best = votes[r]; cj = r; }
+            for (int hw = 0; hw < TM / 16; hw++) {
+                uint32_t used = 0;
+                for (int t = hw * 16; t < hw * 16 + 16; t++) {
+                    if (j >= (int)rows[t].size()) continue;
+                    const Half &h = rows[t][(size_t)j];
+                    int32_t oslot = S->h_api_to_slot[(size_t)h.o];
+                    if (oslot / TM == T) used |= 1u << (oslot % 16);
+                    else if (halo_stamp[(size_t)h.o] == (int32_t)T) used |= 1u << (halo_local[(size_t)h.o] % 16);
+                }
+                for (int t = hw * 16; t < hw * 16 + 16; t++) {
+                    if (j >= (int)rows[t].size()) continue;
+                    const Half &h = rows[t][(size_t)j];
+                    int32_t oslot = S->h_api_to_slot[(size_t)h.o];
+                    if (oslot / TM == T || halo_stamp[(size_t)h.o] == (int32_t)T) continue;
+                    int pick = -1;
+                    if (cj >= 0) {
+                        const int want = (t + cj) & 15;
+                        for (int x = want; pick < 0; x += 16) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
+                    } else {
+                        for (int x = 0; x < (int)th.size() + 16 && pick < 0; x++) {
+                            bool free_slot = x >= (int)th.size() || th[(size_t)x] < 0;
+                            if (free_slot && (!((used >> (x % 16)) & 1u) || used == 0xffffu)) pick = x;
+                        }
+                    }
+                    if (pick >= (int)th.size()) th.resize((size_t)pick + 1, -1);
+                    th[(size_t)pick] = (int32_t)((int64_t)(oslot / TM) * STATE_BLOCK + oslot % TM);
+                    halo_stamp[(size_t)h.o] = (int32_t)T; halo_local[(size_t)h.o] = pick;
+                    used |= 1u << (pick % 16);
+                }
+            }
+        }
+        const int n_halo = (int)th.size();
+        for (int32_t x : th) halo.push_back(x);                   // -1 = hole, skipped by the gather
         for (int j = 0; j < deg; j++) for (int t = 0; t < TM; t++) {   // j-major walk: record slots of one row are consecutive
             if (j >= (int)rows[t].size()) continue;
             const Half &h = rows[t][(size_t)j];
             int32_t oslot = S->h_api_to_slot[(size_t)h.o];
-            int nb;
-            if (oslot / TM == T) nb = oslot % TM;
-            else {
-                if (halo_stamp[(size_t)h.o] != (int32_t)T) {
-                    halo_stamp[(size_t)h.o] = (int32_t)T; halo_local[(size_t)h.o] = n_halo++;
-                    halo.push_back((int32_t)((int64_t)(oslot / TM) * STATE_BLOCK + oslot % TM));
-                }
-                nb = TM + halo_local[(size_t)h.o];
-            }
+            const int nb = (oslot / TM == T) ? oslot % TM : TM + halo_local[(size_t)h.o];
             if (rec_stamp[(size_t)h.s] != (int32_t)T) { rec_stamp[(size_t)h.s] = (int32_t)T; rec_local[(size_t)h.s] = n_rec++; rec_spring.push_back(h.s); }
             int rec = rec_local[(size_t)h.s];
-            if (nb >= MAX_LOCAL || rec >= MAX_REC) { S->why_not = "a tile reaches too many foreign masses or springs"; return TB_OK; }
+            if (nb >= MAX_LOCAL - 1 || rec >= MAX_REC) { S->why_not = "a tile reaches too many foreign masses or springs"; return TB_OK; }
             uint32_t ty = 0;
             if (!e->h_type.empty()) { uint8_t x = e->h_type[(size_t)h.s]; ty = (x == 2) ? 1u : (x == 3) ? 2u : 0u; }
             block[(size_t)j * TM + (size_t)t] =
@@ -319,7 +370,13 @@ static int build_structure(Engine *e, TiledState *S) {
     }
     while (halo.size() % 4) halo.push_back(0);
     halo.resize(halo.size() + 4, 0);   // the last list may be copied rounded up to 16 bytes
-    SmemPlan plan = plan_smem(max_halo, (int)max_blob, S->stage_vel, S->tpm);
+    if (TM + max_halo + 1 > CS_BIG) { S->why_not = "a tile reaches too many foreign masses"; return TB_OK; }
+    S->cs = choose_cs(max_halo, (e->flags & TB_MATH_STRICT) != 0);
+    {   // padding words -> (dummy mass, record 0)
+        const uint32_t pad = (uint32_t)(S->cs - 1) << ELL_NB_SHIFT;
+        for (uint32_t &w : ell) if (!(w & ELL_VALID)) w = pad;
+    }
+    SmemPlan plan = plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm);
     if ((size_t)plan.total > SMEM_LIMIT) { S->why_not = "a tile's working set exceeds the shared-memory budget"; return TB_OK; }
     S->smem_bytes = (size_t)plan.total;
 
@@ -384,9 +441,9 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
     double *omg = dmp + (has_damping ? ((M.n_rec + 1) & ~1u) : 0);
     for (uint32_t r = threadIdx.x; r < M.n_rec; r += blockDim.x) {
         int32_t s = rec_spring[M.rec_off + r];
-        rec[r] = make_double2(k[s], rest[s]);
-        if (has_damping) dmp[r] = damping ? damping[s] : 0.0;
-        if (has_active) omg[r] = omega ? omega[s] : 0.0;
+        rec[r] = s >= 0 ? make_double2(k[s], rest[s]) : make_double2(0.0, 0.0);
+        if (has_damping) dmp[r] = (s >= 0 && damping) ? damping[s] : 0.0;
+        if (has_active) omg[r] = (s >= 0 && omega) ? omega[s] : 0.0;
     }
 }
 
@@ -443,6 +500,8 @@ template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile(
 struct TiledArgs {
     int32_t n_tiles;
     int32_t write_acc;
+    unsigned long long *prof;        // TB_PROFILE=1: per-phase clock64 sums (0 wait full, 1 springs, 2 partial-sum handoff, 3 mass update, 4 producer wait empty, 5 producer wait halo list, 6 producer issue, 7 ell-copy wait)
+    int32_t debug;                   // TB_DEBUG_SKIP bits (timing experiments only): 1 no halo gather, 2 no springs, 4 no mass update
     SmemPlan sp;
     const double *st_in;
     double *st_out;
@@ -455,7 +514,18 @@ struct TiledArgs {
     double *t_out;
 };
 
-struct TileCtrl { uint32_t next_ell_off, next_deg, has_next, pad; };   // producer -> consumers, one per stage
+// producer -> consumers, one per stage: where the NEXT tile's ELL words are and which chunks thread q takes
+// (first chunk / chunk count, one byte per q)
+struct TileCtrl { uint32_t next_ell_off, next_cb, next_nch, has_next; };
+__host__ __device__ inline void chunk_table(int deg, int tpm, uint32_t &cb_packed, uint32_t &nch_packed) {
+    const int n = ell_chunks(deg), c0 = ell_chunks0(n, tpm), cq = ell_chunks_q(n, tpm);
+    cb_packed = 0; nch_packed = (uint32_t)c0;
+    for (int q = 1; q < tpm; q++) {
+        int cb = c0 + (q - 1) * cq, nch = n - cb < cq ? n - cb : cq;
+        if (nch < 0) nch = 0;
+        cb_packed |= (uint32_t)cb << (8 * q); nch_packed |= (uint32_t)nch << (8 * q);
+    }
+}
 
 // Warp roles: warps 0 .. TM*TPM/32-1 are CONSUMERS (thread = (mass t, share q)); the last warp is the PRODUCER
 // that keeps the two stages filled.  Synchronisation is mbarrier-only between the roles:
@@ -463,7 +533,7 @@ struct TileCtrl { uint32_t next_ell_off, next_deg, has_next, pad; };   // produc
 //   empty[s] : one arrival per consumer warp when it has finished reading stage s
 //   hfull[r] : bulk copy of a halo index list (producer-internal)
 // plus one named barrier per 32-mass column and tile parity for handing the partial sums to thread q == 0.
-template <class P, bool DAMPING, bool ACTIVE, int TPM>
+template <class P, bool DAMPING, bool ACTIVE, int TPM, int CS>
 __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_kernel(const __grid_constant__ TiledArgs A,
                                                                    const __grid_constant__ Globals G,
                                                                    const __grid_constant__ MassExtras X) {
@@ -487,6 +557,11 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
+    if (tid < 2) {   // the dummy mass of both stages: far away, at rest
+        double *pp = reinterpret_cast<double *>(smem + sp.off_stage + tid * sp.stage_bytes + sp.st_pos);
+        pp[CS - 1] = 1e30; pp[2 * CS - 1] = 1e30; pp[3 * CS - 1] = 1e30;
+        if (STAGE_VEL) { double *vp = pp + 3 * CS; vp[CS - 1] = 0.0; vp[2 * CS - 1] = 0.0; vp[3 * CS - 1] = 0.0; }
+    }
     __syncthreads();
 
     if (tid >= NT) {
@@ -509,41 +584,52 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         int4 m0a, m0b, m1a, m1b, m2a, m2b, m3a, m3b;
         load_meta(0, m0a, m0b); load_meta(1, m1a, m1b); load_meta(2, m2a, m2b);
         if (lane == 0) { issue_hidx(0, m0a); if (n_my > 1) issue_hidx(1, m1a); }
+        long long pp0 = 0, pp1 = 0, pp2 = 0;
         for (int k = 0; k < n_my; k++) {
             const int s = k & 1;
             __syncwarp();
             load_meta(k + 3, m3a, m3b);
+            long long p0 = A.prof ? clock64() : 0;
             mbar_wait(bar_empty(s), (uint32_t)(((k >> 1) & 1) ^ 1));    // consumers are done with tile k-2
+            long long p1 = A.prof ? clock64() : 0;
             const uint32_t stage = smem_base + (uint32_t)(sp.off_stage + s * sp.stage_bytes);
             if (lane == 0) {
                 TileCtrl *c = reinterpret_cast<TileCtrl *>(smem + sp.off_ctrl) + s;
-                c->next_ell_off = (uint32_t)m1b.x; c->next_deg = (uint32_t)m1b.y; c->has_next = (k + 1 < n_my) ? 1u : 0u; c->pad = 0;
+                uint32_t cbp, nchp;
+                chunk_table(m1b.y, TPM, cbp, nchp);
+                c->next_ell_off = (uint32_t)m1b.x; c->next_cb = cbp; c->next_nch = nchp; c->has_next = (k + 1 < n_my) ? 1u : 0u;
                 mbar_expect_tx(bar_full(s), (uint32_t)m0a.y + (uint32_t)(STATE_BLOCK * 8));
                 bulk_g2s(stage, A.blob + (size_t)(uint32_t)m0a.x * 16, (uint32_t)m0a.y, bar_full(s));
                 const double *sb = A.st_in + tile_of(k) * STATE_BLOCK;
 #pragma unroll
                 for (int c3 = 0; c3 < 3; c3++) {
-                    bulk_g2s(stage + (uint32_t)(sp.st_pos + c3 * sp.cs * 8), sb + c3 * TM, TM * 8, bar_full(s));
+                    bulk_g2s(stage + (uint32_t)(sp.st_pos + c3 * CS * 8), sb + c3 * TM, TM * 8, bar_full(s));
                     bulk_g2s(stage + (uint32_t)(sp.st_vel + c3 * sp.vs * 8), sb + (3 + c3) * TM, TM * 8, bar_full(s));
                 }
                 if (k + 2 < n_my) issue_hidx(k + 2, m2a);
             }
             // halo gather of tile k: the index list was bulk-copied two tiles ago
+            long long p2 = A.prof ? clock64() : 0;
             mbar_wait(bar_halo(k % HALO_RING), (uint32_t)((k / HALO_RING) & 1));
+            long long p3 = A.prof ? clock64() : 0;
             const int n_halo = m0a.w;
             const int32_t *hl = reinterpret_cast<const int32_t *>(smem + sp.off_hring + (k % HALO_RING) * sp.hring_stride);
-            for (int h = lane; h < n_halo; h += 32) {
-                const double *src = A.st_in + hl[h];
+            for (int h = lane; h < ((A.debug & 1) ? 0 : n_halo); h += 32) {
+                const int32_t hi = hl[h];
+                if (hi < 0) continue;
+                const double *src = A.st_in + hi;
                 const uint32_t d = stage + (uint32_t)(sp.st_pos + (TM + h) * 8);
-                cp_async8(d, src); cp_async8(d + (uint32_t)(sp.cs * 8), src + TM); cp_async8(d + (uint32_t)(2 * sp.cs * 8), src + 2 * TM);
+                cp_async8(d, src); cp_async8(d + (uint32_t)(CS * 8), src + TM); cp_async8(d + (uint32_t)(2 * CS * 8), src + 2 * TM);
                 if (STAGE_VEL) {
                     const uint32_t dv = stage + (uint32_t)(sp.st_vel + (TM + h) * 8);
                     cp_async8(dv, src + 3 * TM); cp_async8(dv + (uint32_t)(sp.vs * 8), src + 4 * TM); cp_async8(dv + (uint32_t)(2 * sp.vs * 8), src + 5 * TM);
                 }
             }
             cp_async_arrive_noinc(bar_full(s));
+            if (A.prof) { long long p4 = clock64(); pp0 += p1 - p0; pp1 += p3 - p2; pp2 += (p2 - p1) + (p4 - p3); }
             m0a = m1a; m0b = m1b; m1a = m2a; m1b = m2b; m2a = m3a; m2b = m3b;
         }
+        if (A.prof && lane == 0) { atomicAdd(A.prof + 4, (unsigned long long)pp0); atomicAdd(A.prof + 5, (unsigned long long)pp1); atomicAdd(A.prof + 6, (unsigned long long)pp2); }
         return;
     }
 
@@ -551,19 +637,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     const int t = tid % TM, q = tid / TM;
     const double t_sim = *A.t_in;
     // this thread's ELL words: chunks [cb, cb + nch) of the tile's block, rows of TM words
-    auto my_chunks = [&](int deg, int &cb, int &nch) {
-        const int n = ell_chunks(deg), c0 = ell_chunks0(n, TPM);
-        if (q == 0) { cb = 0; nch = c0; }
-        else {
-            const int cq = ell_chunks_q(n, TPM);
-            cb = c0 + (q - 1) * cq;
-            nch = n - cb < cq ? n - cb : cq;
-            if (nch < 0) nch = 0;
-        }
-    };
-    auto load_ell = [&](uint32_t ell_off, int deg, uint32_t (&dst)[EPT]) {
-        int cb, nch;
-        my_chunks(deg, cb, nch);
+    auto load_ell = [&](uint32_t ell_off, int cb, int nch, uint32_t (&dst)[EPT]) {
         const uint32_t *src = A.ell + ell_off + (size_t)cb * ELL_CHUNK * TM + t;
 #pragma unroll
         for (int g = 0; g < EPT / ELL_CHUNK; g++)
@@ -575,23 +649,33 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     uint32_t ell_cur[EPT], ell_nxt[EPT];
 #pragma unroll
     for (int jj = 0; jj < EPT; jj++) { ell_cur[jj] = 0u; ell_nxt[jj] = 0u; }
+    int nch = 0, nch_nxt = 0;
     {
         const TileMeta *m0 = A.meta + tile_of(0);
-        load_ell(__ldg(&m0->ell_off), (int)__ldg(&m0->deg), ell_cur);
+        uint32_t cbp, nchp;
+        chunk_table((int)__ldg(&m0->deg), TPM, cbp, nchp);
+        nch = (int)((nchp >> (8 * q)) & 0xff);
+        load_ell(__ldg(&m0->ell_off), (int)((cbp >> (8 * q)) & 0xff), nch, ell_cur);
     }
 
+    long long pa0 = 0, pa1 = 0, pa2 = 0, pa3 = 0, pa4 = 0;
     for (int i = 0; i < n_my; i++) {
         const int s = i & 1;
+        long long c0 = A.prof ? clock64() : 0;
         mbar_wait(bar_full(s), (uint32_t)((i >> 1) & 1));     // blob, own state and halo of tile i have landed
+        long long c1 = A.prof ? clock64() : 0;
         const unsigned char *stage = smem + sp.off_stage + s * sp.stage_bytes;
         const TileCtrl ctrl = reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl)[s];
-        if (ctrl.has_next) load_ell(ctrl.next_ell_off, (int)ctrl.next_deg, ell_nxt);   // next tile's words -> registers
-        const int deg = reinterpret_cast<const int32_t *>(stage)[0], n_rec = reinterpret_cast<const int32_t *>(stage)[2];
+        if (ctrl.has_next) {   // next tile's words -> registers
+            nch_nxt = (int)((ctrl.next_nch >> (8 * q)) & 0xff);
+            load_ell(ctrl.next_ell_off, (int)((ctrl.next_cb >> (8 * q)) & 0xff), nch_nxt, ell_nxt);
+        }
+        const int n_rec = reinterpret_cast<const int32_t *>(stage)[2];
         const uint8_t fl = stage[BLOB_FLAGS + t];
         const char *prb = reinterpret_cast<const char *>(stage + BLOB_REC);
         const char *dmb = prb + (size_t)n_rec * 16;
         const char *omb = dmb + (DAMPING ? ((n_rec + 1) & ~1) * 8 : 0);
-        const char *pbx = reinterpret_cast<const char *>(stage + sp.st_pos), *pby = pbx + sp.cs * 8, *pbz = pby + sp.cs * 8;
+        const char *pbx = reinterpret_cast<const char *>(stage + sp.st_pos), *pby = pbx + CS * 8, *pbz = pby + CS * 8;
         const char *vbx = reinterpret_cast<const char *>(stage + sp.st_vel), *vby = vbx + sp.vs * 8, *vbz = vby + sp.vs * 8;
         V3 pos = {reinterpret_cast<const double *>(pbx)[t], reinterpret_cast<const double *>(pby)[t], reinterpret_cast<const double *>(pbz)[t]};
         V3 vel = {0.0, 0.0, 0.0};
@@ -600,8 +684,6 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
 
         // ---- gather this thread's share of the incident springs, ascending row order ------------------------
         V3 force = {0.0, 0.0, 0.0};
-        int cb, nch;
-        my_chunks(deg, cb, nch);
         if (P::strict) {
             if (live) {
 #pragma unroll
@@ -631,14 +713,15 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             // force on this mass = (p_me - p_other) * coef whichever endpoint it is (see physics.cuh)
 #pragma unroll
             for (int g = 0; g < EPT / ELL_CHUNK; g++) {
-                if (g < nch) {
+                if (g < nch && !(A.debug & 2)) {
 #pragma unroll
                     for (int u = 0; u < ELL_CHUNK; u++) {
                         const uint32_t en = ell_cur[g * ELL_CHUNK + u];
                         const uint32_t nbo = en & 0xff8u, rco = (en >> 12) & 0xfff0u;
-                        const double dx = pos.x - *(const double *)(pbx + nbo);
-                        const double dy = pos.y - *(const double *)(pby + nbo);
-                        const double dz = pos.z - *(const double *)(pbz + nbo);
+                        const char *pn = pbx + nbo;
+                        const double dx = pos.x - *(const double *)(pn);
+                        const double dy = pos.y - *(const double *)(pn + CS * 8);
+                        const double dz = pos.z - *(const double *)(pn + 2 * CS * 8);
                         const double2 kr = *(const double2 *)(prb + rco);
                         double rest = kr.y;
                         if (ACTIVE) {
@@ -647,20 +730,19 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                         }
                         const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
                         const double inv = rsqrt_fast(L2);
-                        const double L = L2 * inv;
-                        double coef = kr.x * (rest - L);
+                        // k (rest - L) / L = k (rest / L - 1); padding words read k = 0 and the far dummy mass
+                        double coef = kr.x * fma(rest, inv, -1.0);
                         if (DAMPING) {   // dot(v_left - v_right, dir) * damping along dir; symmetric in the endpoints
                             const double dvx = *(const double *)(vbx + nbo) - vel.x, dvy = *(const double *)(vby + nbo) - vel.y,
                                          dvz = *(const double *)(vbz + nbo) - vel.z;
-                            coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * inv, *(const double *)(dmb + (rco >> 1)), coef);
+                            coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * (inv * inv), *(const double *)(dmb + (rco >> 1)), coef);
                         }
-                        coef *= inv;
-                        coef = (en & ELL_VALID) ? coef : 0.0;
                         force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
                     }
                 }
             }
         }
+        long long c2 = A.prof ? clock64() : 0;
         if (TPM > 1) {   // hand the partial sums to thread q == 0 of the mass, which adds them in a fixed order
             double *part = reinterpret_cast<double *>(smem + sp.off_part + s * sp.part_bytes);
             const int bar_id = 1 + (t >> 5) + (TM / 32) * s;
@@ -678,11 +760,12 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             }
         }
 
+        long long c3 = A.prof ? clock64() : 0;
         // ---- mass update (one thread per mass) ---------------------------------------------------------------
         if (q == 0) {
             const int64_t tile = tile_of(i);
             double *ob = A.st_out + tile * STATE_BLOCK + t;
-            if (live) {
+            if (live && !(A.debug & 4)) {
                 const double mass = reinterpret_cast<const double *>(stage + BLOB_M)[t];
                 const bool extras = X.ext || X.drag || (fl & F_LOCAL) || A.write_acc;
                 const int64_t i_api = extras ? A.slot_to_api[tile * TM + t] : 0;
@@ -694,18 +777,33 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             ob[3 * TM] = vel.x; ob[4 * TM] = vel.y; ob[5 * TM] = vel.z;
         }
         __syncwarp();
+        long long c4 = A.prof ? clock64() : 0;
         if ((tid & 31) == 0) mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
 #pragma unroll
         for (int jj = 0; jj < EPT; jj++) ell_cur[jj] = ell_nxt[jj];
+        nch = nch_nxt;
+        if (A.prof) {
+            unsigned sink = 0;
+#pragma unroll
+            for (int jj = 0; jj < EPT; jj++) sink ^= ell_cur[jj];
+            if (sink == 0x12345u) c4++;                       // forces the pending ELL loads to land before c5
+            long long c5 = clock64();
+            pa0 += c1 - c0; pa1 += c2 - c1; pa2 += c3 - c2; pa3 += c4 - c3; pa4 += c5 - c4;
+        }
+    }
+    if (A.prof && (tid & 31) == 0) {
+        unsigned long long *pp = A.prof + 8 * (q > 0);
+        atomicAdd(pp + 0, (unsigned long long)pa0); atomicAdd(pp + 1, (unsigned long long)pa1); atomicAdd(pp + 2, (unsigned long long)pa2);
+        atomicAdd(pp + 3, (unsigned long long)pa3); atomicAdd(pp + 7, (unsigned long long)pa4);
     }
 }
 
 // ---------------------------------------------------------------- glue ------------------------------------
-template <class P, bool D, bool AC, int TPM>
-static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
+template <class P, bool D, bool AC, int TPM, int CS>
+static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     static size_t configured_smem = 0;     // per template instantiation
     static int blocks_per_sm = 0;
-    auto kern = tiled_step_kernel<P, D, AC, TPM>;
+    auto kern = tiled_step_kernel<P, D, AC, TPM, CS>;
     if (configured_smem != S->smem_bytes) {
         TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S->smem_bytes));
         TB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, TM * TPM + 32, S->smem_bytes));
@@ -717,6 +815,11 @@ static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtr
     S->grid = (int)grid;
     kern<<<(unsigned)grid, TM * TPM + 32, S->smem_bytes, e->stream>>>(A, e->G, X);
     return TB_OK;
+}
+template <class P, bool D, bool AC, int TPM>
+static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
+    if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG>(e, S, A, X);
+    return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL)>(e, S, A, X);
 }
 template <class P, int TPM> static int launch_f(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     bool d = S->has_damping, a = S->has_active;
@@ -733,7 +836,10 @@ bool tiled_supported(const Engine *e) {
     return true;
 }
 
+static unsigned long long *g_prof_dev = nullptr;
+static long long g_prof_launches = 0;
 int tiled_prepare(Engine *e) {
+    if (getenv("TB_PROFILE") && !g_prof_dev) { cudaMalloc((void **)&g_prof_dev, 16 * 8); cudaMemset(g_prof_dev, 0, 16 * 8); }
     if (!e->tiled) e->tiled = new TiledState();
     TiledState *S = e->tiled;
     uint32_t stale = e->tiled_stale;
@@ -770,7 +876,13 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     TiledArgs A;
     A.n_tiles = (int32_t)S->n_tiles;
     A.write_acc = write_acc ? 1 : 0;
-    A.sp = plan_smem(S->max_halo, S->max_blob, S->stage_vel, S->tpm);
+    A.prof = nullptr;
+    if (getenv("TB_PROFILE")) {
+        A.prof = g_prof_dev; g_prof_launches++;
+    }
+    A.debug = 0;
+    if (const char *d = getenv("TB_DEBUG_SKIP")) A.debug = atoi(d);
+    A.sp = plan_smem(S->cs, S->max_halo, S->max_blob, S->stage_vel, S->tpm);
     A.st_in = S->st[e->cur]; A.st_out = S->st[e->cur ^ 1];
     A.blob = S->blob; A.slot_to_api = S->slot_to_api; A.halo = S->halo; A.ell = S->ell; A.meta = S->meta;
     A.acc = e->acc;
@@ -804,6 +916,16 @@ int tiled_to_canonical(Engine *e) {
 }
 
 void tiled_destroy(Engine *e) {
+    if (g_prof_dev && e->tiled && e->tiled->n_tiles > 0) {   // TB_PROFILE=1: average clocks per tile and warp
+        unsigned long long h[16];
+        cudaMemcpy(h, g_prof_dev, sizeof h, cudaMemcpyDeviceToHost);
+        const TiledState *S = e->tiled;
+        double cw0 = (double)g_prof_launches * (double)S->n_tiles * (TM / 32), cwq = cw0 * (S->tpm - 1), pw = (double)g_prof_launches * (double)S->n_tiles;
+        fprintf(stderr, "[tb profile] clocks/tile  q0 warps: wait_full %.0f springs %.0f handoff %.0f mass_update %.0f ell_wait %.0f | q>0 warps: wait_full %.0f springs %.0f handoff %.0f tail %.0f ell_wait %.0f | producer: wait_empty %.0f wait_halo_list %.0f issue %.0f\n",
+                h[0] / cw0, h[1] / cw0, h[2] / cw0, h[3] / cw0, h[7] / cw0, cwq > 0 ? h[8] / cwq : 0, cwq > 0 ? h[9] / cwq : 0, cwq > 0 ? h[10] / cwq : 0,
+                cwq > 0 ? h[11] / cwq : 0, cwq > 0 ? h[15] / cwq : 0, h[4] / pw, h[5] / pw, h[6] / pw);
+        cudaMemset(g_prof_dev, 0, sizeof h); g_prof_launches = 0;
+    }
     if (!e->tiled) return;
     free_structure(e, e->tiled);
     delete e->tiled;
