@@ -5,6 +5,9 @@
  * oracle/_ref/titan_ref_cuda.  Two uses, both on the GPU box:
  *   titan_ref_cuda dump  <scenario> <out.bin>     golden fixtures: initial scene + snapshots after pause(t)
  *   titan_ref_cuda bench <config> <steps>         "Titan's own CUDA build on the same B200" timing
+ *   titan_ref_cuda init  <scenario> <out.bin>     initial scene only (host builders; needs no GPU)
+ * The same source, unchanged, is also compiled against this repo's drop-in facade (include/Titan + libTitan.so ->
+ * titan_b200/bin/titan_facade_dump): identical driver, two engines, dumps compared by tests/test_facade.py.
  * It only calls the reference's public API (include/Titan/sim.h); it contains no step arithmetic.
  *
  * Dump format (little endian): repeated records  u32 name_len, name, u32 dtype(0=f64,1=i32,2=u8), u64 count, data.
@@ -139,13 +142,14 @@ static Scenario build(Simulation &sim, const std::string &name) {
     return sc;
 }
 
-static int do_dump(const std::string &name, const char *path) {
+static int do_dump(const std::string &name, const char *path, bool init_only = false) {
     g_out = fopen(path, "wb");
     if (!g_out) { perror(path); return 1; }
     Simulation sim;
     Scenario sc = build(sim, name);
     dump_masses(sim, "init.");
     dump_springs(sim, "init.", true);
+    if (init_only) { fclose(g_out); return 0; }
     sim.start();
     int snap = 0;
     for (double t : sc.pauses) {
@@ -206,6 +210,7 @@ static int do_bench(const std::string &cfg, long steps) {
 
 int main(int argc, char **argv) {
     if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argv[2], argv[3]);
+    if (argc >= 4 && !strcmp(argv[1], "init")) return do_dump(argv[2], argv[3], true);
     if (argc >= 4 && !strcmp(argv[1], "bench")) return do_bench(argv[2], atol(argv[3]));
     fprintf(stderr, "usage: %s dump <scenario> <out.bin> | bench <c1|c2|latticeN> <steps>\n", argv[0]);
     return 2;

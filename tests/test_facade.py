@@ -1,0 +1,93 @@
+"""The C++ drop-in (include/Titan/*.h + titan_b200/libTitan.so) exercised through the reference's own public API.
+
+* tests/cpp/facade_tests.cpp: behaviour tests in the shape of the reference's test/physics/*_unittest.cpp.
+* titan_b200/bin/titan_facade_dump: oracle/ref_cuda_dump.cu -- the SAME driver source that, linked against the
+  reference's own CUDA engine, produced tests/golden/ref_cuda/*.bin -- compiled unchanged against this facade.
+  Its dumps are compared record by record with those golden files (the reference's own outputs on a B200).
+
+Tolerances: builders / initial scene bit-exact; step count of pause(t) (simulation time) bit-exact; per-mass T
+bit-exact; pos, vel <= 1e-9 relative after up to 1,000 steps (the reference's atomicAdd summation order is
+run-dependent and the facade uses TB_MATH_FAST); acc compared on the force scale; _rest <= 1e-15.
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import scenes
+from test_oracle_vs_reference_cuda import GOLD, read_dump, rel
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "titan_b200", "bin")
+LIB = os.path.join(ROOT, "titan_b200", "libTitan.so")
+
+
+def run(cmd, **kw):
+    return subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=180, **kw)
+
+
+def test_library_exports_the_reference_api():
+    """Every public member function of titan::Simulation (reference include/Titan/sim.h:41-122) is exported."""
+    out = run(["nm", "-D", "--defined-only", "-C", LIB]).stdout
+    names = ["createMass", "createSpring", "deleteMass", "deleteSpring", "get", "set", "getAll", "setAll", "createPlane",
+             "createBall", "clearConstraints", "createContainer", "deleteContainer", "createCube", "createLattice",
+             "createRobotLink", "createBeam", "importFromSTL", "setAllSpringConstantValues", "setAllMassValues",
+             "setTimeStep", "getTimeStep", "setGlobalAcceleration", "defaultRestLengths", "start", "stop", "pause",
+             "resume", "reset", "setBreakpoint", "wait", "waitUntil", "waitForEvent", "time", "running",
+             "printPositions", "getSpringByIndex", "getMassByIndex", "getContainerByIndex"]
+    for n in names:
+        assert "titan::Simulation::%s(" % n in out, n
+    for n in ["titan::Lattice::Lattice(", "titan::Cube::Cube(", "titan::Beam::Beam(", "titan::RobotLink::RobotLink(",
+              "titan::Container::rotate(", "titan::Container::translate(", "titan::Mass::addConstraint(",
+              "titan::Mass::setDrag(", "titan::Mass::fix(", "titan::Spring::defaultLength(", "titan::Spring::setLeft("]:
+        assert n in out, n
+    # the facade reaches the GPU only through the C ABI
+    und = run(["nm", "-D", "--undefined-only", LIB]).stdout
+    assert "tb_run_async" in und and "tb_set_topology" in und and "cuda" not in und.lower()
+
+
+def test_host_behaviour():
+    r = run([os.path.join(BIN, "titan_facade_tests"), "host"])
+    assert r.returncode == 0, r.stdout
+    assert "0 failed" in r.stdout
+
+
+@pytest.mark.parametrize("name", sorted(scenes.SCENARIOS))
+def test_builders_bit_exact_against_reference_dump(name, tmp_path):
+    """Initial scene built through the facade's createLattice/Cube/Beam/... == the reference's, bit for bit."""
+    out = str(tmp_path / "init.bin")
+    r = run([os.path.join(BIN, "titan_facade_dump"), "init", name, out])
+    assert r.returncode == 0, r.stdout
+    a, g = read_dump(out), read_dump(os.path.join(GOLD, "ref_%s.bin" % name))
+    assert len(a) == 15
+    for k, v in a.items():
+        assert v.tobytes() == g[k].tobytes(), k
+
+
+@pytest.mark.gpu
+def test_gpu_behaviour():
+    r = run([os.path.join(BIN, "titan_facade_tests"), "gpu"])
+    print(r.stdout[-3000:])
+    assert r.returncode == 0, r.stdout[-3000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", sorted(scenes.SCENARIOS))
+def test_facade_matches_reference_cuda_dump(name, tmp_path):
+    out = str(tmp_path / "dump.bin")
+    r = run([os.path.join(BIN, "titan_facade_dump"), "dump", name, out])
+    assert r.returncode == 0, r.stdout[-2000:]
+    a, g = read_dump(out), read_dump(os.path.join(GOLD, "ref_%s.bin" % name))
+    assert set(a) == set(g)
+    worst = {}
+    for i, t_pause in enumerate(scenes.PAUSES[name]):
+        p = "snap%d." % i
+        assert a[p + "time"].tobytes() == g[p + "time"].tobytes()        # same number of steps: identical T += dt
+        assert a[p + "T"].tobytes() == g[p + "T"].tobytes()              # per-mass clocks (fixed masses frozen)
+        assert rel(a[p + "rest"], g[p + "rest"]) <= 1e-15
+        for f in ("pos", "vel", "acc"):
+            worst[f] = max(worst.get(f, 0.0), rel(a[p + f], g[p + f]))
+    print(name, worst)
+    assert worst["pos"] <= 1e-9 and worst["vel"] <= 1e-9
+    assert worst["acc"] <= 1e-9 * 1e3      # acc = force/m lives on the force scale k*L/m ~ 1e5

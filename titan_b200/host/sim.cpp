@@ -1,0 +1,742 @@
+// sim.cpp -- titan::Simulation on top of the C ABI of libtitan_b200 (include/titan_b200.h).
+//
+// Layout of this file: (1) object bookkeeping (create/delete, builders, bulk setters -- host only),
+// (2) the packer: host object graph <-> the engine's structure-of-arrays uploads/downloads,
+// (3) lifecycle and the GPU thread.  Reference behaviour cited per function (paths relative to the reference).
+#include <Titan/sim.h>
+
+#include <titan_b200.h>
+
+#include <algorithm>
+#include <cassert>
+#include <chrono>
+#include <iostream>
+#include <limits>
+#include <stdexcept>
+#include <unordered_set>
+
+namespace titan {
+
+namespace {
+const char *kEnded = "The simulation has ended. Cannot modify simulation after the end of the simulation.";
+const char *kRunning = "The simulation is running. Stop the simulation to make changes.";
+const char *kNotStarted = "The simulation has not started. Get and set commands cannot be called before sim.start()";
+}  // namespace
+
+// ================================================================ (1) bookkeeping ================================
+Simulation::Simulation() : Simulation(0) {}
+
+Simulation::Simulation(int device_) : device(device_), dt(0.0001), T(0), _global_acc(0, 0, -9.81) {}   // src/sim.cu:76-86
+
+Mass *Simulation::createMass(Mass *m) {   // src/sim.cu:222-253
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (STARTED && RUNNING) throw std::runtime_error(kRunning);
+    m->ref_count++;
+    masses.push_back(m);
+    if (STARTED) topology_dirty = true;   // uploaded at the next resume()/get()/set() (sync_topology)
+    return m;
+}
+
+Mass *Simulation::createMass() {
+    if (ENDED) throw std::runtime_error(kEnded);
+    return createMass(new Mass());
+}
+
+Mass *Simulation::createMass(const Vec &pos) {
+    if (ENDED) throw std::runtime_error(kEnded);
+    return createMass(new Mass(pos));
+}
+
+Spring *Simulation::createSpring(Spring *s) {   // src/sim.cu:290-322 (exit(1) while running -> exception)
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (STARTED && RUNNING) throw std::runtime_error(kRunning);
+    if (s->_right) s->_right->ref_count++;
+    if (s->_left) s->_left->ref_count++;
+    springs.push_back(s);
+    if (STARTED) topology_dirty = true;
+    return s;
+}
+
+Spring *Simulation::createSpring() {
+    if (ENDED) throw std::runtime_error(kEnded);
+    return createSpring(new Spring());
+}
+
+Spring *Simulation::createSpring(Mass *m1, Mass *m2) {
+    if (ENDED) throw std::runtime_error(kEnded);
+    return createSpring(new Spring(m1, m2));
+}
+
+// A deleted mass that springs still point at stays alive but invalid: those springs are skipped by the step
+// (src/sim.cu:1163), exactly what the reference's `invalidate` kernel arranges (src/sim.cu:343-380).
+void Simulation::deleteMass(Mass *m) {
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (STARTED && RUNNING) throw std::runtime_error(kRunning);
+    masses.erase(std::remove(masses.begin(), masses.end(), m), masses.end());
+    m->valid = false;
+    m->slot = -1;
+    if (m->ref_count > 1) zombies.push_back(m);
+    m->decrementRefCount();
+    if (STARTED) topology_dirty = true;
+}
+
+void Simulation::deleteSpring(Spring *s) {   // src/sim.cu:382-412
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (STARTED && RUNNING) throw std::runtime_error(kRunning);
+    springs.erase(std::remove(springs.begin(), springs.end(), s), springs.end());
+    for (Mass *end : {s->_left, s->_right}) {
+        if (!end) continue;
+        if (!end->valid && end->ref_count == 1) zombies.erase(std::remove(zombies.begin(), zombies.end(), end), zombies.end());
+        end->decrementRefCount();
+    }
+    if (STARTED) { delete s; topology_dirty = true; }   // before start() the reference leaves the object to the caller
+}
+
+void Simulation::deleteContainer(Container *c) {   // src/sim.cu:478-564
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (RUNNING) throw std::runtime_error(kRunning);
+    // springs first, so that no spring is left pointing at a freed mass
+    std::unordered_set<Spring *> dead_springs(c->springs.begin(), c->springs.end());
+    std::vector<Spring *> doomed;
+    for (Spring *s : springs) if (dead_springs.count(s)) doomed.push_back(s);
+    springs.erase(std::remove_if(springs.begin(), springs.end(), [&](Spring *s) { return dead_springs.count(s) != 0; }), springs.end());
+    for (Spring *s : doomed) {
+        for (Mass *end : {s->_left, s->_right}) {
+            if (!end) continue;
+            if (!end->valid && end->ref_count == 1) zombies.erase(std::remove(zombies.begin(), zombies.end(), end), zombies.end());
+            end->decrementRefCount();
+        }
+        delete s;
+    }
+    std::unordered_set<Mass *> dead_masses(c->masses.begin(), c->masses.end());
+    std::vector<Mass *> gone;
+    for (Mass *m : masses) if (dead_masses.count(m)) gone.push_back(m);
+    masses.erase(std::remove_if(masses.begin(), masses.end(), [&](Mass *m) { return dead_masses.count(m) != 0; }), masses.end());
+    for (Mass *m : gone) {
+        m->valid = false;
+        m->slot = -1;
+        if (m->ref_count > 1) zombies.push_back(m);
+        m->decrementRefCount();
+    }
+    containers.erase(std::remove(containers.begin(), containers.end(), c), containers.end());
+    delete c;
+    if (STARTED) topology_dirty = true;
+}
+
+Spring *Simulation::getSpringByIndex(int i) { assert(i >= 0 && (size_t)i < springs.size()); return springs[i]; }
+Mass *Simulation::getMassByIndex(int i) { assert(i >= 0 && (size_t)i < masses.size()); return masses[i]; }
+Container *Simulation::getContainerByIndex(int i) { assert(i >= 0 && (size_t)i < containers.size()); return containers[i]; }
+
+Container *Simulation::createContainer() {
+    Container *c = new Container();
+    containers.push_back(c);
+    return c;
+}
+
+void Simulation::adopt(Container *c) {   // the loops shared by createCube/Lattice/Beam/RobotLink, src/sim.cu:2062-2222
+    masses.reserve(masses.size() + c->masses.size());
+    springs.reserve(springs.size() + c->springs.size());
+    for (Mass *m : c->masses) createMass(m);
+    for (Spring *s : c->springs) createSpring(s);
+    containers.push_back(c);
+}
+
+Cube *Simulation::createCube(const Vec &center, double side_length) {
+    if (ENDED) throw std::runtime_error("The simulation has ended. Cannot create new objects");
+    Cube *c = new Cube(center, side_length);
+    adopt(c);
+    return c;
+}
+
+Lattice *Simulation::createLattice(const Vec &center, const Vec &dims, int nx, int ny, int nz) {
+    if (ENDED) throw std::runtime_error("The simulation has ended. New objects cannot be created.");
+    Lattice *l = new Lattice(center, dims, nx, ny, nz);
+    adopt(l);
+    return l;
+}
+
+Beam *Simulation::createBeam(const Vec &center, const Vec &dims, int nx, int ny, int nz) {
+    if (ENDED) throw std::runtime_error("The simulation has ended. New objects cannot be created.");
+    Beam *b = new Beam(center, dims, nx, ny, nz);
+    adopt(b);
+    return b;
+}
+
+RobotLink *Simulation::createRobotLink(const Vec &pos1, const Vec &pos2, double mass, double max_exp_length,
+                                       double min_exp_length, double expansion_rate, double k, double magnetic_force,
+                                       double radius) {
+    if (ENDED) throw std::runtime_error("The simulation has ended. New objects cannot be created.");
+    RobotLink *l = new RobotLink(pos1, pos2, mass, max_exp_length, min_exp_length, expansion_rate, k, magnetic_force, radius);
+    adopt(l);
+    return l;
+}
+
+Container *Simulation::importFromSTL(const std::string &, double, int) {
+    throw std::runtime_error("importFromSTL is not built in titan-b200 (host preprocessing outside the step path, SURVEY.md 8f)");
+}
+
+void Simulation::createPlane(const Vec &abc, double d) { createPlane(abc, d, 0.0, 0.0); }
+
+void Simulation::createPlane(const Vec &abc, double d, double FRICTION_K, double FRICTION_S) {   // src/sim.cu:2251-2276
+    if (ENDED) throw std::runtime_error("The simulation has ended. New objects cannot be created.");
+    ContactPlane *p = new ContactPlane(abc, d);
+    p->_FRICTION_K = FRICTION_K;
+    p->_FRICTION_S = FRICTION_S;
+    constraints.push_back(p);
+    dev_planes.push_back(*p);
+    constraints_dirty = true;
+}
+
+void Simulation::createBall(const Vec &center, double r) {   // src/sim.cu:2278-2288
+    if (ENDED) throw std::runtime_error("The simulation has ended. New constraints cannot be added.");
+    Ball *b = new Ball(center, r);
+    constraints.push_back(b);
+    dev_balls.push_back(*b);
+    constraints_dirty = true;
+}
+
+// The reference clears only the host list; the device-side planes and balls stay active (src/sim.cu:2290-2293).
+// Reproduced as is: dev_planes / dev_balls are untouched.
+void Simulation::clearConstraints() {
+    for (Constraint *c : constraints) delete c;
+    constraints.clear();
+    constraints_dirty = true;
+}
+
+void Simulation::setAllSpringConstantValues(double k) {
+    if (ENDED) throw std::runtime_error(kEnded);
+    for (Spring *s : springs) s->_k = k;
+}
+
+void Simulation::defaultRestLengths() {
+    if (ENDED) throw std::runtime_error(kEnded);
+    for (Spring *s : springs) s->defaultLength();
+}
+
+void Simulation::setAllMassValues(double m) {
+    if (ENDED) throw std::runtime_error(kEnded);
+    for (Mass *q : masses) q->m += m;
+}
+
+void Simulation::setTimeStep(double delta_t) {   // src/sim.cu:798-808
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (delta_t <= 0) throw std::runtime_error("Cannot set time step to negative or zero value.");
+    dt = delta_t;
+    constraints_dirty = true;
+}
+
+double Simulation::getTimeStep() { return dt; }
+
+void Simulation::setGlobalAcceleration(const Vec &global_acc) {   // src/sim.cu:2334-2340
+    if (RUNNING) throw std::runtime_error("The simulation is running. The global force parameter cannot be changed during runtime");
+    _global_acc = global_acc;
+    constraints_dirty = true;
+}
+
+void Simulation::printPositions() {
+    if (ENDED) throw std::runtime_error("The simulation has ended. You cannot view parameters of the simulation after it has been stopped.");
+    std::cout << "\nHOST MASSES: " << std::endl;
+    int count = 0;
+    for (Mass *m : masses) std::cout << count++ << ": " << m->pos << std::endl;
+    std::cout << std::endl;
+}
+
+// ================================================================ (2) the packer =================================
+void Simulation::engine_check(int rc, const char *what) {
+    if (rc == TB_OK) return;
+    std::string msg = std::string(what) + ": " + (engine ? tb_last_error(engine) : tb_last_error(nullptr));
+    throw std::runtime_error(msg);
+}
+
+namespace {
+
+// Brick edge lengths (bx,by,bz), bx*by*bz <= tile, minimising the bytes one step streams for an nx x ny x nz
+// lattice: per tile `tile` mass slots, one 16-byte record per spring touching the brick, 24 bytes per halo mass.
+void brick_dims(int nx, int ny, int nz, int tile, int out[3]) {
+    double best = std::numeric_limits<double>::max();
+    out[0] = out[1] = out[2] = 1;
+    for (int bx = 1; bx <= std::min(nx, tile); bx++)
+        for (int by = 1; by <= std::min(ny, tile / bx); by++) {
+            int bz = std::min(nz, tile / (bx * by));
+            if (bz < 1) continue;
+            auto cdiv = [](int a, int b) { return (a + b - 1) / b; };
+            double tiles = (double)cdiv(nx, bx) * cdiv(ny, by) * cdiv(nz, bz);
+            double a = bx - 1, b = by - 1, c = bz - 1;
+            double inner = (a * by * bz + bx * b * bz + bx * by * c) + 2 * (a * b * bz + a * by * c + bx * b * c) + 4 * a * b * c;
+            double recs = 26.0 * bx * by * bz - inner;
+            double halo = (double)(bx + 2) * (by + 2) * (bz + 2) - (double)bx * by * bz;
+            double cost = tiles * (tile * 104.0 + 16.0 * recs + 24.0 * halo);
+            if (cost < best) { best = cost; out[0] = bx; out[1] = by; out[2] = bz; }
+        }
+}
+
+tb_plane to_plane(const ContactPlane &p) {
+    tb_plane r;
+    for (int c = 0; c < 3; c++) r.normal[c] = p._normal[c];
+    r.offset = p._offset; r.friction_k = p._FRICTION_K; r.friction_s = p._FRICTION_S;
+    return r;
+}
+
+struct MassPack {   // contiguous arrays for one tb_set_mass_state / tb_set_mass_magnet call
+    std::vector<int32_t> idx, drag;
+    std::vector<double> pos, vel, m, T, ext, rad, stiff, maxmag, magscale;
+    std::vector<uint8_t> fixed, valid;
+    void reserve(size_t n) {
+        idx.reserve(n); drag.reserve(n); pos.reserve(3 * n); vel.reserve(3 * n); m.reserve(n); T.reserve(n); ext.reserve(3 * n);
+        rad.reserve(n); stiff.reserve(n); maxmag.reserve(n); magscale.reserve(n); fixed.reserve(n); valid.reserve(n);
+    }
+};
+
+}  // namespace
+
+// CUDA_MASS(Mass&), src/mass.cu:74-100: m, T, pos, vel, extern_force, magnet fields, fixed, drag, valid = true.
+void Simulation::upload_masses(Mass *const *list, size_t count) {
+    if (count == 0) return;
+    MassPack P;
+    P.reserve(count);
+    bool lc_changed = false;
+    for (size_t j = 0; j < count; j++) {
+        Mass *q = list[j];
+        if (q->slot < 0) continue;   // not on the device (deleted, or foreign)
+        P.idx.push_back(q->slot);
+        for (int c = 0; c < 3; c++) { P.pos.push_back(q->pos[c]); P.vel.push_back(q->vel[c]); P.ext.push_back(q->extern_force[c]); }
+        P.m.push_back(q->m); P.T.push_back(q->T);
+        P.fixed.push_back(q->fixed ? 1 : 0); P.valid.push_back(1);
+        P.drag.push_back((int32_t)q->drag_coefficient);   // int truncation, include/Titan/object.h:213
+        P.rad.push_back(q->rad); P.stiff.push_back(q->stiffness); P.maxmag.push_back(q->max_mag_force); P.magscale.push_back(q->mag_scale_factor);
+        std::vector<LocalConstraintRecord> &held = dev_local[(size_t)q->slot];
+        bool same = held.size() == q->local.size();
+        for (size_t r = 0; same && r < held.size(); r++)
+            same = held[r].kind == q->local[r].kind && held[r].vec == q->local[r].vec && held[r].num == q->local[r].num;
+        if (!same) { held = q->local; lc_changed = true; }
+    }
+    const int64_t n = (int64_t)P.idx.size();
+    if (n == 0) return;
+    const bool whole = n == (int64_t)masses.size() && P.idx.front() == 0 && P.idx.back() == n - 1 && std::is_sorted(P.idx.begin(), P.idx.end());
+    const int32_t *idx = whole ? nullptr : P.idx.data();
+    engine_check(tb_set_mass_state(engine, 0, n, idx, P.pos.data(), P.vel.data(), P.m.data(), P.T.data(), P.ext.data(),
+                                   P.fixed.data(), P.drag.data(), P.valid.data()), "tb_set_mass_state");
+    engine_check(tb_set_mass_magnet(engine, 0, n, idx, P.rad.data(), P.stiff.data(), P.maxmag.data(), P.magscale.data()), "tb_set_mass_magnet");
+    if (lc_changed) local_dirty = true;
+    if (local_dirty) upload_local_constraints();
+}
+
+// CUDA_SPRING(const Spring&), src/spring.cu:37-63.  Endpoints are topology and only change through sync_topology().
+void Simulation::upload_springs(Spring *const *list, size_t count) {
+    if (count == 0) return;
+    std::vector<int32_t> idx, type;
+    std::vector<double> k, rest, damping, omega, lmax, lmin, rate;
+    for (size_t j = 0; j < count; j++) {
+        const Spring *s = list[j];
+        if (s->slot < 0) continue;
+        idx.push_back(s->slot); type.push_back((int32_t)s->_type);
+        k.push_back(s->_k); rest.push_back(s->_rest); damping.push_back(s->_damping); omega.push_back(s->_omega);
+        lmax.push_back(s->_l_max); lmin.push_back(s->_l_min); rate.push_back(s->_rate);
+    }
+    const int64_t n = (int64_t)idx.size();
+    if (n == 0) return;
+    const bool whole = n == (int64_t)springs.size() && idx.front() == 0 && idx.back() == n - 1 && std::is_sorted(idx.begin(), idx.end());
+    engine_check(tb_set_spring_params(engine, 0, n, whole ? nullptr : idx.data(), k.data(), rest.data(), damping.data(), type.data(),
+                                      omega.data(), lmax.data(), lmin.data(), rate.data()), "tb_set_spring_params");
+}
+
+// Mass::operator=(CUDA_MASS&), src/mass.cu:21-49: the device changes pos, vel, acc, T and consumes extern_force.
+void Simulation::download_masses(Mass *const *list, size_t count) {
+    std::vector<int32_t> idx;
+    std::vector<Mass *> who;
+    for (size_t j = 0; j < count; j++) if (list[j]->slot >= 0) { idx.push_back(list[j]->slot); who.push_back(list[j]); }
+    const int64_t n = (int64_t)idx.size();
+    if (n == 0) return;
+    std::vector<double> pos(3 * n), vel(3 * n), acc(3 * n), tt(n), ext(3 * n);
+    const bool whole = n == (int64_t)masses.size() && idx.front() == 0 && idx.back() == n - 1 && std::is_sorted(idx.begin(), idx.end());
+    engine_check(tb_get_mass_state(engine, 0, n, whole ? nullptr : idx.data(), pos.data(), vel.data(), acc.data(), tt.data(), ext.data()),
+                 "tb_get_mass_state");
+    for (int64_t j = 0; j < n; j++) {
+        Mass *q = who[(size_t)j];
+        q->pos = Vec(pos[3 * j], pos[3 * j + 1], pos[3 * j + 2]);
+        q->vel = Vec(vel[3 * j], vel[3 * j + 1], vel[3 * j + 2]);
+        q->acc = Vec(acc[3 * j], acc[3 * j + 1], acc[3 * j + 2]);
+        q->extern_force = Vec(ext[3 * j], ext[3 * j + 1], ext[3 * j + 2]);
+        q->T = tt[j];
+    }
+}
+
+void Simulation::upload_constraints() {
+    std::vector<tb_plane> planes;
+    for (const ContactPlane &p : dev_planes) planes.push_back(to_plane(p));
+    std::vector<tb_ball> balls;
+    for (const Ball &b : dev_balls) {
+        tb_ball r;
+        for (int c = 0; c < 3; c++) r.center[c] = b._center[c];
+        r.radius = b._radius;
+        balls.push_back(r);
+    }
+    engine_check(tb_set_planes(engine, (int32_t)planes.size(), planes.data()), "tb_set_planes");
+    engine_check(tb_set_balls(engine, (int32_t)balls.size(), balls.data()), "tb_set_balls");
+    const double g[3] = {_global_acc[0], _global_acc[1], _global_acc[2]};
+    engine_check(tb_set_globals(engine, g, dt), "tb_set_globals");
+    constraints_dirty = false;
+}
+
+// The per-mass constraint lists the device holds (dev_local) as one CSR table.
+void Simulation::upload_local_constraints() {
+    const size_t nm = masses.size();
+    std::vector<int64_t> ptr(nm + 1, 0);
+    std::vector<tb_local> rec;
+    for (size_t i = 0; i < nm; i++) {
+        for (const LocalConstraintRecord &r : dev_local[i]) {
+            tb_local t;
+            t.kind = r.kind; t.pad = 0; t.num = r.num;
+            for (int c = 0; c < 3; c++) t.vec[c] = r.vec[c];
+            rec.push_back(t);
+        }
+        ptr[i + 1] = (int64_t)rec.size();
+    }
+    engine_check(tb_set_local_constraints(engine, rec.empty() ? nullptr : ptr.data(), rec.data()), "tb_set_local_constraints");
+    local_dirty = false;
+}
+
+// Topology + every field, from the host objects (toArray, src/sim.cu:940-1041).
+void Simulation::upload_everything() {
+    const int64_t nm = (int64_t)masses.size(), ns = (int64_t)springs.size();
+    for (int64_t i = 0; i < nm; i++) masses[(size_t)i]->slot = (int32_t)i;
+    std::vector<int32_t> left((size_t)ns), right((size_t)ns);
+    for (int64_t s = 0; s < ns; s++) {
+        Spring *sp = springs[(size_t)s];
+        sp->slot = (int32_t)s;
+        // nullptr or deleted endpoint -> -1: the spring is skipped by the step (src/sim.cu:1163)
+        left[(size_t)s] = (sp->_left && sp->_left->valid) ? sp->_left->slot : -1;
+        right[(size_t)s] = (sp->_right && sp->_right->valid) ? sp->_right->slot : -1;
+    }
+    engine_check(tb_set_topology(engine, nm, ns, left.data(), right.data()), "tb_set_topology");
+
+    // tile hint: bricks of lattice cells when every mass belongs to exactly one regular grid container
+    std::vector<int32_t> hint((size_t)nm, -1);
+    int32_t base = 0;
+    bool covered = true;
+    for (Container *c : containers) {
+        if (!c->grid_nx || c->masses.size() != (size_t)c->grid_nx * c->grid_ny * c->grid_nz) continue;
+        int b[3];
+        brick_dims(c->grid_nx, c->grid_ny, c->grid_nz, 128, b);
+        const int ntj = (c->grid_ny + b[1] - 1) / b[1], ntk = (c->grid_nz + b[2] - 1) / b[2], nti = (c->grid_nx + b[0] - 1) / b[0];
+        size_t q = 0;
+        for (int i = 0; i < c->grid_nx; i++)
+            for (int j = 0; j < c->grid_ny; j++)
+                for (int k = 0; k < c->grid_nz; k++, q++) {
+                    const Mass *m = c->masses[q];
+                    if (m->slot < 0 || masses[(size_t)m->slot] != m) { covered = false; continue; }
+                    if (hint[(size_t)m->slot] >= 0) covered = false;   // shared between two grids
+                    hint[(size_t)m->slot] = base + ((i / b[0]) * ntj + j / b[1]) * ntk + k / b[2];
+                }
+        base += nti * ntj * ntk;
+    }
+    for (int64_t i = 0; covered && i < nm; i++) covered = hint[(size_t)i] >= 0;
+    if (covered && nm > 0) engine_check(tb_set_tile_hint(engine, hint.data()), "tb_set_tile_hint");
+
+    dev_local.assign((size_t)nm, {});
+    local_dirty = false;
+    upload_masses(masses.data(), masses.size());
+    upload_springs(springs.data(), springs.size());
+    if (local_dirty) upload_local_constraints();
+    upload_constraints();
+    topology_dirty = false;
+}
+
+// createMass/createSpring/delete* while paused (src/sim.cu:231-253,300-322,343-564): the engine's arrays are
+// rebuilt for the new object lists.  Surviving objects keep the DEVICE's dynamic state (pos, vel, T, pending
+// extern_force, _rest); parameters (m, fixed, k, ...) are taken from the host objects.
+void Simulation::sync_topology() {
+    if (!topology_dirty) return;
+    std::vector<Mass *> old_m;
+    for (Mass *q : masses) if (q->slot >= 0) old_m.push_back(q);
+    std::vector<Spring *> old_s;
+    for (Spring *s : springs) if (s->slot >= 0) old_s.push_back(s);
+    // remember what the host objects hold, fetch the device state into them, upload, then restore the host view
+    struct Saved { Vec pos, vel, acc, ext; double T; };
+    std::vector<Saved> host_m(old_m.size());
+    for (size_t j = 0; j < old_m.size(); j++) host_m[j] = {old_m[j]->pos, old_m[j]->vel, old_m[j]->acc, old_m[j]->extern_force, old_m[j]->T};
+    download_masses(old_m.data(), old_m.size());
+    std::vector<double> host_rest(old_s.size());
+    if (!old_s.empty()) {
+        std::vector<int32_t> idx;
+        std::vector<double> rest(old_s.size());
+        for (Spring *s : old_s) idx.push_back(s->slot);
+        engine_check(tb_get_spring_rest(engine, 0, (int64_t)idx.size(), idx.data(), rest.data()), "tb_get_spring_rest");
+        for (size_t j = 0; j < old_s.size(); j++) { host_rest[j] = old_s[j]->_rest; old_s[j]->_rest = rest[j]; }
+    }
+    upload_everything();
+    for (size_t j = 0; j < old_m.size(); j++) {
+        Mass *q = old_m[j];
+        q->pos = host_m[j].pos; q->vel = host_m[j].vel; q->acc = host_m[j].acc; q->extern_force = host_m[j].ext; q->T = host_m[j].T;
+    }
+    for (size_t j = 0; j < old_s.size(); j++) old_s[j]->_rest = host_rest[j];
+}
+
+void Simulation::get(Mass *m) {   // src/sim.cu:589-602
+    if (!STARTED) { std::cerr << kNotStarted << std::endl; return; }
+    if (ENDED) throw std::runtime_error(kEnded);
+    sync_topology();
+    download_masses(&m, 1);
+}
+
+void Simulation::set(Mass *m) {   // src/sim.cu:604-616
+    if (!STARTED) { std::cerr << kNotStarted << std::endl; return; }
+    if (ENDED) throw std::runtime_error(kEnded);
+    sync_topology();
+    upload_masses(&m, 1);
+}
+
+void Simulation::get(Spring *s) {   // src/sim.cu:618-631; Spring::update copies _rest only (src/spring.cu:12-14)
+    if (!STARTED) { std::cerr << kNotStarted << std::endl; return; }
+    if (ENDED) throw std::runtime_error(kEnded);
+    sync_topology();
+    if (s->slot < 0) return;
+    int32_t idx = s->slot;
+    engine_check(tb_get_spring_rest(engine, 0, 1, &idx, &s->_rest), "tb_get_spring_rest");
+}
+
+void Simulation::set(Spring *s) {   // src/sim.cu:633-641
+    if (!STARTED) { std::cerr << kNotStarted << std::endl; return; }
+    sync_topology();
+    upload_springs(&s, 1);
+}
+
+void Simulation::getAll() {   // src/sim.cu:643-654: masses only
+    if (!STARTED) { std::cerr << kNotStarted << std::endl; return; }
+    if (ENDED) throw std::runtime_error(kEnded);
+    sync_topology();
+    download_masses(masses.data(), masses.size());
+}
+
+void Simulation::get(Container *c) {   // src/sim.cu:1051-1092 (without its whole-simulation over-read)
+    if (ENDED) throw std::runtime_error("The simulation has ended. Cannot get updates from the GPU after the end of the simulation.");
+    if (!STARTED) { std::cerr << "sim.get() does nothing if called before the simulation has started." << std::endl; return; }
+    sync_topology();
+    download_masses(c->masses.data(), c->masses.size());
+}
+
+void Simulation::set(Container *c) {   // src/sim.cu:656-718 (the container's own springs, not the simulation's)
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (!STARTED) { std::cerr << kNotStarted << std::endl; return; }
+    sync_topology();
+    upload_masses(c->masses.data(), c->masses.size());
+    upload_springs(c->springs.data(), c->springs.size());
+}
+
+void Simulation::setAll() {   // src/sim.cu:720-765
+    if (ENDED) throw std::runtime_error(kEnded);
+    if (!STARTED) return;
+    sync_topology();
+    upload_masses(masses.data(), masses.size());
+    upload_springs(springs.data(), springs.size());
+}
+
+// ================================================================ (3) lifecycle ==================================
+void Simulation::throw_if_gpu_error() {
+    std::string msg;
+    {
+        std::lock_guard<std::mutex> lk(mtx);
+        msg.swap(gpu_error);
+    }
+    if (!msg.empty()) throw std::runtime_error(msg);
+}
+
+void Simulation::start() {   // src/sim.cu:1547-1591
+    if (ENDED) throw std::runtime_error("The simulation has ended. Cannot call sim.start() after the end of the simulation.");
+    if (masses.size() == 0) throw std::runtime_error("No masses have been added. Please add masses before starting the simulation.");
+    if (STARTED) throw std::runtime_error("The simulation has already been started.");
+    if (dt <= 0) throw std::runtime_error("Simultation timestep Simulation::dt is invalid. Please choose a positive non-zero value.");
+    std::cout << "Starting simulation with " << masses.size() << " masses and " << springs.size() << " springs." << std::endl;
+
+    // no CUDA device -> TB_ERR_NO_DEVICE -> exception: there is no CPU path
+    engine_check(tb_create(device, TB_MATH_FAST, &engine), "tb_create");
+    try {
+        upload_everything();
+        engine_check(tb_run_async(engine, 0, 0.0), "tb_run_async");   // validates the scene (e.g. refuses magnetic masses)
+    } catch (...) {
+        tb_destroy(engine);
+        engine = nullptr;
+        throw;
+    }
+    T = 0;
+    RUNNING = true;
+    STARTED = true;
+    gpu_thread = std::thread(&Simulation::_run, this);
+}
+
+void Simulation::_run() {
+    execute();
+    GPU_DONE = true;
+    cv.notify_all();
+}
+
+// The run loop of src/sim.cu:1704-1841 (Euler branch :1800-1811), batched: instead of one launch group and four
+// device synchronisations per step, whole runs of steps are enqueued (CUDA graphs inside the engine).  How many
+// steps fit before the next breakpoint is decided by replaying the reference's own test `*bpts.begin() <= T`
+// over the same fp64 accumulation `T += dt`.
+void Simulation::execute() {
+    const int CHUNK = 500;   // steps per enqueue; bounds how far T runs ahead of a breakpoint set while running
+    while (true) {
+        double next_bp = std::numeric_limits<double>::infinity();
+        {
+            std::unique_lock<std::mutex> lk(mtx);
+            if (!bpts.empty() && *bpts.begin() <= T) {
+                int rc = tb_sync(engine);   // cudaDeviceSynchronize at the breakpoint, :1708
+                if (rc != TB_OK) gpu_error = std::string("tb_sync: ") + tb_last_error(engine);
+                bpts.erase(bpts.begin());
+                RUNNING = false;
+                cv.notify_all();
+                cv.wait(lk, [&] { return RUNNING.load() || ENDED.load(); });
+                if (ENDED) return;
+                continue;
+            }
+            if (ENDED) return;
+            if (!bpts.empty()) next_bp = *bpts.begin();
+        }
+        double t = T;
+        int64_t n = 0;
+        while (n < CHUNK && !(next_bp <= t)) { t += dt; n++; }
+        int rc = tb_run_async(engine, n, T);
+        if (rc == TB_OK) rc = tb_sync(engine);
+        if (rc != TB_OK) {
+            std::unique_lock<std::mutex> lk(mtx);
+            gpu_error = std::string("step failed: ") + tb_last_error(engine);
+            RUNNING = false;
+            cv.notify_all();
+            cv.wait(lk, [&] { return ENDED.load(); });
+            return;
+        }
+        T = t;
+        cv.notify_all();
+    }
+}
+
+void Simulation::resume() {   // src/sim.cu:1684-1702
+    if (ENDED) throw std::runtime_error("The simulation has ended. Cannot resume the simulation.");
+    if (!STARTED) throw std::runtime_error("The simulation has not started. You cannot resume a simulation before calling sim.start().");
+    if (masses.size() == 0) throw std::runtime_error("No masses have been added. Please add masses before starting the simulation.");
+    throw_if_gpu_error();
+    if (RUNNING) return;
+    sync_topology();
+    if (constraints_dirty) upload_constraints();   // planes/balls created while paused, new dt or g (update_constraints, :1756-1771)
+    engine_check(tb_run_async(engine, 0, T), "tb_run_async");
+    {
+        std::lock_guard<std::mutex> lk(mtx);
+        RUNNING = true;
+    }
+    cv.notify_all();
+}
+
+void Simulation::step(int n) {
+    if (ENDED) throw std::runtime_error("The simulation has ended. Control functions cannot be called.");
+    if (!STARTED) throw std::runtime_error("The simulation has not started. Call sim.start() and pause before sim.step().");
+    if (RUNNING) throw std::runtime_error(kRunning);
+    if (n <= 0) return;
+    sync_topology();
+    if (constraints_dirty) upload_constraints();
+    engine_check(tb_run_async(engine, n, T), "tb_run_async");
+    double t = T;
+    for (int j = 0; j < n; j++) t += dt;
+    T = t;
+    engine_check(tb_sync(engine), "tb_sync");
+}
+
+void Simulation::setBreakpoint(double time) {   // src/sim.cu:814-820
+    if (ENDED) throw std::runtime_error("The simulation has ended. Cannot set breakpoints after the end of the simulation run.");
+    std::lock_guard<std::mutex> lk(mtx);
+    bpts.insert(time);
+}
+
+void Simulation::pause(double t) {   // src/sim.cu:1843-1849
+    if (ENDED) throw std::runtime_error("The simulation has ended. Control functions cannot be called.");
+    setBreakpoint(t);
+    waitForEvent();
+}
+
+void Simulation::wait(double t) {   // src/sim.cu:1851-1860
+    if (ENDED) throw std::runtime_error("The simulation has ended. Control functions cannot be called.");
+    const double until = time() + t;
+    std::unique_lock<std::mutex> lk(mtx);
+    while (RUNNING && T <= until) cv.wait_for(lk, std::chrono::microseconds(200));
+}
+
+void Simulation::waitUntil(double t) {   // src/sim.cu:1862-1870
+    if (ENDED && !FREED) throw std::runtime_error("The simulation has ended. Control functions cannot be called.");
+    std::unique_lock<std::mutex> lk(mtx);
+    while (RUNNING && T <= t) cv.wait_for(lk, std::chrono::microseconds(200));
+}
+
+void Simulation::waitForEvent() {   // src/sim.cu:1872-1880
+    if (ENDED && !FREED) throw std::runtime_error("The simulation has ended. Control functions cannot be called.");
+    {
+        std::unique_lock<std::mutex> lk(mtx);
+        cv.wait(lk, [&] { return !RUNNING; });
+    }
+    throw_if_gpu_error();
+}
+
+double Simulation::time() { return T; }
+bool Simulation::running() { return RUNNING; }
+
+void Simulation::stop() { stop(time()); }   // src/sim.cu:1517-1531
+
+void Simulation::stop(double t) {   // src/sim.cu:1533-1545
+    if (RUNNING) {
+        setBreakpoint(t);
+        waitForEvent();
+    }
+    {
+        std::lock_guard<std::mutex> lk(mtx);
+        ENDED = true;
+    }
+    cv.notify_all();
+    if (gpu_thread.joinable()) gpu_thread.join();
+    freeGPU();
+}
+
+// Everything the simulation created is released; user-held pointers dangle afterwards, as in the reference
+// (src/sim.cu:131-182).
+void Simulation::freeGPU() {
+    if (FREED) return;
+    if (engine) { tb_destroy(engine); engine = nullptr; }
+    for (Spring *s : springs) delete s;
+    for (Mass *m : masses) delete m;
+    for (Mass *m : zombies) delete m;
+    for (Container *c : containers) delete c;
+    for (Constraint *c : constraints) delete c;
+    springs.clear(); masses.clear(); zombies.clear(); containers.clear(); constraints.clear();
+    dev_planes.clear(); dev_balls.clear(); dev_local.clear();
+    FREED = true;
+    ENDED = true;
+}
+
+void Simulation::reset() {   // src/sim.cu:102-129 (which leaks; this one releases)
+    if (STARTED && !FREED) {
+        if (RUNNING) { setBreakpoint(time()); waitForEvent(); }
+        { std::lock_guard<std::mutex> lk(mtx); ENDED = true; }
+        cv.notify_all();
+        if (gpu_thread.joinable()) gpu_thread.join();
+    }
+    FREED = false;
+    freeGPU();
+    bpts.clear();
+    RUNNING = false; STARTED = false; ENDED = false; FREED = false; GPU_DONE = false;
+    topology_dirty = false; constraints_dirty = true; local_dirty = false;
+    T = 0;
+    _global_acc = Vec(0, 0, -9.81);
+}
+
+Simulation::~Simulation() {   // src/sim.cu:184-220
+    std::cerr << "Simulation destructor called." << std::endl;
+    if (STARTED && !FREED) {
+        if (RUNNING) {
+            try { setBreakpoint(time()); waitForEvent(); } catch (...) {}
+        }
+        { std::lock_guard<std::mutex> lk(mtx); ENDED = true; }
+        cv.notify_all();
+    }
+    if (gpu_thread.joinable()) gpu_thread.join();
+    freeGPU();
+}
+
+}  // namespace titan
