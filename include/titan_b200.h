@@ -131,6 +131,43 @@ TB_API int tb_steps_done(tb_engine *e, int64_t *steps);            /* total step
 /* device time in ms of the most recent tb_run_async (CUDA events on the engine stream); call after tb_sync */
 TB_API int tb_last_run_ms(tb_engine *e, double *ms);
 
+/* ---- partitioned simulation: boundary-mass halo exchange over NVLink peer memory ---------------------------
+ * One large system is split by mass over several engines (one per GPU / process).  Each engine holds
+ * its OWN masses plus GHOST copies of the foreign endpoints of its cut springs; every cut spring is stored (and
+ * evaluated) by each engine owning one of its endpoints, so no forces are exchanged and summation order is kept.
+ * The reference has no such layer (single GPU, src/sim.cu:1704-1841); this replaces its single-device loop for
+ * systems beyond one GPU.
+ *
+ * The exchange is fused into the step kernel: tiles whose springs reach ghosts are processed first; the thread that
+ * updates an exported mass also stores its new state straight into the owning slot of the peer's state buffer
+ * (P2P store over NVLink), and when the last such tile of a step is done a step counter is released into each
+ * peer's flag word.  A peer's next step acquires that counter before it reads its ghost slots -- no host
+ * involvement, no separate pack/copy/unpack kernels, capturable in the CUDA graphs of tb_run_async.
+ * All engines of a partition must be advanced by the same tb_run_async calls (same step counts).
+ *
+ * Call order: tb_set_topology / state / parameters (local numbering) -> tb_halo_set_ghosts -> tb_halo_prepare ->
+ * [exchange handles and ghost offsets between engines] -> tb_halo_connect -> tb_halo_set_exports -> tb_run_async. */
+#define TB_MAX_PEERS 8
+typedef struct { unsigned char bytes[320]; } tb_halo_handle;   /* opaque; valid across processes on one node */
+/* Marks `n` local masses as ghosts: never updated or written by this engine; a peer supplies their state. */
+TB_API int tb_halo_set_ghosts(tb_engine *e, int64_t n, const int32_t *mass_idx);
+/* Builds the device layout now (it is otherwise built lazily by the first tb_run_async) and returns the handle a
+ * peer needs to reach this engine's state buffers and flag words. */
+TB_API int tb_halo_prepare(tb_engine *e, tb_halo_handle *out);
+/* For local masses (normally ghosts): the offset, in this engine's state buffers, a peer must store their state at
+ * (position x at offset, the other five components at a fixed stride). */
+TB_API int tb_halo_state_offsets(tb_engine *e, int64_t n, const int32_t *mass_idx, int64_t *offsets);
+/* Opens the peers' buffers.  flag_slot_at_peer[j] = index of THIS engine in peer j's peer list (which of peer j's
+ * flag words this engine signals).  Handles from the same process are used directly, others through CUDA IPC. */
+TB_API int tb_halo_connect(tb_engine *e, int32_t n_peers, const tb_halo_handle *peers, const int32_t *flag_slot_at_peer);
+/* After every step the new state of local mass mass_idx[j] is stored at remote_offset[j] of peer peer_idx[j]. */
+TB_API int tb_halo_set_exports(tb_engine *e, int64_t n, const int32_t *mass_idx, const int32_t *peer_idx,
+                               const int64_t *remote_offset);
+/* Pushes the CURRENT state of every exported mass to the peers (after an upload while paused) and returns when the
+ * stores are visible; the caller then synchronises the engines (barrier) before the next tb_run_async.  Once
+ * connected, a ghost's state is whatever its owner last pushed: uploads to ghost masses are ignored. */
+TB_API int tb_halo_push_now(tb_engine *e);
+
 /* ---- introspection used by tests / bench ---------------------------------------------------------------- */
 typedef struct {
     int64_t nm, ns;

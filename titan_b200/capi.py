@@ -20,7 +20,10 @@ EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_l
            "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
            "tb_get_spring_rest", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
            "tb_run_async", "tb_sync", "tb_steps_done", "tb_last_run_ms", "tb_get_info",
-           "tb_export_positions_f32_dev", "tb_alloc_host"]
+           "tb_export_positions_f32_dev", "tb_alloc_host", "tb_halo_set_ghosts", "tb_halo_prepare",
+           "tb_halo_state_offsets", "tb_halo_connect", "tb_halo_set_exports", "tb_halo_push_now"]
+MAX_PEERS = 8
+HALO_HANDLE_BYTES = 320
 
 
 class Plane(C.Structure):
@@ -85,6 +88,12 @@ def lib():
         L.tb_get_info.argtypes = [_vp, C.POINTER(Info)]
         L.tb_export_positions_f32_dev.argtypes = [_vp, C.POINTER(_vp)]
         L.tb_alloc_host.argtypes = [_vp, C.c_size_t, C.POINTER(_vp)]
+        L.tb_halo_set_ghosts.argtypes = [_vp, C.c_int64, _vp]
+        L.tb_halo_prepare.argtypes = [_vp, _vp]
+        L.tb_halo_state_offsets.argtypes = [_vp, C.c_int64, _vp, _vp]
+        L.tb_halo_connect.argtypes = [_vp, C.c_int32, _vp, _vp]
+        L.tb_halo_set_exports.argtypes = [_vp, C.c_int64, _vp, _vp, _vp]
+        L.tb_halo_push_now.argtypes = [_vp]
         _lib = L
     return _lib
 
@@ -255,6 +264,37 @@ class Engine:
         self._ck(self._L.tb_alloc_host(self._h, C.c_size_t(n), C.byref(p)))
         buf = (C.c_char * n).from_address(p.value)
         return np.frombuffer(buf, dtype=dtype).reshape(shape)
+
+    # ---- partitioned simulation (halo exchange over peer memory) ----------------------------------------
+    def halo_set_ghosts(self, mass_idx):
+        a, ap = _arr(mass_idx, np.int32)
+        self._ck(self._L.tb_halo_set_ghosts(self._h, a.shape[0], ap))
+
+    def halo_prepare(self):
+        """Builds the device layout; returns this engine's handle (bytes) for its peers."""
+        buf = C.create_string_buffer(HALO_HANDLE_BYTES)
+        self._ck(self._L.tb_halo_prepare(self._h, C.cast(buf, _vp)))
+        return buf.raw
+
+    def halo_state_offsets(self, mass_idx):
+        a, ap = _arr(mass_idx, np.int32)
+        out = np.zeros(a.shape[0], dtype=np.int64)
+        self._ck(self._L.tb_halo_state_offsets(self._h, a.shape[0], ap, out.ctypes.data_as(_vp)))
+        return out
+
+    def halo_connect(self, handles, flag_slot_at_peer):
+        blob = C.create_string_buffer(b"".join(handles), HALO_HANDLE_BYTES * max(1, len(handles)))
+        slots, sp = _arr(np.asarray(flag_slot_at_peer, dtype=np.int32).reshape(-1), np.int32)
+        self._ck(self._L.tb_halo_connect(self._h, len(handles), C.cast(blob, _vp), sp))
+
+    def halo_set_exports(self, mass_idx, peer_idx, remote_offset):
+        a, ap = _arr(mass_idx, np.int32)
+        b, bp = _arr(peer_idx, np.int32)
+        c, cp = _arr(remote_offset, np.int64)
+        self._ck(self._L.tb_halo_set_exports(self._h, a.shape[0], ap, bp, cp))
+
+    def halo_push_now(self):
+        self._ck(self._L.tb_halo_push_now(self._h))
 
     def export_positions_f32_dev(self):
         p = _vp()

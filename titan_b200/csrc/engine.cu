@@ -259,6 +259,7 @@ int tb_create(int device, uint32_t flags, tb_engine **out) {
     }
     cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, device);
     if (cudaMalloc((void **)&e->t_dev, 2 * sizeof(double)) != cudaSuccess) { delete e; return TB_ERR_OOM; }
+    if (cudaMalloc((void **)&e->step_dev, 2 * sizeof(long long)) != cudaSuccess) { delete e; return TB_ERR_OOM; }
     e->G.g[0] = 0; e->G.g[1] = 0; e->G.g[2] = -9.81;  // Simulation::Simulation, src/sim.cu:86
     e->G.dt = 0.0001;                                   // src/sim.cu:78
     e->dt_log.push_back({0, e->G.dt});
@@ -277,6 +278,7 @@ void tb_destroy(tb_engine *e) {
     if (e->more_planes) cudaFree(e->more_planes);
     if (e->more_balls) cudaFree(e->more_balls);
     cudaFree(e->t_dev);
+    cudaFree(e->step_dev);
     cudaEventDestroy(e->ev0); cudaEventDestroy(e->ev1);
     cudaStreamDestroy(e->stream);
     delete e;
@@ -343,7 +345,7 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
     e->h_n0.assign((size_t)nm, e->steps_done);
     e->cur = 0;
     e->ext_pending = false;
-    e->any_damping = e->any_active = e->any_actuated = e->any_local = e->any_magnet = e->any_fixed_or_invalid = false;
+    e->any_damping = e->any_active = e->any_actuated = e->any_local = e->any_magnet = e->any_fixed_or_invalid = e->any_ghost = false;
     e->graph_dirty = true; e->tiled_stale = 0xf; e->canon_stale = false; e->tile_hint.clear();
     e->h_type.assign((size_t)ns, 0);
     return TB_OK;
@@ -604,7 +606,7 @@ int tb_set_globals(tb_engine *e, const double g[3], double dt) {
 // ---- run loop ---------------------------------------------------------------------------------------------------
 namespace tb {
 
-__global__ void set_t_kernel(double *t, double v) { *t = v; }
+__global__ void set_t_kernel(double *t, double v, long long *step, long long n) { *t = v; *step = n; }
 
 // ACTUATED_EXPAND / ACTUATED_CONTRACT mutate _rest on the device before the force is evaluated
 // (src/sim.cu:1174-1181); springs with a null or invalid endpoint are skipped first (:1163).
@@ -674,8 +676,9 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     if (nsteps == 0) return TB_OK;
     if (use_tiled(e)) TB_TRY(tiled_prepare(e));       // may discover that the graph does not fit the tiled format
     if (!use_tiled(e) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
+    if (!use_tiled(e) && e->any_ghost) return fail(e, TB_ERR_UNSUPPORTED, "ghost masses (halo exchange) need the tiled step kernel, which does not support this scene");
     TB_CUDA(e, cudaEventRecord(e->ev0, e->stream));
-    set_t_kernel<<<1, 1, 0, e->stream>>>(e->t_dev + e->cur, t0);
+    set_t_kernel<<<1, 1, 0, e->stream>>>(e->t_dev + e->cur, t0, e->step_dev + e->cur, (long long)e->steps_done);
     int64_t left_steps = nsteps;
     if (e->ext_pending) {  // the one-shot external force acts on exactly the first step (src/sim.cu:1300,1365)
         TB_TRY(enqueue_step(e, true, left_steps == 1));
@@ -708,7 +711,7 @@ int tb_sync(tb_engine *e) {
     E_CHECK(e);
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
     TB_CUDA(e, cudaGetLastError());
-    return TB_OK;
+    return tiled_halo_check(e);
 }
 
 int tb_steps_done(tb_engine *e, int64_t *steps) {

@@ -22,7 +22,7 @@
 
 namespace tb {
 
-enum : uint8_t { F_FIXED = 1, F_VALID = 2, F_LOCAL = 4 };
+enum : uint8_t { F_FIXED = 1, F_VALID = 2, F_LOCAL = 4, F_GHOST = 8 };   // ghost: state supplied by a peer engine (halo exchange)
 // what a setter invalidated in the tiled layout: structure (tiles/ELL), spring parameters, mass state, mass flags
 enum : uint32_t { TS_STRUCT = 1, TS_PARAMS = 2, TS_STATE = 4, TS_FLAGS = 8 };
 
@@ -53,6 +53,7 @@ struct Engine {
     tb_plane *more_planes = nullptr;
     tb_ball *more_balls = nullptr;
     double *t_dev = nullptr;       // [2] simulation time, ping-pong with the step parity
+    long long *step_dev = nullptr; // [2] steps completed, ping-pong (halo exchange sequence number)
     float *export_f32 = nullptr;
     int cur = 0;                   // which pos/vel buffer holds the current state
 
@@ -69,7 +70,7 @@ struct Engine {
     int64_t steps_done = 0;
     bool ext_pending = false;      // a non-zero extern force waits for the next step
     bool any_damping = false, any_active = false, any_actuated = false, any_local = false, any_magnet = false;
-    bool any_fixed_or_invalid = false;
+    bool any_fixed_or_invalid = false, any_ghost = false;
     double last_run_ms = 0.0;
     int64_t launches = 0;
     int64_t device_bytes = 0;
@@ -113,6 +114,8 @@ int tiled_to_canonical(Engine *e);               // refresh canonical pos/vel fr
 void tiled_destroy(Engine *e);
 bool tiled_supported(const Engine *e);
 int tiled_info(const Engine *e, tb_info *info);
+bool tiled_halo_connected(const Engine *e);
+int tiled_halo_check(Engine *e);                 // after a sync: did a halo wait time out?
 
 }  // namespace tb
 

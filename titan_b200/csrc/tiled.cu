@@ -30,6 +30,8 @@
 #include <map>
 #include <numeric>
 
+#include <unistd.h>
+
 namespace tb {
 
 #define TB_TRY(x) do { int _rc = (x); if (_rc != TB_OK) return _rc; } while (0)
@@ -84,8 +86,13 @@ struct __align__(16) TileMeta {
     uint32_t deg;         // ELL rows
     uint32_t n_rec;       // spring records in the blob
     uint32_t rec_off;     // first entry of rec_spring (refresh kernels only)
+    uint32_t exp_off;     // first entry of the export table (halo exchange): exp_rows rows of TM entries
+    uint32_t exp_rows;    // 0 = no mass of this tile is a ghost on a peer
+    uint32_t tflags;      // TF_*
+    uint32_t pad;
 };
-static_assert(sizeof(TileMeta) == 32, "TileMeta is copied as two 16-byte words");
+static_assert(sizeof(TileMeta) == 48, "TileMeta is copied as three 16-byte words");
+enum : uint32_t { TF_BOUNDARY = 1 };   // the tile's springs reach ghost masses: wait for the peers before reading, signal after
 
 struct TiledState {
     int64_t n_tiles = 0, n_slots = 0, n_rec = 0, n_ell = 0, n_halo = 0;
@@ -103,8 +110,22 @@ struct TiledState {
     TileMeta *meta = nullptr;
     // host
     std::vector<int32_t> h_slot_to_api, h_api_to_slot;
+    std::vector<TileMeta> h_meta;
     bool supported = false;
     std::string why_not;
+    // ---- halo exchange (partitioned simulation) ----
+    int64_t n_active = 0;                 // tiles the step kernel processes (ghost-only tiles come last and are skipped)
+    int64_t n_boundary = 0;               // tiles [0, n_boundary) reach ghosts
+    bool halo_prepared = false, halo_connected = false;
+    int n_peers = 0;
+    unsigned long long *flags_dev = nullptr;          // [TB_MAX_PEERS] step counters released by the peers
+    unsigned *done_dev = nullptr;                     // boundary-tile completion counter of the running step
+    int *err_dev = nullptr;                           // set when a wait for a peer timed out
+    double *peer_st[TB_MAX_PEERS][2] = {};            // the peers' state buffers (peer memory)
+    unsigned long long *peer_flag[TB_MAX_PEERS] = {}; // this engine's word in each peer's flags array
+    void *ipc_opened[TB_MAX_PEERS][3] = {};           // bases opened with cudaIpcOpenMemHandle (closed on destroy)
+    int2 *exp_tab = nullptr; int64_t n_exp_tab = 0;   // per boundary tile: rows of TM (peer, remote offset) entries
+    int4 *exp_flat = nullptr; int64_t n_exp_flat = 0; // (local state offset, peer, remote offset, 0) for tb_halo_push_now
 };
 
 static inline size_t up16(size_t x) { return (x + 15) & ~(size_t)15; }
@@ -136,29 +157,69 @@ static void rcb(std::vector<int32_t> &order, const double *pos, int64_t nm, int6
 
 // Fills slot_to_api (n_tiles*TM entries, -1 = padding slot) from the caller's hint or from an RCB of the
 // current positions (SoA, 3 planes of nm).  Inside a tile masses are sorted by API index.
-static void assign_tiles(Engine *e, const std::vector<double> &pos_soa, std::vector<int32_t> &slot_to_api) {
+// With ghost masses (halo exchange) own masses and ghosts never share a tile, and tiles are ordered
+//   [tiles whose springs reach a ghost] [interior tiles] [ghost-only tiles]
+// so that the step kernel handles (and exports) the boundary first and skips the ghost-only tail.
+static void assign_tiles(Engine *e, const std::vector<double> &pos_soa, std::vector<int32_t> &slot_to_api,
+                         int64_t *n_boundary, int64_t *n_active) {
     int64_t nm = e->nm;
+    auto ghost = [&](int32_t i) { return (e->h_flags[(size_t)i] & F_GHOST) != 0; };
     std::vector<int32_t> order((size_t)nm);
     std::iota(order.begin(), order.end(), 0);
+    std::stable_partition(order.begin(), order.end(), [&](int32_t i) { return !ghost(i); });
+    const int64_t n_own = e->any_ghost ? (int64_t)(std::find_if(order.begin(), order.end(), ghost) - order.begin()) : nm;
     slot_to_api.clear();
-    if (!e->tile_hint.empty()) {
-        std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return e->tile_hint[a] < e->tile_hint[b]; });
-        int in_tile = 0;
-        for (int64_t q = 0; q < nm; q++) {
-            bool new_tile = q > 0 && (in_tile == TM || e->tile_hint[order[q]] != e->tile_hint[order[q - 1]]);
-            if (new_tile) { slot_to_api.resize(slot_to_api.size() + (size_t)(TM - in_tile), -1); in_tile = 0; }
-            slot_to_api.push_back(order[q]);
-            in_tile++;
+    auto close_tile = [&](int in_tile) { if (in_tile) slot_to_api.resize(slot_to_api.size() + (size_t)(TM - in_tile), -1); };
+    for (int part = 0; part < 2; part++) {      // own masses, then ghosts
+        const int64_t lo = part ? n_own : 0, hi = part ? nm : n_own;
+        if (lo == hi) continue;
+        if (!e->tile_hint.empty()) {
+            std::stable_sort(order.begin() + lo, order.begin() + hi, [&](int32_t a, int32_t b) { return e->tile_hint[a] < e->tile_hint[b]; });
+            int in_tile = 0;
+            for (int64_t q = lo; q < hi; q++) {
+                bool new_tile = q > lo && (in_tile == TM || e->tile_hint[order[q]] != e->tile_hint[order[q - 1]]);
+                if (new_tile) { close_tile(in_tile); in_tile = 0; }
+                slot_to_api.push_back(order[q]);
+                in_tile++;
+            }
+            close_tile(in_tile);
+        } else {
+            int64_t tiles = (hi - lo + TM - 1) / TM;
+            rcb(order, pos_soa.data(), nm, lo, hi, tiles);
+            for (int64_t t = 0; t < tiles; t++)
+                std::sort(order.begin() + lo + t * TM, order.begin() + std::min<int64_t>(hi, lo + (t + 1) * TM));
+            slot_to_api.insert(slot_to_api.end(), order.begin() + lo, order.begin() + hi);
+            close_tile((int)((hi - lo) % TM));
         }
-        slot_to_api.resize(slot_to_api.size() + (size_t)(TM - in_tile), -1);
-        return;
     }
-    int64_t tiles = (nm + TM - 1) / TM;
-    rcb(order, pos_soa.data(), nm, 0, nm, tiles);
-    for (int64_t t = 0; t < tiles; t++)
-        std::sort(order.begin() + t * TM, order.begin() + std::min<int64_t>(nm, (t + 1) * TM));
-    slot_to_api.assign(order.begin(), order.end());
-    slot_to_api.resize((size_t)(tiles * TM), -1);
+    const int64_t n_tiles = (int64_t)slot_to_api.size() / TM;
+    *n_active = n_tiles; *n_boundary = 0;
+    if (!e->any_ghost) return;
+    // classify: 0 = reaches a ghost, 1 = interior, 2 = ghost-only; stable reorder of whole tiles
+    std::vector<uint8_t> cls((size_t)n_tiles, 1);
+    for (int64_t T = 0; T < n_tiles; T++) {
+        bool any_own = false, reaches = false;
+        for (int t = 0; t < TM; t++) {
+            int32_t i = slot_to_api[(size_t)(T * TM + t)];
+            if (i < 0) continue;
+            if (!ghost(i)) any_own = true;
+            for (int32_t q = e->h_row_ptr[(size_t)i]; q < e->h_row_ptr[(size_t)i + 1] && !reaches; q++) {
+                int32_t a = e->h_adj[(size_t)q], sp = a >> 1;
+                int32_t o = (a & 1) ? e->h_left[(size_t)sp] : e->h_right[(size_t)sp];
+                reaches = ghost(o);
+            }
+        }
+        cls[(size_t)T] = !any_own ? 2 : (reaches ? 0 : 1);
+    }
+    std::vector<int64_t> tiles((size_t)n_tiles);
+    std::iota(tiles.begin(), tiles.end(), 0);
+    std::stable_sort(tiles.begin(), tiles.end(), [&](int64_t a, int64_t b) { return cls[(size_t)a] < cls[(size_t)b]; });
+    std::vector<int32_t> re(slot_to_api.size());
+    for (int64_t T = 0; T < n_tiles; T++)
+        std::copy(slot_to_api.begin() + tiles[(size_t)T] * TM, slot_to_api.begin() + (tiles[(size_t)T] + 1) * TM, re.begin() + T * TM);
+    slot_to_api.swap(re);
+    *n_boundary = std::count(cls.begin(), cls.end(), (uint8_t)0);
+    *n_active = n_tiles - std::count(cls.begin(), cls.end(), (uint8_t)2);
 }
 
 // ---------------------------------------------------------------- shared-memory plan -----------------------
@@ -237,7 +298,7 @@ static int build_structure(Engine *e, TiledState *S) {
         pos.resize((size_t)nm * 3);
         TB_CUDA(e, cudaMemcpy(pos.data(), e->pos[e->cur], (size_t)nm * 24, cudaMemcpyDeviceToHost));
     }
-    assign_tiles(e, pos, S->h_slot_to_api);
+    assign_tiles(e, pos, S->h_slot_to_api, &S->n_boundary, &S->n_active);
     std::vector<double>().swap(pos);
     const int64_t n_slots = (int64_t)S->h_slot_to_api.size(), n_tiles = n_slots / TM;
     if (n_tiles * (int64_t)STATE_BLOCK >= ((int64_t)1 << 31)) { S->why_not = "state exceeds int32 halo indices"; return TB_OK; }
@@ -266,7 +327,7 @@ static int build_structure(Engine *e, TiledState *S) {
         for (int t = 0; t < TM; t++) {
             rows[t].clear();
             int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
-            if (i < 0 || !(e->h_flags[(size_t)i] & F_VALID)) continue;
+            if (i < 0 || !(e->h_flags[(size_t)i] & F_VALID) || (e->h_flags[(size_t)i] & F_GHOST)) continue;   // ghosts are updated by their owner
             for (int32_t q = rp[(size_t)i]; q < rp[(size_t)i + 1]; q++) {
                 int32_t a = adj[(size_t)q], s = a >> 1;
                 uint8_t side = (uint8_t)(a & 1);
@@ -361,6 +422,8 @@ static int build_structure(Engine *e, TiledState *S) {
             unique_blocks++;
         }
         M.n_halo = (uint32_t)n_halo; M.n_rec = (uint32_t)n_rec;
+        M.exp_off = 0; M.exp_rows = 0; M.pad = 0;
+        M.tflags = (T < S->n_boundary) ? (uint32_t)TF_BOUNDARY : 0u;
         size_t bb = blob_size(n_rec, S->has_damping, S->has_active);
         if (blob_total / 16 >= ((size_t)1 << 32)) { S->why_not = "blob exceeds 64 GB"; return TB_OK; }
         M.blob_off16 = (uint32_t)(blob_total / 16); M.blob_bytes = (uint32_t)bb;
@@ -393,17 +456,20 @@ static int build_structure(Engine *e, TiledState *S) {
     TB_TRY(upload_vec(e, &S->halo, halo)); TB_TRY(upload_vec(e, &S->rec_spring, rec_spring)); TB_TRY(upload_vec(e, &S->ell, ell));
     TB_CUDA(e, cudaMalloc((void **)&S->meta, (size_t)n_tiles * sizeof(TileMeta)));
     TB_CUDA(e, cudaMemcpy(S->meta, meta.data(), (size_t)n_tiles * sizeof(TileMeta), cudaMemcpyHostToDevice));
+    S->h_meta.swap(meta);
     S->supported = true;
     return TB_OK;
 }
 
 // ---------------------------------------------------------------- refresh kernels -------------------------
 // canonical (API order, 3 planes of stride nm) <-> tile-blocked state
+// skip_ghosts: once the halo exchange is connected a ghost's slot belongs to its owner (the peer pushes into it)
 __global__ void tiled_gather_state(double *st, const double *pos_c, const double *vel_c, const int32_t *slot_to_api,
-                                   int64_t n_slots, int64_t nm) {
+                                   int64_t n_slots, int64_t nm, const uint8_t *flags_c, int skip_ghosts) {
     int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n_slots) return;
     int32_t i = slot_to_api[s];
+    if (skip_ghosts && i >= 0 && (flags_c[i] & F_GHOST)) return;
     double *b = st + (s / TM) * STATE_BLOCK + (s % TM);
     for (int c = 0; c < 3; c++) {
         b[c * TM] = i >= 0 ? pos_c[c * nm + i] : 0.0;
@@ -496,6 +562,16 @@ __device__ __forceinline__ void named_bar_arrive(int id, int count) { asm volati
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+constexpr long long HALO_TIMEOUT_CLOCKS = 1ll << 32;   // ~2 s: a peer that never signals must not hang the GPU
+
 // ---------------------------------------------------------------- the step kernel -------------------------
 struct TiledArgs {
     int32_t n_tiles;
@@ -512,11 +588,22 @@ struct TiledArgs {
     double *acc;                     // canonical (API-ordered) acceleration, stride X.nm
     const double *t_in;
     double *t_out;
+    // ---- halo exchange (n_peers == 0: single-engine simulation, everything below unused) ----
+    int32_t n_peers;
+    int32_t n_boundary_units;        // boundary tiles x consumer warps: arrivals that complete a step's exports
+    const long long *step_in;        // steps completed before this launch (the exchange sequence number)
+    long long *step_out;
+    unsigned long long *my_flags;    // [n_peers] written by the peers: "my exports of step n have landed"
+    unsigned long long *peer_flag[TB_MAX_PEERS];
+    double *peer_out[TB_MAX_PEERS];  // the peers' state buffer this step writes (same ping-pong parity everywhere)
+    const int2 *exp_tab;
+    unsigned *boundary_done;
+    int *halo_err;
 };
 
 // producer -> consumers, one per stage: where the NEXT tile's ELL words are and which chunks thread q takes
 // (first chunk / chunk count, one byte per q)
-struct TileCtrl { uint32_t next_ell_off, next_cb, next_nch, has_next; };
+struct TileCtrl { uint32_t next_ell_off, next_cb, next_nch, has_next, exp_off, exp_rows, tflags, pad; };
 __host__ __device__ inline void chunk_table(int deg, int tpm, uint32_t &cb_packed, uint32_t &nch_packed) {
     const int n = ell_chunks(deg), c0 = ell_chunks0(n, tpm), cq = ell_chunks_q(n, tpm);
     cb_packed = 0; nch_packed = (uint32_t)c0;
@@ -569,11 +656,11 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         const int lane = tid - NT;
         if (blockIdx.x == 0 && lane == 0) *A.t_out = __dadd_rn(*A.t_in, G.dt);   // T += dt, src/sim.cu:1811
         const int4 *mg = reinterpret_cast<const int4 *>(A.meta);
-        auto load_meta = [&](int i, int4 &a, int4 &b) {
-            if (i < n_my) { a = __ldg(mg + 2 * tile_of(i)); b = __ldg(mg + 2 * tile_of(i) + 1); }
-            else { a = make_int4(0, 0, 0, 0); b = a; }
+        auto load_meta = [&](int i, int4 &a, int4 &b, int4 &c) {
+            if (i < n_my) { a = __ldg(mg + 3 * tile_of(i)); b = __ldg(mg + 3 * tile_of(i) + 1); c = __ldg(mg + 3 * tile_of(i) + 2); }
+            else { a = make_int4(0, 0, 0, 0); b = a; c = a; }
         };
-        // a = {blob_off16, blob_bytes, halo_off, n_halo}, b = {ell_off, deg, n_rec, rec_off}
+        // a = {blob_off16, blob_bytes, halo_off, n_halo}, b = {ell_off, deg, n_rec, rec_off}, c = {exp_off, exp_rows, tflags, -}
         auto issue_hidx = [&](int i, const int4 &a) {     // lane 0
             uint32_t bytes = ((uint32_t)a.w * 4u + 15u) & ~15u;
             if (bytes < 16u) bytes = 16u;
@@ -581,20 +668,38 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             mbar_expect_tx(bar_halo(r), bytes);
             bulk_g2s(smem_base + (uint32_t)(sp.off_hring + r * sp.hring_stride), A.halo + (uint32_t)a.z, bytes, bar_halo(r));
         };
-        int4 m0a, m0b, m1a, m1b, m2a, m2b, m3a, m3b;
-        load_meta(0, m0a, m0b); load_meta(1, m1a, m1b); load_meta(2, m2a, m2b);
+        int4 m0a, m0b, m0c, m1a, m1b, m1c, m2a, m2b, m2c, m3a, m3b, m3c;
+        load_meta(0, m0a, m0b, m0c); load_meta(1, m1a, m1b, m1c); load_meta(2, m2a, m2b, m2c);
+        if (blockIdx.x == 0 && lane == 0) *A.step_out = *A.step_in + 1;
+        const unsigned long long seq = (unsigned long long)*A.step_in;
+        bool peers_ready = A.n_peers == 0;
         if (lane == 0) { issue_hidx(0, m0a); if (n_my > 1) issue_hidx(1, m1a); }
         long long pp0 = 0, pp1 = 0, pp2 = 0;
         for (int k = 0; k < n_my; k++) {
             const int s = k & 1;
             __syncwarp();
-            load_meta(k + 3, m3a, m3b);
+            load_meta(k + 3, m3a, m3b, m3c);
             long long p0 = A.prof ? clock64() : 0;
             mbar_wait(bar_empty(s), (uint32_t)(((k >> 1) & 1) ^ 1));    // consumers are done with tile k-2
             long long p1 = A.prof ? clock64() : 0;
             const uint32_t stage = smem_base + (uint32_t)(sp.off_stage + s * sp.stage_bytes);
+            if (!peers_ready && (m0c.z & TF_BOUNDARY)) {
+                // this tile reads ghost slots: every peer must have landed its exports of the previous step
+                // (acquire of the peer's step counter; the peers stored the state before releasing it)
+                if (lane < A.n_peers) {
+                    const long long t0 = clock64();
+                    while (ld_acquire_sys(A.my_flags + lane) < seq) {
+                        if (clock64() - t0 > HALO_TIMEOUT_CLOCKS) { atomicExch(A.halo_err, 1); break; }
+                        __nanosleep(64);
+                    }
+                }
+                __syncwarp();
+                asm volatile("fence.proxy.async;" ::: "memory");   // the bulk copies below read what the peers wrote
+                peers_ready = true;
+            }
             if (lane == 0) {
                 TileCtrl *c = reinterpret_cast<TileCtrl *>(smem + sp.off_ctrl) + s;
+                c->exp_off = (uint32_t)m0c.x; c->exp_rows = (uint32_t)m0c.y; c->tflags = (uint32_t)m0c.z;
                 uint32_t cbp, nchp;
                 chunk_table(m1b.y, TPM, cbp, nchp);
                 c->next_ell_off = (uint32_t)m1b.x; c->next_cb = cbp; c->next_nch = nchp; c->has_next = (k + 1 < n_my) ? 1u : 0u;
@@ -627,7 +732,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             }
             cp_async_arrive_noinc(bar_full(s));
             if (A.prof) { long long p4 = clock64(); pp0 += p1 - p0; pp1 += p3 - p2; pp2 += (p2 - p1) + (p4 - p3); }
-            m0a = m1a; m0b = m1b; m1a = m2a; m1b = m2b; m2a = m3a; m2b = m3b;
+            m0a = m1a; m0b = m1b; m0c = m1c; m1a = m2a; m1b = m2b; m1c = m2c; m2a = m3a; m2b = m3b; m2c = m3c;
         }
         if (A.prof && lane == 0) { atomicAdd(A.prof + 4, (unsigned long long)pp0); atomicAdd(A.prof + 5, (unsigned long long)pp1); atomicAdd(A.prof + 6, (unsigned long long)pp2); }
         return;
@@ -636,6 +741,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     // ============================================= CONSUMER warps ============================================
     const int t = tid % TM, q = tid / TM;
     const double t_sim = *A.t_in;
+    const unsigned long long seq = (unsigned long long)*A.step_in;
     // this thread's ELL words: chunks [cb, cb + nch) of the tile's block, rows of TM words
     auto load_ell = [&](uint32_t ell_off, int cb, int nch, uint32_t (&dst)[EPT]) {
         const uint32_t *src = A.ell + ell_off + (size_t)cb * ELL_CHUNK * TM + t;
@@ -680,7 +786,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         V3 pos = {reinterpret_cast<const double *>(pbx)[t], reinterpret_cast<const double *>(pby)[t], reinterpret_cast<const double *>(pbz)[t]};
         V3 vel = {0.0, 0.0, 0.0};
         if (STAGE_VEL || q == 0) vel = V3{reinterpret_cast<const double *>(vbx)[t], reinterpret_cast<const double *>(vby)[t], reinterpret_cast<const double *>(vbz)[t]};
-        const bool live = (fl & F_VALID) && !(fl & F_FIXED);   // else padding / deleted / fixed: frozen (src/sim.cu:1292-1295)
+        const bool live = (fl & F_VALID) && !(fl & (F_FIXED | F_GHOST));   // else padding / deleted / fixed / ghost: frozen (src/sim.cu:1292-1295)
 
         // ---- gather this thread's share of the incident springs, ascending row order ------------------------
         V3 force = {0.0, 0.0, 0.0};
@@ -773,12 +879,34 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                 mass_update<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force, acc);
                 if (A.write_acc) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
             }
-            ob[0] = pos.x; ob[TM] = pos.y; ob[2 * TM] = pos.z;
-            ob[3 * TM] = vel.x; ob[4 * TM] = vel.y; ob[5 * TM] = vel.z;
+            if (!(fl & F_GHOST)) {     // a ghost's slot belongs to the peer that owns the mass
+                ob[0] = pos.x; ob[TM] = pos.y; ob[2 * TM] = pos.z;
+                ob[3 * TM] = vel.x; ob[4 * TM] = vel.y; ob[5 * TM] = vel.z;
+            }
+            // halo exchange: the new state of a mass that is a ghost elsewhere goes straight into the peer's buffer
+            for (uint32_t r = 0; r < ctrl.exp_rows; r++) {
+                const int2 x = __ldg(A.exp_tab + ctrl.exp_off + r * TM + t);
+                if (x.x >= 0) {
+                    double *d = A.peer_out[x.x] + x.y;
+                    d[0] = pos.x; d[TM] = pos.y; d[2 * TM] = pos.z;
+                    d[3 * TM] = vel.x; d[4 * TM] = vel.y; d[5 * TM] = vel.z;
+                }
+            }
         }
+        if (ctrl.tflags & TF_BOUNDARY) __threadfence_system();   // exports visible before this warp is counted as done
         __syncwarp();
         long long c4 = A.prof ? clock64() : 0;
-        if ((tid & 31) == 0) mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
+        if ((tid & 31) == 0) {
+            mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
+            if ((ctrl.tflags & TF_BOUNDARY) && A.n_peers > 0) {
+                // last boundary warp of the step: release the step counter into every peer's flag word
+                if (atomicAdd(A.boundary_done, 1u) == (unsigned)A.n_boundary_units - 1u) {
+                    *A.boundary_done = 0u;
+                    __threadfence_system();
+                    for (int p = 0; p < A.n_peers; p++) st_release_sys(A.peer_flag[p], seq + 1ull);
+                }
+            }
+        }
 #pragma unroll
         for (int jj = 0; jj < EPT; jj++) ell_cur[jj] = ell_nxt[jj];
         nch = nch_nxt;
@@ -810,8 +938,8 @@ static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtr
         if (blocks_per_sm < 1) return fail(e, TB_ERR_CUDA, "tiled step kernel does not fit on an SM (%zu bytes of shared memory)", S->smem_bytes);
         configured_smem = S->smem_bytes;
     }
-    int64_t grid = std::min<int64_t>(S->n_tiles, (int64_t)e->sm_count * blocks_per_sm);
-    if (const char *g = getenv("TB_GRID")) { int v = atoi(g); if (v > 0) grid = std::min<int64_t>(S->n_tiles, v); }
+    int64_t grid = std::min<int64_t>(S->n_active, (int64_t)e->sm_count * blocks_per_sm);
+    if (const char *g = getenv("TB_GRID")) { int v = atoi(g); if (v > 0) grid = std::min<int64_t>(S->n_active, v); }
     S->grid = (int)grid;
     kern<<<(unsigned)grid, TM * TPM + 32, S->smem_bytes, e->stream>>>(A, e->G, X);
     return TB_OK;
@@ -836,6 +964,7 @@ bool tiled_supported(const Engine *e) {
     return true;
 }
 
+static void halo_release(Engine *e, TiledState *S);
 static unsigned long long *g_prof_dev = nullptr;
 static long long g_prof_launches = 0;
 int tiled_prepare(Engine *e) {
@@ -845,6 +974,8 @@ int tiled_prepare(Engine *e) {
     uint32_t stale = e->tiled_stale;
     if (S->n_tiles > 0 && (S->has_damping != e->any_damping || S->has_active != e->any_active)) stale |= TS_STRUCT;
     if (S->n_tiles == 0 && !(stale & TS_STRUCT) && S->supported) stale |= TS_STRUCT;
+    if ((stale & TS_STRUCT) && S->halo_connected)
+        return fail(e, TB_ERR_INVALID, "the device layout changed after tb_halo_connect: run tb_halo_prepare / connect / set_exports again");
     if (stale & TS_STRUCT) {
         TB_CUDA(e, cudaStreamSynchronize(e->stream));
         if (e->canon_stale) TB_TRY(tiled_to_canonical(e));
@@ -858,7 +989,8 @@ int tiled_prepare(Engine *e) {
     unsigned gs = (unsigned)((S->n_slots + 255) / 256);
     if (stale & TS_STATE) {
         if (e->canon_stale && !(stale & TS_STRUCT)) TB_TRY(tiled_to_canonical(e));  // partial upload landed in canonical
-        tiled_gather_state<<<gs, 256, 0, e->stream>>>(S->st[e->cur], e->pos[e->cur], e->vel[e->cur], S->slot_to_api, S->n_slots, e->nm);
+        tiled_gather_state<<<gs, 256, 0, e->stream>>>(S->st[e->cur], e->pos[e->cur], e->vel[e->cur], S->slot_to_api, S->n_slots, e->nm, e->mflags,
+                                                      S->halo_connected ? 1 : 0);
     }
     if (stale & (TS_FLAGS | TS_STATE))
         tiled_refresh_mass<<<(unsigned)S->n_tiles, TM, 0, e->stream>>>(S->blob, S->meta, S->slot_to_api, e->m, e->mflags);
@@ -874,7 +1006,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     TiledState *S = e->tiled;
     if (!S || !S->supported) return fail(e, TB_ERR_INVALID, "tiled step requested without a tiled layout");
     TiledArgs A;
-    A.n_tiles = (int32_t)S->n_tiles;
+    A.n_tiles = (int32_t)S->n_active;
     A.write_acc = write_acc ? 1 : 0;
     A.prof = nullptr;
     if (getenv("TB_PROFILE")) {
@@ -887,6 +1019,16 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     A.blob = S->blob; A.slot_to_api = S->slot_to_api; A.halo = S->halo; A.ell = S->ell; A.meta = S->meta;
     A.acc = e->acc;
     A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + (e->cur ^ 1);
+    A.step_in = e->step_dev + e->cur; A.step_out = e->step_dev + (e->cur ^ 1);
+    A.n_peers = 0; A.n_boundary_units = 0; A.my_flags = nullptr; A.exp_tab = nullptr; A.boundary_done = nullptr; A.halo_err = nullptr;
+    for (int p = 0; p < TB_MAX_PEERS; p++) { A.peer_flag[p] = nullptr; A.peer_out[p] = nullptr; }
+    if (e->any_ghost || S->n_exp_tab) {
+        if (!S->halo_connected) return fail(e, TB_ERR_INVALID, "ghost masses need tb_halo_prepare / tb_halo_connect / tb_halo_set_exports before tb_run_async");
+        A.n_peers = S->n_peers;
+        A.n_boundary_units = (int32_t)(S->n_boundary * (TM * S->tpm / 32));
+        A.my_flags = S->flags_dev; A.exp_tab = S->exp_tab; A.boundary_done = S->done_dev; A.halo_err = S->err_dev;
+        for (int p = 0; p < S->n_peers; p++) { A.peer_flag[p] = S->peer_flag[p]; A.peer_out[p] = S->peer_st[p][e->cur ^ 1]; }
+    }
     MassExtras X;
     X.ext = (use_ext && e->ext) ? e->ext : nullptr;
     X.drag = e->drag;
@@ -927,10 +1069,241 @@ void tiled_destroy(Engine *e) {
         cudaMemset(g_prof_dev, 0, sizeof h); g_prof_launches = 0;
     }
     if (!e->tiled) return;
+    halo_release(e, e->tiled);
+    if (e->tiled->flags_dev) { cudaFree(e->tiled->flags_dev); cudaFree(e->tiled->done_dev); cudaFree(e->tiled->err_dev); }
     free_structure(e, e->tiled);
     delete e->tiled;
     e->tiled = nullptr;
 }
+
+// ---------------------------------------------------------------- halo exchange: host side ------------------
+struct HandleBlob {                 // the contents of a tb_halo_handle
+    uint64_t magic;
+    int64_t pid;
+    int32_t device, cur;
+    int64_t steps_done, state_doubles;
+    cudaIpcMemHandle_t ipc[3];      // state[0], state[1], flags
+    void *raw[3];                   // the same three, valid inside the owning process
+};
+static_assert(sizeof(HandleBlob) <= sizeof(tb_halo_handle), "tb_halo_handle too small");
+constexpr uint64_t HANDLE_MAGIC = 0x7442323030484c4full;
+constexpr size_t FLAGS_BYTES = 2u << 20;   // its own allocation granule, so that the IPC mapping starts at the flags
+
+static void halo_release(Engine *e, TiledState *S) {
+    (void)e;
+    for (int p = 0; p < TB_MAX_PEERS; p++)
+        for (int b = 0; b < 3; b++)
+            if (S->ipc_opened[p][b]) { cudaIpcCloseMemHandle(S->ipc_opened[p][b]); S->ipc_opened[p][b] = nullptr; }
+    if (S->exp_tab) { cudaFree(S->exp_tab); S->exp_tab = nullptr; }
+    if (S->exp_flat) { cudaFree(S->exp_flat); S->exp_flat = nullptr; }
+    S->n_exp_tab = S->n_exp_flat = 0;
+    S->n_peers = 0;
+    S->halo_connected = false;
+}
+
+bool tiled_halo_connected(const Engine *e) { return e->tiled && e->tiled->halo_connected; }
+
+int tiled_halo_check(Engine *e) {
+    TiledState *S = e->tiled;
+    if (!S || !S->halo_connected || !S->err_dev) return TB_OK;
+    int err = 0;
+    TB_CUDA(e, cudaMemcpy(&err, S->err_dev, sizeof err, cudaMemcpyDeviceToHost));
+    if (err) {
+        cudaMemset(S->err_dev, 0, sizeof err);
+        return fail(e, TB_ERR_CUDA, "halo exchange: a peer engine did not signal its boundary state in time (are all engines of the partition advanced by the same tb_run_async calls?)");
+    }
+    return TB_OK;
+}
+
+// pushes the current state of every exported mass (tb_halo_push_now)
+__global__ void halo_push_kernel(const double *st, const int4 *flat, int64_t n, double *p0, double *p1, double *p2, double *p3,
+                                 double *p4, double *p5, double *p6, double *p7) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    double *peers[TB_MAX_PEERS] = {p0, p1, p2, p3, p4, p5, p6, p7};
+    const int4 x = flat[j];
+    const double *src = st + x.x;
+    double *dst = peers[x.y] + x.z;
+    for (int c = 0; c < 6; c++) dst[c * TM] = src[c * TM];
+    __threadfence_system();
+}
+
+}  // namespace tb
+
+using namespace tb;
+
+extern "C" {
+
+int tb_halo_set_ghosts(tb_engine *e, int64_t n, const int32_t *mass_idx) {
+    if (!e) return TB_ERR_INVALID;
+    cudaSetDevice(e->device);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_halo_set_ghosts before tb_set_topology");
+    if (n < 0 || (n > 0 && !mass_idx)) return fail(e, TB_ERR_INVALID, "tb_halo_set_ghosts: bad arguments");
+    for (int64_t j = 0; j < n; j++) if (mass_idx[j] < 0 || mass_idx[j] >= e->nm) return fail(e, TB_ERR_INVALID, "tb_halo_set_ghosts: index out of range");
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    for (uint8_t &f : e->h_flags) f = (uint8_t)(f & ~F_GHOST);
+    for (int64_t j = 0; j < n; j++) e->h_flags[(size_t)mass_idx[j]] |= F_GHOST;
+    e->any_ghost = n > 0;
+    TB_CUDA(e, cudaMemcpy(e->mflags, e->h_flags.data(), (size_t)e->nm, cudaMemcpyHostToDevice));
+    e->tiled_stale |= TS_STRUCT | TS_FLAGS;
+    e->graph_dirty = true;
+    if (e->tiled) halo_release(e, e->tiled);
+    return TB_OK;
+}
+
+int tb_halo_prepare(tb_engine *e, tb_halo_handle *out) {
+    if (!e || !out) return TB_ERR_INVALID;
+    cudaSetDevice(e->device);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_halo_prepare before tb_set_topology");
+    if (e->any_actuated) return fail(e, TB_ERR_UNSUPPORTED, "halo exchange is not built for ACTUATED_* springs (generic kernel)");
+    if (e->tiled) halo_release(e, e->tiled);
+    e->tiled_stale |= TS_STRUCT;
+    int rc = tiled_prepare(e);
+    if (rc != TB_OK) return rc;
+    TiledState *S = e->tiled;
+    if (!S->supported) return fail(e, TB_ERR_UNSUPPORTED, "halo exchange needs the tiled layout: %s", S->why_not.c_str());
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (!S->flags_dev) {
+        TB_CUDA(e, cudaMalloc((void **)&S->flags_dev, FLAGS_BYTES));
+        TB_CUDA(e, cudaMalloc((void **)&S->done_dev, sizeof(unsigned)));
+        TB_CUDA(e, cudaMalloc((void **)&S->err_dev, sizeof(int)));
+    }
+    // flags start at the current step count: "every export up to the present state has landed" (the caller uploads
+    // consistent ghost state, or calls tb_halo_push_now)
+    std::vector<unsigned long long> init(TB_MAX_PEERS, (unsigned long long)e->steps_done);
+    TB_CUDA(e, cudaMemset(S->flags_dev, 0, FLAGS_BYTES));
+    TB_CUDA(e, cudaMemcpy(S->flags_dev, init.data(), init.size() * 8, cudaMemcpyHostToDevice));
+    TB_CUDA(e, cudaMemset(S->done_dev, 0, sizeof(unsigned)));
+    TB_CUDA(e, cudaMemset(S->err_dev, 0, sizeof(int)));
+    HandleBlob h;
+    memset(&h, 0, sizeof h);
+    h.magic = HANDLE_MAGIC; h.pid = (int64_t)getpid(); h.device = e->device; h.cur = e->cur;
+    h.steps_done = e->steps_done; h.state_doubles = S->n_tiles * STATE_BLOCK;
+    h.raw[0] = S->st[0]; h.raw[1] = S->st[1]; h.raw[2] = S->flags_dev;
+    for (int b = 0; b < 3; b++) TB_CUDA(e, cudaIpcGetMemHandle(&h.ipc[b], h.raw[b]));
+    memset(out, 0, sizeof *out);
+    memcpy(out->bytes, &h, sizeof h);
+    S->halo_prepared = true;
+    return TB_OK;
+}
+
+int tb_halo_state_offsets(tb_engine *e, int64_t n, const int32_t *mass_idx, int64_t *offsets) {
+    if (!e) return TB_ERR_INVALID;
+    TiledState *S = e->tiled;
+    if (!S || !S->halo_prepared) return fail(e, TB_ERR_INVALID, "tb_halo_state_offsets before tb_halo_prepare");
+    for (int64_t j = 0; j < n; j++) {
+        if (mass_idx[j] < 0 || mass_idx[j] >= e->nm) return fail(e, TB_ERR_INVALID, "tb_halo_state_offsets: index out of range");
+        int32_t slot = S->h_api_to_slot[(size_t)mass_idx[j]];
+        offsets[j] = (int64_t)(slot / TM) * STATE_BLOCK + slot % TM;
+    }
+    return TB_OK;
+}
+
+int tb_halo_connect(tb_engine *e, int32_t n_peers, const tb_halo_handle *peers, const int32_t *flag_slot_at_peer) {
+    if (!e) return TB_ERR_INVALID;
+    cudaSetDevice(e->device);
+    TiledState *S = e->tiled;
+    if (!S || !S->halo_prepared) return fail(e, TB_ERR_INVALID, "tb_halo_connect before tb_halo_prepare");
+    if (n_peers < 0 || n_peers > TB_MAX_PEERS || (n_peers > 0 && (!peers || !flag_slot_at_peer)))
+        return fail(e, TB_ERR_INVALID, "tb_halo_connect: between 0 and %d peers", TB_MAX_PEERS);
+    for (int p = 0; p < n_peers; p++) {
+        HandleBlob h;
+        memcpy(&h, peers[p].bytes, sizeof h);
+        if (h.magic != HANDLE_MAGIC) return fail(e, TB_ERR_INVALID, "tb_halo_connect: peer %d is not a tb_halo_handle", p);
+        if (h.cur != e->cur || h.steps_done != e->steps_done)
+            return fail(e, TB_ERR_INVALID, "tb_halo_connect: peer %d is at step %lld, this engine at %lld -- engines of a partition advance together", p, (long long)h.steps_done, (long long)e->steps_done);
+        if (flag_slot_at_peer[p] < 0 || flag_slot_at_peer[p] >= TB_MAX_PEERS) return fail(e, TB_ERR_INVALID, "tb_halo_connect: bad flag slot");
+        void *ptr[3];
+        if (h.pid == (int64_t)getpid()) {
+            for (int b = 0; b < 3; b++) ptr[b] = h.raw[b];
+            if (h.device != e->device) {
+                cudaError_t err = cudaDeviceEnablePeerAccess(h.device, 0);
+                if (err != cudaSuccess && err != cudaErrorPeerAccessAlreadyEnabled) return fail(e, TB_ERR_CUDA, "no peer access from device %d to %d: %s", e->device, h.device, cudaGetErrorString(err));
+                cudaGetLastError();
+            }
+        } else {
+            for (int b = 0; b < 3; b++) {
+                TB_CUDA(e, cudaIpcOpenMemHandle(&ptr[b], h.ipc[b], cudaIpcMemLazyEnablePeerAccess));
+                S->ipc_opened[p][b] = ptr[b];
+            }
+        }
+        S->peer_st[p][0] = (double *)ptr[0]; S->peer_st[p][1] = (double *)ptr[1];
+        S->peer_flag[p] = (unsigned long long *)ptr[2] + flag_slot_at_peer[p];
+    }
+    S->n_peers = n_peers;
+    S->halo_connected = true;
+    e->graph_dirty = true;
+    return TB_OK;
+}
+
+int tb_halo_set_exports(tb_engine *e, int64_t n, const int32_t *mass_idx, const int32_t *peer_idx, const int64_t *remote_offset) {
+    if (!e) return TB_ERR_INVALID;
+    cudaSetDevice(e->device);
+    TiledState *S = e->tiled;
+    if (!S || !S->halo_connected) return fail(e, TB_ERR_INVALID, "tb_halo_set_exports before tb_halo_connect");
+    if (n < 0 || (n > 0 && (!mass_idx || !peer_idx || !remote_offset))) return fail(e, TB_ERR_INVALID, "tb_halo_set_exports: bad arguments");
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (S->exp_tab) { cudaFree(S->exp_tab); S->exp_tab = nullptr; }
+    if (S->exp_flat) { cudaFree(S->exp_flat); S->exp_flat = nullptr; }
+    std::vector<std::vector<std::pair<int32_t, int32_t>>> per_slot;   // only for slots of tiles that export
+    std::vector<int> rows((size_t)S->n_tiles, 0);
+    std::vector<int4> flat((size_t)n);
+    std::map<int64_t, std::vector<std::pair<int32_t, int32_t>>> by_slot;
+    for (int64_t j = 0; j < n; j++) {
+        if (mass_idx[j] < 0 || mass_idx[j] >= e->nm || peer_idx[j] < 0 || peer_idx[j] >= S->n_peers || remote_offset[j] < 0 ||
+            remote_offset[j] >= ((int64_t)1 << 31))
+            return fail(e, TB_ERR_INVALID, "tb_halo_set_exports: entry %lld out of range", (long long)j);
+        if (e->h_flags[(size_t)mass_idx[j]] & F_GHOST) return fail(e, TB_ERR_INVALID, "tb_halo_set_exports: mass %d is a ghost here", mass_idx[j]);
+        int64_t slot = S->h_api_to_slot[(size_t)mass_idx[j]];
+        std::vector<std::pair<int32_t, int32_t>> &v = by_slot[slot];
+        v.push_back({peer_idx[j], (int32_t)remote_offset[j]});
+        rows[(size_t)(slot / TM)] = std::max(rows[(size_t)(slot / TM)], (int)v.size());
+        flat[(size_t)j] = make_int4((int)((slot / TM) * STATE_BLOCK + slot % TM), peer_idx[j], (int)remote_offset[j], 0);
+    }
+    std::vector<int2> tab;
+    for (int64_t T = 0; T < S->n_tiles; T++) {
+        TileMeta &M = S->h_meta[(size_t)T];
+        M.exp_off = (uint32_t)tab.size(); M.exp_rows = (uint32_t)rows[(size_t)T];
+        if (rows[(size_t)T] && T >= S->n_boundary)
+            return fail(e, TB_ERR_INVALID, "tb_halo_set_exports: an exported mass has no ghost neighbour on this engine (inconsistent partition)");
+        tab.resize(tab.size() + (size_t)rows[(size_t)T] * TM, make_int2(-1, 0));
+    }
+    for (auto &kv : by_slot) {
+        const TileMeta &M = S->h_meta[(size_t)(kv.first / TM)];
+        for (size_t r = 0; r < kv.second.size(); r++)
+            tab[(size_t)M.exp_off + r * TM + (size_t)(kv.first % TM)] = make_int2(kv.second[r].first, kv.second[r].second);
+    }
+    S->n_exp_tab = (int64_t)tab.size(); S->n_exp_flat = n;
+    TB_CUDA(e, cudaMalloc((void **)&S->exp_tab, std::max<size_t>(1, tab.size()) * sizeof(int2)));
+    TB_CUDA(e, cudaMalloc((void **)&S->exp_flat, std::max<size_t>(1, flat.size()) * sizeof(int4)));
+    if (!tab.empty()) TB_CUDA(e, cudaMemcpy(S->exp_tab, tab.data(), tab.size() * sizeof(int2), cudaMemcpyHostToDevice));
+    if (!flat.empty()) TB_CUDA(e, cudaMemcpy(S->exp_flat, flat.data(), flat.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    TB_CUDA(e, cudaMemcpy(S->meta, S->h_meta.data(), (size_t)S->n_tiles * sizeof(TileMeta), cudaMemcpyHostToDevice));
+    e->graph_dirty = true;
+    return TB_OK;
+}
+
+int tb_halo_push_now(tb_engine *e) {
+    if (!e) return TB_ERR_INVALID;
+    cudaSetDevice(e->device);
+    TiledState *S = e->tiled;
+    if (!S || !S->halo_connected) return fail(e, TB_ERR_INVALID, "tb_halo_push_now before tb_halo_connect");
+    int rc = tiled_prepare(e);       // brings an upload that landed in the canonical arrays into the tiled state
+    if (rc != TB_OK) return rc;
+    if (S->n_exp_flat > 0) {
+        double *p[TB_MAX_PEERS];
+        for (int q = 0; q < TB_MAX_PEERS; q++) p[q] = S->peer_st[q][e->cur];
+        halo_push_kernel<<<(unsigned)((S->n_exp_flat + 127) / 128), 128, 0, e->stream>>>(S->st[e->cur], S->exp_flat, S->n_exp_flat, p[0], p[1],
+                                                                                       p[2], p[3], p[4], p[5], p[6], p[7]);
+        TB_CUDA(e, cudaGetLastError());
+    }
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    return TB_OK;
+}
+
+}  // extern "C"
+
+namespace tb {
 
 int tiled_info(const Engine *e, tb_info *info) {
     const TiledState *S = e->tiled;

@@ -25,11 +25,18 @@ def lattice_counts(nx, ny, nz):
     return nm, ns
 
 
-def lattice_positions(center, dims, nx, ny, nz):
-    def axis(n, d, c):
-        u = (np.arange(n, dtype=np.float64) / (n - 1.0) - 0.5) if n > 1 else np.zeros(1)
+def lattice_positions(center, dims, nx, ny, nz, i_range=None):
+    """Mass coordinates in reference order; i_range=(a, b) restricts to the i-planes [a, b) of the nx-plane lattice
+    (same doubles as the full lattice: the formula only sees the global index and nx)."""
+    def axis(n, d, c, lo=0, hi=None):
+        hi = n if hi is None else hi
+        u = (np.arange(lo, hi, dtype=np.float64) / (n - 1.0) - 0.5) if n > 1 else np.zeros(1)
         return u * d + c
-    x, y, z = (axis(n, float(d), float(c)) for n, d, c in zip((nx, ny, nz), dims, center))
+    lo, hi = (0, nx) if i_range is None else i_range
+    x = axis(nx, float(dims[0]), float(center[0]), lo, hi)
+    y = axis(ny, float(dims[1]), float(center[1]))
+    z = axis(nz, float(dims[2]), float(center[2]))
+    nx = hi - lo
     pos = np.empty((nx, ny, nz, 3))
     pos[..., 0] = x[:, None, None]
     pos[..., 1] = y[None, :, None]
