@@ -121,12 +121,31 @@ def cpu_port(W, seconds_budget=12.0, min_steps=2):
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference algorithm on the host cores (OpenMP port in oracle/), rank 0 only."""
+    """--impl reference: the reference algorithm on the host cores (OpenMP port in oracle/), rank 0 only.  Each
+    step is a bounded sample of the arm's workload: all of C2; for C4 the planes one rank of the partition owns
+    (plus a ghost plane); for C3 at most 64 robots -- spring-steps/s is normalised by the springs stepped."""
     if rank != 0:
         return
     import oracle
-    W = workload_c2(args.size)
+    if args.workload == "c4":
+        from titan_b200 import lattice, partition
+        n = args.size
+        lo, hi = partition.slab_bounds(n, world)[0]
+        planes = min(n, hi - lo + 1)
+        L = lattice.build_lattice((0.0, 0.0, 0.05 * (n - 1) - 0.001), (0.1 * (planes - 1), 0.1 * (n - 1), 0.1 * (n - 1)), planes, n, n)
+        W = dict(L, plane=PLANE, name="C4 family: %d^3 lattice over %d ranks" % (n, world))
+        sample = "rank 0's share of the lattice (%d of %d i-planes of %dx%d masses)" % (planes, n, n, n)
+    elif args.workload == "c3":
+        per = min(64, args.robots // world)
+        W = workload_c3(per, 0)
+        sample = "%d of the %d robots" % (per, args.robots)
+    else:
+        W = workload_c2(args.size)
+        sample = "the whole workload"
     sc = oracle.Scene(W["pos"], W["left"], W["right"], W["rest"])
+    if "type" in W:
+        sc.type[:] = W["type"]
+        sc.omega[:] = W["omega"]
     n, off, fk, fs = W["plane"]
     sc.planes.append(oracle.make_plane(n, off, fk, fs))
     sc.local = None
@@ -139,7 +158,7 @@ def run_reference(args, rank, world):
     el = time.perf_counter() - t0
     value = sc.ns * inner * args.steps / el
     cores = oracle.omp_threads()
-    sample = "%d bench steps x %d simulation steps of the same workload, OpenMP (%d threads)" % (args.steps, inner, cores)
+    sample = "%s: %d masses, %d springs; %d bench steps x %d simulation steps, OpenMP (%d threads)" % (sample, sc.nm, sc.ns, args.steps, inner, cores)
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / args.steps,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -152,14 +171,46 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+C4_EDGE = {1: 150, 2: 189, 4: 238, 8: 300}     # ~3.4 M masses per GPU; 300^3 on 8 GPUs is config C4
+PLANE = ((0.0, 0.0, 1.0), 0.0, 0.5, 0.6)        # frictional plane z = 0 (mu_k 0.5, mu_s 0.6)
+
+
+def workload_c3(n_robots, first_robot=0):
+    """independent 10^3 soft robots (0.9 m cubes resting 0.1 m above the plane on a 1.2 m grid),
+    spring s of each robot PASSIVE / ACTIVE_CONTRACT_THEN_EXPAND / ACTIVE_EXPAND_THEN_CONTRACT by s % 3, omega = 4 pi.
+    One engine steps all robots of a rank as one disjoint graph (batched SoA, one launch per step)."""
+    from titan_b200 import lattice
+    L = lattice.build_lattice((0.0, 0.0, 0.55), (0.9, 0.9, 0.9), 10, 10, 10)
+    nm1, ns1 = L["pos"].shape[0], L["left"].shape[0]
+    hint1 = lattice.brick_hint(10, 10, 10, tile=125)
+    nt1 = int(hint1.max()) + 1
+    r = np.arange(first_robot, first_robot + n_robots)
+    off = np.zeros((n_robots, 1, 3))
+    off[:, 0, 0] = 1.2 * (r % 64)
+    off[:, 0, 1] = 1.2 * (r // 64)
+    pos = (L["pos"][None, :, :] + off).reshape(-1, 3)
+    base = (np.arange(n_robots, dtype=np.int64) * nm1)[:, None]
+    left = (L["left"][None, :] + base).astype(np.int32).reshape(-1)
+    right = (L["right"][None, :] + base).astype(np.int32).reshape(-1)
+    s = np.arange(ns1)
+    type1 = np.where(s % 3 == 1, 2, np.where(s % 3 == 2, 3, 0)).astype(np.int32)
+    return {"pos": pos, "left": left, "right": right, "rest": np.tile(L["rest"], n_robots), "type": np.tile(type1, n_robots),
+            "omega": np.full(left.size, 4 * np.pi), "plane": PLANE,
+            "tile_hint": (hint1[None, :] + (np.arange(n_robots, dtype=np.int64) * nt1)[:, None]).astype(np.int32).reshape(-1),
+            "name": "C3: %d independent actuated 10^3 soft robots per rank" % n_robots}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="c2")
-    ap.add_argument("--size", type=int, default=100, help="lattice edge (C2 = 100)")
+    ap.add_argument("--workload", default=None, choices=["c2", "c3", "c4"],
+                    help="default: c2 on one GPU, c4 (partitioned lattice, halo exchange) on several")
+    ap.add_argument("--size", type=int, default=None, help="lattice edge (c2: 100; c4: 150/189/238/300 by GPU count)")
+    ap.add_argument("--shape", default=None, help="c4: nx,ny,nz of the whole lattice instead of --size^3")
+    ap.add_argument("--robots", type=int, default=4096, help="c3: robots over all ranks")
     ap.add_argument("--inner", type=int, default=200, help="simulation steps per bench step")
     ap.add_argument("--ref-inner", type=int, default=2, help="simulation steps per bench step, --impl reference")
     ap.add_argument("--strict", action="store_true", help="TB_MATH_STRICT arithmetic")
@@ -173,6 +224,10 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.workload is None:
+        args.workload = "c2" if world == 1 else "c4"
+    if args.size is None:
+        args.size = 100 if args.workload == "c2" else C4_EDGE.get(world, int(round(150 * world ** (1.0 / 3.0))))
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
@@ -189,26 +244,48 @@ def main():
         if dist is not None:
             dist.barrier()
 
-    def max_over_ranks(x):
+    def reduce_ranks(x, op="max"):
         if dist is None:
             return x
         import torch
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
         return float(t.item())
 
-    W = workload_c2(args.size)
-    nm, ns = W["pos"].shape[0], W["left"].shape[0]
     flags = (tb.MATH_STRICT if args.strict else tb.MATH_FAST) | (tb.KERNEL_CSR if args.csr else 0)
     eng = tb.Engine(local_rank, flags)
-    eng.set_topology(nm, W["left"], W["right"])
-    if not args.no_hint:
-        eng.set_tile_hint(W["tile_hint"])     # what Lattice builders pass: bricks of lattice cells
-    eng.set_mass_state(pos=W["pos"])
-    eng.set_spring_params(rest=W["rest"])
-    n, off, fk, fs = W["plane"]
-    eng.set_planes([tb.Plane((tb.capi.C.c_double * 3)(*n), off, fk, fs)])
-    eng.set_globals((0.0, 0.0, -9.81), 1e-4)
+    part, own = None, None
+    if args.workload == "c4":
+        from titan_b200 import distributed, partition
+        n = args.size
+        shp = tuple(int(x) for x in args.shape.split(",")) if args.shape else (n, n, n)
+        part = partition.LatticeSlab((0.0, 0.0, 0.05 * (shp[2] - 1) - 0.001), tuple(0.1 * (x - 1) for x in shp), shp[0], shp[1], shp[2], rank, world)
+        distributed.upload_slab(eng, part, planes=[PLANE], hint=not args.no_hint)
+        if world > 1:
+            distributed.connect(eng, part)
+        own = part.own_local
+        nm_own, ns_own = part.nm_own, part.ns_owned
+        name = "C4 family: one %dx%dx%d lattice on a frictional plane cut into %d i-slabs, halo exchange every step" % (shp + (world,))
+        per_rank = "%d own i-planes of %dx%d masses + ghost planes; cut springs evaluated on both sides" % (part.bounds[rank][1] - part.bounds[rank][0], n, n)
+    else:
+        if args.workload == "c2":
+            W = workload_c2(args.size)
+            per_rank = "independent copy of the workload"
+        else:
+            per = args.robots // world
+            W = workload_c3(per, rank * per)
+            per_rank = "%d of %d robots, no communication" % (per, per * world)
+        name = W["name"]
+        nm_own, ns_own = W["pos"].shape[0], W["left"].shape[0]
+        eng.set_topology(nm_own, W["left"], W["right"])
+        if not args.no_hint:
+            eng.set_tile_hint(W["tile_hint"])     # what Lattice builders pass: bricks of lattice cells
+        eng.set_mass_state(pos=W["pos"])
+        eng.set_spring_params(rest=W["rest"], type=W.get("type"), omega=W.get("omega"))
+        nrm, off, fk, fs = W["plane"]
+        eng.set_planes([tb.Plane((tb.capi.C.c_double * 3)(*nrm), off, fk, fs)])
+        eng.set_globals((0.0, 0.0, -9.81), 1e-4)
+    nm_total, ns_total = int(reduce_ranks(nm_own, "sum")), int(reduce_ranks(ns_own, "sum"))
     dt, inner = 1e-4, args.inner
 
     t_sim = 0.0
@@ -232,20 +309,23 @@ def main():
     dev_ms = eng.last_run_ms()
     barrier()
     launches = eng.info()["launches"] - launches0
-    dev_ms = max_over_ranks(dev_ms)
-    wall = max_over_ranks(wall)
+    dev_ms = reduce_ranks(dev_ms)
+    wall = reduce_ranks(wall)
     sim_steps = inner * args.steps
-    value = world * ns * sim_steps / (dev_ms * 1e-3)
+    value = ns_total * sim_steps / (dev_ms * 1e-3)
 
     info = eng.info()
     peak, peak_src = load_peaks()
     step_us = dev_ms * 1e3 / sim_steps
-    achieved = info["algorithmic_bytes_per_step"] / (step_us * 1e-6) / 1e9
+    # bytes/step = Nm*104 + Ns*B_s over the WHOLE system (cut springs once); per GPU = 1/N of it
+    bs = 36.0 if args.workload == "c3" else 24.0
+    alg_bytes = (104.0 * nm_total + bs * ns_total) / world
+    achieved = alg_bytes / (step_us * 1e-6) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": None, "peak_source": peak_src, "kernel": "tiled_step" if info["kernel"] == 1 else "csr_step",
-                "algorithmic_bytes_per_launch": info["algorithmic_bytes_per_step"], "avg_launch_us": step_us}
+                "algorithmic_bytes_per_launch": alg_bytes, "avg_launch_us": step_us, "per": "GPU"}
     traffic_file = os.path.join(ROOT, "profiles", "traffic_bytes_per_launch.json")
-    if os.path.exists(traffic_file):
+    if os.path.exists(traffic_file) and args.workload == "c2" and args.size == 100:
         try:
             roofline["traffic"] = json.load(open(traffic_file)).get(roofline["kernel"])
         except Exception:
@@ -254,12 +334,18 @@ def main():
     # ---- end to end through host buffers (`e2e`) ---------------------------------------------------------
     e2e = None
     if not args.no_e2e:
-        pos_h, vel_h = eng.alloc_pinned((nm, 3)), eng.alloc_pinned((nm, 3))
-        st = eng.get_mass_state(fields=("pos", "vel"), out={"pos": pos_h, "vel": vel_h})
+        n_io = nm_own
+        pos_h, vel_h = eng.alloc_pinned((n_io, 3)), eng.alloc_pinned((n_io, 3))
+        eng.get_mass_state(idx=own, fields=("pos", "vel"), out={"pos": pos_h, "vel": vel_h})
         def e2e_step():
-            eng.set_mass_state(pos=pos_h, vel=vel_h)                  # H2D from pinned host memory
+            eng.set_mass_state(idx=own, pos=pos_h, vel=vel_h)         # H2D from pinned host memory
+            if part is not None and world > 1:
+                eng.halo_push_now()                                    # refresh the peers' ghost planes
+                barrier()
             advance(inner)
-            eng.get_mass_state(fields=("pos", "vel"), out={"pos": pos_h, "vel": vel_h})   # D2H (syncs)
+            eng.get_mass_state(idx=own, fields=("pos", "vel"), out={"pos": pos_h, "vel": vel_h})   # D2H (syncs)
+            if part is not None and world > 1:
+                barrier()
         for _ in range(2):
             e2e_step()
         barrier()
@@ -267,30 +353,31 @@ def main():
         for _ in range(args.steps):
             e2e_step()
         eng.sync()
-        e2e_s = max_over_ranks(time.perf_counter() - w0)
+        e2e_s = reduce_ranks(time.perf_counter() - w0)
         barrier()
-        e2e = {"value": world * ns * sim_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(nm * 48),
-               "d2h_bytes_per_step": int(nm * 48), "ms_per_step": 1e3 * e2e_s / args.steps,
+        e2e = {"value": ns_total * sim_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(nm_total * 48),
+               "d2h_bytes_per_step": int(nm_total * 48), "ms_per_step": 1e3 * e2e_s / args.steps,
                "call": "tb_set_mass_state(pos,vel) + tb_run_async(%d) + tb_get_mass_state(pos,vel)" % inner}
         assert np.isfinite(pos_h).all()
 
     cpu = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "c2":
         cpu = cpu_port(W)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": W["name"], "masses": nm, "springs": ns, "sim_steps_per_bench_step": inner,
+                "config": {"workload": name, "masses": nm_total, "springs": ns_total, "sim_steps_per_bench_step": inner,
                            "math": "strict" if args.strict else "fast",
                            "tiling": {k: info[k] for k in ("n_tiles", "threads_per_mass", "grid", "smem_bytes",
-                                                           "ell_unique_tiles", "tiled_bytes_per_step")}, "per_rank": "independent copy of the workload",
-                           "l2": "working set per step (%.0f MB) exceeds the 126 MB L2" % (info["algorithmic_bytes_per_step"] / 1e6),
+                                                           "ell_unique_tiles", "tiled_bytes_per_step")}, "per_rank": per_rank,
+                           "l2": "working set per step and GPU (%.0f MB) exceeds the 126 MB L2" % (alg_bytes / 1e6),
                            "timing": "CUDA events on the engine stream, max over ranks", "wall_ms": wall * 1e3},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world,
                 "clocks": clocks.summary()}
         print(json.dumps(line), flush=True)
+    barrier()
     eng.close()
     if dist is not None:
         dist.destroy_process_group()

@@ -201,3 +201,18 @@ def test_lone_engine_of_a_partition_reports_instead_of_hanging(monkeypatch):
         engines[0].sync()
     for en in engines:
         en.close()
+
+
+@pytest.mark.gpu
+def test_one_process_per_gpu_over_cuda_ipc():
+    """The real deployment shape: torchrun, one process per GPU, peer memory opened through CUDA IPC."""
+    if tb.device_count() < 2:
+        pytest.skip("needs at least 2 GPUs")
+    world = min(4, tb.device_count())
+    env = dict(os.environ, PYTHONPATH=ROOT + os.pathsep + os.path.join(ROOT, "tests"))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=%d" % world, "--master-addr",
+                        "127.0.0.1", "--master-port", "29612", os.path.join(ROOT, "tests", "dist_gpu_worker.py")],
+                       env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
+    print(r.stdout[-2000:])
+    assert r.returncode == 0, r.stdout[-3000:]
+    assert r.stdout.count(" OK") == 2

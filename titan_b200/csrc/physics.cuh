@@ -176,6 +176,41 @@ struct MassExtras {                // rarely-used per-mass data; null pointers =
     int64_t nm;                    // plane stride of SoA arrays
 };
 
+// Rarely-taken parts of the mass update live out of line: the step kernels' hot loop is instruction-cache bound
+// (measured: +15 KB of inert code in the loop cost 9-18 % on B200), so only what every mass executes stays inline.
+struct PVF { V3 pos, vel, force; };
+
+// local constraints of one mass, src/sim.cu:1312-1326: contact planes, balls, constraint planes, directions --
+// each kind in record order; always evaluated with the exact (Strict) forms
+static __device__ __noinline__ PVF local_constraints(const MassExtras X, int64_t i, PVF s) {
+    int b = X.lc_ptr[i], e = X.lc_ptr[i + 1];
+#pragma unroll 1
+    for (int j = b; j < e; j++) if (X.lc[j].kind == TB_CONTACT_PLANE) {
+        tb_plane p = {{X.lc[j].vec[0], X.lc[j].vec[1], X.lc[j].vec[2]}, X.lc[j].num, 0.0, 0.0};
+        contact_plane<Strict>(p, s.pos, s.vel, s.force);
+    }
+#pragma unroll 1
+    for (int j = b; j < e; j++) if (X.lc[j].kind == TB_BALL) {
+        tb_ball bl = {{X.lc[j].vec[0], X.lc[j].vec[1], X.lc[j].vec[2]}, X.lc[j].num};
+        ball<Strict>(bl, s.pos, s.force);
+    }
+#pragma unroll 1
+    for (int j = b; j < e; j++) if (X.lc[j].kind == TB_CONSTRAINT_PLANE) constraint_plane<Strict>(X.lc[j], s.vel, s.force);
+#pragma unroll 1
+    for (int j = b; j < e; j++) if (X.lc[j].kind == TB_DIRECTION) direction<Strict>(X.lc[j], s.vel, s.force);
+    return s;
+}
+
+// drag, src/sim.cu:1329-1332 (C is an int on the device, include/Titan/object.h:213)
+template <class P> static __device__ __noinline__ V3 drag_force(V3 vel, V3 force, int c) {
+    double vn = norm3<P>(vel);
+    if (vn != 0.0) {
+        double coef = P::mul((double)(-c), P::mul(vn, vn));
+        acc3<P>(force, div3<P>(scale3<P>(vel, coef), vn));
+    }
+    return force;
+}
+
 // Everything massForcesAndUpdate does after the spring forces are known (src/sim.cu:1299-1365).
 // force: spring-force sum on entry.  Returns new pos/vel through the references; acc_out = force/m.
 template <class P>
@@ -184,35 +219,18 @@ __device__ __forceinline__ void mass_update(const Globals &G, const MassExtras &
     acc3<P>(force, scale3<P>(V3{G.g[0], G.g[1], G.g[2]}, m));                       // :1299
     if (X.ext) acc3<P>(force, V3{X.ext[i], X.ext[X.nm + i], X.ext[2 * X.nm + i]});   // :1300
     else if (P::strict) acc3<P>(force, V3{0.0, 0.0, 0.0});
-#pragma unroll
-    for (int j = 0; j < TB_INLINE_C; j++) if (j < G.n_planes) contact_plane<P>(G.planes[j], pos, vel, force);
-    for (int j = TB_INLINE_C; j < G.n_planes; j++) contact_plane<P>(G.more_planes[j - TB_INLINE_C], pos, vel, force);
-#pragma unroll
-    for (int j = 0; j < TB_INLINE_C; j++) if (j < G.n_balls) ball<P>(G.balls[j], pos, force);
-    for (int j = TB_INLINE_C; j < G.n_balls; j++) ball<P>(G.more_balls[j - TB_INLINE_C], pos, force);
+    // global planes in creation order, then global balls (:1303-1309); one code instance each, looped
+#pragma unroll 1
+    for (int j = 0; j < G.n_planes; j++) contact_plane<P>(j < TB_INLINE_C ? G.planes[j] : G.more_planes[j - TB_INLINE_C], pos, vel, force);
+#pragma unroll 1
+    for (int j = 0; j < G.n_balls; j++) ball<P>(j < TB_INLINE_C ? G.balls[j] : G.more_balls[j - TB_INLINE_C], pos, force);
 
     if (has_local) {                                                                // :1312-1326
-        int b = X.lc_ptr[i], e = X.lc_ptr[i + 1];
-        for (int j = b; j < e; j++) if (X.lc[j].kind == TB_CONTACT_PLANE) {
-            tb_plane p = {{X.lc[j].vec[0], X.lc[j].vec[1], X.lc[j].vec[2]}, X.lc[j].num, 0.0, 0.0};
-            contact_plane<Strict>(p, pos, vel, force);  // rare path: always the exact form
-        }
-        for (int j = b; j < e; j++) if (X.lc[j].kind == TB_BALL) {
-            tb_ball bl = {{X.lc[j].vec[0], X.lc[j].vec[1], X.lc[j].vec[2]}, X.lc[j].num};
-            ball<Strict>(bl, pos, force);
-        }
-        for (int j = b; j < e; j++) if (X.lc[j].kind == TB_CONSTRAINT_PLANE) constraint_plane<Strict>(X.lc[j], vel, force);
-        for (int j = b; j < e; j++) if (X.lc[j].kind == TB_DIRECTION) direction<Strict>(X.lc[j], vel, force);
+        PVF s = local_constraints(X, i, PVF{pos, vel, force});
+        pos = s.pos; vel = s.vel; force = s.force;
     }
 
-    if (P::strict || X.drag) {                                                      // :1329-1332
-        double vn = norm3<P>(vel);
-        if (vn != 0.0) {
-            int c = X.drag ? X.drag[i] : 0;
-            double coef = P::mul((double)(-c), P::mul(vn, vn));
-            acc3<P>(force, div3<P>(scale3<P>(vel, coef), vn));
-        }
-    }
+    if (P::strict || X.drag) force = drag_force<P>(vel, force, X.drag ? X.drag[i] : 0);   // :1329-1332
 
     if (P::strict) {                                                                // :1356-1361
         acc_out = div3<P>(force, m);

@@ -281,7 +281,7 @@ static size_t blob_size(int n_rec, bool damping, bool active) {
 // every SM busy with one thread per mass (fewest instructions and hand-offs; measured best on C2), small ones
 // (fewer tiles than resident CTAs) are latency bound and split each mass's springs over 4 threads.
 static int choose_tpm(const Engine *e, int64_t n_tiles) {
-    if (e->flags & TB_MATH_STRICT) return 1;
+    if ((e->flags & TB_MATH_STRICT) || e->any_ghost) return 1;
     int tpm = n_tiles >= 2 * (int64_t)e->sm_count ? 1 : 4;
     if (const char *s = getenv("TB_TPM")) { int v = atoi(s); if (v == 1 || v == 2 || v == 4) tpm = v; }
     return tpm;
@@ -377,8 +377,12 @@ static int build_structure(Engine *e, TiledState *S) {
                     if (oslot / TM == T || halo_stamp[(size_t)h.o] == (int32_t)T) continue;
                     int pick = -1;
                     if (cj >= 0) {
-                        const int want = (t + cj) & 15;
-                        for (int x = want; pick < 0; x += 16) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
+                        // preferred residue first, but never at the price of a halo list that no longer fits the
+                        // small shared-memory variant: beyond that budget any free slot will do (a bank conflict
+                        // costs a replay, an oversized list costs occupancy or the tiled format altogether)
+                        const int want = (t + cj) & 15, budget = CS_SMALL - TM - 1;
+                        for (int x = want; pick < 0 && x < budget; x += 16) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
+                        for (int x = 0; pick < 0; x++) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
                     } else {
                         for (int x = 0; x < (int)th.size() + 16 && pick < 0; x++) {
                             bool free_slot = x >= (int)th.size() || th[(size_t)x] < 0;
@@ -535,6 +539,17 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// same, with an L2 eviction policy: spring records are streamed exactly once per step, so they should not push the
+// mass state (which neighbouring tiles re-read as their halo) out of the 126 MB L2
+__device__ __forceinline__ void bulk_g2s_hint(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar, uint64_t policy) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar), "l"(policy) : "memory");
+}
+__device__ __forceinline__ uint64_t l2_policy_evict_first() {
+    uint64_t p;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(p));
+    return p;
+}
 // 1/sqrt(x): MUFU.RSQ64H seed (about 2^-22 relative) + one cubically convergent correction; no special-case
 // branch (x == 0 gives NaN exactly like the reference's temp / temp.norm(), include/Titan/vec.h:133-151)
 __device__ __forceinline__ double rsqrt_fast(double x) {
@@ -577,7 +592,8 @@ struct TiledArgs {
     int32_t n_tiles;
     int32_t write_acc;
     unsigned long long *prof;        // TB_PROFILE=1: per-phase clock64 sums (0 wait full, 1 springs, 2 partial-sum handoff, 3 mass update, 4 producer wait empty, 5 producer wait halo list, 6 producer issue, 7 ell-copy wait)
-    int32_t debug;                   // TB_DEBUG_SKIP bits (timing experiments only): 1 no halo gather, 2 no springs, 4 no mass update
+    int32_t l2_hint;                 // 1: stream the spring-record blobs through L2 with evict_first
+    int32_t debug;                   // TB_DEBUG_SKIP bits (timing experiments only): 1 no halo gather, 2 no springs, 4 no mass update, 8 no peer stores, 16 no peer wait
     SmemPlan sp;
     const double *st_in;
     double *st_out;
@@ -614,13 +630,29 @@ __host__ __device__ inline void chunk_table(int deg, int tpm, uint32_t &cb_packe
     }
 }
 
+// A consumer warp has finished `pending` boundary tiles: make its peer stores visible, count them, and -- as the
+// last warp of the step -- release the step counter into every peer's flag word.  Out of line: runs once per warp
+// and step, and the hot loop's instruction footprint matters.
+__device__ __noinline__ void halo_report(const TiledArgs &A, unsigned pending, unsigned long long seq) {
+    __threadfence_system();   // every lane: its own peer stores are performed system-wide ...
+    __syncwarp();             // ... before lane 0 counts the warp's tiles as done
+    if ((threadIdx.x & 31) == 0) {
+        if (atomicAdd(A.boundary_done, pending) + pending == (unsigned)A.n_boundary_units) {
+            *A.boundary_done = 0u;
+            __threadfence_system();
+#pragma unroll 1
+            for (int p = 0; p < A.n_peers; p++) st_release_sys(A.peer_flag[p], seq + 1ull);
+        }
+    }
+}
+
 // Warp roles: warps 0 .. TM*TPM/32-1 are CONSUMERS (thread = (mass t, share q)); the last warp is the PRODUCER
 // that keeps the two stages filled.  Synchronisation is mbarrier-only between the roles:
 //   full[s]  : 1 expect_tx arrival (bulk copies: blob + own state) + 32 cp.async arrivals (halo gather)
 //   empty[s] : one arrival per consumer warp when it has finished reading stage s
 //   hfull[r] : bulk copy of a halo index list (producer-internal)
 // plus one named barrier per 32-mass column and tile parity for handing the partial sums to thread q == 0.
-template <class P, bool DAMPING, bool ACTIVE, int TPM, int CS>
+template <class P, bool DAMPING, bool ACTIVE, int TPM, int CS, bool HALO>
 __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_kernel(const __grid_constant__ TiledArgs A,
                                                                    const __grid_constant__ Globals G,
                                                                    const __grid_constant__ MassExtras X) {
@@ -671,8 +703,9 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         int4 m0a, m0b, m0c, m1a, m1b, m1c, m2a, m2b, m2c, m3a, m3b, m3c;
         load_meta(0, m0a, m0b, m0c); load_meta(1, m1a, m1b, m1c); load_meta(2, m2a, m2b, m2c);
         if (blockIdx.x == 0 && lane == 0) *A.step_out = *A.step_in + 1;
-        const unsigned long long seq = (unsigned long long)*A.step_in;
-        bool peers_ready = A.n_peers == 0;
+        const unsigned long long seq = HALO ? (unsigned long long)*A.step_in : 0ull;
+        bool peers_ready = !HALO || A.n_peers == 0;
+        const uint64_t pol_stream = l2_policy_evict_first();
         if (lane == 0) { issue_hidx(0, m0a); if (n_my > 1) issue_hidx(1, m1a); }
         long long pp0 = 0, pp1 = 0, pp2 = 0;
         for (int k = 0; k < n_my; k++) {
@@ -683,15 +716,17 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             mbar_wait(bar_empty(s), (uint32_t)(((k >> 1) & 1) ^ 1));    // consumers are done with tile k-2
             long long p1 = A.prof ? clock64() : 0;
             const uint32_t stage = smem_base + (uint32_t)(sp.off_stage + s * sp.stage_bytes);
-            if (!peers_ready && (m0c.z & TF_BOUNDARY)) {
+            if constexpr (HALO) if (!peers_ready && (m0c.z & TF_BOUNDARY)) {
                 // this tile reads ghost slots: every peer must have landed its exports of the previous step
                 // (acquire of the peer's step counter; the peers stored the state before releasing it)
-                if (lane < A.n_peers) {
-                    const long long t0 = clock64();
-                    while (ld_acquire_sys(A.my_flags + lane) < seq) {
-                        if (clock64() - t0 > HALO_TIMEOUT_CLOCKS) { atomicExch(A.halo_err, 1); break; }
-                        __nanosleep(64);
-                    }
+                // warp-uniform spin (every lane polls one peer's word; the vote keeps the warp converged)
+                const unsigned long long *word = A.my_flags + (lane < A.n_peers ? lane : 0);
+                const long long t0 = clock64();
+                while (!(A.debug & 16)) {
+                    const bool ok = ld_acquire_sys(word) >= seq;
+                    if (__all_sync(0xffffffffu, ok)) break;
+                    if (__any_sync(0xffffffffu, clock64() - t0 > HALO_TIMEOUT_CLOCKS)) { if (lane == 0) atomicExch(A.halo_err, 1); break; }
+                    __nanosleep(64);
                 }
                 __syncwarp();
                 asm volatile("fence.proxy.async;" ::: "memory");   // the bulk copies below read what the peers wrote
@@ -699,12 +734,13 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             }
             if (lane == 0) {
                 TileCtrl *c = reinterpret_cast<TileCtrl *>(smem + sp.off_ctrl) + s;
-                c->exp_off = (uint32_t)m0c.x; c->exp_rows = (uint32_t)m0c.y; c->tflags = (uint32_t)m0c.z;
+                if (HALO) { c->exp_off = (uint32_t)m0c.x; c->exp_rows = (uint32_t)m0c.y; c->tflags = (uint32_t)m0c.z; }
                 uint32_t cbp, nchp;
                 chunk_table(m1b.y, TPM, cbp, nchp);
                 c->next_ell_off = (uint32_t)m1b.x; c->next_cb = cbp; c->next_nch = nchp; c->has_next = (k + 1 < n_my) ? 1u : 0u;
                 mbar_expect_tx(bar_full(s), (uint32_t)m0a.y + (uint32_t)(STATE_BLOCK * 8));
-                bulk_g2s(stage, A.blob + (size_t)(uint32_t)m0a.x * 16, (uint32_t)m0a.y, bar_full(s));
+                if (A.l2_hint) bulk_g2s_hint(stage, A.blob + (size_t)(uint32_t)m0a.x * 16, (uint32_t)m0a.y, bar_full(s), pol_stream);
+                else bulk_g2s(stage, A.blob + (size_t)(uint32_t)m0a.x * 16, (uint32_t)m0a.y, bar_full(s));
                 const double *sb = A.st_in + tile_of(k) * STATE_BLOCK;
 #pragma unroll
                 for (int c3 = 0; c3 < 3; c3++) {
@@ -741,7 +777,10 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     // ============================================= CONSUMER warps ============================================
     const int t = tid % TM, q = tid / TM;
     const double t_sim = *A.t_in;
-    const unsigned long long seq = (unsigned long long)*A.step_in;
+    const unsigned long long seq = HALO ? (unsigned long long)*A.step_in : 0ull;
+    unsigned pending = 0;   // boundary tiles this warp has finished but not yet reported (HALO)
+    // Boundary tiles come first in the tile order, so they are a prefix of every CTA's sequence: the warp reports
+    // them with ONE system-scope fence when it reaches its first interior tile (or runs out of tiles).
     // this thread's ELL words: chunks [cb, cb + nch) of the tile's block, rows of TM words
     auto load_ell = [&](uint32_t ell_off, int cb, int nch, uint32_t (&dst)[EPT]) {
         const uint32_t *src = A.ell + ell_off + (size_t)cb * ELL_CHUNK * TM + t;
@@ -771,7 +810,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         mbar_wait(bar_full(s), (uint32_t)((i >> 1) & 1));     // blob, own state and halo of tile i have landed
         long long c1 = A.prof ? clock64() : 0;
         const unsigned char *stage = smem + sp.off_stage + s * sp.stage_bytes;
-        const TileCtrl ctrl = reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl)[s];
+        const uint4 ctrl4 = *reinterpret_cast<const uint4 *>(smem + sp.off_ctrl + s * sizeof(TileCtrl));   // next_ell_off, next_cb, next_nch, has_next
+        struct { uint32_t next_ell_off, next_cb, next_nch, has_next; } ctrl = {ctrl4.x, ctrl4.y, ctrl4.z, ctrl4.w};
         if (ctrl.has_next) {   // next tile's words -> registers
             nch_nxt = (int)((ctrl.next_nch >> (8 * q)) & 0xff);
             load_ell(ctrl.next_ell_off, (int)((ctrl.next_cb >> (8 * q)) & 0xff), nch_nxt, ell_nxt);
@@ -879,33 +919,33 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                 mass_update<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force, acc);
                 if (A.write_acc) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
             }
-            if (!(fl & F_GHOST)) {     // a ghost's slot belongs to the peer that owns the mass
+            if (!HALO || !(fl & F_GHOST)) {     // a ghost's slot belongs to the peer that owns the mass
                 ob[0] = pos.x; ob[TM] = pos.y; ob[2 * TM] = pos.z;
                 ob[3 * TM] = vel.x; ob[4 * TM] = vel.y; ob[5 * TM] = vel.z;
             }
-            // halo exchange: the new state of a mass that is a ghost elsewhere goes straight into the peer's buffer
-            for (uint32_t r = 0; r < ctrl.exp_rows; r++) {
-                const int2 x = __ldg(A.exp_tab + ctrl.exp_off + r * TM + t);
-                if (x.x >= 0) {
-                    double *d = A.peer_out[x.x] + x.y;
-                    d[0] = pos.x; d[TM] = pos.y; d[2 * TM] = pos.z;
-                    d[3 * TM] = vel.x; d[4 * TM] = vel.y; d[5 * TM] = vel.z;
+            if (HALO) {
+                // halo exchange: the new state of a mass that is a ghost elsewhere goes straight into the peer's buffer
+                // (the exchange fields of the tile control word are read only now, to keep them out of the hot loop)
+                const TileCtrl *cp = reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl) + s;
+                const uint32_t exp_rows = (A.debug & 8) ? 0u : cp->exp_rows, exp_off = cp->exp_off;
+                for (uint32_t r = 0; r < exp_rows; r++) {
+                    const int2 x = __ldg(A.exp_tab + exp_off + r * TM + t);
+                    if (x.x >= 0) {
+                        double *d = A.peer_out[x.x] + x.y;
+                        d[0] = pos.x; d[TM] = pos.y; d[2 * TM] = pos.z;
+                        d[3 * TM] = vel.x; d[4 * TM] = vel.y; d[5 * TM] = vel.z;
+                    }
                 }
             }
         }
-        if (ctrl.tflags & TF_BOUNDARY) __threadfence_system();   // exports visible before this warp is counted as done
+        bool boundary_tile = false;
+        if (HALO) boundary_tile = (reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl)[s].tflags & TF_BOUNDARY) != 0;
         __syncwarp();
         long long c4 = A.prof ? clock64() : 0;
-        if ((tid & 31) == 0) {
-            mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
-            if ((ctrl.tflags & TF_BOUNDARY) && A.n_peers > 0) {
-                // last boundary warp of the step: release the step counter into every peer's flag word
-                if (atomicAdd(A.boundary_done, 1u) == (unsigned)A.n_boundary_units - 1u) {
-                    *A.boundary_done = 0u;
-                    __threadfence_system();
-                    for (int p = 0; p < A.n_peers; p++) st_release_sys(A.peer_flag[p], seq + 1ull);
-                }
-            }
+        if ((tid & 31) == 0) mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
+        if (HALO && A.n_peers > 0) {
+            if (boundary_tile) pending++;
+            else if (pending) { halo_report(A, pending, seq); pending = 0; }
         }
 #pragma unroll
         for (int jj = 0; jj < EPT; jj++) ell_cur[jj] = ell_nxt[jj];
@@ -919,6 +959,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             pa0 += c1 - c0; pa1 += c2 - c1; pa2 += c3 - c2; pa3 += c4 - c3; pa4 += c5 - c4;
         }
     }
+    if (HALO && pending) halo_report(A, pending, seq);
     if (A.prof && (tid & 31) == 0) {
         unsigned long long *pp = A.prof + 8 * (q > 0);
         atomicAdd(pp + 0, (unsigned long long)pa0); atomicAdd(pp + 1, (unsigned long long)pa1); atomicAdd(pp + 2, (unsigned long long)pa2);
@@ -927,11 +968,11 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
 }
 
 // ---------------------------------------------------------------- glue ------------------------------------
-template <class P, bool D, bool AC, int TPM, int CS>
+template <class P, bool D, bool AC, int TPM, int CS, bool HALO>
 static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     static size_t configured_smem = 0;     // per template instantiation
     static int blocks_per_sm = 0;
-    auto kern = tiled_step_kernel<P, D, AC, TPM, CS>;
+    auto kern = tiled_step_kernel<P, D, AC, TPM, CS, HALO>;
     if (configured_smem != S->smem_bytes) {
         TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S->smem_bytes));
         TB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, TM * TPM + 32, S->smem_bytes));
@@ -946,8 +987,13 @@ static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtr
 }
 template <class P, bool D, bool AC, int TPM>
 static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
-    if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG>(e, S, A, X);
-    return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL)>(e, S, A, X);
+    static const bool force_halo = getenv("TB_FORCE_HALO") != nullptr;   // measurement aid: exchange code compiled in, inert
+    if (A.n_peers > 0 || e->any_ghost || force_halo) {   // partitioned: one thread per mass (choose_tpm), exchange code compiled in
+        if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, 1, CS_BIG, true>(e, S, A, X);
+        return launch_c<P, D, AC, 1, (P::strict ? CS_BIG : CS_SMALL), true>(e, S, A, X);
+    }
+    if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG, false>(e, S, A, X);
+    return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL), false>(e, S, A, X);
 }
 template <class P, int TPM> static int launch_f(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     bool d = S->has_damping, a = S->has_active;
@@ -1013,6 +1059,8 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
         A.prof = g_prof_dev; g_prof_launches++;
     }
     A.debug = 0;
+    A.l2_hint = 1;
+    if (const char *h = getenv("TB_L2_HINT")) A.l2_hint = atoi(h);
     if (const char *d = getenv("TB_DEBUG_SKIP")) A.debug = atoi(d);
     A.sp = plan_smem(S->cs, S->max_halo, S->max_blob, S->stage_vel, S->tpm);
     A.st_in = S->st[e->cur]; A.st_out = S->st[e->cur ^ 1];

@@ -114,12 +114,29 @@ def brick_dims(nx, ny, nz, tile=128):
     return best[1]
 
 
-def brick_hint(nx, ny, nz, tile=128, base=0):
-    """Tile id per mass (reference mass order, i outermost) for tb_set_tile_hint: bricks of lattice cells."""
+def brick_hint(nx, ny, nz, tile=128, base=0, block=None):
+    """Tile id per mass (reference mass order, i outermost) for tb_set_tile_hint: bricks of lattice cells.
+
+    Ids order the tiles in the step kernel.  Bricks are numbered super-block by super-block (`block`^3 bricks each,
+    default TB_TILE_BLOCK or 8) rather than plane by plane: the persistent CTAs then work on a compact 3-D
+    neighbourhood, so the state a tile gathers as its halo was touched a few hundred tiles ago and is still in L2,
+    instead of a whole lattice cross-section (tens of MB of streamed spring records) ago."""
+    import os
+    if block is None:
+        block = int(os.environ.get("TB_TILE_BLOCK", "8"))
     bx, by, bz = brick_dims(nx, ny, nz, tile)
     ti = np.arange(nx, dtype=np.int64) // bx
     tj = np.arange(ny, dtype=np.int64) // by
     tk = np.arange(nz, dtype=np.int64) // bz
-    ntj, ntk = -(-ny // by), -(-nz // bz)
-    ids = (ti[:, None, None] * ntj + tj[None, :, None]) * ntk + tk[None, None, :]
+    nti, ntj, ntk = -(-nx // bx), -(-ny // by), -(-nz // bz)
+    if block and block > 1 and max(nti, ntj, ntk) > block:
+        bi, bj, bk = np.meshgrid(np.arange(nti), np.arange(ntj), np.arange(ntk), indexing="ij")
+        keys = (bk % block, bj % block, bi % block, bk // block, bj // block, bi // block)   # last key = most significant
+        order = np.lexsort(tuple(k.ravel() for k in keys))
+        rank_of = np.empty(order.size, dtype=np.int64)
+        rank_of[order] = np.arange(order.size)
+        brick_id = rank_of.reshape(nti, ntj, ntk)
+    else:
+        brick_id = (np.arange(nti)[:, None, None] * ntj + np.arange(ntj)[None, :, None]) * ntk + np.arange(ntk)[None, None, :]
+    ids = brick_id[ti[:, None, None], tj[None, :, None], tk[None, None, :]]
     return (ids.reshape(-1) + base).astype(np.int32)
