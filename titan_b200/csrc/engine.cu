@@ -348,6 +348,7 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
     e->any_damping = e->any_active = e->any_actuated = e->any_local = e->any_magnet = e->any_fixed_or_invalid = e->any_ghost = false;
     e->graph_dirty = true; e->tiled_stale = 0xf; e->canon_stale = false; e->tile_hint.clear();
     e->h_type.assign((size_t)ns, 0);
+    e->h_omega.clear();
     return TB_OK;
 }
 
@@ -495,6 +496,10 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
             TB_TRY(ensure_spring_array<int32_t>(e, &e->type, 0));
             TB_TRY(up_scalar<int32_t>(e, e->type, type, idx, first, count));
         }
+    }
+    if (omega) {
+        if (e->h_omega.size() != (size_t)e->ns) e->h_omega.assign((size_t)e->ns, 0.0);
+        for (int64_t j = 0; j < count; j++) e->h_omega[(size_t)(idx ? idx[j] : first + j)] = omega[j];
     }
     struct { const double *src; double **dst; } opt[4] = {{omega, &e->omega}, {l_max, &e->l_max}, {l_min, &e->l_min}, {rate, &e->rate}};
     for (auto &o : opt) {

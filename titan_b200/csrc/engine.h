@@ -63,6 +63,7 @@ struct Engine {
     std::vector<tb_ball> balls;
     std::vector<uint8_t> h_flags;  // mirror of mflags
     std::vector<uint8_t> h_type;   // mirror of the spring types
+    std::vector<double> h_omega;   // mirror of the actuation frequencies (distinct-omega sine table of the tiled kernel)
     std::vector<int32_t> h_left, h_right, h_row_ptr, h_adj;  // host copy of the topology + CSR (tile builder)
     std::vector<double> h_T0;      // per-mass T at its last upload
     std::vector<int64_t> h_n0;     // steps_done at that upload

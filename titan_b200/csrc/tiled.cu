@@ -74,6 +74,7 @@ __host__ __device__ constexpr int ell_words_per_thread(int tpm) {
 }
 constexpr size_t SMEM_LIMIT = 227 * 1024;
 constexpr int HALO_RING = 3;
+constexpr int MAX_OMEGA = 64;           // distinct actuation frequencies served from the per-CTA sine table
 constexpr int BLOB_HDR = 16, BLOB_FLAGS = BLOB_HDR, BLOB_M = BLOB_FLAGS + TM, BLOB_REC = BLOB_M + TM * 8;
 constexpr int STATE_BLOCK = 6 * TM;     // doubles per tile in a state buffer
 
@@ -113,6 +114,8 @@ struct TiledState {
     std::vector<TileMeta> h_meta;
     bool supported = false;
     std::string why_not;
+    // distinct actuation frequencies: sin(omega t) is evaluated once per CTA and step instead of once per spring
+    double *omega_tab = nullptr; int n_omega = 0;
     // ---- halo exchange (partitioned simulation) ----
     int64_t n_active = 0;                 // tiles the step kernel processes (ghost-only tiles come last and are skipped)
     int64_t n_boundary = 0;               // tiles [0, n_boundary) reach ghosts
@@ -227,7 +230,7 @@ struct SmemPlan {            // byte offsets inside the dynamic shared memory of
     int32_t cs;              // stride of one position component: TM own masses + halo, even
     int32_t vs;              // stride of one velocity component (cs when halo velocities are staged, else TM)
     int32_t hring_stride;    // bytes of one halo-index ring entry
-    int32_t off_ctrl, off_hring, off_part, part_bytes, off_stage, stage_bytes;
+    int32_t off_ctrl, off_sintab, off_hring, off_part, part_bytes, off_stage, stage_bytes;
     int32_t st_pos, st_vel;  // offsets inside a stage (the blob sits at 0)
     int32_t total;
 };
@@ -243,7 +246,8 @@ static SmemPlan plan_smem(int cs, int max_halo, int max_blob, bool stage_vel, in
     p.vs = stage_vel ? p.cs : TM;
     p.hring_stride = (int32_t)up16((size_t)hp * 4 + 16);
     p.off_ctrl = 64;
-    p.off_hring = 128;
+    p.off_sintab = 128;
+    p.off_hring = 128 + MAX_OMEGA * 8;
     p.off_part = p.off_hring + HALO_RING * p.hring_stride;
     p.part_bytes = (tpm - 1) * 3 * TM * 8;
     p.off_stage = p.off_part + 2 * p.part_bytes;
@@ -503,7 +507,7 @@ __global__ void tiled_refresh_mass(uint8_t *blob, const TileMeta *meta, const in
 // one CTA per tile: the spring records of the tile's blob
 __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const int32_t *rec_spring, const double *k,
                                      const double *rest, const double *damping, const double *omega, int has_damping,
-                                     int has_active) {
+                                     int has_active, const double *omega_tab, int n_omega) {
     const TileMeta M = meta[blockIdx.x];
     uint8_t *b = blob + (size_t)M.blob_off16 * 16;
     double2 *rec = (double2 *)(b + BLOB_REC);
@@ -513,7 +517,15 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
         int32_t s = rec_spring[M.rec_off + r];
         rec[r] = s >= 0 ? make_double2(k[s], rest[s]) : make_double2(0.0, 0.0);
         if (has_damping) dmp[r] = (s >= 0 && damping) ? damping[s] : 0.0;
-        if (has_active) omg[r] = (s >= 0 && omega) ? omega[s] : 0.0;
+        if (has_active) {
+            double w = (s >= 0 && omega) ? omega[s] : 0.0;
+            if (n_omega > 0) {      // table mode: the slot holds the index of omega in the distinct-value table
+                int found = 0;
+                for (int q = 0; q < n_omega; q++) if (__double_as_longlong(omega_tab[q]) == __double_as_longlong(w)) found = q;
+                w = __longlong_as_double((long long)found);
+            }
+            omg[r] = w;
+        }
     }
 }
 
@@ -604,6 +616,8 @@ struct TiledArgs {
     double *acc;                     // canonical (API-ordered) acceleration, stride X.nm
     const double *t_in;
     double *t_out;
+    const double *omega_tab;         // [n_omega] distinct actuation frequencies (n_omega == 0: per-spring sin)
+    int32_t n_omega;
     // ---- halo exchange (n_peers == 0: single-engine simulation, everything below unused) ----
     int32_t n_peers;
     int32_t n_boundary_units;        // boundary tiles x consumer warps: arrivals that complete a step's exports
@@ -628,6 +642,21 @@ __host__ __device__ inline void chunk_table(int deg, int tpm, uint32_t &cb_packe
         if (nch < 0) nch = 0;
         cb_packed |= (uint32_t)cb << (8 * q); nch_packed |= (uint32_t)nch << (8 * q);
     }
+}
+
+// sin(omega t) of an ACTIVE_* spring: from the CTA's table of distinct frequencies (the record then holds the table
+// index), else evaluated per spring, out of line.  Same argument, same sin(): bit-identical either way.
+template <class P> static __device__ __noinline__ double sin_omega_t(double omega, double t) { return sin(P::mul(omega, t)); }
+// Table mode, branch-free: scale = 1 + c sin(omega t), c = 0 / -0.2 / +0.2 for passive / contract-then-expand /
+// expand-then-contract.  Bit-identical to the reference's 1 -/+ 0.2 sin(.) and to rest * 1.0 for passive springs
+// (IEEE: (-0.2) s == -(0.2 s), 1 + (-x) == 1 - x, 1 + 0 s == 1).
+template <class P> __device__ __forceinline__ double actuation_table(int ty, const double *sintab, const char *slot) {
+    const double c = ty == 1 ? -0.2 : (ty == 2 ? 0.2 : 0.0);
+    return P::add(1.0, P::mul(c, sintab[*reinterpret_cast<const int *>(slot)]));
+}
+// ty: 1 = contract-then-expand (1 - 0.2 sin), 2 = expand-then-contract (1 + 0.2 sin), src/sim.cu:1168-1173
+template <class P> __device__ __forceinline__ double actuation_from_sin(int ty, double sn) {
+    return ty == 1 ? P::sub(1.0, P::mul(0.2, sn)) : P::add(1.0, P::mul(0.2, sn));
 }
 
 // A consumer warp has finished `pending` boundary tiles: make its peer stores visible, count them, and -- as the
@@ -676,6 +705,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
+    if (ACTIVE && tid < A.n_omega)   // sin(omega t) once per CTA and step for every distinct omega (src/sim.cu:1168-1173)
+        reinterpret_cast<double *>(smem + sp.off_sintab)[tid] = sin(P::mul(A.omega_tab[tid], *A.t_in));
     if (tid < 2) {   // the dummy mass of both stages: far away, at rest
         double *pp = reinterpret_cast<double *>(smem + sp.off_stage + tid * sp.stage_bytes + sp.st_pos);
         pp[CS - 1] = 1e30; pp[2 * CS - 1] = 1e30; pp[3 * CS - 1] = 1e30;
@@ -777,6 +808,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     // ============================================= CONSUMER warps ============================================
     const int t = tid % TM, q = tid / TM;
     const double t_sim = *A.t_in;
+    const double *sintab = reinterpret_cast<const double *>(smem + sp.off_sintab);
     const unsigned long long seq = HALO ? (unsigned long long)*A.step_in : 0ull;
     unsigned pending = 0;   // boundary tiles this warp has finished but not yet reported (HALO)
     // Boundary tiles come first in the tile order, so they are a prefix of every CTA's sequence: the warp reports
@@ -846,7 +878,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                         spr.damping = DAMPING ? *(const double *)(dmb + (rco >> 1)) : 0.0;
                         if (ACTIVE) {
                             const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                            if (ty) spr.rest_scaled = P::mul(kr.y, actuation_scale<P>(ty + 1, *(const double *)(omb + (rco >> 1)), t_sim));
+                            if (A.n_omega > 0) spr.rest_scaled = P::mul(kr.y, actuation_table<P>(ty, sintab, omb + (rco >> 1)));
+                            else if (ty) spr.rest_scaled = P::mul(kr.y, actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + (rco >> 1)), t_sim)));
                         }
                         if (en & ELL_SIDE) acc3<P>(force, spring_force<P, DAMPING>(po, pos, vo, vel, spr));
                         else { V3 f = spring_force<P, DAMPING>(pos, po, vel, vo, spr); acc3<P>(force, V3{-f.x, -f.y, -f.z}); }
@@ -872,7 +905,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                         double rest = kr.y;
                         if (ACTIVE) {
                             const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                            if (ty) rest = kr.y * actuation_scale<P>(ty + 1, *(const double *)(omb + (rco >> 1)), t_sim);
+                            if (A.n_omega > 0) rest = kr.y * actuation_table<P>(ty, sintab, omb + (rco >> 1));   // branch-free
+                            else if (ty) rest = kr.y * actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + (rco >> 1)), t_sim));
                         }
                         const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
                         const double inv = rsqrt_fast(L2);
@@ -1040,9 +1074,25 @@ int tiled_prepare(Engine *e) {
     }
     if (stale & (TS_FLAGS | TS_STATE))
         tiled_refresh_mass<<<(unsigned)S->n_tiles, TM, 0, e->stream>>>(S->blob, S->meta, S->slot_to_api, e->m, e->mflags);
+    if ((stale & TS_PARAMS) && S->has_active) {
+        // distinct omegas of the ACTIVE_* springs (bit patterns); more than MAX_OMEGA -> per-spring sin() in the kernel
+        std::map<uint64_t, int> seen;
+        std::vector<double> tab;
+        bool table = e->h_omega.size() == (size_t)e->ns && e->h_type.size() == (size_t)e->ns;
+        for (int64_t sp = 0; table && sp < e->ns; sp++) {
+            if (e->h_type[(size_t)sp] != 2 && e->h_type[(size_t)sp] != 3) continue;
+            uint64_t bits; memcpy(&bits, &e->h_omega[(size_t)sp], 8);
+            if (seen.emplace(bits, (int)tab.size()).second) { tab.push_back(e->h_omega[(size_t)sp]); if (tab.size() > (size_t)MAX_OMEGA) table = false; }
+        }
+        if (!S->omega_tab) TB_CUDA(e, cudaMalloc((void **)&S->omega_tab, MAX_OMEGA * 8));
+        S->n_omega = (table && !tab.empty()) ? (int)tab.size() : 0;
+        if (S->n_omega) TB_CUDA(e, cudaMemcpyAsync(S->omega_tab, tab.data(), tab.size() * 8, cudaMemcpyHostToDevice, e->stream));
+        TB_CUDA(e, cudaStreamSynchronize(e->stream));   // `tab` is a local
+        e->graph_dirty = true;
+    }
     if (stale & TS_PARAMS)
         tiled_refresh_params<<<(unsigned)S->n_tiles, 128, 0, e->stream>>>(S->blob, S->meta, S->rec_spring, e->k, e->rest, e->damping,
-                                                                          e->omega, S->has_damping ? 1 : 0, S->has_active ? 1 : 0);
+                                                                          e->omega, S->has_damping ? 1 : 0, S->has_active ? 1 : 0, S->omega_tab, S->n_omega);
     TB_CUDA(e, cudaGetLastError());
     e->tiled_stale = 0;
     return TB_OK;
@@ -1067,6 +1117,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     A.blob = S->blob; A.slot_to_api = S->slot_to_api; A.halo = S->halo; A.ell = S->ell; A.meta = S->meta;
     A.acc = e->acc;
     A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + (e->cur ^ 1);
+    A.omega_tab = S->omega_tab; A.n_omega = S->has_active ? S->n_omega : 0;
     A.step_in = e->step_dev + e->cur; A.step_out = e->step_dev + (e->cur ^ 1);
     A.n_peers = 0; A.n_boundary_units = 0; A.my_flags = nullptr; A.exp_tab = nullptr; A.boundary_done = nullptr; A.halo_err = nullptr;
     for (int p = 0; p < TB_MAX_PEERS; p++) { A.peer_flag[p] = nullptr; A.peer_out[p] = nullptr; }
@@ -1118,6 +1169,7 @@ void tiled_destroy(Engine *e) {
     }
     if (!e->tiled) return;
     halo_release(e, e->tiled);
+    if (e->tiled->omega_tab) cudaFree(e->tiled->omega_tab);
     if (e->tiled->flags_dev) { cudaFree(e->tiled->flags_dev); cudaFree(e->tiled->done_dev); cudaFree(e->tiled->err_dev); }
     free_structure(e, e->tiled);
     delete e->tiled;
