@@ -107,6 +107,11 @@ TB_API int tb_get_mass_state(tb_engine *e, int64_t first, int64_t count, const i
 TB_API int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32_t *idx,
                          const double *k, const double *rest, const double *damping, const int32_t *type,
                          const double *omega, const double *l_max, const double *l_min, const double *rate);
+/* Simulation::deleteSpring after start() (src/sim.cu:382-412) without a topology rebuild: the listed springs become
+ * tombstones -- they keep their index but exert no force from now on (k and damping forced to zero, also after later
+ * tb_set_spring_params calls), which is bit-identical to their absence.  Compaction = a new tb_set_topology.
+ * Used by the topology-optimisation workload (BASELINE config C5: remove the weakest springs every 100 steps). */
+TB_API int tb_remove_springs(tb_engine *e, int64_t n, const int32_t *idx);
 /* Spring::update copies back only _rest (src/spring.cu:12-14) */
 TB_API int tb_get_spring_rest(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, double *rest);
 
@@ -183,6 +188,7 @@ typedef struct {
     int32_t smem_bytes;          /* tiled kernel: dynamic shared memory per CTA */
     int32_t ell_unique_tiles;    /* tiled kernel: distinct incidence (ELL) blocks after content dedupe */
     int64_t tiled_bytes_per_step;/* tiled kernel: bytes one step streams from its tables (blob+state+halo+ELL+meta) */
+    int64_t ns_removed;          /* springs turned into tombstones by tb_remove_springs */
 } tb_info;
 TB_API int tb_get_info(tb_engine *e, tb_info *info);
 /* headless position export, fp64 -> packed fp32 xyz (updateVertices, src/sim.cu:1944-1952); out is a

@@ -18,7 +18,7 @@ CONSTRAINT_PLANE, CONTACT_PLANE, BALL, DIRECTION = range(4)
 
 EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_last_error", "tb_set_topology", "tb_set_tile_hint",
            "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
-           "tb_get_spring_rest", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
+           "tb_get_spring_rest", "tb_remove_springs", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
            "tb_run_async", "tb_sync", "tb_steps_done", "tb_last_run_ms", "tb_get_info",
            "tb_export_positions_f32_dev", "tb_alloc_host", "tb_halo_set_ghosts", "tb_halo_prepare",
            "tb_halo_state_offsets", "tb_halo_connect", "tb_halo_set_exports", "tb_halo_push_now"]
@@ -44,7 +44,7 @@ class Info(C.Structure):
                 ("launches", C.c_int64), ("device_bytes", C.c_int64), ("algorithmic_bytes_per_step", C.c_double),
                 ("sm_count", C.c_int32), ("graph_steps", C.c_int32), ("threads_per_mass", C.c_int32),
                 ("grid", C.c_int32), ("smem_bytes", C.c_int32), ("ell_unique_tiles", C.c_int32),
-                ("tiled_bytes_per_step", C.c_int64)]
+                ("tiled_bytes_per_step", C.c_int64), ("ns_removed", C.c_int64)]
 
 
 class TitanError(RuntimeError):
@@ -77,6 +77,7 @@ def lib():
         L.tb_get_mass_state.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 6
         L.tb_set_spring_params.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 9
         L.tb_get_spring_rest.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp]
+        L.tb_remove_springs.argtypes = [_vp, C.c_int64, _vp]
         L.tb_set_planes.argtypes = [_vp, C.c_int32, _vp]
         L.tb_set_balls.argtypes = [_vp, C.c_int32, _vp]
         L.tb_set_local_constraints.argtypes = [_vp, _vp, _vp]
@@ -256,6 +257,11 @@ class Engine:
         out = np.zeros(count)
         self._ck(self._L.tb_get_spring_rest(self._h, first, count, ip, out.ctypes.data_as(_vp)))
         return out
+
+    def remove_springs(self, idx):
+        """Turn springs into tombstones (no force from now on; indices of the others unchanged)."""
+        a, ap = _arr(idx, np.int32)
+        self._ck(self._L.tb_remove_springs(self._h, a.shape[0], ap))
 
     def alloc_pinned(self, shape, dtype=np.float64):
         """A numpy array over page-locked host memory (tb_alloc_host); freed with the engine."""

@@ -89,6 +89,13 @@ __global__ void gather_scalar(T *dst, const T *src, const int32_t *idx, int64_t 
     if (j >= count) return;
     dst[j] = src[idx ? idx[j] : first + j];
 }
+// tombstones stay dead whatever the caller uploads later (tb_remove_springs)
+__global__ void apply_tombstones_kernel(double *k, double *damping, const uint8_t *removed, int64_t ns) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ns || !removed[s]) return;
+    k[s] = 0.0;
+    if (damping) damping[s] = 0.0;
+}
 template <class T> __global__ void fill_kernel(T *dst, T v, int64_t n) {
     int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j < n) dst[j] = v;
@@ -192,6 +199,8 @@ static void free_all(Engine *e) {
     F(e->k, s1); F(e->rest, s1); F(e->damping, s1); F(e->omega, s1); F(e->l_max, s1); F(e->l_min, s1); F(e->rate, s1);
     F(e->row_ptr, (size_t)(e->nm + 1) * 4); F(e->adj, (size_t)e->ns * 8);
     F(e->export_f32, (size_t)e->nm * 12);
+    F(e->removed_dev, (size_t)e->ns);
+    e->h_removed.clear(); e->n_removed = 0;
     if (e->lc_ptr) { cudaFree(e->lc_ptr); e->lc_ptr = nullptr; }
     if (e->lc) { cudaFree(e->lc); e->lc = nullptr; }
     for (int p = 0; p < 2; p++) if (e->graph[p]) { cudaGraphExecDestroy(e->graph[p]); e->graph[p] = nullptr; }
@@ -508,8 +517,34 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
         TB_TRY(ensure_spring_array<double>(e, o.dst, 0.0));
         TB_TRY(up_scalar<double>(e, *o.dst, o.src, idx, first, count));
     }
+    if (e->n_removed > 0 && (k || damping)) {
+        apply_tombstones_kernel<<<blocks_for(e->ns), 256, 0, e->stream>>>(e->k, e->damping, e->removed_dev, e->ns);
+        TB_CUDA(e, cudaGetLastError());
+    }
     e->tiled_stale |= TS_PARAMS | (type ? TS_STRUCT : 0u);
     e->graph_dirty = true;
+    return TB_OK;
+}
+
+int tb_remove_springs(tb_engine *e, int64_t n, const int32_t *idx) {
+    E_CHECK(e);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_remove_springs before tb_set_topology");
+    if (n < 0 || (n > 0 && !idx)) return fail(e, TB_ERR_INVALID, "tb_remove_springs: bad arguments");
+    TB_TRY(check_range(e, e->ns, 0, n, idx, "tb_remove_springs"));
+    if (n == 0) return TB_OK;
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (e->h_removed.empty()) {
+        e->h_removed.assign((size_t)e->ns, 0);
+        TB_TRY(dev_alloc(e, &e->removed_dev, (size_t)e->ns));
+        TB_CUDA(e, cudaMemsetAsync(e->removed_dev, 0, (size_t)e->ns, e->stream));
+    }
+    std::vector<uint8_t> ones((size_t)n, 1);
+    for (int64_t j = 0; j < n; j++)
+        if (!e->h_removed[(size_t)idx[j]]) { e->h_removed[(size_t)idx[j]] = 1; e->n_removed++; }
+    TB_TRY(up_scalar<uint8_t>(e, e->removed_dev, ones.data(), idx, 0, n));
+    apply_tombstones_kernel<<<blocks_for(e->ns), 256, 0, e->stream>>>(e->k, e->damping, e->removed_dev, e->ns);
+    TB_CUDA(e, cudaGetLastError());
+    e->tiled_stale |= TS_PARAMS;
     return TB_OK;
 }
 
@@ -744,9 +779,10 @@ int tb_get_info(tb_engine *e, tb_info *info) {
     info->device_bytes = e->device_bytes;
     // 104 B per mass (read pos,vel,m; write pos,vel) + per spring 24 B (+8 damping, +12 actuated)
     double bs = 24.0 + (e->any_damping ? 8.0 : 0.0) + ((e->any_active || e->any_actuated) ? 12.0 : 0.0);
-    info->algorithmic_bytes_per_step = 104.0 * (double)e->nm + bs * (double)e->ns;
+    info->algorithmic_bytes_per_step = 104.0 * (double)e->nm + bs * (double)(e->ns - e->n_removed);
     info->sm_count = e->sm_count;
     info->graph_steps = (e->flags & TB_NO_GRAPH) ? 0 : GRAPH_STEPS;
+    info->ns_removed = e->n_removed;
     tiled_info(e, info);
     return TB_OK;
 }

@@ -63,6 +63,9 @@ struct Engine {
     std::vector<tb_ball> balls;
     std::vector<uint8_t> h_flags;  // mirror of mflags
     std::vector<uint8_t> h_type;   // mirror of the spring types
+    std::vector<uint8_t> h_removed; // tombstones (tb_remove_springs); empty until the first removal
+    uint8_t *removed_dev = nullptr;
+    int64_t n_removed = 0;
     std::vector<double> h_omega;   // mirror of the actuation frequencies (distinct-omega sine table of the tiled kernel)
     std::vector<int32_t> h_left, h_right, h_row_ptr, h_adj;  // host copy of the topology + CSR (tile builder)
     std::vector<double> h_T0;      // per-mass T at its last upload
