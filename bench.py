@@ -200,13 +200,92 @@ def workload_c3(n_robots, first_robot=0):
             "name": "C3: %d independent actuated 10^3 soft robots per rank" % n_robots}
 
 
+def run_c5(args, tb, device, flags):
+    """BASELINE config C5: topology optimisation on an n^3 lattice (n = 200) over a frictional plane
+    and a ball cap; every 100 steps ALL spring constants are rewritten from the host (k_s *= 0.9 + 0.2 h(s)) and the
+    0.1 % weakest live springs are removed (tb_remove_springs).  One bench step = one such edit + 100 simulation steps.
+    `value` = live springs x steps / device time of the stepping; `e2e` = the same over wall time including the k
+    upload (8 B per spring) and the removal calls.  Choosing which springs to remove is the application's optimiser
+    and is not timed."""
+    from titan_b200 import lattice
+    n = args.size
+    side = 0.1 * (n - 1)
+    L = lattice.build_lattice((0.0, 0.0, 1.1 + side / 2), (side, side, side), n, n, n)
+    nm, ns = L["pos"].shape[0], L["left"].shape[0]
+    eng = tb.Engine(device, flags)
+    eng.set_topology(nm, L["left"], L["right"])
+    eng.set_tile_hint(lattice.brick_hint(n, n, n))
+    eng.set_mass_state(pos=L["pos"])
+    eng.set_spring_params(rest=L["rest"])
+    eng.set_planes([tb.Plane((tb.capi.C.c_double * 3)(*PLANE[0]), *PLANE[1:])])
+    eng.set_balls([tb.Ball((tb.capi.C.c_double * 3)(0.0, 0.0, -3.0), 4.0)])
+    eng.set_globals((0.0, 0.0, -9.81), 1e-4)
+    del L
+    s = np.arange(ns, dtype=np.uint64)
+    factor = 0.9 + 0.2 * (((s * np.uint64(2654435761)) % np.uint64(2 ** 32)) % np.uint64(1000)).astype(np.float64) / 1000.0
+    del s
+    k = np.full(ns, 10000.0)
+    live = np.ones(ns, dtype=bool)
+    per = args.inner if args.inner != 200 else 100
+    t_sim, dev_ms, wall, spring_steps, removed_total = 0.0, 0.0, 0.0, 0.0, 0
+
+    def pick():
+        kk = np.where(live, k, np.inf)
+        m = max(1, int(0.001 * live.sum()))
+        idx = np.argpartition(kk, m)[:m]
+        return np.sort(idx).astype(np.int32)
+
+    for it in range(args.warmup + args.steps):
+        k *= factor
+        idx = pick()                                  # untimed: the optimiser's decision
+        w0 = time.perf_counter()
+        eng.set_spring_params(k=k)                    # H2D: 8 B per spring
+        eng.remove_springs(idx)
+        eng.run_async(per, t_sim)
+        eng.sync()
+        w1 = time.perf_counter()
+        live[idx] = False
+        for _ in range(per):
+            t_sim += 1e-4
+        if it >= args.warmup:
+            dev_ms += eng.last_run_ms()
+            wall += w1 - w0
+            spring_steps += float(live.sum()) * per
+            removed_total += idx.size
+    info = eng.info()
+    st = eng.get_mass_state(first=0, count=1000, fields=("pos",))
+    assert np.isfinite(st["pos"]).all()
+    peak, peak_src = load_peaks()
+    n_live = float(live.sum())
+    step_us = dev_ms * 1e3 / (per * args.steps)
+    alg = 104.0 * nm + 24.0 * n_live
+    line = {"metric": METRIC, "value": spring_steps / (dev_ms * 1e-3), "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C5: %d^3 lattice, plane + ball cap, every %d steps all k rewritten and the 0.1 %% weakest springs removed" % (n, per),
+                       "masses": nm, "springs": ns, "springs_live_at_end": int(n_live), "removed_in_timed_region": int(removed_total),
+                       "sim_steps_per_bench_step": per, "math": "strict" if args.strict else "fast",
+                       "l2": "working set per step (%.0f MB) exceeds the 126 MB L2" % (alg / 1e6)},
+            "roofline": {"bound": "hbm", "achieved": alg / (step_us * 1e-6) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": alg / (step_us * 1e-6) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                         "kernel": "tiled_step" if info["kernel"] == 1 else "csr_step", "algorithmic_bytes_per_launch": alg,
+                         "avg_launch_us": step_us},
+            "cpu_baseline": None,
+            "e2e": {"value": spring_steps / wall, "unit": UNIT, "h2d_bytes_per_step": int(ns * 8 + removed_total // max(1, args.steps) * 4),
+                    "d2h_bytes_per_step": 0, "ms_per_step": 1e3 * wall / args.steps,
+                    "call": "tb_set_spring_params(k: all springs) + tb_remove_springs + tb_run_async(%d) + tb_sync" % per},
+            "gpu_launches": int(info["launches"])}
+    print(json.dumps(line), flush=True)
+    eng.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=None, choices=["c2", "c3", "c4"],
+    ap.add_argument("--workload", default=None, choices=["c2", "c3", "c4", "c5"],
                     help="default: c2 on one GPU, c4 (partitioned lattice, halo exchange) on several")
     ap.add_argument("--size", type=int, default=None, help="lattice edge (c2: 100; c4: 150/189/238/300 by GPU count)")
     ap.add_argument("--shape", default=None, help="c4: nx,ny,nz of the whole lattice instead of --size^3")
@@ -227,7 +306,7 @@ def main():
     if args.workload is None:
         args.workload = "c2" if world == 1 else "c4"
     if args.size is None:
-        args.size = 100 if args.workload == "c2" else C4_EDGE.get(world, int(round(150 * world ** (1.0 / 3.0))))
+        args.size = {"c2": 100, "c5": 200}.get(args.workload) or C4_EDGE.get(world, int(round(150 * world ** (1.0 / 3.0))))
     if args.impl == "reference":
         run_reference(args, rank, world)
         return
@@ -253,6 +332,9 @@ def main():
         return float(t.item())
 
     flags = (tb.MATH_STRICT if args.strict else tb.MATH_FAST) | (tb.KERNEL_CSR if args.csr else 0)
+    if args.workload == "c5":
+        run_c5(args, tb, local_rank, flags)
+        return
     eng = tb.Engine(local_rank, flags)
     part, own = None, None
     if args.workload == "c4":

@@ -215,3 +215,35 @@ def test_magnetic_masses_fail_loudly():
         eng.run(1, 0.0)
     assert ei.value.status == 4
     eng.close()
+
+
+@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.KERNEL_CSR, tb.MATH_FAST])
+def test_removed_springs_are_bit_identical_to_absent_springs(flags):
+    """tb_remove_springs (tombstones; BASELINE config C5 / Simulation::deleteSpring after start, src/sim.cu:382-412):
+    the system steps exactly as if the springs had never existed, also after a later full k upload."""
+    sc = scenes.SCENARIOS["contact_friction"]()
+    gone = np.arange(3, sc.ns, 17).astype(np.int32)
+    keep = np.setdiff1d(np.arange(sc.ns), gone)
+    # oracle: 40 steps with all springs, then the springs physically absent, stiffer survivors
+    o = sc.copy()
+    o.step(40)
+    import oracle
+    o2 = oracle.Scene(o.pos.copy(), sc.left[keep], sc.right[keep], sc.rest[keep], k=1.0, m=0.1, dt=sc.dt, g=sc.g)
+    o2.vel[:] = o.vel
+    o2.k[:] = sc.k[keep] * 1.25
+    o2.damping[:] = sc.damping[keep]
+    o2.planes.extend(sc.planes)
+    o2.T_sim = o.T_sim
+    o2.step(60)
+    eng = tb.Engine(0, flags)
+    scenes.upload(eng, sc)
+    eng.run(40, 0.0)
+    eng.remove_springs(gone)
+    eng.set_spring_params(k=sc.k * 1.25)          # touches the tombstones too: they must stay dead
+    eng.run(60, o.T_sim)
+    st = eng.get_mass_state()
+    assert eng.info()["ns_removed"] == gone.size
+    eng.close()
+    tol = 0.0 if flags & tb.MATH_STRICT else 1e-9
+    for f in ("pos", "vel"):
+        assert rel(st[f], getattr(o2, f)) <= tol, (f, rel(st[f], getattr(o2, f)))

@@ -89,7 +89,17 @@ void Simulation::deleteSpring(Spring *s) {   // src/sim.cu:382-412
         if (!end->valid && end->ref_count == 1) zombies.erase(std::remove(zombies.begin(), zombies.end(), end), zombies.end());
         end->decrementRefCount();
     }
-    if (STARTED) { delete s; topology_dirty = true; }   // before start() the reference leaves the object to the caller
+    if (STARTED) {
+        // once started the spring becomes a tombstone on the device (no force from now on, indices of the others
+        // unchanged): no topology rebuild; compaction happens at the next create*() re-upload
+        if (s->slot >= 0 && !topology_dirty) {
+            int32_t slot = s->slot;
+            engine_check(tb_remove_springs(engine, 1, &slot), "tb_remove_springs");
+        } else {
+            topology_dirty = true;
+        }
+        delete s;   // before start() the reference leaves the object to the caller
+    }
 }
 
 void Simulation::deleteContainer(Container *c) {   // src/sim.cu:478-564
