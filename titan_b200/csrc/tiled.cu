@@ -689,7 +689,6 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     constexpr bool STAGE_VEL = DAMPING || P::strict;
     constexpr int NT = TM * TPM;                       // consumer threads
     constexpr int NCW = NT / 32;                       // consumer warps
-    constexpr int EPT = ell_words_per_thread(TPM);     // ELL words per thread
     const SmemPlan &sp = A.sp;
     const int tid = threadIdx.x;
     const uint32_t smem_base = smem_u32(smem);
@@ -705,13 +704,41 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    if (ACTIVE && tid < A.n_omega)   // sin(omega t) once per CTA and step for every distinct omega (src/sim.cu:1168-1173)
-        reinterpret_cast<double *>(smem + sp.off_sintab)[tid] = sin(P::mul(A.omega_tab[tid], *A.t_in));
     if (tid < 2) {   // the dummy mass of both stages: far away, at rest
         double *pp = reinterpret_cast<double *>(smem + sp.off_stage + tid * sp.stage_bytes + sp.st_pos);
         pp[CS - 1] = 1e30; pp[2 * CS - 1] = 1e30; pp[3 * CS - 1] = 1e30;
         if (STAGE_VEL) { double *vp = pp + 3 * CS; vp[CS - 1] = 0.0; vp[2 * CS - 1] = 0.0; vp[3 * CS - 1] = 0.0; }
     }
+    // Programmatic dependent launch: the next step's grid may become resident as this grid's CTAs retire.  Everything
+    // up to griddepcontrol.wait touches only per-topology tables (meta, ELL words, halo lists), never the state or
+    // the clocks the previous step is still writing.
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    // this thread's ELL words: chunks [cb, cb + nch) of the tile's block, rows of TM words
+    const int t = tid % TM, q = tid / TM;
+    constexpr int EPT = ell_words_per_thread(TPM);     // ELL words per thread
+    auto load_ell = [&](uint32_t ell_off, int cb, int nch, uint32_t (&dst)[EPT]) {
+        const uint32_t *src = A.ell + ell_off + (size_t)cb * ELL_CHUNK * TM + t;
+#pragma unroll
+        for (int g = 0; g < EPT / ELL_CHUNK; g++)
+            if (g < nch) {
+#pragma unroll
+                for (int u = 0; u < ELL_CHUNK; u++) dst[g * ELL_CHUNK + u] = __ldg(src + (g * ELL_CHUNK + u) * TM);
+            }
+    };
+    uint32_t ell_cur[EPT], ell_nxt[EPT];
+#pragma unroll
+    for (int jj = 0; jj < EPT; jj++) { ell_cur[jj] = 0u; ell_nxt[jj] = 0u; }
+    int nch = 0, nch_nxt = 0;
+    if (tid < NT) {   // consumers: first tile's words are in flight while the previous step drains
+        const TileMeta *m0 = A.meta + tile_of(0);
+        uint32_t cbp, nchp;
+        chunk_table((int)__ldg(&m0->deg), TPM, cbp, nchp);
+        nch = (int)((nchp >> (8 * q)) & 0xff);
+        load_ell(__ldg(&m0->ell_off), (int)((cbp >> (8 * q)) & 0xff), nch, ell_cur);
+    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");   // the previous step is complete and visible from here on
+    if (ACTIVE && tid < A.n_omega)   // sin(omega t) once per CTA and step for every distinct omega (src/sim.cu:1168-1173)
+        reinterpret_cast<double *>(smem + sp.off_sintab)[tid] = sin(P::mul(A.omega_tab[tid], *A.t_in));
     __syncthreads();
 
     if (tid >= NT) {
@@ -806,35 +833,12 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     }
 
     // ============================================= CONSUMER warps ============================================
-    const int t = tid % TM, q = tid / TM;
     const double t_sim = *A.t_in;
     const double *sintab = reinterpret_cast<const double *>(smem + sp.off_sintab);
     const unsigned long long seq = HALO ? (unsigned long long)*A.step_in : 0ull;
     unsigned pending = 0;   // boundary tiles this warp has finished but not yet reported (HALO)
     // Boundary tiles come first in the tile order, so they are a prefix of every CTA's sequence: the warp reports
     // them with ONE system-scope fence when it reaches its first interior tile (or runs out of tiles).
-    // this thread's ELL words: chunks [cb, cb + nch) of the tile's block, rows of TM words
-    auto load_ell = [&](uint32_t ell_off, int cb, int nch, uint32_t (&dst)[EPT]) {
-        const uint32_t *src = A.ell + ell_off + (size_t)cb * ELL_CHUNK * TM + t;
-#pragma unroll
-        for (int g = 0; g < EPT / ELL_CHUNK; g++)
-            if (g < nch) {
-#pragma unroll
-                for (int u = 0; u < ELL_CHUNK; u++) dst[g * ELL_CHUNK + u] = __ldg(src + (g * ELL_CHUNK + u) * TM);
-            }
-    };
-    uint32_t ell_cur[EPT], ell_nxt[EPT];
-#pragma unroll
-    for (int jj = 0; jj < EPT; jj++) { ell_cur[jj] = 0u; ell_nxt[jj] = 0u; }
-    int nch = 0, nch_nxt = 0;
-    {
-        const TileMeta *m0 = A.meta + tile_of(0);
-        uint32_t cbp, nchp;
-        chunk_table((int)__ldg(&m0->deg), TPM, cbp, nchp);
-        nch = (int)((nchp >> (8 * q)) & 0xff);
-        load_ell(__ldg(&m0->ell_off), (int)((cbp >> (8 * q)) & 0xff), nch, ell_cur);
-    }
-
     long long pa0 = 0, pa1 = 0, pa2 = 0, pa3 = 0, pa4 = 0;
     for (int i = 0; i < n_my; i++) {
         const int s = i & 1;
@@ -1016,7 +1020,15 @@ static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtr
     int64_t grid = std::min<int64_t>(S->n_active, (int64_t)e->sm_count * blocks_per_sm);
     if (const char *g = getenv("TB_GRID")) { int v = atoi(g); if (v > 0) grid = std::min<int64_t>(S->n_active, v); }
     S->grid = (int)grid;
-    kern<<<(unsigned)grid, TM * TPM + 32, S->smem_bytes, e->stream>>>(A, e->G, X);
+    // programmatic dependent launch measured on B200 (C2): no gain (135.6 vs 137.0 G spring-steps/s) -> opt-in only
+    static const bool use_pdl = getenv("TB_PDL") != nullptr;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)grid); cfg.blockDim = dim3(TM * TPM + 32); cfg.dynamicSmemBytes = S->smem_bytes; cfg.stream = e->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = use_pdl ? 1 : 0;
+    TB_CUDA(e, cudaLaunchKernelEx(&cfg, kern, A, e->G, X));
     return TB_OK;
 }
 template <class P, bool D, bool AC, int TPM>
