@@ -453,7 +453,7 @@ def main():
                 "config": {"workload": name, "masses": nm_total, "springs": ns_total, "sim_steps_per_bench_step": inner,
                            "math": "strict" if args.strict else "fast",
                            "tiling": {k: info[k] for k in ("n_tiles", "threads_per_mass", "grid", "smem_bytes",
-                                                           "ell_unique_tiles", "tiled_bytes_per_step")}, "per_rank": per_rank,
+                                                           "ell_unique_tiles", "tiled_bytes_per_step", "dict_records")}, "per_rank": per_rank,
                            "l2": "working set per step and GPU (%.0f MB) exceeds the 126 MB L2" % (alg_bytes / 1e6),
                            "timing": "CUDA events on the engine stream, max over ranks", "wall_ms": wall * 1e3},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world,

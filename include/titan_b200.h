@@ -189,6 +189,9 @@ typedef struct {
     int32_t ell_unique_tiles;    /* tiled kernel: distinct incidence (ELL) blocks after content dedupe */
     int64_t tiled_bytes_per_step;/* tiled kernel: bytes one step streams from its tables (blob+state+halo+ELL+meta) */
     int64_t ns_removed;          /* springs turned into tombstones by tb_remove_springs */
+    int32_t dict_records;        /* tiled kernel, dictionary mode: most distinct (k, rest, ...) records in a tile; 0 = one
+                                    record per spring (parameters too diverse, strict arithmetic or TB_DICT=0) */
+    int32_t reserved0;
 } tb_info;
 TB_API int tb_get_info(tb_engine *e, tb_info *info);
 /* headless position export, fp64 -> packed fp32 xyz (updateVertices, src/sim.cu:1944-1952); out is a

@@ -29,6 +29,7 @@
 #include <cstring>
 #include <map>
 #include <numeric>
+#include <unordered_map>
 
 #include <unistd.h>
 
@@ -90,7 +91,7 @@ struct __align__(16) TileMeta {
     uint32_t exp_off;     // first entry of the export table (halo exchange): exp_rows rows of TM entries
     uint32_t exp_rows;    // 0 = no mass of this tile is a ghost on a peer
     uint32_t tflags;      // TF_*
-    uint32_t pad;
+    uint32_t map_off16;   // dictionary mode: the tile's slot -> record byte map in rec_map, in units of 16 bytes
 };
 static_assert(sizeof(TileMeta) == 48, "TileMeta is copied as three 16-byte words");
 enum : uint32_t { TF_BOUNDARY = 1 };   // the tile's springs reach ghost masses: wait for the peers before reading, signal after
@@ -107,6 +108,14 @@ struct TiledState {
     double *st[2] = {nullptr, nullptr};   // tile-blocked state, ping-pong
     uint8_t *blob = nullptr;
     int32_t *slot_to_api = nullptr, *halo = nullptr, *rec_spring = nullptr;
+    // Dictionary mode (see build_structure): springs with bit-identical parameters share one record per tile.
+    bool dict = false;                    // the blobs hold distinct records + a byte map (record slot -> record)
+    int dict_failures = 0;                // parameter uploads that broke the classes; after 2 the mode stays off
+    int64_t n_class_rep = 0;
+    int32_t *class_rep = nullptr;         // [ns] a spring with the same parameters (the class representative)
+    uint8_t *rec_map = nullptr; int64_t n_rec_map = 0;
+    int *dict_bad = nullptr;              // set by dict_check_kernel
+    int max_dict = 0;
     uint32_t *ell = nullptr;
     TileMeta *meta = nullptr;
     // host
@@ -266,8 +275,10 @@ template <class T> static int upload_vec(Engine *e, T **dst, const std::vector<T
 }
 template <class T> static void release(Engine *e, T *&p, size_t count) { dev_free(e, (void *)p, count * sizeof(T)); p = nullptr; }
 
-static void free_structure(Engine *e, TiledState *S) {
-    for (int p = 0; p < 2; p++) release(e, S->st[p], (size_t)S->n_tiles * STATE_BLOCK);
+static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
+    if (!keep_state) for (int p = 0; p < 2; p++) release(e, S->st[p], (size_t)S->n_tiles * STATE_BLOCK);
+    release(e, S->class_rep, (size_t)S->n_class_rep); S->n_class_rep = 0; release(e, S->rec_map, (size_t)S->n_rec_map);
+    S->n_rec_map = 0; S->dict = false;
     release(e, S->blob, S->blob_bytes);
     release(e, S->slot_to_api, (size_t)S->n_slots); release(e, S->halo, (size_t)S->n_halo);
     release(e, S->rec_spring, (size_t)S->n_rec); release(e, S->ell, (size_t)S->n_ell);
@@ -276,9 +287,9 @@ static void free_structure(Engine *e, TiledState *S) {
     S->blob_bytes = 0;
 }
 
-static size_t blob_size(int n_rec, bool damping, bool active) {
+static size_t blob_size(int n_rec, bool damping, bool active, int n_map = 0) {
     size_t np = (size_t)((n_rec + 1) & ~1);
-    return up16((size_t)BLOB_REC + (size_t)n_rec * 16) + (damping ? np * 8 : 0) + (active ? np * 8 : 0);
+    return up16((size_t)BLOB_REC + (size_t)n_rec * 16) + (damping ? np * 8 : 0) + (active ? np * 8 : 0) + up16((size_t)n_map);
 }
 
 // Threads per mass.  Strict arithmetic needs the oracle's summation order (1).  Otherwise: big problems keep
@@ -291,19 +302,71 @@ static int choose_tpm(const Engine *e, int64_t n_tiles) {
     return tpm;
 }
 
+// Parameter classes for the dictionary mode: springs whose (k, rest, damping, omega) are bit-identical.  A lattice
+// built by createLattice has a few hundred classes for millions of springs (one k, rest lengths that differ only by
+// the rounding of the coordinates), so a tile's ~2,000 records collapse to a few dozen: the blob shrinks from ~35 KB
+// to ~4 KB (less HBM traffic, less shared memory per CTA => more resident CTAs).  class_of[s] = dense class id,
+// rep_of[s] = the first spring of the class.  Returns false (mode off) when there are too many classes.
+#ifndef TB_DICT_CTAS
+#define TB_DICT_CTAS 3
+#endif
+constexpr int DICT_CTAS = TB_DICT_CTAS;   // resident CTAs per SM the dictionary-mode kernels are compiled for (register cap)
+constexpr int DICT_MAX_TILE = 256;        // records a tile's byte map can address
+constexpr int DICT_MAX_GLOBAL = 1 << 16;
+static int param_classes(Engine *e, bool damping, bool active, std::vector<int32_t> &class_of, std::vector<int32_t> &rep_of,
+                         bool *ok) {
+    *ok = false;
+    const size_t ns = (size_t)e->ns;
+    std::vector<double> hk(ns), hr(ns), hd, ho;
+    TB_CUDA(e, cudaMemcpy(hk.data(), e->k, ns * 8, cudaMemcpyDeviceToHost));
+    TB_CUDA(e, cudaMemcpy(hr.data(), e->rest, ns * 8, cudaMemcpyDeviceToHost));
+    if (damping && e->damping) { hd.resize(ns); TB_CUDA(e, cudaMemcpy(hd.data(), e->damping, ns * 8, cudaMemcpyDeviceToHost)); }
+    if (active && e->omega) { ho.resize(ns); TB_CUDA(e, cudaMemcpy(ho.data(), e->omega, ns * 8, cudaMemcpyDeviceToHost)); }
+    struct Key { uint64_t a, b, c, d; bool operator==(const Key &o) const { return a == o.a && b == o.b && c == o.c && d == o.d; } };
+    struct KeyHash { size_t operator()(const Key &x) const {
+        uint64_t h = x.a * 0x9E3779B97F4A7C15ull; h ^= (x.b + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full; h ^= h >> 29;
+        h ^= x.c * 0x165667B19E3779F9ull; h ^= x.d * 0x27D4EB2F165667C5ull; return (size_t)(h ^ (h >> 32)); } };
+    std::unordered_map<Key, int32_t, KeyHash> seen;
+    std::vector<int32_t> first;    // class id -> first spring
+    class_of.resize(ns); rep_of.resize(ns);
+    Key last = {0, 0, 0, 0}; int32_t last_class = -1;
+    auto bits = [](double x) { uint64_t u; memcpy(&u, &x, 8); return u; };
+    for (size_t sp = 0; sp < ns; sp++) {
+        Key key = {bits(hk[sp]), bits(hr[sp]), hd.empty() ? 0 : bits(hd[sp]), ho.empty() ? 0 : bits(ho[sp])};
+        int32_t c;
+        if (last_class >= 0 && key == last) c = last_class;
+        else {
+            auto it = seen.find(key);
+            if (it == seen.end()) {
+                if ((int)first.size() >= DICT_MAX_GLOBAL) return TB_OK;
+                c = (int32_t)first.size(); first.push_back((int32_t)sp); seen.emplace(key, c);
+            } else c = it->second;
+            last = key; last_class = c;
+        }
+        class_of[sp] = c; rep_of[sp] = first[(size_t)c];
+    }
+    *ok = true;
+    return TB_OK;
+}
+
 // Builds tiles, ELL rows, halo lists and record tables on the host and uploads them.  Returns TB_OK with
 // S->supported == false (and a reason) when the graph does not fit the tiled format.
-static int build_structure(Engine *e, TiledState *S) {
-    free_structure(e, S);
+// keep_slots: the mass -> slot assignment, the state buffers and the halo-exchange fields of the tile table stay
+// (a rebuild after a parameter upload that broke the dictionary classes; peers keep their pointers and offsets).
+static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, bool allow_dict = true) {
+    std::vector<TileMeta> old_meta;
+    if (keep_slots) old_meta = S->h_meta;
+    free_structure(e, S, keep_slots);
     S->supported = false;
     const int64_t nm = e->nm;
-    std::vector<double> pos;
-    if (e->tile_hint.empty()) {     // current positions (SoA) drive the bisection
-        pos.resize((size_t)nm * 3);
-        TB_CUDA(e, cudaMemcpy(pos.data(), e->pos[e->cur], (size_t)nm * 24, cudaMemcpyDeviceToHost));
+    if (!keep_slots) {
+        std::vector<double> pos;
+        if (e->tile_hint.empty()) {     // current positions (SoA) drive the bisection
+            pos.resize((size_t)nm * 3);
+            TB_CUDA(e, cudaMemcpy(pos.data(), e->pos[e->cur], (size_t)nm * 24, cudaMemcpyDeviceToHost));
+        }
+        assign_tiles(e, pos, S->h_slot_to_api, &S->n_boundary, &S->n_active);
     }
-    assign_tiles(e, pos, S->h_slot_to_api, &S->n_boundary, &S->n_active);
-    std::vector<double>().swap(pos);
     const int64_t n_slots = (int64_t)S->h_slot_to_api.size(), n_tiles = n_slots / TM;
     if (n_tiles * (int64_t)STATE_BLOCK >= ((int64_t)1 << 31)) { S->why_not = "state exceeds int32 halo indices"; return TB_OK; }
     S->h_api_to_slot.assign((size_t)nm, -1);
@@ -312,6 +375,22 @@ static int build_structure(Engine *e, TiledState *S) {
     S->has_damping = e->any_damping; S->has_active = e->any_active;
     S->stage_vel = S->has_damping || (e->flags & TB_MATH_STRICT);
     S->tpm = choose_tpm(e, n_tiles);
+
+    // dictionary mode: fast arithmetic, one thread per mass (the big-problem configuration)
+    static const bool dict_env = !(getenv("TB_DICT") && atoi(getenv("TB_DICT")) == 0);
+    bool dict = allow_dict && dict_env && S->dict_failures < 2 && !(e->flags & TB_MATH_STRICT) && S->tpm == 1 && e->ns > 0;
+    std::vector<int32_t> class_of, rep_of, dict_spring;
+    std::vector<uint8_t> rec_map;
+    std::vector<int32_t> cls_stamp, cls_local;
+    if (dict) {
+        TB_TRY(param_classes(e, S->has_damping, S->has_active, class_of, rep_of, &dict));
+        if (dict) {
+            int32_t n_classes = 0;
+            for (int32_t c : class_of) n_classes = std::max(n_classes, c + 1);
+            cls_stamp.assign((size_t)n_classes, -1); cls_local.assign((size_t)n_classes, 0);
+        }
+    }
+    int max_dict = 0;
 
     std::vector<TileMeta> meta((size_t)n_tiles);
     std::vector<uint32_t> ell, block;
@@ -349,6 +428,7 @@ static int build_structure(Engine *e, TiledState *S) {
         M.rec_off = (uint32_t)rec_spring.size();
         block.assign((size_t)ell_chunks(deg) * ELL_CHUNK * TM, 0u);   // zero rows pad the last chunk
         int n_rec = 1;
+        const size_t rec_first = rec_spring.size();
         rec_spring.push_back(-1);                                 // record 0: k = 0, read by padding ELL words
         // Halo slots are chosen so that the 16 lanes of a half-warp reading row j hit 16 different shared-memory
         // bank pairs (an LDS.64 conflict costs a replay).  Own neighbours sit at local index t + c_j (c_j = the
@@ -430,9 +510,32 @@ static int build_structure(Engine *e, TiledState *S) {
             unique_blocks++;
         }
         M.n_halo = (uint32_t)n_halo; M.n_rec = (uint32_t)n_rec;
-        M.exp_off = 0; M.exp_rows = 0; M.pad = 0;
+        M.exp_off = 0; M.exp_rows = 0; M.map_off16 = 0;
         M.tflags = (T < S->n_boundary) ? (uint32_t)TF_BOUNDARY : 0u;
+        if (keep_slots) { M.exp_off = old_meta[(size_t)T].exp_off; M.exp_rows = old_meta[(size_t)T].exp_rows; M.tflags = old_meta[(size_t)T].tflags; }
         size_t bb = blob_size(n_rec, S->has_damping, S->has_active);
+        if (dict) {
+            // record slots -> the tile's distinct records; slot 0 (padding) -> record 0 (k = 0)
+            while (rec_map.size() % 16) rec_map.push_back(0);
+            M.map_off16 = (uint32_t)(rec_map.size() / 16);
+            M.rec_off = (uint32_t)dict_spring.size();
+            int n_dict = 1;
+            dict_spring.push_back(-1);
+            rec_map.push_back(0);
+            for (int r = 1; r < n_rec && dict; r++) {
+                const int32_t sp = rec_spring[rec_first + (size_t)r], c = class_of[(size_t)sp];
+                if (cls_stamp[(size_t)c] != (int32_t)T) {
+                    if (n_dict >= DICT_MAX_TILE) { dict = false; break; }
+                    cls_stamp[(size_t)c] = (int32_t)T; cls_local[(size_t)c] = n_dict++; dict_spring.push_back(rep_of[(size_t)sp]);
+                }
+                rec_map.push_back((uint8_t)cls_local[(size_t)c]);
+            }
+            if (!dict) return build_structure(e, S, keep_slots, false);   // a tile with too many classes: plain records
+            rec_spring.resize(rec_first);                                  // slot -> spring is not needed in this mode
+            M.n_rec = (uint32_t)n_dict;
+            bb = blob_size(n_dict, S->has_damping, S->has_active, n_rec);
+            max_dict = std::max(max_dict, n_dict);
+        }
         if (blob_total / 16 >= ((size_t)1 << 32)) { S->why_not = "blob exceeds 64 GB"; return TB_OK; }
         M.blob_off16 = (uint32_t)(blob_total / 16); M.blob_bytes = (uint32_t)bb;
         blob_total += bb;
@@ -443,6 +546,7 @@ static int build_structure(Engine *e, TiledState *S) {
     halo.resize(halo.size() + 4, 0);   // the last list may be copied rounded up to 16 bytes
     if (TM + max_halo + 1 > CS_BIG) { S->why_not = "a tile reaches too many foreign masses"; return TB_OK; }
     S->cs = choose_cs(max_halo, (e->flags & TB_MATH_STRICT) != 0);
+    ell.resize(ell.size() + (size_t)(MAX_DEG + 2 * ELL_CHUNK) * TM, 0u);   // the kernel prefetches whole register sets
     {   // padding words -> (dummy mass, record 0)
         const uint32_t pad = (uint32_t)(S->cs - 1) << ELL_NB_SHIFT;
         for (uint32_t &w : ell) if (!(w & ELL_VALID)) w = pad;
@@ -454,9 +558,18 @@ static int build_structure(Engine *e, TiledState *S) {
     S->n_tiles = n_tiles; S->n_slots = n_slots; S->n_rec = (int64_t)rec_spring.size(); S->n_ell = (int64_t)ell.size();
     S->n_halo = (int64_t)halo.size(); S->max_halo = max_halo; S->max_rec = max_rec; S->max_deg = max_deg;
     S->max_blob = (int)max_blob; S->blob_bytes = blob_total; S->ell_unique_tiles = unique_blocks;
-    for (int p = 0; p < 2; p++) {
+    if (!keep_slots) for (int p = 0; p < 2; p++) {
         TB_TRY(dev_alloc(e, &S->st[p], (size_t)n_tiles * STATE_BLOCK));
         TB_CUDA(e, cudaMemset(S->st[p], 0, (size_t)n_tiles * STATE_BLOCK * 8));
+    }
+    S->dict = dict; S->max_dict = max_dict;
+    if (dict) {
+        while (rec_map.size() % 16) rec_map.push_back(0);
+        rec_spring.swap(dict_spring);
+        S->n_rec_map = (int64_t)rec_map.size(); S->n_class_rep = (int64_t)rep_of.size();
+        TB_TRY(upload_vec(e, &S->rec_map, rec_map)); TB_TRY(upload_vec(e, &S->class_rep, rep_of));
+        if (!S->dict_bad) TB_CUDA(e, cudaMalloc((void **)&S->dict_bad, sizeof(int)));
+        S->n_rec = (int64_t)rec_spring.size();
     }
     TB_TRY(dev_alloc(e, &S->blob, blob_total));
     TB_CUDA(e, cudaMemset(S->blob, 0, blob_total));
@@ -504,15 +617,33 @@ __global__ void tiled_refresh_mass(uint8_t *blob, const TileMeta *meta, const in
     b[BLOB_FLAGS + t] = i >= 0 ? flags_c[i] : (uint8_t)0;
     ((double *)(b + BLOB_M))[t] = i >= 0 ? m_c[i] : 1.0;
 }
+// dictionary mode: do all springs still carry the parameters of their class representative (bit for bit)?
+__global__ void dict_check_kernel(int64_t ns, const int32_t *class_rep, const double *k, const double *rest, const double *damping,
+                                  const double *omega, int *bad) {
+    const int64_t sp = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (sp >= ns) return;
+    const int32_t r = class_rep[sp];
+    if (r == sp) return;
+    bool same = __double_as_longlong(k[sp]) == __double_as_longlong(k[r]) && __double_as_longlong(rest[sp]) == __double_as_longlong(rest[r]);
+    if (damping) same = same && __double_as_longlong(damping[sp]) == __double_as_longlong(damping[r]);
+    if (omega) same = same && __double_as_longlong(omega[sp]) == __double_as_longlong(omega[r]);
+    if (!same) *bad = 1;
+}
 // one CTA per tile: the spring records of the tile's blob
 __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const int32_t *rec_spring, const double *k,
                                      const double *rest, const double *damping, const double *omega, int has_damping,
-                                     int has_active, const double *omega_tab, int n_omega) {
+                                     int has_active, const double *omega_tab, int n_omega, const uint8_t *rec_map) {
     const TileMeta M = meta[blockIdx.x];
     uint8_t *b = blob + (size_t)M.blob_off16 * 16;
     double2 *rec = (double2 *)(b + BLOB_REC);
     double *dmp = (double *)(b + ((BLOB_REC + (size_t)M.n_rec * 16 + 15) & ~(size_t)15));
     double *omg = dmp + (has_damping ? ((M.n_rec + 1) & ~1u) : 0);
+    if (rec_map) {   // dictionary mode: the slot -> record byte map follows the records (16-byte units)
+        uint4 *dst = (uint4 *)(omg + (has_active ? ((M.n_rec + 1) & ~1u) : 0));
+        const uint4 *src = (const uint4 *)rec_map + M.map_off16;
+        const uint32_t n16 = (uint32_t)((b + M.blob_bytes - (uint8_t *)dst) / 16);
+        for (uint32_t r = threadIdx.x; r < n16; r += blockDim.x) dst[r] = src[r];
+    }
     for (uint32_t r = threadIdx.x; r < M.n_rec; r += blockDim.x) {
         int32_t s = rec_spring[M.rec_off + r];
         rec[r] = s >= 0 ? make_double2(k[s], rest[s]) : make_double2(0.0, 0.0);
@@ -603,6 +734,7 @@ constexpr long long HALO_TIMEOUT_CLOCKS = 1ll << 32;   // ~2 s: a peer that neve
 struct TiledArgs {
     int32_t n_tiles;
     int32_t write_acc;
+    int prof_lite;                   // TB_PROFILE=2: only the barrier waits and the loop totals
     unsigned long long *prof;        // TB_PROFILE=1: per-phase clock64 sums (0 wait full, 1 springs, 2 partial-sum handoff, 3 mass update, 4 producer wait empty, 5 producer wait halo list, 6 producer issue, 7 ell-copy wait)
     int32_t l2_hint;                 // 1: stream the spring-record blobs through L2 with evict_first
     int32_t debug;                   // TB_DEBUG_SKIP bits (timing experiments only): 1 no halo gather, 2 no springs, 4 no mass update, 8 no peer stores, 16 no peer wait
@@ -637,6 +769,7 @@ struct TileCtrl { uint32_t next_ell_off, next_cb, next_nch, has_next, exp_off, e
 __host__ __device__ inline void chunk_table(int deg, int tpm, uint32_t &cb_packed, uint32_t &nch_packed) {
     const int n = ell_chunks(deg), c0 = ell_chunks0(n, tpm), cq = ell_chunks_q(n, tpm);
     cb_packed = 0; nch_packed = (uint32_t)c0;
+    if (tpm == 1) nch_packed |= (uint32_t)deg << 8;      // one thread per mass: it also learns the exact row count
     for (int q = 1; q < tpm; q++) {
         int cb = c0 + (q - 1) * cq, nch = n - cb < cq ? n - cb : cq;
         if (nch < 0) nch = 0;
@@ -681,8 +814,8 @@ __device__ __noinline__ void halo_report(const TiledArgs &A, unsigned pending, u
 //   empty[s] : one arrival per consumer warp when it has finished reading stage s
 //   hfull[r] : bulk copy of a halo index list (producer-internal)
 // plus one named barrier per 32-mass column and tile parity for handing the partial sums to thread q == 0.
-template <class P, bool DAMPING, bool ACTIVE, int TPM, int CS, bool HALO>
-__global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_kernel(const __grid_constant__ TiledArgs A,
+template <class P, bool DAMPING, bool ACTIVE, int TPM, int CS, bool HALO, bool DICT>
+__global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS : 2) : 1)) tiled_step_kernel(const __grid_constant__ TiledArgs A,
                                                                    const __grid_constant__ Globals G,
                                                                    const __grid_constant__ MassExtras X) {
     extern __shared__ __align__(128) unsigned char smem[];
@@ -725,15 +858,16 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                 for (int u = 0; u < ELL_CHUNK; u++) dst[g * ELL_CHUNK + u] = __ldg(src + (g * ELL_CHUNK + u) * TM);
             }
     };
-    uint32_t ell_cur[EPT], ell_nxt[EPT];
+    uint32_t ell_cur[EPT];
 #pragma unroll
-    for (int jj = 0; jj < EPT; jj++) { ell_cur[jj] = 0u; ell_nxt[jj] = 0u; }
-    int nch = 0, nch_nxt = 0;
+    for (int jj = 0; jj < EPT; jj++) ell_cur[jj] = 0u;
+    int nch = 0, nch_nxt = 0, rows = 0, rows_nxt = 0;   // rows: the tile's ELL rows before padding (TPM == 1 only)
     if (tid < NT) {   // consumers: first tile's words are in flight while the previous step drains
         const TileMeta *m0 = A.meta + tile_of(0);
         uint32_t cbp, nchp;
         chunk_table((int)__ldg(&m0->deg), TPM, cbp, nchp);
         nch = (int)((nchp >> (8 * q)) & 0xff);
+        rows = (int)((nchp >> 8) & 0xff);
         load_ell(__ldg(&m0->ell_off), (int)((cbp >> (8 * q)) & 0xff), nch, ell_cur);
     }
     asm volatile("griddepcontrol.wait;" ::: "memory");   // the previous step is complete and visible from here on
@@ -766,6 +900,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         const uint64_t pol_stream = l2_policy_evict_first();
         if (lane == 0) { issue_hidx(0, m0a); if (n_my > 1) issue_hidx(1, m1a); }
         long long pp0 = 0, pp1 = 0, pp2 = 0;
+        const long long pb = A.prof ? clock64() : 0;
         for (int k = 0; k < n_my; k++) {
             const int s = k & 1;
             __syncwarp();
@@ -808,9 +943,9 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                 if (k + 2 < n_my) issue_hidx(k + 2, m2a);
             }
             // halo gather of tile k: the index list was bulk-copied two tiles ago
-            long long p2 = A.prof ? clock64() : 0;
+            long long p2 = (A.prof && !A.prof_lite) ? clock64() : 0;
             mbar_wait(bar_halo(k % HALO_RING), (uint32_t)((k / HALO_RING) & 1));
-            long long p3 = A.prof ? clock64() : 0;
+            long long p3 = (A.prof && !A.prof_lite) ? clock64() : 0;
             const int n_halo = m0a.w;
             const int32_t *hl = reinterpret_cast<const int32_t *>(smem + sp.off_hring + (k % HALO_RING) * sp.hring_stride);
             for (int h = lane; h < ((A.debug & 1) ? 0 : n_halo); h += 32) {
@@ -825,9 +960,11 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                 }
             }
             cp_async_arrive_noinc(bar_full(s));
-            if (A.prof) { long long p4 = clock64(); pp0 += p1 - p0; pp1 += p3 - p2; pp2 += (p2 - p1) + (p4 - p3); }
+            if (A.prof && A.prof_lite) pp0 += p1 - p0;
+            if (A.prof && !A.prof_lite) { long long p4 = clock64(); pp0 += p1 - p0; pp1 += p3 - p2; pp2 += (p2 - p1) + (p4 - p3); }
             m0a = m1a; m0b = m1b; m0c = m1c; m1a = m2a; m1b = m2b; m1c = m2c; m2a = m3a; m2b = m3b; m2c = m3c;
         }
+        if (A.prof && A.prof_lite) pp2 = clock64() - pb;   // lite: slot 6 = the whole producer loop
         if (A.prof && lane == 0) { atomicAdd(A.prof + 4, (unsigned long long)pp0); atomicAdd(A.prof + 5, (unsigned long long)pp1); atomicAdd(A.prof + 6, (unsigned long long)pp2); }
         return;
     }
@@ -840,6 +977,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
     // Boundary tiles come first in the tile order, so they are a prefix of every CTA's sequence: the warp reports
     // them with ONE system-scope fence when it reaches its first interior tile (or runs out of tiles).
     long long pa0 = 0, pa1 = 0, pa2 = 0, pa3 = 0, pa4 = 0;
+    const long long c_begin = A.prof ? clock64() : 0;
     for (int i = 0; i < n_my; i++) {
         const int s = i & 1;
         long long c0 = A.prof ? clock64() : 0;
@@ -848,15 +986,21 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         const unsigned char *stage = smem + sp.off_stage + s * sp.stage_bytes;
         const uint4 ctrl4 = *reinterpret_cast<const uint4 *>(smem + sp.off_ctrl + s * sizeof(TileCtrl));   // next_ell_off, next_cb, next_nch, has_next
         struct { uint32_t next_ell_off, next_cb, next_nch, has_next; } ctrl = {ctrl4.x, ctrl4.y, ctrl4.z, ctrl4.w};
-        if (ctrl.has_next) {   // next tile's words -> registers
+        // The next tile's ELL words replace this tile's in the same registers, each right after its last use (the
+        // loads are unconditional: the table is padded, words beyond a tile's rows are never evaluated).
+        const uint32_t *nsrc = A.ell + t;
+        if (ctrl.has_next) {
             nch_nxt = (int)((ctrl.next_nch >> (8 * q)) & 0xff);
-            load_ell(ctrl.next_ell_off, (int)((ctrl.next_cb >> (8 * q)) & 0xff), nch_nxt, ell_nxt);
+            rows_nxt = (int)((ctrl.next_nch >> 8) & 0xff);
+            nsrc += ctrl.next_ell_off + (size_t)((ctrl.next_cb >> (8 * q)) & 0xff) * ELL_CHUNK * TM;
         }
         const int n_rec = reinterpret_cast<const int32_t *>(stage)[2];
         const uint8_t fl = stage[BLOB_FLAGS + t];
         const char *prb = reinterpret_cast<const char *>(stage + BLOB_REC);
         const char *dmb = prb + (size_t)n_rec * 16;
         const char *omb = dmb + (DAMPING ? ((n_rec + 1) & ~1) * 8 : 0);
+        // dictionary mode: the ELL word's record slot goes through the tile's byte map to one of n_rec distinct records
+        const uint8_t *mapb = reinterpret_cast<const uint8_t *>(omb + (ACTIVE ? ((n_rec + 1) & ~1) * 8 : 0));
         const char *pbx = reinterpret_cast<const char *>(stage + sp.st_pos), *pby = pbx + CS * 8, *pbz = pby + CS * 8;
         const char *vbx = reinterpret_cast<const char *>(stage + sp.st_vel), *vby = vbx + sp.vs * 8, *vbz = vby + sp.vs * 8;
         V3 pos = {reinterpret_cast<const double *>(pbx)[t], reinterpret_cast<const double *>(pby)[t], reinterpret_cast<const double *>(pbz)[t]};
@@ -890,43 +1034,65 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
                     }
                 }
             }
+#pragma unroll
+            for (int jj = 0; jj < EPT; jj++) ell_cur[jj] = __ldg(nsrc + jj * TM);
         } else {
             // ELL_CHUNK springs at a time without branches (invalid words evaluate a dummy spring whose
             // coefficient is then forced to zero), so their loads and fp64 chains interleave.
             // force on this mass = (p_me - p_other) * coef whichever endpoint it is (see physics.cuh)
+            auto spring = [&](const uint32_t en) {
+                const uint32_t nbo = en & 0xff8u;
+                uint32_t rco = (en >> 12) & 0xfff0u;
+                if (DICT) rco = (uint32_t)mapb[(en >> 16) & 0xfffu] << 4;
+                const char *pn = pbx + nbo;
+                const double dx = pos.x - *(const double *)(pn);
+                const double dy = pos.y - *(const double *)(pn + CS * 8);
+                const double dz = pos.z - *(const double *)(pn + 2 * CS * 8);
+                const double2 kr = *(const double2 *)(prb + rco);
+                double rest = kr.y;
+                if (ACTIVE) {
+                    const int ty = (en >> ELL_TYPE_SHIFT) & 3;
+                    if (A.n_omega > 0) rest = kr.y * actuation_table<P>(ty, sintab, omb + (rco >> 1));   // branch-free
+                    else if (ty) rest = kr.y * actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + (rco >> 1)), t_sim));
+                }
+                const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
+                const double inv = rsqrt_fast(L2);
+                // k (rest - L) / L = k (rest / L - 1); padding words read k = 0 and the far dummy mass
+                double coef = kr.x * fma(rest, inv, -1.0);
+                if (DAMPING) {   // dot(v_left - v_right, dir) * damping along dir; symmetric in the endpoints
+                    const double dvx = *(const double *)(vbx + nbo) - vel.x, dvy = *(const double *)(vby + nbo) - vel.y,
+                                 dvz = *(const double *)(vbz + nbo) - vel.z;
+                    coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * (inv * inv), *(const double *)(dmb + (rco >> 1)), coef);
+                }
+                force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
+            };
+            constexpr int FULL = 7;     // chunks of a tile whose masses have 25..28 incident springs (the lattice interior)
+            if (TPM == 1 && !DAMPING && !ACTIVE && nch == FULL && !(A.debug & 2)) {
+                // the common case as one straight line: no per-chunk branch, so the scheduler can start a chunk's
+                // shared-memory loads while the previous chunk's fp64 chains are still running
+                // A 3-D lattice mass has at most 26 springs: the block's last two rows are then padding, skipped.
+                constexpr int LATTICE_DEG = 26;
 #pragma unroll
-            for (int g = 0; g < EPT / ELL_CHUNK; g++) {
-                if (g < nch && !(A.debug & 2)) {
+                for (int jj = 0; jj < LATTICE_DEG; jj++) { spring(ell_cur[jj]); ell_cur[jj] = __ldg(nsrc + jj * TM); }
+                if (rows > LATTICE_DEG) {
 #pragma unroll
-                    for (int u = 0; u < ELL_CHUNK; u++) {
-                        const uint32_t en = ell_cur[g * ELL_CHUNK + u];
-                        const uint32_t nbo = en & 0xff8u, rco = (en >> 12) & 0xfff0u;
-                        const char *pn = pbx + nbo;
-                        const double dx = pos.x - *(const double *)(pn);
-                        const double dy = pos.y - *(const double *)(pn + CS * 8);
-                        const double dz = pos.z - *(const double *)(pn + 2 * CS * 8);
-                        const double2 kr = *(const double2 *)(prb + rco);
-                        double rest = kr.y;
-                        if (ACTIVE) {
-                            const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                            if (A.n_omega > 0) rest = kr.y * actuation_table<P>(ty, sintab, omb + (rco >> 1));   // branch-free
-                            else if (ty) rest = kr.y * actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + (rco >> 1)), t_sim));
-                        }
-                        const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
-                        const double inv = rsqrt_fast(L2);
-                        // k (rest - L) / L = k (rest / L - 1); padding words read k = 0 and the far dummy mass
-                        double coef = kr.x * fma(rest, inv, -1.0);
-                        if (DAMPING) {   // dot(v_left - v_right, dir) * damping along dir; symmetric in the endpoints
-                            const double dvx = *(const double *)(vbx + nbo) - vel.x, dvy = *(const double *)(vby + nbo) - vel.y,
-                                         dvz = *(const double *)(vbz + nbo) - vel.z;
-                            coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * (inv * inv), *(const double *)(dmb + (rco >> 1)), coef);
-                        }
-                        force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
+                    for (int jj = LATTICE_DEG; jj < FULL * ELL_CHUNK; jj++) spring(ell_cur[jj]);
+                }
+#pragma unroll
+                for (int jj = LATTICE_DEG; jj < EPT; jj++) ell_cur[jj] = __ldg(nsrc + jj * TM);
+            } else {
+#pragma unroll
+                for (int g = 0; g < EPT / ELL_CHUNK; g++) {
+                    if (g < nch && !(A.debug & 2)) {
+#pragma unroll
+                        for (int u = 0; u < ELL_CHUNK; u++) spring(ell_cur[g * ELL_CHUNK + u]);
                     }
+#pragma unroll
+                    for (int u = 0; u < ELL_CHUNK; u++) ell_cur[g * ELL_CHUNK + u] = __ldg(nsrc + (g * ELL_CHUNK + u) * TM);
                 }
             }
         }
-        long long c2 = A.prof ? clock64() : 0;
+        long long c2 = (A.prof && !A.prof_lite) ? clock64() : 0;
         if (TPM > 1) {   // hand the partial sums to thread q == 0 of the mass, which adds them in a fixed order
             double *part = reinterpret_cast<double *>(smem + sp.off_part + s * sp.part_bytes);
             const int bar_id = 1 + (t >> 5) + (TM / 32) * s;
@@ -944,7 +1110,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
             }
         }
 
-        long long c3 = A.prof ? clock64() : 0;
+        long long c3 = (A.prof && !A.prof_lite) ? clock64() : 0;
         // ---- mass update (one thread per mass) ---------------------------------------------------------------
         if (q == 0) {
             const int64_t tile = tile_of(i);
@@ -979,16 +1145,15 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         bool boundary_tile = false;
         if (HALO) boundary_tile = (reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl)[s].tflags & TF_BOUNDARY) != 0;
         __syncwarp();
-        long long c4 = A.prof ? clock64() : 0;
+        long long c4 = (A.prof && !A.prof_lite) ? clock64() : 0;
         if ((tid & 31) == 0) mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
         if (HALO && A.n_peers > 0) {
             if (boundary_tile) pending++;
             else if (pending) { halo_report(A, pending, seq); pending = 0; }
         }
-#pragma unroll
-        for (int jj = 0; jj < EPT; jj++) ell_cur[jj] = ell_nxt[jj];
-        nch = nch_nxt;
-        if (A.prof) {
+        nch = nch_nxt; rows = rows_nxt;
+        if (A.prof && A.prof_lite) pa0 += c1 - c0;
+        if (A.prof && !A.prof_lite) {
             unsigned sink = 0;
 #pragma unroll
             for (int jj = 0; jj < EPT; jj++) sink ^= ell_cur[jj];
@@ -998,6 +1163,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
         }
     }
     if (HALO && pending) halo_report(A, pending, seq);
+    if (A.prof && A.prof_lite) pa1 = clock64() - c_begin;   // lite: slot 1 = the whole tile loop
     if (A.prof && (tid & 31) == 0) {
         unsigned long long *pp = A.prof + 8 * (q > 0);
         atomicAdd(pp + 0, (unsigned long long)pa0); atomicAdd(pp + 1, (unsigned long long)pa1); atomicAdd(pp + 2, (unsigned long long)pa2);
@@ -1006,11 +1172,11 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? 2 : 1)) tiled_step_
 }
 
 // ---------------------------------------------------------------- glue ------------------------------------
-template <class P, bool D, bool AC, int TPM, int CS, bool HALO>
+template <class P, bool D, bool AC, int TPM, int CS, bool HALO, bool DICT>
 static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     static size_t configured_smem = 0;     // per template instantiation
     static int blocks_per_sm = 0;
-    auto kern = tiled_step_kernel<P, D, AC, TPM, CS, HALO>;
+    auto kern = tiled_step_kernel<P, D, AC, TPM, CS, HALO, DICT>;
     if (configured_smem != S->smem_bytes) {
         TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S->smem_bytes));
         TB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, TM * TPM + 32, S->smem_bytes));
@@ -1034,12 +1200,23 @@ static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtr
 template <class P, bool D, bool AC, int TPM>
 static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     static const bool force_halo = getenv("TB_FORCE_HALO") != nullptr;   // measurement aid: exchange code compiled in, inert
+    constexpr bool CAN_DICT = !P::strict && TPM == 1;    // build_structure only chooses the dictionary mode then
+    if (S->dict && !CAN_DICT) return fail(e, TB_ERR_INVALID, "internal: dictionary records with a kernel that cannot read them");
     if (A.n_peers > 0 || e->any_ghost || force_halo) {   // partitioned: one thread per mass (choose_tpm), exchange code compiled in
-        if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, 1, CS_BIG, true>(e, S, A, X);
-        return launch_c<P, D, AC, 1, (P::strict ? CS_BIG : CS_SMALL), true>(e, S, A, X);
+        if (TPM != 1) return fail(e, TB_ERR_INVALID, "internal: halo exchange needs one thread per mass");
+        if (S->dict) {
+            if (A.sp.cs == CS_BIG) return launch_c<P, D, AC, 1, CS_BIG, true, CAN_DICT>(e, S, A, X);
+            return launch_c<P, D, AC, 1, (P::strict ? CS_BIG : CS_SMALL), true, CAN_DICT>(e, S, A, X);
+        }
+        if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, 1, CS_BIG, true, false>(e, S, A, X);
+        return launch_c<P, D, AC, 1, (P::strict ? CS_BIG : CS_SMALL), true, false>(e, S, A, X);
     }
-    if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG, false>(e, S, A, X);
-    return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL), false>(e, S, A, X);
+    if (S->dict) {
+        if (A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG, false, CAN_DICT>(e, S, A, X);
+        return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL), false, CAN_DICT>(e, S, A, X);
+    }
+    if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG, false, false>(e, S, A, X);
+    return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL), false, false>(e, S, A, X);
 }
 template <class P, int TPM> static int launch_f(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     bool d = S->has_damping, a = S->has_active;
@@ -1078,6 +1255,23 @@ int tiled_prepare(Engine *e) {
         stale |= TS_PARAMS | TS_STATE | TS_FLAGS;
     }
     if (!S->supported) return TB_OK;
+    if ((stale & TS_PARAMS) && !(stale & TS_STRUCT) && S->dict) {
+        // the records are shared by parameter class: a parameter upload that splits a class needs new records
+        TB_CUDA(e, cudaMemsetAsync(S->dict_bad, 0, sizeof(int), e->stream));
+        dict_check_kernel<<<(unsigned)((e->ns + 255) / 256), 256, 0, e->stream>>>(e->ns, S->class_rep, e->k, e->rest,
+                                                                                  S->has_damping ? e->damping : nullptr,
+                                                                                  S->has_active ? e->omega : nullptr, S->dict_bad);
+        int bad = 0;
+        TB_CUDA(e, cudaMemcpyAsync(&bad, S->dict_bad, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
+        TB_CUDA(e, cudaStreamSynchronize(e->stream));
+        if (bad) {
+            S->dict_failures++;
+            TB_TRY(build_structure(e, S, /*keep_slots=*/true));
+            e->graph_dirty = true;
+            if (!S->supported) return TB_OK;
+            stale |= TS_PARAMS | TS_FLAGS;
+        }
+    }
     unsigned gs = (unsigned)((S->n_slots + 255) / 256);
     if (stale & TS_STATE) {
         if (e->canon_stale && !(stale & TS_STRUCT)) TB_TRY(tiled_to_canonical(e));  // partial upload landed in canonical
@@ -1104,7 +1298,8 @@ int tiled_prepare(Engine *e) {
     }
     if (stale & TS_PARAMS)
         tiled_refresh_params<<<(unsigned)S->n_tiles, 128, 0, e->stream>>>(S->blob, S->meta, S->rec_spring, e->k, e->rest, e->damping,
-                                                                          e->omega, S->has_damping ? 1 : 0, S->has_active ? 1 : 0, S->omega_tab, S->n_omega);
+                                                                          e->omega, S->has_damping ? 1 : 0, S->has_active ? 1 : 0, S->omega_tab, S->n_omega,
+                                                                          S->dict ? S->rec_map : nullptr);
     TB_CUDA(e, cudaGetLastError());
     e->tiled_stale = 0;
     return TB_OK;
@@ -1116,9 +1311,10 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     TiledArgs A;
     A.n_tiles = (int32_t)S->n_active;
     A.write_acc = write_acc ? 1 : 0;
-    A.prof = nullptr;
+    A.prof = nullptr; A.prof_lite = 0;
     if (getenv("TB_PROFILE")) {
         A.prof = g_prof_dev; g_prof_launches++;
+        A.prof_lite = atoi(getenv("TB_PROFILE")) == 2;
     }
     A.debug = 0;
     A.l2_hint = 1;
@@ -1174,6 +1370,10 @@ void tiled_destroy(Engine *e) {
         cudaMemcpy(h, g_prof_dev, sizeof h, cudaMemcpyDeviceToHost);
         const TiledState *S = e->tiled;
         double cw0 = (double)g_prof_launches * (double)S->n_tiles * (TM / 32), cwq = cw0 * (S->tpm - 1), pw = (double)g_prof_launches * (double)S->n_tiles;
+        if (getenv("TB_PROFILE") && atoi(getenv("TB_PROFILE")) == 2)
+            fprintf(stderr, "[tb profile lite] clocks/tile  consumer warps: wait_full %.0f of %.0f | producer: wait_empty %.0f of %.0f\n",
+                    h[0] / cw0, h[1] / cw0, h[4] / pw, h[6] / pw);
+        else
         fprintf(stderr, "[tb profile] clocks/tile  q0 warps: wait_full %.0f springs %.0f handoff %.0f mass_update %.0f ell_wait %.0f | q>0 warps: wait_full %.0f springs %.0f handoff %.0f tail %.0f ell_wait %.0f | producer: wait_empty %.0f wait_halo_list %.0f issue %.0f\n",
                 h[0] / cw0, h[1] / cw0, h[2] / cw0, h[3] / cw0, h[7] / cw0, cwq > 0 ? h[8] / cwq : 0, cwq > 0 ? h[9] / cwq : 0, cwq > 0 ? h[10] / cwq : 0,
                 cwq > 0 ? h[11] / cwq : 0, cwq > 0 ? h[15] / cwq : 0, h[4] / pw, h[5] / pw, h[6] / pw);
@@ -1425,6 +1625,7 @@ int tiled_info(const Engine *e, tb_info *info) {
     info->grid = S->grid;
     info->smem_bytes = (int32_t)S->smem_bytes;
     info->ell_unique_tiles = (int32_t)S->ell_unique_tiles;
+    info->dict_records = S->dict ? S->max_dict : 0;
     // read: blob + own state + halo gathers + halo lists + ELL words + meta; written: own state
     info->tiled_bytes_per_step = (int64_t)S->blob_bytes + 2 * S->n_tiles * STATE_BLOCK * 8 + S->n_halo * (4 + (S->stage_vel ? 48 : 24)) +
                                  S->n_tiles * (int64_t)sizeof(TileMeta) + S->n_ell * 4;
