@@ -296,6 +296,8 @@ def main():
     ap.add_argument("--csr", action="store_true", help="force the generic CSR kernel")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--distinct-params", action="store_true",
+                    help="give every spring its own k (defeats the dictionary records: one record per spring is streamed)")
     ap.add_argument("--no-hint", action="store_true", help="let the engine bisect positions instead of lattice bricks")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -367,6 +369,11 @@ def main():
         nrm, off, fk, fs = W["plane"]
         eng.set_planes([tb.Plane((tb.capi.C.c_double * 3)(*nrm), off, fk, fs)])
         eng.set_globals((0.0, 0.0, -9.81), 1e-4)
+    if args.distinct_params:   # every spring its own stiffness: no two records alike, the engine keeps one per spring
+        if args.workload == "c4" and world > 1:
+            raise SystemExit("--distinct-params: cut springs would differ between their two owners; use one GPU")
+        ns_eng = eng.info()["ns"]
+        eng.set_spring_params(k=1e4 * (1.0 + 1e-6 * np.arange(ns_eng, dtype=np.float64) / max(1, ns_eng)))
     nm_total, ns_total = int(reduce_ranks(nm_own, "sum")), int(reduce_ranks(ns_own, "sum"))
     dt, inner = 1e-4, args.inner
 
@@ -450,11 +457,14 @@ def main():
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": name, "masses": nm_total, "springs": ns_total, "sim_steps_per_bench_step": inner,
+                "config": {"workload": name, "masses": nm_total, "springs": ns_total,
+                           "spring_parameters": ("distinct k per spring" if args.distinct_params else
+                                                 "as the builders make them (one k, rest lengths from the coordinates)"),
+                           "sim_steps_per_bench_step": inner,
                            "math": "strict" if args.strict else "fast",
                            "tiling": {k: info[k] for k in ("n_tiles", "threads_per_mass", "grid", "smem_bytes",
                                                            "ell_unique_tiles", "tiled_bytes_per_step", "dict_records")}, "per_rank": per_rank,
-                           "l2": "working set per step and GPU (%.0f MB) exceeds the 126 MB L2" % (alg_bytes / 1e6),
+                           "l2": "no flush: one step streams %.0f MB per GPU from its tables and state (%.0f MB algorithmic), more than the 126 MB L2" % (info["tiled_bytes_per_step"] / 1e6 if info["kernel"] == 1 else alg_bytes / 1e6, alg_bytes / 1e6),
                            "timing": "CUDA events on the engine stream, max over ranks", "wall_ms": wall * 1e3},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world,
                 "clocks": clocks.summary()}

@@ -129,7 +129,8 @@ TB_API int tb_set_globals(tb_engine *e, const double g[3], double dt);
 
 /* ---- stepping: Simulation::execute, src/sim.cu:1704-1841 (Euler branch :1800-1811) -------------------- */
 /* Enqueue nsteps steps on the engine stream and return.  t0 is the host Simulation::T at the first of
- * them; step j uses t = t0 (+ dt) j times, accumulated in fp64 exactly like `T += dt` (:1811). */
+ * them; step j uses t = t0 (+ dt) j times, accumulated in fp64 exactly like `T += dt` (:1811).
+ * nsteps == 0 validates the scene and brings the device layout up to date (tiles, records) without launching. */
 TB_API int tb_run_async(tb_engine *e, int64_t nsteps, double t0);
 TB_API int tb_sync(tb_engine *e);                                  /* cudaDeviceSynchronize at a breakpoint, :1708 */
 TB_API int tb_steps_done(tb_engine *e, int64_t *steps);            /* total steps enqueued so far */

@@ -6,6 +6,8 @@ Tolerances (BASELINE.json north_star: <= 1e-9 relative per step in fp64; indexin
   * TB_MATH_FAST (what bench.py times): pos/vel <= 1e-12 relative after 1 step, <= 1e-9 after 100 steps.
 Relative error is max|a-b| / max(1, max|b|) per field.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -247,3 +249,68 @@ def test_removed_springs_are_bit_identical_to_absent_springs(flags):
     tol = 0.0 if flags & tb.MATH_STRICT else 1e-9
     for f in ("pos", "vel"):
         assert rel(st[f], getattr(o2, f)) <= tol, (f, rel(st[f], getattr(o2, f)))
+
+
+@pytest.mark.parametrize("name", ["c2_small", "contact_friction", "active"])
+def test_dictionary_records_are_bit_identical_to_plain_records(name, monkeypatch):
+    """Dictionary mode of the tiled kernel (springs with bit-identical parameters share a record)
+    changes where a spring's (k, rest, damping, omega) is read from, not the arithmetic: results are bit-identical
+    to the one-record-per-spring layout -- also after parameter uploads that split a class (records rebuilt in
+    place) and after an upload that makes every spring different (falls back to plain records)."""
+    if name == "c2_small":
+        sc = scenes.c2_lattice(24)
+    elif name == "active":
+        sc = scenes.SCENARIOS["contact_friction"]()
+        sc.type[:] = np.arange(sc.ns) % 4          # PASSIVE, ACTIVE_*, ...: table mode of the sine
+        sc.omega[:] = 20.0 * (1 + np.arange(sc.ns) % 3)
+    else:
+        sc = scenes.SCENARIOS[name]()
+    monkeypatch.setenv("TB_TPM", "1")               # one thread per mass also for these small scenes
+    engines = []
+    for dict_on in ("0", "1"):
+        monkeypatch.setenv("TB_DICT", dict_on)      # read when the layout is built, i.e. at the first run
+        eng = tb.Engine(0, tb.MATH_FAST)
+        scenes.upload(eng, sc)
+        eng.run(60, 0.0)
+        engines.append(eng)
+    monkeypatch.delenv("TB_DICT")
+    plain, dic = engines
+    assert plain.info()["dict_records"] == 0 and dic.info()["dict_records"] > 0
+    assert plain.info()["kernel"] == 1 and dic.info()["threads_per_mass"] == 1
+
+    def compare(tag):
+        a, b = plain.get_mass_state(), dic.get_mass_state()
+        for f in ("pos", "vel"):
+            assert same_bits(a[f], b[f]), (tag, f, rel(a[f], b[f]))
+
+    compare("initial classes")
+    t = 0.0
+    for _ in range(60):
+        t += sc.dt
+    # (1) a few springs get their own stiffness: classes split, the dictionary is rebuilt with the slots kept
+    k2 = sc.k.copy()
+    k2[5:40:3] *= 1.5
+    for e in engines:
+        e.set_spring_params(k=k2)
+        e.run(50, t)
+    compare("split classes")
+    assert dic.info()["dict_records"] > 0
+    for _ in range(50):
+        t += sc.dt
+    # (2) same values uploaded again: nothing to rebuild
+    for e in engines:
+        e.set_spring_params(k=k2)
+        e.run(10, t)
+    compare("same values again")
+    for _ in range(10):
+        t += sc.dt
+    # (3) every spring different: more classes than a tile's byte map addresses -> plain records from now on
+    k3 = sc.k * (1.0 + 1e-3 * np.arange(sc.ns) / sc.ns)
+    for e in engines:
+        e.set_spring_params(k=k3)
+        e.run(50, t)
+    compare("all different")
+    if sc.ns > 4096:
+        assert dic.info()["dict_records"] == 0
+    for e in engines:
+        e.close()

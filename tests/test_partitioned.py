@@ -149,6 +149,59 @@ def test_partitioned_engines_match_single_engine(kind, world, flags, tol, monkey
 
 
 @pytest.mark.gpu
+def test_parameter_upload_after_connect_rebuilds_records_in_place(monkeypatch):
+    """Partitioned engines run the dictionary-record layout (fast arithmetic, one thread per mass).  A stiffness upload
+    that splits parameter classes rebuilds the records while the mass slots, state buffers and exchange tables the
+    peers hold pointers into stay where they are."""
+    monkeypatch.setenv("TB_GRID", "16")
+    monkeypatch.setenv("TB_TPM", "1")
+    sc, (nx, ny, nz) = make_scene("plain")
+    k2 = sc.k.copy()
+    k2[::7] *= 1.75
+    ref = tb.Engine(0, tb.MATH_FAST)
+    scenes.upload(ref, sc)
+    ref.run(40, 0.0)
+    t40 = 0.0
+    for _ in range(40):
+        t40 += sc.dt
+    ref.set_spring_params(k=k2)
+    ref.run(60, t40)
+    want = ref.get_mass_state()
+    ref.close()
+
+    world = 2
+    owner = owner_slabs(nx, ny, nz, world)
+    parts = [partition.GraphPartition(sc.nm, sc.left, sc.right, owner, r) for r in range(world)]
+    engines = [tb.Engine(0, tb.MATH_FAST) for _ in range(world)]
+    for en, pt in zip(engines, parts):
+        upload_part(en, sc, pt, pt.mass_gid, pt.spring_gid)
+    partition.connect(engines, parts)
+    for en in engines:
+        en.run_async(40, 0.0)
+    for en in engines:
+        en.sync()
+    assert all(en.info()["dict_records"] > 0 for en in engines)
+    for en, pt in zip(engines, parts):
+        en.set_spring_params(k=k2[pt.spring_gid])
+    # These engines share ONE GPU: the rebuild's cudaMalloc/cudaFree wait for the whole device, so every engine
+    # brings its layout up to date (zero-step run) before any of them launches steps that wait for a peer.
+    for en in engines:
+        en.run_async(0, t40)
+    for en in engines:
+        en.run_async(60, t40)
+    for en in engines:
+        en.sync()
+    assert all(en.info()["dict_records"] > 0 for en in engines)
+    err = 0.0
+    for en, pt in zip(engines, parts):
+        st = en.get_mass_state(fields=("pos", "vel"))
+        for f in ("pos", "vel"):
+            err = max(err, float(np.max(np.abs(st[f][pt.own_local] - want[f][pt.mass_gid[pt.own_local]]))))
+        en.close()
+    assert err <= 1e-12, err
+
+
+@pytest.mark.gpu
 def test_upload_while_paused_then_push(monkeypatch):
     """New state uploaded to the owners reaches the ghosts through tb_halo_push_now."""
     monkeypatch.setenv("TB_GRID", "16")

@@ -713,9 +713,9 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "No masses have been added. Please add masses before starting the simulation.");  // src/sim.cu:1552-1554
     if (nsteps < 0) return fail(e, TB_ERR_INVALID, "tb_run_async: negative step count");
     if (e->any_magnet) return fail(e, TB_ERR_UNSUPPORTED, "magnetic masses (rad > 0 or max_mag_force != 0) need the occupancy-grid pass, which is not built (SURVEY.md row N2)");
-    if (nsteps == 0) return TB_OK;
     if (use_tiled(e)) TB_TRY(tiled_prepare(e));       // may discover that the graph does not fit the tiled format
     if (!use_tiled(e) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
+    if (nsteps == 0) return TB_OK;                    // validation + device layout brought up to date, nothing launched
     if (!use_tiled(e) && e->any_ghost) return fail(e, TB_ERR_UNSUPPORTED, "ghost masses (halo exchange) need the tiled step kernel, which does not support this scene");
     TB_CUDA(e, cudaEventRecord(e->ev0, e->stream));
     set_t_kernel<<<1, 1, 0, e->stream>>>(e->t_dev + e->cur, t0, e->step_dev + e->cur, (long long)e->steps_done);

@@ -9,7 +9,7 @@
 //   masses are re-ordered tile-major: slot = tile*TM + t.  Tiles come from the caller's hint (lattice bricks,
 //   tb_set_tile_hint) or from a recursive coordinate bisection of the current positions.
 //   state[2]  : per tile one contiguous block [px py pz vx vy vz][TM] of doubles, ping-pong
-//   blob      : per tile one contiguous block  header | flags[TM] | m[TM] | (k,rest)[n_rec] | dmp[] | omg[]
+//   blob      : per tile one contiguous block  header | flags[TM] | m[TM] | k[] | rest[] | dmp[] | omg[] | byte map
 //               -- one record per spring touching the tile -- fetched with ONE bulk copy
 //   halo      : per tile the state indices of the foreign masses its springs reach (bulk-copied two tiles
 //               ahead, then used as the address list of the cp.async position gather one tile ahead)
@@ -102,7 +102,7 @@ struct TiledState {
     int max_halo = 0, max_rec = 0, max_deg = 0, max_blob = 0;
     int64_t ell_unique_tiles = 0;
     bool has_damping = false, has_active = false, stage_vel = false;
-    int tpm = 4, grid = 0, cs = CS_BIG;
+    int tpm = 4, grid = 0, cs = CS_BIG, nst = 2;
     size_t smem_bytes = 0;
     // device
     double *st[2] = {nullptr, nullptr};   // tile-blocked state, ping-pong
@@ -242,28 +242,31 @@ struct SmemPlan {            // byte offsets inside the dynamic shared memory of
     int32_t off_ctrl, off_sintab, off_hring, off_part, part_bytes, off_stage, stage_bytes;
     int32_t st_pos, st_vel;  // offsets inside a stage (the blob sits at 0)
     int32_t total;
+    int32_t nst;             // stages of the tile ring (2..MAX_STAGES)
 };
-// mbarriers at offset 0: full[2], empty[2], hfull[HALO_RING]
+constexpr int MAX_STAGES = 4;
+// mbarriers at offset 0: full[MAX_STAGES], empty[MAX_STAGES], hfull[HALO_RING]; tile control words at 128
 // Position component stride is a compile-time constant of the kernel (CS_SMALL or CS_BIG doubles) so that the
 // y and z reads are immediate offsets from the x address.  Local index cs-1 is the DUMMY mass (far away, never
 // written by a copy): padding ELL words point at it and at record 0 (k = 0), and so contribute exactly zero.
 static int choose_cs(int max_halo, bool strict) { return (!strict && TM + max_halo + 1 <= CS_SMALL) ? CS_SMALL : CS_BIG; }
-static SmemPlan plan_smem(int cs, int max_halo, int max_blob, bool stage_vel, int tpm) {
+static SmemPlan plan_smem(int cs, int max_halo, int max_blob, bool stage_vel, int tpm, int nst) {
     SmemPlan p;
+    p.nst = nst;
     int hp = (max_halo + 3) & ~3;
     p.cs = cs;
     p.vs = stage_vel ? p.cs : TM;
     p.hring_stride = (int32_t)up16((size_t)hp * 4 + 16);
-    p.off_ctrl = 64;
-    p.off_sintab = 128;
-    p.off_hring = 128 + MAX_OMEGA * 8;
+    p.off_ctrl = 128;
+    p.off_sintab = 128 + MAX_STAGES * 32;
+    p.off_hring = p.off_sintab + MAX_OMEGA * 8;
     p.off_part = p.off_hring + HALO_RING * p.hring_stride;
     p.part_bytes = (tpm - 1) * 3 * TM * 8;
-    p.off_stage = p.off_part + 2 * p.part_bytes;
+    p.off_stage = p.off_part + nst * p.part_bytes;
     p.st_pos = (int32_t)up16((size_t)max_blob);
     p.st_vel = p.st_pos + 3 * p.cs * 8;
     p.stage_bytes = p.st_vel + 3 * p.vs * 8;
-    p.total = p.off_stage + 2 * p.stage_bytes;
+    p.total = p.off_stage + nst * p.stage_bytes;
     return p;
 }
 
@@ -289,7 +292,7 @@ static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
 
 static size_t blob_size(int n_rec, bool damping, bool active, int n_map = 0) {
     size_t np = (size_t)((n_rec + 1) & ~1);
-    return up16((size_t)BLOB_REC + (size_t)n_rec * 16) + (damping ? np * 8 : 0) + (active ? np * 8 : 0) + up16((size_t)n_map);
+    return (size_t)BLOB_REC + np * 16 + (damping ? np * 8 : 0) + (active ? np * 8 : 0) + up16((size_t)n_map);
 }
 
 // Threads per mass.  Strict arithmetic needs the oracle's summation order (1).  Otherwise: big problems keep
@@ -374,10 +377,10 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, bo
 
     S->has_damping = e->any_damping; S->has_active = e->any_active;
     S->stage_vel = S->has_damping || (e->flags & TB_MATH_STRICT);
-    S->tpm = choose_tpm(e, n_tiles);
+    if (!keep_slots) S->tpm = choose_tpm(e, n_tiles);     // a records-only rebuild keeps the summation order
 
     // dictionary mode: fast arithmetic, one thread per mass (the big-problem configuration)
-    static const bool dict_env = !(getenv("TB_DICT") && atoi(getenv("TB_DICT")) == 0);
+    const bool dict_env = !(getenv("TB_DICT") && atoi(getenv("TB_DICT")) == 0);   // TB_DICT=0: one record per spring
     bool dict = allow_dict && dict_env && S->dict_failures < 2 && !(e->flags & TB_MATH_STRICT) && S->tpm == 1 && e->ns > 0;
     std::vector<int32_t> class_of, rep_of, dict_spring;
     std::vector<uint8_t> rec_map;
@@ -551,7 +554,13 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, bo
         const uint32_t pad = (uint32_t)(S->cs - 1) << ELL_NB_SHIFT;
         for (uint32_t &w : ell) if (!(w & ELL_VALID)) w = pad;
     }
-    SmemPlan plan = plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm);
+    // stages of the tile ring (TB_STAGES): the small dictionary blobs leave room for more than two
+    int nst = 2;      // measured on B200 (C2, dictionary mode): 3 stages 183.7 vs 2 stages 187.9 G spring-steps/s
+    if (const char *v = getenv("TB_STAGES")) nst = std::min(MAX_STAGES, std::max(2, atoi(v)));
+    if (S->tpm > 1) nst = 2;    // named barriers of the partial-sum hand-off are numbered for two stages
+    while (nst > 2 && (size_t)plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm, nst).total > SMEM_LIMIT / 3) nst--;
+    S->nst = nst;
+    SmemPlan plan = plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm, nst);
     if ((size_t)plan.total > SMEM_LIMIT) { S->why_not = "a tile's working set exceeds the shared-memory budget"; return TB_OK; }
     S->smem_bytes = (size_t)plan.total;
 
@@ -613,7 +622,7 @@ __global__ void tiled_refresh_mass(uint8_t *blob, const TileMeta *meta, const in
     uint8_t *b = blob + (size_t)M.blob_off16 * 16;
     int t = threadIdx.x;
     int32_t i = slot_to_api[(int64_t)blockIdx.x * TM + t];
-    if (t == 0) { int32_t *h = (int32_t *)b; h[0] = (int32_t)M.deg; h[1] = (int32_t)M.n_halo; h[2] = (int32_t)M.n_rec; h[3] = 0; }
+    if (t == 0) { int32_t *h = (int32_t *)b; h[0] = (int32_t)M.deg; h[1] = (int32_t)M.n_halo; h[2] = (int32_t)M.n_rec; }   // h[3]: tiled_refresh_params
     b[BLOB_FLAGS + t] = i >= 0 ? flags_c[i] : (uint8_t)0;
     ((double *)(b + BLOB_M))[t] = i >= 0 ? m_c[i] : 1.0;
 }
@@ -635,18 +644,25 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
                                      int has_active, const double *omega_tab, int n_omega, const uint8_t *rec_map) {
     const TileMeta M = meta[blockIdx.x];
     uint8_t *b = blob + (size_t)M.blob_off16 * 16;
-    double2 *rec = (double2 *)(b + BLOB_REC);
-    double *dmp = (double *)(b + ((BLOB_REC + (size_t)M.n_rec * 16 + 15) & ~(size_t)15));
-    double *omg = dmp + (has_damping ? ((M.n_rec + 1) & ~1u) : 0);
+    const uint32_t np = (M.n_rec + 1) & ~1u;      // slots per parameter array: k | rest | damping | omega | byte map
+    double *kk = (double *)(b + BLOB_REC), *rr = kk + np;
+    double *dmp = rr + np;
+    double *omg = dmp + (has_damping ? np : 0);
     if (rec_map) {   // dictionary mode: the slot -> record byte map follows the records (16-byte units)
-        uint4 *dst = (uint4 *)(omg + (has_active ? ((M.n_rec + 1) & ~1u) : 0));
+        uint4 *dst = (uint4 *)(omg + (has_active ? np : 0));
         const uint4 *src = (const uint4 *)rec_map + M.map_off16;
         const uint32_t n16 = (uint32_t)((b + M.blob_bytes - (uint8_t *)dst) / 16);
         for (uint32_t r = threadIdx.x; r < n16; r += blockDim.x) dst[r] = src[r];
     }
+    // one stiffness for the whole tile?  (record 0 is the k = 0 record of the padding words and does not count)
+    const int32_t s1 = M.n_rec > 1 ? rec_spring[M.rec_off + 1] : -1;
+    const long long k1 = s1 >= 0 ? __double_as_longlong(k[s1]) : 0;
+    int same = M.n_rec > 1 && s1 >= 0;
     for (uint32_t r = threadIdx.x; r < M.n_rec; r += blockDim.x) {
         int32_t s = rec_spring[M.rec_off + r];
-        rec[r] = s >= 0 ? make_double2(k[s], rest[s]) : make_double2(0.0, 0.0);
+        kk[r] = s >= 0 ? k[s] : 0.0;
+        rr[r] = s >= 0 ? rest[s] : 0.0;
+        if (r > 0 && (s < 0 || __double_as_longlong(k[s]) != k1)) same = 0;
         if (has_damping) dmp[r] = (s >= 0 && damping) ? damping[s] : 0.0;
         if (has_active) {
             double w = (s >= 0 && omega) ? omega[s] : 0.0;
@@ -658,6 +674,8 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
             omg[r] = w;
         }
     }
+    same = __syncthreads_and(same);
+    if (threadIdx.x == 0) ((int32_t *)b)[3] = same;     // header word 3: the step kernel keeps k in a register
 }
 
 // ---------------------------------------------------------------- PTX helpers ------------------------------
@@ -828,16 +846,18 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
     const int n_my = (A.n_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
     auto tile_of = [&](int i) { return (int64_t)blockIdx.x + (int64_t)i * gridDim.x; };
     auto bar_full = [&](int s) { return smem_base + 8u * (uint32_t)s; };
-    auto bar_empty = [&](int s) { return smem_base + 8u * (uint32_t)(2 + s); };
-    auto bar_halo = [&](int r) { return smem_base + 8u * (uint32_t)(4 + r); };
+    auto bar_empty = [&](int s) { return smem_base + 8u * (uint32_t)(MAX_STAGES + s); };
+    auto bar_halo = [&](int r) { return smem_base + 8u * (uint32_t)(2 * MAX_STAGES + r); };
+    static_assert(8 * (2 * MAX_STAGES + HALO_RING) <= 128 && sizeof(TileCtrl) == 32, "barriers, then the control words");
+    const int NST = sp.nst;
 
     if (tid == 0) {
-        for (int s = 0; s < 2; s++) { mbar_init(bar_full(s), 33); mbar_init(bar_empty(s), NCW); }
+        for (int s = 0; s < NST; s++) { mbar_init(bar_full(s), 33); mbar_init(bar_empty(s), NCW); }
         for (int r = 0; r < HALO_RING; r++) mbar_init(bar_halo(r), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
-    if (tid < 2) {   // the dummy mass of both stages: far away, at rest
+    if (tid < NST) {   // the dummy mass of every stage: far away, at rest
         double *pp = reinterpret_cast<double *>(smem + sp.off_stage + tid * sp.stage_bytes + sp.st_pos);
         pp[CS - 1] = 1e30; pp[2 * CS - 1] = 1e30; pp[3 * CS - 1] = 1e30;
         if (STAGE_VEL) { double *vp = pp + 3 * CS; vp[CS - 1] = 0.0; vp[2 * CS - 1] = 0.0; vp[3 * CS - 1] = 0.0; }
@@ -901,12 +921,11 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
         if (lane == 0) { issue_hidx(0, m0a); if (n_my > 1) issue_hidx(1, m1a); }
         long long pp0 = 0, pp1 = 0, pp2 = 0;
         const long long pb = A.prof ? clock64() : 0;
-        for (int k = 0; k < n_my; k++) {
-            const int s = k & 1;
+        for (int k = 0, s = 0, ph = 1; k < n_my; k++) {   // s = k % NST, ph = parity of the stage's previous use
             __syncwarp();
             load_meta(k + 3, m3a, m3b, m3c);
             long long p0 = A.prof ? clock64() : 0;
-            mbar_wait(bar_empty(s), (uint32_t)(((k >> 1) & 1) ^ 1));    // consumers are done with tile k-2
+            mbar_wait(bar_empty(s), (uint32_t)ph);    // consumers are done with tile k - NST
             long long p1 = A.prof ? clock64() : 0;
             const uint32_t stage = smem_base + (uint32_t)(sp.off_stage + s * sp.stage_bytes);
             if constexpr (HALO) if (!peers_ready && (m0c.z & TF_BOUNDARY)) {
@@ -963,6 +982,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
             if (A.prof && A.prof_lite) pp0 += p1 - p0;
             if (A.prof && !A.prof_lite) { long long p4 = clock64(); pp0 += p1 - p0; pp1 += p3 - p2; pp2 += (p2 - p1) + (p4 - p3); }
             m0a = m1a; m0b = m1b; m0c = m1c; m1a = m2a; m1b = m2b; m1c = m2c; m2a = m3a; m2b = m3b; m2c = m3c;
+            if (++s == NST) { s = 0; ph ^= 1; }
         }
         if (A.prof && A.prof_lite) pp2 = clock64() - pb;   // lite: slot 6 = the whole producer loop
         if (A.prof && lane == 0) { atomicAdd(A.prof + 4, (unsigned long long)pp0); atomicAdd(A.prof + 5, (unsigned long long)pp1); atomicAdd(A.prof + 6, (unsigned long long)pp2); }
@@ -978,10 +998,9 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
     // them with ONE system-scope fence when it reaches its first interior tile (or runs out of tiles).
     long long pa0 = 0, pa1 = 0, pa2 = 0, pa3 = 0, pa4 = 0;
     const long long c_begin = A.prof ? clock64() : 0;
-    for (int i = 0; i < n_my; i++) {
-        const int s = i & 1;
+    for (int i = 0, s = 0, ph = 0; i < n_my; i++) {           // s = i % NST, ph = (i / NST) & 1
         long long c0 = A.prof ? clock64() : 0;
-        mbar_wait(bar_full(s), (uint32_t)((i >> 1) & 1));     // blob, own state and halo of tile i have landed
+        mbar_wait(bar_full(s), (uint32_t)ph);     // blob, own state and halo of tile i have landed
         long long c1 = A.prof ? clock64() : 0;
         const unsigned char *stage = smem + sp.off_stage + s * sp.stage_bytes;
         const uint4 ctrl4 = *reinterpret_cast<const uint4 *>(smem + sp.off_ctrl + s * sizeof(TileCtrl));   // next_ell_off, next_cb, next_nch, has_next
@@ -996,11 +1015,18 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
         }
         const int n_rec = reinterpret_cast<const int32_t *>(stage)[2];
         const uint8_t fl = stage[BLOB_FLAGS + t];
-        const char *prb = reinterpret_cast<const char *>(stage + BLOB_REC);
-        const char *dmb = prb + (size_t)n_rec * 16;
-        const char *omb = dmb + (DAMPING ? ((n_rec + 1) & ~1) * 8 : 0);
+        // record arrays (one 8-byte slot per record, np slots each): k | rest | damping | omega | byte map
+        const int np8 = ((n_rec + 1) & ~1) * 8;
+        const char *kb = reinterpret_cast<const char *>(stage + BLOB_REC);
+        const char *rb = kb + np8;
+        const char *dmb = rb + np8;
+        const char *omb = dmb + (DAMPING ? np8 : 0);
+        // Tiles whose records all carry one stiffness (the header says so) keep it in a register: the shared-memory
+        // pipe is the kernel's bottleneck and this takes one of the two parameter loads per spring off it.
+        const bool k_uniform = reinterpret_cast<const int32_t *>(stage)[3] != 0;
+        const double k_tile = k_uniform ? *reinterpret_cast<const double *>(kb + 8) : 0.0;
         // dictionary mode: the ELL word's record slot goes through the tile's byte map to one of n_rec distinct records
-        const uint8_t *mapb = reinterpret_cast<const uint8_t *>(omb + (ACTIVE ? ((n_rec + 1) & ~1) * 8 : 0));
+        const uint8_t *mapb = reinterpret_cast<const uint8_t *>(omb + (ACTIVE ? np8 : 0));
         const char *pbx = reinterpret_cast<const char *>(stage + sp.st_pos), *pby = pbx + CS * 8, *pbz = pby + CS * 8;
         const char *vbx = reinterpret_cast<const char *>(stage + sp.st_vel), *vby = vbx + sp.vs * 8, *vbz = vby + sp.vs * 8;
         V3 pos = {reinterpret_cast<const double *>(pbx)[t], reinterpret_cast<const double *>(pby)[t], reinterpret_cast<const double *>(pbz)[t]};
@@ -1016,18 +1042,18 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 for (int jj = 0; jj < EPT; jj++) {
                     const uint32_t en = (jj < nch * ELL_CHUNK) ? ell_cur[jj] : 0u;
                     if (en & ELL_VALID) {
-                        const uint32_t nbo = en & 0xff8u, rco = (en >> 12) & 0xfff0u;
+                        const uint32_t nbo = en & 0xff8u, rco = (en >> 13) & 0x7ff8u;
                         const V3 po = {*(const double *)(pbx + nbo), *(const double *)(pby + nbo), *(const double *)(pbz + nbo)};
                         const V3 vo = {*(const double *)(vbx + nbo), *(const double *)(vby + nbo), *(const double *)(vbz + nbo)};
-                        const double2 kr = *(const double2 *)(prb + rco);
+                        const double2 kr = make_double2(*(const double *)(kb + rco), *(const double *)(rb + rco));
                         SpringArgs spr;
                         spr.k = kr.x;
                         spr.rest_scaled = kr.y;
-                        spr.damping = DAMPING ? *(const double *)(dmb + (rco >> 1)) : 0.0;
+                        spr.damping = DAMPING ? *(const double *)(dmb + rco) : 0.0;
                         if (ACTIVE) {
                             const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                            if (A.n_omega > 0) spr.rest_scaled = P::mul(kr.y, actuation_table<P>(ty, sintab, omb + (rco >> 1)));
-                            else if (ty) spr.rest_scaled = P::mul(kr.y, actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + (rco >> 1)), t_sim)));
+                            if (A.n_omega > 0) spr.rest_scaled = P::mul(kr.y, actuation_table<P>(ty, sintab, omb + rco));
+                            else if (ty) spr.rest_scaled = P::mul(kr.y, actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim)));
                         }
                         if (en & ELL_SIDE) acc3<P>(force, spring_force<P, DAMPING>(po, pos, vo, vel, spr));
                         else { V3 f = spring_force<P, DAMPING>(pos, po, vel, vo, spr); acc3<P>(force, V3{-f.x, -f.y, -f.z}); }
@@ -1042,18 +1068,20 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
             // force on this mass = (p_me - p_other) * coef whichever endpoint it is (see physics.cuh)
             auto spring = [&](const uint32_t en) {
                 const uint32_t nbo = en & 0xff8u;
-                uint32_t rco = (en >> 12) & 0xfff0u;
-                if (DICT) rco = (uint32_t)mapb[(en >> 16) & 0xfffu] << 4;
+                uint32_t rco = (en >> 13) & 0x7ff8u;       // byte offset of the record's slot in each parameter array
+                if (DICT) rco = (uint32_t)mapb[(en >> 16) & 0xfffu] << 3;
                 const char *pn = pbx + nbo;
                 const double dx = pos.x - *(const double *)(pn);
                 const double dy = pos.y - *(const double *)(pn + CS * 8);
                 const double dz = pos.z - *(const double *)(pn + 2 * CS * 8);
-                const double2 kr = *(const double2 *)(prb + rco);
+                double2 kr;
+                kr.y = *(const double *)(rb + rco);
+                kr.x = k_uniform ? (rco ? k_tile : 0.0) : *(const double *)(kb + rco);   // record 0 (padding words): k = 0
                 double rest = kr.y;
                 if (ACTIVE) {
                     const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                    if (A.n_omega > 0) rest = kr.y * actuation_table<P>(ty, sintab, omb + (rco >> 1));   // branch-free
-                    else if (ty) rest = kr.y * actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + (rco >> 1)), t_sim));
+                    if (A.n_omega > 0) rest = kr.y * actuation_table<P>(ty, sintab, omb + rco);   // branch-free
+                    else if (ty) rest = kr.y * actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim));
                 }
                 const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
                 const double inv = rsqrt_fast(L2);
@@ -1062,7 +1090,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 if (DAMPING) {   // dot(v_left - v_right, dir) * damping along dir; symmetric in the endpoints
                     const double dvx = *(const double *)(vbx + nbo) - vel.x, dvy = *(const double *)(vby + nbo) - vel.y,
                                  dvz = *(const double *)(vbz + nbo) - vel.z;
-                    coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * (inv * inv), *(const double *)(dmb + (rco >> 1)), coef);
+                    coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * (inv * inv), *(const double *)(dmb + rco), coef);
                 }
                 force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
             };
@@ -1152,6 +1180,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
             else if (pending) { halo_report(A, pending, seq); pending = 0; }
         }
         nch = nch_nxt; rows = rows_nxt;
+        if (++s == NST) { s = 0; ph ^= 1; }
         if (A.prof && A.prof_lite) pa0 += c1 - c0;
         if (A.prof && !A.prof_lite) {
             unsigned sink = 0;
@@ -1320,7 +1349,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     A.l2_hint = 1;
     if (const char *h = getenv("TB_L2_HINT")) A.l2_hint = atoi(h);
     if (const char *d = getenv("TB_DEBUG_SKIP")) A.debug = atoi(d);
-    A.sp = plan_smem(S->cs, S->max_halo, S->max_blob, S->stage_vel, S->tpm);
+    A.sp = plan_smem(S->cs, S->max_halo, S->max_blob, S->stage_vel, S->tpm, S->nst);
     A.st_in = S->st[e->cur]; A.st_out = S->st[e->cur ^ 1];
     A.blob = S->blob; A.slot_to_api = S->slot_to_api; A.halo = S->halo; A.ell = S->ell; A.meta = S->meta;
     A.acc = e->acc;
