@@ -771,6 +771,7 @@ struct TiledArgs {
     // ---- halo exchange (n_peers == 0: single-engine simulation, everything below unused) ----
     int32_t n_peers;
     int32_t n_boundary_units;        // boundary tiles x consumer warps: arrivals that complete a step's exports
+    int32_t n_boundary_tiles;        // tiles [0, n_boundary_tiles) reach ghosts or are exported (they come first)
     const long long *step_in;        // steps completed before this launch (the exchange sequence number)
     long long *step_out;
     unsigned long long *my_flags;    // [n_peers] written by the peers: "my exports of step n have landed"
@@ -813,7 +814,8 @@ template <class P> __device__ __forceinline__ double actuation_from_sin(int ty, 
 // A consumer warp has finished `pending` boundary tiles: make its peer stores visible, count them, and -- as the
 // last warp of the step -- release the step counter into every peer's flag word.  Out of line: runs once per warp
 // and step, and the hot loop's instruction footprint matters.
-__device__ __noinline__ void halo_report(const TiledArgs &A, unsigned pending, unsigned long long seq) {
+__device__ __noinline__ void halo_report(const TiledArgs &A, unsigned pending) {
+    const unsigned long long seq = (unsigned long long)*A.step_in;
     __threadfence_system();   // every lane: its own peer stores are performed system-wide ...
     __syncwarp();             // ... before lane 0 counts the warp's tiles as done
     if ((threadIdx.x & 31) == 0) {
@@ -992,10 +994,10 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
     // ============================================= CONSUMER warps ============================================
     const double t_sim = *A.t_in;
     const double *sintab = reinterpret_cast<const double *>(smem + sp.off_sintab);
-    const unsigned long long seq = HALO ? (unsigned long long)*A.step_in : 0ull;
-    unsigned pending = 0;   // boundary tiles this warp has finished but not yet reported (HALO)
-    // Boundary tiles come first in the tile order, so they are a prefix of every CTA's sequence: the warp reports
-    // them with ONE system-scope fence when it reaches its first interior tile (or runs out of tiles).
+    // Boundary tiles come first in the tile order, so they are the first nb_my tiles of this CTA's sequence: each
+    // warp reports them with ONE system-scope fence right after the last of them.
+    const int nb_my = (HALO && A.n_peers > 0 && A.n_boundary_tiles > (int)blockIdx.x)
+                          ? (A.n_boundary_tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
     long long pa0 = 0, pa1 = 0, pa2 = 0, pa3 = 0, pa4 = 0;
     const long long c_begin = A.prof ? clock64() : 0;
     for (int i = 0, s = 0, ph = 0; i < n_my; i++) {           // s = i % NST, ph = (i / NST) & 1
@@ -1170,15 +1172,10 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 }
             }
         }
-        bool boundary_tile = false;
-        if (HALO) boundary_tile = (reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl)[s].tflags & TF_BOUNDARY) != 0;
         __syncwarp();
         long long c4 = (A.prof && !A.prof_lite) ? clock64() : 0;
         if ((tid & 31) == 0) mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
-        if (HALO && A.n_peers > 0) {
-            if (boundary_tile) pending++;
-            else if (pending) { halo_report(A, pending, seq); pending = 0; }
-        }
+        if (HALO && i + 1 == nb_my) halo_report(A, (unsigned)nb_my);   // this warp's exports of the step are all issued
         nch = nch_nxt; rows = rows_nxt;
         if (++s == NST) { s = 0; ph ^= 1; }
         if (A.prof && A.prof_lite) pa0 += c1 - c0;
@@ -1191,7 +1188,6 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
             pa0 += c1 - c0; pa1 += c2 - c1; pa2 += c3 - c2; pa3 += c4 - c3; pa4 += c5 - c4;
         }
     }
-    if (HALO && pending) halo_report(A, pending, seq);
     if (A.prof && A.prof_lite) pa1 = clock64() - c_begin;   // lite: slot 1 = the whole tile loop
     if (A.prof && (tid & 31) == 0) {
         unsigned long long *pp = A.prof + 8 * (q > 0);
@@ -1356,12 +1352,13 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + (e->cur ^ 1);
     A.omega_tab = S->omega_tab; A.n_omega = S->has_active ? S->n_omega : 0;
     A.step_in = e->step_dev + e->cur; A.step_out = e->step_dev + (e->cur ^ 1);
-    A.n_peers = 0; A.n_boundary_units = 0; A.my_flags = nullptr; A.exp_tab = nullptr; A.boundary_done = nullptr; A.halo_err = nullptr;
+    A.n_peers = 0; A.n_boundary_units = 0; A.n_boundary_tiles = 0; A.my_flags = nullptr; A.exp_tab = nullptr; A.boundary_done = nullptr; A.halo_err = nullptr;
     for (int p = 0; p < TB_MAX_PEERS; p++) { A.peer_flag[p] = nullptr; A.peer_out[p] = nullptr; }
     if (e->any_ghost || S->n_exp_tab) {
         if (!S->halo_connected) return fail(e, TB_ERR_INVALID, "ghost masses need tb_halo_prepare / tb_halo_connect / tb_halo_set_exports before tb_run_async");
         A.n_peers = S->n_peers;
         A.n_boundary_units = (int32_t)(S->n_boundary * (TM * S->tpm / 32));
+        A.n_boundary_tiles = (int32_t)S->n_boundary;
         A.my_flags = S->flags_dev; A.exp_tab = S->exp_tab; A.boundary_done = S->done_dev; A.halo_err = S->err_dev;
         for (int p = 0; p < S->n_peers; p++) { A.peer_flag[p] = S->peer_flag[p]; A.peer_out[p] = S->peer_st[p][e->cur ^ 1]; }
     }
