@@ -811,6 +811,19 @@ template <class P> __device__ __forceinline__ double actuation_from_sin(int ty, 
     return ty == 1 ? P::sub(1.0, P::mul(0.2, sn)) : P::add(1.0, P::mul(0.2, sn));
 }
 
+// The new state of the masses of one tile that are ghosts on a peer, stored straight into the peers' state buffers.
+__device__ __noinline__ void halo_export(const TiledArgs &A, uint32_t exp_rows, uint32_t first, V3 pos, V3 vel) {
+#pragma unroll 1
+    for (uint32_t r = 0; r < exp_rows; r++) {
+        const int2 x = __ldg(A.exp_tab + first + r * TM);
+        if (x.x >= 0) {
+            double *d = A.peer_out[x.x] + x.y;
+            d[0] = pos.x; d[TM] = pos.y; d[2 * TM] = pos.z;
+            d[3 * TM] = vel.x; d[4 * TM] = vel.y; d[5 * TM] = vel.z;
+        }
+    }
+}
+
 // A consumer warp has finished `pending` boundary tiles: make its peer stores visible, count them, and -- as the
 // last warp of the step -- release the step counter into every peer's flag word.  Out of line: runs once per warp
 // and step, and the hot loop's instruction footprint matters.
@@ -1161,15 +1174,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 // halo exchange: the new state of a mass that is a ghost elsewhere goes straight into the peer's buffer
                 // (the exchange fields of the tile control word are read only now, to keep them out of the hot loop)
                 const TileCtrl *cp = reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl) + s;
-                const uint32_t exp_rows = (A.debug & 8) ? 0u : cp->exp_rows, exp_off = cp->exp_off;
-                for (uint32_t r = 0; r < exp_rows; r++) {
-                    const int2 x = __ldg(A.exp_tab + exp_off + r * TM + t);
-                    if (x.x >= 0) {
-                        double *d = A.peer_out[x.x] + x.y;
-                        d[0] = pos.x; d[TM] = pos.y; d[2 * TM] = pos.z;
-                        d[3 * TM] = vel.x; d[4 * TM] = vel.y; d[5 * TM] = vel.z;
-                    }
-                }
+                const uint32_t exp_rows = (A.debug & 8) ? 0u : cp->exp_rows;
+                if (exp_rows) halo_export(A, exp_rows, cp->exp_off + (uint32_t)t, pos, vel);   // boundary tiles only, out of line
             }
         }
         __syncwarp();
