@@ -13,7 +13,8 @@
 //   * get(Container*) / set(Container*) touch exactly the container's masses and springs (the reference over-reads,
 //     src/sim.cu:1080-1081,696-701);
 //   * misuse that made the reference exit(1) throws std::runtime_error instead;
-//   * magnetic masses (RobotLink) make start()/resume() throw: the occupancy-grid magnet pass is not built;
+//   * magnetic masses (RobotLink): the occupancy-grid pass sums pair forces in a fixed order from start-of-step
+//     positions (the reference's order and read/update interleaving are scheduling-dependent);
 //   * step(n) is an extension (BASELINE.json names it; the reference has no such call);
 //   * graphics members are absent (headless).
 #ifndef TITAN_B200_SIM_H
@@ -103,8 +104,18 @@ public:
 
     void printPositions();
 
-    Simulation();
-    explicit Simulation(int device);   // extension: choose the CUDA device (the reference always uses device 0)
+    // The reference picks its integrator when the LIBRARY is compiled (CMake option VERLET -> -DVERLET,
+    // CMakeLists.txt:13,90-93; src/sim.cu:1350-1354).  libTitan.so holds both; a user translation unit compiled with
+    // -DVERLET gets the Verlet one through these inline constructors, everything else the default Euler branch.
+#ifdef VERLET
+#define TITAN_B200_INTEGRATOR 1
+#else
+#define TITAN_B200_INTEGRATOR 0
+#endif
+    struct Init {};
+    Simulation() : Simulation(0, TITAN_B200_INTEGRATOR, Init()) {}
+    explicit Simulation(int device) : Simulation(device, TITAN_B200_INTEGRATOR, Init()) {}   // extension: choose the CUDA device (the reference always uses device 0)
+    Simulation(int device, int integrator, Init);   // integrator: 0 = Euler (default build), 1 = VERLET build
     ~Simulation();
     Simulation(const Simulation &) = delete;
     Simulation &operator=(const Simulation &) = delete;
@@ -125,6 +136,7 @@ private:
     // ---- engine side -------------------------------------------------------------------------------------------
     tb_engine *engine = nullptr;
     int device = 0;
+    int integrator = 0;
     void engine_check(int rc, const char *what);
     void upload_everything();              // topology + all state (start, and after topology edits)
     void upload_masses(Mass *const *list, size_t count);

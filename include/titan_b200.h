@@ -42,7 +42,7 @@ typedef enum {
     TB_ERR_INVALID = 1,     /* bad argument / call order */
     TB_ERR_NO_DEVICE = 2,   /* no CUDA device: there is no CPU path */
     TB_ERR_CUDA = 3,        /* a CUDA call failed; see tb_last_error */
-    TB_ERR_UNSUPPORTED = 4, /* feature outside the built scope (e.g. magnetic masses) */
+    TB_ERR_UNSUPPORTED = 4, /* feature outside the built scope (e.g. ghost masses on the generic kernel) */
     TB_ERR_OOM = 5
 } tb_status;
 
@@ -53,6 +53,9 @@ typedef enum {
                              /* to oracle/titan_oracle.c (passive springs; sin() may differ by 1ulp) */
 #define TB_NO_GRAPH 2u       /* launch every step individually instead of CUDA-Graph batches         */
 #define TB_KERNEL_CSR 4u     /* force the generic CSR-gather step kernel (disable the tiled one)     */
+#define TB_INTEGRATOR_VERLET 8u /* the reference's -DVERLET build (CMakeLists.txt:13,90-93; src/sim.cu:1350-1354):    */
+                             /* vel += 0.5*(acc + f/m)*dt; acc = f/m; pos += vel*dt + 0.5*acc*dt^2, no speed clamp; */
+                             /* acc is persistent state (zero at upload, like CUDA_MASS(Mass&)); generic kernel only */
 
 /* SpringType, include/Titan/spring.h:17-18 */
 enum { TB_PASSIVE_SOFT = 0, TB_PASSIVE_STIFF = 1, TB_ACTIVE_CONTRACT_THEN_EXPAND = 2,
@@ -95,8 +98,10 @@ TB_API int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const i
                       const double *pos, const double *vel, const double *m, const double *T,
                       const double *extern_force, const uint8_t *fixed, const int32_t *drag,
                       const uint8_t *valid);
-/* rad, stiffness, max_mag_force, mag_scale_factor (include/Titan/mass.h:97-100).  Any non-zero rad or
- * max_mag_force makes tb_run_async fail with TB_ERR_UNSUPPORTED (magnet pass). */
+/* rad, stiffness, max_mag_force, mag_scale_factor (include/Titan/mass.h:97-100).  Once any mass has a non-zero rad
+ * or max_mag_force every step runs the occupancy-grid + magnet pass (recomputeOG src/sim.cu:893-906,
+ * computeExternalMagnetForcesOG :1250-1281) on the generic step kernel; until then the pass is elided (it would add
+ * exactly +0).  Pair forces are summed in (cell, ascending mass index) order from start-of-step positions. */
 TB_API int tb_set_mass_magnet(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, const double *rad,
                        const double *stiffness, const double *max_mag_force, const double *mag_scale);
 /* Mass::operator=(CUDA_MASS&) src/mass.cu:21-49, Simulation::get/getAll src/sim.cu:589-654,1051-1116 */

@@ -48,7 +48,8 @@ class _Scene(C.Structure):
                 ("n_planes", C.c_int32), ("n_balls", C.c_int32),
                 ("planes", C.POINTER(Plane)), ("balls", C.POINTER(Ball)),
                 ("lc_ptr", _lp), ("lc", C.POINTER(Local)),
-                ("g", C.c_double * 3), ("dt", C.c_double), ("T_sim", C.c_double), ("magnets", C.c_int32)]
+                ("g", C.c_double * 3), ("dt", C.c_double), ("T_sim", C.c_double), ("magnets", C.c_int32),
+                ("verlet", C.c_int32)]
 
 
 def build(force=False):
@@ -205,6 +206,7 @@ class Scene:
         self.dt = float(dt)
         self.T_sim = 0.0
         self.magnets = False
+        self.verlet = False   # the reference's -DVERLET build
 
     def add_local(self, mass_index, kind, vec, num):
         self.local[mass_index].append(make_local(kind, vec, num))
@@ -243,6 +245,7 @@ class Scene:
             keep += [ptr, lc]
         s.g = _v3(self.g)
         s.dt, s.T_sim, s.magnets = self.dt, self.T_sim, int(self.magnets)
+        s.verlet = int(self.verlet)
         return s, keep
 
     def _run(self, fn, *args):

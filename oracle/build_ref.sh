@@ -5,6 +5,7 @@
 # the reference's CMake build is not used and no reference source enters the repo) into
 #   <out_dir>/libtitan_ref_host.so   host-callable reference code + oracle/ref_host_shim.cu   (CPU, runs here)
 #   <out_dir>/titan_ref_cuda         the reference's CUDA engine + oracle/ref_cuda_dump.cu     (needs a GPU)
+#   <out_dir>/titan_ref_cuda_verlet  the same with the reference's VERLET option (CMakeLists.txt:13,90-93)
 # Flags follow the reference's CMakeLists.txt: C++14, separable compilation, -DCONSTRAINTS, no GRAPHICS.
 set -euo pipefail
 REF="${1:-/root/reference}"
@@ -22,6 +23,7 @@ NVFLAGS="-std=c++14 -O3 -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_1
 for f in vec mass spring object sim; do
   nvcc $NVFLAGS -c "$S/src/$f.cu" -o "$SCRATCH/$f.o" &
 done
+nvcc $NVFLAGS -DVERLET -c "$S/src/sim.cu" -o "$SCRATCH/sim_verlet.o" &
 nvcc $NVFLAGS -c "$HERE/ref_host_shim.cu" -o "$SCRATCH/shim.o" &
 nvcc $NVFLAGS -c "$HERE/ref_cuda_dump.cu" -o "$SCRATCH/dump.o" &
 wait
@@ -31,4 +33,7 @@ nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a -shared -Xcompi
 nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a \
   "$SCRATCH/vec.o" "$SCRATCH/mass.o" "$SCRATCH/spring.o" "$SCRATCH/object.o" "$SCRATCH/sim.o" "$SCRATCH/dump.o" \
   -o "$OUT/titan_ref_cuda" -lcudart
-echo "build_ref: built $OUT/libtitan_ref_host.so and $OUT/titan_ref_cuda"
+nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a \
+  "$SCRATCH/vec.o" "$SCRATCH/mass.o" "$SCRATCH/spring.o" "$SCRATCH/object.o" "$SCRATCH/sim_verlet.o" "$SCRATCH/dump.o" \
+  -o "$OUT/titan_ref_cuda_verlet" -lcudart
+echo "build_ref: built $OUT/libtitan_ref_host.so, $OUT/titan_ref_cuda and $OUT/titan_ref_cuda_verlet"

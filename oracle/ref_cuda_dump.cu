@@ -50,6 +50,18 @@ static void dump_masses(Simulation &sim, const std::string &prefix) {
     put_f64(prefix + "m", m); put_f64(prefix + "T", T);
 }
 
+/* magnet fields of the initial scene; written only by scenes that have any, so older dumps keep their record set */
+static void dump_magnet_fields(Simulation &sim) {
+    std::vector<double> rad, stiff, maxmag, scale;
+    bool any = false;
+    for (Mass *q : sim.masses) {
+        rad.push_back(q->rad); stiff.push_back(q->stiffness); maxmag.push_back(q->max_mag_force); scale.push_back(q->mag_scale_factor);
+        any = any || q->rad != 0 || q->max_mag_force != 0 || q->mag_scale_factor != 0;
+    }
+    if (!any) return;
+    put_f64("init.rad", rad); put_f64("init.stiffness", stiff); put_f64("init.max_mag", maxmag); put_f64("init.mag_scale", scale);
+}
+
 static void dump_springs(Simulation &sim, const std::string &prefix, bool topology) {
     std::unordered_map<Mass *, int> index;
     int n = 0;
@@ -134,6 +146,24 @@ static Scenario build(Simulation &sim, const std::string &name) {
         for (Spring *s : b->springs) s->_k = 5e4;
         sim.createPlane(Vec(0, 0, 1), 2.45, 0.2, 0.3);
         sc.pauses = {0.0, 0.001, 0.02};
+    } else if (name == "magnets") {
+        /* magnetic connector masses (RobotLink) + the occupancy-grid pass.  Every interaction inside the 0.14 m cut-off
+         * is between a FREE and a FIXED mass: the reference reads neighbour positions while their threads may already
+         * have moved them (src/sim.cu:1223-1281 inside massForcesAndUpdate), so only such scenes are reproducible. */
+        for (int g = 0; g < 5; g++) {
+            double x0 = -0.988 + 0.5 * g, len = 0.09;
+            RobotLink *l = sim.createRobotLink(Vec(x0, 0.01, 0.5), Vec(x0 + 0.03, 0.02, 0.5 + len), 0.05, 0.12, 0.08, 0.01,
+                                               2000.0, 0.004 * (g + 1), 0.015);
+            l->masses[0]->fix();
+            Mass *p = sim.createMass(Vec(x0 + 0.035 + 0.002 * g, 0.015, 0.5 + len + 0.02 + 0.004 * g));   /* fixed magnet */
+            p->rad = 0.015; p->stiffness = 4000.0; p->max_mag_force = 0.003; p->mag_scale_factor = 0.8;
+            p->fix();
+            sim.createMass(Vec(x0 + 0.03, 0.02, 0.5 + len + 0.35));   /* free, plain, same cell column, beyond the cut-off */
+            Mass *r = sim.createMass(Vec(x0 + 0.03, 0.02 - 0.03, 0.5 + len - 0.03));   /* fixed, susceptible only */
+            r->mag_scale_factor = 0.5;
+            r->fix();
+        }
+        sc.pauses = {0.0, 0.001, 0.005};
     } else {
         fprintf(stderr, "unknown scenario %s\n", name.c_str());
         exit(2);
@@ -148,6 +178,7 @@ static int do_dump(const std::string &name, const char *path, bool init_only = f
     Simulation sim;
     Scenario sc = build(sim, name);
     dump_masses(sim, "init.");
+    dump_magnet_fields(sim);
     dump_springs(sim, "init.", true);
     if (init_only) { fclose(g_out); return 0; }
     sim.start();

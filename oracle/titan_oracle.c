@@ -271,11 +271,18 @@ static void mass_update_one(to_scene *s, int64_t i, const og_t *og) {
         for (int c = 0; c < 3; c++) force[c] += vel[c] * coef / vel_norm;
     }
 
+    if (s->verlet) {                                              /* #elif VERLET, :1350-1354 */
+        double dt2 = s->dt * s->dt;                               /* pow(dt, 2) */
+        for (int c = 0; c < 3; c++) vel[c] += (0.5 * (acc[c] + force[c] / m)) * s->dt;   /* :1351 */
+        for (int c = 0; c < 3; c++) acc[c] = force[c] / m;                               /* :1352 */
+        for (int c = 0; c < 3; c++) pos[c] += vel[c] * s->dt + (0.5 * acc[c]) * dt2;     /* :1353 */
+    } else {
     for (int c = 0; c < 3; c++) acc[c] = force[c] / m;            /* :1356 */
     for (int c = 0; c < 3; c++) vel[c] = vel[c] + acc[c] * s->dt; /* :1357 */
     vel_norm = to_norm(vel);                                      /* :1359-1360 speed clamp */
     if (vel_norm > 1) for (int c = 0; c < 3; c++) vel[c] = vel[c] / vel_norm;
     for (int c = 0; c < 3; c++) pos[c] = pos[c] + vel[c] * s->dt; /* :1361 */
+    }
     s->T[i] += s->dt;                                             /* :1362 */
     for (int c = 0; c < 3; c++) { force[c] = 0.0; ext[c] = 0.0; } /* :1364-1365 */
 }

@@ -70,6 +70,8 @@ typedef struct {
     double dt;
     double T_sim;                            /* Simulation::T */
     int32_t magnets;                         /* run the occupancy-grid magnet pass (a7) */
+    int32_t verlet;                          /* the reference's -DVERLET build (src/sim.cu:1350-1354) instead of the
+                                                default Euler branch (:1355-1362); acc is then persistent state */
 } to_scene;
 
 /* ---- the step (src/sim.cu:1157-1200, 1285-1367, loop 1704-1714 + 1800-1811) ---- */

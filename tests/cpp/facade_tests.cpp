@@ -284,11 +284,25 @@ static void gpu_tests() {
         CHECK(a->vel[1] == vay && sim.masses.size() == 2);
         sim.stop();
     }
-    section("magnetic masses are refused, not silently mis-simulated");
+    section("RobotLink: magnetic connectors pull each other (occupancy-grid + magnet pass)");
     {
-        Simulation sim;
-        sim.createRobotLink(Vec(0, 0, 0), Vec(0.1, 0, 0), 0.2, 0.15, 0.1, 0.009, 5000, 10.0);
-        CHECK(throws([&] { sim.start(); }, "magnetic"));
+        // reference: createRobotLink src/sim.cu:2201-2222, RobotLink src/object.cu:368-384, magnet pass :1223-1281
+        auto gap_after = [](bool attached) {
+            Simulation sim;
+            sim.setGlobalAcceleration(Vec(0, 0, 0));
+            RobotLink *a = sim.createRobotLink(Vec(0, 0, 1), Vec(0.1, 0, 1), 0.2, 0.15, 0.1, 0.009, 5000, 10.0);
+            RobotLink *b = sim.createRobotLink(Vec(0.15, 0, 1), Vec(0.25, 0, 1), 0.2, 0.15, 0.1, 0.009, 5000, 10.0);
+            if (!attached) { a->detach(); b->detach(); }
+            sim.start();
+            sim.pause(0.002);
+            sim.getAll();
+            double gap = b->masses[0]->pos[0] - a->masses[1]->pos[0];
+            sim.stop();
+            return gap;
+        };
+        double pulled = gap_after(true), loose = gap_after(false);
+        CHECK(pulled < 0.05 - 1e-4);            // the facing connectors (5 cm apart, neighbouring grid cells) approach
+        CHECK(std::fabs(loose - 0.05) < 1e-9);  // detached (max_mag_force = 0) and shells apart: nothing acts
     }
 }
 

@@ -114,9 +114,38 @@ def cube_beam():
     return sc
 
 
+def magnets():
+    """Magnetic connector masses (RobotLink, src/object.cu:368-384) + the occupancy-grid pass; same scene as
+    oracle/ref_cuda_dump.cu "magnets".  Per group: link (fixed end, free end), a fixed magnet close to the free end, a
+    free plain mass beyond the cut-off, a fixed susceptible mass."""
+    pos, fixed, m, rad, stiff, maxmag, scale = [], [], [], [], [], [], []
+    left, right, k, rest = [], [], [], []
+    for g in range(5):
+        x0, ln = -0.988 + 0.5 * g, 0.09
+        b = len(pos)
+        force = 0.004 * (g + 1)
+        for p_, fx in (((x0, 0.01, 0.5), 1), ((x0 + 0.03, 0.02, 0.5 + ln), 0)):          # RobotLink ml, mr
+            pos.append(p_); fixed.append(fx); m.append(0.05); rad.append(0.015); stiff.append(5000.0)
+            maxmag.append(force); scale.append(1.0)
+        left.append(b); right.append(b + 1); k.append(2000.0); rest.append(0.08)
+        pos.append((x0 + 0.035 + 0.002 * g, 0.015, 0.5 + ln + 0.02 + 0.004 * g))           # fixed magnet
+        fixed.append(1); m.append(0.1); rad.append(0.015); stiff.append(4000.0); maxmag.append(0.003); scale.append(0.8)
+        pos.append((x0 + 0.03, 0.02, 0.5 + ln + 0.35))                                     # free plain mass
+        fixed.append(0); m.append(0.1); rad.append(0.0); stiff.append(1000.0); maxmag.append(0.0); scale.append(0.0)
+        pos.append((x0 + 0.03, 0.02 - 0.03, 0.5 + ln - 0.03))                              # fixed susceptible mass
+        fixed.append(1); m.append(0.1); rad.append(0.0); stiff.append(1000.0); maxmag.append(0.0); scale.append(0.5)
+    sc = oracle.Scene(np.array(pos), np.array(left), np.array(right), np.array(rest), k=np.array(k), m=np.array(m))
+    sc.fixed[:] = fixed
+    sc.rad[:] = rad; sc.stiffness[:] = stiff; sc.max_mag[:] = maxmag; sc.mag_scale[:] = scale
+    sc.magnets = True
+    return sc
+
+
 SCENARIOS = {"c1_readme": c1_readme, "contact_friction": contact_friction, "actuated": actuated,
-             "local_constraints": local_constraints, "cube_beam": cube_beam}
+             "local_constraints": local_constraints, "cube_beam": cube_beam, "magnets": magnets}
 # pause() times used by oracle/ref_cuda_dump.cu for each scenario
 PAUSES = {"c1_readme": [0.0, 0.001, 0.01, 0.1], "contact_friction": [0.0, 0.001, 0.01, 0.05],
           "actuated": [0.0, 0.001, 0.01, 0.05], "local_constraints": [0.0, 0.002, 0.01],
-          "cube_beam": [0.0, 0.001, 0.02]}
+          "cube_beam": [0.0, 0.001, 0.02], "magnets": [0.0, 0.001, 0.005]}
+# scenarios that were also run through the reference built with -DVERLET (tests/golden/ref_cuda/ref_verlet_<name>.bin)
+VERLET_SCENARIOS = ("c1_readme", "contact_friction", "actuated", "local_constraints")

@@ -207,16 +207,137 @@ def test_determinism_run_to_run():
     assert same_bits(a["pos"], b["pos"]) and same_bits(a["vel"], b["vel"])
 
 
-def test_magnetic_masses_fail_loudly():
-    sc = scenes.lattice_scene((0, 0, 3), (1, 1, 1), 2)
-    sc.rad[:] = 0.015
-    sc.max_mag[:] = 10.0
-    eng = tb.Engine(0)
-    scenes.upload(eng, sc)
-    with pytest.raises(tb.TitanError) as ei:
-        eng.run(1, 0.0)
-    assert ei.value.status == 4
+@pytest.mark.parametrize("nsteps", [1, 10, 137])
+def test_magnet_pass_strict_is_bit_identical(nsteps):
+    """Occupancy-grid + magnet pass (reference src/sim.cu:865-906,1223-1281) on the RobotLink scene
+    whose reference-CUDA dump pins the oracle (tests/golden/ref_cuda/ref_magnets.bin)."""
+    sc = scenes.magnets()
+    o = oracle_after(sc, nsteps)
+    g = run_engine(sc, nsteps, tb.MATH_STRICT)
+    assert g["info"]["kernel"] == 0                       # magnetic scenes run on the generic kernel
+    for f in FIELDS:
+        assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (f, rel(g[f], getattr(o, f)))
+    assert same_bits(g["T"], o.T)
+    assert same_bits(g["extern_force"] + 0.0, o.ext + 0.0)
+
+
+def magnet_cloud(n=4000, seed=12345):
+    """n free magnetic masses dropped at random into a 0.6 x 0.6 x 0.3 m box (about 18 per occupancy-grid cell, many pairs
+    inside the 0.14 m cut-off, some shells intersecting) + a sparse random spring net; one corner cell is crowded
+    beyond the 128-per-cell capacity."""
+    rng = np.random.default_rng(seed)
+    pos = rng.uniform((-0.3, -0.3, 0.2), (0.3, 0.3, 0.5), size=(n, 3))
+    crowd = 150
+    pos[:crowd, 0] = rng.uniform(0.401, 0.439, crowd)     # one cell: x in [0.40, 0.44), y in [0.40, 0.44)
+    pos[:crowd, 1] = rng.uniform(0.401, 0.439, crowd)
+    pos[:crowd, 2] = rng.uniform(0.0, 3.0, crowd)
+    for j in range(4):                                    # outside the grid: coordinates clamp into cell (255, 0)
+        pos[crowd + j] = (6.0 + 0.01 * j, -7.0, 0.3 + 0.01 * j)
+    left = rng.integers(0, n, size=n // 2).astype(np.int32)
+    right = ((left + 1 + rng.integers(0, n - 1, size=n // 2)) % n).astype(np.int32)
+    import oracle
+    rest = np.linalg.norm(pos[left] - pos[right], axis=1)
+    sc = oracle.Scene(pos, left, right, rest, k=50.0, m=0.05)
+    sc.rad[:] = rng.choice([0.0, 0.01, 0.015], size=n)
+    sc.stiffness[:] = rng.choice([1000.0, 5000.0], size=n)
+    sc.max_mag[:] = rng.choice([0.0, 0.002, 0.004], size=n)
+    sc.mag_scale[:] = rng.choice([0.0, 0.5, 1.0], size=n)
+    sc.fixed[rng.integers(0, n, size=n // 10)] = 1
+    sc.ext[::7] = (0.01, -0.02, 0.03)                     # uploaded one-shot force is folded into the pass's output
+    sc.planes.append(oracle.make_plane((0, 0, 1), 0, 0.5, 0.6))
+    sc.magnets = True
+    return sc
+
+
+@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.NO_GRAPH])
+def test_magnet_cloud_strict_is_bit_identical(flags):
+    """Free-free pairs, cell overflow (> 128 masses in a cell keeps the 128 lowest indices), clamped cell coordinates:
+    the engine's deterministic pass (start-of-step positions, ascending index inside a cell) against the oracle's."""
+    sc = magnet_cloud()
+    o = oracle_after(sc, 60)
+    g = run_engine(sc, 60, flags)
+    for f in FIELDS:
+        assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (f, rel(g[f], getattr(o, f)))
+    assert same_bits(g["extern_force"] + 0.0, o.ext + 0.0)
+
+
+def test_magnet_cloud_fast_within_tolerance():
+    sc = magnet_cloud()
+    for nsteps, tol in ((1, 1e-12), (30, 1e-9)):
+        o = oracle_after(sc, nsteps)
+        g = run_engine(sc, nsteps, tb.MATH_FAST)
+        for f in ("pos", "vel"):
+            assert rel(g[f], getattr(o, f)) <= tol, (nsteps, f, rel(g[f], getattr(o, f)))
+
+
+def test_plain_masses_feel_a_magnetic_neighbour():
+    """A mass with rad = 0 and max_mag_force = 0 still gets a shell-intersection force from a neighbour with rad > 0
+    (its own stiffness scales it, src/sim.cu:1230-1232): the lazily stored uniform stiffness must reach the pass."""
+    sc = scenes.lattice_scene((0, 0, 1), (0.02, 0.02, 0.02), 3)   # 27 masses 1 cm apart
+    sc.stiffness[:] = 1000.0
+    eng = tb.Engine(0, tb.MATH_STRICT)
+    scenes.upload(eng, sc)                                 # uniform, non-magnetic: nothing stored, pass elided
+    eng.run(3, 0.0)
+    o = oracle_after(sc, 3)
+    one = np.array([13], dtype=np.int32)
+    eng.set_mass_magnet(idx=one, rad=np.array([0.015]), stiffness=np.array([5000.0]), max_mag_force=np.array([0.0]),
+                        mag_scale=np.array([0.0]))
+    o.rad[13] = 0.015; o.stiffness[13] = 5000.0; o.magnets = True
+    eng.run(5, o.T_sim); o.step(5)
+    st = eng.get_mass_state()
     eng.close()
+    assert same_bits(st["pos"], o.pos) and same_bits(st["vel"] + 0.0, o.vel + 0.0)
+    q = o.copy(); q.magnets = False; q.step(1)
+    o.step(1)
+    assert not same_bits(q.vel, o.vel)                     # the pass does act on this scene
+
+
+VERLET = tb.INTEGRATOR_VERLET
+
+
+@pytest.mark.parametrize("name", ["c1_readme", "contact_friction", "local_constraints", "cube_beam", "magnets"])
+@pytest.mark.parametrize("nsteps", [1, 10, 137])
+def test_verlet_strict_is_bit_identical(name, nsteps):
+    """The reference's VERLET build option (src/sim.cu:1350-1354): acc is persistent state, no clamp."""
+    sc = scenes.SCENARIOS[name]()
+    sc.verlet = True
+    o = oracle_after(sc, nsteps)
+    g = run_engine(sc, nsteps, tb.MATH_STRICT | VERLET, chunks=2 if nsteps > 10 else 1)
+    assert g["info"]["kernel"] == 0
+    for f in FIELDS:
+        assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (name, f, rel(g[f], getattr(o, f)))
+    assert same_bits(g["T"], o.T)
+
+
+@pytest.mark.parametrize("name", ["c1_readme", "contact_friction", "actuated", "local_constraints"])
+def test_verlet_fast_within_tolerance(name):
+    sc = scenes.SCENARIOS[name]()
+    sc.verlet = True
+    for nsteps, tol in ((1, 1e-12), (100, 1e-9)):
+        o = oracle_after(sc, nsteps)
+        g = run_engine(sc, nsteps, tb.MATH_FAST | VERLET)
+        for f in ("pos", "vel"):
+            assert rel(g[f], getattr(o, f)) <= tol, (name, nsteps, f, rel(g[f], getattr(o, f)))
+        assert rel(g["acc"], o.acc) <= 1e3 * max(tol, 1e-11), (name, nsteps, rel(g["acc"], o.acc))
+
+
+def test_verlet_state_upload_resets_acceleration():
+    """set(Mass*) replaces the whole CUDA_MASS by a freshly constructed one whose acc is zero (src/sim.cu:603-616,
+    src/mass.cu:74-100); under Verlet that acc feeds the next velocity update."""
+    sc = scenes.c1_readme()
+    sc.verlet = True
+    eng = tb.Engine(0, tb.MATH_STRICT | VERLET)
+    scenes.upload(eng, sc)
+    eng.run(20, 0.0)
+    o = oracle_after(sc, 20)
+    idx = np.array([0, 31, 124], dtype=np.int32)
+    st = eng.get_mass_state(idx=idx)
+    eng.set_mass_state(idx=idx, pos=st["pos"], vel=st["vel"])
+    o.acc[idx] = 0.0
+    eng.run(20, o.T_sim); o.step(20)
+    st = eng.get_mass_state()
+    eng.close()
+    assert same_bits(st["pos"], o.pos) and same_bits(st["vel"], o.vel) and same_bits(st["acc"] + 0.0, o.acc + 0.0)
 
 
 @pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.KERNEL_CSR, tb.MATH_FAST])

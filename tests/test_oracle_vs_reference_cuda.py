@@ -35,10 +35,10 @@ def rel(a, b):
     return float(np.max(np.abs(a - b)) / max(1.0, float(np.max(np.abs(b)))))
 
 
-@pytest.mark.parametrize("name", sorted(scenes.SCENARIOS))
-def test_oracle_matches_reference_cuda(name):
-    d = read_dump(os.path.join(GOLD, "ref_%s.bin" % name))
+def check_against_dump(name, path, verlet=False):
+    d = read_dump(path)
     sc = scenes.SCENARIOS[name]()
+    sc.verlet = verlet
     # 1. both descriptions of the scenario agree on the initial scene, bit for bit
     same = lambda a, b: (np.ascontiguousarray(a).ravel().view(np.uint64) == b.view(np.uint64)).all()  # noqa: E731
     assert same(sc.pos, d["init.pos"]) and same(sc.vel, d["init.vel"]) and same(sc.m, d["init.m"])
@@ -46,6 +46,11 @@ def test_oracle_matches_reference_cuda(name):
     assert (sc.type == d["init.type"]).all()
     for f in ("k", "rest", "damping", "omega", "l_max", "l_min", "rate"):
         assert same(getattr(sc, f), d["init." + f]), f
+    if sc.magnets:   # magnet fields as the reference's RobotLink / Mass constructors set them
+        for f in ("rad", "stiffness", "max_mag", "mag_scale"):
+            assert same(getattr(sc, f), d["init." + f]), f
+    else:
+        assert "init.rad" not in d
     # 2. every snapshot: same number of steps (time), same state within tolerance
     worst = {}
     for i, t_pause in enumerate(scenes.PAUSES[name]):
@@ -58,7 +63,19 @@ def test_oracle_matches_reference_cuda(name):
             worst[f] = max(worst.get(f, 0.0), e)
         assert rel(sc.T, d[p + "T"]) == 0.0                         # per-mass T (fixed masses frozen)
         assert rel(sc.rest, d[p + "rest"]) <= 1e-15                 # ACTUATED_* rest mutation
-    print(name, worst)
+    print(name, "verlet" if verlet else "euler", worst)
     assert worst["pos"] <= 1e-9 and worst["vel"] <= 1e-9
     # acc = force/m amplifies cancellation in k*(rest-L): compare on the force scale k*L/m ~ 1e5
     assert worst["acc"] <= 1e-9 * 1e3
+
+
+@pytest.mark.parametrize("name", sorted(scenes.SCENARIOS))
+def test_oracle_matches_reference_cuda(name):
+    check_against_dump(name, os.path.join(GOLD, "ref_%s.bin" % name))
+
+
+@pytest.mark.parametrize("name", scenes.VERLET_SCENARIOS)
+def test_oracle_verlet_matches_reference_verlet_build(name):
+    """The oracle's Verlet branch against the reference compiled with its VERLET option (CMakeLists.txt:13,90-93;
+    src/sim.cu:1350-1354), same scenes, same driver (oracle/_ref/titan_ref_cuda_verlet)."""
+    check_against_dump(name, os.path.join(GOLD, "ref_verlet_%s.bin" % name), verlet=True)

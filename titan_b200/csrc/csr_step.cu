@@ -22,7 +22,7 @@ struct CsrArgs {
     double *t_out;
 };
 
-template <class P, bool DAMPING, bool ACTIVE, bool WRITE_ACC>
+template <class P, bool DAMPING, bool ACTIVE, bool WRITE_ACC, bool VERLET>
 __global__ void __launch_bounds__(128) csr_step_kernel(CsrArgs A, Globals G, MassExtras X) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     double t = *A.t_in;
@@ -60,17 +60,19 @@ __global__ void __launch_bounds__(128) csr_step_kernel(CsrArgs A, Globals G, Mas
         else acc3<P>(force, V3{-f.x, -f.y, -f.z});
     }
     V3 acc;
-    mass_update<P>(G, X, i, fl & F_LOCAL, A.m[i], pos, vel, force, acc);
+    if (VERLET) acc = V3{A.acc[i], A.acc[n + i], A.acc[2 * n + i]};   // the previous step's acceleration is state
+    mass_update<P, VERLET>(G, X, i, fl & F_LOCAL, A.m[i], pos, vel, force, acc);
     A.pos_out[i] = pos.x; A.pos_out[n + i] = pos.y; A.pos_out[2 * n + i] = pos.z;
     A.vel_out[i] = vel.x; A.vel_out[n + i] = vel.y; A.vel_out[2 * n + i] = vel.z;
-    if (WRITE_ACC) { A.acc[i] = acc.x; A.acc[n + i] = acc.y; A.acc[2 * n + i] = acc.z; }
+    if (WRITE_ACC || VERLET) { A.acc[i] = acc.x; A.acc[n + i] = acc.y; A.acc[2 * n + i] = acc.z; }
 }
 
 template <class P, bool DAMPING, bool ACTIVE>
 static void launch_w(Engine *e, const CsrArgs &A, const MassExtras &X, bool write_acc) {
     unsigned grid = (unsigned)((e->nm + 127) / 128);
-    if (write_acc) csr_step_kernel<P, DAMPING, ACTIVE, true><<<grid, 128, 0, e->stream>>>(A, e->G, X);
-    else csr_step_kernel<P, DAMPING, ACTIVE, false><<<grid, 128, 0, e->stream>>>(A, e->G, X);
+    if (e->flags & TB_INTEGRATOR_VERLET) csr_step_kernel<P, DAMPING, ACTIVE, true, true><<<grid, 128, 0, e->stream>>>(A, e->G, X);
+    else if (write_acc) csr_step_kernel<P, DAMPING, ACTIVE, true, false><<<grid, 128, 0, e->stream>>>(A, e->G, X);
+    else csr_step_kernel<P, DAMPING, ACTIVE, false, false><<<grid, 128, 0, e->stream>>>(A, e->G, X);
 }
 template <class P> static void launch_p(Engine *e, const CsrArgs &A, const MassExtras &X, bool write_acc) {
     bool d = e->any_damping, a = e->any_active;
@@ -90,7 +92,7 @@ int launch_csr_step(Engine *e, bool use_ext, bool write_acc) {
     A.k = e->k; A.rest = e->rest; A.damping = e->damping; A.omega = e->omega;
     A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + (e->cur ^ 1);
     MassExtras X;
-    X.ext = (use_ext && e->ext) ? e->ext : nullptr;
+    X.ext = e->any_magnet ? e->mag_force : ((use_ext && e->ext) ? e->ext : nullptr);   // magnet.cu folds the uploaded force in
     X.drag = e->drag;
     X.lc_ptr = e->any_local ? e->lc_ptr : nullptr;
     X.lc = e->lc;

@@ -48,7 +48,6 @@ void dev_free(Engine *e, void *p, size_t bytes) {
     e->device_bytes -= (int64_t)bytes;
 }
 
-#define TB_TRY(x) do { int _rc = (x); if (_rc != TB_OK) return _rc; } while (0)
 
 // ---- staging buffers (pinned host + device), grown on demand ------------------------------------------------
 static int stage(Engine *e, size_t bytes) {
@@ -107,6 +106,14 @@ __global__ void clear_ext_kernel(double *ext, const uint8_t *flags, int64_t nm) 
     if (i >= nm) return;
     uint8_t f = flags[i];
     if ((f & F_VALID) && !(f & F_FIXED)) { ext[i] = 0.0; ext[nm + i] = 0.0; ext[2 * nm + i] = 0.0; }
+}
+// set(Mass*) overwrites the whole CUDA_MASS with a freshly constructed one, whose acc is Vec() = 0 (src/sim.cu:603-616,
+// src/mass.cu:74-100); only the Verlet integrator reads acc back, so only there it matters
+__global__ void zero_vec3_kernel(double *dst, int64_t nm, const int32_t *idx, int64_t first, int64_t count) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= count) return;
+    int64_t i = idx ? idx[j] : first + j;
+    dst[i] = 0.0; dst[nm + i] = 0.0; dst[2 * nm + i] = 0.0;
 }
 __global__ void export_f32_kernel(float *dst, const double *pos, int64_t nm) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -200,6 +207,7 @@ static void free_all(Engine *e) {
     F(e->row_ptr, (size_t)(e->nm + 1) * 4); F(e->adj, (size_t)e->ns * 8);
     F(e->export_f32, (size_t)e->nm * 12);
     F(e->removed_dev, (size_t)e->ns);
+    magnet_free(e);
     e->h_removed.clear(); e->n_removed = 0;
     if (e->lc_ptr) { cudaFree(e->lc_ptr); e->lc_ptr = nullptr; }
     if (e->lc) { cudaFree(e->lc); e->lc = nullptr; }
@@ -358,6 +366,7 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
     e->graph_dirty = true; e->tiled_stale = 0xf; e->canon_stale = false; e->tile_hint.clear();
     e->h_type.assign((size_t)ns, 0);
     e->h_omega.clear();
+    e->stiff_seen = e->scale_seen = false;
     return TB_OK;
 }
 
@@ -385,6 +394,12 @@ int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
     if ((pos || vel) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
     if (pos) TB_TRY(up_vec3(e, e->pos[e->cur], pos, idx, first, count));
     if (vel) TB_TRY(up_vec3(e, e->vel[e->cur], vel, idx, first, count));
+    if ((pos || vel) && (e->flags & TB_INTEGRATOR_VERLET)) {
+        int32_t *didx = nullptr;
+        if (idx) { TB_TRY(stage(e, (size_t)count * 4)); TB_TRY(stage_in(e, idx, (size_t)count * 4, 0)); didx = (int32_t *)e->stage_dev; }
+        zero_vec3_kernel<<<blocks_for(count), 256, 0, e->stream>>>(e->acc, e->nm, didx, first, count);
+        TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    }
     if (m) TB_TRY(up_scalar<double>(e, e->m, m, idx, first, count));
     if (extern_force) {
         bool nz = any_nonzero(extern_force, count * 3);
@@ -437,11 +452,39 @@ extern "C" {
 int tb_set_mass_magnet(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, const double *rad,
                        const double *stiffness, const double *max_mag_force, const double *mag_scale) {
     E_CHECK(e);
-    (void)stiffness; (void)mag_scale;
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_set_mass_magnet before tb_set_topology");
     TB_TRY(check_range(e, e->nm, first, count, idx, "tb_set_mass_magnet"));
-    // The occupancy-grid magnet pass (src/sim.cu:865-906,1223-1281) contributes exactly +0 for masses with
-    // rad == 0 and max_mag_force == 0; the engine elides it and refuses to run anything else.
-    if ((rad && any_nonzero(rad, count)) || (max_mag_force && any_nonzero(max_mag_force, count))) e->any_magnet = true;
+    if (count == 0) return TB_OK;
+    // The occupancy-grid magnet pass (src/sim.cu:865-906,1223-1281) contributes exactly +0 while every mass has
+    // rad == 0 and max_mag_force == 0 (all lattice / cube / beam masses): until the first magnetic mass shows up the
+    // fields are not even stored and the pass is elided.  From then on the engine runs it every step (magnet.cu).
+    bool magnetic = (rad && any_nonzero(rad, count)) || (max_mag_force && any_nonzero(max_mag_force, count));
+    if (!e->mag_rad) {
+        // Not stored yet.  A non-magnetic mass still takes part once another mass is magnetic -- its shell stiffness
+        // scales the intersection force it feels (:1230-1232), its mag_scale_factor the pull it exerts (:1235-1237) --
+        // so remember those two while they are uniform (1000 and 0 for every Mass(pos), include/Titan/mass.h:18-19)
+        // and store the arrays as soon as they are not.
+        auto uniform = [&](const double *src, bool &seen, double &value) {
+            if (!src) return true;
+            for (int64_t j = 0; j < count; j++) {
+                if (!seen) { seen = true; value = src[j]; }
+                else if (memcmp(&value, &src[j], 8) != 0) return false;
+            }
+            return true;
+        };
+        bool keep_lazy = uniform(stiffness, e->stiff_seen, e->stiff_uniform) & uniform(mag_scale, e->scale_seen, e->scale_uniform);
+        if (!magnetic && keep_lazy) return TB_OK;
+        TB_CUDA(e, cudaStreamSynchronize(e->stream));
+        TB_TRY(magnet_alloc(e));
+        if (e->stiff_seen) TB_TRY(fill<double>(e, e->mag_stiff, e->stiff_uniform, e->nm));
+        if (e->scale_seen) TB_TRY(fill<double>(e, e->mag_scale, e->scale_uniform, e->nm));
+    }
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (rad) TB_TRY(up_scalar<double>(e, e->mag_rad, rad, idx, first, count));
+    if (stiffness) TB_TRY(up_scalar<double>(e, e->mag_stiff, stiffness, idx, first, count));
+    if (max_mag_force) TB_TRY(up_scalar<double>(e, e->mag_max, max_mag_force, idx, first, count));
+    if (mag_scale) TB_TRY(up_scalar<double>(e, e->mag_scale, mag_scale, idx, first, count));
+    if (magnetic && !e->any_magnet) { e->any_magnet = true; e->graph_dirty = true; }
     return TB_OK;
 }
 
@@ -664,9 +707,12 @@ __global__ void advance_rest_kernel(double *rest, const int32_t *type, const dou
     else { if (x > l_min[s]) rest[s] = __dsub_rn(x, __dmul_rn(rate[s], dt)); }
 }
 
-static bool use_tiled(Engine *e) { return !(e->flags & TB_KERNEL_CSR) && tiled_supported(e); }
+// the tiled kernel covers the default integrator without magnetic masses; everything else runs on the generic kernel
+static bool use_tiled(Engine *e) {
+    return !(e->flags & (TB_KERNEL_CSR | TB_INTEGRATOR_VERLET)) && !e->any_magnet && tiled_supported(e);
+}
 
-// enqueue ONE step (capturable): [advance_rest] + fused spring-gather/mass-update kernel
+// enqueue ONE step (capturable): [advance_rest] + [occupancy grid + magnet pass] + fused spring-gather/mass-update kernel
 static int enqueue_step(Engine *e, bool use_ext, bool write_acc) {
     if (e->any_actuated) {
         if (!e->l_max || !e->l_min || !e->rate) return fail(e, TB_ERR_INVALID, "actuated springs need l_max, l_min and rate");
@@ -674,6 +720,7 @@ static int enqueue_step(Engine *e, bool use_ext, bool write_acc) {
             e->rest, e->type, e->l_max, e->l_min, e->rate, e->left, e->right, e->mflags, e->G.dt, e->ns);
         e->launches++;
     }
+    if (e->any_magnet) TB_TRY(launch_magnet_pass(e, use_ext));   // recomputeOG + magnet forces, src/sim.cu:1775,1298
     int rc = use_tiled(e) ? launch_tiled_step(e, use_ext, write_acc) : launch_csr_step(e, use_ext, write_acc);
     if (rc != TB_OK) return rc;
     e->launches++;
@@ -712,7 +759,6 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     E_CHECK(e);
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "No masses have been added. Please add masses before starting the simulation.");  // src/sim.cu:1552-1554
     if (nsteps < 0) return fail(e, TB_ERR_INVALID, "tb_run_async: negative step count");
-    if (e->any_magnet) return fail(e, TB_ERR_UNSUPPORTED, "magnetic masses (rad > 0 or max_mag_force != 0) need the occupancy-grid pass, which is not built (SURVEY.md row N2)");
     if (use_tiled(e)) TB_TRY(tiled_prepare(e));       // may discover that the graph does not fit the tiled format
     if (!use_tiled(e) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
     if (nsteps == 0) return TB_OK;                    // validation + device layout brought up to date, nothing launched
@@ -735,7 +781,7 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
         if (!e->graph[e->cur]) TB_TRY(build_graph(e, e->cur));
         while (left_steps - 1 >= GRAPH_STEPS) {
             TB_CUDA(e, cudaGraphLaunch(e->graph[e->cur], e->stream));
-            e->launches += (int64_t)GRAPH_STEPS * (e->any_actuated ? 2 : 1);
+            e->launches += (int64_t)GRAPH_STEPS * (1 + (e->any_actuated ? 1 : 0) + (e->any_magnet ? 5 : 0));
             left_steps -= GRAPH_STEPS;
         }
     }

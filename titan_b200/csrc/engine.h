@@ -55,6 +55,13 @@ struct Engine {
     double *t_dev = nullptr;       // [2] simulation time, ping-pong with the step parity
     long long *step_dev = nullptr; // [2] steps completed, ping-pong (halo exchange sequence number)
     float *export_f32 = nullptr;
+    // magnet / occupancy-grid pass (magnet.cu), allocated with the first magnetic mass: per-mass rad, shell
+    // stiffness, max_mag_force, mag_scale_factor (include/Titan/mass.h:97-100), the pass's output (uploaded one-shot
+    // external force + pair forces, [3][nm]) and the cell lists
+    double *mag_rad = nullptr, *mag_stiff = nullptr, *mag_max = nullptr, *mag_scale = nullptr, *mag_force = nullptr;
+    bool stiff_seen = false, scale_seen = false;         // shell stiffness / mag_scale uploaded so far are uniform:
+    double stiff_uniform = 0.0, scale_uniform = 0.0;     //   remembered here instead of stored per mass
+    int32_t *og_cell = nullptr, *og_items = nullptr, *og_sorted = nullptr, *og_counter = nullptr;
     int cur = 0;                   // which pos/vel buffer holds the current state
 
     // host-side knowledge
@@ -106,11 +113,19 @@ int fail(Engine *e, int status, const char *fmt, ...);
                             __FILE__, __LINE__);                                                 \
     } while (0)
 
+#ifndef TB_TRY
+#define TB_TRY(x) do { int _rc = (x); if (_rc != TB_OK) return _rc; } while (0)
+#endif
+
 template <class T> int dev_alloc(Engine *e, T **p, size_t count);
 void dev_free(Engine *e, void *p, size_t bytes);
 
 // csr_step.cu
 int launch_csr_step(Engine *e, bool use_ext, bool write_acc);
+// magnet.cu
+int magnet_alloc(Engine *e);
+void magnet_free(Engine *e);
+int launch_magnet_pass(Engine *e, bool use_ext);   // occupancy grid + pair forces -> e->mag_force
 // tiled.cu
 int tiled_prepare(Engine *e);                    // (re)build tiles if stale
 int launch_tiled_step(Engine *e, bool use_ext, bool write_acc);

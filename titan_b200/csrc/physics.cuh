@@ -224,7 +224,9 @@ template <class P> static __device__ __noinline__ V3 drag_force(V3 vel, V3 force
 
 // Everything massForcesAndUpdate does after the spring forces are known (src/sim.cu:1299-1365).
 // force: spring-force sum on entry.  Returns new pos/vel through the references; acc_out = force/m.
-template <class P>
+// VERLET selects the reference's -DVERLET branch (src/sim.cu:1350-1354) instead of the default semi-implicit Euler
+// one (:1355-1362): acc_out then carries the mass's PREVIOUS acceleration on entry, and there is no speed clamp.
+template <class P, bool VERLET = false>
 __device__ __forceinline__ void mass_update(const Globals &G, const MassExtras &X, int64_t i, bool has_local,
                                             double m, V3 &pos, V3 &vel, V3 force, V3 &acc_out) {
     acc3<P>(force, scale3<P>(V3{G.g[0], G.g[1], G.g[2]}, m));                       // :1299
@@ -243,7 +245,16 @@ __device__ __forceinline__ void mass_update(const Globals &G, const MassExtras &
 
     if (P::strict || X.drag) force = drag_force<P>(vel, force, X.drag ? X.drag[i] : 0);   // :1329-1332
 
-    if (P::strict) {                                                                // :1356-1361
+    if (VERLET) {
+        // vel += 0.5 * (acc + force / m) * dt;  acc = force / m;  pos += vel * dt + 0.5 * acc * pow(dt, 2)
+        V3 a = P::strict ? div3<P>(force, m) : scale3<P>(force, rcp_fast(m));
+        V3 half = scale3<P>(V3{P::add(acc_out.x, a.x), P::add(acc_out.y, a.y), P::add(acc_out.z, a.z)}, 0.5);
+        acc3<P>(vel, scale3<P>(half, G.dt));
+        acc_out = a;
+        V3 step = scale3<P>(vel, G.dt);
+        acc3<P>(step, scale3<P>(scale3<P>(a, 0.5), P::mul(G.dt, G.dt)));
+        acc3<P>(pos, step);
+    } else if (P::strict) {                                                         // :1356-1361
         acc_out = div3<P>(force, m);
         vel = V3{P::add(vel.x, P::mul(acc_out.x, G.dt)), P::add(vel.y, P::mul(acc_out.y, G.dt)),
                  P::add(vel.z, P::mul(acc_out.z, G.dt))};

@@ -35,7 +35,6 @@
 
 namespace tb {
 
-#define TB_TRY(x) do { int _rc = (x); if (_rc != TB_OK) return _rc; } while (0)
 
 constexpr int TM = 128;                 // masses per tile
 // ELL word: bits 3..11 neighbour local index (so `word & 0xff8` is its byte offset in a position array; own

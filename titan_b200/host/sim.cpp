@@ -24,9 +24,9 @@ const char *kNotStarted = "The simulation has not started. Get and set commands 
 }  // namespace
 
 // ================================================================ (1) bookkeeping ================================
-Simulation::Simulation() : Simulation(0) {}
 
-Simulation::Simulation(int device_) : device(device_), dt(0.0001), T(0), _global_acc(0, 0, -9.81) {}   // src/sim.cu:76-86
+Simulation::Simulation(int device_, int integrator_, Init)
+    : device(device_), integrator(integrator_), dt(0.0001), T(0), _global_acc(0, 0, -9.81) {}   // src/sim.cu:76-86
 
 Mass *Simulation::createMass(Mass *m) {   // src/sim.cu:222-253
     if (ENDED) throw std::runtime_error(kEnded);
@@ -559,7 +559,7 @@ void Simulation::start() {   // src/sim.cu:1547-1591
     std::cout << "Starting simulation with " << masses.size() << " masses and " << springs.size() << " springs." << std::endl;
 
     // no CUDA device -> TB_ERR_NO_DEVICE -> exception: there is no CPU path
-    engine_check(tb_create(device, TB_MATH_FAST, &engine), "tb_create");
+    engine_check(tb_create(device, TB_MATH_FAST | (integrator == 1 ? TB_INTEGRATOR_VERLET : 0u), &engine), "tb_create");
     try {
         upload_everything();
         engine_check(tb_run_async(engine, 0, 0.0), "tb_run_async");   // validates the scene (e.g. refuses magnetic masses)
