@@ -8,9 +8,10 @@ A bench "step" is one batch of --inner simulation time steps (default 200) of th
 springs x simulation-steps / second over ALL ranks with state resident in HBM (CUDA events on the engine
 stream, max over ranks); `e2e` is the same metric through the host-buffer C ABI with the upload of the state
 and the download of the result inside the timed region.  Workload at N=1: BASELINE config C2 (100^3 lattice,
-1,000,000 masses, 12,731,796 springs on a frictional plane).  At N>1 every rank steps its own copy of that
-lattice (independent simulations, no collective; weak scaling) unless --workload c4 selects the partitioned
-lattice with halo exchange.
+1,000,000 masses, 12,731,796 springs on a frictional plane).  At N>1 the default is BASELINE config C4: ONE lattice of
+about 150^3 masses per GPU (189^3 / 238^3 / 300^3 at 2 / 4 / 8 GPUs) cut into i-slabs, boundary-mass halo exchange
+over NVLink peer memory inside the step kernel (weak scaling); --workload c2 / c3 at N>1 step independent copies /
+independent robots per rank with no communication.
 `--impl reference` times the reference's algorithm on the host cores: the reference has no CPU implementation
 of the step (its kernels are __global__ only), so this is the OpenMP transcription in oracle/ (kind "port").
 """

@@ -47,6 +47,20 @@ def test_library_exports_the_reference_api():
     assert "tb_run_async" in und and "tb_set_topology" in und and "cuda" not in und.lower()
 
 
+@pytest.mark.parametrize("shape", [(5, 5, 5), (10, 10, 10), (38, 60, 60), (37, 30, 41), (100, 100, 100), (3, 200, 2)])
+def test_facade_tile_hint_equals_the_array_side_builder(shape):
+    """start() gives the engine the same brick decomposition (layered shapes, super-block numbering) as
+    titan_b200.lattice.brick_hint, which bench.py and the partitioned path use."""
+    import ctypes
+    from titan_b200 import lattice
+    L = ctypes.CDLL(LIB)
+    out = np.zeros(shape[0] * shape[1] * shape[2], dtype=np.int32)
+    n = L.titan_b200_brick_hint(*shape, out.ctypes.data_as(ctypes.c_void_p))
+    ref = lattice.brick_hint(*shape)
+    assert n == ref.max() + 1
+    assert (out == ref).all()
+
+
 def test_host_behaviour():
     r = run([os.path.join(BIN, "titan_facade_tests"), "host"])
     assert r.returncode == 0, r.stdout

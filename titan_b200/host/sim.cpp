@@ -8,6 +8,7 @@
 #include <titan_b200.h>
 
 #include <algorithm>
+#include <array>
 #include <cassert>
 #include <chrono>
 #include <iostream>
@@ -260,25 +261,112 @@ void Simulation::engine_check(int rc, const char *what) {
 
 namespace {
 
-// Brick edge lengths (bx,by,bz), bx*by*bz <= tile, minimising the bytes one step streams for an nx x ny x nz
-// lattice: per tile `tile` mass slots, one 16-byte record per spring touching the brick, 24 bytes per halo mass.
-void brick_dims(int nx, int ny, int nz, int tile, int out[3]) {
+// Modelled bytes one tile of a bx x by x bz brick streams per step: `tile` mass slots, one 16-byte record per spring
+// touching the brick (cut springs are stored by both bricks), 24 bytes per halo mass.
+double brick_cost(int bx, int by, int bz, int tile) {
+    double a = bx - 1, b = by - 1, c = bz - 1;
+    double inner = (a * by * bz + bx * b * bz + bx * by * c) + 2 * (a * b * bz + a * by * c + bx * b * c) + 4 * a * b * c;
+    double recs = 26.0 * bx * by * bz - inner;
+    double halo = (double)(bx + 2) * (by + 2) * (bz + 2) - (double)bx * by * bz;
+    return tile * 104.0 + 16.0 * recs + 24.0 * halo;
+}
+int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// Brick edge lengths (bx,by,bz), bx*by*bz <= tile, minimising the modelled bytes of a step over an nx x ny x nz lattice.
+double brick_dims(int nx, int ny, int nz, int tile, int out[3]) {
     double best = std::numeric_limits<double>::max();
     out[0] = out[1] = out[2] = 1;
     for (int bx = 1; bx <= std::min(nx, tile); bx++)
         for (int by = 1; by <= std::min(ny, tile / bx); by++) {
             int bz = std::min(nz, tile / (bx * by));
             if (bz < 1) continue;
-            auto cdiv = [](int a, int b) { return (a + b - 1) / b; };
-            double tiles = (double)cdiv(nx, bx) * cdiv(ny, by) * cdiv(nz, bz);
-            double a = bx - 1, b = by - 1, c = bz - 1;
-            double inner = (a * by * bz + bx * b * bz + bx * by * c) + 2 * (a * b * bz + a * by * c + bx * b * c) + 4 * a * b * c;
-            double recs = 26.0 * bx * by * bz - inner;
-            double halo = (double)(bx + 2) * (by + 2) * (bz + 2) - (double)bx * by * bz;
-            double cost = tiles * (tile * 104.0 + 16.0 * recs + 24.0 * halo);
+            double cost = (double)cdiv(nx, bx) * cdiv(ny, by) * cdiv(nz, bz) * brick_cost(bx, by, bz, tile);
             if (cost < best) { best = cost; out[0] = bx; out[1] = by; out[2] = bz; }
         }
+    return best;
 }
+
+// Layers of bricks along i (thickness, by, bz), thickest first: when nx is not a multiple of the best brick's
+// thickness one shape wastes its last layer, so the thicknesses are chosen by dynamic programming, each layer with its
+// cheapest cross-section (same model; titan_b200/lattice.py::brick_layers is the array-side twin).
+struct BrickLayer { int t, by, bz; bool operator==(const BrickLayer &o) const { return t == o.t && by == o.by && bz == o.bz; } };
+std::vector<BrickLayer> brick_layers(int nx, int ny, int nz, int tile) {
+    int uni[3];
+    double uniform_cost = brick_dims(nx, ny, nz, tile, uni);
+    std::vector<BrickLayer> uniform((size_t)cdiv(nx, uni[0]), BrickLayer{uni[0], uni[1], uni[2]});
+    const int tmax = std::min(nx, tile);
+    std::vector<double> layer_cost((size_t)tmax + 1, std::numeric_limits<double>::max());
+    std::vector<BrickLayer> layer((size_t)tmax + 1);
+    for (int t = 1; t <= tmax; t++)
+        for (int by = 1; by <= std::min(ny, tile / t); by++) {
+            int bz = std::min(nz, tile / (t * by));
+            if (bz < 1) continue;
+            double c = (double)cdiv(ny, by) * cdiv(nz, bz) * brick_cost(t, by, bz, tile);
+            if (c < layer_cost[(size_t)t]) { layer_cost[(size_t)t] = c; layer[(size_t)t] = BrickLayer{t, by, bz}; }
+        }
+    std::vector<double> cost((size_t)nx + 1, std::numeric_limits<double>::max());
+    std::vector<int> pick((size_t)nx + 1, 0);
+    cost[0] = 0;
+    for (int n = 1; n <= nx; n++)
+        for (int t = 1; t <= std::min(n, tmax); t++)
+            if (cost[(size_t)(n - t)] + layer_cost[(size_t)t] < cost[(size_t)n]) { cost[(size_t)n] = cost[(size_t)(n - t)] + layer_cost[(size_t)t]; pick[(size_t)n] = t; }
+    if (uniform_cost <= cost[(size_t)nx]) return uniform;
+    std::vector<BrickLayer> out;
+    for (int n = nx; n > 0; n -= pick[(size_t)n]) out.push_back(layer[(size_t)pick[(size_t)n]]);
+    std::stable_sort(out.begin(), out.end(), [](const BrickLayer &a, const BrickLayer &b) { return a.t > b.t; });
+    return out;
+}
+
+// Tile id of every cell of an nx x ny x nz grid (i outermost), starting at `base`; returns the number of tiles.  Bricks
+// are numbered super-block by super-block (8^3 bricks each) rather than plane by plane, so that the persistent CTAs
+// work on a compact neighbourhood whose halo state is still in L2.
+int32_t brick_ids(int nx, int ny, int nz, int32_t base, std::vector<int32_t> &ids) {
+    const int B = 8;
+    ids.assign((size_t)nx * ny * nz, 0);
+    std::vector<BrickLayer> layers = brick_layers(nx, ny, nz, 128);
+    int32_t next = base;
+    int i0 = 0;
+    for (size_t j = 0; j < layers.size();) {
+        size_t run = 1;
+        while (j + run < layers.size() && layers[j + run] == layers[j]) run++;
+        const BrickLayer L = layers[j];
+        const int planes = std::min(nx - i0, L.t * (int)run);
+        const int nti = cdiv(planes, L.t), ntj = cdiv(ny, L.by), ntk = cdiv(nz, L.bz);
+        std::vector<int32_t> rank((size_t)nti * ntj * ntk);
+        if (std::max(nti, std::max(ntj, ntk)) > B) {
+            std::vector<int32_t> order(rank.size());
+            for (size_t q = 0; q < order.size(); q++) order[q] = (int32_t)q;
+            auto key = [&](int32_t q) {
+                int bi = q / (ntj * ntk), bj = (q / ntk) % ntj, bk = q % ntk;
+                return std::array<int, 6>{bi / B, bj / B, bk / B, bi % B, bj % B, bk % B};
+            };
+            std::sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return key(a) < key(b); });
+            for (size_t r = 0; r < order.size(); r++) rank[(size_t)order[r]] = (int32_t)r;
+        } else {
+            for (size_t q = 0; q < rank.size(); q++) rank[q] = (int32_t)q;
+        }
+        for (int i = 0; i < planes; i++)
+            for (int jj = 0; jj < ny; jj++)
+                for (int k = 0; k < nz; k++)
+                    ids[((size_t)(i0 + i) * ny + jj) * nz + k] = next + rank[((size_t)(i / L.t) * ntj + jj / L.by) * ntk + k / L.bz];
+        next += (int32_t)rank.size();
+        i0 += planes;
+        j += run;
+    }
+    return next - base;
+}
+
+}  // namespace
+
+// test hook (tests/test_facade.py): the tile hint start() hands the engine for an nx x ny x nz lattice
+extern "C" __attribute__((visibility("default"))) int titan_b200_brick_hint(int nx, int ny, int nz, int32_t *out) {
+    std::vector<int32_t> ids;
+    int32_t n = brick_ids(nx, ny, nz, 0, ids);
+    std::copy(ids.begin(), ids.end(), out);
+    return n;
+}
+
+namespace {
 
 tb_plane to_plane(const ContactPlane &p) {
     tb_plane r;
@@ -426,19 +514,15 @@ void Simulation::upload_everything() {
     bool covered = true;
     for (Container *c : containers) {
         if (!c->grid_nx || c->masses.size() != (size_t)c->grid_nx * c->grid_ny * c->grid_nz) continue;
-        int b[3];
-        brick_dims(c->grid_nx, c->grid_ny, c->grid_nz, 128, b);
-        const int ntj = (c->grid_ny + b[1] - 1) / b[1], ntk = (c->grid_nz + b[2] - 1) / b[2], nti = (c->grid_nx + b[0] - 1) / b[0];
-        size_t q = 0;
-        for (int i = 0; i < c->grid_nx; i++)
-            for (int j = 0; j < c->grid_ny; j++)
-                for (int k = 0; k < c->grid_nz; k++, q++) {
-                    const Mass *m = c->masses[q];
-                    if (m->slot < 0 || masses[(size_t)m->slot] != m) { covered = false; continue; }
-                    if (hint[(size_t)m->slot] >= 0) covered = false;   // shared between two grids
-                    hint[(size_t)m->slot] = base + ((i / b[0]) * ntj + j / b[1]) * ntk + k / b[2];
-                }
-        base += nti * ntj * ntk;
+        std::vector<int32_t> ids;
+        const int32_t n_tiles = brick_ids(c->grid_nx, c->grid_ny, c->grid_nz, base, ids);
+        for (size_t q = 0; q < ids.size(); q++) {
+            const Mass *m = c->masses[q];
+            if (m->slot < 0 || masses[(size_t)m->slot] != m) { covered = false; continue; }
+            if (hint[(size_t)m->slot] >= 0) covered = false;   // shared between two grids
+            hint[(size_t)m->slot] = ids[q];
+        }
+        base += n_tiles;
     }
     for (int64_t i = 0; covered && i < nm; i++) covered = hint[(size_t)i] >= 0;
     if (covered && nm > 0) engine_check(tb_set_tile_hint(engine, hint.data()), "tb_set_tile_hint");

@@ -114,17 +114,58 @@ def brick_dims(nx, ny, nz, tile=128):
     return best[1]
 
 
-def brick_hint(nx, ny, nz, tile=128, base=0, block=None):
-    """Tile id per mass (reference mass order, i outermost) for tb_set_tile_hint: bricks of lattice cells.
+def _brick_cost(bx, by, bz, tile):
+    """Modelled bytes one tile of a bx x by x bz brick streams per step (see brick_dims)."""
+    a, b, c = bx - 1, by - 1, bz - 1
+    inner = (a * by * bz + bx * b * bz + bx * by * c) + 2 * (a * b * bz + a * by * c + bx * b * c) + 4 * a * b * c
+    recs = 26 * bx * by * bz - inner
+    halo = (bx + 2) * (by + 2) * (bz + 2) - bx * by * bz
+    return tile * 104 + 16 * recs + 24 * halo
 
-    Ids order the tiles in the step kernel.  Bricks are numbered super-block by super-block (`block`^3 bricks each,
-    default TB_TILE_BLOCK or 8) rather than plane by plane: the persistent CTAs then work on a compact 3-D
-    neighbourhood, so the state a tile gathers as its halo was touched a few hundred tiles ago and is still in L2,
-    instead of a whole lattice cross-section (tens of MB of streamed spring records) ago."""
-    import os
-    if block is None:
-        block = int(os.environ.get("TB_TILE_BLOCK", "8"))
-    bx, by, bz = brick_dims(nx, ny, nz, tile)
+
+def brick_layers(nx, ny, nz, tile=128):
+    """Layers of bricks along i: [(thickness, by, bz), ...] with sum(thickness) == nx.
+
+    One brick shape for the whole lattice (brick_dims) wastes the last layer when nx is not a multiple of the brick
+    thickness -- e.g. the 37/38-plane slabs of a 300^3 lattice over 8 GPUs need 8 layers of 5 x 5 x 5 bricks (28,800 tiles)
+    where 3 layers of 6 x 5 x 4 plus 4 of 5 x 5 x 5 do it in 27,900 (27,000 for 37 planes).  A tile costs about the same
+    time whatever its fill, so the layers are chosen by dynamic programming over the thickness, each layer with its
+    cheapest cross-section under the byte model of brick_dims.  Same-shaped layers are kept adjacent (thickest first) so
+    that congruent bricks share their incidence tables."""
+    layer = {}
+    for t in range(1, min(nx, tile) + 1):
+        best = None
+        for by in range(1, min(ny, tile // t) + 1):
+            bz = min(nz, tile // (t * by))
+            if bz < 1:
+                continue
+            cost = -(-ny // by) * -(-nz // bz) * _brick_cost(t, by, bz, tile)
+            key = (cost, by, -bz)
+            if best is None or key < best[0]:
+                best = (key, (t, by, bz))
+        if best is not None:
+            layer[t] = (best[0][0], best[1])
+    INF = float("inf")
+    cost = [0.0] + [INF] * nx
+    pick = [0] * (nx + 1)
+    for n in range(1, nx + 1):
+        for t, (c, _) in layer.items():
+            if t <= n and cost[n - t] + c < cost[n]:
+                cost[n], pick[n] = cost[n - t] + c, t
+    out, n = [], nx
+    while n > 0:
+        out.append(layer[pick[n]][1])
+        n -= pick[n]
+    out.sort(key=lambda d: -d[0])
+    uni = brick_dims(nx, ny, nz, tile)
+    uniform_cost = -(-nx // uni[0]) * -(-ny // uni[1]) * -(-nz // uni[2]) * _brick_cost(uni[0], uni[1], uni[2], tile)
+    if uniform_cost <= cost[nx]:          # nothing to gain: keep the single shape (and its tile numbering)
+        return [uni] * (-(-nx // uni[0])) if nx % uni[0] == 0 else None
+    return out
+
+
+def _brick_ids(nx, ny, nz, dims, block):
+    bx, by, bz = dims
     ti = np.arange(nx, dtype=np.int64) // bx
     tj = np.arange(ny, dtype=np.int64) // by
     tk = np.arange(nz, dtype=np.int64) // bz
@@ -138,5 +179,35 @@ def brick_hint(nx, ny, nz, tile=128, base=0, block=None):
         brick_id = rank_of.reshape(nti, ntj, ntk)
     else:
         brick_id = (np.arange(nti)[:, None, None] * ntj + np.arange(ntj)[None, :, None]) * ntk + np.arange(ntk)[None, None, :]
-    ids = brick_id[ti[:, None, None], tj[None, :, None], tk[None, None, :]]
+    return brick_id[ti[:, None, None], tj[None, :, None], tk[None, None, :]]
+
+
+def brick_hint(nx, ny, nz, tile=128, base=0, block=None):
+    """Tile id per mass (reference mass order, i outermost) for tb_set_tile_hint: bricks of lattice cells.
+
+    Ids order the tiles in the step kernel.  Bricks are numbered super-block by super-block (`block`^3 bricks each,
+    default TB_TILE_BLOCK or 8) rather than plane by plane: the persistent CTAs then work on a compact 3-D
+    neighbourhood, so the state a tile gathers as its halo was touched a few hundred tiles ago and is still in L2,
+    instead of a whole lattice cross-section (tens of MB of streamed spring records) ago.  When nx is not a multiple of
+    the brick thickness the lattice is cut into layers of differently shaped bricks (brick_layers; TB_BRICK_LAYERS=0
+    keeps one shape)."""
+    import os
+    if block is None:
+        block = int(os.environ.get("TB_TILE_BLOCK", "8"))
+    layers = brick_layers(nx, ny, nz, tile) if os.environ.get("TB_BRICK_LAYERS", "1") != "0" else None
+    if not layers or len(set(layers)) == 1:
+        return (_brick_ids(nx, ny, nz, brick_dims(nx, ny, nz, tile), block).reshape(-1) + base).astype(np.int32)
+    ids = np.empty((nx, ny, nz), dtype=np.int64)
+    i0, nxt = 0, 0
+    j = 0
+    while j < len(layers):                  # one run of equally shaped layers at a time
+        run = 1
+        while j + run < len(layers) and layers[j + run] == layers[j]:
+            run += 1
+        planes = layers[j][0] * run
+        sub = _brick_ids(planes, ny, nz, layers[j], block)
+        ids[i0:i0 + planes] = sub + nxt
+        nxt += int(sub.max()) + 1
+        i0 += planes
+        j += run
     return (ids.reshape(-1) + base).astype(np.int32)
