@@ -61,23 +61,36 @@ class ClockSampler:
 
     def __init__(self, device):
         self.device, self.rows, self.proc = device, [], None
+        self.t0 = self.t1 = None
 
-    def __enter__(self):
+    def start(self, wait_s=10.0):
+        """Launch nvidia-smi and wait for its first line (on an 8-GPU box it needs more than a second to come up, longer
+        than a short timed region), so that samples exist by the time the region begins."""
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
+            t = time.perf_counter()
+            while not self.rows and time.perf_counter() - t < wait_s and self.proc.poll() is None:
+                time.sleep(0.02)
         except OSError:
             self.proc = None
         return self
 
+    def __enter__(self):                      # the timed region
+        if self.proc is None and self.t0 is None:
+            self.start()
+        self.t0 = time.perf_counter()
+        return self
+
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.perf_counter(), [x.strip() for x in line.split(",")]))
 
     def __exit__(self, *a):
+        self.t1 = time.perf_counter()
         if self.proc:
             time.sleep(0.06)
             self.proc.terminate()
@@ -85,7 +98,8 @@ class ClockSampler:
 
     def summary(self):
         sm, mx, reasons = [], [], set()
-        for r in self.rows:
+        inside = [r for t, r in self.rows if self.t0 is not None and self.t0 <= t <= (self.t1 or t) + 0.06]
+        for r in inside:
             try:
                 sm.append(float(r[1])); mx.append(float(r[2]))
             except (ValueError, IndexError):
@@ -386,12 +400,13 @@ def main():
             t_sim += dt
 
     # ---- device-resident throughput (`value`) ------------------------------------------------------------
+    sampler = ClockSampler(local_rank).start()   # before the warm-up: nvidia-smi is slow to come up
     for _ in range(args.warmup):
         advance(inner)
     eng.sync()
     barrier()
     launches0 = eng.info()["launches"]
-    with ClockSampler(local_rank) as clocks:
+    with sampler as clocks:
         w0 = time.perf_counter()
         advance(inner * args.steps)
         eng.sync()
