@@ -197,7 +197,8 @@ typedef struct {
     int64_t ns_removed;          /* springs turned into tombstones by tb_remove_springs */
     int32_t dict_records;        /* tiled kernel, dictionary mode: most distinct (k, rest, ...) records in a tile; 0 = one
                                     record per spring (parameters too diverse, strict arithmetic or TB_DICT=0) */
-    int32_t reserved0;
+    int32_t dict_split_k;        /* 1 = split dictionary: (rest, damping, omega) records shared, stiffness one value per
+                                    record slot (systems whose k is edited spring by spring, BASELINE config C5) */
 } tb_info;
 TB_API int tb_get_info(tb_engine *e, tb_info *info);
 /* headless position export, fp64 -> packed fp32 xyz (updateVertices, src/sim.cu:1944-1952); out is a

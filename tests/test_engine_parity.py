@@ -431,7 +431,31 @@ def test_dictionary_records_are_bit_identical_to_plain_records(name, monkeypatch
         e.set_spring_params(k=k3)
         e.run(50, t)
     compare("all different")
+    # ... but the rest lengths (and damping, omega) still fall into a few classes: split dictionary -- those stay shared,
+    # the stiffness becomes one value per record slot (BASELINE config C5 rewrites every k every 100 steps)
+    assert plain.info()["dict_records"] == 0 and plain.info()["dict_split_k"] == 0
     if sc.ns > 4096:
-        assert dic.info()["dict_records"] == 0
+        assert dic.info()["dict_records"] > 0 and dic.info()["dict_split_k"] == 1
+    for _ in range(50):
+        t += sc.dt
+    # (4) in that mode a new k for every spring needs no rebuild, and removed springs (tombstones: k = 0) stay removed
+    gone = np.arange(7, sc.ns, 23).astype(np.int32)
+    k4 = k3 * (0.9 + 0.2 * ((np.arange(sc.ns) * 2654435761 % 1000) / 1000.0))
+    for e in engines:
+        e.remove_springs(gone)
+        e.set_spring_params(k=k4)
+        e.run(50, t)
+    compare("k rewrite + tombstones")
+    if sc.ns > 4096:
+        assert dic.info()["dict_split_k"] == 1
+    for _ in range(50):
+        t += sc.dt
+    # (5) a rest-length edit that splits a class of the split dictionary: records rebuilt, results unchanged
+    r5 = sc.rest.copy()
+    r5[11:300:7] *= 1.001
+    for e in engines:
+        e.set_spring_params(rest=r5)
+        e.run(30, t)
+    compare("rest edit in split mode")
     for e in engines:
         e.close()

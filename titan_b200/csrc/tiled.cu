@@ -109,7 +109,12 @@ struct TiledState {
     int32_t *slot_to_api = nullptr, *halo = nullptr, *rec_spring = nullptr;
     // Dictionary mode (see build_structure): springs with bit-identical parameters share one record per tile.
     bool dict = false;                    // the blobs hold distinct records + a byte map (record slot -> record)
+    bool dict_split = false;              // ... for (rest, damping, omega) only: the stiffness stays one value per record
+                                          // slot (systems whose k is edited per spring, e.g. topology optimisation)
+    int32_t *krec_spring = nullptr; int64_t n_krec = 0;   // split mode: record slot -> spring, all tiles
+    uint32_t *krec_off = nullptr;                         // split mode: [n_tiles + 1] first slot of each tile in krec_spring
     int dict_failures = 0;                // parameter uploads that broke the classes; after 2 the mode stays off
+    int split_failures = 0;               // the same for the split dictionary
     int64_t n_class_rep = 0;
     int32_t *class_rep = nullptr;         // [ns] a spring with the same parameters (the class representative)
     uint8_t *rec_map = nullptr; int64_t n_rec_map = 0;
@@ -280,7 +285,9 @@ template <class T> static void release(Engine *e, T *&p, size_t count) { dev_fre
 static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
     if (!keep_state) for (int p = 0; p < 2; p++) release(e, S->st[p], (size_t)S->n_tiles * STATE_BLOCK);
     release(e, S->class_rep, (size_t)S->n_class_rep); S->n_class_rep = 0; release(e, S->rec_map, (size_t)S->n_rec_map);
-    S->n_rec_map = 0; S->dict = false;
+    S->n_rec_map = 0; S->dict = false; S->dict_split = false;
+    release(e, S->krec_spring, (size_t)S->n_krec); S->n_krec = 0;
+    if (S->krec_off) { cudaFree(S->krec_off); S->krec_off = nullptr; }
     release(e, S->blob, S->blob_bytes);
     release(e, S->slot_to_api, (size_t)S->n_slots); release(e, S->halo, (size_t)S->n_halo);
     release(e, S->rec_spring, (size_t)S->n_rec); release(e, S->ell, (size_t)S->n_ell);
@@ -289,9 +296,11 @@ static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
     S->blob_bytes = 0;
 }
 
-static size_t blob_size(int n_rec, bool damping, bool active, int n_map = 0) {
-    size_t np = (size_t)((n_rec + 1) & ~1);
-    return (size_t)BLOB_REC + np * 16 + (damping ? np * 8 : 0) + (active ? np * 8 : 0) + up16((size_t)n_map);
+// n_rec records (k | rest | damping | omega arrays of n_rec slots each, rounded up to even), then the byte map of the
+// dictionary modes; n_k >= 0 (split dictionary): the k array has n_k slots of its own (one per record slot)
+static size_t blob_size(int n_rec, bool damping, bool active, int n_map = 0, int n_k = -1) {
+    size_t np = (size_t)((n_rec + 1) & ~1), nk = n_k >= 0 ? (size_t)((n_k + 1) & ~1) : np;
+    return (size_t)BLOB_REC + nk * 8 + np * 8 + (damping ? np * 8 : 0) + (active ? np * 8 : 0) + up16((size_t)n_map);
 }
 
 // Threads per mass.  Strict arithmetic needs the oracle's summation order (1).  Otherwise: big problems keep
@@ -315,7 +324,7 @@ static int choose_tpm(const Engine *e, int64_t n_tiles) {
 constexpr int DICT_CTAS = TB_DICT_CTAS;   // resident CTAs per SM the dictionary-mode kernels are compiled for (register cap)
 constexpr int DICT_MAX_TILE = 256;        // records a tile's byte map can address
 constexpr int DICT_MAX_GLOBAL = 1 << 16;
-static int param_classes(Engine *e, bool damping, bool active, std::vector<int32_t> &class_of, std::vector<int32_t> &rep_of,
+static int param_classes(Engine *e, bool with_k, bool damping, bool active, std::vector<int32_t> &class_of, std::vector<int32_t> &rep_of,
                          bool *ok) {
     *ok = false;
     const size_t ns = (size_t)e->ns;
@@ -334,7 +343,7 @@ static int param_classes(Engine *e, bool damping, bool active, std::vector<int32
     Key last = {0, 0, 0, 0}; int32_t last_class = -1;
     auto bits = [](double x) { uint64_t u; memcpy(&u, &x, 8); return u; };
     for (size_t sp = 0; sp < ns; sp++) {
-        Key key = {bits(hk[sp]), bits(hr[sp]), hd.empty() ? 0 : bits(hd[sp]), ho.empty() ? 0 : bits(ho[sp])};
+        Key key = {with_k ? bits(hk[sp]) : 0, bits(hr[sp]), hd.empty() ? 0 : bits(hd[sp]), ho.empty() ? 0 : bits(ho[sp])};
         int32_t c;
         if (last_class >= 0 && key == last) c = last_class;
         else {
@@ -355,7 +364,9 @@ static int param_classes(Engine *e, bool damping, bool active, std::vector<int32
 // S->supported == false (and a reason) when the graph does not fit the tiled format.
 // keep_slots: the mass -> slot assignment, the state buffers and the halo-exchange fields of the tile table stay
 // (a rebuild after a parameter upload that broke the dictionary classes; peers keep their pointers and offsets).
-static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, bool allow_dict = true) {
+// mode: 1 = try the full dictionary, then (2) the split one -- classes over (rest, damping, omega), k per record slot --
+// then (0) one record per spring.
+static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, int mode = 1) {
     std::vector<TileMeta> old_meta;
     if (keep_slots) old_meta = S->h_meta;
     free_structure(e, S, keep_slots);
@@ -379,13 +390,19 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, bo
     if (!keep_slots) S->tpm = choose_tpm(e, n_tiles);     // a records-only rebuild keeps the summation order
 
     // dictionary mode: fast arithmetic, one thread per mass (the big-problem configuration)
-    const bool dict_env = !(getenv("TB_DICT") && atoi(getenv("TB_DICT")) == 0);   // TB_DICT=0: one record per spring
-    bool dict = allow_dict && dict_env && S->dict_failures < 2 && !(e->flags & TB_MATH_STRICT) && S->tpm == 1 && e->ns > 0;
-    std::vector<int32_t> class_of, rep_of, dict_spring;
+    const int dict_env = getenv("TB_DICT") ? atoi(getenv("TB_DICT")) : 1;   // TB_DICT=0: one record per spring, 2: split only
+    if (mode == 1 && (dict_env == 2 || S->dict_failures >= 2)) mode = 2;
+    if (mode == 2 && S->split_failures >= 2) mode = 0;
+    bool dict = mode != 0 && dict_env != 0 && !(e->flags & TB_MATH_STRICT) && S->tpm == 1 && e->ns > 0;
+    const bool split = dict && mode == 2;
+    const int next_mode = mode == 1 ? 2 : 0;          // what to try when this mode does not fit
+    std::vector<int32_t> class_of, rep_of, dict_spring, kslot_spring;
+    std::vector<uint32_t> krec_off;
     std::vector<uint8_t> rec_map;
     std::vector<int32_t> cls_stamp, cls_local;
     if (dict) {
-        TB_TRY(param_classes(e, S->has_damping, S->has_active, class_of, rep_of, &dict));
+        TB_TRY(param_classes(e, !split, S->has_damping, S->has_active, class_of, rep_of, &dict));
+        if (!dict && next_mode) return build_structure(e, S, keep_slots, next_mode);
         if (dict) {
             int32_t n_classes = 0;
             for (int32_t c : class_of) n_classes = std::max(n_classes, c + 1);
@@ -532,10 +549,14 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, bo
                 }
                 rec_map.push_back((uint8_t)cls_local[(size_t)c]);
             }
-            if (!dict) return build_structure(e, S, keep_slots, false);   // a tile with too many classes: plain records
-            rec_spring.resize(rec_first);                                  // slot -> spring is not needed in this mode
+            if (!dict) return build_structure(e, S, keep_slots, next_mode);   // a tile with too many classes
+            if (split) {                                                   // slot -> spring, for the per-slot stiffness
+                krec_off.push_back((uint32_t)kslot_spring.size());
+                kslot_spring.insert(kslot_spring.end(), rec_spring.begin() + (ptrdiff_t)rec_first, rec_spring.end());
+            }
+            rec_spring.resize(rec_first);
             M.n_rec = (uint32_t)n_dict;
-            bb = blob_size(n_dict, S->has_damping, S->has_active, n_rec);
+            bb = blob_size(n_dict, S->has_damping, S->has_active, n_rec, split ? n_rec : -1);
             max_dict = std::max(max_dict, n_dict);
         }
         if (blob_total / 16 >= ((size_t)1 << 32)) { S->why_not = "blob exceeds 64 GB"; return TB_OK; }
@@ -570,7 +591,14 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, bo
         TB_TRY(dev_alloc(e, &S->st[p], (size_t)n_tiles * STATE_BLOCK));
         TB_CUDA(e, cudaMemset(S->st[p], 0, (size_t)n_tiles * STATE_BLOCK * 8));
     }
-    S->dict = dict; S->max_dict = max_dict;
+    S->dict = dict; S->max_dict = max_dict; S->dict_split = split;
+    if (split) {
+        krec_off.push_back((uint32_t)kslot_spring.size());
+        S->n_krec = (int64_t)kslot_spring.size();
+        TB_TRY(upload_vec(e, &S->krec_spring, kslot_spring));
+        TB_CUDA(e, cudaMalloc((void **)&S->krec_off, krec_off.size() * sizeof(uint32_t)));
+        TB_CUDA(e, cudaMemcpy(S->krec_off, krec_off.data(), krec_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    }
     if (dict) {
         while (rec_map.size() % 16) rec_map.push_back(0);
         rec_spring.swap(dict_spring);
@@ -632,7 +660,8 @@ __global__ void dict_check_kernel(int64_t ns, const int32_t *class_rep, const do
     if (sp >= ns) return;
     const int32_t r = class_rep[sp];
     if (r == sp) return;
-    bool same = __double_as_longlong(k[sp]) == __double_as_longlong(k[r]) && __double_as_longlong(rest[sp]) == __double_as_longlong(rest[r]);
+    bool same = __double_as_longlong(rest[sp]) == __double_as_longlong(rest[r]);
+    if (k) same = same && __double_as_longlong(k[sp]) == __double_as_longlong(k[r]);      // null: split dictionary, k is per slot
     if (damping) same = same && __double_as_longlong(damping[sp]) == __double_as_longlong(damping[r]);
     if (omega) same = same && __double_as_longlong(omega[sp]) == __double_as_longlong(omega[r]);
     if (!same) *bad = 1;
@@ -640,11 +669,15 @@ __global__ void dict_check_kernel(int64_t ns, const int32_t *class_rep, const do
 // one CTA per tile: the spring records of the tile's blob
 __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const int32_t *rec_spring, const double *k,
                                      const double *rest, const double *damping, const double *omega, int has_damping,
-                                     int has_active, const double *omega_tab, int n_omega, const uint8_t *rec_map) {
+                                     int has_active, const double *omega_tab, int n_omega, const uint8_t *rec_map,
+                                     const int32_t *krec_spring, const uint32_t *krec_off) {
     const TileMeta M = meta[blockIdx.x];
     uint8_t *b = blob + (size_t)M.blob_off16 * 16;
     const uint32_t np = (M.n_rec + 1) & ~1u;      // slots per parameter array: k | rest | damping | omega | byte map
-    double *kk = (double *)(b + BLOB_REC), *rr = kk + np;
+    // split dictionary: the k array has one slot per record slot of the tile, the other arrays one per distinct record
+    const uint32_t k0 = krec_off ? krec_off[blockIdx.x] : 0u, n_k = krec_off ? krec_off[blockIdx.x + 1] - k0 : 0u;
+    const uint32_t nk = krec_off ? ((n_k + 1) & ~1u) : np;
+    double *kk = (double *)(b + BLOB_REC), *rr = kk + nk;
     double *dmp = rr + np;
     double *omg = dmp + (has_damping ? np : 0);
     if (rec_map) {   // dictionary mode: the slot -> record byte map follows the records (16-byte units)
@@ -656,10 +689,14 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
     // one stiffness for the whole tile?  (record 0 is the k = 0 record of the padding words and does not count)
     const int32_t s1 = M.n_rec > 1 ? rec_spring[M.rec_off + 1] : -1;
     const long long k1 = s1 >= 0 ? __double_as_longlong(k[s1]) : 0;
-    int same = M.n_rec > 1 && s1 >= 0;
+    int same = M.n_rec > 1 && s1 >= 0 && !krec_off;
+    for (uint32_t r = threadIdx.x; r < n_k; r += blockDim.x) {
+        int32_t s = krec_spring[k0 + r];
+        kk[r] = s >= 0 ? k[s] : 0.0;
+    }
     for (uint32_t r = threadIdx.x; r < M.n_rec; r += blockDim.x) {
         int32_t s = rec_spring[M.rec_off + r];
-        kk[r] = s >= 0 ? k[s] : 0.0;
+        if (!krec_off) kk[r] = s >= 0 ? k[s] : 0.0;
         rr[r] = s >= 0 ? rest[s] : 0.0;
         if (r > 0 && (s < 0 || __double_as_longlong(k[s]) != k1)) same = 0;
         if (has_damping) dmp[r] = (s >= 0 && damping) ? damping[s] : 0.0;
@@ -674,7 +711,9 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
         }
     }
     same = __syncthreads_and(same);
-    if (threadIdx.x == 0) ((int32_t *)b)[3] = same;     // header word 3: the step kernel keeps k in a register
+    // header word 3: bit 0 = one stiffness for the whole tile (the step kernel keeps it in a register), bits 8.. = slots
+    // of the k array in split-dictionary mode
+    if (threadIdx.x == 0) ((int32_t *)b)[3] = same | (int32_t)(n_k << 8);
 }
 
 // ---------------------------------------------------------------- PTX helpers ------------------------------
@@ -846,7 +885,9 @@ __device__ __noinline__ void halo_report(const TiledArgs &A, unsigned pending) {
 //   empty[s] : one arrival per consumer warp when it has finished reading stage s
 //   hfull[r] : bulk copy of a halo index list (producer-internal)
 // plus one named barrier per 32-mass column and tile parity for handing the partial sums to thread q == 0.
-template <class P, bool DAMPING, bool ACTIVE, int TPM, int CS, bool HALO, bool DICT>
+// DICT: 0 = one record per spring, 1 = per-tile dictionary of (k, rest, damping, omega), 2 = dictionary of (rest, damping,
+// omega) with the stiffness stored per record slot
+template <class P, bool DAMPING, bool ACTIVE, int TPM, int CS, bool HALO, int DICT>
 __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS : 2) : 1)) tiled_step_kernel(const __grid_constant__ TiledArgs A,
                                                                    const __grid_constant__ Globals G,
                                                                    const __grid_constant__ MassExtras X) {
@@ -1030,14 +1071,16 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
         const int n_rec = reinterpret_cast<const int32_t *>(stage)[2];
         const uint8_t fl = stage[BLOB_FLAGS + t];
         // record arrays (one 8-byte slot per record, np slots each): k | rest | damping | omega | byte map
+        const int hdr3 = reinterpret_cast<const int32_t *>(stage)[3];
         const int np8 = ((n_rec + 1) & ~1) * 8;
+        const int nk8 = DICT == 2 ? (((hdr3 >> 8) + 1) & ~1) * 8 : np8;
         const char *kb = reinterpret_cast<const char *>(stage + BLOB_REC);
-        const char *rb = kb + np8;
+        const char *rb = kb + nk8;
         const char *dmb = rb + np8;
         const char *omb = dmb + (DAMPING ? np8 : 0);
         // Tiles whose records all carry one stiffness (the header says so) keep it in a register: the shared-memory
         // pipe is the kernel's bottleneck and this takes one of the two parameter loads per spring off it.
-        const bool k_uniform = reinterpret_cast<const int32_t *>(stage)[3] != 0;
+        const bool k_uniform = DICT != 2 && (hdr3 & 1);
         const double k_tile = k_uniform ? *reinterpret_cast<const double *>(kb + 8) : 0.0;
         // dictionary mode: the ELL word's record slot goes through the tile's byte map to one of n_rec distinct records
         const uint8_t *mapb = reinterpret_cast<const uint8_t *>(omb + (ACTIVE ? np8 : 0));
@@ -1083,6 +1126,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
             auto spring = [&](const uint32_t en) {
                 const uint32_t nbo = en & 0xff8u;
                 uint32_t rco = (en >> 13) & 0x7ff8u;       // byte offset of the record's slot in each parameter array
+                const uint32_t kco = rco;                  // DICT == 2: the stiffness stays with the slot
                 if (DICT) rco = (uint32_t)mapb[(en >> 16) & 0xfffu] << 3;
                 const char *pn = pbx + nbo;
                 const double dx = pos.x - *(const double *)(pn);
@@ -1090,7 +1134,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 const double dz = pos.z - *(const double *)(pn + 2 * CS * 8);
                 double2 kr;
                 kr.y = *(const double *)(rb + rco);
-                kr.x = k_uniform ? (rco ? k_tile : 0.0) : *(const double *)(kb + rco);   // record 0 (padding words): k = 0
+                kr.x = k_uniform ? (rco ? k_tile : 0.0) : *(const double *)(kb + (DICT == 2 ? kco : rco));   // record 0 (padding words): k = 0
                 double rest = kr.y;
                 if (ACTIVE) {
                     const int ty = (en >> ELL_TYPE_SHIFT) & 3;
@@ -1202,7 +1246,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
 }
 
 // ---------------------------------------------------------------- glue ------------------------------------
-template <class P, bool D, bool AC, int TPM, int CS, bool HALO, bool DICT>
+template <class P, bool D, bool AC, int TPM, int CS, bool HALO, int DICT>
 static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     static size_t configured_smem = 0;     // per template instantiation
     static int blocks_per_sm = 0;
@@ -1232,21 +1276,18 @@ static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtr
     static const bool force_halo = getenv("TB_FORCE_HALO") != nullptr;   // measurement aid: exchange code compiled in, inert
     constexpr bool CAN_DICT = !P::strict && TPM == 1;    // build_structure only chooses the dictionary mode then
     if (S->dict && !CAN_DICT) return fail(e, TB_ERR_INVALID, "internal: dictionary records with a kernel that cannot read them");
+    constexpr int D1 = CAN_DICT ? 1 : 0, D2 = CAN_DICT ? 2 : 0;
+    constexpr int CSS = P::strict ? CS_BIG : CS_SMALL, TPS = P::strict ? 1 : TPM;
+    const bool big = P::strict || A.sp.cs == CS_BIG;
     if (A.n_peers > 0 || e->any_ghost || force_halo) {   // partitioned: one thread per mass (choose_tpm), exchange code compiled in
         if (TPM != 1) return fail(e, TB_ERR_INVALID, "internal: halo exchange needs one thread per mass");
-        if (S->dict) {
-            if (A.sp.cs == CS_BIG) return launch_c<P, D, AC, 1, CS_BIG, true, CAN_DICT>(e, S, A, X);
-            return launch_c<P, D, AC, 1, (P::strict ? CS_BIG : CS_SMALL), true, CAN_DICT>(e, S, A, X);
-        }
-        if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, 1, CS_BIG, true, false>(e, S, A, X);
-        return launch_c<P, D, AC, 1, (P::strict ? CS_BIG : CS_SMALL), true, false>(e, S, A, X);
+        if (S->dict && S->dict_split) return big ? launch_c<P, D, AC, 1, CS_BIG, true, D2>(e, S, A, X) : launch_c<P, D, AC, 1, CSS, true, D2>(e, S, A, X);
+        if (S->dict) return big ? launch_c<P, D, AC, 1, CS_BIG, true, D1>(e, S, A, X) : launch_c<P, D, AC, 1, CSS, true, D1>(e, S, A, X);
+        return big ? launch_c<P, D, AC, 1, CS_BIG, true, 0>(e, S, A, X) : launch_c<P, D, AC, 1, CSS, true, 0>(e, S, A, X);
     }
-    if (S->dict) {
-        if (A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG, false, CAN_DICT>(e, S, A, X);
-        return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL), false, CAN_DICT>(e, S, A, X);
-    }
-    if (P::strict || A.sp.cs == CS_BIG) return launch_c<P, D, AC, TPM, CS_BIG, false, false>(e, S, A, X);
-    return launch_c<P, D, AC, (P::strict ? 1 : TPM), (P::strict ? CS_BIG : CS_SMALL), false, false>(e, S, A, X);
+    if (S->dict && S->dict_split) return big ? launch_c<P, D, AC, TPM, CS_BIG, false, D2>(e, S, A, X) : launch_c<P, D, AC, TPS, CSS, false, D2>(e, S, A, X);
+    if (S->dict) return big ? launch_c<P, D, AC, TPM, CS_BIG, false, D1>(e, S, A, X) : launch_c<P, D, AC, TPS, CSS, false, D1>(e, S, A, X);
+    return big ? launch_c<P, D, AC, TPM, CS_BIG, false, 0>(e, S, A, X) : launch_c<P, D, AC, TPS, CSS, false, 0>(e, S, A, X);
 }
 template <class P, int TPM> static int launch_f(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
     bool d = S->has_damping, a = S->has_active;
@@ -1288,14 +1329,14 @@ int tiled_prepare(Engine *e) {
     if ((stale & TS_PARAMS) && !(stale & TS_STRUCT) && S->dict) {
         // the records are shared by parameter class: a parameter upload that splits a class needs new records
         TB_CUDA(e, cudaMemsetAsync(S->dict_bad, 0, sizeof(int), e->stream));
-        dict_check_kernel<<<(unsigned)((e->ns + 255) / 256), 256, 0, e->stream>>>(e->ns, S->class_rep, e->k, e->rest,
+        dict_check_kernel<<<(unsigned)((e->ns + 255) / 256), 256, 0, e->stream>>>(e->ns, S->class_rep, S->dict_split ? nullptr : e->k, e->rest,
                                                                                   S->has_damping ? e->damping : nullptr,
                                                                                   S->has_active ? e->omega : nullptr, S->dict_bad);
         int bad = 0;
         TB_CUDA(e, cudaMemcpyAsync(&bad, S->dict_bad, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
         TB_CUDA(e, cudaStreamSynchronize(e->stream));
         if (bad) {
-            S->dict_failures++;
+            if (S->dict_split) S->split_failures++; else S->dict_failures++;
             TB_TRY(build_structure(e, S, /*keep_slots=*/true));
             e->graph_dirty = true;
             if (!S->supported) return TB_OK;
@@ -1329,7 +1370,8 @@ int tiled_prepare(Engine *e) {
     if (stale & TS_PARAMS)
         tiled_refresh_params<<<(unsigned)S->n_tiles, 128, 0, e->stream>>>(S->blob, S->meta, S->rec_spring, e->k, e->rest, e->damping,
                                                                           e->omega, S->has_damping ? 1 : 0, S->has_active ? 1 : 0, S->omega_tab, S->n_omega,
-                                                                          S->dict ? S->rec_map : nullptr);
+                                                                          S->dict ? S->rec_map : nullptr, S->dict_split ? S->krec_spring : nullptr,
+                                                                          S->dict_split ? S->krec_off : nullptr);
     TB_CUDA(e, cudaGetLastError());
     e->tiled_stale = 0;
     return TB_OK;
@@ -1657,6 +1699,7 @@ int tiled_info(const Engine *e, tb_info *info) {
     info->smem_bytes = (int32_t)S->smem_bytes;
     info->ell_unique_tiles = (int32_t)S->ell_unique_tiles;
     info->dict_records = S->dict ? S->max_dict : 0;
+    info->dict_split_k = (S->dict && S->dict_split) ? 1 : 0;
     // read: blob + own state + halo gathers + halo lists + ELL words + meta; written: own state
     info->tiled_bytes_per_step = (int64_t)S->blob_bytes + 2 * S->n_tiles * STATE_BLOCK * 8 + S->n_halo * (4 + (S->stage_vel ? 48 : 24)) +
                                  S->n_tiles * (int64_t)sizeof(TileMeta) + S->n_ell * 4;
