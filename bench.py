@@ -239,7 +239,8 @@ def run_c5(args, tb, device, flags):
     s = np.arange(ns, dtype=np.uint64)
     factor = 0.9 + 0.2 * (((s * np.uint64(2654435761)) % np.uint64(2 ** 32)) % np.uint64(1000)).astype(np.float64) / 1000.0
     del s
-    k = np.full(ns, 10000.0)
+    k = eng.alloc_pinned((ns,))                       # the optimiser's stiffness array lives in page-locked memory
+    k[:] = 10000.0
     live = np.ones(ns, dtype=bool)
     per = args.inner if args.inner != 200 else 100
     t_sim, dev_ms, wall, spring_steps, removed_total = 0.0, 0.0, 0.0, 0.0, 0

@@ -318,6 +318,10 @@ static int choose_tpm(const Engine *e, int64_t n_tiles) {
 // the rounding of the coordinates), so a tile's ~2,000 records collapse to a few dozen: the blob shrinks from ~35 KB
 // to ~4 KB (less HBM traffic, less shared memory per CTA => more resident CTAs).  class_of[s] = dense class id,
 // rep_of[s] = the first spring of the class.  Returns false (mode off) when there are too many classes.
+#ifndef TB_ACTIVE_STRAIGHT
+#define TB_ACTIVE_STRAIGHT 0    // 1: ACTIVE_* springs (sine-table actuation) also take the straight-line full-degree path;
+                                // measured on B200 (C3): 98.5 vs 110 G spring-steps/s with the chunked loop -> off
+#endif
 #ifndef TB_DICT_CTAS
 #define TB_DICT_CTAS 3
 #endif
@@ -1153,7 +1157,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
             };
             constexpr int FULL = 7;     // chunks of a tile whose masses have 25..28 incident springs (the lattice interior)
-            if (TPM == 1 && !DAMPING && !ACTIVE && nch == FULL && !(A.debug & 2)) {
+            if (TPM == 1 && !DAMPING && (!ACTIVE || TB_ACTIVE_STRAIGHT) && nch == FULL && !(A.debug & 2)) {
                 // the common case as one straight line: no per-chunk branch, so the scheduler can start a chunk's
                 // shared-memory loads while the previous chunk's fp64 chains are still running
                 // A 3-D lattice mass has at most 26 springs: the block's last two rows are then padding, skipped.
