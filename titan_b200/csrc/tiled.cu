@@ -23,6 +23,8 @@
 // ascending-spring-index summation exactly (TB_MATH_STRICT).
 #include "engine.h"
 
+#include <type_traits>
+
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -318,10 +320,6 @@ static int choose_tpm(const Engine *e, int64_t n_tiles) {
 // the rounding of the coordinates), so a tile's ~2,000 records collapse to a few dozen: the blob shrinks from ~35 KB
 // to ~4 KB (less HBM traffic, less shared memory per CTA => more resident CTAs).  class_of[s] = dense class id,
 // rep_of[s] = the first spring of the class.  Returns false (mode off) when there are too many classes.
-#ifndef TB_ACTIVE_STRAIGHT
-#define TB_ACTIVE_STRAIGHT 0    // 1: ACTIVE_* springs (sine-table actuation) also take the straight-line full-degree path;
-                                // measured on B200 (C3): 98.5 vs 110 G spring-steps/s with the chunked loop -> off
-#endif
 #ifndef TB_DICT_CTAS
 #define TB_DICT_CTAS 3
 #endif
@@ -337,17 +335,19 @@ static int param_classes(Engine *e, bool with_k, bool damping, bool active, std:
     TB_CUDA(e, cudaMemcpy(hr.data(), e->rest, ns * 8, cudaMemcpyDeviceToHost));
     if (damping && e->damping) { hd.resize(ns); TB_CUDA(e, cudaMemcpy(hd.data(), e->damping, ns * 8, cudaMemcpyDeviceToHost)); }
     if (active && e->omega) { ho.resize(ns); TB_CUDA(e, cudaMemcpy(ho.data(), e->omega, ns * 8, cudaMemcpyDeviceToHost)); }
-    struct Key { uint64_t a, b, c, d; bool operator==(const Key &o) const { return a == o.a && b == o.b && c == o.c && d == o.d; } };
+    const bool typed = active && e->h_type.size() == ns;    // the actuation type is part of a record (sine-table mode scales per record)
+    struct Key { uint64_t a, b, c, d, t; bool operator==(const Key &o) const { return a == o.a && b == o.b && c == o.c && d == o.d && t == o.t; } };
     struct KeyHash { size_t operator()(const Key &x) const {
         uint64_t h = x.a * 0x9E3779B97F4A7C15ull; h ^= (x.b + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full; h ^= h >> 29;
-        h ^= x.c * 0x165667B19E3779F9ull; h ^= x.d * 0x27D4EB2F165667C5ull; return (size_t)(h ^ (h >> 32)); } };
+        h ^= x.c * 0x165667B19E3779F9ull; h ^= (x.d + x.t) * 0x27D4EB2F165667C5ull; return (size_t)(h ^ (h >> 32)); } };
     std::unordered_map<Key, int32_t, KeyHash> seen;
     std::vector<int32_t> first;    // class id -> first spring
     class_of.resize(ns); rep_of.resize(ns);
-    Key last = {0, 0, 0, 0}; int32_t last_class = -1;
+    Key last = {0, 0, 0, 0, 0}; int32_t last_class = -1;
     auto bits = [](double x) { uint64_t u; memcpy(&u, &x, 8); return u; };
     for (size_t sp = 0; sp < ns; sp++) {
-        Key key = {with_k ? bits(hk[sp]) : 0, bits(hr[sp]), hd.empty() ? 0 : bits(hd[sp]), ho.empty() ? 0 : bits(ho[sp])};
+        Key key = {with_k ? bits(hk[sp]) : 0, bits(hr[sp]), hd.empty() ? 0 : bits(hd[sp]), ho.empty() ? 0 : bits(ho[sp]),
+                   typed ? (uint64_t)(e->h_type[sp] == 2 ? 1 : e->h_type[sp] == 3 ? 2 : 0) : 0};
         int32_t c;
         if (last_class >= 0 && key == last) c = last_class;
         else {
@@ -658,8 +658,9 @@ __global__ void tiled_refresh_mass(uint8_t *blob, const TileMeta *meta, const in
     ((double *)(b + BLOB_M))[t] = i >= 0 ? m_c[i] : 1.0;
 }
 // dictionary mode: do all springs still carry the parameters of their class representative (bit for bit)?
+__device__ __forceinline__ int actuation_code(int type) { return type == TB_ACTIVE_CONTRACT_THEN_EXPAND ? 1 : type == TB_ACTIVE_EXPAND_THEN_CONTRACT ? 2 : 0; }
 __global__ void dict_check_kernel(int64_t ns, const int32_t *class_rep, const double *k, const double *rest, const double *damping,
-                                  const double *omega, int *bad) {
+                                  const double *omega, const int32_t *type, int *bad) {
     const int64_t sp = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (sp >= ns) return;
     const int32_t r = class_rep[sp];
@@ -668,13 +669,14 @@ __global__ void dict_check_kernel(int64_t ns, const int32_t *class_rep, const do
     if (k) same = same && __double_as_longlong(k[sp]) == __double_as_longlong(k[r]);      // null: split dictionary, k is per slot
     if (damping) same = same && __double_as_longlong(damping[sp]) == __double_as_longlong(damping[r]);
     if (omega) same = same && __double_as_longlong(omega[sp]) == __double_as_longlong(omega[r]);
+    if (type) same = same && actuation_code(type[sp]) == actuation_code(type[r]);
     if (!same) *bad = 1;
 }
 // one CTA per tile: the spring records of the tile's blob
 __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const int32_t *rec_spring, const double *k,
                                      const double *rest, const double *damping, const double *omega, int has_damping,
                                      int has_active, const double *omega_tab, int n_omega, const uint8_t *rec_map,
-                                     const int32_t *krec_spring, const uint32_t *krec_off) {
+                                     const int32_t *krec_spring, const uint32_t *krec_off, const int32_t *type) {
     const TileMeta M = meta[blockIdx.x];
     uint8_t *b = blob + (size_t)M.blob_off16 * 16;
     const uint32_t np = (M.n_rec + 1) & ~1u;      // slots per parameter array: k | rest | damping | omega | byte map
@@ -706,10 +708,11 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
         if (has_damping) dmp[r] = (s >= 0 && damping) ? damping[s] : 0.0;
         if (has_active) {
             double w = (s >= 0 && omega) ? omega[s] : 0.0;
-            if (n_omega > 0) {      // table mode: the slot holds the index of omega in the distinct-value table
-                int found = 0;
+            if (n_omega > 0) {      // table mode: the slot holds the index of omega in the distinct-value table (bits 0..15)
+                int found = 0;      // and the record's actuation code (bits 16..17): the step kernel scales rest per record
                 for (int q = 0; q < n_omega; q++) if (__double_as_longlong(omega_tab[q]) == __double_as_longlong(w)) found = q;
-                w = __longlong_as_double((long long)found);
+                const int code = (s >= 0 && type) ? actuation_code(type[s]) : 0;
+                w = __longlong_as_double((long long)(found | (code << 16)));
             }
             omg[r] = w;
         }
@@ -841,13 +844,6 @@ __host__ __device__ inline void chunk_table(int deg, int tpm, uint32_t &cb_packe
 // sin(omega t) of an ACTIVE_* spring: from the CTA's table of distinct frequencies (the record then holds the table
 // index), else evaluated per spring, out of line.  Same argument, same sin(): bit-identical either way.
 template <class P> static __device__ __noinline__ double sin_omega_t(double omega, double t) { return sin(P::mul(omega, t)); }
-// Table mode, branch-free: scale = 1 + c sin(omega t), c = 0 / -0.2 / +0.2 for passive / contract-then-expand /
-// expand-then-contract.  Bit-identical to the reference's 1 -/+ 0.2 sin(.) and to rest * 1.0 for passive springs
-// (IEEE: (-0.2) s == -(0.2 s), 1 + (-x) == 1 - x, 1 + 0 s == 1).
-template <class P> __device__ __forceinline__ double actuation_table(int ty, const double *sintab, const char *slot) {
-    const double c = ty == 1 ? -0.2 : (ty == 2 ? 0.2 : 0.0);
-    return P::add(1.0, P::mul(c, sintab[*reinterpret_cast<const int *>(slot)]));
-}
 // ty: 1 = contract-then-expand (1 - 0.2 sin), 2 = expand-then-contract (1 + 0.2 sin), src/sim.cu:1168-1173
 template <class P> __device__ __forceinline__ double actuation_from_sin(int ty, double sn) {
     return ty == 1 ? P::sub(1.0, P::mul(0.2, sn)) : P::add(1.0, P::mul(0.2, sn));
@@ -1090,6 +1086,20 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
         const uint8_t *mapb = reinterpret_cast<const uint8_t *>(omb + (ACTIVE ? np8 : 0));
         const char *pbx = reinterpret_cast<const char *>(stage + sp.st_pos), *pby = pbx + CS * 8, *pbz = pby + CS * 8;
         const char *vbx = reinterpret_cast<const char *>(stage + sp.st_vel), *vby = vbx + sp.vs * 8, *vbz = vby + sp.vs * 8;
+        // Sine-table actuation: a record carries its actuation code, so rest * (1 -/+ 0.2 sin(omega t)) is evaluated once
+        // per record and tile, in place in the staged copy (the same two operations the reference applies per spring,
+        // src/sim.cu:1168-1173), and the spring loop below is the passive one.
+        const bool act_table = ACTIVE && A.n_omega > 0;
+        if (act_table) {
+            double *rw = reinterpret_cast<double *>(const_cast<char *>(rb));
+            for (int r = tid; r < n_rec; r += NT) {
+                const int slot = *reinterpret_cast<const int *>(omb + 8 * r);
+                const int ty = (slot >> 16) & 3;
+                const double c = ty == 1 ? -0.2 : (ty == 2 ? 0.2 : 0.0);
+                rw[r] = P::mul(rw[r], P::add(1.0, P::mul(c, sintab[slot & 0xffff])));
+            }
+            named_bar_sync(15, NT);
+        }
         V3 pos = {reinterpret_cast<const double *>(pbx)[t], reinterpret_cast<const double *>(pby)[t], reinterpret_cast<const double *>(pbz)[t]};
         V3 vel = {0.0, 0.0, 0.0};
         if (STAGE_VEL || q == 0) vel = V3{reinterpret_cast<const double *>(vbx)[t], reinterpret_cast<const double *>(vby)[t], reinterpret_cast<const double *>(vbz)[t]};
@@ -1113,7 +1123,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                         spr.damping = DAMPING ? *(const double *)(dmb + rco) : 0.0;
                         if (ACTIVE) {
                             const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                            if (A.n_omega > 0) spr.rest_scaled = P::mul(kr.y, actuation_table<P>(ty, sintab, omb + rco));
+                            if (act_table) spr.rest_scaled = kr.y;       // scaled per record above
                             else if (ty) spr.rest_scaled = P::mul(kr.y, actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim)));
                         }
                         if (en & ELL_SIDE) acc3<P>(force, spring_force<P, DAMPING>(po, pos, vo, vel, spr));
@@ -1127,7 +1137,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
             // ELL_CHUNK springs at a time without branches (invalid words evaluate a dummy spring whose
             // coefficient is then forced to zero), so their loads and fp64 chains interleave.
             // force on this mass = (p_me - p_other) * coef whichever endpoint it is (see physics.cuh)
-            auto spring = [&](const uint32_t en) {
+            auto spring_t = [&](const uint32_t en, auto per_spring_sine) {
+                constexpr bool SINE = decltype(per_spring_sine)::value;   // more distinct omegas than the table holds
                 const uint32_t nbo = en & 0xff8u;
                 uint32_t rco = (en >> 13) & 0x7ff8u;       // byte offset of the record's slot in each parameter array
                 const uint32_t kco = rco;                  // DICT == 2: the stiffness stays with the slot
@@ -1140,10 +1151,9 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 kr.y = *(const double *)(rb + rco);
                 kr.x = k_uniform ? (rco ? k_tile : 0.0) : *(const double *)(kb + (DICT == 2 ? kco : rco));   // record 0 (padding words): k = 0
                 double rest = kr.y;
-                if (ACTIVE) {
+                if (ACTIVE && SINE) {
                     const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                    if (A.n_omega > 0) rest = kr.y * actuation_table<P>(ty, sintab, omb + rco);   // branch-free
-                    else if (ty) rest = kr.y * actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim));
+                    if (ty) rest = kr.y * actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim));
                 }
                 const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
                 const double inv = rsqrt_fast(L2);
@@ -1156,8 +1166,10 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 }
                 force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
             };
+            auto spring = [&](const uint32_t en) { spring_t(en, std::false_type{}); };       // passive, or scaled per record
+            auto spring_sine = [&](const uint32_t en) { spring_t(en, std::true_type{}); };
             constexpr int FULL = 7;     // chunks of a tile whose masses have 25..28 incident springs (the lattice interior)
-            if (TPM == 1 && !DAMPING && (!ACTIVE || TB_ACTIVE_STRAIGHT) && nch == FULL && !(A.debug & 2)) {
+            if (TPM == 1 && !DAMPING && (!ACTIVE || act_table) && nch == FULL && !(A.debug & 2)) {
                 // the common case as one straight line: no per-chunk branch, so the scheduler can start a chunk's
                 // shared-memory loads while the previous chunk's fp64 chains are still running
                 // A 3-D lattice mass has at most 26 springs: the block's last two rows are then padding, skipped.
@@ -1174,8 +1186,13 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
 #pragma unroll
                 for (int g = 0; g < EPT / ELL_CHUNK; g++) {
                     if (g < nch && !(A.debug & 2)) {
+                        if (ACTIVE && !act_table) {
 #pragma unroll
-                        for (int u = 0; u < ELL_CHUNK; u++) spring(ell_cur[g * ELL_CHUNK + u]);
+                            for (int u = 0; u < ELL_CHUNK; u++) spring_sine(ell_cur[g * ELL_CHUNK + u]);
+                        } else {
+#pragma unroll
+                            for (int u = 0; u < ELL_CHUNK; u++) spring(ell_cur[g * ELL_CHUNK + u]);
+                        }
                     }
 #pragma unroll
                     for (int u = 0; u < ELL_CHUNK; u++) ell_cur[g * ELL_CHUNK + u] = __ldg(nsrc + (g * ELL_CHUNK + u) * TM);
@@ -1227,6 +1244,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
         }
         __syncwarp();
         long long c4 = (A.prof && !A.prof_lite) ? clock64() : 0;
+        if (act_table) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the staged rest lengths were rewritten in place
         if ((tid & 31) == 0) mbar_arrive(bar_empty(s));     // this warp no longer reads stage s
         if (HALO && i + 1 == nb_my) halo_report(A, (unsigned)nb_my);   // this warp's exports of the step are all issued
         nch = nch_nxt; rows = rows_nxt;
@@ -1335,7 +1353,8 @@ int tiled_prepare(Engine *e) {
         TB_CUDA(e, cudaMemsetAsync(S->dict_bad, 0, sizeof(int), e->stream));
         dict_check_kernel<<<(unsigned)((e->ns + 255) / 256), 256, 0, e->stream>>>(e->ns, S->class_rep, S->dict_split ? nullptr : e->k, e->rest,
                                                                                   S->has_damping ? e->damping : nullptr,
-                                                                                  S->has_active ? e->omega : nullptr, S->dict_bad);
+                                                                                  S->has_active ? e->omega : nullptr,
+                                                                                  S->has_active ? e->type : nullptr, S->dict_bad);
         int bad = 0;
         TB_CUDA(e, cudaMemcpyAsync(&bad, S->dict_bad, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
         TB_CUDA(e, cudaStreamSynchronize(e->stream));
@@ -1375,7 +1394,7 @@ int tiled_prepare(Engine *e) {
         tiled_refresh_params<<<(unsigned)S->n_tiles, 128, 0, e->stream>>>(S->blob, S->meta, S->rec_spring, e->k, e->rest, e->damping,
                                                                           e->omega, S->has_damping ? 1 : 0, S->has_active ? 1 : 0, S->omega_tab, S->n_omega,
                                                                           S->dict ? S->rec_map : nullptr, S->dict_split ? S->krec_spring : nullptr,
-                                                                          S->dict_split ? S->krec_off : nullptr);
+                                                                          S->dict_split ? S->krec_off : nullptr, S->has_active ? e->type : nullptr);
     TB_CUDA(e, cudaGetLastError());
     e->tiled_stale = 0;
     return TB_OK;
