@@ -314,6 +314,7 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--distinct-params", action="store_true",
                     help="give every spring its own k (defeats the dictionary records: one record per spring is streamed)")
+    ap.add_argument("--verlet", action="store_true", help="the reference's VERLET build option instead of its default Euler step")
     ap.add_argument("--no-hint", action="store_true", help="let the engine bisect positions instead of lattice bricks")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
@@ -350,6 +351,8 @@ def main():
         return float(t.item())
 
     flags = (tb.MATH_STRICT if args.strict else tb.MATH_FAST) | (tb.KERNEL_CSR if args.csr else 0)
+    if args.verlet:
+        flags |= tb.INTEGRATOR_VERLET
     if args.workload == "c5":
         run_c5(args, tb, local_rank, flags)
         return

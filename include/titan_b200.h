@@ -55,7 +55,7 @@ typedef enum {
 #define TB_KERNEL_CSR 4u     /* force the generic CSR-gather step kernel (disable the tiled one)     */
 #define TB_INTEGRATOR_VERLET 8u /* the reference's -DVERLET build (CMakeLists.txt:13,90-93; src/sim.cu:1350-1354):    */
                              /* vel += 0.5*(acc + f/m)*dt; acc = f/m; pos += vel*dt + 0.5*acc*dt^2, no speed clamp; */
-                             /* acc is persistent state (zero at upload, like CUDA_MASS(Mass&)); generic kernel only */
+                             /* acc is persistent state (zero at upload, like CUDA_MASS(Mass&)); both step kernels    */
 
 /* SpringType, include/Titan/spring.h:17-18 */
 enum { TB_PASSIVE_SOFT = 0, TB_PASSIVE_STIFF = 1, TB_ACTIVE_CONTRACT_THEN_EXPAND = 2,

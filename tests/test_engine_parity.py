@@ -297,13 +297,16 @@ VERLET = tb.INTEGRATOR_VERLET
 
 @pytest.mark.parametrize("name", ["c1_readme", "contact_friction", "local_constraints", "cube_beam", "magnets"])
 @pytest.mark.parametrize("nsteps", [1, 10, 137])
-def test_verlet_strict_is_bit_identical(name, nsteps):
-    """The reference's VERLET build option (src/sim.cu:1350-1354): acc is persistent state, no clamp."""
+@pytest.mark.parametrize("kernel", [0, tb.KERNEL_CSR])
+def test_verlet_strict_is_bit_identical(name, nsteps, kernel):
+    """The reference's VERLET build option (src/sim.cu:1350-1354): acc is persistent state, no clamp.
+    Both step kernels (tiled: the previous acceleration is read from / stored to the canonical array by the mass's
+    thread; generic)."""
     sc = scenes.SCENARIOS[name]()
     sc.verlet = True
     o = oracle_after(sc, nsteps)
-    g = run_engine(sc, nsteps, tb.MATH_STRICT | VERLET, chunks=2 if nsteps > 10 else 1)
-    assert g["info"]["kernel"] == 0
+    g = run_engine(sc, nsteps, tb.MATH_STRICT | VERLET | kernel, chunks=2 if nsteps > 10 else 1)
+    assert g["info"]["kernel"] == (0 if (kernel or name == "magnets") else 1)
     for f in FIELDS:
         assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (name, f, rel(g[f], getattr(o, f)))
     assert same_bits(g["T"], o.T)
@@ -319,6 +322,19 @@ def test_verlet_fast_within_tolerance(name):
         for f in ("pos", "vel"):
             assert rel(g[f], getattr(o, f)) <= tol, (name, nsteps, f, rel(g[f], getattr(o, f)))
         assert rel(g["acc"], o.acc) <= 1e3 * max(tol, 1e-11), (name, nsteps, rel(g["acc"], o.acc))
+
+
+def test_verlet_tiled_dictionary_kernel_within_tolerance(monkeypatch):
+    """Verlet on the configuration bench.py runs (fast arithmetic, one thread per mass, dictionary records)."""
+    monkeypatch.setenv("TB_TPM", "1")               # one thread per mass also for this small scene
+    sc = scenes.c2_lattice(24)
+    sc.verlet = True
+    o = oracle_after(sc, 100)
+    g = run_engine(sc, 100, tb.MATH_FAST | VERLET)
+    assert g["info"]["kernel"] == 1 and g["info"]["dict_records"] > 0
+    for f in ("pos", "vel"):
+        assert rel(g[f], getattr(o, f)) <= 1e-9, (f, rel(g[f], getattr(o, f)))
+    assert rel(g["acc"], o.acc) <= 1e-8 * 1e3
 
 
 def test_verlet_state_upload_resets_acceleration():

@@ -707,9 +707,10 @@ __global__ void advance_rest_kernel(double *rest, const int32_t *type, const dou
     else { if (x > l_min[s]) rest[s] = __dsub_rn(x, __dmul_rn(rate[s], dt)); }
 }
 
-// the tiled kernel covers the default integrator without magnetic masses; everything else runs on the generic kernel
+// the tiled kernel covers both integrators; scenes with magnetic masses run on the generic kernel (the occupancy-grid
+// pass reads canonical positions)
 static bool use_tiled(Engine *e) {
-    return !(e->flags & (TB_KERNEL_CSR | TB_INTEGRATOR_VERLET)) && !e->any_magnet && tiled_supported(e);
+    return !(e->flags & TB_KERNEL_CSR) && !e->any_magnet && tiled_supported(e);
 }
 
 // enqueue ONE step (capturable): [advance_rest] + [occupancy grid + magnet pass] + fused spring-gather/mass-update kernel

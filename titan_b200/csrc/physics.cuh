@@ -222,13 +222,11 @@ template <class P> static __device__ __noinline__ V3 drag_force(V3 vel, V3 force
     return force;
 }
 
-// Everything massForcesAndUpdate does after the spring forces are known (src/sim.cu:1299-1365).
-// force: spring-force sum on entry.  Returns new pos/vel through the references; acc_out = force/m.
-// VERLET selects the reference's -DVERLET branch (src/sim.cu:1350-1354) instead of the default semi-implicit Euler
-// one (:1355-1362): acc_out then carries the mass's PREVIOUS acceleration on entry, and there is no speed clamp.
-template <class P, bool VERLET = false>
-__device__ __forceinline__ void mass_update(const Globals &G, const MassExtras &X, int64_t i, bool has_local,
-                                            double m, V3 &pos, V3 &vel, V3 force, V3 &acc_out) {
+// Everything massForcesAndUpdate adds to the spring-force sum before it integrates (src/sim.cu:1299-1332): gravity,
+// external force, global planes and balls, local constraints (may also change vel), drag.
+template <class P>
+__device__ __forceinline__ V3 mass_forces(const Globals &G, const MassExtras &X, int64_t i, bool has_local, double m,
+                                          V3 &pos, V3 &vel, V3 force) {
     acc3<P>(force, scale3<P>(V3{G.g[0], G.g[1], G.g[2]}, m));                       // :1299
     if (X.ext) acc3<P>(force, V3{X.ext[i], X.ext[X.nm + i], X.ext[2 * X.nm + i]});   // :1300
     else if (P::strict) acc3<P>(force, V3{0.0, 0.0, 0.0});
@@ -244,32 +242,50 @@ __device__ __forceinline__ void mass_update(const Globals &G, const MassExtras &
     }
 
     if (P::strict || X.drag) force = drag_force<P>(vel, force, X.drag ? X.drag[i] : 0);   // :1329-1332
+    return force;
+}
 
-    if (VERLET) {
-        // vel += 0.5 * (acc + force / m) * dt;  acc = force / m;  pos += vel * dt + 0.5 * acc * pow(dt, 2)
-        V3 a = P::strict ? div3<P>(force, m) : scale3<P>(force, rcp_fast(m));
-        V3 half = scale3<P>(V3{P::add(acc_out.x, a.x), P::add(acc_out.y, a.y), P::add(acc_out.z, a.z)}, 0.5);
-        acc3<P>(vel, scale3<P>(half, G.dt));
-        acc_out = a;
-        V3 step = scale3<P>(vel, G.dt);
-        acc3<P>(step, scale3<P>(scale3<P>(a, 0.5), P::mul(G.dt, G.dt)));
-        acc3<P>(pos, step);
-    } else if (P::strict) {                                                         // :1356-1361
+// default integrator (src/sim.cu:1355-1362): acc = f/m; vel += acc dt; speed clamp; pos += vel dt
+template <class P>
+__device__ __forceinline__ void euler_tail(double dt, double m, const V3 &force, V3 &pos, V3 &vel, V3 &acc_out) {
+    if (P::strict) {                                                                // :1356-1361
         acc_out = div3<P>(force, m);
-        vel = V3{P::add(vel.x, P::mul(acc_out.x, G.dt)), P::add(vel.y, P::mul(acc_out.y, G.dt)),
-                 P::add(vel.z, P::mul(acc_out.z, G.dt))};
+        vel = V3{P::add(vel.x, P::mul(acc_out.x, dt)), P::add(vel.y, P::mul(acc_out.y, dt)), P::add(vel.z, P::mul(acc_out.z, dt))};
         double vn = norm3<P>(vel);
         if (vn > 1) vel = div3<P>(vel, vn);                                         // speed clamp :1359-1360
-        pos = V3{P::add(pos.x, P::mul(vel.x, G.dt)), P::add(pos.y, P::mul(vel.y, G.dt)),
-                 P::add(pos.z, P::mul(vel.z, G.dt))};
+        pos = V3{P::add(pos.x, P::mul(vel.x, dt)), P::add(pos.y, P::mul(vel.y, dt)), P::add(pos.z, P::mul(vel.z, dt))};
     } else {
         double rm = rcp_fast(m);
         acc_out = V3{force.x * rm, force.y * rm, force.z * rm};
-        vel = V3{vel.x + acc_out.x * G.dt, vel.y + acc_out.y * G.dt, vel.z + acc_out.z * G.dt};
+        vel = V3{vel.x + acc_out.x * dt, vel.y + acc_out.y * dt, vel.z + acc_out.z * dt};
         double v2 = vel.x * vel.x + vel.y * vel.y + vel.z * vel.z;
         if (v2 > 1.0) { double r = rsqrt(v2); vel = V3{vel.x * r, vel.y * r, vel.z * r}; }
-        pos = V3{pos.x + vel.x * G.dt, pos.y + vel.y * G.dt, pos.z + vel.z * G.dt};
+        pos = V3{pos.x + vel.x * dt, pos.y + vel.y * dt, pos.z + vel.z * dt};
     }
+}
+
+// the reference's -DVERLET branch (src/sim.cu:1350-1354): vel += 0.5 * (acc + force / m) * dt;  acc = force / m;
+// pos += vel * dt + 0.5 * acc * pow(dt, 2).  acc carries the previous step's acceleration in, the new one out.
+template <class P>
+__device__ __forceinline__ void verlet_tail(double dt, double m, const V3 &force, V3 &pos, V3 &vel, V3 &acc) {
+    V3 a = P::strict ? div3<P>(force, m) : scale3<P>(force, rcp_fast(m));
+    V3 half = scale3<P>(V3{P::add(acc.x, a.x), P::add(acc.y, a.y), P::add(acc.z, a.z)}, 0.5);
+    acc3<P>(vel, scale3<P>(half, dt));
+    acc = a;
+    V3 step = scale3<P>(vel, dt);
+    acc3<P>(step, scale3<P>(scale3<P>(a, 0.5), P::mul(dt, dt)));
+    acc3<P>(pos, step);
+}
+
+// Everything massForcesAndUpdate does after the spring forces are known (src/sim.cu:1299-1365).
+// force: spring-force sum on entry.  Returns new pos/vel through the references; acc_out = force/m.
+// VERLET: acc_out carries the mass's PREVIOUS acceleration on entry, and there is no speed clamp.
+template <class P, bool VERLET = false>
+__device__ __forceinline__ void mass_update(const Globals &G, const MassExtras &X, int64_t i, bool has_local,
+                                            double m, V3 &pos, V3 &vel, V3 force, V3 &acc_out) {
+    force = mass_forces<P>(G, X, i, has_local, m, pos, vel, force);
+    if (VERLET) verlet_tail<P>(G.dt, m, force, pos, vel, acc_out);
+    else euler_tail<P>(G.dt, m, force, pos, vel, acc_out);
 }
 
 }  // namespace tb

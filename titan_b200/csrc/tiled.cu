@@ -796,7 +796,7 @@ constexpr long long HALO_TIMEOUT_CLOCKS = 1ll << 32;   // ~2 s: a peer that neve
 // ---------------------------------------------------------------- the step kernel -------------------------
 struct TiledArgs {
     int32_t n_tiles;
-    int32_t write_acc;
+    int32_t write_acc;               // 1: store acc (canonical array); 2: Verlet -- acc is state, read and stored every step
     int prof_lite;                   // TB_PROFILE=2: only the barrier waits and the loop totals
     unsigned long long *prof;        // TB_PROFILE=1: per-phase clock64 sums (0 wait full, 1 springs, 2 partial-sum handoff, 3 mass update, 4 producer wait empty, 5 producer wait halo list, 6 producer issue, 7 ell-copy wait)
     int32_t l2_hint;                 // 1: stream the spring-record blobs through L2 with evict_first
@@ -1227,7 +1227,13 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 const bool extras = X.ext || X.drag || (fl & F_LOCAL) || A.write_acc;
                 const int64_t i_api = extras ? A.slot_to_api[tile * TM + t] : 0;
                 V3 acc;
-                mass_update<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force, acc);
+                force = mass_forces<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force);
+                if (A.write_acc == 2) {     // the reference's VERLET build: the previous acceleration is state, kept in the
+                    acc = V3{A.acc[i_api], A.acc[X.nm + i_api], A.acc[2 * X.nm + i_api]};   // canonical array by this thread
+                    verlet_tail<P>(G.dt, mass, force, pos, vel, acc);
+                } else {
+                    euler_tail<P>(G.dt, mass, force, pos, vel, acc);
+                }
                 if (A.write_acc) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
             }
             if (!HALO || !(fl & F_GHOST)) {     // a ghost's slot belongs to the peer that owns the mass
@@ -1405,7 +1411,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     if (!S || !S->supported) return fail(e, TB_ERR_INVALID, "tiled step requested without a tiled layout");
     TiledArgs A;
     A.n_tiles = (int32_t)S->n_active;
-    A.write_acc = write_acc ? 1 : 0;
+    A.write_acc = (e->flags & TB_INTEGRATOR_VERLET) ? 2 : (write_acc ? 1 : 0);
     A.prof = nullptr; A.prof_lite = 0;
     if (getenv("TB_PROFILE")) {
         A.prof = g_prof_dev; g_prof_launches++;
