@@ -195,6 +195,13 @@ def brick_hint(nx, ny, nz, tile=128, base=0, block=None):
     if block is None:
         block = int(os.environ.get("TB_TILE_BLOCK", "8"))
     layers = brick_layers(nx, ny, nz, tile) if os.environ.get("TB_BRICK_LAYERS", "1") != "0" else None
+    spec = os.environ.get("TB_BRICK_SPEC")      # experiment knob: "8x4x4*10,5x5x5*4" = layers along i, in this order
+    if spec:
+        layers = []
+        for part in spec.split(","):
+            dims, _, rep = part.partition("*")
+            layers += [tuple(int(v) for v in dims.split("x"))] * int(rep or 1)
+        assert sum(l[0] for l in layers) == nx, "TB_BRICK_SPEC does not add up to nx"
     if not layers or len(set(layers)) == 1:
         return (_brick_ids(nx, ny, nz, brick_dims(nx, ny, nz, tile), block).reshape(-1) + base).astype(np.int32)
     ids = np.empty((nx, ny, nz), dtype=np.int64)
