@@ -204,6 +204,13 @@ TB_API int tb_get_info(tb_engine *e, tb_info *info);
 /* headless position export, fp64 -> packed fp32 xyz (updateVertices, src/sim.cu:1944-1952); out is a
  * DEVICE pointer to nm*3 floats owned by the engine, valid until the next call. */
 TB_API int tb_export_positions_f32_dev(tb_engine *e, const float **out_dev);
+/* the matching line list (updateIndices, src/sim.cu:1957-1980): 2*ns uint32 (left, right) mass indices in spring order;
+ * springs the step skips (null or invalid endpoint, tombstones) are the degenerate line (0, 0).  DEVICE pointer owned by
+ * the engine, valid until the next call. */
+TB_API int tb_export_indices_dev(tb_engine *e, const uint32_t **out_dev);
+/* copy `bytes` from a device pointer handed out by this engine (the two exports above) into host memory: what a headless
+ * consumer uses in place of the reference's OpenGL buffer mapping (src/sim.cu:1982-2043) */
+TB_API int tb_read_device(tb_engine *e, void *dst_host, const void *src_dev, size_t bytes);
 
 /* page-locked host memory for upload/download buffers (the reference stages through pageable `new[]`
  * arrays, src/sim.cu:948-962,1099-1101); owned by the engine, released by tb_destroy */

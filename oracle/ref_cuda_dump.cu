@@ -211,6 +211,20 @@ static int do_bench(const std::string &cfg, long steps) {
         double side = 0.1 * (n - 1);
         sim.createLattice(Vec(0, 0, side / 2 - 0.001), Vec(side, side, side), n, n, n);
         sim.createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
+    } else if (cfg == "c3_64") {
+        /* SURVEY.md 8(d) C3 restricted to what one Titan Simulation can hold: 64 actuated 10^3 robots on an 8 x 8 grid
+         * (1.2 m pitch, inside the +-5.12 m occupancy grid), spring s of each robot passive / contract-then-expand /
+         * expand-then-contract by s % 3, omega = 4 pi, one frictional plane */
+        for (int r = 0; r < 64; r++) {
+            Lattice *l = sim.createLattice(Vec(-4.2 + 1.2 * (r % 8), -4.2 + 1.2 * (r / 8), 0.55), Vec(0.9, 0.9, 0.9), 10, 10, 10);
+            int n = 0;
+            for (Spring *s : l->springs) {
+                s->_type = (n % 3 == 1) ? ACTIVE_CONTRACT_THEN_EXPAND : (n % 3 == 2) ? ACTIVE_EXPAND_THEN_CONTRACT : PASSIVE_SOFT;
+                s->_omega = 4 * 3.14159265358979323846;
+                n++;
+            }
+        }
+        sim.createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
     } else {
         fprintf(stderr, "unknown bench config %s\n", cfg.c_str());
         return 2;
@@ -243,6 +257,6 @@ int main(int argc, char **argv) {
     if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argv[2], argv[3]);
     if (argc >= 4 && !strcmp(argv[1], "init")) return do_dump(argv[2], argv[3], true);
     if (argc >= 4 && !strcmp(argv[1], "bench")) return do_bench(argv[2], atol(argv[3]));
-    fprintf(stderr, "usage: %s dump <scenario> <out.bin> | bench <c1|c2|latticeN> <steps>\n", argv[0]);
+    fprintf(stderr, "usage: %s dump <scenario> <out.bin> | bench <c1|c2|c3_64|latticeN> <steps>\n", argv[0]);
     return 2;
 }

@@ -292,6 +292,29 @@ def test_plain_masses_feel_a_magnetic_neighbour():
     assert not same_bits(q.vel, o.vel)                     # the pass does act on this scene
 
 
+def test_headless_export_buffers():
+    """Row N3: fp32 packed xyz + line list in device memory (updateVertices / updateIndices, src/sim.cu:1944-1980)
+    without a graphics API; also after steps on the tiled kernel (state is brought back to API order first)."""
+    sc = scenes.contact_friction()
+    sc.valid[7] = 0
+    sc.left[3] = -1
+    eng = tb.Engine(0, tb.MATH_FAST)
+    scenes.upload(eng, sc)
+    eng.run(25, 0.0)
+    gone = np.array([10, 11], dtype=np.int32)
+    eng.remove_springs(gone)
+    st = eng.get_mass_state()
+    xyz = eng.read_device(eng.export_positions_f32_dev(), (sc.nm, 3), np.float32)
+    assert (xyz == st["pos"].astype(np.float32)).all()
+    idx = eng.read_device(eng.export_indices_dev(), (sc.ns, 2), np.uint32)
+    want = np.stack([sc.left, sc.right], axis=1).astype(np.int64)
+    skip = (sc.left < 0) | (sc.right < 0) | (sc.left == 7) | (sc.right == 7)
+    skip[gone] = True
+    want[skip] = 0
+    assert (idx == want.astype(np.uint32)).all()
+    eng.close()
+
+
 VERLET = tb.INTEGRATOR_VERLET
 
 

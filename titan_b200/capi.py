@@ -20,7 +20,7 @@ EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_l
            "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
            "tb_get_spring_rest", "tb_remove_springs", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
            "tb_run_async", "tb_sync", "tb_steps_done", "tb_last_run_ms", "tb_get_info",
-           "tb_export_positions_f32_dev", "tb_alloc_host", "tb_halo_set_ghosts", "tb_halo_prepare",
+           "tb_export_positions_f32_dev", "tb_export_indices_dev", "tb_read_device", "tb_alloc_host", "tb_halo_set_ghosts", "tb_halo_prepare",
            "tb_halo_state_offsets", "tb_halo_connect", "tb_halo_set_exports", "tb_halo_push_now"]
 MAX_PEERS = 8
 HALO_HANDLE_BYTES = 320
@@ -89,6 +89,8 @@ def lib():
         L.tb_last_run_ms.argtypes = [_vp, C.POINTER(C.c_double)]
         L.tb_get_info.argtypes = [_vp, C.POINTER(Info)]
         L.tb_export_positions_f32_dev.argtypes = [_vp, C.POINTER(_vp)]
+        L.tb_export_indices_dev.argtypes = [_vp, C.POINTER(_vp)]
+        L.tb_read_device.argtypes = [_vp, _vp, _vp, C.c_size_t]
         L.tb_alloc_host.argtypes = [_vp, C.c_size_t, C.POINTER(_vp)]
         L.tb_halo_set_ghosts.argtypes = [_vp, C.c_int64, _vp]
         L.tb_halo_prepare.argtypes = [_vp, _vp]
@@ -307,3 +309,14 @@ class Engine:
         p = _vp()
         self._ck(self._L.tb_export_positions_f32_dev(self._h, C.byref(p)))
         return p.value
+
+    def export_indices_dev(self):
+        p = _vp()
+        self._ck(self._L.tb_export_indices_dev(self._h, C.byref(p)))
+        return p.value
+
+    def read_device(self, dev_ptr, shape, dtype):
+        """Host copy of a device buffer the engine handed out (tb_read_device)."""
+        out = np.empty(shape, dtype=dtype)
+        self._ck(self._L.tb_read_device(self._h, out.ctypes.data_as(_vp), _vp(dev_ptr), C.c_size_t(out.nbytes)))
+        return out

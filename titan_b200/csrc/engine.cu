@@ -121,6 +121,19 @@ __global__ void export_f32_kernel(float *dst, const double *pos, int64_t nm) {
     dst[3 * i] = (float)pos[i]; dst[3 * i + 1] = (float)pos[nm + i]; dst[3 * i + 2] = (float)pos[2 * nm + i];
 }
 
+// updateIndices, src/sim.cu:1957-1980: the line list (left, right) per spring; skipped springs (null / invalid endpoint,
+// here also tombstones) become the degenerate line (0, 0).  The reference searches the mass table per spring
+// (O(Ns * Nm)); here the endpoints ARE indices.
+__global__ void export_indices_kernel(uint32_t *dst, const int32_t *left, const int32_t *right, const uint8_t *flags,
+                                      const uint8_t *removed, int64_t ns) {
+    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= ns) return;
+    int l = left[s], r = right[s];
+    bool skip = l < 0 || r < 0 || !(flags[l] & F_VALID) || !(flags[r] & F_VALID) || (removed && removed[s]);
+    dst[2 * s] = skip ? 0u : (uint32_t)l;
+    dst[2 * s + 1] = skip ? 0u : (uint32_t)r;
+}
+
 static inline unsigned blocks_for(int64_t n, int t = 256) { return (unsigned)std::max<int64_t>(1, (n + t - 1) / t); }
 
 template <class T> static int fill(Engine *e, T *dst, T v, int64_t n) {
@@ -206,6 +219,7 @@ static void free_all(Engine *e) {
     F(e->k, s1); F(e->rest, s1); F(e->damping, s1); F(e->omega, s1); F(e->l_max, s1); F(e->l_min, s1); F(e->rate, s1);
     F(e->row_ptr, (size_t)(e->nm + 1) * 4); F(e->adj, (size_t)e->ns * 8);
     F(e->export_f32, (size_t)e->nm * 12);
+    F(e->export_idx, (size_t)e->ns * 8);
     F(e->removed_dev, (size_t)e->ns);
     magnet_free(e);
     e->h_removed.clear(); e->n_removed = 0;
@@ -843,6 +857,25 @@ int tb_export_positions_f32_dev(tb_engine *e, const float **out_dev) {
     TB_CUDA(e, cudaGetLastError());
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
     *out_dev = e->export_f32;
+    return TB_OK;
+}
+
+int tb_export_indices_dev(tb_engine *e, const uint32_t **out_dev) {
+    E_CHECK(e);
+    if (!out_dev || e->ns == 0) return fail(e, TB_ERR_INVALID, "tb_export_indices_dev: nothing to export");
+    if (!e->export_idx) TB_TRY(dev_alloc(e, &e->export_idx, (size_t)e->ns * 2));
+    export_indices_kernel<<<blocks_for(e->ns), 256, 0, e->stream>>>(e->export_idx, e->left, e->right, e->mflags, e->removed_dev, e->ns);
+    TB_CUDA(e, cudaGetLastError());
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    *out_dev = e->export_idx;
+    return TB_OK;
+}
+
+int tb_read_device(tb_engine *e, void *dst_host, const void *src_dev, size_t bytes) {
+    E_CHECK(e);
+    if (!dst_host || !src_dev) return fail(e, TB_ERR_INVALID, "tb_read_device: null pointer");
+    TB_CUDA(e, cudaMemcpyAsync(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost, e->stream));
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
     return TB_OK;
 }
 

@@ -55,6 +55,7 @@ struct Engine {
     double *t_dev = nullptr;       // [2] simulation time, ping-pong with the step parity
     long long *step_dev = nullptr; // [2] steps completed, ping-pong (halo exchange sequence number)
     float *export_f32 = nullptr;
+    uint32_t *export_idx = nullptr;   // [2 * ns] line list of the last tb_export_indices_dev
     // magnet / occupancy-grid pass (magnet.cu), allocated with the first magnetic mass: per-mass rad, shell
     // stiffness, max_mag_force, mag_scale_factor (include/Titan/mass.h:97-100), the pass's output (uploaded one-shot
     // external force + pair forces, [3][nm]) and the cell lists
