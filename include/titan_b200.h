@@ -53,6 +53,8 @@ typedef enum {
                              /* to oracle/titan_oracle.c (passive springs; sin() may differ by 1ulp) */
 #define TB_NO_GRAPH 2u       /* launch every step individually instead of CUDA-Graph batches         */
 #define TB_KERNEL_CSR 4u     /* force the generic CSR-gather step kernel (disable the tiled one)     */
+#define TB_NO_RESIDENT 16u   /* never use the resident small-system kernel (<= 8 tiles: one cluster launch runs all steps   */
+                             /* of a tb_run_async with the state in shared memory); stream every step instead           */
 #define TB_INTEGRATOR_VERLET 8u /* the reference's -DVERLET build (CMakeLists.txt:13,90-93; src/sim.cu:1350-1354):    */
                              /* vel += 0.5*(acc + f/m)*dt; acc = f/m; pos += vel*dt + 0.5*acc*dt^2, no speed clamp; */
                              /* acc is persistent state (zero at upload, like CUDA_MASS(Mass&)); both step kernels    */

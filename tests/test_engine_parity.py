@@ -52,12 +52,18 @@ def oracle_after(sc, nsteps):
     return o
 
 
+# Small scenes (<= 8 tiles) run on the resident cluster kernel (all steps of a run in one launch, state in shared memory)
+# unless NO_RESIDENT asks for the streaming kernel: both are checked.
+KERNELS = [0, tb.NO_RESIDENT]
+
+
 @pytest.mark.parametrize("name", ["c1_readme", "contact_friction", "local_constraints", "cube_beam"])
 @pytest.mark.parametrize("nsteps", [1, 10, 137])
-def test_strict_is_bit_identical(name, nsteps):
+@pytest.mark.parametrize("kern", KERNELS)
+def test_strict_is_bit_identical(name, nsteps, kern):
     sc = scenes.SCENARIOS[name]()
     o = oracle_after(sc, nsteps)
-    g = run_engine(sc, nsteps, tb.MATH_STRICT)
+    g = run_engine(sc, nsteps, tb.MATH_STRICT | kern)
     for f in FIELDS:
         assert rel(g[f], getattr(o, f)) == 0.0, (name, f, rel(g[f], getattr(o, f)))
         assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (name, f)  # "+ 0.0" folds -0 into +0
@@ -77,11 +83,12 @@ def test_strict_actuated(nsteps):
 
 
 @pytest.mark.parametrize("name", sorted(scenes.SCENARIOS))
-def test_fast_within_tolerance(name):
+@pytest.mark.parametrize("kern", KERNELS)
+def test_fast_within_tolerance(name, kern):
     sc = scenes.SCENARIOS[name]()
     for nsteps, tol in ((1, 1e-12), (100, 1e-9)):
         o = oracle_after(sc, nsteps)
-        g = run_engine(sc, nsteps, tb.MATH_FAST)
+        g = run_engine(sc, nsteps, tb.MATH_FAST | kern)
         for f in ("pos", "vel"):
             assert rel(g[f], getattr(o, f)) <= tol, (name, nsteps, f, rel(g[f], getattr(o, f)))
         # acc = force/m amplifies the cancellation in k*(rest - L): its rounding noise lives on the force
@@ -90,7 +97,8 @@ def test_fast_within_tolerance(name):
         assert same_bits(g["T"], o.T)
 
 
-@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.NO_GRAPH, tb.MATH_STRICT | tb.KERNEL_CSR])
+@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.NO_GRAPH, tb.MATH_STRICT | tb.KERNEL_CSR,
+                                   tb.MATH_STRICT | tb.NO_RESIDENT, tb.MATH_STRICT | tb.NO_RESIDENT | tb.NO_GRAPH])
 def test_graph_batches_and_chunking_do_not_change_results(flags):
     sc = scenes.contact_friction()
     ref = run_engine(sc, 237, tb.MATH_STRICT | tb.NO_GRAPH | tb.KERNEL_CSR)
@@ -320,7 +328,7 @@ VERLET = tb.INTEGRATOR_VERLET
 
 @pytest.mark.parametrize("name", ["c1_readme", "contact_friction", "local_constraints", "cube_beam", "magnets"])
 @pytest.mark.parametrize("nsteps", [1, 10, 137])
-@pytest.mark.parametrize("kernel", [0, tb.KERNEL_CSR])
+@pytest.mark.parametrize("kernel", [0, tb.KERNEL_CSR, tb.NO_RESIDENT])
 def test_verlet_strict_is_bit_identical(name, nsteps, kernel):
     """The reference's VERLET build option (src/sim.cu:1350-1354): acc is persistent state, no clamp.
     Both step kernels (tiled: the previous acceleration is read from / stored to the canonical array by the mass's
@@ -329,7 +337,7 @@ def test_verlet_strict_is_bit_identical(name, nsteps, kernel):
     sc.verlet = True
     o = oracle_after(sc, nsteps)
     g = run_engine(sc, nsteps, tb.MATH_STRICT | VERLET | kernel, chunks=2 if nsteps > 10 else 1)
-    assert g["info"]["kernel"] == (0 if (kernel or name == "magnets") else 1)
+    assert g["info"]["kernel"] == (0 if (kernel == tb.KERNEL_CSR or name == "magnets") else 1)
     for f in FIELDS:
         assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (name, f, rel(g[f], getattr(o, f)))
     assert same_bits(g["T"], o.T)
@@ -345,6 +353,24 @@ def test_verlet_fast_within_tolerance(name):
         for f in ("pos", "vel"):
             assert rel(g[f], getattr(o, f)) <= tol, (name, nsteps, f, rel(g[f], getattr(o, f)))
         assert rel(g["acc"], o.acc) <= 1e3 * max(tol, 1e-11), (name, nsteps, rel(g["acc"], o.acc))
+
+
+@pytest.mark.parametrize("nsteps", [1, 2, 3, 50, 51])
+def test_resident_kernel_equals_streaming_kernel_bitwise(nsteps):
+    """Odd and even step counts (the resident kernel leaves the state in either ping-pong buffer), chunked runs, an
+    uploaded one-shot external force (consumed by one streaming step first), actuated + damped springs."""
+    sc = scenes.actuated()
+    sc.type[sc.type >= 4] = 0                    # ACTUATED_* springs run on the generic kernel
+    sc.ext[::5] = (0.3, -0.2, 0.1)
+    a = run_engine(sc, nsteps, tb.MATH_STRICT, chunks=2 if nsteps > 3 else 1)
+    b = run_engine(sc, nsteps, tb.MATH_STRICT | tb.NO_RESIDENT, chunks=2 if nsteps > 3 else 1)
+    assert a["info"]["kernel"] == 1 and b["info"]["kernel"] == 1
+    for f in FIELDS + ("T", "extern_force"):
+        assert same_bits(a[f] + 0.0, b[f] + 0.0), f
+    fa = run_engine(sc, nsteps, tb.MATH_FAST)
+    fb = run_engine(sc, nsteps, tb.MATH_FAST | tb.NO_RESIDENT)
+    for f in ("pos", "vel"):
+        assert rel(fa[f], fb[f]) <= 1e-12, f
 
 
 def test_verlet_tiled_dictionary_kernel_within_tolerance(monkeypatch):
@@ -429,7 +455,7 @@ def test_dictionary_records_are_bit_identical_to_plain_records(name, monkeypatch
     engines = []
     for dict_on in ("0", "1"):
         monkeypatch.setenv("TB_DICT", dict_on)      # read when the layout is built, i.e. at the first run
-        eng = tb.Engine(0, tb.MATH_FAST)
+        eng = tb.Engine(0, tb.MATH_FAST | tb.NO_RESIDENT)   # the streaming kernel also for the small scenes
         scenes.upload(eng, sc)
         eng.run(60, 0.0)
         engines.append(eng)

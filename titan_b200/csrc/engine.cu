@@ -787,6 +787,14 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
         e->ext_pending = false;
         left_steps--;
     }
+    // Small systems (<= 8 tiles): every remaining step in one cluster launch, state resident in shared memory
+    while (left_steps > 0 && use_tiled(e) && tiled_resident_ok(e)) {
+        const int chunk = (int)std::min<int64_t>(left_steps, (int64_t)1 << 20);
+        TB_TRY(launch_tiled_resident(e, chunk, chunk == left_steps));
+        e->launches++;
+        e->cur ^= (chunk & 1);
+        left_steps -= chunk;
+    }
     bool graphs = !(e->flags & TB_NO_GRAPH);
     if (graphs && left_steps - 1 >= GRAPH_STEPS) {
         if (e->graph_dirty) {

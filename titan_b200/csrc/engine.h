@@ -135,6 +135,8 @@ void tiled_destroy(Engine *e);
 bool tiled_supported(const Engine *e);
 int tiled_info(const Engine *e, tb_info *info);
 bool tiled_halo_connected(const Engine *e);
+bool tiled_resident_ok(const Engine *e);         // <= 8 tiles, no peers: all steps of a run in one cluster launch
+int launch_tiled_resident(Engine *e, int nsteps, bool write_acc);
 int tiled_halo_check(Engine *e);                 // after a sync: did a halo wait time out?
 
 }  // namespace tb

@@ -23,6 +23,7 @@
 // ascending-spring-index summation exactly (TB_MATH_STRICT).
 #include "engine.h"
 
+#include <cooperative_groups.h>
 #include <type_traits>
 
 #include <algorithm>
@@ -1513,6 +1514,273 @@ static void halo_release(Engine *e, TiledState *S) {
     S->n_exp_tab = S->n_exp_flat = 0;
     S->n_peers = 0;
     S->halo_connected = false;
+}
+
+
+// ---------------------------------------------------------------- resident small-system kernel -------------
+// Systems of at most 8 tiles (<= 1,024 masses: the README example, a single soft robot) are bound by launch latency,
+// not bandwidth: one step of the streaming kernel above costs ~6 us of which almost nothing is work.  This kernel
+// runs ALL requested steps in ONE launch: one thread-block cluster, one CTA per tile, the state resident in shared
+// memory for the whole run.  Per step every CTA copies the foreign masses its springs reach out of its neighbours'
+// shared memory (distributed shared memory, ld.shared::cluster), evaluates its masses from local shared memory exactly
+// like the streaming kernel (same ELL words, same records, same arithmetic, one thread per mass in ascending spring
+// order -- also the oracle's order), writes the other state buffer and meets the cluster at ONE barrier.  The run loop
+// of the reference (src/sim.cu:1800-1811: springs with t = T, masses, T += dt) becomes the loop of this kernel; HBM is
+// touched at the start and at the end.
+struct ResidentArgs {
+    int32_t nsteps, cs, vs, stage_vel, dict_mode, verlet, write_acc, n_omega;
+    int32_t off_halo, off_hptr, off_sintab, off_pos, off_vel, total;     // shared-memory byte offsets (the blob sits at 0)
+    const double *st_in; double *st_out;
+    const uint8_t *blob; const int32_t *slot_to_api, *halo; const uint32_t *ell; const TileMeta *meta;
+    double *acc; const double *t_in; double *t_out; const long long *step_in; long long *step_out; const double *omega_tab;
+};
+constexpr int RES_ROWS = MAX_DEG;      // ELL words a thread keeps in registers
+constexpr int RES_MAX_TILES = 8;       // portable thread-block cluster size
+
+template <class P, bool DAMPING, bool ACTIVE>
+__global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_constant__ ResidentArgs A, const __grid_constant__ Globals G,
+                                                               const __grid_constant__ MassExtras X) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    extern __shared__ __align__(128) unsigned char smem[];
+    const int t = threadIdx.x, tile = blockIdx.x;
+    const TileMeta M = A.meta[tile];
+    const int cs = A.cs, vs = A.vs;
+    // ---- one-time loads: blob, halo list, ELL words, own state ------------------------------------------------
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(A.blob + (size_t)M.blob_off16 * 16);
+        uint4 *dst = reinterpret_cast<uint4 *>(smem);
+        for (uint32_t q = t; q < M.blob_bytes / 16; q += TM) dst[q] = src[q];
+        int32_t *hl = reinterpret_cast<int32_t *>(smem + A.off_halo);
+        for (uint32_t h = t; h < M.n_halo; h += TM) hl[h] = A.halo[M.halo_off + h];
+    }
+    uint32_t ell[RES_ROWS];
+    const int rows = (int)ell_chunks((int)M.deg) * ELL_CHUNK;
+#pragma unroll
+    for (int j = 0; j < RES_ROWS; j++)     // rows beyond the block: the padding word (dummy mass, record 0 with k = 0)
+        ell[j] = (j < rows) ? __ldg(A.ell + M.ell_off + (size_t)j * TM + t) : ((uint32_t)(A.cs - 1) << ELL_NB_SHIFT);
+    double *Pb = reinterpret_cast<double *>(smem + A.off_pos), *Vb = reinterpret_cast<double *>(smem + A.off_vel);
+    auto Pc = [&](int buf, int c) { return Pb + (size_t)(buf * 3 + c) * cs; };
+    auto Vc = [&](int buf, int c) { return Vb + (size_t)(buf * 3 + c) * vs; };
+    {
+        const double *sb = A.st_in + (size_t)tile * STATE_BLOCK + t;
+        for (int c = 0; c < 3; c++) { Pc(0, c)[t] = sb[c * TM]; Vc(0, c)[t] = sb[(3 + c) * TM]; }
+        if (t == 0) for (int b = 0; b < 2; b++) for (int c = 0; c < 3; c++) {      // the dummy mass: far away, at rest
+            Pc(b, c)[cs - 1] = 1e30;
+            if (A.stage_vel) Vc(b, c)[vs - 1] = 0.0;
+        }
+    }
+    __syncthreads();
+    const int n_rec = reinterpret_cast<const int32_t *>(smem)[2], hdr3 = reinterpret_cast<const int32_t *>(smem)[3];
+    const int np8 = ((n_rec + 1) & ~1) * 8;
+    const int nk8 = A.dict_mode == 2 ? (((hdr3 >> 8) + 1) & ~1) * 8 : np8;
+    const char *kb = reinterpret_cast<const char *>(smem + BLOB_REC), *rb = kb + nk8, *dmb = rb + np8;
+    const char *omb = dmb + (DAMPING ? np8 : 0);
+    const uint8_t *mapb = reinterpret_cast<const uint8_t *>(omb + (ACTIVE ? np8 : 0));
+    const uint8_t fl = smem[BLOB_FLAGS + t];
+    const double mass = reinterpret_cast<const double *>(smem + BLOB_M)[t];
+    const bool live = (fl & F_VALID) && !(fl & (F_FIXED | F_GHOST));
+    const int64_t i_api = A.slot_to_api[(size_t)tile * TM + t];
+    const int32_t *hl = reinterpret_cast<const int32_t *>(smem + A.off_halo);
+    double *sintab = reinterpret_cast<double *>(smem + A.off_sintab);
+    V3 acc = {0.0, 0.0, 0.0};
+    if (A.verlet && live) acc = V3{A.acc[i_api], A.acc[X.nm + i_api], A.acc[2 * X.nm + i_api]};
+    double t_sim = *A.t_in;
+    // Halo exchange by PUSH: the owner of a mass stores its new state straight into the halo slots of the CTAs whose
+    // springs reach it (remote shared-memory stores do not stall the writer; a pull would pay a load round trip per
+    // step).  Each CTA registers its halo slots with the owners once: exp_cnt[slot] destinations per own mass,
+    // exp_dst[slot][k] = generic pointer to the destination's position buffer 0, x component.
+    int *exp_cnt = reinterpret_cast<int *>(smem + A.off_hptr);
+    double **exp_dst = reinterpret_cast<double **>(smem + A.off_hptr + TM * 4);
+    const ptrdiff_t v_minus_p = (A.off_vel - A.off_pos) / 8;
+    exp_cnt[t] = 0;
+    cluster.sync();
+    {
+        double *my_p = cluster.map_shared_rank(Pb, cluster.block_rank());
+        for (uint32_t h = t; h < M.n_halo; h += TM) {
+            const int32_t hi = hl[h];
+            if (hi < 0) continue;
+            const int owner = hi / STATE_BLOCK, slot = hi % STATE_BLOCK;
+            const int k = atomicAdd(cluster.map_shared_rank(exp_cnt, owner) + slot, 1);
+            cluster.map_shared_rank(exp_dst, owner)[slot * (RES_MAX_TILES - 1) + k] = my_p + TM + h;
+        }
+    }
+    cluster.sync();
+    const int n_exp = exp_cnt[t];
+    auto push = [&](int buf, const V3 &p, const V3 &v) {
+        for (int k = 0; k < n_exp; k++) {
+            double *d = exp_dst[t * (RES_MAX_TILES - 1) + k];
+            d[(size_t)(buf * 3 + 0) * cs] = p.x; d[(size_t)(buf * 3 + 1) * cs] = p.y; d[(size_t)(buf * 3 + 2) * cs] = p.z;
+            if (A.stage_vel) {
+                double *dv = d + v_minus_p;
+                dv[(size_t)(buf * 3 + 0) * vs] = v.x; dv[(size_t)(buf * 3 + 1) * vs] = v.y; dv[(size_t)(buf * 3 + 2) * vs] = v.z;
+            }
+        }
+    };
+    push(0, V3{Pc(0, 0)[t], Pc(0, 1)[t], Pc(0, 2)[t]}, V3{Vc(0, 0)[t], Vc(0, 1)[t], Vc(0, 2)[t]});
+    if (ACTIVE && t < A.n_omega) sintab[t] = sin(P::mul(A.omega_tab[t], t_sim));
+    cluster.sync();                                   // every CTA's state buffer 0, halo included, is in place
+
+    int cur = 0;
+    for (int step = 0; step < A.nsteps; step++, cur ^= 1) {
+        // the halo slots of buffer `cur` were filled by their owners before the barrier that ended the previous step
+        if (step > 0) { if (gridDim.x > 1) cluster.barrier_wait(); else __syncthreads(); }
+        const char *pbx = reinterpret_cast<const char *>(Pc(cur, 0)), *pby = reinterpret_cast<const char *>(Pc(cur, 1)),
+                   *pbz = reinterpret_cast<const char *>(Pc(cur, 2));
+        const char *vbx = reinterpret_cast<const char *>(Vc(cur, 0)), *vby = reinterpret_cast<const char *>(Vc(cur, 1)),
+                   *vbz = reinterpret_cast<const char *>(Vc(cur, 2));
+        V3 pos = {Pc(cur, 0)[t], Pc(cur, 1)[t], Pc(cur, 2)[t]}, vel = {Vc(cur, 0)[t], Vc(cur, 1)[t], Vc(cur, 2)[t]};
+        if (live) {
+            V3 force = {0.0, 0.0, 0.0};
+            // one spring; padding words evaluate a dummy spring (far-away mass, k = 0) that contributes exactly zero, so
+            // the fast form needs no branch and the springs of a chunk interleave
+            auto spring = [&](const uint32_t en) {
+                if (P::strict && !(en & ELL_VALID)) return;
+                const uint32_t nbo = en & 0xff8u;
+                uint32_t rco = (en >> 13) & 0x7ff8u;
+                const uint32_t kco = rco;
+                if (A.dict_mode) rco = (uint32_t)mapb[(en >> 16) & 0xfffu] << 3;
+                const double k = *(const double *)(kb + (A.dict_mode == 2 ? kco : rco));
+                double rest = *(const double *)(rb + rco);
+                if (ACTIVE) {
+                    if (A.n_omega > 0) {     // table mode: the record's slot holds the table index and its actuation code
+                        const int slot = *reinterpret_cast<const int *>(omb + rco), ty = (slot >> 16) & 3;
+                        const double c = ty == 1 ? -0.2 : (ty == 2 ? 0.2 : 0.0);
+                        rest = P::mul(rest, P::add(1.0, P::mul(c, sintab[slot & 0xffff])));
+                    } else {
+                        const int ty = (en >> ELL_TYPE_SHIFT) & 3;
+                        if (ty) rest = P::mul(rest, actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim)));
+                    }
+                }
+                const V3 po = {*(const double *)(pbx + nbo), *(const double *)(pby + nbo), *(const double *)(pbz + nbo)};
+                if (P::strict) {
+                    V3 vo = {0.0, 0.0, 0.0};
+                    if (A.stage_vel) vo = V3{*(const double *)(vbx + nbo), *(const double *)(vby + nbo), *(const double *)(vbz + nbo)};
+                    SpringArgs spr;
+                    spr.k = k; spr.rest_scaled = rest; spr.damping = DAMPING ? *(const double *)(dmb + rco) : 0.0;
+                    if (en & ELL_SIDE) acc3<P>(force, spring_force<P, DAMPING>(po, pos, vo, vel, spr));
+                    else { V3 f = spring_force<P, DAMPING>(pos, po, vel, vo, spr); acc3<P>(force, V3{-f.x, -f.y, -f.z}); }
+                } else {   // the streaming kernel's fast form: force on this mass = (p_me - p_other) * coef
+                    const double dx = pos.x - po.x, dy = pos.y - po.y, dz = pos.z - po.z;
+                    const double L2 = fma(dz, dz, fma(dy, dy, dx * dx));
+                    const double inv = rsqrt_fast(L2);
+                    double coef = k * fma(rest, inv, -1.0);
+                    if (DAMPING) {
+                        const double dvx = *(const double *)(vbx + nbo) - vel.x, dvy = *(const double *)(vby + nbo) - vel.y,
+                                     dvz = *(const double *)(vbz + nbo) - vel.z;
+                        coef = fma(fma(dvz, dz, fma(dvy, dy, dvx * dx)) * (inv * inv), *(const double *)(dmb + rco), coef);
+                    }
+                    force.x = fma(dx, coef, force.x); force.y = fma(dy, coef, force.y); force.z = fma(dz, coef, force.z);
+                }
+            };
+            // up to 28 rows (every 3-D lattice) as one straight line, so that independent springs overlap: with one warp
+            // per scheduler there is nothing else to hide the fp64 / MUFU latencies behind
+            constexpr int STRAIGHT = 28;
+#pragma unroll
+            for (int j = 0; j < STRAIGHT; j++) spring(ell[j]);
+            if (rows > STRAIGHT) {
+#pragma unroll
+                for (int j = STRAIGHT; j < RES_ROWS; j++) spring(ell[j]);
+            }
+            force = mass_forces<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force);
+            if (A.verlet) verlet_tail<P>(G.dt, mass, force, pos, vel, acc);
+            else euler_tail<P>(G.dt, mass, force, pos, vel, acc);
+        }
+        const int nxt = cur ^ 1;
+        Pc(nxt, 0)[t] = pos.x; Pc(nxt, 1)[t] = pos.y; Pc(nxt, 2)[t] = pos.z;
+        Vc(nxt, 0)[t] = vel.x; Vc(nxt, 1)[t] = vel.y; Vc(nxt, 2)[t] = vel.z;
+        push(nxt, pos, vel);
+        t_sim = __dadd_rn(t_sim, G.dt);               // T += dt, src/sim.cu:1811
+        if (ACTIVE && A.n_omega > 0) {                // the table is read by this CTA's threads only: separate it from
+            __syncthreads();                          // this step's readers, the barrier below publishes it
+            if (t < A.n_omega) sintab[t] = sin(P::mul(A.omega_tab[t], t_sim));
+        }
+        // all new states visible, nobody still reads the old ones: arrive here, wait at the top of the next step
+        if (gridDim.x > 1) cluster.barrier_arrive();
+    }
+    // ---- back to HBM ----------------------------------------------------------------------------------------
+    if (gridDim.x > 1) cluster.barrier_wait();   // also keeps every CTA's shared memory alive until all pushes have landed
+    else __syncthreads();
+    {
+        double *ob = A.st_out + (size_t)tile * STATE_BLOCK + t;
+        for (int c = 0; c < 3; c++) { ob[c * TM] = Pc(cur, c)[t]; ob[(3 + c) * TM] = Vc(cur, c)[t]; }
+        if (live && (A.write_acc || A.verlet) && A.nsteps > 0) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
+        if (tile == 0 && t == 0) { *A.t_out = t_sim; *A.step_out = *A.step_in + A.nsteps; }
+    }
+}
+
+static bool resident_env() { static const bool on = !(getenv("TB_RESIDENT") && atoi(getenv("TB_RESIDENT")) == 0); return on; }
+
+// Can the whole system live in one cluster?  (All tiles processed by this engine, none waiting for a peer.)
+bool tiled_resident_ok(const Engine *e) {
+    const TiledState *S = e->tiled;
+    if (!S || !S->supported || (e->flags & TB_NO_RESIDENT) || !resident_env()) return false;
+    if (S->n_tiles < 1 || S->n_tiles > RES_MAX_TILES || S->n_active != S->n_tiles) return false;
+    if (e->any_ghost || S->n_exp_tab || S->halo_connected) return false;
+    return true;
+}
+
+template <class P, bool D, bool AC>
+static int launch_resident_t(Engine *e, TiledState *S, const ResidentArgs &A, const MassExtras &X) {
+    auto kern = resident_step_kernel<P, D, AC>;
+    static int configured = -1;
+    if (configured != A.total) {
+        TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, A.total));
+        configured = A.total;
+    }
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)S->n_tiles); cfg.blockDim = dim3(TM); cfg.dynamicSmemBytes = (size_t)A.total; cfg.stream = e->stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)S->n_tiles; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    TB_CUDA(e, cudaLaunchKernelEx(&cfg, kern, A, e->G, X));
+    return TB_OK;
+}
+
+// nsteps steps in one launch; the caller flips e->cur by nsteps & 1 afterwards
+int launch_tiled_resident(Engine *e, int nsteps, bool write_acc) {
+    TiledState *S = e->tiled;
+    if (!tiled_resident_ok(e)) return fail(e, TB_ERR_INVALID, "resident kernel requested for a system it does not fit");
+    ResidentArgs A;
+    A.nsteps = nsteps;
+    A.cs = S->cs; A.vs = S->stage_vel ? S->cs : TM; A.stage_vel = S->stage_vel ? 1 : 0;
+    A.dict_mode = S->dict ? (S->dict_split ? 2 : 1) : 0;
+    A.verlet = (e->flags & TB_INTEGRATOR_VERLET) ? 1 : 0;
+    A.write_acc = write_acc ? 1 : 0;
+    A.n_omega = S->has_active ? S->n_omega : 0;
+    A.off_halo = (int32_t)up16((size_t)S->max_blob);
+    A.off_hptr = A.off_halo + (int32_t)up16((size_t)(S->max_halo + 4) * 4);
+    A.off_sintab = A.off_hptr + (int32_t)up16((size_t)TM * 4 + (size_t)TM * (RES_MAX_TILES - 1) * 8);
+    A.off_pos = A.off_sintab + MAX_OMEGA * 8;
+    A.off_vel = A.off_pos + 2 * 3 * A.cs * 8;
+    A.total = A.off_vel + 2 * 3 * A.vs * 8;
+    if ((size_t)A.total > SMEM_LIMIT) return fail(e, TB_ERR_INVALID, "resident kernel: working set exceeds shared memory");
+    const int out = e->cur ^ (nsteps & 1);
+    A.st_in = S->st[e->cur]; A.st_out = S->st[out];
+    A.blob = S->blob; A.slot_to_api = S->slot_to_api; A.halo = S->halo; A.ell = S->ell; A.meta = S->meta;
+    A.acc = e->acc;
+    A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + out;
+    A.step_in = e->step_dev + e->cur; A.step_out = e->step_dev + out;
+    A.omega_tab = S->omega_tab;
+    MassExtras X;
+    X.ext = nullptr;                                  // a pending one-shot force is consumed by a streaming step first
+    X.drag = e->drag;
+    X.lc_ptr = e->any_local ? e->lc_ptr : nullptr;
+    X.lc = e->lc;
+    X.nm = e->nm;
+    const bool d = S->has_damping, a = S->has_active;
+    int rc;
+    if (e->flags & TB_MATH_STRICT) {
+        rc = d ? (a ? launch_resident_t<Strict, true, true>(e, S, A, X) : launch_resident_t<Strict, true, false>(e, S, A, X))
+               : (a ? launch_resident_t<Strict, false, true>(e, S, A, X) : launch_resident_t<Strict, false, false>(e, S, A, X));
+    } else {
+        rc = d ? (a ? launch_resident_t<Fast, true, true>(e, S, A, X) : launch_resident_t<Fast, true, false>(e, S, A, X))
+               : (a ? launch_resident_t<Fast, false, true>(e, S, A, X) : launch_resident_t<Fast, false, false>(e, S, A, X));
+    }
+    if (rc != TB_OK) return rc;
+    TB_CUDA(e, cudaGetLastError());
+    return TB_OK;
 }
 
 bool tiled_halo_connected(const Engine *e) { return e->tiled && e->tiled->halo_connected; }
