@@ -373,6 +373,38 @@ def test_resident_kernel_equals_streaming_kernel_bitwise(nsteps):
         assert rel(fa[f], fb[f]) <= 1e-12, f
 
 
+def test_resident_kernel_runs_independent_systems_as_separate_clusters():
+    """Four independent 10 x 10 x 5 robots in one engine (bricks of 5^3: four tiles each): the resident kernel launches
+    one cluster per robot; bit-identical to the streaming kernel and to the oracle."""
+    import oracle
+    from titan_b200 import lattice
+    parts, hints, nm1 = [], [], 500
+    for r in range(4):
+        L = lattice.build_lattice((1.5 * r, 0.0, 0.25 + 0.01 * r), (0.9, 0.9, 0.4), 10, 10, 5)
+        parts.append(L)
+        h = lattice.brick_hint(10, 10, 5)
+        hints.append(h + r * (int(h.max()) + 1))
+    pos = np.vstack([p["pos"] for p in parts])
+    left = np.concatenate([p["left"] + r * nm1 for r, p in enumerate(parts)])
+    right = np.concatenate([p["right"] + r * nm1 for r, p in enumerate(parts)])
+    rest = np.concatenate([p["rest"] for p in parts])
+    sc = oracle.Scene(pos, left, right, rest)
+    sc.vel[:, 2] = -0.3
+    sc.planes.append(oracle.make_plane((0, 0, 1), 0, 0.5, 0.6))
+    o = oracle_after(sc, 61)
+    out = []
+    for flags in (tb.MATH_STRICT, tb.MATH_STRICT | tb.NO_RESIDENT):
+        eng = tb.Engine(0, flags)
+        scenes.upload(eng, sc)
+        eng.set_tile_hint(np.concatenate(hints).astype(np.int32))
+        eng.run(61, 0.0)
+        out.append(eng.get_mass_state())
+        assert eng.info()["n_tiles"] == 16 and eng.info()["kernel"] == 1
+        eng.close()
+    for f in ("pos", "vel"):
+        assert same_bits(out[0][f], out[1][f]) and same_bits(out[0][f] + 0.0, getattr(o, f) + 0.0), f
+
+
 def test_verlet_tiled_dictionary_kernel_within_tolerance(monkeypatch):
     """Verlet on the configuration bench.py runs (fast arithmetic, one thread per mass, dictionary records)."""
     monkeypatch.setenv("TB_TPM", "1")               # one thread per mass also for this small scene
