@@ -373,6 +373,23 @@ def test_resident_kernel_equals_streaming_kernel_bitwise(nsteps):
         assert rel(fa[f], fb[f]) <= 1e-12, f
 
 
+def test_more_actuation_frequencies_than_the_sine_table_holds():
+    """Every ACTIVE_* spring its own omega (> 64 distinct values): sin(omega t) is evaluated per spring, on both tiled
+    kernels; the oracle's glibc sin may differ from the device's by an ulp."""
+    sc = scenes.actuated()
+    sc.type[sc.type >= 4] = 0
+    sc.omega[:] = 10.0 + 0.37 * np.arange(sc.ns)
+    o = oracle_after(sc, 40)
+    a = run_engine(sc, 40, tb.MATH_STRICT)
+    b = run_engine(sc, 40, tb.MATH_STRICT | tb.NO_RESIDENT)
+    for f in ("pos", "vel"):
+        assert same_bits(a[f], b[f]), f
+        assert rel(a[f], getattr(o, f)) <= 1e-13, (f, rel(a[f], getattr(o, f)))
+    fa = run_engine(sc, 40, tb.MATH_FAST)
+    for f in ("pos", "vel"):
+        assert rel(fa[f], getattr(o, f)) <= 1e-10, (f, rel(fa[f], getattr(o, f)))
+
+
 def test_resident_kernel_runs_independent_systems_as_separate_clusters():
     """Four independent 10 x 10 x 5 robots in one engine (bricks of 5^3: four tiles each): the resident kernel launches
     one cluster per robot; bit-identical to the streaming kernel and to the oracle."""

@@ -311,8 +311,11 @@ static size_t blob_size(int n_rec, bool damping, bool active, int n_map = 0, int
 // Threads per mass.  Strict arithmetic needs the oracle's summation order (1).  Otherwise: big problems keep
 // every SM busy with one thread per mass (fewest instructions and hand-offs; measured best on C2), small ones
 // (fewer tiles than resident CTAs) are latency bound and split each mass's springs over 4 threads.
+static bool resident_env();
 static int choose_tpm(const Engine *e, int64_t n_tiles) {
     if ((e->flags & TB_MATH_STRICT) || e->any_ghost) return 1;
+    // a system of <= 8 tiles runs on the resident cluster kernel: one thread per mass (which also allows dictionary records)
+    if (n_tiles <= 8 && !(e->flags & TB_NO_RESIDENT) && resident_env() && !getenv("TB_TPM")) return 1;
     int tpm = n_tiles >= 2 * (int64_t)e->sm_count ? 1 : 4;
     if (const char *s = getenv("TB_TPM")) { int v = atoi(s); if (v == 1 || v == 2 || v == 4) tpm = v; }
     return tpm;
@@ -1546,7 +1549,7 @@ static void halo_release(Engine *e, TiledState *S) {
 // touched at the start and at the end.
 struct ResidentArgs {
     int32_t nsteps, cs, vs, stage_vel, dict_mode, verlet, write_acc, n_omega;
-    int32_t off_halo, off_hptr, off_sintab, off_pos, off_vel, total;     // shared-memory byte offsets (the blob sits at 0)
+    int32_t off_halo, off_hptr, off_sintab, off_rs, off_pos, off_vel, total;     // shared-memory byte offsets (the blob sits at 0)
     const double *st_in; double *st_out;
     const uint8_t *blob; const int32_t *slot_to_api, *halo; const uint32_t *ell; const TileMeta *meta;
     double *acc; const double *t_in; double *t_out; const long long *step_in; long long *step_out; const double *omega_tab;
@@ -1601,6 +1604,24 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
     const int64_t i_api = A.slot_to_api[(size_t)tile * TM + t];
     const int32_t *hl = reinterpret_cast<const int32_t *>(smem + A.off_halo);
     double *sintab = reinterpret_cast<double *>(smem + A.off_sintab);
+    // sine-table actuation: rest * (1 -/+ 0.2 sin(omega t)) once per record and step (the record carries its actuation
+    // code), into a table of its own -- the blob stays as loaded
+    double *rs = reinterpret_cast<double *>(smem + A.off_rs);
+    const char *rsb = reinterpret_cast<const char *>(rs);
+    const bool act_table = ACTIVE && A.n_omega > 0;
+    // sin(omega t) is a long dependent chain: the LAST threads of the CTA (padding slots of a 5 x 5 x 5 brick) evaluate it
+    // for the NEXT step at the top of a step, off the critical path of the barrier
+    auto fill_sintab = [&](double t_for) {
+        const int w = TM - 1 - t;
+        if (w < A.n_omega) sintab[w] = sin(P::mul(A.omega_tab[w], t_for));
+    };
+    auto scale_records = [&]() {
+        for (int r = t; r < n_rec; r += TM) {
+            const int slot = *reinterpret_cast<const int *>(omb + 8 * r), ty = (slot >> 16) & 3;
+            const double c = ty == 1 ? -0.2 : (ty == 2 ? 0.2 : 0.0);
+            rs[r] = P::mul(*reinterpret_cast<const double *>(rb + 8 * r), P::add(1.0, P::mul(c, sintab[slot & 0xffff])));
+        }
+    };
     V3 acc = {0.0, 0.0, 0.0};
     if (A.verlet && live) acc = V3{A.acc[i_api], A.acc[X.nm + i_api], A.acc[2 * X.nm + i_api]};
     double t_sim = *A.t_in;
@@ -1636,13 +1657,14 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
         }
     };
     push(0, V3{Pc(0, 0)[t], Pc(0, 1)[t], Pc(0, 2)[t]}, V3{Vc(0, 0)[t], Vc(0, 1)[t], Vc(0, 2)[t]});
-    if (ACTIVE && t < A.n_omega) sintab[t] = sin(P::mul(A.omega_tab[t], t_sim));
+    if (act_table) { fill_sintab(t_sim); __syncthreads(); scale_records(); }
     cluster.sync();                                   // every CTA's state buffer 0, halo included, is in place
 
     int cur = 0;
     for (int step = 0; step < A.nsteps; step++, cur ^= 1) {
         // the halo slots of buffer `cur` were filled by their owners before the barrier that ended the previous step
         if (step > 0) { if (multi) cluster.barrier_wait(); else __syncthreads(); }
+        if (act_table) fill_sintab(__dadd_rn(t_sim, G.dt));      // for the next step; this step reads only `rs`
         const char *pbx = reinterpret_cast<const char *>(Pc(cur, 0)), *pby = reinterpret_cast<const char *>(Pc(cur, 1)),
                    *pbz = reinterpret_cast<const char *>(Pc(cur, 2));
         const char *vbx = reinterpret_cast<const char *>(Vc(cur, 0)), *vby = reinterpret_cast<const char *>(Vc(cur, 1)),
@@ -1652,23 +1674,18 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
             V3 force = {0.0, 0.0, 0.0};
             // one spring; padding words evaluate a dummy spring (far-away mass, k = 0) that contributes exactly zero, so
             // the fast form needs no branch and the springs of a chunk interleave
-            auto spring = [&](const uint32_t en) {
-                if (P::strict && !(en & ELL_VALID)) return;
+            auto spring_t = [&](const uint32_t en, auto per_spring_sine) {
+                constexpr bool SINE = decltype(per_spring_sine)::value;   // more distinct omegas than the table holds: a call
+                if (P::strict && !(en & ELL_VALID)) return;               // per spring, kept out of the common straight line
                 const uint32_t nbo = en & 0xff8u;
                 uint32_t rco = (en >> 13) & 0x7ff8u;
                 const uint32_t kco = rco;
                 if (A.dict_mode) rco = (uint32_t)mapb[(en >> 16) & 0xfffu] << 3;
                 const double k = *(const double *)(kb + (A.dict_mode == 2 ? kco : rco));
-                double rest = *(const double *)(rb + rco);
-                if (ACTIVE) {
-                    if (A.n_omega > 0) {     // table mode: the record's slot holds the table index and its actuation code
-                        const int slot = *reinterpret_cast<const int *>(omb + rco), ty = (slot >> 16) & 3;
-                        const double c = ty == 1 ? -0.2 : (ty == 2 ? 0.2 : 0.0);
-                        rest = P::mul(rest, P::add(1.0, P::mul(c, sintab[slot & 0xffff])));
-                    } else {
-                        const int ty = (en >> ELL_TYPE_SHIFT) & 3;
-                        if (ty) rest = P::mul(rest, actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim)));
-                    }
+                double rest = *(const double *)((act_table ? rsb : rb) + rco);    // table mode: scaled per record
+                if (ACTIVE && SINE) {
+                    const int ty = (en >> ELL_TYPE_SHIFT) & 3;
+                    if (ty) rest = P::mul(rest, actuation_from_sin<P>(ty, sin_omega_t<P>(*(const double *)(omb + rco), t_sim)));
                 }
                 const V3 po = {*(const double *)(pbx + nbo), *(const double *)(pby + nbo), *(const double *)(pbz + nbo)};
                 if (P::strict) {
@@ -1694,11 +1711,25 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
             // up to 28 rows (every 3-D lattice) as one straight line, so that independent springs overlap: with one warp
             // per scheduler there is nothing else to hide the fp64 / MUFU latencies behind
             constexpr int STRAIGHT = 28;
+            if (ACTIVE && !act_table) {
+#pragma unroll 1
+                for (int g = 0; g < RES_ROWS / ELL_CHUNK; g++) {
+                    if (g * ELL_CHUNK >= rows) break;
 #pragma unroll
-            for (int j = 0; j < STRAIGHT; j++) spring(ell[j]);
-            if (rows > STRAIGHT) {
+                    for (int u = 0; u < ELL_CHUNK; u++) {
+                        uint32_t en = 0;
 #pragma unroll
-                for (int j = STRAIGHT; j < RES_ROWS; j++) spring(ell[j]);
+                        for (int j = 0; j < RES_ROWS; j++) if (j == g * ELL_CHUNK + u) en = ell[j];   // register array, dynamic g
+                        spring_t(en, std::true_type{});
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < STRAIGHT; j++) spring_t(ell[j], std::false_type{});
+                if (rows > STRAIGHT) {
+#pragma unroll
+                    for (int j = STRAIGHT; j < RES_ROWS; j++) spring_t(ell[j], std::false_type{});
+                }
             }
             force = mass_forces<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force);
             if (A.verlet) verlet_tail<P>(G.dt, mass, force, pos, vel, acc);
@@ -1709,9 +1740,9 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
         Vc(nxt, 0)[t] = vel.x; Vc(nxt, 1)[t] = vel.y; Vc(nxt, 2)[t] = vel.z;
         push(nxt, pos, vel);
         t_sim = __dadd_rn(t_sim, G.dt);               // T += dt, src/sim.cu:1811
-        if (ACTIVE && A.n_omega > 0) {                // the table is read by this CTA's threads only: separate it from
-            __syncthreads();                          // this step's readers, the barrier below publishes it
-            if (t < A.n_omega) sintab[t] = sin(P::mul(A.omega_tab[t], t_sim));
+        if (act_table) {                              // the tables are read by this CTA's threads only: separate them from
+            __syncthreads();                          // this step's readers, the barrier below publishes the new ones
+            scale_records();
         }
         // all new states visible, nobody still reads the old ones: arrive here, wait at the top of the next step
         if (multi) cluster.barrier_arrive();
@@ -1774,7 +1805,8 @@ int launch_tiled_resident(Engine *e, int nsteps, bool write_acc) {
     A.off_halo = (int32_t)up16((size_t)S->max_blob);
     A.off_hptr = A.off_halo + (int32_t)up16((size_t)(S->max_halo + 4) * 4);
     A.off_sintab = A.off_hptr + (int32_t)up16((size_t)TM * 4 + (size_t)TM * (RES_MAX_TILES - 1) * 8);
-    A.off_pos = A.off_sintab + MAX_OMEGA * 8;
+    A.off_rs = A.off_sintab + MAX_OMEGA * 8;
+    A.off_pos = A.off_rs + (int32_t)up16((size_t)((S->dict ? S->max_dict : S->max_rec) + 2) * 8);
     A.off_vel = A.off_pos + 2 * 3 * A.cs * 8;
     A.total = A.off_vel + 2 * 3 * A.vs * 8;
     if ((size_t)A.total > SMEM_LIMIT) return fail(e, TB_ERR_INVALID, "resident kernel: working set exceeds shared memory");
