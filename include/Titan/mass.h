@@ -27,8 +27,8 @@ public:
     Vec pos;     // m
     Vec vel;     // m/s
 
-    // magnet-link properties (include/Titan/mass.h:27-31).  Magnetic masses need the occupancy-grid pass, which
-    // this engine refuses to run (TB_ERR_UNSUPPORTED) rather than silently skipping.
+    // magnet-link properties (include/Titan/mass.h:27-31): once any mass has rad > 0 or max_mag_force != 0 the engine runs
+    // the occupancy-grid + magnet pass every step (titan_b200/csrc/magnet.cu)
     double rad;
     double stiffness;
     double max_mag_force;
@@ -37,7 +37,7 @@ public:
     void setExternalForce(const Vec &v) { extern_force = v; }  // acts for ONE step after each upload (src/sim.cu:1365)
     Vec acceleration() { return acc; }
 
-    int og_idx;  // kept for source compatibility; the occupancy grid does not exist here
+    int og_idx;  // kept for source compatibility; the engine's occupancy grid is a per-step counting sort, not a table of pointers
 
     void addConstraint(CONSTRAINT_TYPE type, const Vec &vec, double num);
     void clearConstraints(CONSTRAINT_TYPE type);

@@ -646,7 +646,7 @@ void Simulation::start() {   // src/sim.cu:1547-1591
     engine_check(tb_create(device, TB_MATH_FAST | (integrator == 1 ? TB_INTEGRATOR_VERLET : 0u), &engine), "tb_create");
     try {
         upload_everything();
-        engine_check(tb_run_async(engine, 0, 0.0), "tb_run_async");   // validates the scene (e.g. refuses magnetic masses)
+        engine_check(tb_run_async(engine, 0, 0.0), "tb_run_async");   // validates the scene and brings the device layout up to date
     } catch (...) {
         tb_destroy(engine);
         engine = nullptr;
