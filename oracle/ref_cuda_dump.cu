@@ -14,6 +14,10 @@
  */
 #include <Titan/sim.h>
 
+#ifndef DUMP_IMPL                 // the facade build of this same file passes its own name
+#define DUMP_IMPL "titan_cuda_reference"
+#endif
+
 #include <chrono>
 #include <cmath>
 #include <cstdint>
@@ -245,7 +249,7 @@ static int do_bench(const std::string &cfg, long steps) {
     double Tb = sim.time();
     long done = lround((Tb - Ta) / dt);
     double sec = std::chrono::duration<double>(t3 - t2).count();
-    printf("{\"impl\": \"titan_cuda_reference\", \"config\": \"%s\", \"masses\": %zu, \"springs\": %zu, \"steps\": %ld, "
+    printf("{\"impl\": \"" DUMP_IMPL "\", \"config\": \"%s\", \"masses\": %zu, \"springs\": %zu, \"steps\": %ld, "
            "\"seconds\": %.6f, \"spring_steps_per_s\": %.6e, \"upload_seconds\": %.3f}\n",
            cfg.c_str(), nm, ns, done, sec, (double)ns * done / sec, std::chrono::duration<double>(t1 - t0).count());
     fflush(stdout);

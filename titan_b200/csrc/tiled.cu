@@ -1723,6 +1723,12 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
                         spring_t(en, std::true_type{});
                     }
                 }
+            } else if (rows <= 8) {            // low-degree systems (the README cube: 7 springs per mass) skip the padding rows
+#pragma unroll
+                for (int j = 0; j < 8; j++) spring_t(ell[j], std::false_type{});
+            } else if (rows <= 16) {
+#pragma unroll
+                for (int j = 0; j < 16; j++) spring_t(ell[j], std::false_type{});
             } else {
 #pragma unroll
                 for (int j = 0; j < STRAIGHT; j++) spring_t(ell[j], std::false_type{});
