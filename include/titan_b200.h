@@ -102,8 +102,9 @@ TB_API int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const i
                       const uint8_t *valid);
 /* rad, stiffness, max_mag_force, mag_scale_factor (include/Titan/mass.h:97-100).  Once any mass has a non-zero rad
  * or max_mag_force every step runs the occupancy-grid + magnet pass (recomputeOG src/sim.cu:893-906,
- * computeExternalMagnetForcesOG :1250-1281) on the generic step kernel; until then the pass is elided (it would add
- * exactly +0).  Pair forces are summed in (cell, ascending mass index) order from start-of-step positions. */
+ * computeExternalMagnetForcesOG :1250-1281) in front of the step kernel (tiled or generic); until then the pass is elided
+ * (it would add exactly +0).  Not available together with ghost masses.  Pair forces are summed in (cell, ascending
+ * mass index) order from start-of-step positions. */
 TB_API int tb_set_mass_magnet(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, const double *rad,
                        const double *stiffness, const double *max_mag_force, const double *mag_scale);
 /* Mass::operator=(CUDA_MASS&) src/mass.cu:21-49, Simulation::get/getAll src/sim.cu:589-654,1051-1116 */

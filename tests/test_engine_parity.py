@@ -215,14 +215,16 @@ def test_determinism_run_to_run():
     assert same_bits(a["pos"], b["pos"]) and same_bits(a["vel"], b["vel"])
 
 
+@pytest.mark.parametrize("kernel", [0, tb.KERNEL_CSR])
 @pytest.mark.parametrize("nsteps", [1, 10, 137])
-def test_magnet_pass_strict_is_bit_identical(nsteps):
+def test_magnet_pass_strict_is_bit_identical(nsteps, kernel):
     """Occupancy-grid + magnet pass (reference src/sim.cu:865-906,1223-1281) on the RobotLink scene
-    whose reference-CUDA dump pins the oracle (tests/golden/ref_cuda/ref_magnets.bin)."""
+    whose reference-CUDA dump pins the oracle (tests/golden/ref_cuda/ref_magnets.bin); in front of the tiled kernel (the
+    pass reads the tile-blocked state through the mass -> slot map) and of the generic one."""
     sc = scenes.magnets()
     o = oracle_after(sc, nsteps)
-    g = run_engine(sc, nsteps, tb.MATH_STRICT)
-    assert g["info"]["kernel"] == 0                       # magnetic scenes run on the generic kernel
+    g = run_engine(sc, nsteps, tb.MATH_STRICT | kernel, chunks=2 if nsteps > 10 else 1)
+    assert g["info"]["kernel"] == (0 if kernel else 1)
     for f in FIELDS:
         assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (f, rel(g[f], getattr(o, f)))
     assert same_bits(g["T"], o.T)
@@ -257,13 +259,14 @@ def magnet_cloud(n=4000, seed=12345):
     return sc
 
 
-@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.NO_GRAPH])
+@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_STRICT | tb.NO_GRAPH, tb.MATH_STRICT | tb.KERNEL_CSR])
 def test_magnet_cloud_strict_is_bit_identical(flags):
     """Free-free pairs, cell overflow (> 128 masses in a cell keeps the 128 lowest indices), clamped cell coordinates:
     the engine's deterministic pass (start-of-step positions, ascending index inside a cell) against the oracle's."""
     sc = magnet_cloud()
     o = oracle_after(sc, 60)
     g = run_engine(sc, 60, flags)
+    assert g["info"]["kernel"] == (0 if flags & tb.KERNEL_CSR else 1)   # isolated masses and a random spring net fit the tiles
     for f in FIELDS:
         assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (f, rel(g[f], getattr(o, f)))
     assert same_bits(g["extern_force"] + 0.0, o.ext + 0.0)
@@ -337,7 +340,7 @@ def test_verlet_strict_is_bit_identical(name, nsteps, kernel):
     sc.verlet = True
     o = oracle_after(sc, nsteps)
     g = run_engine(sc, nsteps, tb.MATH_STRICT | VERLET | kernel, chunks=2 if nsteps > 10 else 1)
-    assert g["info"]["kernel"] == (0 if (kernel == tb.KERNEL_CSR or name == "magnets") else 1)
+    assert g["info"]["kernel"] == (0 if kernel == tb.KERNEL_CSR else 1)
     for f in FIELDS:
         assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (name, f, rel(g[f], getattr(o, f)))
     assert same_bits(g["T"], o.T)

@@ -721,10 +721,11 @@ __global__ void advance_rest_kernel(double *rest, const int32_t *type, const dou
     else { if (x > l_min[s]) rest[s] = __dsub_rn(x, __dmul_rn(rate[s], dt)); }
 }
 
-// the tiled kernel covers both integrators; scenes with magnetic masses run on the generic kernel (the occupancy-grid
-// pass reads canonical positions)
+// the tiled kernel covers both integrators and takes the magnet pass's forces like an uploaded external force; a
+// partitioned scene (ghost masses) with magnets is not supported (the pass would need the peers' positions before the
+// step's halo exchange)
 static bool use_tiled(Engine *e) {
-    return !(e->flags & TB_KERNEL_CSR) && !e->any_magnet && tiled_supported(e);
+    return !(e->flags & TB_KERNEL_CSR) && !(e->any_magnet && e->any_ghost) && tiled_supported(e);
 }
 
 // enqueue ONE step (capturable): [advance_rest] + [occupancy grid + magnet pass] + fused spring-gather/mass-update kernel
@@ -735,7 +736,7 @@ static int enqueue_step(Engine *e, bool use_ext, bool write_acc) {
             e->rest, e->type, e->l_max, e->l_min, e->rate, e->left, e->right, e->mflags, e->G.dt, e->ns);
         e->launches++;
     }
-    if (e->any_magnet) TB_TRY(launch_magnet_pass(e, use_ext));   // recomputeOG + magnet forces, src/sim.cu:1775,1298
+    if (e->any_magnet) TB_TRY(launch_magnet_pass(e, use_ext, use_tiled(e)));   // recomputeOG + magnet forces, src/sim.cu:1775,1298
     int rc = use_tiled(e) ? launch_tiled_step(e, use_ext, write_acc) : launch_csr_step(e, use_ext, write_acc);
     if (rc != TB_OK) return rc;
     e->launches++;

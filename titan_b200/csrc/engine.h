@@ -126,7 +126,19 @@ int launch_csr_step(Engine *e, bool use_ext, bool write_acc);
 // magnet.cu
 int magnet_alloc(Engine *e);
 void magnet_free(Engine *e);
-int launch_magnet_pass(Engine *e, bool use_ext);   // occupancy grid + pair forces -> e->mag_force
+int launch_magnet_pass(Engine *e, bool use_ext, bool tiled);   // occupancy grid + pair forces -> e->mag_force
+// Where the start-of-step positions live: canonical planes [3][nm] (generic kernel), or the tile-blocked state of the
+// tiled kernel (blocks of 6 x 128 doubles: x y z vx vy vz of the tile's 128 slots) addressed through api_to_slot.
+struct PosView {
+    const double *base = nullptr; const int32_t *api_to_slot = nullptr; int64_t nm = 0;
+#ifdef __CUDACC__
+    __device__ __forceinline__ double ld(int64_t i, int c) const {
+        if (!api_to_slot) return base[c * nm + i];
+        const int32_t s = api_to_slot[i];
+        return base[(int64_t)(s >> 7) * 768 + c * 128 + (s & 127)];
+    }
+#endif
+};
 // tiled.cu
 int tiled_prepare(Engine *e);                    // (re)build tiles if stale
 int launch_tiled_step(Engine *e, bool use_ext, bool write_acc);
@@ -137,6 +149,7 @@ int tiled_info(const Engine *e, tb_info *info);
 bool tiled_halo_connected(const Engine *e);
 bool tiled_resident_ok(const Engine *e);         // <= 8 tiles, no peers: all steps of a run in one cluster launch
 int launch_tiled_resident(Engine *e, int nsteps, bool write_acc);
+void tiled_pos_view(const Engine *e, PosView *v); // the current state buffer of the tiled kernel
 int tiled_halo_check(Engine *e);                 // after a sync: did a halo wait time out?
 
 }  // namespace tb

@@ -20,8 +20,9 @@
 // threads lose the race and prints from the device).
 //
 // The output is a full external-force array (uploaded one-shot force + pair forces) which the generic step kernel
-// (csr_step.cu) consumes as `extern_force` (src/sim.cu:1298-1300).  Scenes with magnetic masses always run on the
-// generic kernel; the tiled kernel's permuted state is not visible to this pass.
+// (csr_step.cu) or the tiled one consumes as `extern_force` (src/sim.cu:1298-1300).  In front of the tiled kernel the pass
+// reads the tile-blocked state through the mass -> slot map (PosView); cells and pair order stay in API indices, so both
+// kernels see the same forces bit for bit.
 #include "engine.h"
 
 namespace tb {
@@ -39,12 +40,12 @@ __device__ __forceinline__ int og_coord(double raw) {
     return v > OG_DIM - 1 ? OG_DIM - 1 : (v < 0 ? 0 : v);
 }
 
-__global__ void og_cell_kernel(int64_t nm, const double *pos, const uint8_t *flags, int32_t *cell, int32_t *counter) {
+__global__ void og_cell_kernel(int64_t nm, const PosView pos, const uint8_t *flags, int32_t *cell, int32_t *counter) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nm) return;
     int c = -1;
     if (flags[i] & F_VALID) {
-        c = OG_DIM * og_coord(pos[i]) + og_coord(pos[nm + i]);   // getOgCounterIdx, :835-837
+        c = OG_DIM * og_coord(pos.ld(i, 0)) + og_coord(pos.ld(i, 1));   // getOgCounterIdx, :835-837
         atomicAdd(&counter[c], 1);
     }
     cell[i] = c;
@@ -91,7 +92,7 @@ __global__ void og_rank_kernel(int64_t nm, const int32_t *cell, const int32_t *s
 
 struct MagnetArgs {
     int64_t nm;
-    const double *pos;          // start-of-step positions, [3][nm]
+    PosView pos;                // start-of-step positions
     const uint8_t *flags;
     const double *rad, *stiffness, *max_mag, *mag_scale;
     const int32_t *start, *sorted;
@@ -107,7 +108,7 @@ template <class P> __global__ void __launch_bounds__(128) magnet_force_kernel(Ma
     if (A.ext_in) ext = V3{A.ext_in[i], A.ext_in[n + i], A.ext_in[2 * n + i]};
     uint8_t fl = A.flags[i];
     if ((fl & F_VALID) && !(fl & F_FIXED)) {                      // fixed masses return before the pass, :1292-1298
-        V3 p1 = {A.pos[i], A.pos[n + i], A.pos[2 * n + i]};
+        V3 p1 = {A.pos.ld(i, 0), A.pos.ld(i, 1), A.pos.ld(i, 2)};
         double rad1 = A.rad[i], st1 = A.stiffness[i], mm1 = A.max_mag[i];
         int cx = og_coord(p1.x), cy = og_coord(p1.y);
 #pragma unroll 1
@@ -123,7 +124,7 @@ template <class P> __global__ void __launch_bounds__(128) magnet_force_kernel(Ma
                 for (int q = q0; q < q1; q++) {
                     int j = A.sorted[q];
                     if (j == (int)i) continue;                                     // :1273
-                    V3 temp = sub3<P>(p1, V3{A.pos[j], A.pos[n + j], A.pos[2 * n + j]});
+                    V3 temp = sub3<P>(p1, V3{A.pos.ld(j, 0), A.pos.ld(j, 1), A.pos.ld(j, 2)});
                     double tn = norm3<P>(temp);
                     double inter = P::sub(tn, P::add(rad1, A.rad[j]));
                     V3 ef = {0.0, 0.0, 0.0};
@@ -168,12 +169,14 @@ void magnet_free(Engine *e) {
 }
 
 // one occupancy-grid rebuild + magnet pass over the current state (capturable); 5 launches + 1 memset
-int launch_magnet_pass(Engine *e, bool use_ext) {
+int launch_magnet_pass(Engine *e, bool use_ext, bool tiled) {
     if (!e->mag_rad) return fail(e, TB_ERR_INVALID, "magnet pass without magnet fields");
     const int64_t nm = e->nm;
     const unsigned grid = (unsigned)((nm + 255) / 256);
     int32_t *counter = e->og_counter, *start = counter + OG_CELLS, *cursor = start + OG_CELLS + 1;
-    const double *pos = e->pos[e->cur];
+    PosView pos;
+    pos.base = e->pos[e->cur]; pos.nm = nm;
+    if (tiled) tiled_pos_view(e, &pos);
     TB_CUDA(e, cudaMemsetAsync(counter, 0, (size_t)OG_CELLS * 4, e->stream));
     og_cell_kernel<<<grid, 256, 0, e->stream>>>(nm, pos, e->mflags, e->og_cell, counter);
     og_scan_kernel<<<1, 1024, 0, e->stream>>>(counter, start, cursor);

@@ -109,7 +109,7 @@ struct TiledState {
     // device
     double *st[2] = {nullptr, nullptr};   // tile-blocked state, ping-pong
     uint8_t *blob = nullptr;
-    int32_t *slot_to_api = nullptr, *halo = nullptr, *rec_spring = nullptr;
+    int32_t *slot_to_api = nullptr, *api_to_slot = nullptr, *halo = nullptr, *rec_spring = nullptr;
     // Dictionary mode (see build_structure): springs with bit-identical parameters share one record per tile.
     bool dict = false;                    // the blobs hold distinct records + a byte map (record slot -> record)
     bool dict_split = false;              // ... for (rest, damping, omega) only: the stiffness stays one value per record
@@ -129,6 +129,7 @@ struct TiledState {
     TileMeta *meta = nullptr;
     // host
     std::vector<int32_t> h_slot_to_api, h_api_to_slot;
+    size_t n_api = 0;                       // entries of the device copy api_to_slot (made when a magnet pass needs it)
     std::vector<TileMeta> h_meta;
     bool supported = false;
     std::string why_not;
@@ -295,6 +296,7 @@ static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
     if (S->krec_off) { cudaFree(S->krec_off); S->krec_off = nullptr; }
     release(e, S->blob, S->blob_bytes);
     release(e, S->slot_to_api, (size_t)S->n_slots); release(e, S->halo, (size_t)S->n_halo);
+    release(e, S->api_to_slot, S->n_api); S->n_api = 0;
     release(e, S->rec_spring, (size_t)S->n_rec); release(e, S->ell, (size_t)S->n_ell);
     if (S->meta) { cudaFree(S->meta); S->meta = nullptr; }
     S->n_tiles = S->n_slots = S->n_rec = S->n_ell = S->n_halo = 0;
@@ -1393,6 +1395,10 @@ int tiled_prepare(Engine *e) {
             stale |= TS_PARAMS | TS_FLAGS;
         }
     }
+    if (e->any_magnet && !S->api_to_slot) {           // the magnet pass looks masses up by API index
+        TB_TRY(upload_vec(e, &S->api_to_slot, S->h_api_to_slot));
+        S->n_api = S->h_api_to_slot.size();
+    }
     unsigned gs = (unsigned)((S->n_slots + 255) / 256);
     if (stale & TS_STATE) {
         if (e->canon_stale && !(stale & TS_STRUCT)) TB_TRY(tiled_to_canonical(e));  // partial upload landed in canonical
@@ -1460,7 +1466,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
         for (int p = 0; p < S->n_peers; p++) { A.peer_flag[p] = S->peer_flag[p]; A.peer_out[p] = S->peer_st[p][e->cur ^ 1]; }
     }
     MassExtras X;
-    X.ext = (use_ext && e->ext) ? e->ext : nullptr;
+    X.ext = e->any_magnet ? e->mag_force : ((use_ext && e->ext) ? e->ext : nullptr);   // magnet.cu folds the uploaded force in
     X.drag = e->drag;
     X.lc_ptr = e->any_local ? e->lc_ptr : nullptr;
     X.lc = e->lc;
@@ -1775,7 +1781,7 @@ bool tiled_resident_ok(const Engine *e) {
     // 12.3 vs 7.2 us): resident while every cluster gets an SM of its own
     const int64_t max_tiles = getenv("TB_RESIDENT_MAX_TILES") ? atoll(getenv("TB_RESIDENT_MAX_TILES")) : std::max(8, e->sm_count);
     if (S->n_tiles < 1 || S->res_cluster < 1 || S->n_tiles > max_tiles || S->n_active != S->n_tiles) return false;
-    if (e->any_ghost || S->n_exp_tab || S->halo_connected) return false;
+    if (e->any_ghost || e->any_magnet || S->n_exp_tab || S->halo_connected) return false;   // the magnet pass runs between steps
     return true;
 }
 
@@ -1841,6 +1847,12 @@ int launch_tiled_resident(Engine *e, int nsteps, bool write_acc) {
     if (rc != TB_OK) return rc;
     TB_CUDA(e, cudaGetLastError());
     return TB_OK;
+}
+
+static_assert(TM == 128 && STATE_BLOCK == 768, "PosView::ld (engine.h) spells these out");
+void tiled_pos_view(const Engine *e, PosView *v) {
+    const TiledState *S = e->tiled;
+    v->base = S->st[e->cur]; v->api_to_slot = S->api_to_slot; v->nm = e->nm;
 }
 
 bool tiled_halo_connected(const Engine *e) { return e->tiled && e->tiled->halo_connected; }
