@@ -41,6 +41,7 @@ template int dev_alloc<uint16_t>(Engine *, uint16_t **, size_t);
 template int dev_alloc<tb_local>(Engine *, tb_local **, size_t);
 template int dev_alloc<tb_plane>(Engine *, tb_plane **, size_t);
 template int dev_alloc<tb_ball>(Engine *, tb_ball **, size_t);
+template int dev_alloc<float4>(Engine *, float4 **, size_t);
 
 void dev_free(Engine *e, void *p, size_t bytes) {
     if (!p) return;

@@ -63,6 +63,8 @@ struct Engine {
     bool stiff_seen = false, scale_seen = false;         // shell stiffness / mag_scale uploaded so far are uniform:
     double stiff_uniform = 0.0, scale_uniform = 0.0;     //   remembered here instead of stored per mass
     int32_t *og_cell = nullptr, *og_items = nullptr, *og_sorted = nullptr, *og_counter = nullptr;
+    double *og_pos = nullptr;        // positions in og_sorted order, [3][nm]
+    float4 *og_posf = nullptr;       // (float x, y, z, mass index) in og_sorted order
     int cur = 0;                   // which pos/vel buffer holds the current state
 
     // host-side knowledge

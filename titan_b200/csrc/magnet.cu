@@ -9,10 +9,10 @@
 // Here the grid is a counting sort of the mass indices by cell, rebuilt every step from the start-of-step positions
 // (the ping-pong buffer the step kernel reads):
 //     og_cell_kernel   cell id per mass + population count per cell
-//     og_scan_kernel   exclusive scan of the 65,536 populations (one CTA)
+//     og_scan_kernel   exclusive scan of the 65,536 populations (64 CTAs, each sums what lies in front of it)
 //     og_fill_kernel   masses into their cell's segment (arbitrary order)
-//     og_rank_kernel   ... brought into ascending mass index (rank inside the segment)
-//     magnet_force_kernel   per free mass: the 3 x 3 cells in the reference's (x offset, y offset) order, the
+//     og_rank_kernel   ... brought into ascending mass index (rank inside the segment), positions copied alongside
+//     magnet_force_kernel   per free mass (threads in sorted order): the 3 x 3 cells in the reference's (x offset, y offset) order, the
 //                      first 128 masses of each cell in ascending index, one pair force at a time added to the
 //                      mass's external force (the order the CPU oracle of the tests follows too)
 // so results are reproducible and, under TB_MATH_STRICT, bit-identical to the oracle.  Cells hold 4 B per mass
@@ -40,37 +40,51 @@ __device__ __forceinline__ int og_coord(double raw) {
     return v > OG_DIM - 1 ? OG_DIM - 1 : (v < 0 ? 0 : v);
 }
 
-__global__ void og_cell_kernel(int64_t nm, const PosView pos, const uint8_t *flags, int32_t *cell, int32_t *counter) {
+// masses that are not valid take no part: their row of the output is just the uploaded force
+__global__ void og_cell_kernel(int64_t nm, const PosView pos, const uint8_t *flags, int32_t *cell, int32_t *counter,
+                               const double *ext_in, double *ext_out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nm) return;
     int c = -1;
     if (flags[i] & F_VALID) {
         c = OG_DIM * og_coord(pos.ld(i, 0)) + og_coord(pos.ld(i, 1));   // getOgCounterIdx, :835-837
         atomicAdd(&counter[c], 1);
+    } else {
+        for (int k = 0; k < 3; k++) ext_out[k * nm + i] = ext_in ? ext_in[k * nm + i] : 0.0;
     }
     cell[i] = c;
 }
 
-// one CTA of 1024 threads, 64 cells each: start[c] = sum of counter[0..c), start[OG_CELLS] = total; cursor = start
-__global__ void __launch_bounds__(1024) og_scan_kernel(const int32_t *counter, int32_t *start, int32_t *cursor) {
-    __shared__ int32_t part[1024];
-    const int per = OG_CELLS / 1024;
-    int t = threadIdx.x, base = t * per, sum = 0;
-    for (int q = 0; q < per; q++) sum += counter[base + q];
-    part[t] = sum;
+// exclusive scan of the cell populations: start[c] = sum of counter[0..c), start[OG_CELLS] = total; cursor = start.
+// 64 CTAs of 1,024 cells each; a CTA adds up everything in front of its cells itself (coalesced, independent loads out
+// of L2: at most 63 per thread) instead of waiting for its predecessors -- integers, so the grouping does not matter.
+constexpr int OG_SCAN_T = 1024;
+__global__ void __launch_bounds__(OG_SCAN_T) og_scan_kernel(const int32_t *counter, int32_t *start, int32_t *cursor) {
+    __shared__ int32_t wsum[32], wpre[32];
+    const int t = threadIdx.x, b = blockIdx.x, lane = t & 31, w = t >> 5;
+    int prev = 0;
+#pragma unroll 8
+    for (int q = 0; q < b; q++) prev += counter[q * OG_SCAN_T + t];
+    const int own = counter[b * OG_SCAN_T + t];
+    int incl = own;
+    for (int off = 1; off < 32; off <<= 1) { int v = __shfl_up_sync(0xffffffffu, incl, off); if (lane >= off) incl += v; }
+    for (int off = 16; off; off >>= 1) prev += __shfl_xor_sync(0xffffffffu, prev, off);
+    if (lane == 31) wsum[w] = incl;
+    if (lane == 0) wpre[w] = prev;
     __syncthreads();
-    for (int off = 1; off < 1024; off <<= 1) {
-        int v = (t >= off) ? part[t - off] : 0;
-        __syncthreads();
-        part[t] += v;
-        __syncthreads();
+    if (w == 0) {
+        const int v = wsum[lane];
+        int iv = v, pv = wpre[lane];
+        for (int off = 1; off < 32; off <<= 1) { int u = __shfl_up_sync(0xffffffffu, iv, off); if (lane >= off) iv += u; }
+        for (int off = 16; off; off >>= 1) pv += __shfl_xor_sync(0xffffffffu, pv, off);
+        __syncwarp();
+        wsum[lane] = iv - v;                  // cells of this CTA in front of warp `lane`
+        if (lane == 0) wpre[0] = pv;          // cells in front of this CTA
     }
-    int run = part[t] - sum;
-    for (int q = 0; q < per; q++) {
-        start[base + q] = run; cursor[base + q] = run;
-        run += counter[base + q];
-    }
-    if (t == 1023) start[OG_CELLS] = run;
+    __syncthreads();
+    const int run = wpre[0] + wsum[w] + incl - own;
+    start[b * OG_SCAN_T + t] = run; cursor[b * OG_SCAN_T + t] = run;
+    if (b == gridDim.x - 1 && t == OG_SCAN_T - 1) start[OG_CELLS] = run + own;
 }
 
 __global__ void og_fill_kernel(int64_t nm, const int32_t *cell, int32_t *cursor, int32_t *items) {
@@ -80,7 +94,10 @@ __global__ void og_fill_kernel(int64_t nm, const int32_t *cell, int32_t *cursor,
     if (c >= 0) items[atomicAdd(&cursor[c], 1)] = (int32_t)i;
 }
 
-__global__ void og_rank_kernel(int64_t nm, const int32_t *cell, const int32_t *start, const int32_t *items, int32_t *sorted) {
+// ... and the positions with them (spos, [3][nm] by place in the sorted list): the pair loop then reads addresses it
+// knows in advance instead of chasing sorted[q] -> slot -> position
+__global__ void og_rank_kernel(int64_t nm, const PosView pos, const int32_t *cell, const int32_t *start, const int32_t *items,
+                               int32_t *sorted, double *spos, float4 *sposf) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nm) return;
     int c = cell[i];
@@ -88,6 +105,10 @@ __global__ void og_rank_kernel(int64_t nm, const int32_t *cell, const int32_t *s
     int b = start[c], e = start[c + 1], rank = 0;
     for (int q = b; q < e; q++) rank += items[q] < (int32_t)i;
     sorted[b + rank] = (int32_t)i;
+    double p[3];
+    for (int k = 0; k < 3; k++) { p[k] = pos.ld(i, k); spos[k * nm + b + rank] = p[k]; }
+    // single-precision copy + the mass index in one 16-byte word: what the neighbour scan of the pair kernel reads
+    sposf[b + rank] = make_float4(__double2float_rn(p[0]), __double2float_rn(p[1]), __double2float_rn(p[2]), __int_as_float((int)i));
 }
 
 struct MagnetArgs {
@@ -96,50 +117,88 @@ struct MagnetArgs {
     const uint8_t *flags;
     const double *rad, *stiffness, *max_mag, *mag_scale;
     const int32_t *start, *sorted;
+    const double *spos;         // positions by place in `sorted`, [3][nm]
+    const float4 *sposf;        // (float x, y, z, mass index) by place in `sorted`
     const double *ext_in;       // uploaded one-shot external force or null (= 0)
     double *ext_out;            // [3][nm]
 };
 
+#define MAG_D2_GATE 0.0197   // > 0.14^2 with room for the rounding of the sum: farther pairs need no square root
+#define MAG_D2_GATE_F 0.0225f // 0.15^2: the single-precision pre-test of the neighbour scan
+
+// computeExternalMagnetForce, src/sim.cu:1223-1241, for one neighbour inside the gate: shell contact + inverse-square
+// magnet.  No component of the result is ever -0 (it is 0 + a - b with a, b possibly signed zeros).
+template <class P>
+__device__ __forceinline__ V3 pair_force(const MagnetArgs &A, const V3 &temp, double d2, double rad1, double st1, double mm1, int j) {
+    V3 ef = {0.0, 0.0, 0.0};
+    const double tn = P::sqrt(d2);                                                    // norm3: d2 is its radicand
+    if (tn < MAG_CUTOFF) {
+        const double inter = P::sub(tn, P::add(rad1, A.rad[j]));
+        V3 dir = div3<P>(temp, tn);
+        if (inter < 0.0) acc3<P>(ef, scale3<P>(dir, P::mul(fabs(inter), st1)));       // shells intersect, :1230-1232
+        double tn2 = P::mul(tn, tn);
+        double c2 = P::div(P::mul(A.mag_scale[j], mm1), tn2 > 1e-12 ? tn2 : 1e-12);
+        dec3<P>(ef, scale3<P>(dir, c2));                                              // :1235-1237
+    }
+    return ef;
+}
+
+// One thread per place in the sorted list: the threads of a warp sit in the same cell and walk the same nine segments
+// (broadcast loads).  Nearly every neighbour of a 2-D cell list is beyond the 0.14 m cut-off (a whole z column shares a
+// cell) and adds exactly zero, but in a warp SOME lane is near the current neighbour at almost every step, so a
+// straightforward loop runs the expensive branch (square root, four divisions) every time at 1/32 efficiency.  Hence
+// two nested loops: each lane scans forward with a cheap test (single-precision squared distance against a gate above
+// the cut-off, one 16-byte load per neighbour) to ITS next near neighbour, the warp meets (__syncwarp), all lanes evaluate their pair together.  Order of a mass's
+// sum: unchanged (near pairs in list order); the skipped zero terms only matter for a sum that is still -0, which the
+// reference's first `+ 0` would turn into +0: `seen`.
 template <class P> __global__ void __launch_bounds__(128) magnet_force_kernel(MagnetArgs A) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= A.nm) return;
+    const int64_t place = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool active = place < A.nm && place < A.start[OG_CELLS];
+    const unsigned mask = __ballot_sync(0xffffffffu, active);    // the lanes that take part in the warp-wide steps below
+    if (!active) return;
     const int64_t n = A.nm;
+    const int i = A.sorted[place];
     V3 ext = {0.0, 0.0, 0.0};
     if (A.ext_in) ext = V3{A.ext_in[i], A.ext_in[n + i], A.ext_in[2 * n + i]};
-    uint8_t fl = A.flags[i];
-    if ((fl & F_VALID) && !(fl & F_FIXED)) {                      // fixed masses return before the pass, :1292-1298
-        V3 p1 = {A.pos.ld(i, 0), A.pos.ld(i, 1), A.pos.ld(i, 2)};
-        double rad1 = A.rad[i], st1 = A.stiffness[i], mm1 = A.max_mag[i];
-        int cx = og_coord(p1.x), cy = og_coord(p1.y);
-#pragma unroll 1
-        for (int a = -1; a <= 1; a++) {
-#pragma unroll 1
-            for (int b = -1; b <= 1; b++) {
-                int x = cx + a, y = cy + b;
-                if (x < 0 || y < 0 || !(x < OG_DIM) || !(y < OG_DIM)) continue;   // :1262
-                int c = OG_DIM * x + y;
-                int q0 = A.start[c], q1 = A.start[c + 1];
-                if (q1 - q0 > OG_CAP) q1 = q0 + OG_CAP;
-#pragma unroll 1
-                for (int q = q0; q < q1; q++) {
-                    int j = A.sorted[q];
-                    if (j == (int)i) continue;                                     // :1273
-                    V3 temp = sub3<P>(p1, V3{A.pos.ld(j, 0), A.pos.ld(j, 1), A.pos.ld(j, 2)});
-                    double tn = norm3<P>(temp);
-                    double inter = P::sub(tn, P::add(rad1, A.rad[j]));
-                    V3 ef = {0.0, 0.0, 0.0};
-                    if (tn < MAG_CUTOFF) {
-                        V3 dir = div3<P>(temp, tn);
-                        if (inter < 0.0) acc3<P>(ef, scale3<P>(dir, P::mul(fabs(inter), st1)));   // shells intersect, :1230-1232
-                        double tn2 = P::mul(tn, tn);
-                        double c2 = P::div(P::mul(A.mag_scale[j], mm1), tn2 > 1e-12 ? tn2 : 1e-12);
-                        dec3<P>(ef, scale3<P>(dir, c2));                                          // :1235-1237
-                    }
-                    acc3<P>(ext, ef);                                                             // :1240
-                }
+    const V3 p1 = {A.spos[place], A.spos[n + place], A.spos[2 * n + place]};
+    const double rad1 = A.rad[i], st1 = A.stiffness[i], mm1 = A.max_mag[i];
+    const int cx = og_coord(p1.x), cy = og_coord(p1.y);
+    // the scan's test runs in single precision on the float copies: gate 0.15 m, i.e. 1 cm of slack for their rounding,
+    // enough while this mass is within 10 km of the origin; farther out (or not finite) every neighbour is a candidate
+    const float x1f = __double2float_rn(p1.x), y1f = __double2float_rn(p1.y), z1f = __double2float_rn(p1.z);
+    const bool wide = !(fabsf(x1f) + fabsf(y1f) + fabsf(z1f) < 1e4f);
+    int ci = -1, q = 0, q1 = 0;                                   // segment ci = 3 * (a + 1) + (b + 1): the reference's loop order, :1256-1258
+    bool seen = false;
+    bool more = !(A.flags[i] & F_FIXED);                          // fixed masses return before the pass, :1292-1298
+    while (__any_sync(mask, more)) {
+        int qc = 0, j = 0;
+        bool found = false;
+        while (more) {                                            // cheap scan to this lane's next candidate
+            if (q >= q1) {
+                if (++ci >= 9) { more = false; break; }
+                const int x = cx + ci / 3 - 1, y = cy + ci % 3 - 1;
+                if (x < 0 || y < 0 || !(x < OG_DIM) || !(y < OG_DIM)) continue;       // :1262
+                const int c = OG_DIM * x + y;
+                q = A.start[c]; q1 = A.start[c + 1];
+                if (q1 - q > OG_CAP) q1 = q + OG_CAP;
+                continue;
             }
+            const float4 f = A.sposf[q];
+            const int jj = __float_as_int(f.w);
+            q++;
+            if (jj == i) continue;                                                    // :1273
+            seen = true;
+            const float dx = x1f - f.x, dy = y1f - f.y, dz = z1f - f.z;
+            if (wide || fmaf(dz, dz, fmaf(dy, dy, dx * dx)) < MAG_D2_GATE_F) { found = true; qc = q - 1; j = jj; break; }
+        }
+        __syncwarp(mask);                                         // everyone has its candidate (or is through): evaluate together
+        if (found) {
+            const V3 temp = sub3<P>(p1, V3{A.spos[qc], A.spos[n + qc], A.spos[2 * n + qc]});
+            const double d2 = P::add(P::add(P::mul(temp.x, temp.x), P::mul(temp.y, temp.y)), P::mul(temp.z, temp.z));
+            if (d2 < MAG_D2_GATE) acc3<P>(ext, pair_force<P>(A, temp, d2, rad1, st1, mm1, j));   // :1240
         }
     }
+    if (seen) ext = V3{P::add(ext.x, 0.0), P::add(ext.y, 0.0), P::add(ext.z, 0.0)};
     A.ext_out[i] = ext.x; A.ext_out[n + i] = ext.y; A.ext_out[2 * n + i] = ext.z;
 }
 
@@ -152,6 +211,8 @@ int magnet_alloc(Engine *e) {
         TB_CUDA(e, cudaMemsetAsync(*p, 0, nm * 8, e->stream));
     }
     TB_TRY(dev_alloc(e, &e->mag_force, nm * 3));
+    TB_TRY(dev_alloc(e, &e->og_pos, nm * 3));
+    TB_TRY(dev_alloc(e, &e->og_posf, nm));
     TB_TRY(dev_alloc(e, &e->og_cell, nm));
     TB_TRY(dev_alloc(e, &e->og_items, nm));
     TB_TRY(dev_alloc(e, &e->og_sorted, nm));
@@ -163,7 +224,7 @@ void magnet_free(Engine *e) {
     auto F = [&](auto *&p, size_t bytes) { dev_free(e, (void *)p, bytes); p = nullptr; };
     size_t nm = (size_t)e->nm;
     F(e->mag_rad, nm * 8); F(e->mag_stiff, nm * 8); F(e->mag_max, nm * 8); F(e->mag_scale, nm * 8);
-    F(e->mag_force, nm * 24);
+    F(e->mag_force, nm * 24); F(e->og_pos, nm * 24); F(e->og_posf, nm * 16);
     F(e->og_cell, nm * 4); F(e->og_items, nm * 4); F(e->og_sorted, nm * 4);
     F(e->og_counter, ((size_t)3 * OG_CELLS + 1) * 4);
 }
@@ -178,14 +239,14 @@ int launch_magnet_pass(Engine *e, bool use_ext, bool tiled) {
     pos.base = e->pos[e->cur]; pos.nm = nm;
     if (tiled) tiled_pos_view(e, &pos);
     TB_CUDA(e, cudaMemsetAsync(counter, 0, (size_t)OG_CELLS * 4, e->stream));
-    og_cell_kernel<<<grid, 256, 0, e->stream>>>(nm, pos, e->mflags, e->og_cell, counter);
-    og_scan_kernel<<<1, 1024, 0, e->stream>>>(counter, start, cursor);
+    og_cell_kernel<<<grid, 256, 0, e->stream>>>(nm, pos, e->mflags, e->og_cell, counter, (use_ext && e->ext) ? e->ext : nullptr, e->mag_force);
+    og_scan_kernel<<<OG_CELLS / OG_SCAN_T, OG_SCAN_T, 0, e->stream>>>(counter, start, cursor);
     og_fill_kernel<<<grid, 256, 0, e->stream>>>(nm, e->og_cell, cursor, e->og_items);
-    og_rank_kernel<<<grid, 256, 0, e->stream>>>(nm, e->og_cell, start, e->og_items, e->og_sorted);
+    og_rank_kernel<<<grid, 256, 0, e->stream>>>(nm, pos, e->og_cell, start, e->og_items, e->og_sorted, e->og_pos, e->og_posf);
     MagnetArgs A;
     A.nm = nm; A.pos = pos; A.flags = e->mflags;
     A.rad = e->mag_rad; A.stiffness = e->mag_stiff; A.max_mag = e->mag_max; A.mag_scale = e->mag_scale;
-    A.start = start; A.sorted = e->og_sorted;
+    A.start = start; A.sorted = e->og_sorted; A.spos = e->og_pos; A.sposf = e->og_posf;
     A.ext_in = (use_ext && e->ext) ? e->ext : nullptr;
     A.ext_out = e->mag_force;
     const unsigned g2 = (unsigned)((nm + 127) / 128);
