@@ -124,6 +124,7 @@ struct MagnetArgs {
 };
 
 #define MAG_D2_GATE 0.0197   // > 0.14^2 with room for the rounding of the sum: farther pairs need no square root
+constexpr int MAG_BATCH = 8;
 #define MAG_D2_GATE_F 0.0225f // 0.15^2: the single-precision pre-test of the neighbour scan
 
 // computeExternalMagnetForce, src/sim.cu:1223-1241, for one neighbour inside the gate: shell contact + inverse-square
@@ -183,13 +184,27 @@ template <class P> __global__ void __launch_bounds__(128) magnet_force_kernel(Ma
                 if (q1 - q > OG_CAP) q1 = q + OG_CAP;
                 continue;
             }
-            const float4 f = A.sposf[q];
-            const int jj = __float_as_int(f.w);
-            q++;
-            if (jj == i) continue;                                                    // :1273
-            seen = true;
-            const float dx = x1f - f.x, dy = y1f - f.y, dz = z1f - f.z;
-            if (wide || fmaf(dz, dz, fmaf(dy, dy, dx * dx)) < MAG_D2_GATE_F) { found = true; qc = q - 1; j = jj; break; }
+            // MAG_BATCH records (one 128-byte line) per trip: the list is read once, straight out of L2, and a trip that
+            // waits for one record at a time pays that latency for every 32-byte sector
+            float4 f[MAG_BATCH];
+#pragma unroll
+            for (int u = 0; u < MAG_BATCH; u++) f[u] = A.sposf[q + u];   // past q1: another cell's records or the array's padding, masked below
+            int hit = -1;
+#pragma unroll
+            for (int u = MAG_BATCH - 1; u >= 0; u--) {            // the FIRST candidate of the batch wins
+                const int jj = __float_as_int(f[u].w);
+                const float dx = x1f - f[u].x, dy = y1f - f[u].y, dz = z1f - f[u].z;
+                const bool other = q + u < q1 && jj != i;                             // :1273
+                seen |= other;
+                if (other && (wide || fmaf(dz, dz, fmaf(dy, dy, dx * dx)) < MAG_D2_GATE_F)) { hit = u; j = jj; }
+            }
+            if (hit >= 0) {
+                // records of the batch in front of the hit are done; `seen` may have looked past it, which is harmless:
+                // the candidate itself is a neighbour, so a neighbour has been seen either way
+                found = true; qc = q + hit; q = qc + 1;
+                break;
+            }
+            q += MAG_BATCH;
         }
         __syncwarp(mask);                                         // everyone has its candidate (or is through): evaluate together
         if (found) {
@@ -212,7 +227,8 @@ int magnet_alloc(Engine *e) {
     }
     TB_TRY(dev_alloc(e, &e->mag_force, nm * 3));
     TB_TRY(dev_alloc(e, &e->og_pos, nm * 3));
-    TB_TRY(dev_alloc(e, &e->og_posf, nm));
+    TB_TRY(dev_alloc(e, &e->og_posf, nm + MAG_BATCH));          // the pair kernel reads whole batches
+    TB_CUDA(e, cudaMemsetAsync(e->og_posf, 0, (nm + MAG_BATCH) * sizeof(float4), e->stream));
     TB_TRY(dev_alloc(e, &e->og_cell, nm));
     TB_TRY(dev_alloc(e, &e->og_items, nm));
     TB_TRY(dev_alloc(e, &e->og_sorted, nm));
@@ -224,7 +240,7 @@ void magnet_free(Engine *e) {
     auto F = [&](auto *&p, size_t bytes) { dev_free(e, (void *)p, bytes); p = nullptr; };
     size_t nm = (size_t)e->nm;
     F(e->mag_rad, nm * 8); F(e->mag_stiff, nm * 8); F(e->mag_max, nm * 8); F(e->mag_scale, nm * 8);
-    F(e->mag_force, nm * 24); F(e->og_pos, nm * 24); F(e->og_posf, nm * 16);
+    F(e->mag_force, nm * 24); F(e->og_pos, nm * 24); F(e->og_posf, (nm + MAG_BATCH) * 16);
     F(e->og_cell, nm * 4); F(e->og_items, nm * 4); F(e->og_sorted, nm * 4);
     F(e->og_counter, ((size_t)3 * OG_CELLS + 1) * 4);
 }
