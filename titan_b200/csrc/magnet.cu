@@ -135,43 +135,111 @@ __device__ __forceinline__ V3 pair_force(const MagnetArgs &A, const V3 &temp, do
     const double tn = P::sqrt(d2);                                                    // norm3: d2 is its radicand
     if (tn < MAG_CUTOFF) {
         const double inter = P::sub(tn, P::add(rad1, A.rad[j]));
-        V3 dir = div3<P>(temp, tn);
+        // Fast: reciprocals instead of the four IEEE divisions (whose zero numerators -- a neighbour straight above --
+        // take the division's slow path)
+        V3 dir = P::strict ? div3<P>(temp, tn) : scale3<P>(temp, rcp_fast(tn));
         if (inter < 0.0) acc3<P>(ef, scale3<P>(dir, P::mul(fabs(inter), st1)));       // shells intersect, :1230-1232
         double tn2 = P::mul(tn, tn);
-        double c2 = P::div(P::mul(A.mag_scale[j], mm1), tn2 > 1e-12 ? tn2 : 1e-12);
+        tn2 = tn2 > 1e-12 ? tn2 : 1e-12;
+        double c2 = P::strict ? P::div(P::mul(A.mag_scale[j], mm1), tn2) : P::mul(P::mul(A.mag_scale[j], mm1), rcp_fast(tn2));
         dec3<P>(ef, scale3<P>(dir, c2));                                              // :1235-1237
     }
     return ef;
 }
 
-// One thread per place in the sorted list: the threads of a warp sit in the same cell and walk the same nine segments
-// (broadcast loads).  Nearly every neighbour of a 2-D cell list is beyond the 0.14 m cut-off (a whole z column shares a
-// cell) and adds exactly zero, but in a warp SOME lane is near the current neighbour at almost every step, so a
+// One thread per place in the sorted list: the threads of a warp sit in the same cell (or a few cells) and need the same
+// nine lists.  Nearly every neighbour of a 2-D cell list is beyond the 0.14 m cut-off (a whole z column shares a cell)
+// and adds exactly zero, but in a warp SOME lane is near the current neighbour at almost every step, so a
 // straightforward loop runs the expensive branch (square root, four divisions) every time at 1/32 efficiency.  Hence
-// two nested loops: each lane scans forward with a cheap test (single-precision squared distance against a gate above
-// the cut-off, one 16-byte load per neighbour) to ITS next near neighbour, the warp meets (__syncwarp), all lanes evaluate their pair together.  Order of a mass's
-// sum: unchanged (near pairs in list order); the skipped zero terms only matter for a sum that is still -0, which the
-// reference's first `+ 0` would turn into +0: `seen`.
+// two phases per batch of neighbours: a cheap test (single-precision squared distance against a gate above the
+// cut-off, on 16-byte records) marks each lane's candidates, then the warp evaluates candidates together, one round
+// per candidate.  Order of a mass's sum: unchanged (its candidates in list order); the skipped zero terms only matter
+// for a sum that is still -0, which the reference's first `+ 0` would turn into +0: `seen`.
+constexpr int MAG_LOCKSTEP_MIN = 4;   // lanes of a warp in the same cell from which the warp walks that cell's lists together
+
 template <class P> __global__ void __launch_bounds__(128) magnet_force_kernel(MagnetArgs A) {
+    __shared__ float4 stage[4][32];                               // one batch of neighbour records per warp
+    constexpr unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t place = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const bool active = place < A.nm && place < A.start[OG_CELLS];
-    const unsigned mask = __ballot_sync(0xffffffffu, active);    // the lanes that take part in the warp-wide steps below
-    if (!active) return;
+    const bool active = place < A.nm && place < A.start[OG_CELLS];   // idle lanes stay for the warp-wide steps
     const int64_t n = A.nm;
-    const int i = A.sorted[place];
-    V3 ext = {0.0, 0.0, 0.0};
-    if (A.ext_in) ext = V3{A.ext_in[i], A.ext_in[n + i], A.ext_in[2 * n + i]};
-    const V3 p1 = {A.spos[place], A.spos[n + place], A.spos[2 * n + place]};
-    const double rad1 = A.rad[i], st1 = A.stiffness[i], mm1 = A.max_mag[i];
+    int i = -1;
+    V3 ext = {0.0, 0.0, 0.0}, p1 = {0.0, 0.0, 0.0};
+    double rad1 = 0.0, st1 = 0.0, mm1 = 0.0;
+    bool more = false;
+    if (active) {
+        i = A.sorted[place];
+        if (A.ext_in) ext = V3{A.ext_in[i], A.ext_in[n + i], A.ext_in[2 * n + i]};
+        p1 = V3{A.spos[place], A.spos[n + place], A.spos[2 * n + place]};
+        rad1 = A.rad[i]; st1 = A.stiffness[i]; mm1 = A.max_mag[i];
+        more = !(A.flags[i] & F_FIXED);                           // fixed masses return before the pass, :1292-1298
+    }
     const int cx = og_coord(p1.x), cy = og_coord(p1.y);
     // the scan's test runs in single precision on the float copies: gate 0.15 m, i.e. 1 cm of slack for their rounding,
     // enough while this mass is within 10 km of the origin; farther out (or not finite) every neighbour is a candidate
     const float x1f = __double2float_rn(p1.x), y1f = __double2float_rn(p1.y), z1f = __double2float_rn(p1.z);
     const bool wide = !(fabsf(x1f) + fabsf(y1f) + fabsf(z1f) < 1e4f);
-    int ci = -1, q = 0, q1 = 0;                                   // segment ci = 3 * (a + 1) + (b + 1): the reference's loop order, :1256-1258
     bool seen = false;
-    bool more = !(A.flags[i] & F_FIXED);                          // fixed masses return before the pass, :1292-1298
-    while (__any_sync(mask, more)) {
+    auto evaluate = [&](int qc, int j) {                          // the exact test and the pair force, in fp64
+        const V3 temp = sub3<P>(p1, V3{A.spos[qc], A.spos[n + qc], A.spos[2 * n + qc]});
+        const double d2 = P::add(P::add(P::mul(temp.x, temp.x), P::mul(temp.y, temp.y)), P::mul(temp.z, temp.z));
+        if (d2 < MAG_D2_GATE) acc3<P>(ext, pair_force<P>(A, temp, d2, rad1, st1, mm1, j));       // :1240
+    };
+
+    // ---- lanes that share a cell (a z column of a lattice: dozens) walk its nine lists together: a batch of 32 records
+    // is loaded once by the warp, every lane tests all of them (a bit per candidate), then the candidates are evaluated
+    // in list order, one warp-wide round per bit
+    const int key = more ? OG_DIM * cx + cy : -1;
+    unsigned todo = __ballot_sync(FULL, key >= 0);
+    while (todo) {
+        const int lk = __shfl_sync(FULL, key, __ffs(todo) - 1);
+        const bool mine = key == lk;
+        const unsigned group = __ballot_sync(FULL, mine);
+        todo &= ~group;
+        if (__popc(group) < MAG_LOCKSTEP_MIN) continue;           // few lanes: each scans for itself below
+        const int gx = lk / OG_DIM, gy = lk % OG_DIM;
+#pragma unroll 1
+        for (int ci = 0; ci < 9; ci++) {                          // 3 * (a + 1) + (b + 1): the reference's loop order, :1256-1258
+            const int x = gx + ci / 3 - 1, y = gy + ci % 3 - 1;
+            if (x < 0 || y < 0 || !(x < OG_DIM) || !(y < OG_DIM)) continue;           // :1262
+            const int c = OG_DIM * x + y;
+            const int q0 = A.start[c];
+            int q1 = A.start[c + 1];
+            if (q1 - q0 > OG_CAP) q1 = q0 + OG_CAP;
+#pragma unroll 1
+            for (int base = q0; base < q1; base += 32) {
+                const int cnt = q1 - base < 32 ? q1 - base : 32;
+                __syncwarp();
+                if (lane < cnt) stage[w][lane] = A.sposf[base + lane];
+                __syncwarp();
+                unsigned m = 0;
+                if (mine) {
+#pragma unroll 4
+                    for (int k = 0; k < cnt; k++) {
+                        const float4 f = stage[w][k];
+                        const float dx = x1f - f.x, dy = y1f - f.y, dz = z1f - f.z;
+                        const bool other = __float_as_int(f.w) != i;                  // :1273
+                        seen |= other;
+                        const bool near = fmaf(dz, dz, fmaf(dy, dy, dx * dx)) < MAG_D2_GATE_F;
+                        m |= (unsigned)(other & (wide | near)) << k;                  // no branches: one predicate per record
+                    }
+                }
+                while (__any_sync(FULL, m != 0)) {
+                    if (m) {
+                        const int k = __ffs(m) - 1;
+                        m &= m - 1;
+                        evaluate(base + k, __float_as_int(stage[w][k].w));
+                    }
+                }
+            }
+        }
+        if (mine) more = false;
+    }
+
+    // ---- the rest (sparse scenes: a lane's cell is its own): every lane scans its own lists
+    int ci = -1, q = 0, q1 = 0;
+    while (__any_sync(FULL, more)) {
         int qc = 0, j = 0;
         bool found = false;
         while (more) {                                            // cheap scan to this lane's next candidate
@@ -196,7 +264,8 @@ template <class P> __global__ void __launch_bounds__(128) magnet_force_kernel(Ma
                 const float dx = x1f - f[u].x, dy = y1f - f[u].y, dz = z1f - f[u].z;
                 const bool other = q + u < q1 && jj != i;                             // :1273
                 seen |= other;
-                if (other && (wide || fmaf(dz, dz, fmaf(dy, dy, dx * dx)) < MAG_D2_GATE_F)) { hit = u; j = jj; }
+                const bool cand = other & (wide | (fmaf(dz, dz, fmaf(dy, dy, dx * dx)) < MAG_D2_GATE_F));
+                hit = cand ? u : hit; j = cand ? jj : j;
             }
             if (hit >= 0) {
                 // records of the batch in front of the hit are done; `seen` may have looked past it, which is harmless:
@@ -206,13 +275,10 @@ template <class P> __global__ void __launch_bounds__(128) magnet_force_kernel(Ma
             }
             q += MAG_BATCH;
         }
-        __syncwarp(mask);                                         // everyone has its candidate (or is through): evaluate together
-        if (found) {
-            const V3 temp = sub3<P>(p1, V3{A.spos[qc], A.spos[n + qc], A.spos[2 * n + qc]});
-            const double d2 = P::add(P::add(P::mul(temp.x, temp.x), P::mul(temp.y, temp.y)), P::mul(temp.z, temp.z));
-            if (d2 < MAG_D2_GATE) acc3<P>(ext, pair_force<P>(A, temp, d2, rad1, st1, mm1, j));   // :1240
-        }
+        __syncwarp();                                             // everyone has its candidate (or is through): evaluate together
+        if (found) evaluate(qc, j);
     }
+    if (!active) return;
     if (seen) ext = V3{P::add(ext.x, 0.0), P::add(ext.y, 0.0), P::add(ext.z, 0.0)};
     A.ext_out[i] = ext.x; A.ext_out[n + i] = ext.y; A.ext_out[2 * n + i] = ext.z;
 }
