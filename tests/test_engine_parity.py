@@ -272,6 +272,24 @@ def test_magnet_cloud_strict_is_bit_identical(flags):
     assert same_bits(g["extern_force"] + 0.0, o.ext + 0.0)
 
 
+@pytest.mark.parametrize("shift", [(2.0e4, 0.0, 0.0), (0.0, -3.0e5, 1.0e3)])
+def test_magnet_pass_far_from_the_origin(shift):
+    """Masses tens of kilometres out: every cell coordinate on that axis clamps to the grid's border, and the pair
+    kernel's single-precision neighbour pre-test is switched off (its rounding would exceed the gate's slack) -- every
+    listed neighbour goes through the exact fp64 test.  Still bit-identical to the oracle."""
+    sc = magnet_cloud(n=700, seed=99)
+    sc.pos += np.array(shift)
+    sc.planes.clear()
+    o = oracle_after(sc, 20)
+    for kernel in (0, tb.KERNEL_CSR):
+        g = run_engine(sc, 20, tb.MATH_STRICT | kernel)
+        for f in FIELDS:
+            assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (kernel, f, rel(g[f], getattr(o, f)))
+    moved = oracle_after(sc, 1)
+    still = sc.copy(); still.magnets = False; still.step(1)
+    assert not same_bits(moved.vel, still.vel)            # pairs inside the cut-off exist out there too
+
+
 def test_magnet_cloud_fast_within_tolerance():
     sc = magnet_cloud()
     for nsteps, tol in ((1, 1e-12), (30, 1e-9)):
