@@ -151,7 +151,8 @@ private:
 
     // ---- lifecycle ---------------------------------------------------------------------------------------------
     double dt;
-    std::atomic<double> T;   // advanced by the GPU thread as steps are ENQUEUED; equals device time whenever paused
+    double dt_engine = 0.0001;   // the time step last uploaded to the engine (upload_constraints): what the run loop advances T by
+    std::atomic<double> T;   // advanced by the GPU thread as batches of steps COMPLETE; equals device time whenever paused
     Vec _global_acc;
     std::vector<Constraint *> constraints;
     std::vector<ContactPlane> dev_planes;  // what createPlane pushed to the device list (survives clearConstraints,

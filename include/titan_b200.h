@@ -142,6 +142,10 @@ TB_API int tb_set_globals(tb_engine *e, const double g[3], double dt);
 TB_API int tb_run_async(tb_engine *e, int64_t nsteps, double t0);
 TB_API int tb_sync(tb_engine *e);                                  /* cudaDeviceSynchronize at a breakpoint, :1708 */
 TB_API int tb_steps_done(tb_engine *e, int64_t *steps);            /* total steps enqueued so far */
+/* Blocks until the device has completed the first `steps` steps ever enqueued (<= tb_steps_done), later ones may still
+ * be running: lets the run loop keep the next batch queued behind the one it waits for, where the reference drains the
+ * device after every single step (cudaDeviceSynchronize, src/sim.cu:1771-1776). */
+TB_API int tb_wait_steps(tb_engine *e, int64_t steps);
 /* device time in ms of the most recent tb_run_async (CUDA events on the engine stream); call after tb_sync */
 TB_API int tb_last_run_ms(tb_engine *e, double *ms);
 

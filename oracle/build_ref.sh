@@ -4,7 +4,7 @@
 # Compiles the REFERENCE's own sources (from a headless-patched scratch copy under /tmp, see patch_ref.py;
 # the reference's CMake build is not used and no reference source enters the repo) into
 #   <out_dir>/libtitan_ref_host.so   host-callable reference code + oracle/ref_host_shim.cu   (CPU, runs here)
-#   <out_dir>/titan_ref_cuda         the reference's CUDA engine + oracle/ref_cuda_dump.cu     (needs a GPU)
+#   <out_dir>/titan_ref_cuda         the reference's CUDA engine + tests/cpp/titan_api_driver.cu (needs a GPU)
 #   <out_dir>/titan_ref_cuda_verlet  the same with the reference's VERLET option (CMakeLists.txt:13,90-93)
 # Flags follow the reference's CMakeLists.txt: C++14, separable compilation, -DCONSTRAINTS, no GRAPHICS.
 set -euo pipefail
@@ -25,7 +25,7 @@ for f in vec mass spring object sim; do
 done
 nvcc $NVFLAGS -DVERLET -c "$S/src/sim.cu" -o "$SCRATCH/sim_verlet.o" &
 nvcc $NVFLAGS -c "$HERE/ref_host_shim.cu" -o "$SCRATCH/shim.o" &
-nvcc $NVFLAGS -c "$HERE/ref_cuda_dump.cu" -o "$SCRATCH/dump.o" &
+nvcc $NVFLAGS -c "$HERE/../tests/cpp/titan_api_driver.cu" -o "$SCRATCH/dump.o" &
 wait
 nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a -shared -Xcompiler -fPIC \
   "$SCRATCH/vec.o" "$SCRATCH/mass.o" "$SCRATCH/spring.o" "$SCRATCH/object.o" "$SCRATCH/shim.o" \

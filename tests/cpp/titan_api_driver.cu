@@ -1,14 +1,17 @@
 /*
- * ref_cuda_dump.cu -- runs the REFERENCE's own CUDA engine on a GPU and dumps state.  TEST INFRASTRUCTURE ONLY.
- *
- * Linked against the reference's (headless-patched, see patch_ref.py) vec/mass/spring/object/sim.cu into
- * oracle/_ref/titan_ref_cuda.  Two uses, both on the GPU box:
- *   titan_ref_cuda dump  <scenario> <out.bin>     golden fixtures: initial scene + snapshots after pause(t)
- *   titan_ref_cuda bench <config> <steps>         "Titan's own CUDA build on the same B200" timing
- *   titan_ref_cuda init  <scenario> <out.bin>     initial scene only (host builders; needs no GPU)
- * The same source, unchanged, is also compiled against this repo's drop-in facade (include/Titan + libTitan.so ->
- * titan_b200/bin/titan_facade_dump): identical driver, two engines, dumps compared by tests/test_facade.py.
- * It only calls the reference's public API (include/Titan/sim.h); it contains no step arithmetic.
+ * titan_api_driver.cu -- a USER PROGRAM of the public Titan API (include/Titan/sim.h); it contains no step
+ * arithmetic.  TEST / BENCH INFRASTRUCTURE ONLY.  One source, two engines:
+ *   oracle/_ref/titan_ref_cuda      linked (oracle/build_ref.sh) against the REFERENCE's own, headless-patched
+ *                                   vec/mass/spring/object/sim.cu: the golden-fixture generator and the
+ *                                   "Titan's own CUDA build on the same B200" baseline of bench.py
+ *   tests/cpp/bin/titan_facade_dump compiled unchanged (tests/cpp/Makefile) against this repo's drop-in facade
+ *                                   (include/Titan + libTitan.so); tests/test_facade.py compares the two
+ * Modes:
+ *   dump      <scenario> <out.bin>          initial scene + snapshots after pause(t)
+ *   init      <scenario> <out.bin>          initial scene only (host builders; needs no GPU)
+ *   bench     <config> <steps>              wall clock around pause() for `steps` steps
+ *   bench_e2e <config> <steps> <batches>    end to end through host Mass objects: every batch is
+ *                                           setAll() + resume() + pause(t + steps dt) + getAll(), all timed
  *
  * Dump format (little endian): repeated records  u32 name_len, name, u32 dtype(0=f64,1=i32,2=u8), u64 count, data.
  */
@@ -257,10 +260,60 @@ static int do_bench(const std::string &cfg, long steps) {
     return 0;
 }
 
+/* bench_e2e: what a user of the reference's integration loop pays per batch of `steps` steps when the state crosses the
+ * boundary both ways: setAll() (host Mass objects -> device), resume(), pause(), getAll() (device -> host Mass objects).
+ * bytes = 48 B (pos, vel) per mass each way is the payload counted; the call moves what its implementation moves. */
+static int do_bench_e2e(const std::string &cfg, long steps, long batches) {
+    Simulation sim;
+    if (cfg == "c1") {
+        sim.createLattice(Vec(0, 0, 10), Vec(5, 5, 5), 5, 5, 5);
+        sim.createPlane(Vec(0, 0, 1), 0);
+    } else if (cfg == "c2" || cfg.rfind("lattice", 0) == 0) {
+        int n = (cfg == "c2") ? 100 : atoi(cfg.c_str() + 7);
+        double side = 0.1 * (n - 1);
+        sim.createLattice(Vec(0, 0, side / 2 - 0.001), Vec(side, side, side), n, n, n);
+        sim.createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
+    } else {
+        fprintf(stderr, "unknown bench_e2e config %s\n", cfg.c_str());
+        return 2;
+    }
+    size_t ns = sim.springs.size(), nm = sim.masses.size();
+    double dt = sim.getTimeStep();
+    auto t0 = std::chrono::steady_clock::now();
+    sim.start();
+    sim.pause(0.0);
+    auto t1 = std::chrono::steady_clock::now();
+    auto batch = [&]() {
+        double T = sim.time();
+        sim.setAll();
+        sim.resume();
+        sim.pause(T + (steps - 0.5) * dt);
+        sim.getAll();
+        return lround((sim.time() - T) / dt);
+    };
+    for (int w = 0; w < 2; w++) batch();                       /* warm-up */
+    long done = 0;
+    auto t2 = std::chrono::steady_clock::now();
+    for (long b = 0; b < batches; b++) done += batch();
+    auto t3 = std::chrono::steady_clock::now();
+    double sec = std::chrono::duration<double>(t3 - t2).count(), check = 0;
+    for (Mass *q : sim.masses) check += q->pos[2];
+    printf("{\"impl\": \"" DUMP_IMPL "\", \"mode\": \"e2e\", \"config\": \"%s\", \"masses\": %zu, \"springs\": %zu, "
+           "\"steps\": %ld, \"batches\": %ld, \"seconds\": %.6f, \"spring_steps_per_s\": %.6e, \"upload_seconds\": %.3f, "
+           "\"h2d_bytes_per_batch\": %zu, \"d2h_bytes_per_batch\": %zu, \"mean_z\": %.17g, "
+           "\"call\": \"Simulation::setAll + resume + pause + getAll\"}\n",
+           cfg.c_str(), nm, ns, done, batches, sec, (double)ns * done / sec, std::chrono::duration<double>(t1 - t0).count(),
+           nm * 48, nm * 48, check / (double)nm);
+    fflush(stdout);
+    sim.stop();
+    return 0;
+}
+
 int main(int argc, char **argv) {
+    if (argc >= 5 && !strcmp(argv[1], "bench_e2e")) return do_bench_e2e(argv[2], atol(argv[3]), atol(argv[4]));
     if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argv[2], argv[3]);
     if (argc >= 4 && !strcmp(argv[1], "init")) return do_dump(argv[2], argv[3], true);
     if (argc >= 4 && !strcmp(argv[1], "bench")) return do_bench(argv[2], atol(argv[3]));
-    fprintf(stderr, "usage: %s dump <scenario> <out.bin> | bench <c1|c2|c3_64|latticeN> <steps>\n", argv[0]);
+    fprintf(stderr, "usage: %s dump <scenario> <out.bin> | bench <c1|c2|c3_64|latticeN> <steps> | bench_e2e <c1|c2|latticeN> <steps> <batches>\n", argv[0]);
     return 2;
 }

@@ -116,7 +116,7 @@ def cube_beam():
 
 def magnets():
     """Magnetic connector masses (RobotLink, src/object.cu:368-384) + the occupancy-grid pass; same scene as
-    oracle/ref_cuda_dump.cu "magnets".  Per group: link (fixed end, free end), a fixed magnet close to the free end, a
+    tests/cpp/titan_api_driver.cu "magnets".  Per group: link (fixed end, free end), a fixed magnet close to the free end, a
     free plain mass beyond the cut-off, a fixed susceptible mass."""
     pos, fixed, m, rad, stiff, maxmag, scale = [], [], [], [], [], [], []
     left, right, k, rest = [], [], [], []
@@ -143,7 +143,7 @@ def magnets():
 
 SCENARIOS = {"c1_readme": c1_readme, "contact_friction": contact_friction, "actuated": actuated,
              "local_constraints": local_constraints, "cube_beam": cube_beam, "magnets": magnets}
-# pause() times used by oracle/ref_cuda_dump.cu for each scenario
+# pause() times used by tests/cpp/titan_api_driver.cu for each scenario
 PAUSES = {"c1_readme": [0.0, 0.001, 0.01, 0.1], "contact_friction": [0.0, 0.001, 0.01, 0.05],
           "actuated": [0.0, 0.001, 0.01, 0.05], "local_constraints": [0.0, 0.002, 0.01],
           "cube_beam": [0.0, 0.001, 0.02], "magnets": [0.0, 0.001, 0.005]}

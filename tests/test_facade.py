@@ -1,7 +1,7 @@
 """The C++ drop-in (include/Titan/*.h + titan_b200/libTitan.so) exercised through the reference's own public API.
 
 * tests/cpp/facade_tests.cpp: behaviour tests in the shape of the reference's test/physics/*_unittest.cpp.
-* titan_b200/bin/titan_facade_dump: oracle/ref_cuda_dump.cu -- the SAME driver source that, linked against the
+* tests/cpp/bin/titan_facade_dump: tests/cpp/titan_api_driver.cu -- the SAME driver source that, linked against the
   reference's own CUDA engine, produced tests/golden/ref_cuda/*.bin -- compiled unchanged against this facade.
   Its dumps are compared record by record with those golden files (the reference's own outputs on a B200).
 
@@ -19,7 +19,7 @@ import scenes
 from test_oracle_vs_reference_cuda import GOLD, read_dump, rel
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-BIN = os.path.join(ROOT, "titan_b200", "bin")
+BIN = os.path.join(ROOT, "tests", "cpp", "bin")
 LIB = os.path.join(ROOT, "titan_b200", "libTitan.so")
 
 

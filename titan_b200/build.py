@@ -24,6 +24,15 @@ def build_host():
     return os.path.join(_PKG, "libTitan.so")
 
 
+def build_programs():
+    """User programs of the facade (API driver, C++ tests): tests/cpp/bin/."""
+    d = os.path.join(os.path.dirname(_PKG), "tests", "cpp")
+    if os.path.exists(os.path.join(d, "Makefile")):
+        _make(d)
+    return os.path.join(d, "bin")
+
+
 def build_all():
     build_engine()
     build_host()
+    build_programs()

@@ -19,7 +19,7 @@ CONSTRAINT_PLANE, CONTACT_PLANE, BALL, DIRECTION = range(4)
 EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_last_error", "tb_set_topology", "tb_set_tile_hint",
            "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
            "tb_get_spring_rest", "tb_remove_springs", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
-           "tb_run_async", "tb_sync", "tb_steps_done", "tb_last_run_ms", "tb_get_info",
+           "tb_run_async", "tb_sync", "tb_steps_done", "tb_wait_steps", "tb_last_run_ms", "tb_get_info",
            "tb_export_positions_f32_dev", "tb_export_indices_dev", "tb_read_device", "tb_alloc_host", "tb_halo_set_ghosts", "tb_halo_prepare",
            "tb_halo_state_offsets", "tb_halo_connect", "tb_halo_set_exports", "tb_halo_push_now"]
 MAX_PEERS = 8
@@ -86,6 +86,7 @@ def lib():
         L.tb_run_async.argtypes = [_vp, C.c_int64, C.c_double]
         L.tb_sync.argtypes = [_vp]
         L.tb_steps_done.argtypes = [_vp, C.POINTER(C.c_int64)]
+        L.tb_wait_steps.argtypes = [_vp, C.c_int64]
         L.tb_last_run_ms.argtypes = [_vp, C.POINTER(C.c_double)]
         L.tb_get_info.argtypes = [_vp, C.POINTER(Info)]
         L.tb_export_positions_f32_dev.argtypes = [_vp, C.POINTER(_vp)]

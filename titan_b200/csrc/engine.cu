@@ -289,6 +289,8 @@ int tb_create(int device, uint32_t flags, tb_engine **out) {
         delete e;
         return TB_ERR_CUDA;
     }
+    for (cudaEvent_t &ev : e->run_ev)
+        if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) { g_create_error = "cudaEventCreate failed"; delete e; return TB_ERR_CUDA; }
     cudaDeviceGetAttribute(&e->sm_count, cudaDevAttrMultiProcessorCount, device);
     if (cudaMalloc((void **)&e->t_dev, 2 * sizeof(double)) != cudaSuccess) { delete e; return TB_ERR_OOM; }
     if (cudaMalloc((void **)&e->step_dev, 2 * sizeof(long long)) != cudaSuccess) { delete e; return TB_ERR_OOM; }
@@ -312,6 +314,7 @@ void tb_destroy(tb_engine *e) {
     cudaFree(e->t_dev);
     cudaFree(e->step_dev);
     cudaEventDestroy(e->ev0); cudaEventDestroy(e->ev1);
+    for (cudaEvent_t ev : e->run_ev) if (ev) cudaEventDestroy(ev);
     cudaStreamDestroy(e->stream);
     delete e;
 }
@@ -814,6 +817,11 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     TB_CUDA(e, cudaEventRecord(e->ev1, e->stream));
     TB_CUDA(e, cudaGetLastError());
     e->steps_done += nsteps;
+    {
+        const int slot = (int)(e->run_count++ % Engine::RUN_RING);
+        TB_CUDA(e, cudaEventRecord(e->run_ev[slot], e->stream));
+        e->run_ev_steps[slot] = e->steps_done;
+    }
     if (use_tiled(e)) e->canon_stale = true;
     return TB_OK;
 }
@@ -823,6 +831,21 @@ int tb_sync(tb_engine *e) {
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
     TB_CUDA(e, cudaGetLastError());
     return tiled_halo_check(e);
+}
+
+int tb_wait_steps(tb_engine *e, int64_t steps) {
+    E_CHECK(e);
+    if (steps > e->steps_done) return fail(e, TB_ERR_INVALID, "tb_wait_steps: %lld steps were never enqueued (%lld so far)", (long long)steps, (long long)e->steps_done);
+    // the earliest recorded run that reaches `steps`; runs older than the ring have completed if any ring entry has
+    int best = -1;
+    const int64_t live = std::min<int64_t>(e->run_count, Engine::RUN_RING);
+    for (int64_t r = 0; r < live; r++) {
+        const int slot = (int)((e->run_count - 1 - r) % Engine::RUN_RING);
+        if (e->run_ev_steps[slot] >= steps) best = slot; else break;    // newest to oldest: step counts descend
+    }
+    if (best < 0) return TB_OK;                   // nothing enqueued yet
+    TB_CUDA(e, cudaEventSynchronize(e->run_ev[best]));
+    return TB_OK;
 }
 
 int tb_steps_done(tb_engine *e, int64_t *steps) {

@@ -35,6 +35,11 @@ struct Engine {
     uint32_t flags = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    // tb_wait_steps: one event per tb_run_async in a small ring, tagged with the step count reached when it completes
+    static constexpr int RUN_RING = 8;
+    cudaEvent_t run_ev[RUN_RING] = {};
+    int64_t run_ev_steps[RUN_RING] = {};
+    int64_t run_count = 0;
     std::string err;
     int sm_count = 0;
 

@@ -31,6 +31,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <map>
+#include <mutex>
 #include <numeric>
 #include <unordered_map>
 
@@ -40,6 +41,7 @@ namespace tb {
 
 
 constexpr int TM = 128;                 // masses per tile
+constexpr int MAX_DEVICES = 64;         // per-device launch configuration caches (beyond that: configured on every launch)
 // ELL word: bits 3..11 neighbour local index (so `word & 0xff8` is its byte offset in a position array; own
 // masses 0..TM-1, halo TM..), bits 16..27 record slot (`(word >> 12) & 0xfff0` = byte offset of the (k,rest)
 // record), bits 28..29 actuation (0 passive, 1 contract-then-expand, 2 expand-then-contract), bit 30 this mass
@@ -1299,14 +1301,23 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
 // ---------------------------------------------------------------- glue ------------------------------------
 template <class P, bool D, bool AC, int TPM, int CS, bool HALO, int DICT>
 static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
-    static size_t configured_smem = 0;     // per template instantiation
-    static int blocks_per_sm = 0;
+    // The dynamic shared-memory limit of a kernel is a per-device (per-context) attribute: remembered per template
+    // instantiation AND device, under a lock (engines on several GPUs, or several facade GPU threads, in one process).
+    static std::mutex mu;
+    static size_t configured_smem[MAX_DEVICES] = {};
+    static int blocks_per_sm_dev[MAX_DEVICES] = {};
     auto kern = tiled_step_kernel<P, D, AC, TPM, CS, HALO, DICT>;
-    if (configured_smem != S->smem_bytes) {
-        TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S->smem_bytes));
-        TB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kern, TM * TPM + 32, S->smem_bytes));
-        if (blocks_per_sm < 1) return fail(e, TB_ERR_CUDA, "tiled step kernel does not fit on an SM (%zu bytes of shared memory)", S->smem_bytes);
-        configured_smem = S->smem_bytes;
+    int blocks_per_sm = 0;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        const int dv = e->device % MAX_DEVICES;
+        if (configured_smem[dv] != S->smem_bytes || e->device >= MAX_DEVICES) {
+            TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S->smem_bytes));
+            TB_CUDA(e, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm_dev[dv], kern, TM * TPM + 32, S->smem_bytes));
+            if (blocks_per_sm_dev[dv] < 1) return fail(e, TB_ERR_CUDA, "tiled step kernel does not fit on an SM (%zu bytes of shared memory)", S->smem_bytes);
+            configured_smem[dv] = S->smem_bytes;
+        }
+        blocks_per_sm = blocks_per_sm_dev[dv];
     }
     int64_t grid = std::min<int64_t>(S->n_active, (int64_t)e->sm_count * blocks_per_sm);
     if (const char *g = getenv("TB_GRID")) { int v = atoi(g); if (v > 0) grid = std::min<int64_t>(S->n_active, v); }
@@ -1788,10 +1799,17 @@ bool tiled_resident_ok(const Engine *e) {
 template <class P, bool D, bool AC>
 static int launch_resident_t(Engine *e, TiledState *S, const ResidentArgs &A, const MassExtras &X) {
     auto kern = resident_step_kernel<P, D, AC>;
-    static int configured = -1;
-    if (configured != A.total) {
-        TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, A.total));
-        configured = A.total;
+    {   // per device, see launch_c
+        static std::mutex mu;
+        static int configured[MAX_DEVICES];
+        static bool init = false;
+        std::lock_guard<std::mutex> lock(mu);
+        if (!init) { for (int &c : configured) c = -1; init = true; }
+        const int dv = e->device % MAX_DEVICES;
+        if (configured[dv] != A.total || e->device >= MAX_DEVICES) {
+            TB_CUDA(e, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, A.total));
+            configured[dv] = A.total;
+        }
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)S->n_tiles); cfg.blockDim = dim3(TM); cfg.dynamicSmemBytes = (size_t)A.total; cfg.stream = e->stream;

@@ -11,6 +11,7 @@
 #include <array>
 #include <cassert>
 #include <chrono>
+#include <deque>
 #include <iostream>
 #include <limits>
 #include <stdexcept>
@@ -473,6 +474,7 @@ void Simulation::upload_constraints() {
     engine_check(tb_set_balls(engine, (int32_t)balls.size(), balls.data()), "tb_set_balls");
     const double g[3] = {_global_acc[0], _global_acc[1], _global_acc[2]};
     engine_check(tb_set_globals(engine, g, dt), "tb_set_globals");
+    dt_engine = dt;        // what execute() accumulates T with: setTimeStep() while running takes effect at the next resume()
     constraints_dirty = false;
 }
 
@@ -664,44 +666,71 @@ void Simulation::_run() {
     cv.notify_all();
 }
 
-// The run loop of src/sim.cu:1704-1841 (Euler branch :1800-1811), batched: instead of one launch group and four
-// device synchronisations per step, whole runs of steps are enqueued (CUDA graphs inside the engine).  How many
-// steps fit before the next breakpoint is decided by replaying the reference's own test `*bpts.begin() <= T`
-// over the same fp64 accumulation `T += dt`.
+// The run loop of src/sim.cu:1704-1841 (Euler branch :1800-1811), batched and pipelined: instead of one launch group
+// and four device synchronisations per step, whole runs of steps are enqueued (CUDA graphs inside the engine), and the
+// next batch is enqueued BEFORE the loop waits for the previous one, so the device never drains between batches (a
+// small system on the resident kernel finishes 500 steps in under a millisecond).  How many steps fit before the
+// next breakpoint is decided by replaying the reference's own test `*bpts.begin() <= T` over the same fp64
+// accumulation `T += dt`.  The breakpoint set is re-read before every batch, and batches are sized to about a
+// millisecond of device time, so a breakpoint set while running (pause(time()), stop()) is honoured within two batches.
 void Simulation::execute() {
-    const int CHUNK = 500;   // steps per enqueue; bounds how far T runs ahead of a breakpoint set while running
+    int64_t chunk = 50;                       // steps per enqueue, adapted to ~1 ms of device time (50 .. 1000)
+    double T_enq = T;                         // simulation time after every step enqueued so far
+    int64_t enq = 0;                          // steps enqueued by this loop since the last drain
+    int64_t base = 0;                         // engine step count at the last drain
+    struct Batch { int64_t upto; double T_after; std::chrono::steady_clock::time_point t_enq; int64_t n; };
+    std::deque<Batch> inflight;
+    tb_steps_done(engine, &base);
+    auto fail_and_park = [&](const char *what) {
+        std::unique_lock<std::mutex> lk(mtx);
+        gpu_error = std::string(what) + tb_last_error(engine);
+        RUNNING = false;
+        cv.notify_all();
+        cv.wait(lk, [&] { return ENDED.load(); });
+    };
     while (true) {
         double next_bp = std::numeric_limits<double>::infinity();
         {
             std::unique_lock<std::mutex> lk(mtx);
-            if (!bpts.empty() && *bpts.begin() <= T) {
+            if (!bpts.empty() && *bpts.begin() <= T_enq) {
                 int rc = tb_sync(engine);   // cudaDeviceSynchronize at the breakpoint, :1708
                 if (rc != TB_OK) gpu_error = std::string("tb_sync: ") + tb_last_error(engine);
+                T = T_enq;
+                inflight.clear();
                 bpts.erase(bpts.begin());
                 RUNNING = false;
                 cv.notify_all();
                 cv.wait(lk, [&] { return RUNNING.load() || ENDED.load(); });
                 if (ENDED) return;
+                // the user thread may have stepped / edited while paused: pick up its time and the engine's step count
+                T_enq = T; enq = 0;
+                tb_steps_done(engine, &base);
                 continue;
             }
             if (ENDED) return;
             if (!bpts.empty()) next_bp = *bpts.begin();
         }
-        double t = T;
+        const double step_dt = dt_engine;     // the dt the engine was given at the last resume()/start()
+        double t = T_enq;
         int64_t n = 0;
-        while (n < CHUNK && !(next_bp <= t)) { t += dt; n++; }
-        int rc = tb_run_async(engine, n, T);
-        if (rc == TB_OK) rc = tb_sync(engine);
-        if (rc != TB_OK) {
-            std::unique_lock<std::mutex> lk(mtx);
-            gpu_error = std::string("step failed: ") + tb_last_error(engine);
-            RUNNING = false;
+        while (n < chunk && !(next_bp <= t)) { t += step_dt; n++; }
+        if (tb_run_async(engine, n, T_enq) != TB_OK) { fail_and_park("step failed: "); return; }
+        enq += n;
+        T_enq = t;
+        inflight.push_back({base + enq, t, std::chrono::steady_clock::now(), n});
+        while (inflight.size() >= 2) {        // wait for the older batch; the newer one keeps the device busy
+            const Batch b = inflight.front();
+            inflight.pop_front();
+            if (tb_wait_steps(engine, b.upto) != TB_OK) { fail_and_park("step failed: "); return; }
+            T = b.T_after;
             cv.notify_all();
-            cv.wait(lk, [&] { return ENDED.load(); });
-            return;
+            // about one millisecond of device time per batch (the wait above returns once per batch in steady state)
+            const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - b.t_enq).count() / 2.0;
+            if (ms > 0 && b.n == chunk) {
+                const double want = (double)chunk / std::max(ms, 1e-3);
+                chunk = (int64_t)std::min(1000.0, std::max(50.0, 0.5 * (double)chunk + 0.5 * want));
+            }
         }
-        T = t;
-        cv.notify_all();
     }
 }
 
@@ -730,7 +759,7 @@ void Simulation::step(int n) {
     if (constraints_dirty) upload_constraints();
     engine_check(tb_run_async(engine, n, T), "tb_run_async");
     double t = T;
-    for (int j = 0; j < n; j++) t += dt;
+    for (int j = 0; j < n; j++) t += dt_engine;
     T = t;
     engine_check(tb_sync(engine), "tb_sync");
 }
