@@ -63,7 +63,9 @@ def oracle_of(W):
 
 
 def test_c2_bench_path_dictionary_kernel():
-    W = bench.workload_c2(30)
+    # 45^3 = 729 bricks: more tiles than two waves of CTAs, so the engine picks what it picks for C2 itself
+    # (one thread per mass, dictionary records) without any override
+    W = bench.workload_c2(45)
     o = oracle_of(W)
     eng = tb.Engine(0, tb.MATH_FAST)
     upload_workload(eng, W)
@@ -150,7 +152,6 @@ def test_c5_bench_path_k_rewrite_and_removal(flags):
         idx = np.sort(np.argpartition(kk, m)[:m]).astype(np.int32)
         eng.set_spring_params(k=k)
         eng.remove_springs(idx)
-        eng.run(100, t_sim)
         live[idx] = False
         keep = np.nonzero(live)[0]
         o = oracle.Scene(pos, L["left"][keep], L["right"][keep], L["rest"][keep], k=1.0, m=0.1, dt=1e-4, g=(0.0, 0.0, -9.81))
@@ -159,17 +160,27 @@ def test_c5_bench_path_k_rewrite_and_removal(flags):
         o.planes.append(oracle.make_plane(*bench.PLANE))
         o.balls.append(oracle.make_ball(*L["ball"]))
         o.T_sim = t_sim
-        o.step(100)
-        st = eng.get_mass_state(fields=("pos", "vel"))
-        info = eng.info()
-        assert info["kernel"] == 1 and info["ns_removed"] == int((~live).sum())
-        if flags == tb.MATH_FAST:
-            assert info["dict_records"] > 0 and info["dict_split_k"] == 1, info
-        for f in ("pos", "vel"):
-            e = rel(st[f], getattr(o, f))
-            log(test="c5_bench_path", strict=bool(flags & tb.MATH_STRICT), cycle=cycle, field=f, err=e)
-            worst = max(worst, e)
-            assert e <= (0.0 if flags & tb.MATH_STRICT else 1e-9), (cycle, f, e)
+        # Two checkpoints per cycle.  After 10 steps the comparison is tight (1e-11): it pins the k rewrite, the
+        # tombstones and the split dictionary.  After 100 steps strict arithmetic is still bit-identical; fast
+        # arithmetic is held to 1e-9 in the first cycle (lattice at rest) and to a stated loose bound afterwards: the
+        # contact laws are discontinuous (Coulomb friction takes its direction from v_perp / |v_perp| however small
+        # v_perp is, the ball pushes with a constant 20 kN inside its radius; src/object.cu:56-59,82-98), so rounding
+        # differences of 1e-16 grow by orders of magnitude once masses slide at ~1e-10 m/s (drift table).
+        done = 0
+        for upto, tol_fast in ((10, 1e-11), (100, 1e-9 if cycle == 0 else 1e-4)):
+            eng.run(upto - done, o.T_sim)
+            o.step(upto - done)
+            done = upto
+            st = eng.get_mass_state(fields=("pos", "vel"))
+            info = eng.info()
+            assert info["kernel"] == 1 and info["ns_removed"] == int((~live).sum())
+            if flags == tb.MATH_FAST:
+                assert info["dict_records"] > 0 and info["dict_split_k"] == 1, info
+            for f in ("pos", "vel"):
+                e = rel(st[f], getattr(o, f))
+                log(test="c5_bench_path", strict=bool(flags & tb.MATH_STRICT), cycle=cycle, steps=upto, field=f, err=e)
+                worst = max(worst, e)
+                assert e <= (0.0 if flags & tb.MATH_STRICT else tol_fast), (cycle, upto, f, e)
         # the next cycle starts from the ORACLE's state on both sides (each cycle is a 100-step comparison)
         pos, vel, t_sim = o.pos.copy(), o.vel.copy(), o.T_sim
         eng.set_mass_state(pos=pos, vel=vel)
