@@ -219,6 +219,19 @@ TB_API int tb_export_indices_dev(tb_engine *e, const uint32_t **out_dev);
  * consumer uses in place of the reference's OpenGL buffer mapping (src/sim.cu:1982-2043) */
 TB_API int tb_read_device(tb_engine *e, void *dst_host, const void *src_dev, size_t bytes);
 
+/* ---- download that allocates nothing ------------------------------------------------------------------------------
+ * No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as tb_get_mass_state for
+ * pos and/or vel (NULL = skip), bit for bit, but the gather kernel's scratch is a file-scope `static __device__` array
+ * inside the library instead of the engine's growable staging buffer: the call makes no cudaMalloc / cudaFree.  At most
+ * tb_static_scratch_max_masses() (65,536) masses per call; more -> TB_ERR_INVALID with a message saying so (download in
+ * windows, or use tb_get_mass_state).  The array costs 1.75 MiB on every GPU that loads the library, until the process
+ * exits.  All calls on one device share it and it keeps the previous call's contents (nothing needs clearing: a call
+ * reads back only what it wrote); calls that overlap on the GPU -- engines of the same device driven from different
+ * threads -- race, so serialise them. */
+TB_API int64_t tb_static_scratch_max_masses(void);
+TB_API int tb_get_mass_state_static(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, double *pos, double *vel);
+
 /* page-locked host memory for upload/download buffers (the reference stages through pageable `new[]`
  * arrays, src/sim.cu:948-962,1099-1101); owned by the engine, released by tb_destroy */
 TB_API int tb_alloc_host(tb_engine *e, size_t bytes, void **out);

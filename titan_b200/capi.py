@@ -20,7 +20,8 @@ EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_l
            "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
            "tb_get_spring_rest", "tb_remove_springs", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
            "tb_run_async", "tb_sync", "tb_steps_done", "tb_wait_steps", "tb_last_run_ms", "tb_get_info",
-           "tb_export_positions_f32_dev", "tb_export_indices_dev", "tb_read_device", "tb_alloc_host", "tb_halo_set_ghosts", "tb_halo_prepare",
+           "tb_export_positions_f32_dev", "tb_export_indices_dev", "tb_read_device", "tb_alloc_host",
+           "tb_static_scratch_max_masses", "tb_get_mass_state_static", "tb_halo_set_ghosts", "tb_halo_prepare",
            "tb_halo_state_offsets", "tb_halo_connect", "tb_halo_set_exports", "tb_halo_push_now"]
 MAX_PEERS = 8
 HALO_HANDLE_BYTES = 320
@@ -93,6 +94,9 @@ def lib():
         L.tb_export_indices_dev.argtypes = [_vp, C.POINTER(_vp)]
         L.tb_read_device.argtypes = [_vp, _vp, _vp, C.c_size_t]
         L.tb_alloc_host.argtypes = [_vp, C.c_size_t, C.POINTER(_vp)]
+        L.tb_static_scratch_max_masses.restype = C.c_int64
+        L.tb_static_scratch_max_masses.argtypes = []
+        L.tb_get_mass_state_static.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp, _vp]
         L.tb_halo_set_ghosts.argtypes = [_vp, C.c_int64, _vp]
         L.tb_halo_prepare.argtypes = [_vp, _vp]
         L.tb_halo_state_offsets.argtypes = [_vp, C.c_int64, _vp, _vp]

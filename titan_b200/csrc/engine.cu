@@ -3,6 +3,8 @@
 // into CUDA graphs.  The step kernels themselves live in csr_step.cu and tiled.cu.
 #include "engine.h"
 
+#include <mutex>
+
 #include <algorithm>
 #include <cstdarg>
 #include <cstdio>
@@ -845,6 +847,73 @@ int tb_wait_steps(tb_engine *e, int64_t steps) {
     }
     if (best < 0) return TB_OK;                   // nothing enqueued yet
     TB_CUDA(e, cudaEventSynchronize(e->run_ev[best]));
+    return TB_OK;
+}
+
+}  // extern "C"
+
+// ---- download without any allocation: gather scratch in a file-scope device array ------------------------------------
+// tb_get_mass_state stages its gather through e->stage_dev, which grows by cudaMalloc on demand.  Callers that must not
+// allocate get this variant: the same gather kernel, its scratch in the array below.  Every GPU that loads the library
+// holds these 1.75 MiB until the process exits.  ONE array per device: every call on that device shares it (calls that
+// overlap on the GPU -- two engines of one device used from two threads -- race), and it keeps the previous call's
+// contents; nothing in it has to start at zero, a call reads back only what it has written first.
+namespace tb {
+constexpr int64_t STATIC_MAX_MASSES = 65536;
+constexpr size_t STATIC_IDX_BYTES = (size_t)STATIC_MAX_MASSES * 4;
+static __device__ __align__(256) unsigned char g_static_scratch[STATIC_IDX_BYTES + (size_t)STATIC_MAX_MASSES * 24];
+
+// In host code `g_static_scratch` is only a stand-in for the symbol, not a device address: the address is asked for
+// once per device, with that device current.
+static int static_scratch_ptr(Engine *e, unsigned char **out) {
+    constexpr int MAXD = 64;
+    static std::mutex mu;
+    static unsigned char *cached[MAXD] = {};
+    std::lock_guard<std::mutex> lock(mu);
+    int cur = -1;
+    TB_CUDA(e, cudaGetDevice(&cur));
+    if (cur != e->device) TB_CUDA(e, cudaSetDevice(e->device));
+    if (e->device < MAXD && cached[e->device]) { *out = cached[e->device]; return TB_OK; }
+    void *p = nullptr;
+    TB_CUDA(e, cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p) return fail(e, TB_ERR_CUDA, "cudaGetSymbolAddress returned a null address for the static scratch");
+    if (e->device < MAXD) cached[e->device] = (unsigned char *)p;
+    *out = (unsigned char *)p;
+    return TB_OK;
+}
+}  // namespace tb
+
+extern "C" {
+
+int64_t tb_static_scratch_max_masses(void) { return tb::STATIC_MAX_MASSES; }
+
+int tb_get_mass_state_static(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, double *pos, double *vel) {
+    E_CHECK(e);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_get_mass_state_static before tb_set_topology");
+    if (count > STATIC_MAX_MASSES)
+        return fail(e, TB_ERR_INVALID, "tb_get_mass_state_static: %lld masses exceed the static scratch (at most %lld per call; use "
+                    "tb_get_mass_state, or several calls)", (long long)count, (long long)STATIC_MAX_MASSES);
+    TB_TRY(check_range(e, e->nm, first, count, idx, "tb_get_mass_state_static"));
+    if (count == 0 || (!pos && !vel)) return TB_OK;
+    unsigned char *scratch = nullptr;
+    TB_TRY(static_scratch_ptr(e, &scratch));
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (e->canon_stale) TB_TRY(tiled_to_canonical(e));       // kernel + sync, no allocation
+    const int32_t *didx = nullptr;
+    if (idx) {
+        TB_CUDA(e, cudaMemcpyAsync(scratch, idx, (size_t)count * 4, cudaMemcpyHostToDevice, e->stream));
+        didx = (const int32_t *)scratch;
+    }
+    double *tmp = (double *)(scratch + STATIC_IDX_BYTES);
+    const double *src[2] = {e->pos[e->cur], e->vel[e->cur]};
+    double *dst[2] = {pos, vel};
+    for (int f = 0; f < 2; f++) {
+        if (!dst[f]) continue;
+        gather_vec3<<<blocks_for(count), 256, 0, e->stream>>>(tmp, src[f], e->nm, didx, first, count);
+        TB_CUDA(e, cudaGetLastError());
+        TB_CUDA(e, cudaMemcpyAsync(dst[f], tmp, (size_t)count * 24, cudaMemcpyDeviceToHost, e->stream));
+        TB_CUDA(e, cudaStreamSynchronize(e->stream));        // `tmp` is reused by the next field
+    }
     return TB_OK;
 }
 
