@@ -2,6 +2,8 @@
 # round-3 baseline on today's box: GPU suite, bench lines of the workloads the verdict names, source-level ncu of the step kernel
 TAG=${1:-r3a}; OUT=gpurun_out; mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.max.sm,power.limit --format=csv > $OUT/${TAG}_gpu.txt
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -x -q -m gpu > $OUT/${TAG}_pytest_zz_alone.log 2>&1; echo "zz alone rc=$?"; tail -1 $OUT/${TAG}_pytest_zz_alone.log
+python -m pytest tests -q -m gpu --collect-only 2>/dev/null | grep "::" | tail -2
 TB_PARITY_LOG=$OUT/${TAG}_parity_errors.jsonl timeout 1200 python -m pytest tests -q -m gpu > $OUT/${TAG}_pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -2 $OUT/${TAG}_pytest_gpu.log
 B="python bench.py --no-cpu-baseline --no-e2e"
 timeout 300 $B > $OUT/${TAG}_c2.json 2> $OUT/${TAG}_c2.err; echo "c2 rc=$?"
