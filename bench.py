@@ -141,6 +141,8 @@ def run_reference(args, rank, world):
     (plus a ghost plane); for C3 at most 64 robots -- spring-steps/s is normalised by the springs stepped."""
     if rank != 0:
         return
+    # torchrun exports OMP_NUM_THREADS=1 to its workers: the reference arm uses every host core, whatever launched it
+    os.environ["OMP_NUM_THREADS"] = str(args.ref_threads or os.cpu_count() or 1)
     import oracle
     if args.workload == "c4":
         from titan_b200 import lattice, partition
@@ -184,6 +186,117 @@ def run_reference(args, rank, world):
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), flush=True)
+
+
+FACADE_DRIVER = os.path.join(ROOT, "tests", "cpp", "bin", "titan_facade_dump")   # tests/cpp/titan_api_driver.cu against libTitan.so
+TITAN_CUDA = os.path.join(ROOT, "oracle", "_ref", "titan_ref_cuda")               # the same driver against the reference's own CUDA engine
+
+
+def _last_json(text):
+    for line in reversed(text.splitlines()):
+        line = line.strip()
+        if line.startswith("{"):
+            try:
+                return json.loads(line)
+            except ValueError:
+                continue
+    return None
+
+
+def facade_e2e(config, inner, batches, timeout=600):
+    """`e2e` through the API the reference's users call: a C++ program (tests/cpp/titan_api_driver.cu, mode bench_e2e)
+    builds the workload with titan::Simulation::createLattice/createPlane and times, per batch, setAll() (host Mass /
+    Spring objects -> device) + resume() + pause(t + inner dt) + getAll() (device -> host Mass objects)."""
+    if not os.path.exists(FACADE_DRIVER):
+        return {"unavailable": "tests/cpp/bin/titan_facade_dump is not built"}
+    try:
+        r = subprocess.run([FACADE_DRIVER, "bench_e2e", config, str(inner), str(batches)], capture_output=True, text=True, timeout=timeout)
+    except subprocess.TimeoutExpired:
+        return {"unavailable": "facade driver timed out"}
+    d = _last_json(r.stdout)
+    if r.returncode != 0 or d is None:
+        return {"unavailable": "facade driver failed (rc %d): %s" % (r.returncode, (r.stderr or r.stdout)[-200:])}
+    return {"value": d["spring_steps_per_s"], "unit": UNIT, "h2d_bytes_per_step": int(d["h2d_bytes_per_batch"]),
+            "d2h_bytes_per_step": int(d["d2h_bytes_per_batch"]), "ms_per_step": 1e3 * d["seconds"] / max(1, d["batches"]),
+            "sim_steps": int(d["steps"]), "batches": int(d["batches"]), "start_seconds": d["upload_seconds"],
+            "call": "titan::Simulation::setAll() + resume() + pause(t) + getAll() on host Mass/Spring objects (libTitan.so)"}
+
+
+def titan_cuda_baseline(config, steps, timeout=900):
+    """Titan's own CUDA kernels (reference sources, headless-patched, built for sm_100a by oracle/build_ref.sh) on this GPU:
+    wall clock around Simulation::pause for `steps` steps, start()'s upload reported separately."""
+    if not os.path.exists(TITAN_CUDA):
+        return {"unavailable": "oracle/_ref/titan_ref_cuda is not built (needs /root/reference at build time)"}
+    try:
+        r = subprocess.run([TITAN_CUDA, "bench", config, str(steps)], capture_output=True, text=True, timeout=timeout)
+    except subprocess.TimeoutExpired:
+        return {"unavailable": "titan_ref_cuda timed out"}
+    d = _last_json(r.stdout)
+    if r.returncode != 0 or d is None:
+        return {"unavailable": "titan_ref_cuda failed (rc %d)" % r.returncode}
+    return {"value": d["spring_steps_per_s"], "unit": UNIT, "steps": int(d["steps"]), "seconds": d["seconds"],
+            "upload_seconds": d["upload_seconds"], "kind": "reference CUDA kernels (computeSpringForces + massForcesAndUpdate, src/sim.cu) on the same GPU"}
+
+
+def parity_n(tb, dist, local_rank, rank, world):
+    """N > 1, before anything is timed: the ranks step a 48 x 24 x 24 lattice cut into i-slabs (halo exchange over peer
+    memory) for 230 steps, rank 0 steps the whole lattice on one engine; max |difference| over pos and vel, strict and fast
+    arithmetic.  Strict must be bit-identical, fast <= 1e-12; otherwise the run fails."""
+    import torch
+    from titan_b200 import distributed, lattice, partition
+    n, steps = (48, 24, 24), 230
+    c, d = (0.0, 0.0, 0.1 * (n[2] - 1) / 2 - 0.001), (0.1 * (n[0] - 1), 0.1 * (n[1] - 1), 0.1 * (n[2] - 1))
+    saved = os.environ.get("TB_TPM")
+    os.environ["TB_TPM"] = "1"      # the single engine sums per mass like the partitioned ones (one thread per mass)
+    out = {}
+    try:
+        for flags, label, tol in ((tb.MATH_STRICT, "strict_max_abs", 0.0), (tb.MATH_FAST, "fast_max_abs", 1e-12)):
+            part = partition.LatticeSlab(c, d, n[0], n[1], n[2], rank, world)
+            eng = tb.Engine(local_rank, flags)
+            distributed.upload_slab(eng, part, planes=[PLANE])
+            distributed.connect(eng, part)
+            t = 0.0
+            for chunk in (1, 29, steps - 30):
+                eng.run_async(chunk, t)
+                eng.sync()
+                for _ in range(chunk):
+                    t += 1e-4
+            dist.barrier()
+            st = eng.get_mass_state(idx=part.own_local, fields=("pos", "vel"))
+            eng.close()
+            gathered = [None] * world
+            dist.all_gather_object(gathered, (part.mass_gid[part.own_local], st["pos"], st["vel"]))
+            err = torch.zeros(1, dtype=torch.float64, device="cuda")
+            if rank == 0:
+                L = lattice.build_lattice(c, d, *n)
+                ref = tb.Engine(local_rank, flags)
+                ref.set_topology(L["pos"].shape[0], L["left"], L["right"])
+                ref.set_tile_hint(lattice.brick_hint(*n))
+                ref.set_mass_state(pos=L["pos"])
+                ref.set_spring_params(rest=L["rest"])
+                ref.set_planes([tb.Plane((tb.capi.C.c_double * 3)(*PLANE[0]), *PLANE[1:])])
+                ref.set_globals((0.0, 0.0, -9.81), 1e-4)
+                ref.run(steps, 0.0)
+                want = ref.get_mass_state(fields=("pos", "vel"))
+                ref.close()
+                e = 0.0
+                for gid, pos, vel in gathered:
+                    e = max(e, float(np.max(np.abs(pos - want["pos"][gid]))), float(np.max(np.abs(vel - want["vel"][gid]))))
+                err[0] = e
+            dist.broadcast(err, 0)
+            out[label] = float(err.item())
+            if not out[label] <= tol:
+                if rank == 0:
+                    print(json.dumps({"error": "N>1 parity check failed", "parity_n": out}), flush=True)
+                dist.barrier()
+                raise SystemExit(1)
+    finally:
+        if saved is None:
+            os.environ.pop("TB_TPM", None)
+        else:
+            os.environ["TB_TPM"] = saved
+    out["check"] = "48x24x24 lattice in %d i-slabs, 230 steps, vs one engine" % world
+    return out
 
 
 C4_EDGE = {1: 150, 2: 189, 4: 238, 8: 300}     # SURVEY.md 8(d): ~3.4 M masses per GPU; 300^3 on 8 GPUs is config C4
@@ -316,6 +429,11 @@ def main():
                     help="give every spring its own k (defeats the dictionary records: one record per spring is streamed)")
     ap.add_argument("--verlet", action="store_true", help="the reference's VERLET build option instead of its default Euler step")
     ap.add_argument("--no-hint", action="store_true", help="let the engine bisect positions instead of lattice bricks")
+    ap.add_argument("--ref-threads", type=int, default=0, help="--impl reference: OpenMP threads (default: all host cores)")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the N=1 extras of the default line: facade e2e, Titan-CUDA baseline, 150^3 weak-scaling base, distinct-parameter roofline")
+    ap.add_argument("--no-titan-cuda", action="store_true", help="skip the Titan-CUDA baseline (its start() alone takes about 70 s on C2)")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip the partition-vs-single-engine parity check before timing")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -350,6 +468,9 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
         return float(t.item())
 
+    parity = None
+    if world > 1 and args.workload == "c4" and not args.no_parity:
+        parity = parity_n(tb, dist, local_rank, rank, world)
     flags = (tb.MATH_STRICT if args.strict else tb.MATH_FAST) | (tb.KERNEL_CSR if args.csr else 0)
     if args.verlet:
         flags |= tb.INTEGRATOR_VERLET
@@ -473,6 +594,52 @@ def main():
     if rank == 0 and world == 1 and not args.no_cpu_baseline and args.workload == "c2":
         cpu = cpu_port(W)
 
+    # ---- N = 1 extras of the default line ------------------------------------------------------------------
+    extras = {}
+    default_line = (world == 1 and args.workload == "c2" and not args.no_extras and not args.distinct_params
+                    and not args.strict and not args.csr and not args.verlet)
+    if default_line:
+        def timed(engine, nsteps, warm):
+            t = 0.0
+            engine.run_async(warm, t)
+            engine.sync()
+            engine.run_async(nsteps, warm * dt)
+            engine.sync()
+            return engine.last_run_ms()
+        # (1) the same lattice with one stiffness per spring: no two (k, rest) records alike -> the general-system figure
+        ns_eng = info["ns"]
+        eng.set_spring_params(k=1e4 * (1.0 + 1e-6 * np.arange(ns_eng, dtype=np.float64) / max(1, ns_eng)))
+        ms = timed(eng, sim_steps, args.warmup * inner)
+        us = ms * 1e3 / sim_steps
+        di = eng.info()
+        roofline["distinct_params"] = {"achieved": alg_bytes / (us * 1e-6) / 1e9, "frac": alg_bytes / (us * 1e-6) / 1e9 / peak,
+                                       "value": ns_total * sim_steps / (ms * 1e-3), "avg_launch_us": us,
+                                       "dict_records": di["dict_records"], "dict_split_k": di["dict_split_k"],
+                                       "what": "same lattice, every spring its own k (tb_set_spring_params): stiffness streamed per spring"}
+        eng.close()
+        eng = None
+        # (2) weak-scaling base of SURVEY.md 8(e): the 150^3 lattice (one GPU's share of C4) on this GPU alone
+        from titan_b200 import distributed, partition
+        nb = C4_EDGE[1]
+        pb = partition.LatticeSlab((0.0, 0.0, 0.05 * (nb - 1) - 0.001), tuple(0.1 * (nb - 1) for _ in range(3)), nb, nb, nb, 0, 1)
+        eb = tb.Engine(local_rank, flags)
+        distributed.upload_slab(eb, pb, planes=[PLANE])
+        ms = timed(eb, sim_steps, args.warmup * inner)
+        extras["weak_base"] = {"size": nb, "masses": int(pb.nm_own), "springs": int(pb.ns_owned),
+                               "value": pb.ns_owned * sim_steps / (ms * 1e-3), "unit": UNIT, "avg_launch_us": ms * 1e3 / sim_steps,
+                               "frac": (104.0 * pb.nm_own + 24.0 * pb.ns_owned) / (ms * 1e-3 / sim_steps) / 1e9 / peak}
+        eb.close()
+        del pb
+        # (3) Titan's own CUDA kernels on this GPU, (4) e2e through titan::Simulation
+        if not args.no_titan_cuda:
+            extras["titan_cuda_baseline"] = titan_cuda_baseline("c2" if args.size == 100 else "lattice%d" % args.size, 200)
+        fe = facade_e2e("c2" if args.size == 100 else "lattice%d" % args.size, inner, args.steps)
+        extras["e2e_cabi"] = e2e
+        if "value" in fe:
+            e2e = fe
+        else:
+            extras["e2e_facade"] = fe
+
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": dev_ms / args.steps, "higher_is_better": True,
@@ -488,9 +655,13 @@ def main():
                            "timing": "CUDA events on the engine stream, max over ranks", "wall_ms": wall * 1e3},
                 "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches) * world,
                 "clocks": clocks.summary()}
+        line.update(extras)
+        if parity is not None:
+            line["parity_n"] = parity
         print(json.dumps(line), flush=True)
     barrier()
-    eng.close()
+    if eng is not None:
+        eng.close()
     if dist is not None:
         dist.destroy_process_group()
 

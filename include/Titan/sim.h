@@ -145,6 +145,11 @@ private:
     void upload_constraints();             // global planes/balls + globals (g, dt)
     void upload_local_constraints();
     void sync_topology();                  // re-upload after create*/delete* while paused, keeping device state
+    struct HostStage;                      // pinned staging arrays + shadow of the parameter arrays the device holds (sim.cpp)
+    HostStage *hs = nullptr;
+    bool upload_masses_whole();            // setAll / start fast paths: packed by all host cores into pinned memory, parameter
+    bool upload_springs_whole();           //   arrays uploaded only when they differ from what the device already holds
+    bool download_masses_whole();
     std::vector<std::vector<LocalConstraintRecord>> dev_local;   // per engine slot: what the device currently holds
     bool topology_dirty = false, constraints_dirty = true, local_dirty = false;
     std::vector<Mass *> zombies;           // deleted masses still referenced by springs (freed with the simulation)

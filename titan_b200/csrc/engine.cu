@@ -525,12 +525,13 @@ int tb_get_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
     }
     if (T) {
         // masses uploaded together share (T0, n0): memoise the last replay
-        double key_T0 = 0, val = 0; int64_t key_n0 = -1; uint8_t key_f = 0xff;
+        double key_T0 = 0, val = 0; int64_t key_n0 = -1;
         for (int64_t j = 0; j < count; j++) {
             int64_t i = idx ? idx[j] : first + j;
             uint8_t f = (uint8_t)(e->h_flags[(size_t)i] & (F_FIXED | F_VALID));
-            if (!(key_n0 == e->h_n0[(size_t)i] && key_f == f && memcmp(&key_T0, &e->h_T0[(size_t)i], 8) == 0)) {
-                key_T0 = e->h_T0[(size_t)i]; key_n0 = e->h_n0[(size_t)i]; key_f = f;
+            if ((f & F_FIXED) || !(f & F_VALID)) { T[j] = e->h_T0[(size_t)i]; continue; }   // frozen: no replay, memo untouched
+            if (!(key_n0 == e->h_n0[(size_t)i] && memcmp(&key_T0, &e->h_T0[(size_t)i], 8) == 0)) {
+                key_T0 = e->h_T0[(size_t)i]; key_n0 = e->h_n0[(size_t)i];
                 val = replay_T(e, i, f);
             }
             T[j] = val;
@@ -554,6 +555,7 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
         TB_TRY(up_scalar<double>(e, e->damping, damping, idx, first, count));
         e->any_damping = true;
     }
+    bool type_changed = false;    // the tile structure encodes the actuation class per incidence word: rebuilt only on a real change
     if (type) {
         bool nonpassive = false;
         for (int64_t j = 0; j < count; j++) {
@@ -561,7 +563,11 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
             nonpassive |= type[j] >= 2;
         }
         if (e->h_type.size() != (size_t)e->ns) e->h_type.assign((size_t)e->ns, 0);
-        for (int64_t j = 0; j < count; j++) e->h_type[(size_t)(idx ? idx[j] : first + j)] = (uint8_t)type[j];
+        for (int64_t j = 0; j < count; j++) {
+            uint8_t &held = e->h_type[(size_t)(idx ? idx[j] : first + j)];
+            type_changed |= (held < 2 ? 0 : held) != (type[j] < 2 ? 0 : type[j]);   // PASSIVE_SOFT and PASSIVE_STIFF are one class
+            held = (uint8_t)type[j];
+        }
         e->any_active = e->any_actuated = false;
         for (uint8_t ty : e->h_type) { if (ty == 2 || ty == 3) e->any_active = true; if (ty >= 4) e->any_actuated = true; }
         if (e->type || nonpassive) {
@@ -584,7 +590,7 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
         apply_tombstones_kernel<<<blocks_for(e->ns), 256, 0, e->stream>>>(e->k, e->damping, e->removed_dev, e->ns);
         TB_CUDA(e, cudaGetLastError());
     }
-    e->tiled_stale |= TS_PARAMS | (type ? TS_STRUCT : 0u);
+    e->tiled_stale |= TS_PARAMS | (type_changed ? TS_STRUCT : 0u);
     e->graph_dirty = true;
     return TB_OK;
 }

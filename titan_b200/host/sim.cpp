@@ -11,10 +11,13 @@
 #include <array>
 #include <cassert>
 #include <chrono>
+#include <cstdlib>
+#include <cstring>
 #include <deque>
 #include <iostream>
 #include <limits>
 #include <stdexcept>
+#include <thread>
 #include <unordered_set>
 
 namespace titan {
@@ -388,9 +391,124 @@ struct MassPack {   // contiguous arrays for one tb_set_mass_state / tb_set_mass
 
 }  // namespace
 
+// ---- whole-simulation transfers (setAll / getAll / start) --------------------------------------------------------
+// The reference's setAll()/getAll() rebuild a packed array of 240-byte CUDA_MASS / 80-byte CUDA_SPRING structs on one host
+// thread and copy it through pageable memory (src/sim.cu:720-765,1094-1116).  Here the host objects are packed by all
+// host cores straight into page-locked staging arrays (pos, vel, T every time: the dynamic state), and the parameter
+// arrays (m, fixed, drag, magnet fields; k, rest, damping, type, omega, l_max, l_min, rate) are compared with a shadow of
+// what the device already holds and uploaded only when they differ -- same device contents afterwards, a fraction of the
+// bytes and none of the tile-structure rebuilds a spring-type upload would otherwise trigger.
+template <class F> static void parallel_for(size_t n, F f) {
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nt = n < 32768 ? 1u : std::min(32u, hw);
+    if (nt == 1) { f((size_t)0, n); return; }
+    std::vector<std::thread> th;
+    const size_t per = (n + nt - 1) / nt;
+    for (unsigned t = 0; t < nt; t++) {
+        const size_t lo = std::min(n, t * per), hi = std::min(n, lo + per);
+        if (lo < hi) th.emplace_back([=, &f] { f(lo, hi); });
+    }
+    for (std::thread &t : th) t.join();
+}
+
+// TITAN_B200_TIMING=1: wall-clock phases of the whole-simulation transfers on stderr
+struct PhaseTimer {
+    const char *what; bool on; std::chrono::steady_clock::time_point t0;
+    explicit PhaseTimer(const char *w) : what(w), on(getenv("TITAN_B200_TIMING") != nullptr), t0(std::chrono::steady_clock::now()) {}
+    void lap(const char *phase) {
+        if (!on) return;
+        auto t1 = std::chrono::steady_clock::now();
+        std::cerr << "[titan_b200] " << what << ": " << phase << " " << std::chrono::duration<double, std::milli>(t1 - t0).count() << " ms" << std::endl;
+        t0 = t1;
+    }
+};
+
+struct Simulation::HostStage {
+    size_t cap = 0;
+    double *pos = nullptr, *vel = nullptr, *acc = nullptr, *T = nullptr, *ext = nullptr;   // pinned (owned by the engine)
+    bool mass_valid = false, spring_valid = false, ext_uploaded_nonzero = false;
+    std::vector<double> m, rad, stiff, maxmag, magscale, k, rest, damping, omega, lmax, lmin, rate;
+    std::vector<uint8_t> fixed;
+    std::vector<int32_t> drag, type;
+};
+
+bool Simulation::upload_masses_whole() {
+    const size_t n = masses.size();
+    if (n == 0 || !engine) return false;
+    if (!hs) hs = new HostStage();
+    PhaseTimer pt("setAll masses");
+    if (hs->cap < n) {
+        const size_t cap = n + n / 4 + 1024;
+        void *p = nullptr;
+        engine_check(tb_alloc_host(engine, cap * 13 * sizeof(double), &p), "tb_alloc_host");
+        double *d = (double *)p;
+        hs->pos = d; hs->vel = d + 3 * cap; hs->acc = d + 6 * cap; hs->ext = d + 9 * cap; hs->T = d + 12 * cap;
+        hs->cap = cap;
+    }
+    const bool first = !hs->mass_valid || hs->m.size() != n;
+    if (first) {
+        hs->m.resize(n); hs->rad.resize(n); hs->stiff.resize(n); hs->maxmag.resize(n); hs->magscale.resize(n);
+        hs->fixed.resize(n); hs->drag.resize(n);
+    }
+    std::atomic<bool> in_order{true}, ext_nonzero{false}, lc_changed{false};
+    std::atomic<unsigned> changed{0};
+    auto differs = [](double a, double b) { return std::memcmp(&a, &b, 8) != 0; };
+    parallel_for(n, [&](size_t lo, size_t hi) {
+        bool nz = false, lc = false;
+        unsigned ch = 0;
+        for (size_t j = lo; j < hi; j++) {
+            Mass *q = masses[j];
+            if (q->slot != (int32_t)j) { in_order = false; return; }
+            for (int c = 0; c < 3; c++) {
+                hs->pos[3 * j + c] = q->pos[c]; hs->vel[3 * j + c] = q->vel[c]; hs->ext[3 * j + c] = q->extern_force[c];
+                nz |= q->extern_force[c] != 0.0;
+            }
+            hs->T[j] = q->T;
+            if (differs(hs->m[j], q->m)) { hs->m[j] = q->m; ch |= 1u; }
+            const uint8_t fx = q->fixed ? 1 : 0;
+            if (hs->fixed[j] != fx) { hs->fixed[j] = fx; ch |= 2u; }
+            const int32_t dr = (int32_t)q->drag_coefficient;   // int truncation, include/Titan/object.h:213
+            if (hs->drag[j] != dr) { hs->drag[j] = dr; ch |= 4u; }
+            if (differs(hs->rad[j], q->rad)) { hs->rad[j] = q->rad; ch |= 8u; }
+            if (differs(hs->stiff[j], q->stiffness)) { hs->stiff[j] = q->stiffness; ch |= 8u; }
+            if (differs(hs->maxmag[j], q->max_mag_force)) { hs->maxmag[j] = q->max_mag_force; ch |= 8u; }
+            if (differs(hs->magscale[j], q->mag_scale_factor)) { hs->magscale[j] = q->mag_scale_factor; ch |= 8u; }
+            std::vector<LocalConstraintRecord> &held = dev_local[j];
+            bool same = held.size() == q->local.size();
+            for (size_t r = 0; same && r < held.size(); r++)
+                same = held[r].kind == q->local[r].kind && held[r].vec == q->local[r].vec && held[r].num == q->local[r].num;
+            if (!same) { held = q->local; lc = true; }
+        }
+        if (nz) ext_nonzero = true;
+        if (lc) lc_changed = true;
+        if (ch) changed |= ch;
+    });
+    if (!in_order) { hs->mass_valid = false; return false; }
+    pt.lap("pack");
+    const unsigned ch = first ? 0xfu : changed.load();
+    // the device consumes extern_force (one shot, src/sim.cu:1365) but fixed masses keep theirs: upload whenever this or the
+    // previous upload carried a non-zero force
+    const bool up_ext = ext_nonzero || hs->ext_uploaded_nonzero || first;
+    std::vector<uint8_t> valid;
+    if (first) valid.assign(n, 1);
+    engine_check(tb_set_mass_state(engine, 0, (int64_t)n, nullptr, hs->pos, hs->vel, (ch & 1u) ? hs->m.data() : nullptr, hs->T,
+                                   up_ext ? hs->ext : nullptr, (ch & 2u) ? hs->fixed.data() : nullptr, (ch & 4u) ? hs->drag.data() : nullptr,
+                                   first ? valid.data() : nullptr), "tb_set_mass_state");
+    hs->ext_uploaded_nonzero = ext_nonzero;
+    if (ch & 8u)
+        engine_check(tb_set_mass_magnet(engine, 0, (int64_t)n, nullptr, hs->rad.data(), hs->stiff.data(), hs->maxmag.data(), hs->magscale.data()), "tb_set_mass_magnet");
+    hs->mass_valid = true;
+    if (lc_changed) local_dirty = true;
+    if (local_dirty) upload_local_constraints();
+    pt.lap("upload");
+    return true;
+}
+
 // CUDA_MASS(Mass&), src/mass.cu:74-100: m, T, pos, vel, extern_force, magnet fields, fixed, drag, valid = true.
 void Simulation::upload_masses(Mass *const *list, size_t count) {
     if (count == 0) return;
+    if (list == masses.data() && count == masses.size() && upload_masses_whole()) return;
+    if (hs) hs->mass_valid = false;        // a partial upload: the shadow no longer mirrors the device
     MassPack P;
     P.reserve(count);
     bool lc_changed = false;
@@ -420,9 +538,84 @@ void Simulation::upload_masses(Mass *const *list, size_t count) {
     if (local_dirty) upload_local_constraints();
 }
 
+bool Simulation::upload_springs_whole() {
+    const size_t n = springs.size();
+    if (n == 0 || !engine) return false;
+    if (!hs) hs = new HostStage();
+    PhaseTimer pt("setAll springs");
+    const bool first = !hs->spring_valid || hs->k.size() != n;
+    if (first) {
+        hs->k.resize(n); hs->rest.resize(n); hs->damping.resize(n); hs->omega.resize(n); hs->lmax.resize(n); hs->lmin.resize(n);
+        hs->rate.resize(n); hs->type.resize(n);
+    }
+    // one pass over the host objects by all cores: every field is compared with the shadow IN PLACE (bit pattern) and the
+    // shadow updated, so afterwards the shadow holds the new values and the flags say which arrays the device lacks
+    std::atomic<bool> in_order{true}, actuated{false};
+    std::atomic<unsigned> changed{0};
+    auto differs = [](double a, double b) { return std::memcmp(&a, &b, 8) != 0; };
+    parallel_for(n, [&](size_t lo, size_t hi) {
+        bool act = false;
+        unsigned ch = 0;
+        for (size_t j = lo; j < hi; j++) {
+            const Spring *sp = springs[j];
+            if (sp->slot != (int32_t)j) { in_order = false; return; }
+            if (differs(hs->k[j], sp->_k)) { hs->k[j] = sp->_k; ch |= 1u; }
+            if (differs(hs->rest[j], sp->_rest)) { hs->rest[j] = sp->_rest; ch |= 2u; }
+            if (differs(hs->damping[j], sp->_damping)) { hs->damping[j] = sp->_damping; ch |= 4u; }
+            if (differs(hs->omega[j], sp->_omega)) { hs->omega[j] = sp->_omega; ch |= 8u; }
+            if (differs(hs->lmax[j], sp->_l_max)) { hs->lmax[j] = sp->_l_max; ch |= 16u; }
+            if (differs(hs->lmin[j], sp->_l_min)) { hs->lmin[j] = sp->_l_min; ch |= 32u; }
+            if (differs(hs->rate[j], sp->_rate)) { hs->rate[j] = sp->_rate; ch |= 64u; }
+            if (hs->type[j] != (int32_t)sp->_type) { hs->type[j] = (int32_t)sp->_type; ch |= 128u; }
+            act |= sp->_type == ACTUATED_EXPAND || sp->_type == ACTUATED_CONTRACT;
+        }
+        if (act) actuated = true;
+        if (ch) changed |= ch;
+    });
+    if (!in_order) { hs->spring_valid = false; return false; }
+    pt.lap("scan");
+    unsigned ch = first ? 0xffu : changed.load();
+    if (actuated) ch |= 2u;                  // the device advances _rest of ACTUATED_* springs: the host value always goes down
+    if (ch)
+        engine_check(tb_set_spring_params(engine, 0, (int64_t)n, nullptr, (ch & 1u) ? hs->k.data() : nullptr, (ch & 2u) ? hs->rest.data() : nullptr,
+                                          (ch & 4u) ? hs->damping.data() : nullptr, (ch & 128u) ? hs->type.data() : nullptr,
+                                          (ch & 8u) ? hs->omega.data() : nullptr, (ch & 16u) ? hs->lmax.data() : nullptr,
+                                          (ch & 32u) ? hs->lmin.data() : nullptr, (ch & 64u) ? hs->rate.data() : nullptr), "tb_set_spring_params");
+    hs->spring_valid = true;
+    pt.lap("upload");
+    return true;
+}
+
+bool Simulation::download_masses_whole() {
+    const size_t n = masses.size();
+    if (n == 0 || !engine || !hs || hs->cap < n) return false;
+    std::atomic<bool> in_order{true};
+    parallel_for(n, [&](size_t lo, size_t hi) {
+        for (size_t j = lo; j < hi; j++) if (masses[j]->slot != (int32_t)j) { in_order = false; return; }
+    });
+    if (!in_order) return false;
+    PhaseTimer pt("getAll");
+    engine_check(tb_get_mass_state(engine, 0, (int64_t)n, nullptr, hs->pos, hs->vel, hs->acc, hs->T, hs->ext), "tb_get_mass_state");
+    pt.lap("download");
+    parallel_for(n, [&](size_t lo, size_t hi) {
+        for (size_t j = lo; j < hi; j++) {
+            Mass *q = masses[j];
+            q->pos = Vec(hs->pos[3 * j], hs->pos[3 * j + 1], hs->pos[3 * j + 2]);
+            q->vel = Vec(hs->vel[3 * j], hs->vel[3 * j + 1], hs->vel[3 * j + 2]);
+            q->acc = Vec(hs->acc[3 * j], hs->acc[3 * j + 1], hs->acc[3 * j + 2]);
+            q->extern_force = Vec(hs->ext[3 * j], hs->ext[3 * j + 1], hs->ext[3 * j + 2]);
+            q->T = hs->T[j];
+        }
+    });
+    pt.lap("unpack");
+    return true;
+}
+
 // CUDA_SPRING(const Spring&), src/spring.cu:37-63.  Endpoints are topology and only change through sync_topology().
 void Simulation::upload_springs(Spring *const *list, size_t count) {
     if (count == 0) return;
+    if (list == springs.data() && count == springs.size() && upload_springs_whole()) return;
+    if (hs) hs->spring_valid = false;
     std::vector<int32_t> idx, type;
     std::vector<double> k, rest, damping, omega, lmax, lmin, rate;
     for (size_t j = 0; j < count; j++) {
@@ -441,6 +634,7 @@ void Simulation::upload_springs(Spring *const *list, size_t count) {
 
 // Mass::operator=(CUDA_MASS&), src/mass.cu:21-49: the device changes pos, vel, acc, T and consumes extern_force.
 void Simulation::download_masses(Mass *const *list, size_t count) {
+    if (list == masses.data() && count == masses.size() && download_masses_whole()) return;
     std::vector<int32_t> idx;
     std::vector<Mass *> who;
     for (size_t j = 0; j < count; j++) if (list[j]->slot >= 0) { idx.push_back(list[j]->slot); who.push_back(list[j]); }
@@ -509,6 +703,7 @@ void Simulation::upload_everything() {
         right[(size_t)s] = (sp->_right && sp->_right->valid) ? sp->_right->slot : -1;
     }
     engine_check(tb_set_topology(engine, nm, ns, left.data(), right.data()), "tb_set_topology");
+    if (hs) { hs->mass_valid = hs->spring_valid = hs->ext_uploaded_nonzero = false; }   // the device is back at its defaults
 
     // tile hint: bricks of lattice cells when every mass belongs to exactly one regular grid container
     std::vector<int32_t> hint((size_t)nm, -1);
@@ -822,6 +1017,7 @@ void Simulation::stop(double t) {   // src/sim.cu:1533-1545
 void Simulation::freeGPU() {
     if (FREED) return;
     if (engine) { tb_destroy(engine); engine = nullptr; }
+    delete hs; hs = nullptr;               // its pinned arrays went with the engine
     for (Spring *s : springs) delete s;
     for (Mass *m : masses) delete m;
     for (Mass *m : zombies) delete m;
