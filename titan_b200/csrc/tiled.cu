@@ -53,6 +53,11 @@ constexpr int MAX_LOCAL = 512;
 constexpr int MAX_REC = 4096;
 constexpr int CS_SMALL = 384, CS_BIG = MAX_LOCAL;   // shared-memory stride of one position component (see plan_smem)
 constexpr int ELL_CHUNK = 4;            // springs evaluated together, branch-free, by one thread (ILP)
+// Local indices [cs - N_DUMMY, cs) of every position array are DUMMY masses (far away, at rest, never written by a copy):
+// padding incidence words point at one of them and at record 0 (k = 0), and so contribute exactly zero.  Sixteen of them,
+// one per 8-byte bank pair, so that a padding lane never collides with the live lanes of its half-warp.
+constexpr int N_DUMMY = 16;
+constexpr uint32_t PAD_NB = 512 - N_DUMMY;   // provisional dummy index in a padding word (rebased once cs is known)
 
 // Which of a mass's TPM threads takes which ELL rows, in chunks of ELL_CHUNK rows (blocks are padded with zero
 // rows to a whole number of chunks).  Thread 0 also runs the mass update (worth about MASS_UPDATE_ROWS springs),
@@ -259,9 +264,8 @@ struct SmemPlan {            // byte offsets inside the dynamic shared memory of
 constexpr int MAX_STAGES = 4;
 // mbarriers at offset 0: full[MAX_STAGES], empty[MAX_STAGES], hfull[HALO_RING]; tile control words at 128
 // Position component stride is a compile-time constant of the kernel (CS_SMALL or CS_BIG doubles) so that the
-// y and z reads are immediate offsets from the x address.  Local index cs-1 is the DUMMY mass (far away, never
-// written by a copy): padding ELL words point at it and at record 0 (k = 0), and so contribute exactly zero.
-static int choose_cs(int max_halo, bool strict) { return (!strict && TM + max_halo + 1 <= CS_SMALL) ? CS_SMALL : CS_BIG; }
+// y and z reads are immediate offsets from the x address.  The last N_DUMMY local indices are the dummy masses.
+static int choose_cs(int max_halo, bool strict) { return (!strict && TM + max_halo + N_DUMMY <= CS_SMALL) ? CS_SMALL : CS_BIG; }
 static SmemPlan plan_smem(int cs, int max_halo, int max_blob, bool stage_vel, int tpm, int nst) {
     SmemPlan p;
     p.nst = nst;
@@ -433,6 +437,9 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
     std::vector<int32_t> rec_stamp((size_t)e->ns, -1), rec_local((size_t)e->ns, 0);
     struct Half { int32_t s; int32_t o; uint8_t side; };
     std::vector<std::vector<Half>> rows(TM);
+    std::vector<Half> aligned;
+    int cjs[MAX_DEG];
+    const bool align_rows = !(getenv("TB_ALIGN_ROWS") && atoi(getenv("TB_ALIGN_ROWS")) == 0);   // measurement aid
     std::vector<int32_t> th;   // halo list of the tile being built (-1 = hole)
     int max_halo = 0, max_rec = 0, max_deg = 0;
     size_t blob_total = 0, max_blob = 0;
@@ -454,6 +461,31 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
             deg = std::max(deg, (int)rows[t].size());
         }
         if (deg > MAX_DEG) { S->why_not = "a mass has more incident springs than the ELL format holds"; return TB_OK; }
+        // Row alignment: a mass with fewer springs than the tile's fullest one (a lattice surface) gets HOLES so that its
+        // springs sit in the rows of the same springs of a full mass -- "same" = same offset in API index, which on a
+        // lattice is the direction.  Order per mass is unchanged (ascending spring index), only padding moves; every row
+        // then holds one direction, its in-tile neighbours are t + const, and a half-warp's reads spread over all banks.
+        // A mass whose offsets are no subsequence of the template's keeps its compact rows.
+        if (deg > 1 && align_rows) {
+            int tmpl = -1;
+            for (int t = 0; t < TM && tmpl < 0; t++) if ((int)rows[t].size() == deg) tmpl = t;
+            const int32_t i_tmpl = S->h_slot_to_api[(size_t)(T * TM + tmpl)];
+            for (int t = 0; t < TM; t++) {
+                const int d = (int)rows[t].size();
+                if (d == 0 || d == deg) continue;
+                const int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
+                aligned.assign((size_t)deg, Half{-1, 0, 0});
+                int p = 0;
+                bool ok = true;
+                for (int q = 0; q < d && ok; q++) {
+                    const int32_t key = rows[t][(size_t)q].o - i;
+                    while (p < deg && rows[tmpl][(size_t)p].o - i_tmpl != key) p++;
+                    if (p == deg) ok = false; else aligned[(size_t)p++] = rows[t][(size_t)q];
+                }
+                if (ok) rows[t] = aligned;
+            }
+        }
+        auto has = [&](int t, int j) { return j < (int)rows[t].size() && rows[t][(size_t)j].s >= 0; };
         TileMeta &M = meta[(size_t)T];
         M.deg = (uint32_t)deg;
         while (halo.size() % 4) halo.push_back(0);               // 16-byte aligned halo lists (bulk copy)
@@ -473,22 +505,23 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         for (int j = 0; j < deg; j++) {
             int votes[16] = {0}, cj = -1, best = 0;
             for (int t = 0; t < TM; t++) {
-                if (j >= (int)rows[t].size()) continue;
+                if (!has(t, j)) continue;
                 int32_t oslot = S->h_api_to_slot[(size_t)rows[t][(size_t)j].o];
                 if (oslot / TM == T) votes[((oslot % TM) - t) & 15]++;
             }
             for (int r = 0; r < 16; r++) if (votes[r] > best) { best = votes[r]; cj = r; }
+            cjs[j] = cj;
             for (int hw = 0; hw < TM / 16; hw++) {
                 uint32_t used = 0;
                 for (int t = hw * 16; t < hw * 16 + 16; t++) {
-                    if (j >= (int)rows[t].size()) continue;
+                    if (!has(t, j)) continue;
                     const Half &h = rows[t][(size_t)j];
                     int32_t oslot = S->h_api_to_slot[(size_t)h.o];
                     if (oslot / TM == T) used |= 1u << (oslot % 16);
                     else if (halo_stamp[(size_t)h.o] == (int32_t)T) used |= 1u << (halo_local[(size_t)h.o] % 16);
                 }
                 for (int t = hw * 16; t < hw * 16 + 16; t++) {
-                    if (j >= (int)rows[t].size()) continue;
+                    if (!has(t, j)) continue;
                     const Half &h = rows[t][(size_t)j];
                     int32_t oslot = S->h_api_to_slot[(size_t)h.o];
                     if (oslot / TM == T || halo_stamp[(size_t)h.o] == (int32_t)T) continue;
@@ -497,7 +530,7 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
                         // preferred residue first, but never at the price of a halo list that no longer fits the
                         // small shared-memory variant: beyond that budget any free slot will do (a bank conflict
                         // costs a replay, an oversized list costs occupancy or the tiled format altogether)
-                        const int want = (t + cj) & 15, budget = CS_SMALL - TM - 1;
+                        const int want = (t + cj) & 15, budget = CS_SMALL - TM - N_DUMMY;
                         for (int x = want; pick < 0 && x < budget; x += 16) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
                         for (int x = 0; pick < 0; x++) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
                     } else {
@@ -515,14 +548,19 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         }
         const int n_halo = (int)th.size();
         for (int32_t x : th) halo.push_back(x);                   // -1 = hole, skipped by the gather
+        // padding words: the dummy mass in the bank pair the lane's own neighbour would occupy, record 0
+        for (size_t w = 0; w < block.size(); w++) {
+            const int j = (int)(w / TM), t = (int)(w % TM);
+            block[w] = (PAD_NB + (uint32_t)((t + ((j < deg && cjs[j] >= 0) ? cjs[j] : 0)) & 15)) << ELL_NB_SHIFT;
+        }
         for (int j = 0; j < deg; j++) for (int t = 0; t < TM; t++) {   // j-major walk: record slots of one row are consecutive
-            if (j >= (int)rows[t].size()) continue;
+            if (!has(t, j)) continue;
             const Half &h = rows[t][(size_t)j];
             int32_t oslot = S->h_api_to_slot[(size_t)h.o];
             const int nb = (oslot / TM == T) ? oslot % TM : TM + halo_local[(size_t)h.o];
             if (rec_stamp[(size_t)h.s] != (int32_t)T) { rec_stamp[(size_t)h.s] = (int32_t)T; rec_local[(size_t)h.s] = n_rec++; rec_spring.push_back(h.s); }
             int rec = rec_local[(size_t)h.s];
-            if (nb >= MAX_LOCAL - 1 || rec >= MAX_REC) { S->why_not = "a tile reaches too many foreign masses or springs"; return TB_OK; }
+            if (nb >= MAX_LOCAL - N_DUMMY || rec >= MAX_REC) { S->why_not = "a tile reaches too many foreign masses or springs"; return TB_OK; }
             uint32_t ty = 0;
             if (!e->h_type.empty()) { uint8_t x = e->h_type[(size_t)h.s]; ty = (x == 2) ? 1u : (x == 3) ? 2u : 0u; }
             block[(size_t)j * TM + (size_t)t] =
@@ -581,12 +619,13 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
     }
     while (halo.size() % 4) halo.push_back(0);
     halo.resize(halo.size() + 4, 0);   // the last list may be copied rounded up to 16 bytes
-    if (TM + max_halo + 1 > CS_BIG) { S->why_not = "a tile reaches too many foreign masses"; return TB_OK; }
+    if (TM + max_halo + N_DUMMY > CS_BIG) { S->why_not = "a tile reaches too many foreign masses"; return TB_OK; }
     S->cs = choose_cs(max_halo, (e->flags & TB_MATH_STRICT) != 0);
     ell.resize(ell.size() + (size_t)(MAX_DEG + 2 * ELL_CHUNK) * TM, 0u);   // the kernel prefetches whole register sets
-    {   // padding words -> (dummy mass, record 0)
-        const uint32_t pad = (uint32_t)(S->cs - 1) << ELL_NB_SHIFT;
-        for (uint32_t &w : ell) if (!(w & ELL_VALID)) w = pad;
+    {   // padding words: provisional dummy index -> the stride's own dummies [cs - N_DUMMY, cs)
+        const uint32_t base = (uint32_t)(S->cs - N_DUMMY);
+        for (uint32_t &w : ell)
+            if (!(w & ELL_VALID)) { const uint32_t nb = (w >> ELL_NB_SHIFT) & 0x1ffu; w = (base + (nb >= PAD_NB ? nb - PAD_NB : 0u)) << ELL_NB_SHIFT; }
     }
     // stages of the tile ring (TB_STAGES): the small dictionary blobs leave room for more than two
     int nst = 2;      // measured on B200 (C2, dictionary mode): 3 stages 183.7 vs 2 stages 187.9 G spring-steps/s
@@ -939,8 +978,10 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
     }
     if (tid < NST) {   // the dummy mass of every stage: far away, at rest
         double *pp = reinterpret_cast<double *>(smem + sp.off_stage + tid * sp.stage_bytes + sp.st_pos);
-        pp[CS - 1] = 1e30; pp[2 * CS - 1] = 1e30; pp[3 * CS - 1] = 1e30;
-        if (STAGE_VEL) { double *vp = pp + 3 * CS; vp[CS - 1] = 0.0; vp[2 * CS - 1] = 0.0; vp[3 * CS - 1] = 0.0; }
+        for (int d = 1; d <= N_DUMMY; d++) {
+            pp[CS - d] = 1e30; pp[2 * CS - d] = 1e30; pp[3 * CS - d] = 1e30;
+            if (STAGE_VEL) { double *vp = pp + 3 * CS; vp[CS - d] = 0.0; vp[2 * CS - d] = 0.0; vp[3 * CS - d] = 0.0; }
+        }
     }
     // Programmatic dependent launch: the next step's grid may become resident as this grid's CTAs retire.  Everything
     // up to griddepcontrol.wait touches only per-topology tables (meta, ELL words, halo lists), never the state or
@@ -1299,8 +1340,19 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
 }
 
 // ---------------------------------------------------------------- glue ------------------------------------
+// -DTB_DEV_BUILD compiles only the variants a kernel experiment needs (fast arithmetic, one thread per mass, small stride,
+// no damping, no halo exchange): the full set takes minutes to build.  Never used for a shipped library.
+template <class P, bool D, bool AC, int TPM, int CS, bool HALO, int DICT> constexpr bool variant_built() {
+#ifdef TB_DEV_BUILD
+    return !P::strict && TPM == 1 && CS == CS_SMALL && !D && !HALO;
+#else
+    return true;
+#endif
+}
 template <class P, bool D, bool AC, int TPM, int CS, bool HALO, int DICT>
 static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
+    if constexpr (!variant_built<P, D, AC, TPM, CS, HALO, DICT>()) return fail(e, TB_ERR_UNSUPPORTED, "this kernel variant is not part of a TB_DEV_BUILD library");
+    else {
     // The dynamic shared-memory limit of a kernel is a per-device (per-context) attribute: remembered per template
     // instantiation AND device, under a lock (engines on several GPUs, or several facade GPU threads, in one process).
     static std::mutex mu;
@@ -1332,6 +1384,7 @@ static int launch_c(Engine *e, TiledState *S, const TiledArgs &A, const MassExtr
     cfg.attrs = attr; cfg.numAttrs = use_pdl ? 1 : 0;
     TB_CUDA(e, cudaLaunchKernelEx(&cfg, kern, A, e->G, X));
     return TB_OK;
+    }
 }
 template <class P, bool D, bool AC, int TPM>
 static int launch_v(Engine *e, TiledState *S, const TiledArgs &A, const MassExtras &X) {
@@ -1603,9 +1656,9 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
     {
         const double *sb = A.st_in + (size_t)tile * STATE_BLOCK + t;
         for (int c = 0; c < 3; c++) { Pc(0, c)[t] = sb[c * TM]; Vc(0, c)[t] = sb[(3 + c) * TM]; }
-        if (t == 0) for (int b = 0; b < 2; b++) for (int c = 0; c < 3; c++) {      // the dummy mass: far away, at rest
-            Pc(b, c)[cs - 1] = 1e30;
-            if (A.stage_vel) Vc(b, c)[vs - 1] = 0.0;
+        if (t < N_DUMMY) for (int b = 0; b < 2; b++) for (int c = 0; c < 3; c++) {      // the dummy masses: far away, at rest
+            Pc(b, c)[cs - 1 - t] = 1e30;
+            if (A.stage_vel) Vc(b, c)[vs - 1 - t] = 0.0;
         }
     }
     __syncthreads();
