@@ -594,3 +594,58 @@ def test_dictionary_records_are_bit_identical_to_plain_records(name, monkeypatch
     compare("rest edit in split mode")
     for e in engines:
         e.close()
+
+
+def lattice_with_actuated_links(n=16):
+    """An n^3 lattice resting on a plane plus ACTUATED_EXPAND / ACTUATED_CONTRACT springs (what RobotLink::expand /
+    contract switch on, src/object.cu:386-421) between some of its masses, one of them across two bricks."""
+    sc = scenes.c2_lattice(n)
+    import oracle
+    pairs = [(0, 1), (5, 5 + n * n), (n ** 3 - 1, n ** 3 - 2), (7 * n * n + 3 * n + 2, 12 * n * n + 3 * n + 2)]
+    left = np.concatenate([sc.left, [a for a, _ in pairs]]).astype(np.int32)
+    right = np.concatenate([sc.right, [b for _, b in pairs]]).astype(np.int32)
+    rest_new = [float(np.linalg.norm(sc.pos[a] - sc.pos[b])) for a, b in pairs]
+    rest = np.concatenate([sc.rest, rest_new])
+    s2 = oracle.Scene(sc.pos, left, right, rest, k=10000.0, m=0.1, dt=sc.dt, g=sc.g)
+    s2.planes.extend(sc.planes)
+    for q in range(len(pairs)):
+        s = sc.ns + q
+        s2.type[s] = 4 + (q % 2)
+        s2.k[s] = 500.0
+        s2.l_max[s] = rest_new[q] * 1.01
+        s2.l_min[s] = rest_new[q] * 0.99
+        s2.rate[s] = 0.02 + 0.01 * q
+    return s2
+
+
+def test_actuated_springs_stay_on_the_tiled_kernel(monkeypatch):
+    """ACTUATED_* springs (device-side _rest mutation, src/sim.cu:1174-1181) no longer send the system to the generic
+    kernel: the mutation runs over the list of such springs and writes their private record in the tile blobs."""
+    # (1) the small all-types scene, strict: bit-identical rest lengths, state within the sin() ulp
+    sc = scenes.actuated()
+    for nsteps in (1, 60):
+        o = oracle_after(sc, nsteps)
+        g = run_engine(sc, nsteps, tb.MATH_STRICT | tb.NO_RESIDENT)
+        assert g["info"]["kernel"] == 1
+        assert same_bits(g["rest"], o.rest)
+        for f in ("pos", "vel"):
+            assert rel(g[f], getattr(o, f)) <= 1e-13, (nsteps, f)
+    # (2) a lattice with a few actuated links, fast arithmetic, one thread per mass: dictionary records for the lattice
+    # springs, a private record per actuated spring
+    monkeypatch.setenv("TB_TPM", "1")
+    sc = lattice_with_actuated_links(16)
+    for flags in (tb.MATH_STRICT, tb.MATH_FAST):
+        for nsteps, tol in ((1, 1e-12), (100, 1e-9)):
+            o = oracle_after(sc, nsteps)
+            g = run_engine(sc, nsteps, flags | tb.NO_RESIDENT, chunks=2 if nsteps > 1 else 1)
+            assert g["info"]["kernel"] == 1
+            if flags == tb.MATH_FAST:
+                assert g["info"]["dict_records"] > 0
+            assert same_bits(g["rest"], o.rest), (flags, nsteps)
+            for f in ("pos", "vel"):
+                e = rel(g[f], getattr(o, f))
+                assert e <= (0.0 if flags == tb.MATH_STRICT else tol), (flags, nsteps, f, e)
+    # (3) the generic kernel walks the same list
+    o = oracle_after(sc, 30)
+    g = run_engine(sc, 30, tb.MATH_STRICT | tb.KERNEL_CSR)
+    assert g["info"]["kernel"] == 0 and same_bits(g["rest"], o.rest) and same_bits(g["pos"], o.pos)

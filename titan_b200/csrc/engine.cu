@@ -39,6 +39,7 @@ template int dev_alloc<int32_t>(Engine *, int32_t **, size_t);
 template int dev_alloc<uint8_t>(Engine *, uint8_t **, size_t);
 template int dev_alloc<float>(Engine *, float **, size_t);
 template int dev_alloc<uint32_t>(Engine *, uint32_t **, size_t);
+template int dev_alloc<uint64_t>(Engine *, uint64_t **, size_t);
 template int dev_alloc<uint16_t>(Engine *, uint16_t **, size_t);
 template int dev_alloc<tb_local>(Engine *, tb_local **, size_t);
 template int dev_alloc<tb_plane>(Engine *, tb_plane **, size_t);
@@ -224,6 +225,7 @@ static void free_all(Engine *e) {
     F(e->export_f32, (size_t)e->nm * 12);
     F(e->export_idx, (size_t)e->ns * 8);
     F(e->removed_dev, (size_t)e->ns);
+    F(e->act_idx, (size_t)e->n_act * 4); e->n_act = 0; e->act_dirty = true; e->h_act.clear();
     magnet_free(e);
     e->h_removed.clear(); e->n_removed = 0;
     if (e->lc_ptr) { cudaFree(e->lc_ptr); e->lc_ptr = nullptr; }
@@ -570,6 +572,7 @@ int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, const int32
         }
         e->any_active = e->any_actuated = false;
         for (uint8_t ty : e->h_type) { if (ty == 2 || ty == 3) e->any_active = true; if (ty >= 4) e->any_actuated = true; }
+        if (type_changed) e->act_dirty = true;
         if (e->type || nonpassive) {
             TB_TRY(ensure_spring_array<int32_t>(e, &e->type, 0));
             TB_TRY(up_scalar<int32_t>(e, e->type, type, idx, first, count));
@@ -719,18 +722,46 @@ __global__ void set_t_kernel(double *t, double v, long long *step, long long n) 
 
 // ACTUATED_EXPAND / ACTUATED_CONTRACT mutate _rest on the device before the force is evaluated
 // (src/sim.cu:1174-1181); springs with a null or invalid endpoint are skipped first (:1163).
+// One thread per ACTUATED_* spring (the list e->act_idx).  The tiled kernel reads rest lengths from its record blobs: the
+// same thread stores the new value into the spring's private record in each tile that holds it (slots: two byte offsets
+// per list entry, ~0 = none; dictionary classes key actuated springs by index, so the record is theirs alone).
 __global__ void advance_rest_kernel(double *rest, const int32_t *type, const double *l_max, const double *l_min,
                                     const double *rate, const int32_t *left, const int32_t *right,
-                                    const uint8_t *flags, double dt, int64_t ns) {
-    int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (s >= ns) return;
+                                    const uint8_t *flags, double dt, const int32_t *act_idx, int64_t n_act,
+                                    const uint64_t *slots, uint8_t *blob) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_act) return;
+    const int32_t s = act_idx[j];
     int ty = type[s];
     if (ty < TB_ACTUATED_EXPAND) return;
     int l = left[s], r = right[s];
     if (l < 0 || r < 0 || !(flags[l] & F_VALID) || !(flags[r] & F_VALID)) return;
     double x = rest[s];
-    if (ty == TB_ACTUATED_EXPAND) { if (x < l_max[s]) rest[s] = __dadd_rn(x, __dmul_rn(rate[s], dt)); }
-    else { if (x > l_min[s]) rest[s] = __dsub_rn(x, __dmul_rn(rate[s], dt)); }
+    if (ty == TB_ACTUATED_EXPAND) { if (x < l_max[s]) x = __dadd_rn(x, __dmul_rn(rate[s], dt)); }
+    else { if (x > l_min[s]) x = __dsub_rn(x, __dmul_rn(rate[s], dt)); }
+    rest[s] = x;
+    if (slots)
+        for (int q = 0; q < 2; q++) {
+            const uint64_t off = slots[2 * j + q];
+            if (off != ~0ull) *reinterpret_cast<double *>(blob + off) = x;
+        }
+}
+
+// (re)builds the device list of actuated springs; outside any stream capture (it allocates)
+int prepare_actuated(Engine *e) {
+    if (!e->act_dirty) return TB_OK;
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    dev_free(e, (void *)e->act_idx, (size_t)e->n_act * 4); e->act_idx = nullptr; e->n_act = 0;
+    e->h_act.clear();
+    for (int64_t s = 0; s < (int64_t)e->h_type.size(); s++) if (e->h_type[(size_t)s] >= TB_ACTUATED_EXPAND) e->h_act.push_back((int32_t)s);
+    e->n_act = (int64_t)e->h_act.size();
+    if (e->n_act) {
+        TB_TRY(dev_alloc(e, &e->act_idx, (size_t)e->n_act));
+        TB_CUDA(e, cudaMemcpy(e->act_idx, e->h_act.data(), (size_t)e->n_act * 4, cudaMemcpyHostToDevice));
+    }
+    e->act_dirty = false;
+    e->graph_dirty = true;
+    return TB_OK;
 }
 
 // the tiled kernel covers both integrators and takes the magnet pass's forces like an uploaded external force; a
@@ -744,8 +775,13 @@ static bool use_tiled(Engine *e) {
 static int enqueue_step(Engine *e, bool use_ext, bool write_acc) {
     if (e->any_actuated) {
         if (!e->l_max || !e->l_min || !e->rate) return fail(e, TB_ERR_INVALID, "actuated springs need l_max, l_min and rate");
-        advance_rest_kernel<<<(unsigned)((e->ns + 255) / 256), 256, 0, e->stream>>>(
-            e->rest, e->type, e->l_max, e->l_min, e->rate, e->left, e->right, e->mflags, e->G.dt, e->ns);
+        const uint64_t *slots = nullptr; uint8_t *blob = nullptr;
+        if (use_tiled(e)) {
+            tiled_actuated_targets(e, &slots, &blob);
+            if (e->n_act > 0 && !slots) return fail(e, TB_ERR_INVALID, "internal: the tiled layout does not know where the rest lengths of the actuated springs live");
+        }
+        advance_rest_kernel<<<blocks_for(e->n_act), 256, 0, e->stream>>>(
+            e->rest, e->type, e->l_max, e->l_min, e->rate, e->left, e->right, e->mflags, e->G.dt, e->act_idx, e->n_act, slots, blob);
         e->launches++;
     }
     if (e->any_magnet) TB_TRY(launch_magnet_pass(e, use_ext, use_tiled(e)));   // recomputeOG + magnet forces, src/sim.cu:1775,1298
@@ -787,6 +823,7 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     E_CHECK(e);
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "No masses have been added. Please add masses before starting the simulation.");  // src/sim.cu:1552-1554
     if (nsteps < 0) return fail(e, TB_ERR_INVALID, "tb_run_async: negative step count");
+    if (e->any_actuated) TB_TRY(prepare_actuated(e));   // before tiled_prepare: the tile builder records where their rest lengths live
     if (use_tiled(e)) TB_TRY(tiled_prepare(e));       // may discover that the graph does not fit the tiled format
     if (!use_tiled(e) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
     if (nsteps == 0) return TB_OK;                    // validation + device layout brought up to date, nothing launched

@@ -53,6 +53,10 @@ struct Engine {
     double *k = nullptr, *rest = nullptr, *damping = nullptr, *omega = nullptr, *l_max = nullptr,
            *l_min = nullptr, *rate = nullptr;
     int32_t *row_ptr = nullptr, *adj = nullptr;
+    // ACTUATED_EXPAND / ACTUATED_CONTRACT springs (RobotLink), ascending spring index: the per-step _rest mutation
+    // (src/sim.cu:1174-1181) runs over this list only
+    int32_t *act_idx = nullptr; int64_t n_act = 0; bool act_dirty = true;
+    std::vector<int32_t> h_act;
     int32_t *lc_ptr = nullptr;
     tb_local *lc = nullptr;
     tb_plane *more_planes = nullptr;
@@ -128,6 +132,8 @@ int fail(Engine *e, int status, const char *fmt, ...);
 template <class T> int dev_alloc(Engine *e, T **p, size_t count);
 void dev_free(Engine *e, void *p, size_t bytes);
 
+// engine.cu: (re)builds e->act_idx / e->h_act, the list of ACTUATED_* springs; allocates, so never under stream capture
+int prepare_actuated(Engine *e);
 // csr_step.cu
 int launch_csr_step(Engine *e, bool use_ext, bool write_acc);
 // magnet.cu
@@ -157,6 +163,9 @@ bool tiled_halo_connected(const Engine *e);
 bool tiled_resident_ok(const Engine *e);         // <= 8 tiles, no peers: all steps of a run in one cluster launch
 int launch_tiled_resident(Engine *e, int nsteps, bool write_acc);
 void tiled_pos_view(const Engine *e, PosView *v); // the current state buffer of the tiled kernel
+// where the tiled layout keeps the rest length of the j-th actuated spring (e->h_act order): up to two byte offsets into the
+// record blobs per spring (~0 = none), or nulls when the tiled layout is not in use
+void tiled_actuated_targets(const Engine *e, const uint64_t **slots, uint8_t **blob);
 int tiled_halo_check(Engine *e);                 // after a sync: did a halo wait time out?
 
 }  // namespace tb

@@ -123,6 +123,8 @@ struct TiledState {
                                           // slot (systems whose k is edited per spring, e.g. topology optimisation)
     int32_t *krec_spring = nullptr; int64_t n_krec = 0;   // split mode: record slot -> spring, all tiles
     uint32_t *krec_off = nullptr;                         // split mode: [n_tiles + 1] first slot of each tile in krec_spring
+    uint64_t *act_slots = nullptr; int64_t n_act_slots = 0;   // [2 * e->n_act] blob byte offsets of the rest length of every
+                                          // ACTUATED_* spring (its private record in each tile that holds it), ~0 = none
     int dict_failures = 0;                // parameter uploads that broke the classes; after 2 the mode stays off
     int split_failures = 0;               // the same for the split dictionary
     int64_t n_class_rep = 0;
@@ -299,6 +301,7 @@ static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
     release(e, S->class_rep, (size_t)S->n_class_rep); S->n_class_rep = 0; release(e, S->rec_map, (size_t)S->n_rec_map);
     S->n_rec_map = 0; S->dict = false; S->dict_split = false;
     release(e, S->krec_spring, (size_t)S->n_krec); S->n_krec = 0;
+    release(e, S->act_slots, (size_t)S->n_act_slots); S->n_act_slots = 0;
     if (S->krec_off) { cudaFree(S->krec_off); S->krec_off = nullptr; }
     release(e, S->blob, S->blob_bytes);
     release(e, S->slot_to_api, (size_t)S->n_slots); release(e, S->halo, (size_t)S->n_halo);
@@ -360,8 +363,10 @@ static int param_classes(Engine *e, bool with_k, bool damping, bool active, std:
     Key last = {0, 0, 0, 0, 0}; int32_t last_class = -1;
     auto bits = [](double x) { uint64_t u; memcpy(&u, &x, 8); return u; };
     for (size_t sp = 0; sp < ns; sp++) {
+        // an ACTUATED_* spring's rest length changes every step (advance_rest_kernel writes it into the record): a class of its own
+        const uint64_t own = (e->h_type.size() == ns && e->h_type[sp] >= TB_ACTUATED_EXPAND) ? ((uint64_t)(sp + 1) << 8) : 0;
         Key key = {with_k ? bits(hk[sp]) : 0, bits(hr[sp]), hd.empty() ? 0 : bits(hd[sp]), ho.empty() ? 0 : bits(ho[sp]),
-                   typed ? (uint64_t)(e->h_type[sp] == 2 ? 1 : e->h_type[sp] == 3 ? 2 : 0) : 0};
+                   own | (typed ? (uint64_t)(e->h_type[sp] == 2 ? 1 : e->h_type[sp] == 3 ? 2 : 0) : 0)};
         int32_t c;
         if (last_class >= 0 && key == last) c = last_class;
         else {
@@ -438,6 +443,8 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
     struct Half { int32_t s; int32_t o; uint8_t side; };
     std::vector<std::vector<Half>> rows(TM);
     std::vector<Half> aligned;
+    std::vector<std::pair<int32_t, int>> act_here;          // (actuated spring, its record) of the tile being built
+    std::vector<std::pair<int32_t, uint64_t>> act_found;    // (actuated spring, blob byte offset of its rest length), all tiles
     int cjs[MAX_DEG];
     const bool align_rows = !(getenv("TB_ALIGN_ROWS") && atoi(getenv("TB_ALIGN_ROWS")) == 0);   // measurement aid
     std::vector<int32_t> th;   // halo list of the tile being built (-1 = hole)
@@ -585,6 +592,11 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         M.tflags = (T < S->n_boundary) ? (uint32_t)TF_BOUNDARY : 0u;
         if (keep_slots) { M.exp_off = old_meta[(size_t)T].exp_off; M.exp_rows = old_meta[(size_t)T].exp_rows; M.tflags = old_meta[(size_t)T].tflags; }
         size_t bb = blob_size(n_rec, S->has_damping, S->has_active);
+        act_here.clear();
+        for (int r = 1; r < n_rec && e->any_actuated && !dict; r++) {
+            const int32_t sp = rec_spring[rec_first + (size_t)r];
+            if (sp >= 0 && e->h_type[(size_t)sp] >= TB_ACTUATED_EXPAND) act_here.push_back({sp, r});
+        }
         if (dict) {
             // record slots -> the tile's distinct records; slot 0 (padding) -> record 0 (k = 0)
             while (rec_map.size() % 16) rec_map.push_back(0);
@@ -602,6 +614,10 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
                 rec_map.push_back((uint8_t)cls_local[(size_t)c]);
             }
             if (!dict) return build_structure(e, S, keep_slots, next_mode);   // a tile with too many classes
+            for (int r = 1; r < n_dict && e->any_actuated; r++) {
+                const int32_t sp = dict_spring[(size_t)M.rec_off + (size_t)r];
+                if (sp >= 0 && e->h_type[(size_t)sp] >= TB_ACTUATED_EXPAND) act_here.push_back({sp, r});
+            }
             if (split) {                                                   // slot -> spring, for the per-slot stiffness
                 krec_off.push_back((uint32_t)kslot_spring.size());
                 kslot_spring.insert(kslot_spring.end(), rec_spring.begin() + (ptrdiff_t)rec_first, rec_spring.end());
@@ -613,6 +629,11 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         }
         if (blob_total / 16 >= ((size_t)1 << 32)) { S->why_not = "blob exceeds 64 GB"; return TB_OK; }
         M.blob_off16 = (uint32_t)(blob_total / 16); M.blob_bytes = (uint32_t)bb;
+        {   // where the rest lengths of this tile's actuated springs sit: after the k array (blob_size / tiled_refresh_params)
+            const size_t np = (size_t)((M.n_rec + 1) & ~1u), nk = (dict && split) ? (size_t)((n_rec + 1) & ~1) : np;
+            for (const std::pair<int32_t, int> &a : act_here)
+                act_found.push_back({a.first, (uint64_t)blob_total + (uint64_t)BLOB_REC + nk * 8 + (uint64_t)a.second * 8});
+        }
         blob_total += bb;
         max_blob = std::max(max_blob, bb);
         max_halo = std::max(max_halo, n_halo); max_rec = std::max(max_rec, n_rec); max_deg = std::max(max_deg, deg);
@@ -674,6 +695,18 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         TB_TRY(upload_vec(e, &S->rec_map, rec_map)); TB_TRY(upload_vec(e, &S->class_rep, rep_of));
         if (!S->dict_bad) TB_CUDA(e, cudaMalloc((void **)&S->dict_bad, sizeof(int)));
         S->n_rec = (int64_t)rec_spring.size();
+    }
+    if (e->any_actuated && !e->h_act.empty()) {
+        std::vector<uint64_t> slots(e->h_act.size() * 2, ~0ull);
+        for (const std::pair<int32_t, uint64_t> &a : act_found) {
+            const size_t j = (size_t)(std::lower_bound(e->h_act.begin(), e->h_act.end(), a.first) - e->h_act.begin());
+            if (j >= e->h_act.size() || e->h_act[j] != a.first) continue;
+            if (slots[2 * j] == ~0ull) slots[2 * j] = a.second;
+            else if (slots[2 * j + 1] == ~0ull) slots[2 * j + 1] = a.second;
+            else { S->why_not = "an actuated spring has records in more than two tiles"; return TB_OK; }
+        }
+        S->n_act_slots = (int64_t)slots.size();
+        TB_TRY(upload_vec(e, &S->act_slots, slots));
     }
     TB_TRY(dev_alloc(e, &S->blob, blob_total));
     TB_CUDA(e, cudaMemset(S->blob, 0, blob_total));
@@ -1070,7 +1103,9 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 if (HALO) { c->exp_off = (uint32_t)m0c.x; c->exp_rows = (uint32_t)m0c.y; c->tflags = (uint32_t)m0c.z; }
                 uint32_t cbp, nchp;
                 chunk_table(m1b.y, TPM, cbp, nchp);
-                c->next_ell_off = (uint32_t)m1b.x; c->next_cb = cbp; c->next_nch = nchp; c->has_next = (k + 1 < n_my) ? 1u : 0u;
+                // has_next: bit 0 = another tile follows; bit 1 (halo exchange) = masses of THIS tile are ghosts on a peer
+                c->next_ell_off = (uint32_t)m1b.x; c->next_cb = cbp; c->next_nch = nchp;
+                c->has_next = ((k + 1 < n_my) ? 1u : 0u) | ((HALO && m0c.y) ? 2u : 0u);
                 mbar_expect_tx(bar_full(s), (uint32_t)m0a.y + (uint32_t)(STATE_BLOCK * 8));
                 if (A.l2_hint) bulk_g2s_hint(stage, A.blob + (size_t)(uint32_t)m0a.x * 16, (uint32_t)m0a.y, bar_full(s), pol_stream);
                 else bulk_g2s(stage, A.blob + (size_t)(uint32_t)m0a.x * 16, (uint32_t)m0a.y, bar_full(s));
@@ -1129,7 +1164,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
         // The next tile's ELL words replace this tile's in the same registers, each right after its last use (the
         // loads are unconditional: the table is padded, words beyond a tile's rows are never evaluated).
         const uint32_t *nsrc = A.ell + t;
-        if (ctrl.has_next) {
+        if (ctrl.has_next & 1u) {
             nch_nxt = (int)((ctrl.next_nch >> (8 * q)) & 0xff);
             rows_nxt = (int)((ctrl.next_nch >> 8) & 0xff);
             nsrc += ctrl.next_ell_off + (size_t)((ctrl.next_cb >> (8 * q)) & 0xff) * ELL_CHUNK * TM;
@@ -1302,13 +1337,13 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 }
                 if (A.write_acc) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
             }
-            if (!HALO || !(fl & F_GHOST)) {     // a ghost's slot belongs to the peer that owns the mass
-                ob[0] = pos.x; ob[TM] = pos.y; ob[2 * TM] = pos.z;
-                ob[3 * TM] = vel.x; ob[4 * TM] = vel.y; ob[5 * TM] = vel.z;
-            }
-            if (HALO) {
-                // halo exchange: the new state of a mass that is a ghost elsewhere goes straight into the peer's buffer
-                // (the exchange fields of the tile control word are read only now, to keep them out of the hot loop)
+            // (a ghost's slot belongs to the peer that owns the mass -- but ghosts live in tiles of their own, which are
+            // never processed: assign_tiles)
+            ob[0] = pos.x; ob[TM] = pos.y; ob[2 * TM] = pos.z;
+            ob[3 * TM] = vel.x; ob[4 * TM] = vel.y; ob[5 * TM] = vel.z;
+            if (HALO && (ctrl.has_next & 2u)) {
+                // halo exchange: the new state of a mass that is a ghost elsewhere goes straight into the peer's buffer;
+                // the tile control word says whether this tile exports at all, its exchange fields are read only then
                 const TileCtrl *cp = reinterpret_cast<const TileCtrl *>(smem + sp.off_ctrl) + s;
                 const uint32_t exp_rows = (A.debug & 8) ? 0u : cp->exp_rows;
                 if (exp_rows) halo_export(A, exp_rows, cp->exp_off + (uint32_t)t, pos, vel);   // boundary tiles only, out of line
@@ -1413,7 +1448,7 @@ template <class P, int TPM> static int launch_f(Engine *e, TiledState *S, const 
 }
 
 bool tiled_supported(const Engine *e) {
-    if (e->any_actuated || e->nm == 0) return false;   // ACTUATED_* springs mutate _rest: generic kernel
+    if (e->nm == 0) return false;
     const TiledState *S = e->tiled;
     if (S && !(e->tiled_stale & TS_STRUCT) && !S->supported) return false;
     return true;
@@ -1426,6 +1461,7 @@ int tiled_prepare(Engine *e) {
     if (getenv("TB_PROFILE") && !g_prof_dev) { cudaMalloc((void **)&g_prof_dev, 16 * 8); cudaMemset(g_prof_dev, 0, 16 * 8); }
     if (!e->tiled) e->tiled = new TiledState();
     TiledState *S = e->tiled;
+    if (e->any_actuated) TB_TRY(prepare_actuated(e));     // the tile builder records where their rest lengths live
     uint32_t stale = e->tiled_stale;
     if (S->n_tiles > 0 && (S->has_damping != e->any_damping || S->has_active != e->any_active)) stale |= TS_STRUCT;
     if (S->n_tiles == 0 && !(stale & TS_STRUCT) && S->supported) stale |= TS_STRUCT;
@@ -1846,6 +1882,7 @@ bool tiled_resident_ok(const Engine *e) {
     const int64_t max_tiles = getenv("TB_RESIDENT_MAX_TILES") ? atoll(getenv("TB_RESIDENT_MAX_TILES")) : std::max(8, e->sm_count);
     if (S->n_tiles < 1 || S->res_cluster < 1 || S->n_tiles > max_tiles || S->n_active != S->n_tiles) return false;
     if (e->any_ghost || e->any_magnet || S->n_exp_tab || S->halo_connected) return false;   // the magnet pass runs between steps
+    if (e->any_actuated) return false;      // ... and so does the _rest mutation of ACTUATED_* springs (advance_rest_kernel)
     return true;
 }
 
@@ -1926,6 +1963,13 @@ void tiled_pos_view(const Engine *e, PosView *v) {
     v->base = S->st[e->cur]; v->api_to_slot = S->api_to_slot; v->nm = e->nm;
 }
 
+void tiled_actuated_targets(const Engine *e, const uint64_t **slots, uint8_t **blob) {
+    const TiledState *S = e->tiled;
+    const bool ok = S && S->supported && S->act_slots && S->n_act_slots == 2 * e->n_act;
+    *slots = ok ? S->act_slots : nullptr;
+    *blob = ok ? S->blob : nullptr;
+}
+
 bool tiled_halo_connected(const Engine *e) { return e->tiled && e->tiled->halo_connected; }
 
 int tiled_halo_check(Engine *e) {
@@ -1980,7 +2024,6 @@ int tb_halo_prepare(tb_engine *e, tb_halo_handle *out) {
     if (!e || !out) return TB_ERR_INVALID;
     cudaSetDevice(e->device);
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_halo_prepare before tb_set_topology");
-    if (e->any_actuated) return fail(e, TB_ERR_UNSUPPORTED, "halo exchange is not built for ACTUATED_* springs (generic kernel)");
     if (e->tiled) halo_release(e, e->tiled);
     e->tiled_stale |= TS_STRUCT;
     int rc = tiled_prepare(e);
