@@ -722,13 +722,11 @@ __global__ void set_t_kernel(double *t, double v, long long *step, long long n) 
 
 // ACTUATED_EXPAND / ACTUATED_CONTRACT mutate _rest on the device before the force is evaluated
 // (src/sim.cu:1174-1181); springs with a null or invalid endpoint are skipped first (:1163).
-// One thread per ACTUATED_* spring (the list e->act_idx).  The tiled kernel reads rest lengths from its record blobs: the
-// same thread stores the new value into the spring's private record in each tile that holds it (slots: two byte offsets
-// per list entry, ~0 = none; dictionary classes key actuated springs by index, so the record is theirs alone).
+// One thread per ACTUATED_* spring (the list e->act_idx): the generic kernel's pre-pass.  The tiled kernels advance the
+// records of their tiles themselves (tiled.cu: advance_actuated_records) and keep e->rest current.
 __global__ void advance_rest_kernel(double *rest, const int32_t *type, const double *l_max, const double *l_min,
                                     const double *rate, const int32_t *left, const int32_t *right,
-                                    const uint8_t *flags, double dt, const int32_t *act_idx, int64_t n_act,
-                                    const uint64_t *slots, uint8_t *blob) {
+                                    const uint8_t *flags, double dt, const int32_t *act_idx, int64_t n_act) {
     int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n_act) return;
     const int32_t s = act_idx[j];
@@ -740,11 +738,6 @@ __global__ void advance_rest_kernel(double *rest, const int32_t *type, const dou
     if (ty == TB_ACTUATED_EXPAND) { if (x < l_max[s]) x = __dadd_rn(x, __dmul_rn(rate[s], dt)); }
     else { if (x > l_min[s]) x = __dsub_rn(x, __dmul_rn(rate[s], dt)); }
     rest[s] = x;
-    if (slots)
-        for (int q = 0; q < 2; q++) {
-            const uint64_t off = slots[2 * j + q];
-            if (off != ~0ull) *reinterpret_cast<double *>(blob + off) = x;
-        }
 }
 
 // (re)builds the device list of actuated springs; outside any stream capture (it allocates)
@@ -775,14 +768,11 @@ static bool use_tiled(Engine *e) {
 static int enqueue_step(Engine *e, bool use_ext, bool write_acc) {
     if (e->any_actuated) {
         if (!e->l_max || !e->l_min || !e->rate) return fail(e, TB_ERR_INVALID, "actuated springs need l_max, l_min and rate");
-        const uint64_t *slots = nullptr; uint8_t *blob = nullptr;
-        if (use_tiled(e)) {
-            tiled_actuated_targets(e, &slots, &blob);
-            if (e->n_act > 0 && !slots) return fail(e, TB_ERR_INVALID, "internal: the tiled layout does not know where the rest lengths of the actuated springs live");
+        if (!use_tiled(e)) {     // the tiled kernels advance the records of their own tiles
+            advance_rest_kernel<<<blocks_for(e->n_act), 256, 0, e->stream>>>(
+                e->rest, e->type, e->l_max, e->l_min, e->rate, e->left, e->right, e->mflags, e->G.dt, e->act_idx, e->n_act);
+            e->launches++;
         }
-        advance_rest_kernel<<<blocks_for(e->n_act), 256, 0, e->stream>>>(
-            e->rest, e->type, e->l_max, e->l_min, e->rate, e->left, e->right, e->mflags, e->G.dt, e->act_idx, e->n_act, slots, blob);
-        e->launches++;
     }
     if (e->any_magnet) TB_TRY(launch_magnet_pass(e, use_ext, use_tiled(e)));   // recomputeOG + magnet forces, src/sim.cu:1775,1298
     int rc = use_tiled(e) ? launch_tiled_step(e, use_ext, write_acc) : launch_csr_step(e, use_ext, write_acc);
@@ -823,7 +813,10 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     E_CHECK(e);
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "No masses have been added. Please add masses before starting the simulation.");  // src/sim.cu:1552-1554
     if (nsteps < 0) return fail(e, TB_ERR_INVALID, "tb_run_async: negative step count");
-    if (e->any_actuated) TB_TRY(prepare_actuated(e));   // before tiled_prepare: the tile builder records where their rest lengths live
+    if (e->any_actuated) {
+        if (!e->l_max || !e->l_min || !e->rate) return fail(e, TB_ERR_INVALID, "actuated springs need l_max, l_min and rate");
+        TB_TRY(prepare_actuated(e));   // before tiled_prepare: the tile builder records where their rest lengths live
+    }
     if (use_tiled(e)) TB_TRY(tiled_prepare(e));       // may discover that the graph does not fit the tiled format
     if (!use_tiled(e) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
     if (nsteps == 0) return TB_OK;                    // validation + device layout brought up to date, nothing launched
@@ -854,7 +847,7 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
         if (!e->graph[e->cur]) TB_TRY(build_graph(e, e->cur));
         while (left_steps - 1 >= GRAPH_STEPS) {
             TB_CUDA(e, cudaGraphLaunch(e->graph[e->cur], e->stream));
-            e->launches += (int64_t)GRAPH_STEPS * (1 + (e->any_actuated ? 1 : 0) + (e->any_magnet ? 5 : 0));
+            e->launches += (int64_t)GRAPH_STEPS * (1 + ((e->any_actuated && !use_tiled(e)) ? 1 : 0) + (e->any_magnet ? 5 : 0));
             left_steps -= GRAPH_STEPS;
         }
     }

@@ -163,9 +163,6 @@ bool tiled_halo_connected(const Engine *e);
 bool tiled_resident_ok(const Engine *e);         // <= 8 tiles, no peers: all steps of a run in one cluster launch
 int launch_tiled_resident(Engine *e, int nsteps, bool write_acc);
 void tiled_pos_view(const Engine *e, PosView *v); // the current state buffer of the tiled kernel
-// where the tiled layout keeps the rest length of the j-th actuated spring (e->h_act order): up to two byte offsets into the
-// record blobs per spring (~0 = none), or nulls when the tiled layout is not in use
-void tiled_actuated_targets(const Engine *e, const uint64_t **slots, uint8_t **blob);
 int tiled_halo_check(Engine *e);                 // after a sync: did a halo wait time out?
 
 }  // namespace tb

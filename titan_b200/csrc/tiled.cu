@@ -103,7 +103,8 @@ struct __align__(16) TileMeta {
     uint32_t map_off16;   // dictionary mode: the tile's slot -> record byte map in rec_map, in units of 16 bytes
 };
 static_assert(sizeof(TileMeta) == 48, "TileMeta is copied as three 16-byte words");
-enum : uint32_t { TF_BOUNDARY = 1 };   // the tile's springs reach ghost masses: wait for the peers before reading, signal after
+enum : uint32_t { TF_BOUNDARY = 1, TF_ACTUATED = 2 };   // ACTUATED: records of this tile are advanced before it is staged
+//   // the tile's springs reach ghost masses: wait for the peers before reading, signal after
 
 struct TiledState {
     int64_t n_tiles = 0, n_slots = 0, n_rec = 0, n_ell = 0, n_halo = 0;
@@ -123,8 +124,10 @@ struct TiledState {
                                           // slot (systems whose k is edited per spring, e.g. topology optimisation)
     int32_t *krec_spring = nullptr; int64_t n_krec = 0;   // split mode: record slot -> spring, all tiles
     uint32_t *krec_off = nullptr;                         // split mode: [n_tiles + 1] first slot of each tile in krec_spring
-    uint64_t *act_slots = nullptr; int64_t n_act_slots = 0;   // [2 * e->n_act] blob byte offsets of the rest length of every
-                                          // ACTUATED_* spring (its private record in each tile that holds it), ~0 = none
+    // ACTUATED_* springs: per tile the records whose rest length the step kernel advances before it stages the tile
+    // (x = byte offset of the rest slot inside the tile's blob, y = spring, z = 1 on the copy that also keeps the canonical
+    // rest array current -- a cut spring has a record in two tiles, both advance theirs identically)
+    uint32_t *act_tile_off = nullptr; int4 *act_rec = nullptr; int64_t n_act_rec = 0;
     int dict_failures = 0;                // parameter uploads that broke the classes; after 2 the mode stays off
     int split_failures = 0;               // the same for the split dictionary
     int64_t n_class_rep = 0;
@@ -301,7 +304,9 @@ static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
     release(e, S->class_rep, (size_t)S->n_class_rep); S->n_class_rep = 0; release(e, S->rec_map, (size_t)S->n_rec_map);
     S->n_rec_map = 0; S->dict = false; S->dict_split = false;
     release(e, S->krec_spring, (size_t)S->n_krec); S->n_krec = 0;
-    release(e, S->act_slots, (size_t)S->n_act_slots); S->n_act_slots = 0;
+    if (S->act_tile_off) { cudaFree(S->act_tile_off); S->act_tile_off = nullptr; }
+    if (S->act_rec) { cudaFree(S->act_rec); S->act_rec = nullptr; }
+    S->n_act_rec = 0;
     if (S->krec_off) { cudaFree(S->krec_off); S->krec_off = nullptr; }
     release(e, S->blob, S->blob_bytes);
     release(e, S->slot_to_api, (size_t)S->n_slots); release(e, S->halo, (size_t)S->n_halo);
@@ -444,7 +449,9 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
     std::vector<std::vector<Half>> rows(TM);
     std::vector<Half> aligned;
     std::vector<std::pair<int32_t, int>> act_here;          // (actuated spring, its record) of the tile being built
-    std::vector<std::pair<int32_t, uint64_t>> act_found;    // (actuated spring, blob byte offset of its rest length), all tiles
+    std::vector<int4> act_rec;                              // per-tile lists, all tiles
+    std::vector<uint32_t> act_tile_off;
+    std::vector<uint8_t> act_seen(e->h_act.size(), 0);      // the first record of a spring is its primary copy
     int cjs[MAX_DEG];
     const bool align_rows = !(getenv("TB_ALIGN_ROWS") && atoi(getenv("TB_ALIGN_ROWS")) == 0);   // measurement aid
     std::vector<int32_t> th;   // halo list of the tile being built (-1 = hole)
@@ -631,8 +638,14 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         M.blob_off16 = (uint32_t)(blob_total / 16); M.blob_bytes = (uint32_t)bb;
         {   // where the rest lengths of this tile's actuated springs sit: after the k array (blob_size / tiled_refresh_params)
             const size_t np = (size_t)((M.n_rec + 1) & ~1u), nk = (dict && split) ? (size_t)((n_rec + 1) & ~1) : np;
-            for (const std::pair<int32_t, int> &a : act_here)
-                act_found.push_back({a.first, (uint64_t)blob_total + (uint64_t)BLOB_REC + nk * 8 + (uint64_t)a.second * 8});
+            act_tile_off.push_back((uint32_t)act_rec.size());
+            for (const std::pair<int32_t, int> &a : act_here) {
+                const size_t j = (size_t)(std::lower_bound(e->h_act.begin(), e->h_act.end(), a.first) - e->h_act.begin());
+                const bool known = j < e->h_act.size() && e->h_act[j] == a.first;
+                act_rec.push_back(make_int4((int)(BLOB_REC + nk * 8 + (size_t)a.second * 8), a.first, (known && !act_seen[j]) ? 1 : 0, 0));
+                if (known) act_seen[j] = 1;
+            }
+            M.tflags = (M.tflags & ~(uint32_t)TF_ACTUATED) | (act_here.empty() ? 0u : (uint32_t)TF_ACTUATED);
         }
         blob_total += bb;
         max_blob = std::max(max_blob, bb);
@@ -696,17 +709,13 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         if (!S->dict_bad) TB_CUDA(e, cudaMalloc((void **)&S->dict_bad, sizeof(int)));
         S->n_rec = (int64_t)rec_spring.size();
     }
-    if (e->any_actuated && !e->h_act.empty()) {
-        std::vector<uint64_t> slots(e->h_act.size() * 2, ~0ull);
-        for (const std::pair<int32_t, uint64_t> &a : act_found) {
-            const size_t j = (size_t)(std::lower_bound(e->h_act.begin(), e->h_act.end(), a.first) - e->h_act.begin());
-            if (j >= e->h_act.size() || e->h_act[j] != a.first) continue;
-            if (slots[2 * j] == ~0ull) slots[2 * j] = a.second;
-            else if (slots[2 * j + 1] == ~0ull) slots[2 * j + 1] = a.second;
-            else { S->why_not = "an actuated spring has records in more than two tiles"; return TB_OK; }
-        }
-        S->n_act_slots = (int64_t)slots.size();
-        TB_TRY(upload_vec(e, &S->act_slots, slots));
+    if (!act_rec.empty()) {
+        act_tile_off.push_back((uint32_t)act_rec.size());
+        S->n_act_rec = (int64_t)act_rec.size();
+        TB_CUDA(e, cudaMalloc((void **)&S->act_tile_off, act_tile_off.size() * sizeof(uint32_t)));
+        TB_CUDA(e, cudaMemcpy(S->act_tile_off, act_tile_off.data(), act_tile_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        TB_CUDA(e, cudaMalloc((void **)&S->act_rec, act_rec.size() * sizeof(int4)));
+        TB_CUDA(e, cudaMemcpy(S->act_rec, act_rec.data(), act_rec.size() * sizeof(int4), cudaMemcpyHostToDevice));
     }
     TB_TRY(dev_alloc(e, &S->blob, blob_total));
     TB_CUDA(e, cudaMemset(S->blob, 0, blob_total));
@@ -910,6 +919,9 @@ struct TiledArgs {
     double *t_out;
     const double *omega_tab;         // [n_omega] distinct actuation frequencies (n_omega == 0: per-spring sin)
     int32_t n_omega;
+    // ---- ACTUATED_* springs (tiles flagged TF_ACTUATED only)
+    const uint32_t *act_tile_off; const int4 *act_rec;
+    double *rest_canon; const int32_t *type; const double *l_max, *l_min, *rate;
     // ---- halo exchange (n_peers == 0: single-engine simulation, everything below unused) ----
     int32_t n_peers;
     int32_t n_boundary_units;        // boundary tiles x consumer warps: arrivals that complete a step's exports
@@ -957,6 +969,29 @@ __device__ __noinline__ void halo_export(const TiledArgs &A, uint32_t exp_rows, 
             d[3 * TM] = vel.x; d[4 * TM] = vel.y; d[5 * TM] = vel.z;
         }
     }
+}
+
+// ACTUATED_EXPAND / ACTUATED_CONTRACT (src/sim.cu:1174-1181): `if (_rest < _l_max) _rest += _rate * dt` /
+// `if (_rest > _l_min) _rest -= _rate * dt`, applied to the spring's record before the force of the step is evaluated.
+__device__ __forceinline__ double advance_rest(int ty, double x, double l_max, double l_min, double rate, double dt) {
+    if (ty == TB_ACTUATED_EXPAND) { if (x < l_max) x = __dadd_rn(x, __dmul_rn(rate, dt)); }
+    else if (ty == TB_ACTUATED_CONTRACT) { if (x > l_min) x = __dsub_rn(x, __dmul_rn(rate, dt)); }
+    return x;
+}
+// The producer warp, before it stages a tile flagged TF_ACTUATED: advance the tile's actuated records in the blob (this
+// CTA is the only reader and writer of this tile's blob), then order those stores before the bulk copy that follows.
+template <class ARGS>
+__device__ __noinline__ void advance_actuated_records(const ARGS &A, double dt, int64_t tile, uint8_t *blob_tile, int lane) {
+    const uint32_t lo = __ldg(A.act_tile_off + tile), hi = __ldg(A.act_tile_off + tile + 1);
+    for (uint32_t q = lo + (uint32_t)lane; q < hi; q += 32) {
+        const int4 r = __ldg(A.act_rec + q);
+        double *slot = reinterpret_cast<double *>(blob_tile + r.x);
+        const double x = advance_rest(A.type[r.y], *slot, A.l_max[r.y], A.l_min[r.y], A.rate[r.y], dt);
+        *slot = x;
+        if (r.z) A.rest_canon[r.y] = x;
+    }
+    __syncwarp();
+    asm volatile("fence.proxy.async;" ::: "memory");
 }
 
 // A consumer warp has finished `pending` boundary tiles: make its peer stores visible, count them, and -- as the
@@ -1098,6 +1133,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 asm volatile("fence.proxy.async;" ::: "memory");   // the bulk copies below read what the peers wrote
                 peers_ready = true;
             }
+            if (m0c.z & TF_ACTUATED)
+                advance_actuated_records(A, G.dt, tile_of(k), const_cast<uint8_t *>(A.blob) + (size_t)(uint32_t)m0a.x * 16, lane);
             if (lane == 0) {
                 TileCtrl *c = reinterpret_cast<TileCtrl *>(smem + sp.off_ctrl) + s;
                 if (HALO) { c->exp_off = (uint32_t)m0c.x; c->exp_rows = (uint32_t)m0c.y; c->tflags = (uint32_t)m0c.z; }
@@ -1554,6 +1591,8 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     A.acc = e->acc;
     A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + (e->cur ^ 1);
     A.omega_tab = S->omega_tab; A.n_omega = S->has_active ? S->n_omega : 0;
+    A.act_tile_off = S->act_tile_off; A.act_rec = S->act_rec;
+    A.rest_canon = e->rest; A.type = e->type; A.l_max = e->l_max; A.l_min = e->l_min; A.rate = e->rate;
     A.step_in = e->step_dev + e->cur; A.step_out = e->step_dev + (e->cur ^ 1);
     A.n_peers = 0; A.n_boundary_units = 0; A.n_boundary_tiles = 0; A.my_flags = nullptr; A.exp_tab = nullptr; A.boundary_done = nullptr; A.halo_err = nullptr;
     for (int p = 0; p < TB_MAX_PEERS; p++) { A.peer_flag[p] = nullptr; A.peer_out[p] = nullptr; }
@@ -1659,6 +1698,9 @@ struct ResidentArgs {
     const double *st_in; double *st_out;
     const uint8_t *blob; const int32_t *slot_to_api, *halo; const uint32_t *ell; const TileMeta *meta;
     double *acc; const double *t_in; double *t_out; const long long *step_in; long long *step_out; const double *omega_tab;
+    // ACTUATED_* springs (tiles flagged TF_ACTUATED only), as in TiledArgs
+    const uint32_t *act_tile_off; const int4 *act_rec;
+    double *rest_canon; const int32_t *type; const double *l_max, *l_min, *rate;
 };
 constexpr int RES_ROWS = MAX_DEG;      // ELL words a thread keeps in registers
 constexpr int RES_MAX_TILES = 8;       // portable thread-block cluster size
@@ -1728,6 +1770,17 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
             rs[r] = P::mul(*reinterpret_cast<const double *>(rb + 8 * r), P::add(1.0, P::mul(c, sintab[slot & 0xffff])));
         }
     };
+    // ACTUATED_* records of this tile: advanced in the resident copy of the blob before every step's forces
+    // (src/sim.cu:1174-1181), written back to HBM (blob and canonical rest array) at the end of the run
+    const uint32_t act_lo = (M.tflags & TF_ACTUATED) ? A.act_tile_off[tile] : 0u, act_hi = (M.tflags & TF_ACTUATED) ? A.act_tile_off[tile + 1] : 0u;
+    const bool has_act = act_hi > act_lo;             // uniform over the CTA
+    auto advance_records = [&]() {
+        for (uint32_t q = act_lo + (uint32_t)t; q < act_hi; q += TM) {
+            const int4 r = A.act_rec[q];
+            double *slot = reinterpret_cast<double *>(smem + r.x);
+            *slot = advance_rest(A.type[r.y], *slot, A.l_max[r.y], A.l_min[r.y], A.rate[r.y], G.dt);
+        }
+    };
     V3 acc = {0.0, 0.0, 0.0};
     if (A.verlet && live) acc = V3{A.acc[i_api], A.acc[X.nm + i_api], A.acc[2 * X.nm + i_api]};
     double t_sim = *A.t_in;
@@ -1763,6 +1816,7 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
         }
     };
     push(0, V3{Pc(0, 0)[t], Pc(0, 1)[t], Pc(0, 2)[t]}, V3{Vc(0, 0)[t], Vc(0, 1)[t], Vc(0, 2)[t]});
+    if (has_act && A.nsteps > 0) { advance_records(); __syncthreads(); }      // for the first step
     if (act_table) { fill_sintab(t_sim); __syncthreads(); scale_records(); }
     cluster.sync();                                   // every CTA's state buffer 0, halo included, is in place
 
@@ -1852,6 +1906,10 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
         Vc(nxt, 0)[t] = vel.x; Vc(nxt, 1)[t] = vel.y; Vc(nxt, 2)[t] = vel.z;
         push(nxt, pos, vel);
         t_sim = __dadd_rn(t_sim, G.dt);               // T += dt, src/sim.cu:1811
+        if (has_act && step + 1 < A.nsteps) {         // the next step's rest lengths: after this step's readers, before the
+            __syncthreads();                          // tables below and the barrier at the top of the next step
+            advance_records();
+        }
         if (act_table) {                              // the tables are read by this CTA's threads only: separate them from
             __syncthreads();                          // this step's readers, the barrier below publishes the new ones
             scale_records();
@@ -1867,6 +1925,15 @@ __global__ void __launch_bounds__(TM, 1) resident_step_kernel(const __grid_const
         for (int c = 0; c < 3; c++) { ob[c * TM] = Pc(cur, c)[t]; ob[(3 + c) * TM] = Vc(cur, c)[t]; }
         if (live && (A.write_acc || A.verlet) && A.nsteps > 0) { A.acc[i_api] = acc.x; A.acc[X.nm + i_api] = acc.y; A.acc[2 * X.nm + i_api] = acc.z; }
         if (tile == 0 && t == 0) { *A.t_out = t_sim; *A.step_out = *A.step_in + A.nsteps; }
+        if (has_act && A.nsteps > 0) {
+            uint8_t *blob_tile = const_cast<uint8_t *>(A.blob) + (size_t)M.blob_off16 * 16;
+            for (uint32_t q = act_lo + (uint32_t)t; q < act_hi; q += TM) {
+                const int4 r = A.act_rec[q];
+                const double x = *reinterpret_cast<const double *>(smem + r.x);
+                *reinterpret_cast<double *>(blob_tile + r.x) = x;
+                if (r.z) A.rest_canon[r.y] = x;
+            }
+        }
     }
 }
 
@@ -1882,7 +1949,6 @@ bool tiled_resident_ok(const Engine *e) {
     const int64_t max_tiles = getenv("TB_RESIDENT_MAX_TILES") ? atoll(getenv("TB_RESIDENT_MAX_TILES")) : std::max(8, e->sm_count);
     if (S->n_tiles < 1 || S->res_cluster < 1 || S->n_tiles > max_tiles || S->n_active != S->n_tiles) return false;
     if (e->any_ghost || e->any_magnet || S->n_exp_tab || S->halo_connected) return false;   // the magnet pass runs between steps
-    if (e->any_actuated) return false;      // ... and so does the _rest mutation of ACTUATED_* springs (advance_rest_kernel)
     return true;
 }
 
@@ -1937,6 +2003,8 @@ int launch_tiled_resident(Engine *e, int nsteps, bool write_acc) {
     A.t_in = e->t_dev + e->cur; A.t_out = e->t_dev + out;
     A.step_in = e->step_dev + e->cur; A.step_out = e->step_dev + out;
     A.omega_tab = S->omega_tab;
+    A.act_tile_off = S->act_tile_off; A.act_rec = S->act_rec;
+    A.rest_canon = e->rest; A.type = e->type; A.l_max = e->l_max; A.l_min = e->l_min; A.rate = e->rate;
     MassExtras X;
     X.ext = nullptr;                                  // a pending one-shot force is consumed by a streaming step first
     X.drag = e->drag;
@@ -1961,13 +2029,6 @@ static_assert(TM == 128 && STATE_BLOCK == 768, "PosView::ld (engine.h) spells th
 void tiled_pos_view(const Engine *e, PosView *v) {
     const TiledState *S = e->tiled;
     v->base = S->st[e->cur]; v->api_to_slot = S->api_to_slot; v->nm = e->nm;
-}
-
-void tiled_actuated_targets(const Engine *e, const uint64_t **slots, uint8_t **blob) {
-    const TiledState *S = e->tiled;
-    const bool ok = S && S->supported && S->act_slots && S->n_act_slots == 2 * e->n_act;
-    *slots = ok ? S->act_slots : nullptr;
-    *blob = ok ? S->blob : nullptr;
 }
 
 bool tiled_halo_connected(const Engine *e) { return e->tiled && e->tiled->halo_connected; }
