@@ -90,6 +90,12 @@ def make_scene(kind):
         sc.damping[:] = np.where(s % 3 == 0, 0.05, 0.0)
         sc.type[:] = np.where(s % 4 == 1, 2, np.where(s % 4 == 2, 3, 0))
         sc.omega[:] = 4 * np.pi
+    if kind == "actuated":      # RobotLink-style springs (device-side _rest mutation), many of them across the slab cuts
+        act = s % 11 == 3
+        sc.type[act] = 4 + (s[act] % 2)
+        sc.l_max[act] = sc.rest[act] * 1.004
+        sc.l_min[act] = sc.rest[act] * 0.996
+        sc.rate[act] = 0.05 + 0.01 * (s[act] % 5)
     return sc, (nx, ny, nz)
 
 
@@ -97,14 +103,15 @@ def upload_part(eng, sc, part, sel_m, sel_s):
     """Upload the local piece of a global oracle scene (sel_m / sel_s: global ids of local masses / springs)."""
     eng.set_topology(sel_m.size, part.left, part.right)
     eng.set_mass_state(pos=sc.pos[sel_m], vel=sc.vel[sel_m], m=sc.m[sel_m])
-    eng.set_spring_params(k=sc.k[sel_s], rest=sc.rest[sel_s], damping=sc.damping[sel_s], type=sc.type[sel_s], omega=sc.omega[sel_s])
+    eng.set_spring_params(k=sc.k[sel_s], rest=sc.rest[sel_s], damping=sc.damping[sel_s], type=sc.type[sel_s], omega=sc.omega[sel_s],
+                          l_max=sc.l_max[sel_s], l_min=sc.l_min[sel_s], rate=sc.rate[sel_s])
     eng.set_planes([tb.Plane((tb.capi.C.c_double * 3)(*p.normal), p.offset, p.friction_k, p.friction_s) for p in sc.planes])
     eng.set_globals(sc.g, sc.dt)
     eng.halo_set_ghosts(part.ghost_local)
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("kind", ["plain", "damped_active"])
+@pytest.mark.parametrize("kind", ["plain", "damped_active", "actuated"])
 @pytest.mark.parametrize("world,flags,tol", [(2, tb.MATH_STRICT, 0.0), (3, tb.MATH_STRICT, 0.0), (3, tb.MATH_FAST, 1e-12)])
 def test_partitioned_engines_match_single_engine(kind, world, flags, tol, monkeypatch):
     monkeypatch.setenv("TB_GRID", "16")     # all engines of the partition co-resident on one GPU
@@ -114,6 +121,7 @@ def test_partitioned_engines_match_single_engine(kind, world, flags, tol, monkey
     scenes.upload(ref, sc)
     ref.run(steps, 0.0)
     want = ref.get_mass_state()
+    want_rest = ref.get_spring_rest()
     ref.close()
     if kind == "plain" and flags == tb.MATH_STRICT:
         o = sc.copy(); o.step(steps)
@@ -138,6 +146,8 @@ def test_partitioned_engines_match_single_engine(kind, world, flags, tol, monkey
         st = en.get_mass_state(fields=("pos", "vel"))
         got_pos[pt.mass_gid[pt.own_local]] = st["pos"][pt.own_local]
         got_vel[pt.mass_gid[pt.own_local]] = st["vel"][pt.own_local]
+        # every engine advanced the rest lengths of its springs (cut ones on both sides) exactly like the single engine
+        assert en.get_spring_rest().tobytes() == want_rest[pt.spring_gid].tobytes()
         # ghosts hold the owner's latest state
         gh = en.get_mass_state(idx=pt.ghost_local, fields=("pos",))["pos"]
         assert np.max(np.abs(gh - want["pos"][pt.ghost_gid])) <= max(tol, 0.0) * 10 + (0 if tol == 0 else 1e-12)
