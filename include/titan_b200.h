@@ -186,6 +186,51 @@ TB_API int tb_halo_set_exports(tb_engine *e, int64_t n, const int32_t *mass_idx,
  * connected, a ghost's state is whatever its owner last pushed: uploads to ghost masses are ignored. */
 TB_API int tb_halo_push_now(tb_engine *e);
 
+/* ---- several GPUs behind one handle (tb_create_partitioned, tb_batch_create) -------------------------
+ * The reference runs one Simulation on one device (no cudaSetDevice anywhere in src/sim.cu) and cannot run two at once
+ * (static flags, include/Titan/sim.h:150-154).  A tb_group owns one engine per listed device IN ONE PROCESS and presents
+ * them as one system in GLOBAL mass / spring numbering:
+ *   tb_create_partitioned  one large system cut by an owner map (engine index per mass; NULL = equal contiguous index
+ *                          ranges, i.e. i-slabs of a reference-ordered lattice).  Each engine holds its own masses, ghost
+ *                          copies of the foreign endpoints of its cut springs and every spring with an own endpoint (global
+ *                          order, so sums are ordered as on one engine: bit-identical under TB_MATH_STRICT); the boundary
+ *                          state is exchanged inside the step kernel over peer memory (tb_halo_*, wired by the group).
+ *   tb_batch_create        independent simulations (the RL batch, BASELINE config C3) laid end to end in the global
+ *                          numbering; whole simulations go to engines in contiguous blocks balanced by mass count: no
+ *                          spring is cut, nothing is exchanged.
+ * The tb_group_* calls mirror their tb_* namesakes with global indices: mass uploads go to the owner (ghost copies follow
+ * by a push before the next run), spring parameters to every engine holding the spring, downloads come from the owner.
+ * One host thread drives the group: launches are asynchronous and the engines meet inside their kernels. */
+typedef struct tb_group tb_group;
+TB_API int tb_create_partitioned(int32_t ndev, const int32_t *devices, uint32_t flags, tb_group **out);
+TB_API int tb_batch_create(int32_t ndev, const int32_t *devices, uint32_t flags, int64_t nsims, const int64_t *masses_per_sim, tb_group **out);
+TB_API void tb_group_destroy(tb_group *g);
+TB_API const char *tb_group_last_error(const tb_group *g);
+TB_API int32_t tb_group_size(const tb_group *g);
+TB_API tb_engine *tb_group_engine(tb_group *g, int32_t r);            /* for tb_get_info and the like; owned by the group */
+TB_API int tb_group_set_topology(tb_group *g, int64_t nm, int64_t ns, const int32_t *left, const int32_t *right, const int32_t *owner);
+TB_API int tb_group_set_tile_hint(tb_group *g, const int32_t *tile_of_mass);
+TB_API int tb_group_set_mass_state(tb_group *g, int64_t first, int64_t count, const int32_t *idx, const double *pos, const double *vel,
+                                   const double *m, const double *T, const double *extern_force, const uint8_t *fixed,
+                                   const int32_t *drag, const uint8_t *valid);
+TB_API int tb_group_set_mass_magnet(tb_group *g, int64_t first, int64_t count, const int32_t *idx, const double *rad,
+                                    const double *stiffness, const double *max_mag_force, const double *mag_scale);
+TB_API int tb_group_get_mass_state(tb_group *g, int64_t first, int64_t count, const int32_t *idx, double *pos, double *vel,
+                                   double *acc, double *T, double *extern_force);
+TB_API int tb_group_set_spring_params(tb_group *g, int64_t first, int64_t count, const int32_t *idx, const double *k,
+                                      const double *rest, const double *damping, const int32_t *type, const double *omega,
+                                      const double *l_max, const double *l_min, const double *rate);
+TB_API int tb_group_get_spring_rest(tb_group *g, int64_t first, int64_t count, const int32_t *idx, double *rest);
+TB_API int tb_group_remove_springs(tb_group *g, int64_t n, const int32_t *idx);
+TB_API int tb_group_set_planes(tb_group *g, int32_t n, const tb_plane *planes);
+TB_API int tb_group_set_balls(tb_group *g, int32_t n, const tb_ball *balls);
+TB_API int tb_group_set_globals(tb_group *g, const double gravity[3], double dt);
+TB_API int tb_group_run_async(tb_group *g, int64_t nsteps, double t0);   /* every engine, same step count */
+TB_API int tb_group_sync(tb_group *g);
+TB_API int tb_group_wait_steps(tb_group *g, int64_t steps);
+TB_API int tb_group_last_run_ms(tb_group *g, double *ms);                /* max over the engines, after tb_group_sync */
+TB_API int tb_group_steps_done(tb_group *g, int64_t *steps);
+
 /* ---- introspection used by tests / bench ---------------------------------------------------------------- */
 typedef struct {
     int64_t nm, ns;

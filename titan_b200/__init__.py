@@ -4,7 +4,7 @@ Python here is plumbing only (ctypes onto the C ABI, build helper, bench/test dr
 libtitan_b200.so (CUDA kernels + C ABI, titan_b200/csrc) and libTitan.so (the C++ `titan::Simulation`
 facade, titan_b200/host + include/Titan).
 """
-from .capi import (Engine, TitanError, Plane, Ball, Local, device_count, lib, LIB_PATH, EXPORTS,  # noqa: F401
+from .capi import (Engine, Group, TitanError, Plane, Ball, Local, device_count, lib, LIB_PATH, EXPORTS,  # noqa: F401
                    MATH_FAST, MATH_STRICT, NO_GRAPH, KERNEL_CSR, INTEGRATOR_VERLET, NO_RESIDENT)
 from .build import build_all  # noqa: F401
 

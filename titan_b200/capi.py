@@ -23,6 +23,11 @@ EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_l
            "tb_export_positions_f32_dev", "tb_export_indices_dev", "tb_read_device", "tb_alloc_host",
            "tb_static_scratch_max_masses", "tb_get_mass_state_static", "tb_halo_set_ghosts", "tb_halo_prepare",
            "tb_halo_state_offsets", "tb_halo_connect", "tb_halo_set_exports", "tb_halo_push_now"]
+EXPORTS += ["tb_create_partitioned", "tb_batch_create", "tb_group_destroy", "tb_group_last_error", "tb_group_size", "tb_group_engine",
+            "tb_group_set_topology", "tb_group_set_tile_hint", "tb_group_set_mass_state", "tb_group_set_mass_magnet",
+            "tb_group_get_mass_state", "tb_group_set_spring_params", "tb_group_get_spring_rest", "tb_group_remove_springs",
+            "tb_group_set_planes", "tb_group_set_balls", "tb_group_set_globals", "tb_group_run_async", "tb_group_sync",
+            "tb_group_wait_steps", "tb_group_last_run_ms", "tb_group_steps_done"]
 MAX_PEERS = 8
 HALO_HANDLE_BYTES = 320
 
@@ -103,6 +108,31 @@ def lib():
         L.tb_halo_connect.argtypes = [_vp, C.c_int32, _vp, _vp]
         L.tb_halo_set_exports.argtypes = [_vp, C.c_int64, _vp, _vp, _vp]
         L.tb_halo_push_now.argtypes = [_vp]
+        L.tb_create_partitioned.argtypes = [C.c_int32, _vp, C.c_uint32, C.POINTER(_vp)]
+        L.tb_batch_create.argtypes = [C.c_int32, _vp, C.c_uint32, C.c_int64, _vp, C.POINTER(_vp)]
+        L.tb_group_destroy.argtypes = [_vp]
+        L.tb_group_destroy.restype = None
+        L.tb_group_last_error.argtypes = [_vp]
+        L.tb_group_last_error.restype = C.c_char_p
+        L.tb_group_size.argtypes = [_vp]
+        L.tb_group_engine.argtypes = [_vp, C.c_int32]
+        L.tb_group_engine.restype = _vp
+        L.tb_group_set_topology.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp, _vp]
+        L.tb_group_set_tile_hint.argtypes = [_vp, _vp]
+        L.tb_group_set_mass_state.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 9
+        L.tb_group_set_mass_magnet.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 5
+        L.tb_group_get_mass_state.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 6
+        L.tb_group_set_spring_params.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 9
+        L.tb_group_get_spring_rest.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp]
+        L.tb_group_remove_springs.argtypes = [_vp, C.c_int64, _vp]
+        L.tb_group_set_planes.argtypes = [_vp, C.c_int32, _vp]
+        L.tb_group_set_balls.argtypes = [_vp, C.c_int32, _vp]
+        L.tb_group_set_globals.argtypes = [_vp, _vp, C.c_double]
+        L.tb_group_run_async.argtypes = [_vp, C.c_int64, C.c_double]
+        L.tb_group_sync.argtypes = [_vp]
+        L.tb_group_wait_steps.argtypes = [_vp, C.c_int64]
+        L.tb_group_last_run_ms.argtypes = [_vp, C.POINTER(C.c_double)]
+        L.tb_group_steps_done.argtypes = [_vp, C.POINTER(C.c_int64)]
         _lib = L
     return _lib
 
@@ -325,3 +355,66 @@ class Engine:
         out = np.empty(shape, dtype=dtype)
         self._ck(self._L.tb_read_device(self._h, out.ctypes.data_as(_vp), _vp(dev_ptr), C.c_size_t(out.nbytes)))
         return out
+
+
+class _GroupLib:
+    """Routes Engine's tb_xxx calls to their tb_group_xxx namesakes (same signatures, global indices)."""
+
+    def __init__(self, L):
+        self._L = L
+
+    def __getattr__(self, name):
+        if name.startswith("tb_") and hasattr(self._L, "tb_group_" + name[3:]):
+            return getattr(self._L, "tb_group_" + name[3:])
+        raise AttributeError("%s has no tb_group_ counterpart" % name)
+
+
+class Group(Engine):
+    """One tb_group: several engines in this process behind one handle (tb_create_partitioned / tb_batch_create).
+    Same methods as Engine, with global mass / spring indices."""
+
+    def __init__(self, devices, flags=MATH_FAST, batch_sizes=None):
+        L = lib()
+        dev, dp = _arr(devices, np.int32)
+        h = _vp()
+        if batch_sizes is None:
+            rc = L.tb_create_partitioned(dev.shape[0], dp, int(flags), C.byref(h))
+        else:
+            bs, bp = _arr(batch_sizes, np.int64)
+            rc = L.tb_batch_create(dev.shape[0], dp, int(flags), bs.shape[0], bp, C.byref(h))
+        if rc != 0:
+            raise TitanError(rc, L.tb_last_error(None).decode())
+        self._raw = L
+        self._L = _GroupLib(L)
+        self._h = h
+        self.nm = self.ns = 0
+
+    def set_topology(self, nm, left, right, owner=None):
+        l, lp = _arr(left, np.int32)
+        r, rp = _arr(right, np.int32)
+        o, op = _arr(owner, np.int32)
+        self._ck(self._raw.tb_group_set_topology(self._h, int(nm), l.shape[0], lp, rp, op))
+        self.nm, self.ns = int(nm), int(l.shape[0])
+
+    def engines(self):
+        return [self._raw.tb_group_engine(self._h, r) for r in range(self._raw.tb_group_size(self._h))]
+
+    def info(self):
+        """per-engine tb_info dicts"""
+        out = []
+        for e in self.engines():
+            i = Info()
+            self._raw.tb_get_info(_vp(e), C.byref(i))
+            out.append({f: getattr(i, f) for f, _ in Info._fields_})
+        return out
+
+    def alloc_pinned(self, shape, dtype=np.float64):
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = _vp()
+        rc = self._raw.tb_alloc_host(_vp(self.engines()[0]), C.c_size_t(n), C.byref(p))
+        if rc != 0:
+            raise TitanError(rc, "tb_alloc_host failed")
+        return np.frombuffer((C.c_char * n).from_address(p.value), dtype=dtype).reshape(shape)
+
+    def set_local_constraints(self, rows):
+        raise NotImplementedError("per-mass local constraints are not routed through tb_group")
