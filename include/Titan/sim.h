@@ -35,6 +35,7 @@
 #include "vec.h"
 
 struct tb_engine;  // include/titan_b200.h
+struct tb_group;
 
 namespace titan {
 
@@ -116,6 +117,12 @@ public:
     Simulation() : Simulation(0, TITAN_B200_INTEGRATOR, Init()) {}
     explicit Simulation(int device) : Simulation(device, TITAN_B200_INTEGRATOR, Init()) {}   // extension: choose the CUDA device (the reference always uses device 0)
     Simulation(int device, int integrator, Init);   // integrator: 0 = Euler (default build), 1 = VERLET build
+    // extension: ONE simulation over several GPUs of this machine (tb_create_partitioned, include/titan_b200.h).  A single
+    // lattice is cut into i-slabs, independent bodies (containers no spring connects) go whole to the GPUs in turn; the
+    // boundary masses are exchanged inside the step kernel over NVLink peer memory.  Same API, same results (the per-mass
+    // summation order is kept); per-mass constraints (Mass::addConstraint) are single-GPU only.
+    explicit Simulation(const std::vector<int> &devices) : Simulation(devices, TITAN_B200_INTEGRATOR, Init()) {}
+    Simulation(const std::vector<int> &devices, int integrator, Init);
     ~Simulation();
     Simulation(const Simulation &) = delete;
     Simulation &operator=(const Simulation &) = delete;
@@ -135,8 +142,11 @@ private:
 
     // ---- engine side -------------------------------------------------------------------------------------------
     tb_engine *engine = nullptr;
+    tb_group *group = nullptr;             // several GPUs: the engines live in the group, `engine` is its first (non-null = started)
     int device = 0;
     int integrator = 0;
+    std::vector<int> devices;
+    struct Dev dev() const;
     void engine_check(int rc, const char *what);
     void upload_everything();              // topology + all state (start, and after topology edits)
     void upload_masses(Mass *const *list, size_t count);

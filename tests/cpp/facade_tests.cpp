@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstring>
 #include <functional>
+#include <memory>
 #include <stdexcept>
 #include <string>
 
@@ -306,11 +307,78 @@ static void gpu_tests() {
     }
 }
 
+// Simulation(std::vector<int> devices): one simulation over several GPUs through the same public API.  `second` = 0 puts both
+// engines on device 0 (single-GPU box; run with TB_GRID=16 so that they are co-resident), 1 uses a second GPU.  With
+// TB_TPM=1 both sides sum a mass's springs in the same order, so the states are identical to the last bit.
+static void multi_tests(int second) {
+    section("one lattice over two GPUs (i-slabs, halo exchange in the step kernel) equals the single-GPU run");
+    {
+        auto run = [&](bool multi, std::vector<double> &out) {
+            std::unique_ptr<Simulation> sim(multi ? new Simulation(std::vector<int>{0, second}) : new Simulation());
+            Lattice *l = sim->createLattice(Vec(0, 0, 0.29), Vec(1.1, 0.5, 0.5), 12, 6, 6);
+            int n = 0;
+            for (Mass *q : l->masses) { q->vel = Vec(0.2 + 0.001 * (n % 7), 0, -0.3 + 0.002 * (n % 5)); n++; }
+            sim->createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
+            sim->start();
+            sim->pause(0.01);
+            sim->getAll();
+            l->masses[100]->pos = l->masses[100]->pos + Vec(0.01, 0, 0);      // edit across the API, both sides alike
+            sim->setAll();
+            sim->resume();
+            sim->pause(0.02);
+            sim->getAll();
+            for (Mass *q : sim->masses) for (int c = 0; c < 3; c++) { out.push_back(q->pos[c]); out.push_back(q->vel[c]); }
+            CHECK(std::fabs(sim->time() - 0.02) < 2e-4);
+            sim->stop();
+        };
+        std::vector<double> one, two;
+        run(false, one);
+        run(true, two);
+        CHECK(one.size() == two.size() && one.size() == 12 * 6 * 6 * 6);
+        double worst = 0;
+        for (size_t q = 0; q < one.size() && q < two.size(); q++) worst = std::max(worst, std::fabs(one[q] - two[q]));
+        std::printf("  max |single - two engines| = %.3e\n", worst);
+        CHECK(worst <= 1e-12);
+    }
+    section("independent bodies go whole to the GPUs (no exchange)");
+    {
+        auto run = [&](bool multi, std::vector<double> &out) {
+            std::unique_ptr<Simulation> sim(multi ? new Simulation(std::vector<int>{0, second}) : new Simulation());
+            for (int r = 0; r < 5; r++) {
+                Lattice *l = sim->createLattice(Vec(1.0 * r, 0, 0.3 + 0.01 * r), Vec(0.4, 0.4, 0.4), 5, 5, 5);
+                int n = 0;
+                for (Spring *s : l->springs) { s->_type = (n % 3 == 1) ? ACTIVE_CONTRACT_THEN_EXPAND : (n % 3 == 2) ? ACTIVE_EXPAND_THEN_CONTRACT : PASSIVE_SOFT; s->_omega = 12.566370614359172; n++; }
+            }
+            sim->createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
+            sim->start();
+            sim->pause(0.015);
+            sim->getAll();
+            for (Mass *q : sim->masses) for (int c = 0; c < 3; c++) out.push_back(q->pos[c]);
+            sim->stop();
+        };
+        std::vector<double> one, two;
+        run(false, one);
+        run(true, two);
+        double worst = 0;
+        for (size_t q = 0; q < one.size() && q < two.size(); q++) worst = std::max(worst, std::fabs(one[q] - two[q]));
+        std::printf("  max |single - two engines| = %.3e\n", worst);
+        CHECK(one.size() == two.size() && worst <= 1e-12);
+    }
+    section("per-mass constraints are refused on several GPUs");
+    {
+        Simulation sim(std::vector<int>{0, second});
+        Lattice *l = sim.createLattice(Vec(0, 0, 1), Vec(1, 1, 1), 4, 4, 4);
+        l->masses[3]->addConstraint(CONSTRAINT_PLANE, Vec(0, 0, 1), 0.1);
+        CHECK(throws([&] { sim.start(); }, "multi-GPU"));
+    }
+}
+
 int main(int argc, char **argv) {
     const std::string what = argc > 1 ? argv[1] : "host";
     if (what == "host") host_tests();
     else if (what == "gpu") gpu_tests();
-    else { std::fprintf(stderr, "usage: %s host|gpu\n", argv[0]); return 2; }
+    else if (what == "multi") multi_tests(argc > 2 ? std::atoi(argv[2]) : 0);
+    else { std::fprintf(stderr, "usage: %s host|gpu|multi [second device]\n", argv[0]); return 2; }
     std::printf("%d checks, %d failed\n", g_checks, g_failed);
     return g_failed;
 }

@@ -86,6 +86,18 @@ def test_gpu_behaviour():
     assert r.returncode == 0, r.stdout[-3000:]
 
 
+@pytest.mark.gpu
+def test_simulation_over_several_gpus():
+    """titan::Simulation(std::vector<int> devices): same API, same results; on a single-GPU box both engines share device 0."""
+    import titan_b200 as tb
+    second = 1 if tb.device_count() >= 2 else 0
+    env = dict(os.environ, TB_GRID="16", TB_TPM="1")
+    r = subprocess.run([os.path.join(BIN, "titan_facade_tests"), "multi", str(second)], env=env, stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=600)
+    print(r.stdout[-3000:])
+    assert r.returncode == 0, r.stdout[-3000:]
+
+
 CASES = [(n, False) for n in sorted(scenes.SCENARIOS)] + [(n, True) for n in scenes.VERLET_SCENARIOS]
 
 

@@ -22,6 +22,45 @@
 
 namespace titan {
 
+// One GPU or several behind the same calls: every engine call of this file goes through a Dev, which forwards to the single
+// engine or to the group (include/titan_b200.h, tb_group_*: the same signatures with global indices).
+struct Dev { tb_engine *e; tb_group *g; };
+namespace {
+inline const char *dv_last_error(Dev d) { return d.g ? tb_group_last_error(d.g) : tb_last_error(d.e); }
+inline int dv_set_topology(Dev d, int64_t nm, int64_t ns, const int32_t *l, const int32_t *r, const int32_t *owner) {
+    return d.g ? tb_group_set_topology(d.g, nm, ns, l, r, owner) : tb_set_topology(d.e, nm, ns, l, r);
+}
+inline int dv_set_tile_hint(Dev d, const int32_t *h) { return d.g ? tb_group_set_tile_hint(d.g, h) : tb_set_tile_hint(d.e, h); }
+inline int dv_set_mass_state(Dev d, int64_t first, int64_t count, const int32_t *idx, const double *pos, const double *vel, const double *m,
+                             const double *T, const double *ext, const uint8_t *fixed, const int32_t *drag, const uint8_t *valid) {
+    return d.g ? tb_group_set_mass_state(d.g, first, count, idx, pos, vel, m, T, ext, fixed, drag, valid)
+               : tb_set_mass_state(d.e, first, count, idx, pos, vel, m, T, ext, fixed, drag, valid);
+}
+inline int dv_set_mass_magnet(Dev d, int64_t first, int64_t count, const int32_t *idx, const double *a, const double *b, const double *c, const double *e) {
+    return d.g ? tb_group_set_mass_magnet(d.g, first, count, idx, a, b, c, e) : tb_set_mass_magnet(d.e, first, count, idx, a, b, c, e);
+}
+inline int dv_get_mass_state(Dev d, int64_t first, int64_t count, const int32_t *idx, double *pos, double *vel, double *acc, double *T, double *ext) {
+    return d.g ? tb_group_get_mass_state(d.g, first, count, idx, pos, vel, acc, T, ext) : tb_get_mass_state(d.e, first, count, idx, pos, vel, acc, T, ext);
+}
+inline int dv_set_spring_params(Dev d, int64_t first, int64_t count, const int32_t *idx, const double *k, const double *rest, const double *damping,
+                                const int32_t *type, const double *omega, const double *lmax, const double *lmin, const double *rate) {
+    return d.g ? tb_group_set_spring_params(d.g, first, count, idx, k, rest, damping, type, omega, lmax, lmin, rate)
+               : tb_set_spring_params(d.e, first, count, idx, k, rest, damping, type, omega, lmax, lmin, rate);
+}
+inline int dv_get_spring_rest(Dev d, int64_t first, int64_t count, const int32_t *idx, double *rest) {
+    return d.g ? tb_group_get_spring_rest(d.g, first, count, idx, rest) : tb_get_spring_rest(d.e, first, count, idx, rest);
+}
+inline int dv_remove_springs(Dev d, int64_t n, const int32_t *idx) { return d.g ? tb_group_remove_springs(d.g, n, idx) : tb_remove_springs(d.e, n, idx); }
+inline int dv_set_planes(Dev d, int32_t n, const tb_plane *p) { return d.g ? tb_group_set_planes(d.g, n, p) : tb_set_planes(d.e, n, p); }
+inline int dv_set_balls(Dev d, int32_t n, const tb_ball *b) { return d.g ? tb_group_set_balls(d.g, n, b) : tb_set_balls(d.e, n, b); }
+inline int dv_set_globals(Dev d, const double g[3], double dt) { return d.g ? tb_group_set_globals(d.g, g, dt) : tb_set_globals(d.e, g, dt); }
+inline int dv_run_async(Dev d, int64_t n, double t0) { return d.g ? tb_group_run_async(d.g, n, t0) : tb_run_async(d.e, n, t0); }
+inline int dv_sync(Dev d) { return d.g ? tb_group_sync(d.g) : tb_sync(d.e); }
+inline int dv_wait_steps(Dev d, int64_t n) { return d.g ? tb_group_wait_steps(d.g, n) : tb_wait_steps(d.e, n); }
+inline int dv_steps_done(Dev d, int64_t *n) { return d.g ? tb_group_steps_done(d.g, n) : tb_steps_done(d.e, n); }
+inline int dv_alloc_host(Dev d, size_t bytes, void **out) { return tb_alloc_host(d.g ? tb_group_engine(d.g, 0) : d.e, bytes, out); }
+}  // namespace
+
 namespace {
 const char *kEnded = "The simulation has ended. Cannot modify simulation after the end of the simulation.";
 const char *kRunning = "The simulation is running. Stop the simulation to make changes.";
@@ -32,6 +71,11 @@ const char *kNotStarted = "The simulation has not started. Get and set commands 
 
 Simulation::Simulation(int device_, int integrator_, Init)
     : device(device_), integrator(integrator_), dt(0.0001), T(0), _global_acc(0, 0, -9.81) {}   // src/sim.cu:76-86
+
+Simulation::Simulation(const std::vector<int> &devices_, int integrator_, Init)
+    : device(devices_.empty() ? 0 : devices_[0]), integrator(integrator_), devices(devices_), dt(0.0001), T(0), _global_acc(0, 0, -9.81) {}
+
+Dev Simulation::dev() const { return Dev{engine, group}; }
 
 Mass *Simulation::createMass(Mass *m) {   // src/sim.cu:222-253
     if (ENDED) throw std::runtime_error(kEnded);
@@ -99,7 +143,7 @@ void Simulation::deleteSpring(Spring *s) {   // src/sim.cu:382-412
         // unchanged): no topology rebuild; compaction happens at the next create*() re-upload
         if (s->slot >= 0 && !topology_dirty) {
             int32_t slot = s->slot;
-            engine_check(tb_remove_springs(engine, 1, &slot), "tb_remove_springs");
+            engine_check(dv_remove_springs(dev(), 1, &slot), "tb_remove_springs");
         } else {
             topology_dirty = true;
         }
@@ -259,7 +303,7 @@ void Simulation::printPositions() {
 // ================================================================ (2) the packer =================================
 void Simulation::engine_check(int rc, const char *what) {
     if (rc == TB_OK) return;
-    std::string msg = std::string(what) + ": " + (engine ? tb_last_error(engine) : tb_last_error(nullptr));
+    std::string msg = std::string(what) + ": " + (engine ? dv_last_error(dev()) : tb_last_error(nullptr));
     throw std::runtime_error(msg);
 }
 
@@ -440,7 +484,7 @@ bool Simulation::upload_masses_whole() {
     if (hs->cap < n) {
         const size_t cap = n + n / 4 + 1024;
         void *p = nullptr;
-        engine_check(tb_alloc_host(engine, cap * 13 * sizeof(double), &p), "tb_alloc_host");
+        engine_check(dv_alloc_host(dev(), cap * 13 * sizeof(double), &p), "tb_alloc_host");
         double *d = (double *)p;
         hs->pos = d; hs->vel = d + 3 * cap; hs->acc = d + 6 * cap; hs->ext = d + 9 * cap; hs->T = d + 12 * cap;
         hs->cap = cap;
@@ -491,12 +535,12 @@ bool Simulation::upload_masses_whole() {
     const bool up_ext = ext_nonzero || hs->ext_uploaded_nonzero || first;
     std::vector<uint8_t> valid;
     if (first) valid.assign(n, 1);
-    engine_check(tb_set_mass_state(engine, 0, (int64_t)n, nullptr, hs->pos, hs->vel, (ch & 1u) ? hs->m.data() : nullptr, hs->T,
+    engine_check(dv_set_mass_state(dev(), 0, (int64_t)n, nullptr, hs->pos, hs->vel, (ch & 1u) ? hs->m.data() : nullptr, hs->T,
                                    up_ext ? hs->ext : nullptr, (ch & 2u) ? hs->fixed.data() : nullptr, (ch & 4u) ? hs->drag.data() : nullptr,
                                    first ? valid.data() : nullptr), "tb_set_mass_state");
     hs->ext_uploaded_nonzero = ext_nonzero;
     if (ch & 8u)
-        engine_check(tb_set_mass_magnet(engine, 0, (int64_t)n, nullptr, hs->rad.data(), hs->stiff.data(), hs->maxmag.data(), hs->magscale.data()), "tb_set_mass_magnet");
+        engine_check(dv_set_mass_magnet(dev(), 0, (int64_t)n, nullptr, hs->rad.data(), hs->stiff.data(), hs->maxmag.data(), hs->magscale.data()), "tb_set_mass_magnet");
     hs->mass_valid = true;
     if (lc_changed) local_dirty = true;
     if (local_dirty) upload_local_constraints();
@@ -531,9 +575,9 @@ void Simulation::upload_masses(Mass *const *list, size_t count) {
     if (n == 0) return;
     const bool whole = n == (int64_t)masses.size() && P.idx.front() == 0 && P.idx.back() == n - 1 && std::is_sorted(P.idx.begin(), P.idx.end());
     const int32_t *idx = whole ? nullptr : P.idx.data();
-    engine_check(tb_set_mass_state(engine, 0, n, idx, P.pos.data(), P.vel.data(), P.m.data(), P.T.data(), P.ext.data(),
+    engine_check(dv_set_mass_state(dev(), 0, n, idx, P.pos.data(), P.vel.data(), P.m.data(), P.T.data(), P.ext.data(),
                                    P.fixed.data(), P.drag.data(), P.valid.data()), "tb_set_mass_state");
-    engine_check(tb_set_mass_magnet(engine, 0, n, idx, P.rad.data(), P.stiff.data(), P.maxmag.data(), P.magscale.data()), "tb_set_mass_magnet");
+    engine_check(dv_set_mass_magnet(dev(), 0, n, idx, P.rad.data(), P.stiff.data(), P.maxmag.data(), P.magscale.data()), "tb_set_mass_magnet");
     if (lc_changed) local_dirty = true;
     if (local_dirty) upload_local_constraints();
 }
@@ -577,7 +621,7 @@ bool Simulation::upload_springs_whole() {
     unsigned ch = first ? 0xffu : changed.load();
     if (actuated) ch |= 2u;                  // the device advances _rest of ACTUATED_* springs: the host value always goes down
     if (ch)
-        engine_check(tb_set_spring_params(engine, 0, (int64_t)n, nullptr, (ch & 1u) ? hs->k.data() : nullptr, (ch & 2u) ? hs->rest.data() : nullptr,
+        engine_check(dv_set_spring_params(dev(), 0, (int64_t)n, nullptr, (ch & 1u) ? hs->k.data() : nullptr, (ch & 2u) ? hs->rest.data() : nullptr,
                                           (ch & 4u) ? hs->damping.data() : nullptr, (ch & 128u) ? hs->type.data() : nullptr,
                                           (ch & 8u) ? hs->omega.data() : nullptr, (ch & 16u) ? hs->lmax.data() : nullptr,
                                           (ch & 32u) ? hs->lmin.data() : nullptr, (ch & 64u) ? hs->rate.data() : nullptr), "tb_set_spring_params");
@@ -595,7 +639,7 @@ bool Simulation::download_masses_whole() {
     });
     if (!in_order) return false;
     PhaseTimer pt("getAll");
-    engine_check(tb_get_mass_state(engine, 0, (int64_t)n, nullptr, hs->pos, hs->vel, hs->acc, hs->T, hs->ext), "tb_get_mass_state");
+    engine_check(dv_get_mass_state(dev(), 0, (int64_t)n, nullptr, hs->pos, hs->vel, hs->acc, hs->T, hs->ext), "tb_get_mass_state");
     pt.lap("download");
     parallel_for(n, [&](size_t lo, size_t hi) {
         for (size_t j = lo; j < hi; j++) {
@@ -628,7 +672,7 @@ void Simulation::upload_springs(Spring *const *list, size_t count) {
     const int64_t n = (int64_t)idx.size();
     if (n == 0) return;
     const bool whole = n == (int64_t)springs.size() && idx.front() == 0 && idx.back() == n - 1 && std::is_sorted(idx.begin(), idx.end());
-    engine_check(tb_set_spring_params(engine, 0, n, whole ? nullptr : idx.data(), k.data(), rest.data(), damping.data(), type.data(),
+    engine_check(dv_set_spring_params(dev(), 0, n, whole ? nullptr : idx.data(), k.data(), rest.data(), damping.data(), type.data(),
                                       omega.data(), lmax.data(), lmin.data(), rate.data()), "tb_set_spring_params");
 }
 
@@ -642,7 +686,7 @@ void Simulation::download_masses(Mass *const *list, size_t count) {
     if (n == 0) return;
     std::vector<double> pos(3 * n), vel(3 * n), acc(3 * n), tt(n), ext(3 * n);
     const bool whole = n == (int64_t)masses.size() && idx.front() == 0 && idx.back() == n - 1 && std::is_sorted(idx.begin(), idx.end());
-    engine_check(tb_get_mass_state(engine, 0, n, whole ? nullptr : idx.data(), pos.data(), vel.data(), acc.data(), tt.data(), ext.data()),
+    engine_check(dv_get_mass_state(dev(), 0, n, whole ? nullptr : idx.data(), pos.data(), vel.data(), acc.data(), tt.data(), ext.data()),
                  "tb_get_mass_state");
     for (int64_t j = 0; j < n; j++) {
         Mass *q = who[(size_t)j];
@@ -664,10 +708,10 @@ void Simulation::upload_constraints() {
         r.radius = b._radius;
         balls.push_back(r);
     }
-    engine_check(tb_set_planes(engine, (int32_t)planes.size(), planes.data()), "tb_set_planes");
-    engine_check(tb_set_balls(engine, (int32_t)balls.size(), balls.data()), "tb_set_balls");
+    engine_check(dv_set_planes(dev(), (int32_t)planes.size(), planes.data()), "tb_set_planes");
+    engine_check(dv_set_balls(dev(), (int32_t)balls.size(), balls.data()), "tb_set_balls");
     const double g[3] = {_global_acc[0], _global_acc[1], _global_acc[2]};
-    engine_check(tb_set_globals(engine, g, dt), "tb_set_globals");
+    engine_check(dv_set_globals(dev(), g, dt), "tb_set_globals");
     dt_engine = dt;        // what execute() accumulates T with: setTimeStep() while running takes effect at the next resume()
     constraints_dirty = false;
 }
@@ -686,6 +730,11 @@ void Simulation::upload_local_constraints() {
         }
         ptr[i + 1] = (int64_t)rec.size();
     }
+    if (group) {
+        if (!rec.empty()) throw std::runtime_error("per-mass constraints (Mass::addConstraint) are not available on a multi-GPU Simulation");
+        local_dirty = false;
+        return;
+    }
     engine_check(tb_set_local_constraints(engine, rec.empty() ? nullptr : ptr.data(), rec.data()), "tb_set_local_constraints");
     local_dirty = false;
 }
@@ -702,27 +751,78 @@ void Simulation::upload_everything() {
         left[(size_t)s] = (sp->_left && sp->_left->valid) ? sp->_left->slot : -1;
         right[(size_t)s] = (sp->_right && sp->_right->valid) ? sp->_right->slot : -1;
     }
-    engine_check(tb_set_topology(engine, nm, ns, left.data(), right.data()), "tb_set_topology");
-    if (hs) { hs->mass_valid = hs->spring_valid = hs->ext_uploaded_nonzero = false; }   // the device is back at its defaults
-
-    // tile hint: bricks of lattice cells when every mass belongs to exactly one regular grid container
+    // ---- several GPUs: who owns which mass -----------------------------------------------------------------------
+    // (a) one grid container holding every mass (createLattice): i-slabs, whole planes per GPU, each slab with its own bricks;
+    // (b) bodies no spring connects (every mass in exactly one container): whole containers to the GPUs in turn, balanced by
+    //     mass count -- nothing is exchanged; (c) anything else: equal contiguous index ranges, tiles by coordinate bisection.
+    std::vector<int32_t> owner;
     std::vector<int32_t> hint((size_t)nm, -1);
-    int32_t base = 0;
     bool covered = true;
-    for (Container *c : containers) {
-        if (!c->grid_nx || c->masses.size() != (size_t)c->grid_nx * c->grid_ny * c->grid_nz) continue;
-        std::vector<int32_t> ids;
-        const int32_t n_tiles = brick_ids(c->grid_nx, c->grid_ny, c->grid_nz, base, ids);
-        for (size_t q = 0; q < ids.size(); q++) {
-            const Mass *m = c->masses[q];
-            if (m->slot < 0 || masses[(size_t)m->slot] != m) { covered = false; continue; }
-            if (hint[(size_t)m->slot] >= 0) covered = false;   // shared between two grids
-            hint[(size_t)m->slot] = ids[q];
+    const size_t W = group ? devices.size() : 1;
+    const Container *grid = nullptr;
+    if (containers.size() == 1 && containers[0]->grid_nx && containers[0]->masses.size() == (size_t)nm &&
+        (size_t)containers[0]->grid_nx * containers[0]->grid_ny * containers[0]->grid_nz == (size_t)nm)
+        grid = containers[0];
+    if (grid) for (int64_t i = 0; i < nm && grid; i++) if (grid->masses[(size_t)i] != masses[(size_t)i]) grid = nullptr;   // same order
+    if (group && grid && (size_t)grid->grid_nx >= W) {
+        const int nx = grid->grid_nx, plane = grid->grid_ny * grid->grid_nz;
+        owner.resize((size_t)nm);
+        int32_t base = 0;
+        for (size_t r = 0; r < W; r++) {
+            const int lo = (int)(r * (size_t)(nx / (int)W) + std::min<size_t>(r, (size_t)(nx % (int)W)));
+            const int hi = lo + nx / (int)W + (r < (size_t)(nx % (int)W) ? 1 : 0);
+            std::vector<int32_t> ids;
+            const int32_t n_tiles = brick_ids(hi - lo, grid->grid_ny, grid->grid_nz, base, ids);
+            for (int64_t i = (int64_t)lo * plane; i < (int64_t)hi * plane; i++) { owner[(size_t)i] = (int32_t)r; hint[(size_t)i] = ids[(size_t)(i - (int64_t)lo * plane)]; }
+            base += n_tiles;
         }
-        base += n_tiles;
+    } else {
+        // tile hint: bricks of lattice cells when every mass belongs to exactly one regular grid container
+        std::vector<int32_t> cid((size_t)nm, -1);
+        bool one_container_each = true;
+        int32_t base = 0, c_index = 0;
+        for (Container *c : containers) {
+            for (const Mass *m : c->masses) {
+                if (m->slot < 0 || masses[(size_t)m->slot] != m) continue;
+                if (cid[(size_t)m->slot] >= 0) one_container_each = false;
+                cid[(size_t)m->slot] = c_index;
+            }
+            c_index++;
+            if (!c->grid_nx || c->masses.size() != (size_t)c->grid_nx * c->grid_ny * c->grid_nz) continue;
+            std::vector<int32_t> ids;
+            const int32_t n_tiles = brick_ids(c->grid_nx, c->grid_ny, c->grid_nz, base, ids);
+            for (size_t q = 0; q < ids.size(); q++) {
+                const Mass *m = c->masses[q];
+                if (m->slot < 0 || masses[(size_t)m->slot] != m) { covered = false; continue; }
+                if (hint[(size_t)m->slot] >= 0) covered = false;   // shared between two grids
+                hint[(size_t)m->slot] = ids[q];
+            }
+            base += n_tiles;
+        }
+        for (int64_t i = 0; covered && i < nm; i++) covered = hint[(size_t)i] >= 0;
+        if (group) {
+            for (int64_t i = 0; one_container_each && i < nm; i++) one_container_each = cid[(size_t)i] >= 0;
+            for (int64_t sidx = 0; one_container_each && sidx < ns; sidx++)
+                if (left[(size_t)sidx] >= 0 && right[(size_t)sidx] >= 0 && cid[(size_t)left[(size_t)sidx]] != cid[(size_t)right[(size_t)sidx]]) one_container_each = false;
+            if (one_container_each && containers.size() >= W) {
+                std::vector<int64_t> count(containers.size(), 0);
+                for (int64_t i = 0; i < nm; i++) count[(size_t)cid[(size_t)i]]++;
+                std::vector<int32_t> where(containers.size(), 0);
+                int64_t at = 0;
+                size_t r = 0;
+                for (size_t c = 0; c < containers.size(); c++) {
+                    while (r + 1 < W && at * (int64_t)W >= (int64_t)(r + 1) * nm) r++;
+                    where[c] = (int32_t)r;
+                    at += count[c];
+                }
+                owner.resize((size_t)nm);
+                for (int64_t i = 0; i < nm; i++) owner[(size_t)i] = where[(size_t)cid[(size_t)i]];
+            }
+        }
     }
-    for (int64_t i = 0; covered && i < nm; i++) covered = hint[(size_t)i] >= 0;
-    if (covered && nm > 0) engine_check(tb_set_tile_hint(engine, hint.data()), "tb_set_tile_hint");
+    engine_check(dv_set_topology(dev(), nm, ns, left.data(), right.data(), owner.empty() ? nullptr : owner.data()), "tb_set_topology");
+    if (hs) { hs->mass_valid = hs->spring_valid = hs->ext_uploaded_nonzero = false; }   // the device is back at its defaults
+    if (covered && nm > 0) engine_check(dv_set_tile_hint(dev(), hint.data()), "tb_set_tile_hint");
 
     dev_local.assign((size_t)nm, {});
     local_dirty = false;
@@ -752,7 +852,7 @@ void Simulation::sync_topology() {
         std::vector<int32_t> idx;
         std::vector<double> rest(old_s.size());
         for (Spring *s : old_s) idx.push_back(s->slot);
-        engine_check(tb_get_spring_rest(engine, 0, (int64_t)idx.size(), idx.data(), rest.data()), "tb_get_spring_rest");
+        engine_check(dv_get_spring_rest(dev(), 0, (int64_t)idx.size(), idx.data(), rest.data()), "tb_get_spring_rest");
         for (size_t j = 0; j < old_s.size(); j++) { host_rest[j] = old_s[j]->_rest; old_s[j]->_rest = rest[j]; }
     }
     upload_everything();
@@ -783,7 +883,7 @@ void Simulation::get(Spring *s) {   // src/sim.cu:618-631; Spring::update copies
     sync_topology();
     if (s->slot < 0) return;
     int32_t idx = s->slot;
-    engine_check(tb_get_spring_rest(engine, 0, 1, &idx, &s->_rest), "tb_get_spring_rest");
+    engine_check(dv_get_spring_rest(dev(), 0, 1, &idx, &s->_rest), "tb_get_spring_rest");
 }
 
 void Simulation::set(Spring *s) {   // src/sim.cu:633-641
@@ -840,13 +940,20 @@ void Simulation::start() {   // src/sim.cu:1547-1591
     std::cout << "Starting simulation with " << masses.size() << " masses and " << springs.size() << " springs." << std::endl;
 
     // no CUDA device -> TB_ERR_NO_DEVICE -> exception: there is no CPU path
-    engine_check(tb_create(device, TB_MATH_FAST | (integrator == 1 ? TB_INTEGRATOR_VERLET : 0u), &engine), "tb_create");
+    const uint32_t eflags = TB_MATH_FAST | (integrator == 1 ? TB_INTEGRATOR_VERLET : 0u);
+    if (devices.size() > 1) {
+        std::vector<int32_t> dv(devices.begin(), devices.end());
+        engine_check(tb_create_partitioned((int32_t)dv.size(), dv.data(), eflags, &group), "tb_create_partitioned");
+        engine = tb_group_engine(group, 0);      // non-null marks "on the device"; every call goes through dev()
+    } else {
+        engine_check(tb_create(device, eflags, &engine), "tb_create");
+    }
     try {
         upload_everything();
-        engine_check(tb_run_async(engine, 0, 0.0), "tb_run_async");   // validates the scene and brings the device layout up to date
+        engine_check(dv_run_async(dev(), 0, 0.0), "tb_run_async");   // validates the scene and brings the device layout up to date
     } catch (...) {
-        tb_destroy(engine);
-        engine = nullptr;
+        if (group) tb_group_destroy(group); else tb_destroy(engine);
+        engine = nullptr; group = nullptr;
         throw;
     }
     T = 0;
@@ -875,10 +982,10 @@ void Simulation::execute() {
     int64_t base = 0;                         // engine step count at the last drain
     struct Batch { int64_t upto; double T_after; std::chrono::steady_clock::time_point t_enq; int64_t n; };
     std::deque<Batch> inflight;
-    tb_steps_done(engine, &base);
+    dv_steps_done(dev(), &base);
     auto fail_and_park = [&](const char *what) {
         std::unique_lock<std::mutex> lk(mtx);
-        gpu_error = std::string(what) + tb_last_error(engine);
+        gpu_error = std::string(what) + dv_last_error(dev());
         RUNNING = false;
         cv.notify_all();
         cv.wait(lk, [&] { return ENDED.load(); });
@@ -888,8 +995,8 @@ void Simulation::execute() {
         {
             std::unique_lock<std::mutex> lk(mtx);
             if (!bpts.empty() && *bpts.begin() <= T_enq) {
-                int rc = tb_sync(engine);   // cudaDeviceSynchronize at the breakpoint, :1708
-                if (rc != TB_OK) gpu_error = std::string("tb_sync: ") + tb_last_error(engine);
+                int rc = dv_sync(dev());   // cudaDeviceSynchronize at the breakpoint, :1708
+                if (rc != TB_OK) gpu_error = std::string("tb_sync: ") + dv_last_error(dev());
                 T = T_enq;
                 inflight.clear();
                 bpts.erase(bpts.begin());
@@ -899,7 +1006,7 @@ void Simulation::execute() {
                 if (ENDED) return;
                 // the user thread may have stepped / edited while paused: pick up its time and the engine's step count
                 T_enq = T; enq = 0;
-                tb_steps_done(engine, &base);
+                dv_steps_done(dev(), &base);
                 continue;
             }
             if (ENDED) return;
@@ -909,14 +1016,14 @@ void Simulation::execute() {
         double t = T_enq;
         int64_t n = 0;
         while (n < chunk && !(next_bp <= t)) { t += step_dt; n++; }
-        if (tb_run_async(engine, n, T_enq) != TB_OK) { fail_and_park("step failed: "); return; }
+        if (dv_run_async(dev(), n, T_enq) != TB_OK) { fail_and_park("step failed: "); return; }
         enq += n;
         T_enq = t;
         inflight.push_back({base + enq, t, std::chrono::steady_clock::now(), n});
         while (inflight.size() >= 2) {        // wait for the older batch; the newer one keeps the device busy
             const Batch b = inflight.front();
             inflight.pop_front();
-            if (tb_wait_steps(engine, b.upto) != TB_OK) { fail_and_park("step failed: "); return; }
+            if (dv_wait_steps(dev(), b.upto) != TB_OK) { fail_and_park("step failed: "); return; }
             T = b.T_after;
             cv.notify_all();
             // about one millisecond of device time per batch (the wait above returns once per batch in steady state)
@@ -937,7 +1044,7 @@ void Simulation::resume() {   // src/sim.cu:1684-1702
     if (RUNNING) return;
     sync_topology();
     if (constraints_dirty) upload_constraints();   // planes/balls created while paused, new dt or g (update_constraints, :1756-1771)
-    engine_check(tb_run_async(engine, 0, T), "tb_run_async");
+    engine_check(dv_run_async(dev(), 0, T), "tb_run_async");
     {
         std::lock_guard<std::mutex> lk(mtx);
         RUNNING = true;
@@ -952,11 +1059,11 @@ void Simulation::step(int n) {
     if (n <= 0) return;
     sync_topology();
     if (constraints_dirty) upload_constraints();
-    engine_check(tb_run_async(engine, n, T), "tb_run_async");
+    engine_check(dv_run_async(dev(), n, T), "tb_run_async");
     double t = T;
     for (int j = 0; j < n; j++) t += dt_engine;
     T = t;
-    engine_check(tb_sync(engine), "tb_sync");
+    engine_check(dv_sync(dev()), "tb_sync");
 }
 
 void Simulation::setBreakpoint(double time) {   // src/sim.cu:814-820
@@ -1016,6 +1123,7 @@ void Simulation::stop(double t) {   // src/sim.cu:1533-1545
 // (src/sim.cu:131-182).
 void Simulation::freeGPU() {
     if (FREED) return;
+    if (group) { tb_group_destroy(group); group = nullptr; engine = nullptr; }
     if (engine) { tb_destroy(engine); engine = nullptr; }
     delete hs; hs = nullptr;               // its pinned arrays went with the engine
     for (Spring *s : springs) delete s;
