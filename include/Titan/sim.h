@@ -34,6 +34,7 @@
 #include "spring.h"
 #include "vec.h"
 
+#define TITAN_B200_FACADE 1   // lets a user program tell this drop-in from the reference headers (multi-GPU constructor, step())
 struct tb_engine;  // include/titan_b200.h
 struct tb_group;
 
@@ -154,7 +155,10 @@ private:
     void download_masses(Mass *const *list, size_t count);
     void upload_constraints();             // global planes/balls + globals (g, dt)
     void upload_local_constraints();
-    void sync_topology();                  // re-upload after create*/delete* while paused, keeping device state
+    void sync_topology();                  // create*/delete* while paused reach the device: appended / invalidated in place, or re-uploaded
+    bool append_topology();                // new masses / springs at the end of the lists -> tb_add_masses / tb_add_springs
+    bool append_dirty = false;
+    int64_t dev_nm = 0, dev_ns = 0;        // masses / springs the device holds (deleted ones keep their index)
     struct HostStage;                      // pinned staging arrays + shadow of the parameter arrays the device holds (sim.cpp)
     HostStage *hs = nullptr;
     bool upload_masses_whole();            // setAll / start fast paths: packed by all host cores into pinned memory, parameter

@@ -117,9 +117,25 @@ TB_API int tb_set_spring_params(tb_engine *e, int64_t first, int64_t count, cons
                          const double *omega, const double *l_max, const double *l_min, const double *rate);
 /* Simulation::deleteSpring after start() (src/sim.cu:382-412) without a topology rebuild: the listed springs become
  * tombstones -- they keep their index but exert no force from now on (k and damping forced to zero, also after later
- * tb_set_spring_params calls), which is bit-identical to their absence.  Compaction = a new tb_set_topology.
+ * tb_set_spring_params calls), which is bit-identical to their absence.  Compaction: tb_compact.
  * Used by the topology-optimisation workload (BASELINE config C5: remove the weakest springs every 100 steps). */
 TB_API int tb_remove_springs(tb_engine *e, int64_t n, const int32_t *idx);
+/* Periodic compaction (thrust::remove in the reference's delete paths, src/sim.cu:371,401,519-552): rebuilds the device layout
+ * at the next run without the incidence words of removed springs.  Mass and spring indices do not change.  Removals of up to a
+ * few thousand springs are compacted on the spot, tile by tile; large scattered removals (topology optimisation) are better
+ * left in place: their dead words cost ~0.1 % of a step, while dropping them makes every tile's incidence block unique and
+ * defeats the content dedupe that keeps a lattice's blocks L2-resident (measured on C5: 168 -> 151 G spring-steps/s). */
+TB_API int tb_compact(tb_engine *e);
+/* Simulation::createMass / createSpring after start() (src/sim.cu:231-253,300-322), without re-uploading the system: the arrays
+ * grow by n entries with the defaults of tb_set_topology (the new masses are [old nm, old nm + n), the new springs
+ * [old ns, old ns + n): fill them with tb_set_mass_state / tb_set_spring_params), and at the next run only the tiles the new
+ * springs touch are rebuilt; new masses get tiles of their own.  Results equal a fresh upload of the enlarged system (the
+ * per-mass summation order is by spring index whatever the tiling).  TB_ERR_UNSUPPORTED where only a re-upload will do
+ * (engines of a partition; tb_add_masses with magnet fields or per-mass constraints on the device).
+ * Simulation::deleteMass after start (:343-380) is tb_set_mass_state(valid = 0): the mass freezes and its springs become
+ * tombstones, again without a rebuild. */
+TB_API int tb_add_masses(tb_engine *e, int64_t n);
+TB_API int tb_add_springs(tb_engine *e, int64_t n, const int32_t *left, const int32_t *right);
 /* Spring::update copies back only _rest (src/spring.cu:12-14) */
 TB_API int tb_get_spring_rest(tb_engine *e, int64_t first, int64_t count, const int32_t *idx, double *rest);
 

@@ -309,7 +309,50 @@ static int do_bench_e2e(const std::string &cfg, long steps, long batches) {
     return 0;
 }
 
+#ifdef TITAN_B200_FACADE
+/* bench_multi: ONE lattice over ndev GPUs through titan::Simulation(std::vector<int>) -- the facade cuts it into i-slabs
+ * (tb_create_partitioned), the boundary masses are exchanged inside the step kernel.  Wall clock around pause(). */
+static int do_bench_multi(const std::string &cfg, long steps, int ndev) {
+    std::vector<int> devices;
+    for (int d = 0; d < ndev; d++) devices.push_back(d);
+    Simulation sim(devices);
+    int n = (cfg == "c2") ? 100 : atoi(cfg.c_str() + 7);
+    if (n < 2) { fprintf(stderr, "bench_multi: config latticeN\n"); return 2; }
+    double side = 0.1 * (n - 1);
+    auto t0 = std::chrono::steady_clock::now();
+    sim.createLattice(Vec(0, 0, side / 2 - 0.001), Vec(side, side, side), n, n, n);
+    sim.createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
+    size_t ns = sim.springs.size(), nm = sim.masses.size();
+    double dt = sim.getTimeStep();
+    auto t1 = std::chrono::steady_clock::now();
+    sim.start();
+    sim.pause(0.0);
+    auto t2 = std::chrono::steady_clock::now();
+    double T = sim.time();
+    sim.resume(); sim.pause(T + 99.5 * dt);                    /* warm-up: 100 steps */
+    double Ta = sim.time();
+    auto t3 = std::chrono::steady_clock::now();
+    sim.resume(); sim.pause(Ta + (steps - 0.5) * dt);
+    auto t4 = std::chrono::steady_clock::now();
+    long done = lround((sim.time() - Ta) / dt);
+    double sec = std::chrono::duration<double>(t4 - t3).count();
+    sim.getAll();
+    double check = 0;
+    for (Mass *q : sim.masses) check += q->pos[2];
+    printf("{\"impl\": \"" DUMP_IMPL "\", \"mode\": \"multi\", \"config\": \"%s\", \"n_gpus\": %d, \"masses\": %zu, \"springs\": %zu, "
+           "\"steps\": %ld, \"seconds\": %.6f, \"spring_steps_per_s\": %.6e, \"build_seconds\": %.3f, \"upload_seconds\": %.3f, \"mean_z\": %.17g}\n",
+           cfg.c_str(), ndev, nm, ns, done, sec, (double)ns * done / sec, std::chrono::duration<double>(t1 - t0).count(),
+           std::chrono::duration<double>(t2 - t1).count(), check / (double)nm);
+    fflush(stdout);
+    sim.stop();
+    return 0;
+}
+#endif
+
 int main(int argc, char **argv) {
+#ifdef TITAN_B200_FACADE
+    if (argc >= 5 && !strcmp(argv[1], "bench_multi")) return do_bench_multi(argv[2], atol(argv[3]), atoi(argv[4]));
+#endif
     if (argc >= 5 && !strcmp(argv[1], "bench_e2e")) return do_bench_e2e(argv[2], atol(argv[3]), atol(argv[4]));
     if (argc >= 4 && !strcmp(argv[1], "dump")) return do_dump(argv[2], argv[3]);
     if (argc >= 4 && !strcmp(argv[1], "init")) return do_dump(argv[2], argv[3], true);

@@ -18,7 +18,7 @@ CONSTRAINT_PLANE, CONTACT_PLANE, BALL, DIRECTION = range(4)
 
 EXPORTS = ["tb_abi_version", "tb_device_count", "tb_create", "tb_destroy", "tb_last_error", "tb_set_topology", "tb_set_tile_hint",
            "tb_set_mass_state", "tb_set_mass_magnet", "tb_get_mass_state", "tb_set_spring_params",
-           "tb_get_spring_rest", "tb_remove_springs", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
+           "tb_get_spring_rest", "tb_remove_springs", "tb_compact", "tb_add_masses", "tb_add_springs", "tb_set_planes", "tb_set_balls", "tb_set_local_constraints", "tb_set_globals",
            "tb_run_async", "tb_sync", "tb_steps_done", "tb_wait_steps", "tb_last_run_ms", "tb_get_info",
            "tb_export_positions_f32_dev", "tb_export_indices_dev", "tb_read_device", "tb_alloc_host",
            "tb_static_scratch_max_masses", "tb_get_mass_state_static", "tb_halo_set_ghosts", "tb_halo_prepare",
@@ -85,6 +85,9 @@ def lib():
         L.tb_set_spring_params.argtypes = [_vp, C.c_int64, C.c_int64] + [_vp] * 9
         L.tb_get_spring_rest.argtypes = [_vp, C.c_int64, C.c_int64, _vp, _vp]
         L.tb_remove_springs.argtypes = [_vp, C.c_int64, _vp]
+        L.tb_add_masses.argtypes = [_vp, C.c_int64]
+        L.tb_compact.argtypes = [_vp]
+        L.tb_add_springs.argtypes = [_vp, C.c_int64, _vp, _vp]
         L.tb_set_planes.argtypes = [_vp, C.c_int32, _vp]
         L.tb_set_balls.argtypes = [_vp, C.c_int32, _vp]
         L.tb_set_local_constraints.argtypes = [_vp, _vp, _vp]
@@ -300,6 +303,25 @@ class Engine:
         """Turn springs into tombstones (no force from now on; indices of the others unchanged)."""
         a, ap = _arr(idx, np.int32)
         self._ck(self._L.tb_remove_springs(self._h, a.shape[0], ap))
+
+    def compact(self):
+        self._ck(self._L.tb_compact(self._h))
+
+    def add_masses(self, n):
+        """Grow by n masses (defaults); returns the index of the first new one."""
+        first = self.nm
+        self._ck(self._L.tb_add_masses(self._h, int(n)))
+        self.nm += int(n)
+        return first
+
+    def add_springs(self, left, right):
+        """Grow by len(left) springs (default parameters); returns the index of the first new one."""
+        l, lp = _arr(left, np.int32)
+        r, rp = _arr(right, np.int32)
+        first = self.ns
+        self._ck(self._L.tb_add_springs(self._h, l.shape[0], lp, rp))
+        self.ns += int(l.shape[0])
+        return first
 
     def alloc_pinned(self, shape, dtype=np.float64):
         """A numpy array over page-locked host memory (tb_alloc_host); freed with the engine."""

@@ -221,7 +221,9 @@ static void free_all(Engine *e) {
     F(e->m, m1); F(e->mflags, (size_t)e->nm); F(e->drag, (size_t)e->nm * 4);
     F(e->left, s4); F(e->right, s4); F(e->type, s4);
     F(e->k, s1); F(e->rest, s1); F(e->damping, s1); F(e->omega, s1); F(e->l_max, s1); F(e->l_min, s1); F(e->rate, s1);
-    F(e->row_ptr, (size_t)(e->nm + 1) * 4); F(e->adj, (size_t)e->ns * 8);
+    F(e->row_ptr, (size_t)e->row_ptr_cap * 4); F(e->adj, (size_t)e->adj_cap * 4); e->row_ptr_cap = e->adj_cap = 0;
+    e->csr_nm = e->csr_ns = 0; e->extra_adj.clear(); e->patch_masses.clear(); e->patch_springs.clear();
+    e->patch_needs_layout = e->removed_unpatched = e->compact_requested = false;
     F(e->export_f32, (size_t)e->nm * 12);
     F(e->export_idx, (size_t)e->ns * 8);
     F(e->removed_dev, (size_t)e->ns);
@@ -342,7 +344,6 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
     TB_TRY(dev_alloc(e, &e->mflags, (size_t)nm));
     TB_TRY(dev_alloc(e, &e->left, (size_t)ns)); TB_TRY(dev_alloc(e, &e->right, (size_t)ns));
     TB_TRY(dev_alloc(e, &e->k, (size_t)ns)); TB_TRY(dev_alloc(e, &e->rest, (size_t)ns));
-    TB_TRY(dev_alloc(e, &e->row_ptr, (size_t)nm + 1)); TB_TRY(dev_alloc(e, &e->adj, (size_t)ns * 2));
     for (int p = 0; p < 2; p++) {
         TB_CUDA(e, cudaMemsetAsync(e->pos[p], 0, n3 * 8, e->stream));
         TB_CUDA(e, cudaMemsetAsync(e->vel[p], 0, n3 * 8, e->stream));
@@ -356,28 +357,9 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
         TB_CUDA(e, cudaMemcpyAsync(e->left, left, (size_t)ns * 4, cudaMemcpyHostToDevice, e->stream));
         TB_CUDA(e, cudaMemcpyAsync(e->right, right, (size_t)ns * 4, cudaMemcpyHostToDevice, e->stream));
     }
-    // CSR incidence: ascending spring index per mass; right entry before left entry (the reference adds to
-    // the right endpoint first, src/sim.cu:1187-1193)
     e->h_left.assign(left, left + ns); e->h_right.assign(right, right + ns);
-    std::vector<int32_t> &ptr = e->h_row_ptr;
-    ptr.assign((size_t)nm + 1, 0);
-    for (int64_t s = 0; s < ns; s++) {
-        if (left[s] < 0 || right[s] < 0) continue;
-        ptr[(size_t)right[s] + 1]++; ptr[(size_t)left[s] + 1]++;
-    }
-    for (int64_t i = 0; i < nm; i++) ptr[(size_t)i + 1] += ptr[(size_t)i];
-    std::vector<int32_t> &adj = e->h_adj;
-    adj.assign((size_t)std::max<int64_t>(1, ptr[(size_t)nm]), 0);
-    {
-        std::vector<int32_t> cursor(ptr.begin(), ptr.end() - 1);
-        for (int64_t s = 0; s < ns; s++) {
-            if (left[s] < 0 || right[s] < 0) continue;
-            adj[(size_t)cursor[(size_t)right[s]]++] = (int32_t)(2 * s + 1);
-            adj[(size_t)cursor[(size_t)left[s]]++] = (int32_t)(2 * s);
-        }
-    }
-    TB_CUDA(e, cudaMemcpyAsync(e->row_ptr, ptr.data(), ((size_t)nm + 1) * 4, cudaMemcpyHostToDevice, e->stream));
-    if (ptr[(size_t)nm]) TB_CUDA(e, cudaMemcpyAsync(e->adj, adj.data(), (size_t)ptr[(size_t)nm] * 4, cudaMemcpyHostToDevice, e->stream));
+    e->csr_nm = e->csr_ns = 0; e->extra_adj.clear();
+    TB_TRY(ensure_csr(e));
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
     e->h_flags.assign((size_t)nm, F_VALID);
     e->h_T0.assign((size_t)nm, 0.0);
@@ -442,12 +424,23 @@ int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
         if (e->drag) TB_TRY(up_scalar<int32_t>(e, e->drag, drag, idx, first, count));
     }
     bool flags_changed = false, valid_changed = false;
+    std::vector<int32_t> orphaned;        // springs of masses that just became invalid
     for (int64_t j = 0; j < count; j++) {
         int64_t i = idx ? idx[j] : first + j;
         uint8_t f = e->h_flags[(size_t)i], nf = f;
         if (fixed) nf = (uint8_t)((nf & ~F_FIXED) | (fixed[j] ? F_FIXED : 0));
         if (valid) nf = (uint8_t)((nf & ~F_VALID) | (valid[j] ? F_VALID : 0));
-        if (nf != f) { e->h_flags[(size_t)i] = nf; flags_changed = true; valid_changed |= ((nf ^ f) & F_VALID) != 0; }
+        if (nf != f) {
+            e->h_flags[(size_t)i] = nf; flags_changed = true;
+            if ((f & F_VALID) && !(nf & F_VALID) && !(e->flags & TB_KERNEL_CSR)) {
+                // Simulation::deleteMass after start (src/sim.cu:343-380): the mass is frozen and every spring attached to it
+                // is skipped from now on (:1163).  No structure rebuild: the tile's flag byte freezes the mass, and its springs
+                // become tombstones (tb_remove_springs), which is bit-identical to skipping them.
+                if (i < e->csr_nm) for (int32_t q = e->h_row_ptr[(size_t)i]; q < e->h_row_ptr[(size_t)i + 1]; q++) orphaned.push_back(e->h_adj[(size_t)q] >> 1);
+                auto it = e->extra_adj.find((int32_t)i);
+                if (it != e->extra_adj.end()) for (int32_t a : it->second) orphaned.push_back(a >> 1);
+            } else valid_changed |= ((nf ^ f) & F_VALID) != 0;
+        }
         if (T) { e->h_T0[(size_t)i] = T[j]; e->h_n0[(size_t)i] = e->steps_done; }
         else if (nf != f) {
             // fixed/valid status changes: freeze the T accumulated so far (under the OLD flags) and restart
@@ -464,6 +457,11 @@ int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
     if (pos || vel || m) e->tiled_stale |= TS_STATE;
     if (flags_changed) e->tiled_stale |= TS_FLAGS | (valid_changed ? TS_STRUCT : 0u);
     if (flags_changed || drag) e->graph_dirty = true;
+    if (!orphaned.empty()) {
+        std::sort(orphaned.begin(), orphaned.end());
+        orphaned.erase(std::unique(orphaned.begin(), orphaned.end()), orphaned.end());
+        TB_TRY(tb_remove_springs(e, (int64_t)orphaned.size(), orphaned.data()));
+    }
     return TB_OK;
 }
 
@@ -616,7 +614,128 @@ int tb_remove_springs(tb_engine *e, int64_t n, const int32_t *idx) {
     TB_TRY(up_scalar<uint8_t>(e, e->removed_dev, ones.data(), idx, 0, n));
     apply_tombstones_kernel<<<blocks_for(e->ns), 256, 0, e->stream>>>(e->k, e->damping, e->removed_dev, e->ns);
     TB_CUDA(e, cudaGetLastError());
+    // A handful of springs: the tiles holding them are rebuilt without them (no dead incidence words, parameter classes
+    // untouched).  Many (topology optimisation removes 0.1 % of all springs at a time, everywhere): they stay in place with
+    // k = 0 until the next rebuild of their tile or tb_compact.
+    if (n <= 4096 && e->patch_springs.size() + (size_t)n <= 8192 && !e->any_ghost && !tiled_halo_connected(e)) {
+        for (int64_t j = 0; j < n; j++) e->patch_springs.push_back(idx[j]);
+        e->tiled_stale |= TS_PATCH;
+    } else e->removed_unpatched = true;
     e->tiled_stale |= TS_PARAMS;
+    e->graph_dirty = true;
+    return TB_OK;
+}
+
+int tb_compact(tb_engine *e) {
+    E_CHECK(e);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_compact before tb_set_topology");
+    if (tiled_halo_connected(e)) return fail(e, TB_ERR_UNSUPPORTED, "tb_compact: not on a connected engine of a partition (its peers hold offsets into the layout)");
+    e->compact_requested = true;
+    e->tiled_stale |= TS_STRUCT;          // this rebuild leaves the incidence words of removed springs out of the rows
+    e->graph_dirty = true;
+    return TB_OK;
+}
+
+}  // extern "C"
+
+namespace tb {
+// n_old -> n_new elements (x3 planes when `planes` == 3: [3][n] arrays change their plane stride), new entries = value
+template <class T> __global__ void regrow_kernel(T *dst, const T *src, int64_t n_old, int64_t n_new, int planes, T value) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_new * planes) return;
+    const int64_t c = q / n_new, i = q % n_new;
+    dst[q] = i < n_old ? src[c * n_old + i] : value;
+}
+template <class T> static int regrow(Engine *e, T **p, int64_t n_old, int64_t n_new, int planes, T value) {
+    if (!*p) return TB_OK;             // optional array that was never allocated: stays that way
+    T *bigger = nullptr;
+    TB_TRY(dev_alloc(e, &bigger, (size_t)(n_new * planes)));
+    regrow_kernel<T><<<blocks_for(n_new * planes), 256, 0, e->stream>>>(bigger, *p, n_old, n_new, planes, value);
+    TB_CUDA(e, cudaGetLastError());
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    dev_free(e, (void *)*p, (size_t)(n_old * planes) * sizeof(T));
+    *p = bigger;
+    return TB_OK;
+}
+}  // namespace tb
+
+extern "C" {
+
+int tb_add_masses(tb_engine *e, int64_t n) {
+    E_CHECK(e);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_add_masses before tb_set_topology");
+    if (n < 0 || e->nm + n >= (int64_t)1 << 31) return fail(e, TB_ERR_INVALID, "tb_add_masses: bad count");
+    if (n == 0) return TB_OK;
+    if (e->any_ghost || tiled_halo_connected(e)) return fail(e, TB_ERR_UNSUPPORTED, "tb_add_masses: not on an engine of a partition (re-upload the topology)");
+    if (e->mag_rad || e->lc_ptr) return fail(e, TB_ERR_UNSUPPORTED, "tb_add_masses: not with magnet fields or per-mass constraints on the device (re-upload the topology)");
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (e->canon_stale) TB_TRY(tiled_to_canonical(e));     // the canonical arrays are about to move
+    const int64_t n0 = e->nm, n1 = e->nm + n;
+    for (int p = 0; p < 2; p++) { TB_TRY(regrow<double>(e, &e->pos[p], n0, n1, 3, 0.0)); TB_TRY(regrow<double>(e, &e->vel[p], n0, n1, 3, 0.0)); }
+    TB_TRY(regrow<double>(e, &e->acc, n0, n1, 3, 0.0));
+    TB_TRY(regrow<double>(e, &e->ext, n0, n1, 3, 0.0));
+    TB_TRY(regrow<double>(e, &e->m, n0, n1, 1, 0.1));                    // Mass default, include/Titan/mass.h:18
+    TB_TRY(regrow<uint8_t>(e, &e->mflags, n0, n1, 1, (uint8_t)F_VALID));
+    TB_TRY(regrow<int32_t>(e, &e->drag, n0, n1, 1, 0));
+    dev_free(e, (void *)e->export_f32, (size_t)n0 * 12); e->export_f32 = nullptr;
+    e->h_flags.resize((size_t)n1, F_VALID);
+    e->h_T0.resize((size_t)n1, 0.0);
+    e->h_n0.resize((size_t)n1, e->steps_done);
+    if (!e->tile_hint.empty()) {       // the new masses stay together in tiles of their own at the next full build
+        int32_t fresh = 0;
+        for (int32_t h : e->tile_hint) fresh = std::max(fresh, h + 1);
+        e->tile_hint.resize((size_t)n1, fresh);
+    }
+    for (int64_t i = n0; i < n1; i++) e->patch_masses.push_back((int32_t)i);
+    e->patch_needs_layout = true;
+    e->nm = n1;
+    e->tiled_stale |= TS_PATCH | TS_STATE | TS_FLAGS;
+    e->graph_dirty = true;
+    return TB_OK;
+}
+
+int tb_add_springs(tb_engine *e, int64_t n, const int32_t *left, const int32_t *right) {
+    E_CHECK(e);
+    if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_add_springs before tb_set_topology");
+    if (n < 0 || (n > 0 && (!left || !right)) || e->ns + n >= (int64_t)1 << 30) return fail(e, TB_ERR_INVALID, "tb_add_springs: bad arguments");
+    if (n == 0) return TB_OK;
+    for (int64_t j = 0; j < n; j++)
+        if (left[j] < -1 || left[j] >= e->nm || right[j] < -1 || right[j] >= e->nm) return fail(e, TB_ERR_INVALID, "tb_add_springs: spring %lld has an endpoint outside [-1,%lld)", (long long)j, (long long)e->nm);
+    if (tiled_halo_connected(e)) return fail(e, TB_ERR_UNSUPPORTED, "tb_add_springs: not on a connected engine of a partition (re-upload the topology)");
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    const int64_t n0 = e->ns, n1 = e->ns + n;
+    if (n0 == 0) {       // a system that had no spring at all: the arrays were allocated with one placeholder element
+        dev_free(e, (void *)e->left, 4); dev_free(e, (void *)e->right, 4); dev_free(e, (void *)e->k, 8); dev_free(e, (void *)e->rest, 8);
+        TB_TRY(dev_alloc(e, &e->left, (size_t)n1)); TB_TRY(dev_alloc(e, &e->right, (size_t)n1)); TB_TRY(dev_alloc(e, &e->k, (size_t)n1)); TB_TRY(dev_alloc(e, &e->rest, (size_t)n1));
+        TB_TRY(fill<double>(e, e->k, 10000.0, n1)); TB_TRY(fill<double>(e, e->rest, 1.0, n1));
+    } else {
+        TB_TRY(regrow<int32_t>(e, &e->left, n0, n1, 1, -1)); TB_TRY(regrow<int32_t>(e, &e->right, n0, n1, 1, -1));
+        TB_TRY(regrow<double>(e, &e->k, n0, n1, 1, 10000.0));               // Spring default, include/Titan/spring.h:25
+        TB_TRY(regrow<double>(e, &e->rest, n0, n1, 1, 1.0));
+    }
+    TB_TRY(regrow<int32_t>(e, &e->type, n0, n1, 1, 0));
+    TB_TRY(regrow<double>(e, &e->damping, n0, n1, 1, 0.0)); TB_TRY(regrow<double>(e, &e->omega, n0, n1, 1, 0.0));
+    TB_TRY(regrow<double>(e, &e->l_max, n0, n1, 1, 0.0)); TB_TRY(regrow<double>(e, &e->l_min, n0, n1, 1, 0.0));
+    TB_TRY(regrow<double>(e, &e->rate, n0, n1, 1, 0.0));
+    TB_TRY(regrow<uint8_t>(e, &e->removed_dev, n0, n1, 1, (uint8_t)0));
+    dev_free(e, (void *)e->export_idx, (size_t)n0 * 8); e->export_idx = nullptr;
+    TB_CUDA(e, cudaMemcpy(e->left + n0, left, (size_t)n * 4, cudaMemcpyHostToDevice));
+    TB_CUDA(e, cudaMemcpy(e->right + n0, right, (size_t)n * 4, cudaMemcpyHostToDevice));
+    e->h_left.insert(e->h_left.end(), left, left + n); e->h_right.insert(e->h_right.end(), right, right + n);
+    e->h_type.resize((size_t)n1, 0);
+    if (!e->h_omega.empty()) e->h_omega.resize((size_t)n1, 0.0);
+    if (!e->h_removed.empty()) e->h_removed.resize((size_t)n1, 0);
+    for (int64_t j = 0; j < n; j++) {
+        const int32_t s = (int32_t)(n0 + j);
+        e->patch_springs.push_back(s);
+        if (left[j] < 0 || right[j] < 0) continue;
+        e->extra_adj[right[j]].push_back(2 * s + 1);
+        e->extra_adj[left[j]].push_back(2 * s);
+    }
+    e->ns = n1;
+    e->patch_needs_layout = true;
+    e->tiled_stale |= TS_PATCH | TS_PARAMS;
+    e->graph_dirty = true;
     return TB_OK;
 }
 
@@ -740,6 +859,45 @@ __global__ void advance_rest_kernel(double *rest, const int32_t *type, const dou
     rest[s] = x;
 }
 
+// CSR incidence from the host copy of the topology: ascending spring index per mass; right entry before left entry (the
+// reference adds to the right endpoint first, src/sim.cu:1187-1193).  Springs with a null endpoint have no entry.
+int ensure_csr(Engine *e) {
+    if (e->csr_nm == e->nm && e->csr_ns == e->ns && e->extra_adj.empty()) return TB_OK;
+    const int64_t nm = e->nm, ns = e->ns;
+    const std::vector<int32_t> &left = e->h_left, &right = e->h_right;
+    std::vector<int32_t> &ptr = e->h_row_ptr;
+    ptr.assign((size_t)nm + 1, 0);
+    for (int64_t s = 0; s < ns; s++) {
+        if (left[(size_t)s] < 0 || right[(size_t)s] < 0) continue;
+        ptr[(size_t)right[(size_t)s] + 1]++; ptr[(size_t)left[(size_t)s] + 1]++;
+    }
+    for (int64_t i = 0; i < nm; i++) ptr[(size_t)i + 1] += ptr[(size_t)i];
+    std::vector<int32_t> &adj = e->h_adj;
+    adj.assign((size_t)std::max<int64_t>(1, ptr[(size_t)nm]), 0);
+    {
+        std::vector<int32_t> cursor(ptr.begin(), ptr.end() - 1);
+        for (int64_t s = 0; s < ns; s++) {
+            if (left[(size_t)s] < 0 || right[(size_t)s] < 0) continue;
+            adj[(size_t)cursor[(size_t)right[(size_t)s]]++] = (int32_t)(2 * s + 1);
+            adj[(size_t)cursor[(size_t)left[(size_t)s]]++] = (int32_t)(2 * s);
+        }
+    }
+    TB_CUDA(e, cudaStreamSynchronize(e->stream));
+    if (e->row_ptr_cap < nm + 1) {
+        dev_free(e, (void *)e->row_ptr, (size_t)e->row_ptr_cap * 4); e->row_ptr = nullptr;
+        TB_TRY(dev_alloc(e, &e->row_ptr, (size_t)nm + 1)); e->row_ptr_cap = nm + 1;
+    }
+    if (e->adj_cap < (int64_t)adj.size()) {
+        dev_free(e, (void *)e->adj, (size_t)e->adj_cap * 4); e->adj = nullptr;
+        TB_TRY(dev_alloc(e, &e->adj, adj.size())); e->adj_cap = (int64_t)adj.size();
+    }
+    TB_CUDA(e, cudaMemcpy(e->row_ptr, ptr.data(), ((size_t)nm + 1) * 4, cudaMemcpyHostToDevice));
+    TB_CUDA(e, cudaMemcpy(e->adj, adj.data(), adj.size() * 4, cudaMemcpyHostToDevice));
+    e->csr_nm = nm; e->csr_ns = ns; e->extra_adj.clear();
+    e->graph_dirty = true;
+    return TB_OK;
+}
+
 // (re)builds the device list of actuated springs; outside any stream capture (it allocates)
 int prepare_actuated(Engine *e) {
     if (!e->act_dirty) return TB_OK;
@@ -819,6 +977,7 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     }
     if (use_tiled(e)) TB_TRY(tiled_prepare(e));       // may discover that the graph does not fit the tiled format
     if (!use_tiled(e) && e->canon_stale) TB_TRY(tiled_to_canonical(e));
+    if (!use_tiled(e)) TB_TRY(ensure_csr(e));
     if (nsteps == 0) return TB_OK;                    // validation + device layout brought up to date, nothing launched
     if (!use_tiled(e) && e->any_ghost) return fail(e, TB_ERR_UNSUPPORTED, "ghost masses (halo exchange) need the tiled step kernel, which does not support this scene");
     TB_CUDA(e, cudaEventRecord(e->ev0, e->stream));

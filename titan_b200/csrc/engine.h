@@ -14,6 +14,7 @@
 
 #include <cstdint>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -24,7 +25,7 @@ namespace tb {
 
 enum : uint8_t { F_FIXED = 1, F_VALID = 2, F_LOCAL = 4, F_GHOST = 8 };   // ghost: state supplied by a peer engine (halo exchange)
 // what a setter invalidated in the tiled layout: structure (tiles/ELL), spring parameters, mass state, mass flags
-enum : uint32_t { TS_STRUCT = 1, TS_PARAMS = 2, TS_STATE = 4, TS_FLAGS = 8 };
+enum : uint32_t { TS_STRUCT = 1, TS_PARAMS = 2, TS_STATE = 4, TS_FLAGS = 8, TS_PATCH = 16 };   // PATCH: masses / springs were appended
 
 struct DtSegment { int64_t first_step; double dt; };
 
@@ -87,6 +88,14 @@ struct Engine {
     int64_t n_removed = 0;
     std::vector<double> h_omega;   // mirror of the actuation frequencies (distinct-omega sine table of the tiled kernel)
     std::vector<int32_t> h_left, h_right, h_row_ptr, h_adj;  // host copy of the topology + CSR (tile builder)
+    // the CSR covers masses [0, csr_nm) and springs [0, csr_ns); incidences of springs added since (tb_add_springs) wait in
+    // extra_adj (mass -> 2*spring+side, ascending) until ensure_csr folds them in
+    int64_t csr_nm = 0, csr_ns = 0, row_ptr_cap = 0, adj_cap = 0;
+    std::vector<int32_t> patch_masses, patch_springs;        // added / removed since the tiled layout was last brought up to date (TS_PATCH)
+    bool patch_needs_layout = false;      // ... and some of them are additions: if the tiles cannot be patched, everything is rebuilt
+    bool compact_requested = false;       // tb_compact: the next full build leaves the incidence words of removed springs out
+    bool removed_unpatched = false;       // tombstones whose incidence words are still in their tiles (they read k = 0 from their record)
+    std::unordered_map<int32_t, std::vector<int32_t>> extra_adj;
     std::vector<double> h_T0;      // per-mass T at its last upload
     std::vector<int64_t> h_n0;     // steps_done at that upload
     std::vector<DtSegment> dt_log;
@@ -132,6 +141,8 @@ int fail(Engine *e, int status, const char *fmt, ...);
 template <class T> int dev_alloc(Engine *e, T **p, size_t count);
 void dev_free(Engine *e, void *p, size_t bytes);
 
+// engine.cu: host + device CSR brought up to date with the current topology (after tb_add_masses / tb_add_springs)
+int ensure_csr(Engine *e);
 // engine.cu: (re)builds e->act_idx / e->h_act, the list of ACTUATED_* springs; allocates, so never under stream capture
 int prepare_actuated(Engine *e);
 // csr_step.cu

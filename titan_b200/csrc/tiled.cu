@@ -30,9 +30,12 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
+#include <chrono>
 #include <map>
 #include <mutex>
 #include <numeric>
+#include <thread>
 #include <unordered_map>
 
 #include <unistd.h>
@@ -106,7 +109,31 @@ static_assert(sizeof(TileMeta) == 48, "TileMeta is copied as three 16-byte words
 enum : uint32_t { TF_BOUNDARY = 1, TF_ACTUATED = 2 };   // ACTUATED: records of this tile are advanced before it is staged
 //   // the tile's springs reach ghost masses: wait for the peers before reading, signal after
 
+// a parameter class of the dictionary modes: bit patterns of (k, rest, damping, omega) + actuation code / private tag
+struct ClassKey { uint64_t a, b, c, d, t; bool operator==(const ClassKey &o) const { return a == o.a && b == o.b && c == o.c && d == o.d && t == o.t; } };
+struct ClassKeyHash { size_t operator()(const ClassKey &x) const {
+    uint64_t h = x.a * 0x9E3779B97F4A7C15ull; h ^= (x.b + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full; h ^= h >> 29;
+    h ^= x.c * 0x165667B19E3779F9ull; h ^= (x.d + x.t) * 0x27D4EB2F165667C5ull; return (size_t)(h ^ (h >> 32)); } };
+
+// Host copies of the tables the tiled kernel reads, kept so that single tiles can be rebuilt later (merge_tile).
+struct HostTables {
+    std::unordered_map<ClassKey, int32_t, ClassKeyHash> class_seen;   // class key -> dense id
+    std::vector<int32_t> class_first;                            // class id -> first spring (the representative)
+    std::vector<uint32_t> ell;                                   // deduplicated incidence blocks (without the prefetch tail)
+    std::map<uint64_t, std::vector<uint32_t>> ell_index;         // content hash -> offsets of stored blocks
+    int64_t unique_blocks = 0;
+    std::vector<int32_t> halo, rec_spring, kslot_spring;
+    std::vector<uint32_t> krec_off;                              // split dictionary: (first slot, slots) per tile in kslot_spring
+    std::vector<uint8_t> rec_map;
+    std::vector<int32_t> class_of, rep_of;                       // parameter classes (dictionary modes)
+    std::vector<std::vector<int4>> act;                          // per tile: actuated records
+    std::vector<int32_t> tile_slots;                             // per tile: record slots
+    size_t blob_total = 0;
+};
+
 struct TiledState {
+    HostTables H;
+    int build_mode = 1;                   // record mode of the last build (1 full dictionary, 2 split, 0 plain)
     int64_t n_tiles = 0, n_slots = 0, n_rec = 0, n_ell = 0, n_halo = 0;
     size_t blob_bytes = 0;
     int max_halo = 0, max_rec = 0, max_deg = 0, max_blob = 0;
@@ -348,44 +375,425 @@ static int choose_tpm(const Engine *e, int64_t n_tiles) {
 constexpr int DICT_CTAS = TB_DICT_CTAS;   // resident CTAs per SM the dictionary-mode kernels are compiled for (register cap)
 constexpr int DICT_MAX_TILE = 256;        // records a tile's byte map can address
 constexpr int DICT_MAX_GLOBAL = 1 << 16;
-static int param_classes(Engine *e, bool with_k, bool damping, bool active, std::vector<int32_t> &class_of, std::vector<int32_t> &rep_of,
-                         bool *ok) {
+static int param_classes(Engine *e, bool with_k, bool damping, bool active, HostTables &H, int64_t s0, bool *ok) {
     *ok = false;
-    const size_t ns = (size_t)e->ns;
-    std::vector<double> hk(ns), hr(ns), hd, ho;
-    TB_CUDA(e, cudaMemcpy(hk.data(), e->k, ns * 8, cudaMemcpyDeviceToHost));
-    TB_CUDA(e, cudaMemcpy(hr.data(), e->rest, ns * 8, cudaMemcpyDeviceToHost));
-    if (damping && e->damping) { hd.resize(ns); TB_CUDA(e, cudaMemcpy(hd.data(), e->damping, ns * 8, cudaMemcpyDeviceToHost)); }
-    if (active && e->omega) { ho.resize(ns); TB_CUDA(e, cudaMemcpy(ho.data(), e->omega, ns * 8, cudaMemcpyDeviceToHost)); }
+    const size_t ns = (size_t)e->ns, n = ns - (size_t)s0;
+    std::vector<double> hk(n), hr(n), hd, ho;
+    if (n) {
+        TB_CUDA(e, cudaMemcpy(hk.data(), e->k + s0, n * 8, cudaMemcpyDeviceToHost));
+        TB_CUDA(e, cudaMemcpy(hr.data(), e->rest + s0, n * 8, cudaMemcpyDeviceToHost));
+        if (damping && e->damping) { hd.resize(n); TB_CUDA(e, cudaMemcpy(hd.data(), e->damping + s0, n * 8, cudaMemcpyDeviceToHost)); }
+        if (active && e->omega) { ho.resize(n); TB_CUDA(e, cudaMemcpy(ho.data(), e->omega + s0, n * 8, cudaMemcpyDeviceToHost)); }
+    }
     const bool typed = active && e->h_type.size() == ns;    // the actuation type is part of a record (sine-table mode scales per record)
-    struct Key { uint64_t a, b, c, d, t; bool operator==(const Key &o) const { return a == o.a && b == o.b && c == o.c && d == o.d && t == o.t; } };
-    struct KeyHash { size_t operator()(const Key &x) const {
-        uint64_t h = x.a * 0x9E3779B97F4A7C15ull; h ^= (x.b + 0x7F4A7C15ull) * 0xC2B2AE3D27D4EB4Full; h ^= h >> 29;
-        h ^= x.c * 0x165667B19E3779F9ull; h ^= (x.d + x.t) * 0x27D4EB2F165667C5ull; return (size_t)(h ^ (h >> 32)); } };
-    std::unordered_map<Key, int32_t, KeyHash> seen;
-    std::vector<int32_t> first;    // class id -> first spring
-    class_of.resize(ns); rep_of.resize(ns);
-    Key last = {0, 0, 0, 0, 0}; int32_t last_class = -1;
+    if (s0 == 0) { H.class_seen.clear(); H.class_first.clear(); }
+    H.class_of.resize(ns); H.rep_of.resize(ns);
+    ClassKey last = {0, 0, 0, 0, 0}; int32_t last_class = -1;
     auto bits = [](double x) { uint64_t u; memcpy(&u, &x, 8); return u; };
-    for (size_t sp = 0; sp < ns; sp++) {
-        // an ACTUATED_* spring's rest length changes every step (advance_rest_kernel writes it into the record): a class of its own
-        const uint64_t own = (e->h_type.size() == ns && e->h_type[sp] >= TB_ACTUATED_EXPAND) ? ((uint64_t)(sp + 1) << 8) : 0;
-        Key key = {with_k ? bits(hk[sp]) : 0, bits(hr[sp]), hd.empty() ? 0 : bits(hd[sp]), ho.empty() ? 0 : bits(ho[sp]),
-                   own | (typed ? (uint64_t)(e->h_type[sp] == 2 ? 1 : e->h_type[sp] == 3 ? 2 : 0) : 0)};
+    for (size_t sp = (size_t)s0; sp < ns; sp++) {
+        const size_t q = sp - (size_t)s0;
+        // an ACTUATED_* spring's rest length changes every step (the step kernel advances it in its record): a class of its own
+        uint64_t own = (e->h_type.size() == ns && e->h_type[sp] >= TB_ACTUATED_EXPAND) ? ((uint64_t)(sp + 1) << 8) : 0;
+        if (!e->h_removed.empty() && e->h_removed[sp]) own |= 1ull << 48;     // tombstones (k, damping zeroed) never represent live springs
+        ClassKey key = {with_k ? bits(hk[q]) : 0, bits(hr[q]), hd.empty() ? 0 : bits(hd[q]), ho.empty() ? 0 : bits(ho[q]),
+                        own | (typed ? (uint64_t)(e->h_type[sp] == 2 ? 1 : e->h_type[sp] == 3 ? 2 : 0) : 0)};
         int32_t c;
         if (last_class >= 0 && key == last) c = last_class;
         else {
-            auto it = seen.find(key);
-            if (it == seen.end()) {
-                if ((int)first.size() >= DICT_MAX_GLOBAL) return TB_OK;
-                c = (int32_t)first.size(); first.push_back((int32_t)sp); seen.emplace(key, c);
+            auto it = H.class_seen.find(key);
+            if (it == H.class_seen.end()) {
+                if ((int)H.class_first.size() >= DICT_MAX_GLOBAL) return TB_OK;
+                c = (int32_t)H.class_first.size(); H.class_first.push_back((int32_t)sp); H.class_seen.emplace(key, c);
             } else c = it->second;
             last = key; last_class = c;
         }
-        class_of[sp] = c; rep_of[sp] = first[(size_t)c];
+        H.class_of[sp] = c; H.rep_of[sp] = H.class_first[(size_t)c];
     }
     *ok = true;
     return TB_OK;
+}
+
+// Distinct actuation frequencies of the ACTIVE_* springs (bit patterns).  At most MAX_OMEGA of them: sin(omega t) is
+// evaluated once per CTA and step and the records carry a table index; more: per-spring sin() in the kernel (false).
+static bool omega_table(const Engine *e, std::vector<double> &tab) {
+    tab.clear();
+    if (e->h_omega.size() != (size_t)e->ns || e->h_type.size() != (size_t)e->ns) return false;
+    std::map<uint64_t, int> seen;
+    for (int64_t sp = 0; sp < e->ns; sp++) {
+        if (e->h_type[(size_t)sp] != 2 && e->h_type[(size_t)sp] != 3) continue;
+        uint64_t bits; memcpy(&bits, &e->h_omega[(size_t)sp], 8);
+        if (seen.emplace(bits, (int)tab.size()).second) { tab.push_back(e->h_omega[(size_t)sp]); if (tab.size() > (size_t)MAX_OMEGA) return false; }
+    }
+    return !tab.empty();
+}
+
+// ---------------------------------------------------------------- structure build (host), phase 1: one tile ------------
+// What one tile contributes to the tables of the tiled layout.  Pure function of the topology, the mass -> slot assignment and
+// the parameter classes: tiles are built independently (all host cores at start(); a handful of tiles after tb_add_springs).
+struct TileOut {
+    int deg = 0;                          // ELL rows
+    int n_slots = 1;                      // record slots an incidence word can name (slot 0 = the k = 0 record of the padding words)
+    int n_final = 1;                      // records stored in the blob: n_slots (one per spring) or the tile's distinct classes
+    std::vector<uint32_t> block;          // incidence words [rows rounded up to ELL_CHUNK][TM], provisional dummy indices
+    std::vector<int32_t> th;              // halo list: state index of every foreign mass, -1 = hole
+    std::vector<int32_t> recs;            // spring behind every final record (-1 for record 0)
+    std::vector<int32_t> kslots;          // split dictionary: spring behind every record SLOT
+    std::vector<uint8_t> map;             // dictionary modes: slot -> record
+    std::vector<std::pair<int32_t, int>> act;   // (ACTUATED_* spring, its final record)
+    const char *why_not = nullptr;        // the tile does not fit the tiled format
+    bool dict_overflow = false;           // more distinct records than a tile's byte map addresses: try the next record mode
+};
+struct BuildCfg {
+    bool dict = false, split = false, align_rows = true;
+    bool drop_removed = false;            // leave the incidence words of removed springs out (tile patches, tb_compact)
+    const std::vector<int32_t> *class_of = nullptr, *rep_of = nullptr;
+};
+
+static void build_tile(const Engine *e, const TiledState *S, int64_t T, const BuildCfg &cfg, TileOut &o) {
+    struct Half { int32_t s; int32_t o; uint8_t side; };
+    std::vector<Half> rows[TM];
+    std::vector<Half> aligned;
+    const std::vector<int32_t> &rp = e->h_row_ptr, &adj = e->h_adj;
+    int deg = 0;
+    for (int t = 0; t < TM; t++) {
+        int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
+        if (i < 0 || !(e->h_flags[(size_t)i] & F_VALID) || (e->h_flags[(size_t)i] & F_GHOST)) continue;   // ghosts are updated by their owner
+        auto take = [&](int32_t a) {
+            const int32_t s = a >> 1;
+            const uint8_t side = (uint8_t)(a & 1);
+            const int32_t other = side ? e->h_left[(size_t)s] : e->h_right[(size_t)s];
+            if (other < 0 || !(e->h_flags[(size_t)other] & F_VALID)) return;   // spring skipped, src/sim.cu:1163
+            // a tombstone (tb_remove_springs) keeps its incidence word (it reads k = 0) unless this build compacts: dropping the
+            // words of scattered removals makes every tile's block unique, and the content dedupe that keeps the blocks of a
+            // lattice L2-resident is worth far more than 0.1 % of dead words (C5: 168 -> 151 G spring-steps/s when dropped)
+            if (cfg.drop_removed && !e->h_removed.empty() && e->h_removed[(size_t)s]) return;
+            rows[t].push_back({s, other, side});
+        };
+        if ((int64_t)i < e->csr_nm) for (int32_t q = rp[(size_t)i]; q < rp[(size_t)i + 1]; q++) take(adj[(size_t)q]);
+        if (!e->extra_adj.empty()) {        // springs added since the CSR was built: higher indices, so they come last
+            auto it = e->extra_adj.find(i);
+            if (it != e->extra_adj.end()) for (int32_t a : it->second) take(a);
+        }
+        deg = std::max(deg, (int)rows[t].size());
+    }
+    o.deg = deg;
+    if (deg > MAX_DEG) { o.why_not = "a mass has more incident springs than the ELL format holds"; return; }
+    // Row alignment: a mass with fewer springs than the tile's fullest one (a lattice surface) gets HOLES so that its
+    // springs sit in the rows of the same springs of a full mass -- "same" = same offset in API index, which on a
+    // lattice is the direction.  Order per mass is unchanged (ascending spring index), only padding moves; every row
+    // then holds one direction, its in-tile neighbours are t + const, and a half-warp's reads spread over all banks.
+    // A mass whose offsets are no subsequence of the template's keeps its compact rows.
+    if (deg > 1 && cfg.align_rows) {
+        int tmpl = -1;
+        for (int t = 0; t < TM && tmpl < 0; t++) if ((int)rows[t].size() == deg) tmpl = t;
+        const int32_t i_tmpl = S->h_slot_to_api[(size_t)(T * TM + tmpl)];
+        for (int t = 0; t < TM; t++) {
+            const int d = (int)rows[t].size();
+            if (d == 0 || d == deg) continue;
+            const int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
+            aligned.assign((size_t)deg, Half{-1, 0, 0});
+            int p = 0;
+            bool ok = true;
+            for (int q = 0; q < d && ok; q++) {
+                const int32_t key = rows[t][(size_t)q].o - i;
+                while (p < deg && rows[tmpl][(size_t)p].o - i_tmpl != key) p++;
+                if (p == deg) ok = false; else aligned[(size_t)p++] = rows[t][(size_t)q];
+            }
+            if (ok) rows[t] = aligned;
+        }
+    }
+    auto has = [&](int t, int j) { return j < (int)rows[t].size() && rows[t][(size_t)j].s >= 0; };
+    o.block.assign((size_t)ell_chunks(deg) * ELL_CHUNK * TM, 0u);   // zero rows pad the last chunk
+    // Halo slots are chosen so that the 16 lanes of a half-warp reading row j hit 16 different shared-memory
+    // bank pairs (an LDS.64 conflict costs a replay).  Own neighbours sit at local index t + c_j (c_j = the
+    // row's dominant offset), so a foreign mass met by lane t in row j wants a slot = t + c_j (mod 16): on a
+    // lattice brick every row that reaches the mass asks for the same residue (the brick's linear index
+    // extended over its shell), which makes every row conflict-free.  Other graphs fall back to the lowest
+    // free slot whose residue no lane of the half-warp uses.  Unused slots (holes) are not gathered.
+    std::vector<int32_t> &th = o.th;
+    th.clear();
+    std::unordered_map<int32_t, int32_t> halo_local;      // foreign mass -> its halo slot in this tile
+    int cjs[MAX_DEG];
+    for (int j = 0; j < deg; j++) {
+        int votes[16] = {0}, cj = -1, best = 0;
+        for (int t = 0; t < TM; t++) {
+            if (!has(t, j)) continue;
+            int32_t oslot = S->h_api_to_slot[(size_t)rows[t][(size_t)j].o];
+            if (oslot / TM == T) votes[((oslot % TM) - t) & 15]++;
+        }
+        for (int r = 0; r < 16; r++) if (votes[r] > best) { best = votes[r]; cj = r; }
+        cjs[j] = cj;
+        for (int hw = 0; hw < TM / 16; hw++) {
+            uint32_t used = 0;
+            for (int t = hw * 16; t < hw * 16 + 16; t++) {
+                if (!has(t, j)) continue;
+                const Half &h = rows[t][(size_t)j];
+                int32_t oslot = S->h_api_to_slot[(size_t)h.o];
+                if (oslot / TM == T) used |= 1u << (oslot % 16);
+                else { auto it = halo_local.find(h.o); if (it != halo_local.end()) used |= 1u << (it->second % 16); }
+            }
+            for (int t = hw * 16; t < hw * 16 + 16; t++) {
+                if (!has(t, j)) continue;
+                const Half &h = rows[t][(size_t)j];
+                int32_t oslot = S->h_api_to_slot[(size_t)h.o];
+                if (oslot / TM == T || halo_local.count(h.o)) continue;
+                int pick = -1;
+                if (cj >= 0) {
+                    // preferred residue first, but never at the price of a halo list that no longer fits the
+                    // small shared-memory variant: beyond that budget any free slot will do (a bank conflict
+                    // costs a replay, an oversized list costs occupancy or the tiled format altogether)
+                    const int want = (t + cj) & 15, budget = CS_SMALL - TM - N_DUMMY;
+                    for (int x = want; pick < 0 && x < budget; x += 16) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
+                    for (int x = 0; pick < 0; x++) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
+                } else {
+                    for (int x = 0; x < (int)th.size() + 16 && pick < 0; x++) {
+                        bool free_slot = x >= (int)th.size() || th[(size_t)x] < 0;
+                        if (free_slot && (!((used >> (x % 16)) & 1u) || used == 0xffffu)) pick = x;
+                    }
+                }
+                if (pick >= (int)th.size()) th.resize((size_t)pick + 1, -1);
+                th[(size_t)pick] = (int32_t)((int64_t)(oslot / TM) * STATE_BLOCK + oslot % TM);
+                halo_local[h.o] = pick;
+                used |= 1u << (pick % 16);
+            }
+        }
+    }
+    // padding words: the dummy mass in the bank pair the lane's own neighbour would occupy, record 0
+    for (size_t w = 0; w < o.block.size(); w++) {
+        const int j = (int)(w / TM), t = (int)(w % TM);
+        o.block[w] = (PAD_NB + (uint32_t)((t + ((j < deg && cjs[j] >= 0) ? cjs[j] : 0)) & 15)) << ELL_NB_SHIFT;
+    }
+    std::vector<int32_t> slot_spring(1, -1);              // record slot -> spring; slot 0: k = 0, read by padding words
+    std::unordered_map<int32_t, int32_t> rec_local;       // spring -> its record slot in this tile
+    for (int j = 0; j < deg; j++) for (int t = 0; t < TM; t++) {   // j-major walk: record slots of one row are consecutive
+        if (!has(t, j)) continue;
+        const Half &h = rows[t][(size_t)j];
+        int32_t oslot = S->h_api_to_slot[(size_t)h.o];
+        const int nb = (oslot / TM == T) ? oslot % TM : TM + halo_local[h.o];
+        auto it = rec_local.find(h.s);
+        if (it == rec_local.end()) { it = rec_local.emplace(h.s, (int32_t)slot_spring.size()).first; slot_spring.push_back(h.s); }
+        const int rec = it->second;
+        if (nb >= MAX_LOCAL - N_DUMMY || rec >= MAX_REC) { o.why_not = "a tile reaches too many foreign masses or springs"; return; }
+        uint32_t ty = 0;
+        if (!e->h_type.empty()) { uint8_t x = e->h_type[(size_t)h.s]; ty = (x == 2) ? 1u : (x == 3) ? 2u : 0u; }
+        o.block[(size_t)j * TM + (size_t)t] =
+            ((uint32_t)nb << ELL_NB_SHIFT) | ((uint32_t)rec << ELL_REC_SHIFT) | (h.side ? ELL_SIDE : 0u) | (ty << ELL_TYPE_SHIFT) | ELL_VALID;
+    }
+    const int n_rec = (int)slot_spring.size();
+    o.n_slots = n_rec;
+    const bool actuated = e->any_actuated && !e->h_type.empty();
+    if (!cfg.dict) {
+        o.n_final = n_rec;
+        o.recs.swap(slot_spring);
+        for (int r = 1; r < n_rec && actuated; r++)
+            if (e->h_type[(size_t)o.recs[(size_t)r]] >= TB_ACTUATED_EXPAND) o.act.push_back({o.recs[(size_t)r], r});
+        return;
+    }
+    // dictionary modes: record slots -> the tile's distinct records; slot 0 (padding) -> record 0 (k = 0)
+    std::unordered_map<int32_t, int32_t> cls_local;       // parameter class -> its record in this tile
+    o.recs.assign(1, -1);
+    o.map.assign(1, 0);
+    for (int r = 1; r < n_rec; r++) {
+        const int32_t sp = slot_spring[(size_t)r], c = (*cfg.class_of)[(size_t)sp];
+        auto it = cls_local.find(c);
+        if (it == cls_local.end()) {
+            if ((int)o.recs.size() >= DICT_MAX_TILE) { o.dict_overflow = true; return; }
+            it = cls_local.emplace(c, (int32_t)o.recs.size()).first;
+            o.recs.push_back((*cfg.rep_of)[(size_t)sp]);
+        }
+        o.map.push_back((uint8_t)it->second);
+    }
+    o.n_final = (int)o.recs.size();
+    for (int r = 1; r < o.n_final && actuated; r++)
+        if (e->h_type[(size_t)o.recs[(size_t)r]] >= TB_ACTUATED_EXPAND) o.act.push_back({o.recs[(size_t)r], r});
+    if (cfg.split) o.kslots.swap(slot_spring);             // slot -> spring, for the per-slot stiffness
+}
+
+// ---------------------------------------------------------------- structure build (host), phase 2: merge + upload -----
+// Host copies of the tables the tiled kernel reads (TiledState::H), kept so that single tiles can be rebuilt later: a rebuilt
+// tile's lists are appended and its TileMeta redirected (the old entries stay behind until the next full build).
+
+// appends tile T's contribution; the dummy indices of its padding words are rebased to stride cs first
+static const char *merge_tile(Engine *e, TiledState *S, int64_t T, TileOut &o, bool keep_exchange) {
+    HostTables &H = S->H;
+    TileMeta &M = S->h_meta[(size_t)T];
+    const TileMeta old = M;
+    const bool dict = S->dict, split = S->dict_split;
+    {   // padding words: provisional dummy index -> the stride's own dummies [cs - N_DUMMY, cs)
+        const uint32_t base = (uint32_t)(S->cs - N_DUMMY);
+        for (uint32_t &w : o.block)
+            if (!(w & ELL_VALID)) { const uint32_t nb = (w >> ELL_NB_SHIFT) & 0x1ffu; w = (base + (nb >= PAD_NB ? nb - PAD_NB : 0u)) << ELL_NB_SHIFT; }
+    }
+    M.deg = (uint32_t)o.deg;
+    while (H.halo.size() % 4) H.halo.push_back(0);               // 16-byte aligned halo lists (bulk copy)
+    M.halo_off = (uint32_t)H.halo.size();
+    M.n_halo = (uint32_t)o.th.size();
+    H.halo.insert(H.halo.end(), o.th.begin(), o.th.end());      // -1 = hole, skipped by the gather
+    // content dedupe of the ELL block (FNV-1a over the words, verified by comparison)
+    uint64_t hsh = 1469598103934665603ull ^ (uint64_t)o.deg;
+    for (uint32_t w : o.block) { hsh ^= w; hsh *= 1099511628211ull; }
+    bool found = false;
+    std::vector<uint32_t> &cands = H.ell_index[hsh];
+    for (uint32_t off : cands)
+        if (off + o.block.size() <= H.ell.size() && std::equal(o.block.begin(), o.block.end(), H.ell.begin() + off)) { M.ell_off = off; found = true; break; }
+    if (!found) {
+        if (H.ell.size() + o.block.size() >= ((size_t)1 << 31)) return "ELL table exceeds int32 offsets";
+        M.ell_off = (uint32_t)H.ell.size();
+        cands.push_back(M.ell_off);
+        H.ell.insert(H.ell.end(), o.block.begin(), o.block.end());
+        H.unique_blocks++;
+    }
+    M.n_rec = (uint32_t)o.n_final;
+    M.rec_off = (uint32_t)H.rec_spring.size();
+    H.rec_spring.insert(H.rec_spring.end(), o.recs.begin(), o.recs.end());
+    M.map_off16 = 0;
+    size_t bb = blob_size(o.n_final, S->has_damping, S->has_active);
+    if (dict) {
+        while (H.rec_map.size() % 16) H.rec_map.push_back(0);
+        M.map_off16 = (uint32_t)(H.rec_map.size() / 16);
+        H.rec_map.insert(H.rec_map.end(), o.map.begin(), o.map.end());
+        if (split) {
+            H.krec_off[2 * (size_t)T] = (uint32_t)H.kslot_spring.size();
+            H.krec_off[2 * (size_t)T + 1] = (uint32_t)o.kslots.size();
+            H.kslot_spring.insert(H.kslot_spring.end(), o.kslots.begin(), o.kslots.end());
+        }
+        bb = blob_size(o.n_final, S->has_damping, S->has_active, o.n_slots, split ? o.n_slots : -1);
+    }
+    M.exp_off = 0; M.exp_rows = 0;
+    M.tflags = (T < S->n_boundary) ? (uint32_t)TF_BOUNDARY : 0u;
+    if (keep_exchange) { M.exp_off = old.exp_off; M.exp_rows = old.exp_rows; M.tflags = old.tflags; }
+    if (H.blob_total / 16 >= ((size_t)1 << 32)) return "blob exceeds 64 GB";
+    M.blob_off16 = (uint32_t)(H.blob_total / 16); M.blob_bytes = (uint32_t)bb;
+    H.blob_total += bb;
+    {   // where the rest lengths of this tile's actuated springs sit: after the k array (blob_size / tiled_refresh_params)
+        const size_t np = (size_t)((M.n_rec + 1) & ~1u), nk = (dict && split) ? (size_t)((o.n_slots + 1) & ~1) : np;
+        std::vector<int4> &list = H.act[(size_t)T];
+        list.clear();
+        for (const std::pair<int32_t, int> &a : o.act) list.push_back(make_int4((int)(BLOB_REC + nk * 8 + (size_t)a.second * 8), a.first, 0, 0));
+        M.tflags = (M.tflags & ~(uint32_t)TF_ACTUATED) | (o.act.empty() ? 0u : (uint32_t)TF_ACTUATED);
+    }
+    H.tile_slots[(size_t)T] = o.n_slots;
+    (void)e;
+    return nullptr;
+}
+
+// maxima, shared-memory plan, cluster grouping, then every table to the device.  The state buffers survive (and grow with
+// the tile count); the blobs are re-allocated, so the caller refreshes parameters and flags afterwards.
+static int finalize_and_upload(Engine *e, TiledState *S, int64_t old_tiles) {
+    HostTables &H = S->H;
+    const int64_t n_tiles = (int64_t)S->h_meta.size();
+    int max_halo = 0, max_rec = 0, max_deg = 0, max_dict = 0;
+    size_t max_blob = 0;
+    for (int64_t T = 0; T < n_tiles; T++) {
+        const TileMeta &M = S->h_meta[(size_t)T];
+        max_halo = std::max(max_halo, (int)M.n_halo); max_deg = std::max(max_deg, (int)M.deg);
+        max_rec = std::max(max_rec, H.tile_slots[(size_t)T]); max_blob = std::max(max_blob, (size_t)M.blob_bytes);
+        if (S->dict) max_dict = std::max(max_dict, (int)M.n_rec);
+    }
+    // stages of the tile ring (TB_STAGES): the small dictionary blobs leave room for more than two
+    int nst = 2;      // measured on B200 (C2, dictionary mode): 3 stages 183.7 vs 2 stages 187.9 G spring-steps/s
+    if (const char *v = getenv("TB_STAGES")) nst = std::min(MAX_STAGES, std::max(2, atoi(v)));
+    if (S->tpm > 1) nst = 2;    // named barriers of the partial-sum hand-off are numbered for two stages
+    while (nst > 2 && (size_t)plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm, nst).total > SMEM_LIMIT / 3) nst--;
+    S->nst = nst;
+    SmemPlan plan = plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm, nst);
+    if ((size_t)plan.total > SMEM_LIMIT) { S->why_not = "a tile's working set exceeds the shared-memory budget"; S->supported = false; return TB_OK; }
+    S->smem_bytes = (size_t)plan.total;
+    // smallest group size c <= 8 such that every tile's foreign masses live in its own aligned group of c tiles
+    S->res_cluster = 0;
+    for (int c = 1; c <= 8 && !S->res_cluster; c++) {
+        if (n_tiles % c) continue;
+        bool ok = true;
+        for (int64_t T = 0; T < n_tiles && ok; T++) {
+            const TileMeta &M = S->h_meta[(size_t)T];
+            const int64_t base = T - T % c;
+            for (uint32_t h = 0; h < M.n_halo && ok; h++) {
+                const int32_t hi = H.halo[(size_t)M.halo_off + h];
+                if (hi >= 0 && (hi / STATE_BLOCK < base || hi / STATE_BLOCK >= base + c)) ok = false;
+            }
+        }
+        if (ok) S->res_cluster = c;
+    }
+    // the primary copy of an actuated spring (the one that keeps the canonical rest array current): its first record in tile order
+    std::vector<int4> act_rec;
+    std::vector<uint32_t> act_tile_off;
+    if (e->any_actuated) {
+        std::vector<uint8_t> seen(e->h_act.size(), 0);
+        for (int64_t T = 0; T < n_tiles; T++) {
+            act_tile_off.push_back((uint32_t)act_rec.size());
+            for (int4 r : H.act[(size_t)T]) {
+                const size_t j = (size_t)(std::lower_bound(e->h_act.begin(), e->h_act.end(), r.y) - e->h_act.begin());
+                const bool known = j < e->h_act.size() && e->h_act[j] == r.y;
+                r.z = (known && !seen[j]) ? 1 : 0;
+                if (known) seen[j] = 1;
+                act_rec.push_back(r);
+            }
+        }
+        act_tile_off.push_back((uint32_t)act_rec.size());
+    }
+    const bool dict_mode = S->dict, split_mode = S->dict_split;
+    free_structure(e, S, /*keep_state=*/true);       // device tables only; the host tables above stay
+    S->dict = dict_mode; S->dict_split = split_mode;
+    const int64_t n_slots = (int64_t)S->h_slot_to_api.size();
+    S->n_tiles = n_tiles; S->n_slots = n_slots;
+    S->max_halo = max_halo; S->max_rec = max_rec; S->max_deg = max_deg; S->max_dict = max_dict;
+    S->max_blob = (int)max_blob; S->blob_bytes = H.blob_total; S->ell_unique_tiles = H.unique_blocks;
+    if (old_tiles != n_tiles) {                      // first build, or tiles appended for new masses: the state moves to larger buffers
+        for (int p = 0; p < 2; p++) {
+            double *bigger = nullptr;
+            TB_TRY(dev_alloc(e, &bigger, (size_t)n_tiles * STATE_BLOCK));
+            TB_CUDA(e, cudaMemset(bigger, 0, (size_t)n_tiles * STATE_BLOCK * 8));
+            if (S->st[p] && old_tiles > 0) TB_CUDA(e, cudaMemcpy(bigger, S->st[p], (size_t)std::min(old_tiles, n_tiles) * STATE_BLOCK * 8, cudaMemcpyDeviceToDevice));
+            release(e, S->st[p], (size_t)old_tiles * STATE_BLOCK);
+            S->st[p] = bigger;
+        }
+    }
+    std::vector<int32_t> halo(H.halo);
+    while (halo.size() % 4) halo.push_back(0);
+    halo.resize(halo.size() + 4, 0);   // the last list may be copied rounded up to 16 bytes
+    std::vector<uint32_t> ell(H.ell);
+    ell.resize(ell.size() + (size_t)(MAX_DEG + 2 * ELL_CHUNK) * TM, (uint32_t)(S->cs - N_DUMMY) << ELL_NB_SHIFT);   // the kernel prefetches whole register sets
+    S->n_halo = (int64_t)halo.size(); S->n_ell = (int64_t)ell.size(); S->n_rec = (int64_t)H.rec_spring.size();
+    if (S->dict && S->dict_split) {
+        S->n_krec = (int64_t)H.kslot_spring.size();
+        TB_TRY(upload_vec(e, &S->krec_spring, H.kslot_spring));
+        TB_CUDA(e, cudaMalloc((void **)&S->krec_off, H.krec_off.size() * sizeof(uint32_t)));
+        TB_CUDA(e, cudaMemcpy(S->krec_off, H.krec_off.data(), H.krec_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    }
+    if (S->dict) {
+        std::vector<uint8_t> rec_map(H.rec_map);
+        while (rec_map.size() % 16) rec_map.push_back(0);
+        rec_map.resize(rec_map.size() + 16, 0);
+        S->n_rec_map = (int64_t)rec_map.size(); S->n_class_rep = (int64_t)H.rep_of.size();
+        TB_TRY(upload_vec(e, &S->rec_map, rec_map)); TB_TRY(upload_vec(e, &S->class_rep, H.rep_of));
+        if (!S->dict_bad) TB_CUDA(e, cudaMalloc((void **)&S->dict_bad, sizeof(int)));
+    }
+    if (!act_rec.empty()) {
+        S->n_act_rec = (int64_t)act_rec.size();
+        TB_CUDA(e, cudaMalloc((void **)&S->act_tile_off, act_tile_off.size() * sizeof(uint32_t)));
+        TB_CUDA(e, cudaMemcpy(S->act_tile_off, act_tile_off.data(), act_tile_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        TB_CUDA(e, cudaMalloc((void **)&S->act_rec, act_rec.size() * sizeof(int4)));
+        TB_CUDA(e, cudaMemcpy(S->act_rec, act_rec.data(), act_rec.size() * sizeof(int4), cudaMemcpyHostToDevice));
+    }
+    TB_TRY(dev_alloc(e, &S->blob, H.blob_total));
+    TB_CUDA(e, cudaMemset(S->blob, 0, H.blob_total));
+    TB_TRY(upload_vec(e, &S->slot_to_api, S->h_slot_to_api));
+    TB_TRY(upload_vec(e, &S->halo, halo)); TB_TRY(upload_vec(e, &S->rec_spring, H.rec_spring)); TB_TRY(upload_vec(e, &S->ell, ell));
+    TB_CUDA(e, cudaMalloc((void **)&S->meta, (size_t)n_tiles * sizeof(TileMeta)));
+    TB_CUDA(e, cudaMemcpy(S->meta, S->h_meta.data(), (size_t)n_tiles * sizeof(TileMeta), cudaMemcpyHostToDevice));
+    S->supported = true;
+    return TB_OK;
+}
+
+template <class F> static void parallel_tiles(int64_t n, F f) {
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const unsigned nt = n < 64 ? 1u : std::min(32u, hw);
+    if (nt == 1) { for (int64_t T = 0; T < n; T++) f(T); return; }
+    std::atomic<int64_t> next{0};
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nt; t++)
+        th.emplace_back([&] { for (int64_t T = next.fetch_add(16); T < n; T = next.fetch_add(16)) for (int64_t q = T; q < std::min(n, T + 16); q++) f(q); });
+    for (std::thread &t : th) t.join();
 }
 
 // Builds tiles, ELL rows, halo lists and record tables on the host and uploads them.  Returns TB_OK with
@@ -395,10 +803,10 @@ static int param_classes(Engine *e, bool with_k, bool damping, bool active, std:
 // mode: 1 = try the full dictionary, then (2) the split one -- classes over (rest, damping, omega), k per record slot --
 // then (0) one record per spring.
 static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, int mode = 1) {
-    std::vector<TileMeta> old_meta;
-    if (keep_slots) old_meta = S->h_meta;
-    free_structure(e, S, keep_slots);
+    const int64_t old_tiles = keep_slots ? S->n_tiles : 0;
+    if (!keep_slots) free_structure(e, S, false);
     S->supported = false;
+    TB_TRY(ensure_csr(e));                        // masses / springs added since the last build join the CSR
     const int64_t nm = e->nm;
     if (!keep_slots) {
         std::vector<double> pos;
@@ -422,309 +830,104 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
     if (mode == 1 && (dict_env == 2 || S->dict_failures >= 2)) mode = 2;
     if (mode == 2 && S->split_failures >= 2) mode = 0;
     bool dict = mode != 0 && dict_env != 0 && !(e->flags & TB_MATH_STRICT) && S->tpm == 1 && e->ns > 0;
+    if (dict && S->has_active) {      // dictionary records scale their rest length per record from the sine table
+        std::vector<double> tab;
+        if (!omega_table(e, tab)) dict = false;
+    }
     const bool split = dict && mode == 2;
     const int next_mode = mode == 1 ? 2 : 0;          // what to try when this mode does not fit
-    std::vector<int32_t> class_of, rep_of, dict_spring, kslot_spring;
-    std::vector<uint32_t> krec_off;
-    std::vector<uint8_t> rec_map;
-    std::vector<int32_t> cls_stamp, cls_local;
+    HostTables &H = S->H;
+    H = HostTables();
     if (dict) {
-        TB_TRY(param_classes(e, !split, S->has_damping, S->has_active, class_of, rep_of, &dict));
+        TB_TRY(param_classes(e, !split, S->has_damping, S->has_active, H, 0, &dict));
         if (!dict && next_mode) return build_structure(e, S, keep_slots, next_mode);
-        if (dict) {
-            int32_t n_classes = 0;
-            for (int32_t c : class_of) n_classes = std::max(n_classes, c + 1);
-            cls_stamp.assign((size_t)n_classes, -1); cls_local.assign((size_t)n_classes, 0);
-        }
     }
-    int max_dict = 0;
+    BuildCfg cfg;
+    cfg.dict = dict; cfg.split = split;
+    cfg.align_rows = !(getenv("TB_ALIGN_ROWS") && atoi(getenv("TB_ALIGN_ROWS")) == 0);   // measurement aid
+    cfg.class_of = &H.class_of; cfg.rep_of = &H.rep_of;
+    cfg.drop_removed = e->compact_requested;
 
-    std::vector<TileMeta> meta((size_t)n_tiles);
-    std::vector<uint32_t> ell, block;
-    std::map<uint64_t, std::vector<uint32_t>> ell_index;   // content hash -> offsets of stored blocks
-    std::vector<int32_t> halo, rec_spring;
-    std::vector<int32_t> halo_stamp((size_t)nm, -1), halo_local((size_t)nm, 0);
-    std::vector<int32_t> rec_stamp((size_t)e->ns, -1), rec_local((size_t)e->ns, 0);
-    struct Half { int32_t s; int32_t o; uint8_t side; };
-    std::vector<std::vector<Half>> rows(TM);
-    std::vector<Half> aligned;
-    std::vector<std::pair<int32_t, int>> act_here;          // (actuated spring, its record) of the tile being built
-    std::vector<int4> act_rec;                              // per-tile lists, all tiles
-    std::vector<uint32_t> act_tile_off;
-    std::vector<uint8_t> act_seen(e->h_act.size(), 0);      // the first record of a spring is its primary copy
-    int cjs[MAX_DEG];
-    const bool align_rows = !(getenv("TB_ALIGN_ROWS") && atoi(getenv("TB_ALIGN_ROWS")) == 0);   // measurement aid
-    std::vector<int32_t> th;   // halo list of the tile being built (-1 = hole)
-    int max_halo = 0, max_rec = 0, max_deg = 0;
-    size_t blob_total = 0, max_blob = 0;
-    int64_t unique_blocks = 0;
-    const std::vector<int32_t> &rp = e->h_row_ptr, &adj = e->h_adj;
-    for (int64_t T = 0; T < n_tiles; T++) {
-        int deg = 0;
-        for (int t = 0; t < TM; t++) {
-            rows[t].clear();
-            int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
-            if (i < 0 || !(e->h_flags[(size_t)i] & F_VALID) || (e->h_flags[(size_t)i] & F_GHOST)) continue;   // ghosts are updated by their owner
-            for (int32_t q = rp[(size_t)i]; q < rp[(size_t)i + 1]; q++) {
-                int32_t a = adj[(size_t)q], s = a >> 1;
-                uint8_t side = (uint8_t)(a & 1);
-                int32_t o = side ? e->h_left[(size_t)s] : e->h_right[(size_t)s];
-                if (!(e->h_flags[(size_t)o] & F_VALID)) continue;   // spring skipped, src/sim.cu:1163
-                rows[t].push_back({s, o, side});
-            }
-            deg = std::max(deg, (int)rows[t].size());
-        }
-        if (deg > MAX_DEG) { S->why_not = "a mass has more incident springs than the ELL format holds"; return TB_OK; }
-        // Row alignment: a mass with fewer springs than the tile's fullest one (a lattice surface) gets HOLES so that its
-        // springs sit in the rows of the same springs of a full mass -- "same" = same offset in API index, which on a
-        // lattice is the direction.  Order per mass is unchanged (ascending spring index), only padding moves; every row
-        // then holds one direction, its in-tile neighbours are t + const, and a half-warp's reads spread over all banks.
-        // A mass whose offsets are no subsequence of the template's keeps its compact rows.
-        if (deg > 1 && align_rows) {
-            int tmpl = -1;
-            for (int t = 0; t < TM && tmpl < 0; t++) if ((int)rows[t].size() == deg) tmpl = t;
-            const int32_t i_tmpl = S->h_slot_to_api[(size_t)(T * TM + tmpl)];
-            for (int t = 0; t < TM; t++) {
-                const int d = (int)rows[t].size();
-                if (d == 0 || d == deg) continue;
-                const int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
-                aligned.assign((size_t)deg, Half{-1, 0, 0});
-                int p = 0;
-                bool ok = true;
-                for (int q = 0; q < d && ok; q++) {
-                    const int32_t key = rows[t][(size_t)q].o - i;
-                    while (p < deg && rows[tmpl][(size_t)p].o - i_tmpl != key) p++;
-                    if (p == deg) ok = false; else aligned[(size_t)p++] = rows[t][(size_t)q];
-                }
-                if (ok) rows[t] = aligned;
-            }
-        }
-        auto has = [&](int t, int j) { return j < (int)rows[t].size() && rows[t][(size_t)j].s >= 0; };
-        TileMeta &M = meta[(size_t)T];
-        M.deg = (uint32_t)deg;
-        while (halo.size() % 4) halo.push_back(0);               // 16-byte aligned halo lists (bulk copy)
-        M.halo_off = (uint32_t)halo.size();
-        M.rec_off = (uint32_t)rec_spring.size();
-        block.assign((size_t)ell_chunks(deg) * ELL_CHUNK * TM, 0u);   // zero rows pad the last chunk
-        int n_rec = 1;
-        const size_t rec_first = rec_spring.size();
-        rec_spring.push_back(-1);                                 // record 0: k = 0, read by padding ELL words
-        // Halo slots are chosen so that the 16 lanes of a half-warp reading row j hit 16 different shared-memory
-        // bank pairs (an LDS.64 conflict costs a replay).  Own neighbours sit at local index t + c_j (c_j = the
-        // row's dominant offset), so a foreign mass met by lane t in row j wants a slot = t + c_j (mod 16): on a
-        // lattice brick every row that reaches the mass asks for the same residue (the brick's linear index
-        // extended over its shell), which makes every row conflict-free.  Other graphs fall back to the lowest
-        // free slot whose residue no lane of the half-warp uses.  Unused slots (holes) are not gathered.
-        th.clear();
-        for (int j = 0; j < deg; j++) {
-            int votes[16] = {0}, cj = -1, best = 0;
-            for (int t = 0; t < TM; t++) {
-                if (!has(t, j)) continue;
-                int32_t oslot = S->h_api_to_slot[(size_t)rows[t][(size_t)j].o];
-                if (oslot / TM == T) votes[((oslot % TM) - t) & 15]++;
-            }
-            for (int r = 0; r < 16; r++) if (votes[r] > best) { best = votes[r]; cj = r; }
-            cjs[j] = cj;
-            for (int hw = 0; hw < TM / 16; hw++) {
-                uint32_t used = 0;
-                for (int t = hw * 16; t < hw * 16 + 16; t++) {
-                    if (!has(t, j)) continue;
-                    const Half &h = rows[t][(size_t)j];
-                    int32_t oslot = S->h_api_to_slot[(size_t)h.o];
-                    if (oslot / TM == T) used |= 1u << (oslot % 16);
-                    else if (halo_stamp[(size_t)h.o] == (int32_t)T) used |= 1u << (halo_local[(size_t)h.o] % 16);
-                }
-                for (int t = hw * 16; t < hw * 16 + 16; t++) {
-                    if (!has(t, j)) continue;
-                    const Half &h = rows[t][(size_t)j];
-                    int32_t oslot = S->h_api_to_slot[(size_t)h.o];
-                    if (oslot / TM == T || halo_stamp[(size_t)h.o] == (int32_t)T) continue;
-                    int pick = -1;
-                    if (cj >= 0) {
-                        // preferred residue first, but never at the price of a halo list that no longer fits the
-                        // small shared-memory variant: beyond that budget any free slot will do (a bank conflict
-                        // costs a replay, an oversized list costs occupancy or the tiled format altogether)
-                        const int want = (t + cj) & 15, budget = CS_SMALL - TM - N_DUMMY;
-                        for (int x = want; pick < 0 && x < budget; x += 16) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
-                        for (int x = 0; pick < 0; x++) if (x >= (int)th.size() || th[(size_t)x] < 0) pick = x;
-                    } else {
-                        for (int x = 0; x < (int)th.size() + 16 && pick < 0; x++) {
-                            bool free_slot = x >= (int)th.size() || th[(size_t)x] < 0;
-                            if (free_slot && (!((used >> (x % 16)) & 1u) || used == 0xffffu)) pick = x;
-                        }
-                    }
-                    if (pick >= (int)th.size()) th.resize((size_t)pick + 1, -1);
-                    th[(size_t)pick] = (int32_t)((int64_t)(oslot / TM) * STATE_BLOCK + oslot % TM);
-                    halo_stamp[(size_t)h.o] = (int32_t)T; halo_local[(size_t)h.o] = pick;
-                    used |= 1u << (pick % 16);
-                }
-            }
-        }
-        const int n_halo = (int)th.size();
-        for (int32_t x : th) halo.push_back(x);                   // -1 = hole, skipped by the gather
-        // padding words: the dummy mass in the bank pair the lane's own neighbour would occupy, record 0
-        for (size_t w = 0; w < block.size(); w++) {
-            const int j = (int)(w / TM), t = (int)(w % TM);
-            block[w] = (PAD_NB + (uint32_t)((t + ((j < deg && cjs[j] >= 0) ? cjs[j] : 0)) & 15)) << ELL_NB_SHIFT;
-        }
-        for (int j = 0; j < deg; j++) for (int t = 0; t < TM; t++) {   // j-major walk: record slots of one row are consecutive
-            if (!has(t, j)) continue;
-            const Half &h = rows[t][(size_t)j];
-            int32_t oslot = S->h_api_to_slot[(size_t)h.o];
-            const int nb = (oslot / TM == T) ? oslot % TM : TM + halo_local[(size_t)h.o];
-            if (rec_stamp[(size_t)h.s] != (int32_t)T) { rec_stamp[(size_t)h.s] = (int32_t)T; rec_local[(size_t)h.s] = n_rec++; rec_spring.push_back(h.s); }
-            int rec = rec_local[(size_t)h.s];
-            if (nb >= MAX_LOCAL - N_DUMMY || rec >= MAX_REC) { S->why_not = "a tile reaches too many foreign masses or springs"; return TB_OK; }
-            uint32_t ty = 0;
-            if (!e->h_type.empty()) { uint8_t x = e->h_type[(size_t)h.s]; ty = (x == 2) ? 1u : (x == 3) ? 2u : 0u; }
-            block[(size_t)j * TM + (size_t)t] =
-                ((uint32_t)nb << ELL_NB_SHIFT) | ((uint32_t)rec << ELL_REC_SHIFT) | (h.side ? ELL_SIDE : 0u) | (ty << ELL_TYPE_SHIFT) | ELL_VALID;
-        }
-        // content dedupe of the ELL block (FNV-1a over the words, verified by comparison)
-        uint64_t hsh = 1469598103934665603ull ^ (uint64_t)deg;
-        for (uint32_t w : block) { hsh ^= w; hsh *= 1099511628211ull; }
-        bool found = false;
-        std::vector<uint32_t> &cands = ell_index[hsh];
-        for (uint32_t off : cands)
-            if (off + block.size() <= ell.size() && std::equal(block.begin(), block.end(), ell.begin() + off)) { M.ell_off = off; found = true; break; }
-        if (!found) {
-            if (ell.size() + block.size() >= ((size_t)1 << 31)) { S->why_not = "ELL table exceeds int32 offsets"; return TB_OK; }
-            M.ell_off = (uint32_t)ell.size();
-            cands.push_back(M.ell_off);
-            ell.insert(ell.end(), block.begin(), block.end());
-            unique_blocks++;
-        }
-        M.n_halo = (uint32_t)n_halo; M.n_rec = (uint32_t)n_rec;
-        M.exp_off = 0; M.exp_rows = 0; M.map_off16 = 0;
-        M.tflags = (T < S->n_boundary) ? (uint32_t)TF_BOUNDARY : 0u;
-        if (keep_slots) { M.exp_off = old_meta[(size_t)T].exp_off; M.exp_rows = old_meta[(size_t)T].exp_rows; M.tflags = old_meta[(size_t)T].tflags; }
-        size_t bb = blob_size(n_rec, S->has_damping, S->has_active);
-        act_here.clear();
-        for (int r = 1; r < n_rec && e->any_actuated && !dict; r++) {
-            const int32_t sp = rec_spring[rec_first + (size_t)r];
-            if (sp >= 0 && e->h_type[(size_t)sp] >= TB_ACTUATED_EXPAND) act_here.push_back({sp, r});
-        }
-        if (dict) {
-            // record slots -> the tile's distinct records; slot 0 (padding) -> record 0 (k = 0)
-            while (rec_map.size() % 16) rec_map.push_back(0);
-            M.map_off16 = (uint32_t)(rec_map.size() / 16);
-            M.rec_off = (uint32_t)dict_spring.size();
-            int n_dict = 1;
-            dict_spring.push_back(-1);
-            rec_map.push_back(0);
-            for (int r = 1; r < n_rec && dict; r++) {
-                const int32_t sp = rec_spring[rec_first + (size_t)r], c = class_of[(size_t)sp];
-                if (cls_stamp[(size_t)c] != (int32_t)T) {
-                    if (n_dict >= DICT_MAX_TILE) { dict = false; break; }
-                    cls_stamp[(size_t)c] = (int32_t)T; cls_local[(size_t)c] = n_dict++; dict_spring.push_back(rep_of[(size_t)sp]);
-                }
-                rec_map.push_back((uint8_t)cls_local[(size_t)c]);
-            }
-            if (!dict) return build_structure(e, S, keep_slots, next_mode);   // a tile with too many classes
-            for (int r = 1; r < n_dict && e->any_actuated; r++) {
-                const int32_t sp = dict_spring[(size_t)M.rec_off + (size_t)r];
-                if (sp >= 0 && e->h_type[(size_t)sp] >= TB_ACTUATED_EXPAND) act_here.push_back({sp, r});
-            }
-            if (split) {                                                   // slot -> spring, for the per-slot stiffness
-                krec_off.push_back((uint32_t)kslot_spring.size());
-                kslot_spring.insert(kslot_spring.end(), rec_spring.begin() + (ptrdiff_t)rec_first, rec_spring.end());
-            }
-            rec_spring.resize(rec_first);
-            M.n_rec = (uint32_t)n_dict;
-            bb = blob_size(n_dict, S->has_damping, S->has_active, n_rec, split ? n_rec : -1);
-            max_dict = std::max(max_dict, n_dict);
-        }
-        if (blob_total / 16 >= ((size_t)1 << 32)) { S->why_not = "blob exceeds 64 GB"; return TB_OK; }
-        M.blob_off16 = (uint32_t)(blob_total / 16); M.blob_bytes = (uint32_t)bb;
-        {   // where the rest lengths of this tile's actuated springs sit: after the k array (blob_size / tiled_refresh_params)
-            const size_t np = (size_t)((M.n_rec + 1) & ~1u), nk = (dict && split) ? (size_t)((n_rec + 1) & ~1) : np;
-            act_tile_off.push_back((uint32_t)act_rec.size());
-            for (const std::pair<int32_t, int> &a : act_here) {
-                const size_t j = (size_t)(std::lower_bound(e->h_act.begin(), e->h_act.end(), a.first) - e->h_act.begin());
-                const bool known = j < e->h_act.size() && e->h_act[j] == a.first;
-                act_rec.push_back(make_int4((int)(BLOB_REC + nk * 8 + (size_t)a.second * 8), a.first, (known && !act_seen[j]) ? 1 : 0, 0));
-                if (known) act_seen[j] = 1;
-            }
-            M.tflags = (M.tflags & ~(uint32_t)TF_ACTUATED) | (act_here.empty() ? 0u : (uint32_t)TF_ACTUATED);
-        }
-        blob_total += bb;
-        max_blob = std::max(max_blob, bb);
-        max_halo = std::max(max_halo, n_halo); max_rec = std::max(max_rec, n_rec); max_deg = std::max(max_deg, deg);
+    std::vector<TileOut> outs((size_t)n_tiles);
+    parallel_tiles(n_tiles, [&](int64_t T) { build_tile(e, S, T, cfg, outs[(size_t)T]); });
+    int max_halo = 0;
+    for (const TileOut &o : outs) {
+        if (o.why_not) { S->why_not = o.why_not; return TB_OK; }
+        if (o.dict_overflow) return build_structure(e, S, keep_slots, next_mode);   // a tile with too many classes
+        max_halo = std::max(max_halo, (int)o.th.size());
     }
-    while (halo.size() % 4) halo.push_back(0);
-    halo.resize(halo.size() + 4, 0);   // the last list may be copied rounded up to 16 bytes
     if (TM + max_halo + N_DUMMY > CS_BIG) { S->why_not = "a tile reaches too many foreign masses"; return TB_OK; }
     S->cs = choose_cs(max_halo, (e->flags & TB_MATH_STRICT) != 0);
-    ell.resize(ell.size() + (size_t)(MAX_DEG + 2 * ELL_CHUNK) * TM, 0u);   // the kernel prefetches whole register sets
-    {   // padding words: provisional dummy index -> the stride's own dummies [cs - N_DUMMY, cs)
-        const uint32_t base = (uint32_t)(S->cs - N_DUMMY);
-        for (uint32_t &w : ell)
-            if (!(w & ELL_VALID)) { const uint32_t nb = (w >> ELL_NB_SHIFT) & 0x1ffu; w = (base + (nb >= PAD_NB ? nb - PAD_NB : 0u)) << ELL_NB_SHIFT; }
+    S->dict = dict; S->dict_split = split; S->build_mode = mode;
+    S->h_meta.resize((size_t)n_tiles);            // keep_slots: the old entries hand over their exchange fields
+    if (!keep_slots) std::fill(S->h_meta.begin(), S->h_meta.end(), TileMeta());
+    H.act.assign((size_t)n_tiles, {});
+    H.tile_slots.assign((size_t)n_tiles, 1);
+    H.krec_off.assign(split ? 2 * (size_t)n_tiles : 0, 0u);
+    for (int64_t T = 0; T < n_tiles; T++) {
+        const char *why = merge_tile(e, S, T, outs[(size_t)T], keep_slots);
+        if (why) { S->why_not = why; return TB_OK; }
+        TileOut().block.swap(outs[(size_t)T].block);      // release as we go
     }
-    // stages of the tile ring (TB_STAGES): the small dictionary blobs leave room for more than two
-    int nst = 2;      // measured on B200 (C2, dictionary mode): 3 stages 183.7 vs 2 stages 187.9 G spring-steps/s
-    if (const char *v = getenv("TB_STAGES")) nst = std::min(MAX_STAGES, std::max(2, atoi(v)));
-    if (S->tpm > 1) nst = 2;    // named barriers of the partial-sum hand-off are numbered for two stages
-    while (nst > 2 && (size_t)plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm, nst).total > SMEM_LIMIT / 3) nst--;
-    S->nst = nst;
-    SmemPlan plan = plan_smem(S->cs, max_halo, (int)max_blob, S->stage_vel, S->tpm, nst);
-    if ((size_t)plan.total > SMEM_LIMIT) { S->why_not = "a tile's working set exceeds the shared-memory budget"; return TB_OK; }
-    S->smem_bytes = (size_t)plan.total;
+    e->compact_requested = false;
+    return finalize_and_upload(e, S, old_tiles);
+}
 
-    // smallest group size c <= 8 such that every tile's foreign masses live in its own aligned group of c tiles
-    S->res_cluster = 0;
-    for (int c = 1; c <= 8 && !S->res_cluster; c++) {
-        if (n_tiles % c) continue;
-        bool ok = true;
-        for (int64_t T = 0; T < n_tiles && ok; T++) {
-            const TileMeta &M = meta[(size_t)T];
-            const int64_t base = T - T % c;
-            for (uint32_t h = 0; h < M.n_halo && ok; h++) {
-                const int32_t hi = halo[(size_t)M.halo_off + h];
-                if (hi >= 0 && (hi / STATE_BLOCK < base || hi / STATE_BLOCK >= base + c)) ok = false;
-            }
-        }
-        if (ok) S->res_cluster = c;
+// Masses / springs were appended (tb_add_masses / tb_add_springs): new masses get tiles of their own at the end, and only the
+// tiles holding an endpoint of a new spring are rebuilt.  *done = false: the layout cannot absorb the edit (a tile outgrows the
+// format or the record mode) -- the caller rebuilds everything.
+static int patch_structure(Engine *e, TiledState *S, bool *done) {
+    *done = false;
+    if (!S->supported || S->n_tiles == 0 || e->any_ghost || S->halo_connected || S->n_active != S->n_tiles) return TB_OK;
+    if ((int64_t)S->h_meta.size() != S->n_tiles || (int64_t)S->H.tile_slots.size() != S->n_tiles) return TB_OK;
+    HostTables &H = S->H;
+    const int64_t old_tiles = S->n_tiles;
+    const auto w0 = std::chrono::steady_clock::now();
+    // new masses: tiles of their own, in index order
+    std::vector<int64_t> touched;
+    S->h_api_to_slot.resize((size_t)e->nm, -1);
+    for (size_t q = 0; q < e->patch_masses.size(); q++) {
+        if (q % TM == 0) { touched.push_back((int64_t)S->h_slot_to_api.size() / TM); S->h_slot_to_api.resize(S->h_slot_to_api.size() + TM, -1); }
+        const size_t slot = S->h_slot_to_api.size() - TM + q % TM;
+        S->h_slot_to_api[slot] = e->patch_masses[q];
+        S->h_api_to_slot[(size_t)e->patch_masses[q]] = (int32_t)slot;
     }
-    S->n_tiles = n_tiles; S->n_slots = n_slots; S->n_rec = (int64_t)rec_spring.size(); S->n_ell = (int64_t)ell.size();
-    S->n_halo = (int64_t)halo.size(); S->max_halo = max_halo; S->max_rec = max_rec; S->max_deg = max_deg;
-    S->max_blob = (int)max_blob; S->blob_bytes = blob_total; S->ell_unique_tiles = unique_blocks;
-    if (!keep_slots) for (int p = 0; p < 2; p++) {
-        TB_TRY(dev_alloc(e, &S->st[p], (size_t)n_tiles * STATE_BLOCK));
-        TB_CUDA(e, cudaMemset(S->st[p], 0, (size_t)n_tiles * STATE_BLOCK * 8));
+    const int64_t n_tiles = (int64_t)S->h_slot_to_api.size() / TM;
+    if (n_tiles * (int64_t)STATE_BLOCK >= ((int64_t)1 << 31)) return TB_OK;
+    for (int32_t sp : e->patch_springs)
+        for (int32_t end : {e->h_left[(size_t)sp], e->h_right[(size_t)sp]})
+            if (end >= 0 && S->h_api_to_slot[(size_t)end] >= 0) touched.push_back(S->h_api_to_slot[(size_t)end] / TM);
+    std::sort(touched.begin(), touched.end());
+    touched.erase(std::unique(touched.begin(), touched.end()), touched.end());
+    if (S->dict && (int64_t)H.class_of.size() < e->ns) {
+        bool ok = false;
+        TB_TRY(param_classes(e, !S->dict_split, S->has_damping, S->has_active, H, (int64_t)H.class_of.size(), &ok));
+        if (!ok) return TB_OK;
     }
-    S->dict = dict; S->max_dict = max_dict; S->dict_split = split;
-    if (split) {
-        krec_off.push_back((uint32_t)kslot_spring.size());
-        S->n_krec = (int64_t)kslot_spring.size();
-        TB_TRY(upload_vec(e, &S->krec_spring, kslot_spring));
-        TB_CUDA(e, cudaMalloc((void **)&S->krec_off, krec_off.size() * sizeof(uint32_t)));
-        TB_CUDA(e, cudaMemcpy(S->krec_off, krec_off.data(), krec_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    BuildCfg cfg;
+    cfg.dict = S->dict; cfg.split = S->dict_split;
+    cfg.align_rows = !(getenv("TB_ALIGN_ROWS") && atoi(getenv("TB_ALIGN_ROWS")) == 0);
+    cfg.class_of = &H.class_of; cfg.rep_of = &H.rep_of;
+    cfg.drop_removed = true;
+    std::vector<TileOut> outs(touched.size());
+    parallel_tiles((int64_t)touched.size(), [&](int64_t q) { build_tile(e, S, touched[(size_t)q], cfg, outs[(size_t)q]); });
+    for (size_t q = 0; q < touched.size(); q++)
+        if (outs[q].why_not || outs[q].dict_overflow || TM + (int)outs[q].th.size() + N_DUMMY > S->cs) return TB_OK;
+    S->h_meta.resize((size_t)n_tiles, TileMeta());
+    H.act.resize((size_t)n_tiles);
+    H.tile_slots.resize((size_t)n_tiles, 1);
+    if (S->dict_split) H.krec_off.resize(2 * (size_t)n_tiles, 0u);
+    S->n_active = n_tiles;
+    for (size_t q = 0; q < touched.size(); q++) {
+        const char *why = merge_tile(e, S, touched[q], outs[q], touched[q] < old_tiles);
+        if (why) return TB_OK;
     }
-    if (dict) {
-        while (rec_map.size() % 16) rec_map.push_back(0);
-        rec_spring.swap(dict_spring);
-        S->n_rec_map = (int64_t)rec_map.size(); S->n_class_rep = (int64_t)rep_of.size();
-        TB_TRY(upload_vec(e, &S->rec_map, rec_map)); TB_TRY(upload_vec(e, &S->class_rep, rep_of));
-        if (!S->dict_bad) TB_CUDA(e, cudaMalloc((void **)&S->dict_bad, sizeof(int)));
-        S->n_rec = (int64_t)rec_spring.size();
-    }
-    if (!act_rec.empty()) {
-        act_tile_off.push_back((uint32_t)act_rec.size());
-        S->n_act_rec = (int64_t)act_rec.size();
-        TB_CUDA(e, cudaMalloc((void **)&S->act_tile_off, act_tile_off.size() * sizeof(uint32_t)));
-        TB_CUDA(e, cudaMemcpy(S->act_tile_off, act_tile_off.data(), act_tile_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
-        TB_CUDA(e, cudaMalloc((void **)&S->act_rec, act_rec.size() * sizeof(int4)));
-        TB_CUDA(e, cudaMemcpy(S->act_rec, act_rec.data(), act_rec.size() * sizeof(int4), cudaMemcpyHostToDevice));
-    }
-    TB_TRY(dev_alloc(e, &S->blob, blob_total));
-    TB_CUDA(e, cudaMemset(S->blob, 0, blob_total));
-    TB_TRY(upload_vec(e, &S->slot_to_api, S->h_slot_to_api));
-    TB_TRY(upload_vec(e, &S->halo, halo)); TB_TRY(upload_vec(e, &S->rec_spring, rec_spring)); TB_TRY(upload_vec(e, &S->ell, ell));
-    TB_CUDA(e, cudaMalloc((void **)&S->meta, (size_t)n_tiles * sizeof(TileMeta)));
-    TB_CUDA(e, cudaMemcpy(S->meta, meta.data(), (size_t)n_tiles * sizeof(TileMeta), cudaMemcpyHostToDevice));
-    S->h_meta.swap(meta);
-    S->supported = true;
+    const auto w1 = std::chrono::steady_clock::now();
+    TB_TRY(finalize_and_upload(e, S, old_tiles));
+    if (getenv("TB_TIMING"))
+        fprintf(stderr, "[tb timing]   %zu tiles rebuilt in %.2f ms, tables re-uploaded in %.2f ms\n", touched.size(),
+                std::chrono::duration<double, std::milli>(w1 - w0).count(), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w1).count());
+    *done = S->supported;
     return TB_OK;
 }
 
@@ -766,17 +969,21 @@ __global__ void tiled_refresh_mass(uint8_t *blob, const TileMeta *meta, const in
 // dictionary mode: do all springs still carry the parameters of their class representative (bit for bit)?
 __device__ __forceinline__ int actuation_code(int type) { return type == TB_ACTIVE_CONTRACT_THEN_EXPAND ? 1 : type == TB_ACTIVE_EXPAND_THEN_CONTRACT ? 2 : 0; }
 __global__ void dict_check_kernel(int64_t ns, const int32_t *class_rep, const double *k, const double *rest, const double *damping,
-                                  const double *omega, const int32_t *type, int *bad) {
+                                  const double *omega, const int32_t *type, const uint8_t *removed, int rep_matters, int *bad) {
     const int64_t sp = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (sp >= ns) return;
     const int32_t r = class_rep[sp];
     if (r == sp) return;
+    if (removed && removed[sp]) return;           // a tombstone is in no tile's rows any more (or reads k = 0 from its own slot)
+    // its class lost its representative, whose k and damping are zero now: matters where records take those from it (full
+    // dictionary, or damped springs); the rest length and omega of a tombstone are still those of its class
+    if (removed && removed[r]) { if (rep_matters) atomicOr(bad, 2); return; }
     bool same = __double_as_longlong(rest[sp]) == __double_as_longlong(rest[r]);
     if (k) same = same && __double_as_longlong(k[sp]) == __double_as_longlong(k[r]);      // null: split dictionary, k is per slot
     if (damping) same = same && __double_as_longlong(damping[sp]) == __double_as_longlong(damping[r]);
     if (omega) same = same && __double_as_longlong(omega[sp]) == __double_as_longlong(omega[r]);
     if (type) same = same && actuation_code(type[sp]) == actuation_code(type[r]);
-    if (!same) *bad = 1;
+    if (!same) atomicOr(bad, 1);
 }
 // one CTA per tile: the spring records of the tile's blob
 __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const int32_t *rec_spring, const double *k,
@@ -787,7 +994,7 @@ __global__ void tiled_refresh_params(uint8_t *blob, const TileMeta *meta, const 
     uint8_t *b = blob + (size_t)M.blob_off16 * 16;
     const uint32_t np = (M.n_rec + 1) & ~1u;      // slots per parameter array: k | rest | damping | omega | byte map
     // split dictionary: the k array has one slot per record slot of the tile, the other arrays one per distinct record
-    const uint32_t k0 = krec_off ? krec_off[blockIdx.x] : 0u, n_k = krec_off ? krec_off[blockIdx.x + 1] - k0 : 0u;
+    const uint32_t k0 = krec_off ? krec_off[2 * blockIdx.x] : 0u, n_k = krec_off ? krec_off[2 * blockIdx.x + 1] : 0u;
     const uint32_t nk = krec_off ? ((n_k + 1) & ~1u) : np;
     double *kk = (double *)(b + BLOB_REC), *rr = kk + nk;
     double *dmp = rr + np;
@@ -1504,6 +1711,24 @@ int tiled_prepare(Engine *e) {
     if (S->n_tiles == 0 && !(stale & TS_STRUCT) && S->supported) stale |= TS_STRUCT;
     if ((stale & TS_STRUCT) && S->halo_connected)
         return fail(e, TB_ERR_INVALID, "the device layout changed after tb_halo_connect: run tb_halo_prepare / connect / set_exports again");
+    if ((stale & TS_PATCH) && !(stale & TS_STRUCT)) {
+        TB_CUDA(e, cudaStreamSynchronize(e->stream));
+        if (e->canon_stale) TB_TRY(tiled_to_canonical(e));
+        bool done = false;
+        const auto w0 = std::chrono::steady_clock::now();
+        TB_TRY(patch_structure(e, S, &done));
+        if (getenv("TB_TIMING"))
+            fprintf(stderr, "[tb timing] patch_structure (%zu masses, %zu springs) %s: %.2f ms\n", e->patch_masses.size(), e->patch_springs.size(),
+                    done ? "done" : "needs a full build", std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w0).count());
+        if (done) {
+            e->graph_dirty = true;
+            stale |= TS_PARAMS | TS_STATE | TS_FLAGS;       // the blobs were re-allocated; new tiles want their state
+            if (S->api_to_slot) { release(e, S->api_to_slot, S->n_api); S->n_api = 0; }
+        } else if (e->patch_needs_layout) stale |= TS_STRUCT;   // the layout cannot absorb the additions: build it afresh
+        else e->removed_unpatched = true;                       // removals only: they stay in place with k = 0
+    }
+    e->patch_masses.clear(); e->patch_springs.clear(); e->patch_needs_layout = false;
+    stale &= ~(uint32_t)TS_PATCH;
     if (stale & TS_STRUCT) {
         TB_CUDA(e, cudaStreamSynchronize(e->stream));
         if (e->canon_stale) TB_TRY(tiled_to_canonical(e));
@@ -1520,12 +1745,21 @@ int tiled_prepare(Engine *e) {
         dict_check_kernel<<<(unsigned)((e->ns + 255) / 256), 256, 0, e->stream>>>(e->ns, S->class_rep, S->dict_split ? nullptr : e->k, e->rest,
                                                                                   S->has_damping ? e->damping : nullptr,
                                                                                   S->has_active ? e->omega : nullptr,
-                                                                                  S->has_active ? e->type : nullptr, S->dict_bad);
+                                                                                  S->has_active ? e->type : nullptr, e->removed_dev,
+                                                                                  (!S->dict_split || S->has_damping) ? 1 : 0, S->dict_bad);
         int bad = 0;
         TB_CUDA(e, cudaMemcpyAsync(&bad, S->dict_bad, sizeof(int), cudaMemcpyDeviceToHost, e->stream));
         TB_CUDA(e, cudaStreamSynchronize(e->stream));
+        // full dictionary: a tombstone still named by an incidence word shares its record (and its k) with its class
+        bool forced = e->removed_unpatched && !S->dict_split;
+        if (bad == 2) forced = true;          // only representatives were lost: the classes themselves still hold
+        if (forced) bad |= 1;
+        if (S->has_active) {      // the records of actuated springs index the sine table: it must still exist
+            std::vector<double> tab;
+            if (!omega_table(e, tab)) bad = 1;
+        }
         if (bad) {
-            if (S->dict_split) S->split_failures++; else S->dict_failures++;
+            if (!forced) { if (S->dict_split) S->split_failures++; else S->dict_failures++; }
             TB_TRY(build_structure(e, S, /*keep_slots=*/true));
             e->graph_dirty = true;
             if (!S->supported) return TB_OK;
@@ -1567,6 +1801,7 @@ int tiled_prepare(Engine *e) {
                                                                           S->dict_split ? S->krec_off : nullptr, S->has_active ? e->type : nullptr);
     TB_CUDA(e, cudaGetLastError());
     e->tiled_stale = 0;
+    e->removed_unpatched = false;
     return TB_OK;
 }
 

@@ -82,7 +82,7 @@ Mass *Simulation::createMass(Mass *m) {   // src/sim.cu:222-253
     if (STARTED && RUNNING) throw std::runtime_error(kRunning);
     m->ref_count++;
     masses.push_back(m);
-    if (STARTED) topology_dirty = true;   // uploaded at the next resume()/get()/set() (sync_topology)
+    if (STARTED) append_dirty = true;     // appended on the device at the next resume()/get()/set() (sync_topology)
     return m;
 }
 
@@ -102,7 +102,7 @@ Spring *Simulation::createSpring(Spring *s) {   // src/sim.cu:290-322 (exit(1) w
     if (s->_right) s->_right->ref_count++;
     if (s->_left) s->_left->ref_count++;
     springs.push_back(s);
-    if (STARTED) topology_dirty = true;
+    if (STARTED) append_dirty = true;
     return s;
 }
 
@@ -123,10 +123,19 @@ void Simulation::deleteMass(Mass *m) {
     if (STARTED && RUNNING) throw std::runtime_error(kRunning);
     masses.erase(std::remove(masses.begin(), masses.end(), m), masses.end());
     m->valid = false;
+    if (STARTED && m->slot >= 0 && !topology_dirty) {
+        // on the device the mass freezes where it is and its springs exert no force from now on (tb_set_mass_state valid = 0:
+        // flag byte + tombstones, no rebuild) -- what the reference's `invalidate` kernel arranges
+        if (group) topology_dirty = true;
+        else {
+            const int32_t slot = m->slot;
+            const uint8_t zero = 0;
+            engine_check(tb_set_mass_state(engine, 0, 1, &slot, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, &zero), "tb_set_mass_state");
+        }
+    }
     m->slot = -1;
     if (m->ref_count > 1) zombies.push_back(m);
     m->decrementRefCount();
-    if (STARTED) topology_dirty = true;
 }
 
 void Simulation::deleteSpring(Spring *s) {   // src/sim.cu:382-412
@@ -144,9 +153,7 @@ void Simulation::deleteSpring(Spring *s) {   // src/sim.cu:382-412
         if (s->slot >= 0 && !topology_dirty) {
             int32_t slot = s->slot;
             engine_check(dv_remove_springs(dev(), 1, &slot), "tb_remove_springs");
-        } else {
-            topology_dirty = true;
-        }
+        }                                     // slot < 0: created while paused and never uploaded -- nothing to undo
         delete s;   // before start() the reference leaves the object to the caller
     }
 }
@@ -821,6 +828,7 @@ void Simulation::upload_everything() {
         }
     }
     engine_check(dv_set_topology(dev(), nm, ns, left.data(), right.data(), owner.empty() ? nullptr : owner.data()), "tb_set_topology");
+    dev_nm = nm; dev_ns = ns;
     if (hs) { hs->mass_valid = hs->spring_valid = hs->ext_uploaded_nonzero = false; }   // the device is back at its defaults
     if (covered && nm > 0) engine_check(dv_set_tile_hint(dev(), hint.data()), "tb_set_tile_hint");
 
@@ -831,12 +839,53 @@ void Simulation::upload_everything() {
     if (local_dirty) upload_local_constraints();
     upload_constraints();
     topology_dirty = false;
+    append_dirty = false;
 }
 
 // createMass/createSpring/delete* while paused (src/sim.cu:231-253,300-322,343-564): the engine's arrays are
 // rebuilt for the new object lists.  Surviving objects keep the DEVICE's dynamic state (pos, vel, T, pending
 // extern_force, _rest); parameters (m, fixed, k, ...) are taken from the host objects.
+// Masses and springs created while paused sit at the end of the lists with slot < 0: they are appended on the device
+// (tb_add_masses / tb_add_springs: only the tiles they touch are rebuilt).  false = this edit needs the full re-upload.
+bool Simulation::append_topology() {
+    if (group) return false;
+    std::vector<Mass *> new_m;
+    for (Mass *q : masses) if (q->slot < 0) new_m.push_back(q);
+    std::vector<Spring *> new_s;
+    for (Spring *sp : springs) if (sp->slot < 0) new_s.push_back(sp);
+    if (!new_m.empty()) {
+        int rc = tb_add_masses(engine, (int64_t)new_m.size());
+        if (rc == TB_ERR_UNSUPPORTED) return false;
+        engine_check(rc, "tb_add_masses");
+        for (Mass *q : new_m) q->slot = (int32_t)dev_nm++;
+        dev_local.resize((size_t)dev_nm);
+        if (hs) hs->mass_valid = false;
+        upload_masses(new_m.data(), new_m.size());
+    }
+    if (!new_s.empty()) {
+        std::vector<int32_t> left, right;
+        for (Spring *sp : new_s) {
+            left.push_back((sp->_left && sp->_left->valid) ? sp->_left->slot : -1);
+            right.push_back((sp->_right && sp->_right->valid) ? sp->_right->slot : -1);
+        }
+        int rc = tb_add_springs(engine, (int64_t)new_s.size(), left.data(), right.data());
+        if (rc == TB_ERR_UNSUPPORTED) {
+            if (!new_m.empty()) throw std::runtime_error(std::string("tb_add_springs: ") + tb_last_error(engine));
+            return false;
+        }
+        engine_check(rc, "tb_add_springs");
+        for (Spring *sp : new_s) sp->slot = (int32_t)dev_ns++;
+        if (hs) hs->spring_valid = false;
+        upload_springs(new_s.data(), new_s.size());
+    }
+    return true;
+}
+
 void Simulation::sync_topology() {
+    if (!topology_dirty && append_dirty) {
+        if (append_topology()) { append_dirty = false; return; }
+        topology_dirty = true;
+    }
     if (!topology_dirty) return;
     std::vector<Mass *> old_m;
     for (Mass *q : masses) if (q->slot >= 0) old_m.push_back(q);
@@ -1148,7 +1197,8 @@ void Simulation::reset() {   // src/sim.cu:102-129 (which leaks; this one releas
     freeGPU();
     bpts.clear();
     RUNNING = false; STARTED = false; ENDED = false; FREED = false; GPU_DONE = false;
-    topology_dirty = false; constraints_dirty = true; local_dirty = false;
+    topology_dirty = false; append_dirty = false; constraints_dirty = true; local_dirty = false;
+    dev_nm = dev_ns = 0;
     T = 0;
     _global_acc = Vec(0, 0, -9.81);
 }
