@@ -109,7 +109,9 @@ public:
     // The reference picks its integrator when the LIBRARY is compiled (CMake option VERLET -> -DVERLET,
     // CMakeLists.txt:13,90-93; src/sim.cu:1350-1354).  libTitan.so holds both; a user translation unit compiled with
     // -DVERLET gets the Verlet one through these inline constructors, everything else the default Euler branch.
-#ifdef VERLET
+#if defined(RK2)            /* "overrides Verlet and other methods", CMakeLists.txt:95-100 */
+#define TITAN_B200_INTEGRATOR 2
+#elif defined(VERLET)
 #define TITAN_B200_INTEGRATOR 1
 #else
 #define TITAN_B200_INTEGRATOR 0
@@ -117,7 +119,7 @@ public:
     struct Init {};
     Simulation() : Simulation(0, TITAN_B200_INTEGRATOR, Init()) {}
     explicit Simulation(int device) : Simulation(device, TITAN_B200_INTEGRATOR, Init()) {}   // extension: choose the CUDA device (the reference always uses device 0)
-    Simulation(int device, int integrator, Init);   // integrator: 0 = Euler (default build), 1 = VERLET build
+    Simulation(int device, int integrator, Init);   // integrator: 0 = Euler (default build), 1 = VERLET build, 2 = RK2 build (call sites repaired)
     // extension: ONE simulation over several GPUs of this machine (tb_create_partitioned, include/titan_b200.h).  A single
     // lattice is cut into i-slabs, independent bodies (containers no spring connects) go whole to the GPUs in turn; the
     // boundary masses are exchanged inside the step kernel over NVLink peer memory.  Same API, same results (the per-mass

@@ -59,6 +59,12 @@ typedef enum {
                              /* vel += 0.5*(acc + f/m)*dt; acc = f/m; pos += vel*dt + 0.5*acc*dt^2, no speed clamp; */
                              /* acc is persistent state (zero at upload, like CUDA_MASS(Mass&)); both step kernels    */
 
+#define TB_INTEGRATOR_RK2 32u /* the reference's -DRK2 build (CMakeLists.txt:14,95-100; src/sim.cu:1336-1349,1778-1799) with its two call sites  */
+                             /* repaired to pass the arguments the kernel declares (as shipped they do not compile): midpoint rule,      */
+                             /* two force evaluations (two kernel launches) per step, T += 0.5 dt per stage, no speed clamp; ACTUATED_*  */
+                             /* springs advance their rest length in both evaluations, as computeSpringForces does.  Streaming and      */
+                             /* generic kernels; not on a partition, not with magnetic masses (fails loudly)                             */
+
 /* SpringType, include/Titan/spring.h:17-18 */
 enum { TB_PASSIVE_SOFT = 0, TB_PASSIVE_STIFF = 1, TB_ACTIVE_CONTRACT_THEN_EXPAND = 2,
        TB_ACTIVE_EXPAND_THEN_CONTRACT = 3, TB_ACTUATED_EXPAND = 4, TB_ACTUATED_CONTRACT = 5 };

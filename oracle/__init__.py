@@ -49,7 +49,7 @@ class _Scene(C.Structure):
                 ("planes", C.POINTER(Plane)), ("balls", C.POINTER(Ball)),
                 ("lc_ptr", _lp), ("lc", C.POINTER(Local)),
                 ("g", C.c_double * 3), ("dt", C.c_double), ("T_sim", C.c_double), ("magnets", C.c_int32),
-                ("verlet", C.c_int32)]
+                ("verlet", C.c_int32), ("bk_pos", _dp), ("bk_vel", _dp)]
 
 
 def build(force=False):
@@ -207,6 +207,7 @@ class Scene:
         self.T_sim = 0.0
         self.magnets = False
         self.verlet = False   # the reference's -DVERLET build
+        self.rk2 = False      # ... its -DRK2 build (call sites repaired)
 
     def add_local(self, mass_index, kind, vec, num):
         self.local[mass_index].append(make_local(kind, vec, num))
@@ -245,7 +246,11 @@ class Scene:
             keep += [ptr, lc]
         s.g = _v3(self.g)
         s.dt, s.T_sim, s.magnets = self.dt, self.T_sim, int(self.magnets)
-        s.verlet = int(self.verlet)
+        s.verlet = 2 if getattr(self, "rk2", False) else int(self.verlet)
+        if s.verlet == 2:
+            bk = np.zeros((2, self.nm, 3))
+            s.bk_pos, s.bk_vel = _d(bk[0]), _d(bk[1])
+            keep.append(bk)
         return s, keep
 
     def _run(self, fn, *args):

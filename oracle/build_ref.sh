@@ -6,6 +6,7 @@
 #   <out_dir>/libtitan_ref_host.so   host-callable reference code + oracle/ref_host_shim.cu   (CPU, runs here)
 #   <out_dir>/titan_ref_cuda         the reference's CUDA engine + tests/cpp/titan_api_driver.cu (needs a GPU)
 #   <out_dir>/titan_ref_cuda_verlet  the same with the reference's VERLET option (CMakeLists.txt:13,90-93)
+#   <out_dir>/titan_ref_cuda_rk2     the same with its RK2 option (CMakeLists.txt:14,95-100), call sites repaired by patch_ref.py
 # Flags follow the reference's CMakeLists.txt: C++14, separable compilation, -DCONSTRAINTS, no GRAPHICS.
 set -euo pipefail
 REF="${1:-/root/reference}"
@@ -24,6 +25,12 @@ for f in vec mass spring object sim; do
   nvcc $NVFLAGS -c "$S/src/$f.cu" -o "$SCRATCH/$f.o" &
 done
 nvcc $NVFLAGS -DVERLET -c "$S/src/sim.cu" -o "$SCRATCH/sim_verlet.o" &
+# the RK2 option needs C++17 (if constexpr) and is a PUBLIC define (CUDA_MASS grows two backup vectors): everything is rebuilt
+NVFLAGS_RK2="${NVFLAGS/-std=c++14/-std=c++17} -DRK2"
+for f in vec mass spring object sim; do
+  nvcc $NVFLAGS_RK2 -c "$S/src/$f.cu" -o "$SCRATCH/${f}_rk2.o" &
+done
+nvcc $NVFLAGS_RK2 -c "$HERE/../tests/cpp/titan_api_driver.cu" -o "$SCRATCH/dump_rk2.o" &
 nvcc $NVFLAGS -c "$HERE/ref_host_shim.cu" -o "$SCRATCH/shim.o" &
 nvcc $NVFLAGS -c "$HERE/../tests/cpp/titan_api_driver.cu" -o "$SCRATCH/dump.o" &
 wait
@@ -36,4 +43,7 @@ nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a \
 nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a \
   "$SCRATCH/vec.o" "$SCRATCH/mass.o" "$SCRATCH/spring.o" "$SCRATCH/object.o" "$SCRATCH/sim_verlet.o" "$SCRATCH/dump.o" \
   -o "$OUT/titan_ref_cuda_verlet" -lcudart
+nvcc -ccbin /usr/bin/g++ -gencode arch=compute_100a,code=sm_100a \
+  "$SCRATCH/vec_rk2.o" "$SCRATCH/mass_rk2.o" "$SCRATCH/spring_rk2.o" "$SCRATCH/object_rk2.o" "$SCRATCH/sim_rk2.o" "$SCRATCH/dump_rk2.o" \
+  -o "$OUT/titan_ref_cuda_rk2" -lcudart
 echo "build_ref: built $OUT/libtitan_ref_host.so, $OUT/titan_ref_cuda and $OUT/titan_ref_cuda_verlet"

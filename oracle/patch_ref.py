@@ -57,6 +57,14 @@ def main(ref, out):
         # 6. t_fps_now exists only under GRAPHICS
         t = sub_once(t, "    t_fps_now = std::chrono::system_clock::now(); // set initial before times\n",
                      "#ifdef GRAPHICS\n    t_fps_now = std::chrono::system_clock::now();\n#endif\n", "sim.cu t_fps_now")
+        # 7. RK2 build only (-DRK2): the two call sites pass 6 arguments to the 12-argument kernel (src/sim.cu:1786,1795 vs
+        #    :1285-1286) and cannot compile.  Repaired = the argument list the default branch passes (:1808-1809).  No
+        #    effect on the default and VERLET builds (the lines sit inside #ifdef RK2).
+        broken = "(d_mass, masses.size(), dt, T, _global_acc, d_constraints);"
+        fixed = ("(d_mass, masses.size(), dt, T, _global_acc, d_constraints,\n"
+                 "                d_occupancy_grid, d_og_counter, occupancy_grid_dim, occupancy_grid_offset, occupancy_grid_max_masses_per_cell, og_cell_size);")
+        for tag in ("massForcesAndUpdate<true><<<massBlocksPerGrid, THREADS_PER_BLOCK>>>", "massForcesAndUpdate<false><<<massBlocksPerGrid, THREADS_PER_BLOCK>>>"):
+            t = sub_once(t, tag + broken, tag + fixed, "sim.cu RK2 call " + tag[:26])
         return t
 
     edit("src/sim.cu", sim)

@@ -235,7 +235,9 @@ static void magnet_forces(const to_scene *s, const og_t *og, int64_t i, double e
 /* ------------------------------------------------------------------ mass update -------------------------- */
 
 /* one mass of massForcesAndUpdate, src/sim.cu:1289-1366, default Euler branch */
-static void mass_update_one(to_scene *s, int64_t i, const og_t *og) {
+/* rk2: 0 = not the RK2 build; 1 = massForcesAndUpdate<true> (half step, :1336-1343); 2 = <false> (full step from the
+ * backup with the mid-point velocity and acceleration, :1344-1348) */
+static void mass_update_one(to_scene *s, int64_t i, const og_t *og, int rk2) {
     if (s->fixed[i] == 1) return; /* :1294 -- nothing happens, not even the force reset or T */
     double *force = s->force + 3 * i, *pos = s->pos + 3 * i, *vel = s->vel + 3 * i;
     double *ext = s->ext + 3 * i, *acc = s->acc + 3 * i;
@@ -271,7 +273,26 @@ static void mass_update_one(to_scene *s, int64_t i, const og_t *og) {
         for (int c = 0; c < 3; c++) force[c] += vel[c] * coef / vel_norm;
     }
 
-    if (s->verlet) {                                              /* #elif VERLET, :1350-1354 */
+    if (rk2 == 1) {                                               /* #ifdef RK2, step == true, :1337-1343 */
+        double *bp = s->bk_pos + 3 * i, *bv = s->bk_vel + 3 * i;
+        for (int c = 0; c < 3; c++) acc[c] = force[c] / m;
+        for (int c = 0; c < 3; c++) { bv[c] = vel[c]; bp[c] = pos[c]; }
+        for (int c = 0; c < 3; c++) pos[c] = pos[c] + (0.5 * vel[c]) * s->dt;
+        for (int c = 0; c < 3; c++) vel[c] = vel[c] + (0.5 * acc[c]) * s->dt;
+        s->T[i] += 0.5 * s->dt;
+        for (int c = 0; c < 3; c++) { force[c] = 0.0; ext[c] = 0.0; }
+        return;
+    }
+    if (rk2 == 2) {                                               /* step == false, :1344-1348 */
+        const double *bp = s->bk_pos + 3 * i, *bv = s->bk_vel + 3 * i;
+        for (int c = 0; c < 3; c++) acc[c] = force[c] / m;
+        for (int c = 0; c < 3; c++) pos[c] = bp[c] + vel[c] * s->dt;
+        for (int c = 0; c < 3; c++) vel[c] = bv[c] + acc[c] * s->dt;
+        s->T[i] += 0.5 * s->dt;
+        for (int c = 0; c < 3; c++) { force[c] = 0.0; ext[c] = 0.0; }
+        return;
+    }
+    if (s->verlet == 1) {                                         /* #elif VERLET, :1350-1354 */
         double dt2 = s->dt * s->dt;                               /* pow(dt, 2) */
         for (int c = 0; c < 3; c++) vel[c] += (0.5 * (acc[c] + force[c] / m)) * s->dt;   /* :1351 */
         for (int c = 0; c < 3; c++) acc[c] = force[c] / m;                               /* :1352 */
@@ -299,7 +320,7 @@ static void og_free(og_t *og) { if (og) { free(og->counter); free(og->cells); fr
 void to_mass_update(to_scene *s) {
     og_t *og = NULL;
     if (s->magnets) { og = og_alloc(s); og_build(s, og); }
-    for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og);
+    for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og, 0);
     og_free(og);
 }
 
@@ -308,8 +329,17 @@ void to_step(to_scene *s, int64_t nsteps) {
     og_t *og = s->magnets ? og_alloc(s) : NULL;
     for (int64_t n = 0; n < nsteps; n++) {
         if (og) og_build(s, og);                                  /* recomputeOG, :1775 */
+        if (s->verlet == 2) {                                     /* #ifdef RK2, :1778-1799 (call sites repaired) */
+            to_spring_forces(s, s->T_sim);
+            for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og, 1);
+            s->T_sim += 0.5 * s->dt;
+            to_spring_forces(s, s->T_sim);
+            for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og, 2);
+            s->T_sim += 0.5 * s->dt;
+            continue;
+        }
         to_spring_forces(s, s->T_sim);
-        for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og);
+        for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og, 0);
         s->T_sim += s->dt;
     }
     og_free(og);
@@ -358,7 +388,7 @@ void to_step_omp(to_scene *s, int64_t nsteps) {
             }
         }
 #pragma omp parallel for schedule(static)
-        for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og);
+        for (int64_t i = 0; i < s->nm; i++) if (s->valid[i]) mass_update_one(s, i, og, 0);
         s->T_sim += s->dt;
     }
     og_free(og);

@@ -70,8 +70,11 @@ typedef struct {
     double dt;
     double T_sim;                            /* Simulation::T */
     int32_t magnets;                         /* run the occupancy-grid magnet pass (a7) */
-    int32_t verlet;                          /* the reference's -DVERLET build (src/sim.cu:1350-1354) instead of the
-                                                default Euler branch (:1355-1362); acc is then persistent state */
+    int32_t verlet;                          /* integrator: 0 = default Euler branch (src/sim.cu:1355-1362); 1 = the reference's
+                                                -DVERLET build (:1350-1354), acc is then persistent state; 2 = its -DRK2 build
+                                                (:1336-1349, loop :1778-1799 with the call sites repaired to pass the arguments
+                                                the kernel declares -- as shipped they do not compile) */
+    double *bk_pos, *bk_vel;                 /* nm*3 each, RK2 only: CUDA_MASS::__rk2_backup_pos/vel (include/Titan/mass.h:111-114) */
 } to_scene;
 
 /* ---- the step (src/sim.cu:1157-1200, 1285-1367, loop 1704-1714 + 1800-1811) ---- */

@@ -149,3 +149,5 @@ PAUSES = {"c1_readme": [0.0, 0.001, 0.01, 0.1], "contact_friction": [0.0, 0.001,
           "cube_beam": [0.0, 0.001, 0.02], "magnets": [0.0, 0.001, 0.005]}
 # scenarios that were also run through the reference built with -DVERLET (tests/golden/ref_cuda/ref_verlet_<name>.bin)
 VERLET_SCENARIOS = ("c1_readme", "contact_friction", "actuated", "local_constraints")
+# ... and through the reference built with -DRK2, call sites repaired (tests/golden/ref_cuda/ref_rk2_<name>.bin)
+RK2_SCENARIOS = ("c1_readme", "contact_friction", "actuated", "local_constraints")

@@ -649,3 +649,38 @@ def test_actuated_springs_stay_on_the_tiled_kernel(monkeypatch):
     o = oracle_after(sc, 30)
     g = run_engine(sc, 30, tb.MATH_STRICT | tb.KERNEL_CSR)
     assert g["info"]["kernel"] == 0 and same_bits(g["rest"], o.rest) and same_bits(g["pos"], o.pos)
+
+
+@pytest.mark.parametrize("name", ["c1_readme", "contact_friction", "local_constraints", "cube_beam", "actuated"])
+@pytest.mark.parametrize("kern", [0, tb.KERNEL_CSR], ids=["tiled", "generic"])
+def test_rk2_integrator(name, kern):
+    """TB_INTEGRATOR_RK2 (the reference's -DRK2 build with its call sites repaired, src/sim.cu:1336-1349,1778-1799): two force
+    evaluations per step, T += 0.5 dt per half.  Strict arithmetic is bit-identical to the oracle's RK2 branch (1e-13 where
+    sin() is involved), fast arithmetic within 1e-12 / 1e-9; per-mass T and the rest lengths of ACTUATED_* springs (advanced in
+    both halves, as computeSpringForces does) are bit-identical."""
+    sc = scenes.SCENARIOS[name]()
+    sc.rk2 = True
+    for nsteps in (1, 60):
+        o = oracle_after(sc, nsteps)
+        g = run_engine(sc, nsteps, tb.MATH_STRICT | tb.INTEGRATOR_RK2 | kern)
+        assert g["info"]["kernel"] == (0 if kern else 1)
+        assert same_bits(g["T"], o.T) and same_bits(g["rest"], o.rest)
+        for f in FIELDS:
+            if name == "actuated":
+                assert rel(g[f], getattr(o, f)) <= (1e-13 if f != "acc" else 1e-9), (name, nsteps, f)
+            else:
+                assert same_bits(g[f] + 0.0, getattr(o, f) + 0.0), (name, nsteps, f)
+        f_ = run_engine(sc, nsteps, tb.MATH_FAST | tb.INTEGRATOR_RK2 | kern, chunks=2 if nsteps > 1 else 1)
+        for f in ("pos", "vel"):
+            assert rel(f_[f], getattr(o, f)) <= (1e-12 if nsteps == 1 else 1e-9), (name, nsteps, f)
+        assert same_bits(f_["T"], o.T)
+
+
+def test_rk2_refuses_what_it_is_not_built_for():
+    sc = scenes.magnets()
+    eng = tb.Engine(0, tb.MATH_FAST | tb.INTEGRATOR_RK2)
+    scenes.upload(eng, sc)
+    with pytest.raises(tb.TitanError) as ei:
+        eng.run(1, 0.0)
+    assert ei.value.status == 4 and "RK2" in str(ei.value)
+    eng.close()

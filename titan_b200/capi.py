@@ -11,7 +11,7 @@ import numpy as np
 _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("TITAN_B200_LIB") or os.path.join(_PKG, "libtitan_b200.so")   # override: A/B builds on one GPU box
 
-MATH_FAST, MATH_STRICT, NO_GRAPH, KERNEL_CSR, INTEGRATOR_VERLET, NO_RESIDENT = 0, 1, 2, 4, 8, 16
+MATH_FAST, MATH_STRICT, NO_GRAPH, KERNEL_CSR, INTEGRATOR_VERLET, NO_RESIDENT, INTEGRATOR_RK2 = 0, 1, 2, 4, 8, 16, 32
 PASSIVE_SOFT, PASSIVE_STIFF, ACTIVE_CONTRACT_THEN_EXPAND, ACTIVE_EXPAND_THEN_CONTRACT, ACTUATED_EXPAND, \
     ACTUATED_CONTRACT = range(6)
 CONSTRAINT_PLANE, CONTACT_PLANE, BALL, DIRECTION = range(4)

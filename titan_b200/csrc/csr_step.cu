@@ -20,13 +20,15 @@ struct CsrArgs {
     const double *k, *rest, *damping, *omega;
     const double *t_in;
     double *t_out;
+    int rk2_stage;           // the reference's RK2 build: 1 = half step, 2 = full step from the backup (the state before stage 1,
+                             // which still sits in the output buffer: ping-pong)
 };
 
 template <class P, bool DAMPING, bool ACTIVE, bool WRITE_ACC, bool VERLET>
 __global__ void __launch_bounds__(128) csr_step_kernel(CsrArgs A, Globals G, MassExtras X) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     double t = *A.t_in;
-    if (i == 0) *A.t_out = __dadd_rn(t, G.dt);      // T += dt, src/sim.cu:1811
+    if (i == 0) *A.t_out = __dadd_rn(t, A.rk2_stage ? __dmul_rn(0.5, G.dt) : G.dt);      // T += dt, src/sim.cu:1811 (RK2: 0.5 dt per stage)
     if (i >= A.nm) return;
     const int64_t n = A.nm;
     uint8_t fl = A.flags[i];
@@ -61,6 +63,17 @@ __global__ void __launch_bounds__(128) csr_step_kernel(CsrArgs A, Globals G, Mas
     }
     V3 acc;
     if (VERLET) acc = V3{A.acc[i], A.acc[n + i], A.acc[2 * n + i]};   // the previous step's acceleration is state
+    if (A.rk2_stage) {
+        force = mass_forces<P>(G, X, i, fl & F_LOCAL, A.m[i], pos, vel, force);
+        double *bvel = (fl & F_LOCAL) ? X.rk2_bvel : nullptr;      // backup taken after the constraints projected the velocity
+        if (A.rk2_stage == 1) {
+            if (bvel) { bvel[i] = vel.x; bvel[n + i] = vel.y; bvel[2 * n + i] = vel.z; }
+            rk2_stage1_tail<P>(G.dt, A.m[i], force, pos, vel, acc);
+        } else {
+            const V3 bv = bvel ? V3{bvel[i], bvel[n + i], bvel[2 * n + i]} : V3{A.vel_out[i], A.vel_out[n + i], A.vel_out[2 * n + i]};
+            rk2_stage2_tail<P>(G.dt, A.m[i], force, V3{A.pos_out[i], A.pos_out[n + i], A.pos_out[2 * n + i]}, bv, pos, vel, acc);
+        }
+    } else
     mass_update<P, VERLET>(G, X, i, fl & F_LOCAL, A.m[i], pos, vel, force, acc);
     A.pos_out[i] = pos.x; A.pos_out[n + i] = pos.y; A.pos_out[2 * n + i] = pos.z;
     A.vel_out[i] = vel.x; A.vel_out[n + i] = vel.y; A.vel_out[2 * n + i] = vel.z;
@@ -82,9 +95,10 @@ template <class P> static void launch_p(Engine *e, const CsrArgs &A, const MassE
     else launch_w<P, false, false>(e, A, X, write_acc);
 }
 
-int launch_csr_step(Engine *e, bool use_ext, bool write_acc) {
+int launch_csr_step(Engine *e, bool use_ext, bool write_acc, int rk2_stage) {
     CsrArgs A;
     A.nm = e->nm;
+    A.rk2_stage = rk2_stage;
     A.pos_in = e->pos[e->cur]; A.vel_in = e->vel[e->cur];
     A.pos_out = e->pos[e->cur ^ 1]; A.vel_out = e->vel[e->cur ^ 1];
     A.acc = e->acc; A.m = e->m; A.flags = e->mflags;
@@ -97,6 +111,7 @@ int launch_csr_step(Engine *e, bool use_ext, bool write_acc) {
     X.lc_ptr = e->any_local ? e->lc_ptr : nullptr;
     X.lc = e->lc;
     X.nm = e->nm;
+    X.rk2_bvel = (rk2_stage && e->any_local) ? e->rk2_bvel : nullptr;
     if (e->any_active && !e->type) return fail(e, TB_ERR_INVALID, "active springs without type array");
     if (e->flags & TB_MATH_STRICT) launch_p<Strict>(e, A, X, write_acc);
     else launch_p<Fast>(e, A, X, write_acc);

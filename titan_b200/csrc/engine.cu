@@ -217,7 +217,7 @@ template <class T> static int down_scalar(Engine *e, T *dst_host, const T *src, 
 static void free_all(Engine *e) {
     auto F = [&](auto *&p, size_t bytes) { dev_free(e, (void *)p, bytes); p = nullptr; };
     size_t m3 = (size_t)e->nm * 24, m1 = (size_t)e->nm * 8, s1 = (size_t)e->ns * 8, s4 = (size_t)e->ns * 4;
-    F(e->pos[0], m3); F(e->pos[1], m3); F(e->vel[0], m3); F(e->vel[1], m3); F(e->acc, m3); F(e->ext, m3);
+    F(e->pos[0], m3); F(e->pos[1], m3); F(e->vel[0], m3); F(e->vel[1], m3); F(e->acc, m3); F(e->ext, m3); F(e->rk2_bvel, m3);
     F(e->m, m1); F(e->mflags, (size_t)e->nm); F(e->drag, (size_t)e->nm * 4);
     F(e->left, s4); F(e->right, s4); F(e->type, s4);
     F(e->k, s1); F(e->rest, s1); F(e->damping, s1); F(e->omega, s1); F(e->l_max, s1); F(e->l_min, s1); F(e->rate, s1);
@@ -255,7 +255,8 @@ static double replay_T(Engine *e, int64_t i, uint8_t flags) {
         if (seg_end <= from) continue;
         int64_t n = std::min(seg_end, to) - from;
         double dt = e->dt_log[s].dt;
-        for (int64_t q = 0; q < n; q++) T += dt;
+        if (e->flags & TB_INTEGRATOR_RK2) { const double h = 0.5 * dt; for (int64_t q = 0; q < n; q++) { T += h; T += h; } }   // :1342,1348
+        else for (int64_t q = 0; q < n; q++) T += dt;
         from += n;
     }
     return T;
@@ -932,6 +933,24 @@ static int enqueue_step(Engine *e, bool use_ext, bool write_acc) {
             e->launches++;
         }
     }
+    if (e->flags & TB_INTEGRATOR_RK2) {
+        // two force evaluations per step (src/sim.cu:1778-1799): half step into the other buffer, then the full step from the
+        // backup -- which is what the first buffer still holds when the second launch overwrites it, slot by slot
+        if (e->any_magnet || e->any_ghost) return fail(e, TB_ERR_UNSUPPORTED, "the RK2 integrator is not built for magnetic masses or partitioned systems");
+        for (int stage = 1; stage <= 2; stage++) {
+            if (stage == 2 && e->any_actuated && !use_tiled(e)) {     // computeSpringForces runs (and advances _rest) in both halves
+                advance_rest_kernel<<<blocks_for(e->n_act), 256, 0, e->stream>>>(
+                    e->rest, e->type, e->l_max, e->l_min, e->rate, e->left, e->right, e->mflags, e->G.dt, e->act_idx, e->n_act);
+                e->launches++;
+            }
+            int rc = use_tiled(e) ? launch_tiled_step(e, use_ext && stage == 1, write_acc && stage == 2, stage)
+                                  : launch_csr_step(e, use_ext && stage == 1, write_acc && stage == 2, stage);
+            if (rc != TB_OK) return rc;
+            e->launches++;
+            e->cur ^= 1;
+        }
+        return TB_OK;
+    }
     if (e->any_magnet) TB_TRY(launch_magnet_pass(e, use_ext, use_tiled(e)));   // recomputeOG + magnet forces, src/sim.cu:1775,1298
     int rc = use_tiled(e) ? launch_tiled_step(e, use_ext, write_acc) : launch_csr_step(e, use_ext, write_acc);
     if (rc != TB_OK) return rc;
@@ -971,6 +990,7 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     E_CHECK(e);
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "No masses have been added. Please add masses before starting the simulation.");  // src/sim.cu:1552-1554
     if (nsteps < 0) return fail(e, TB_ERR_INVALID, "tb_run_async: negative step count");
+    if ((e->flags & TB_INTEGRATOR_RK2) && e->any_local && !e->rk2_bvel) TB_TRY(dev_alloc(e, &e->rk2_bvel, (size_t)e->nm * 3));
     if (e->any_actuated) {
         if (!e->l_max || !e->l_min || !e->rate) return fail(e, TB_ERR_INVALID, "actuated springs need l_max, l_min and rate");
         TB_TRY(prepare_actuated(e));   // before tiled_prepare: the tile builder records where their rest lengths live
@@ -1006,7 +1026,7 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
         if (!e->graph[e->cur]) TB_TRY(build_graph(e, e->cur));
         while (left_steps - 1 >= GRAPH_STEPS) {
             TB_CUDA(e, cudaGraphLaunch(e->graph[e->cur], e->stream));
-            e->launches += (int64_t)GRAPH_STEPS * (1 + ((e->any_actuated && !use_tiled(e)) ? 1 : 0) + (e->any_magnet ? 5 : 0));
+            e->launches += (int64_t)GRAPH_STEPS * (((e->flags & TB_INTEGRATOR_RK2) ? 2 : 1) * (1 + ((e->any_actuated && !use_tiled(e)) ? 1 : 0)) + (e->any_magnet ? 5 : 0));
             left_steps -= GRAPH_STEPS;
         }
     }

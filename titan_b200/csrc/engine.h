@@ -62,6 +62,7 @@ struct Engine {
     tb_local *lc = nullptr;
     tb_plane *more_planes = nullptr;
     tb_ball *more_balls = nullptr;
+    double *rk2_bvel = nullptr;    // [3][nm] RK2 + local constraints: velocity backups of stage 1 (MassExtras::rk2_bvel)
     double *t_dev = nullptr;       // [2] simulation time, ping-pong with the step parity
     long long *step_dev = nullptr; // [2] steps completed, ping-pong (halo exchange sequence number)
     float *export_f32 = nullptr;
@@ -146,7 +147,7 @@ int ensure_csr(Engine *e);
 // engine.cu: (re)builds e->act_idx / e->h_act, the list of ACTUATED_* springs; allocates, so never under stream capture
 int prepare_actuated(Engine *e);
 // csr_step.cu
-int launch_csr_step(Engine *e, bool use_ext, bool write_acc);
+int launch_csr_step(Engine *e, bool use_ext, bool write_acc, int rk2_stage = 0);
 // magnet.cu
 int magnet_alloc(Engine *e);
 void magnet_free(Engine *e);
@@ -165,7 +166,7 @@ struct PosView {
 };
 // tiled.cu
 int tiled_prepare(Engine *e);                    // (re)build tiles if stale
-int launch_tiled_step(Engine *e, bool use_ext, bool write_acc);
+int launch_tiled_step(Engine *e, bool use_ext, bool write_acc, int rk2_stage = 0);
 int tiled_to_canonical(Engine *e);               // refresh canonical pos/vel from tiles
 void tiled_destroy(Engine *e);
 bool tiled_supported(const Engine *e);

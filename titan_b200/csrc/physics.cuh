@@ -185,6 +185,8 @@ struct MassExtras {                // rarely-used per-mass data; null pointers =
     const int32_t *lc_ptr;         // [nm+1] local-constraint CSR (or null)
     const tb_local *lc;
     int64_t nm;                    // plane stride of SoA arrays
+    double *rk2_bvel = nullptr;    // [3][nm] RK2 build with local constraints: the velocity backup of stage 1 is taken AFTER the
+                                   // constraints have projected the velocity (src/sim.cu:1312-1326 mutate mass.vel, :1338 copies it)
 };
 
 // Rarely-taken parts of the mass update live out of line: the step kernels' hot loop is instruction-cache bound
@@ -275,6 +277,24 @@ __device__ __forceinline__ void verlet_tail(double dt, double m, const V3 &force
     V3 step = scale3<P>(vel, dt);
     acc3<P>(step, scale3<P>(scale3<P>(a, 0.5), P::mul(dt, dt)));
     acc3<P>(pos, step);
+}
+
+// The reference's -DRK2 build (src/sim.cu:1336-1349 inside massForcesAndUpdate<step>, loop :1778-1799; as shipped its two
+// call sites pass 6 arguments to the 12-argument kernel and do not compile -- "repaired" = the same call with the arguments
+// the kernel declares).  Midpoint rule in two force evaluations, no speed clamp:
+//   stage 1 (step == true):  acc = f/m; backup = (pos, vel); pos += 0.5 vel dt; vel += 0.5 acc dt; T += 0.5 dt
+//   stage 2 (step == false): acc = f/m (forces at the midpoint state); pos = backup_pos + vel_mid dt; vel = backup_vel + acc dt
+template <class P>
+__device__ __forceinline__ void rk2_stage1_tail(double dt, double m, const V3 &force, V3 &pos, V3 &vel, V3 &acc) {
+    acc = P::strict ? div3<P>(force, m) : scale3<P>(force, rcp_fast(m));
+    acc3<P>(pos, scale3<P>(scale3<P>(vel, 0.5), dt));
+    acc3<P>(vel, scale3<P>(scale3<P>(acc, 0.5), dt));
+}
+template <class P>
+__device__ __forceinline__ void rk2_stage2_tail(double dt, double m, const V3 &force, const V3 &bpos, const V3 &bvel, V3 &pos, V3 &vel, V3 &acc) {
+    acc = P::strict ? div3<P>(force, m) : scale3<P>(force, rcp_fast(m));
+    pos = bpos; acc3<P>(pos, scale3<P>(vel, dt));
+    vel = bvel; acc3<P>(vel, scale3<P>(acc, dt));
 }
 
 // Everything massForcesAndUpdate does after the spring forces are known (src/sim.cu:1299-1365).

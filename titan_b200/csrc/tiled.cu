@@ -1110,6 +1110,7 @@ constexpr long long HALO_TIMEOUT_CLOCKS = 1ll << 32;   // ~2 s: a peer that neve
 struct TiledArgs {
     int32_t n_tiles;
     int32_t write_acc;               // 1: store acc (canonical array); 2: Verlet -- acc is state, read and stored every step
+    int32_t rk2_stage;               // the reference's RK2 build: 1 = half step (massForcesAndUpdate<true>), 2 = full step from the backup
     int prof_lite;                   // TB_PROFILE=2: only the barrier waits and the loop totals
     unsigned long long *prof;        // TB_PROFILE=1: per-phase clock64 sums (0 wait full, 1 springs, 2 partial-sum handoff, 3 mass update, 4 producer wait empty, 5 producer wait halo list, 6 producer issue, 7 ell-copy wait)
     int32_t l2_hint;                 // 1: stream the spring-record blobs through L2 with evict_first
@@ -1199,6 +1200,22 @@ __device__ __noinline__ void advance_actuated_records(const ARGS &A, double dt, 
     }
     __syncwarp();
     asm volatile("fence.proxy.async;" ::: "memory");
+}
+
+// RK2 build (physics.cuh): stage 1 is a half step into the other state buffer; stage 2 steps from the BACKUP -- the state
+// before stage 1, which still sits in the slot this thread is about to overwrite (ping-pong buffers; nobody else reads it).
+// A mass with local constraints keeps its velocity backup in a side array: the constraints project the velocity in place before
+// the backup is taken (MassExtras::rk2_bvel).
+template <class P>
+__device__ __noinline__ void rk2_tail(int stage, double dt, double mass, const V3 &force, const double *ob, V3 &pos, V3 &vel, V3 &acc,
+                                      double *bvel, int64_t i_api, int64_t nm) {
+    if (stage == 1) {
+        if (bvel) { bvel[i_api] = vel.x; bvel[nm + i_api] = vel.y; bvel[2 * nm + i_api] = vel.z; }
+        rk2_stage1_tail<P>(dt, mass, force, pos, vel, acc);
+    } else {
+        const V3 bv = bvel ? V3{bvel[i_api], bvel[nm + i_api], bvel[2 * nm + i_api]} : V3{ob[3 * TM], ob[4 * TM], ob[5 * TM]};
+        rk2_stage2_tail<P>(dt, mass, force, V3{ob[0], ob[TM], ob[2 * TM]}, bv, pos, vel, acc);
+    }
 }
 
 // A consumer warp has finished `pending` boundary tiles: make its peer stores visible, count them, and -- as the
@@ -1294,7 +1311,7 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
     if (tid >= NT) {
         // =========================================== PRODUCER warp ===========================================
         const int lane = tid - NT;
-        if (blockIdx.x == 0 && lane == 0) *A.t_out = __dadd_rn(*A.t_in, G.dt);   // T += dt, src/sim.cu:1811
+        if (blockIdx.x == 0 && lane == 0) *A.t_out = __dadd_rn(*A.t_in, A.rk2_stage ? __dmul_rn(0.5, G.dt) : G.dt);   // T += dt, src/sim.cu:1811 (RK2: T += 0.5 * dt per stage, :1789,1798)
         const int4 *mg = reinterpret_cast<const int4 *>(A.meta);
         auto load_meta = [&](int i, int4 &a, int4 &b, int4 &c) {
             if (i < n_my) { a = __ldg(mg + 3 * tile_of(i)); b = __ldg(mg + 3 * tile_of(i) + 1); c = __ldg(mg + 3 * tile_of(i) + 2); }
@@ -1576,6 +1593,8 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 if (A.write_acc == 2) {     // the reference's VERLET build: the previous acceleration is state, kept in the
                     acc = V3{A.acc[i_api], A.acc[X.nm + i_api], A.acc[2 * X.nm + i_api]};   // canonical array by this thread
                     verlet_tail<P>(G.dt, mass, force, pos, vel, acc);
+                } else if (A.rk2_stage) {   // the reference's RK2 build: two launches per step (out of line, rare)
+                    rk2_tail<P>(A.rk2_stage, G.dt, mass, force, ob, pos, vel, acc, (fl & F_LOCAL) ? X.rk2_bvel : nullptr, i_api, X.nm);
                 } else {
                     euler_tail<P>(G.dt, mass, force, pos, vel, acc);
                 }
@@ -1805,12 +1824,13 @@ int tiled_prepare(Engine *e) {
     return TB_OK;
 }
 
-int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
+int launch_tiled_step(Engine *e, bool use_ext, bool write_acc, int rk2_stage) {
     TiledState *S = e->tiled;
     if (!S || !S->supported) return fail(e, TB_ERR_INVALID, "tiled step requested without a tiled layout");
     TiledArgs A;
     A.n_tiles = (int32_t)S->n_active;
     A.write_acc = (e->flags & TB_INTEGRATOR_VERLET) ? 2 : (write_acc ? 1 : 0);
+    A.rk2_stage = rk2_stage;
     A.prof = nullptr; A.prof_lite = 0;
     if (getenv("TB_PROFILE")) {
         A.prof = g_prof_dev; g_prof_launches++;
@@ -1845,6 +1865,7 @@ int launch_tiled_step(Engine *e, bool use_ext, bool write_acc) {
     X.lc_ptr = e->any_local ? e->lc_ptr : nullptr;
     X.lc = e->lc;
     X.nm = e->nm;
+    X.rk2_bvel = (rk2_stage && e->any_local) ? e->rk2_bvel : nullptr;
     int rc;
     if (e->flags & TB_MATH_STRICT) rc = launch_f<Strict, 1>(e, S, A, X);
     else if (S->tpm == 4) rc = launch_f<Fast, 4>(e, S, A, X);
@@ -2184,6 +2205,7 @@ bool tiled_resident_ok(const Engine *e) {
     const int64_t max_tiles = getenv("TB_RESIDENT_MAX_TILES") ? atoll(getenv("TB_RESIDENT_MAX_TILES")) : std::max(8, e->sm_count);
     if (S->n_tiles < 1 || S->res_cluster < 1 || S->n_tiles > max_tiles || S->n_active != S->n_tiles) return false;
     if (e->any_ghost || e->any_magnet || S->n_exp_tab || S->halo_connected) return false;   // the magnet pass runs between steps
+    if (e->flags & TB_INTEGRATOR_RK2) return false;     // two launches per step (streaming or generic kernel)
     return true;
 }
 

@@ -989,7 +989,7 @@ void Simulation::start() {   // src/sim.cu:1547-1591
     std::cout << "Starting simulation with " << masses.size() << " masses and " << springs.size() << " springs." << std::endl;
 
     // no CUDA device -> TB_ERR_NO_DEVICE -> exception: there is no CPU path
-    const uint32_t eflags = TB_MATH_FAST | (integrator == 1 ? TB_INTEGRATOR_VERLET : 0u);
+    const uint32_t eflags = TB_MATH_FAST | (integrator == 1 ? TB_INTEGRATOR_VERLET : 0u) | (integrator == 2 ? TB_INTEGRATOR_RK2 : 0u);
     if (devices.size() > 1) {
         std::vector<int32_t> dv(devices.begin(), devices.end());
         engine_check(tb_create_partitioned((int32_t)dv.size(), dv.data(), eflags, &group), "tb_create_partitioned");
@@ -1064,7 +1064,8 @@ void Simulation::execute() {
         const double step_dt = dt_engine;     // the dt the engine was given at the last resume()/start()
         double t = T_enq;
         int64_t n = 0;
-        while (n < chunk && !(next_bp <= t)) { t += step_dt; n++; }
+        if (integrator == 2) { const double h = 0.5 * step_dt; while (n < chunk && !(next_bp <= t)) { t += h; t += h; n++; } }   // T += 0.5 * dt twice, src/sim.cu:1789,1798
+        else while (n < chunk && !(next_bp <= t)) { t += step_dt; n++; }
         if (dv_run_async(dev(), n, T_enq) != TB_OK) { fail_and_park("step failed: "); return; }
         enq += n;
         T_enq = t;
@@ -1110,7 +1111,8 @@ void Simulation::step(int n) {
     if (constraints_dirty) upload_constraints();
     engine_check(dv_run_async(dev(), n, T), "tb_run_async");
     double t = T;
-    for (int j = 0; j < n; j++) t += dt_engine;
+    if (integrator == 2) { const double h = 0.5 * dt_engine; for (int j = 0; j < n; j++) { t += h; t += h; } }
+    else for (int j = 0; j < n; j++) t += dt_engine;
     T = t;
     engine_check(dv_sync(dev()), "tb_sync");
 }
