@@ -428,6 +428,7 @@ def main():
     ap.add_argument("--distinct-params", action="store_true",
                     help="give every spring its own k (defeats the dictionary records: one record per spring is streamed)")
     ap.add_argument("--verlet", action="store_true", help="the reference's VERLET build option instead of its default Euler step")
+    ap.add_argument("--rk2", action="store_true", help="the reference's RK2 build option (repaired): two force evaluations per step")
     ap.add_argument("--no-hint", action="store_true", help="let the engine bisect positions instead of lattice bricks")
     ap.add_argument("--ref-threads", type=int, default=0, help="--impl reference: OpenMP threads (default: all host cores)")
     ap.add_argument("--no-extras", action="store_true",
@@ -474,6 +475,8 @@ def main():
     flags = (tb.MATH_STRICT if args.strict else tb.MATH_FAST) | (tb.KERNEL_CSR if args.csr else 0)
     if args.verlet:
         flags |= tb.INTEGRATOR_VERLET
+    if args.rk2:
+        flags |= tb.INTEGRATOR_RK2
     if args.workload == "c5":
         run_c5(args, tb, local_rank, flags)
         return
@@ -597,7 +600,7 @@ def main():
     # ---- N = 1 extras of the default line ------------------------------------------------------------------
     extras = {}
     default_line = (world == 1 and args.workload == "c2" and not args.no_extras and not args.distinct_params
-                    and not args.strict and not args.csr and not args.verlet)
+                    and not args.strict and not args.csr and not args.verlet and not args.rk2)
     if default_line:
         def timed(engine, nsteps, warm):
             t = 0.0
@@ -649,6 +652,7 @@ def main():
                                                  "as the builders make them (one k, rest lengths from the coordinates)"),
                            "sim_steps_per_bench_step": inner,
                            "math": "strict" if args.strict else "fast",
+                           "integrator": "rk2 (two force evaluations per step)" if args.rk2 else "verlet" if args.verlet else "euler",
                            "tiling": {k: info[k] for k in ("n_tiles", "threads_per_mass", "grid", "smem_bytes",
                                                            "ell_unique_tiles", "tiled_bytes_per_step", "dict_records")}, "per_rank": per_rank,
                            "l2": "no flush: one step streams %.0f MB per GPU from its tables and state (%.0f MB algorithmic), more than the 126 MB L2" % (info["tiled_bytes_per_step"] / 1e6 if info["kernel"] == 1 else alg_bytes / 1e6, alg_bytes / 1e6),
