@@ -320,6 +320,8 @@ static void multi_tests(int second) {
             for (Mass *q : l->masses) { q->vel = Vec(0.2 + 0.001 * (n % 7), 0, -0.3 + 0.002 * (n % 5)); n++; }
             sim->createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
             sim->start();
+            sim->pause(0.0);                                                   // a breakpoint before any step was timed
+            sim->resume();
             sim->pause(0.01);
             sim->getAll();
             l->masses[100]->pos = l->masses[100]->pos + Vec(0.01, 0, 0);      // edit across the API, both sides alike

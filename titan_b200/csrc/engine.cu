@@ -1142,6 +1142,7 @@ int tb_last_run_ms(tb_engine *e, double *ms) {
     E_CHECK(e);
     if (!ms) return TB_ERR_INVALID;
     float f = 0;
+    if (e->run_count == 0) { *ms = 0.0; return TB_OK; }   // nothing timed yet: the events were never recorded (cudaEventElapsedTime would fail)
     TB_CUDA(e, cudaEventSynchronize(e->ev1));
     TB_CUDA(e, cudaEventElapsedTime(&f, e->ev0, e->ev1));
     *ms = f;
