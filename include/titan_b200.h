@@ -273,6 +273,9 @@ typedef struct {
                                     record per spring (parameters too diverse, strict arithmetic or TB_DICT=0) */
     int32_t dict_split_k;        /* 1 = split dictionary: (rest, damping, omega) records shared, stiffness one value per
                                     record slot (systems whose k is edited spring by spring, BASELINE config C5) */
+    int32_t layout_uploads;      /* tiled kernel: times the tile tables were allocated and uploaded whole (first build, record-mode
+                                    change, an edit that outgrew the room left in them) */
+    int32_t layout_patches;      /* tiled kernel: topology edits written into the room left in the tables, nothing re-allocated */
 } tb_info;
 TB_API int tb_get_info(tb_engine *e, tb_info *info);
 /* headless position export, fp64 -> packed fp32 xyz (updateVertices, src/sim.cu:1944-1952); out is a

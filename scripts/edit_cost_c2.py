@@ -1,7 +1,8 @@
 #!/usr/bin/env python3
 """Cost of topology edits on BASELINE config C2 (100^3, 1 M masses, 12.7 M springs) through the C ABI: the first full build, then
 1,000 springs + 100 masses added (a local edit and a scattered one), 100 masses deleted, each followed by a zero-step run that
-brings the device layout up to date.  Run on the GPU box."""
+brings the device layout up to date.  The first edit re-allocates the per-spring / per-mass arrays and the tile tables with room
+to grow; the later ones fill that room in place (a scattered edit that touches a fifth of all tiles outgrows it).  Run on the GPU box."""
 import json, sys, time
 import numpy as np
 sys.path.insert(0, '.')
@@ -19,7 +20,7 @@ eng.run(200, 0.0)
 out = {"upload_s": t1 - t0, "first_layout_build_s": t2 - t1}
 rng = np.random.RandomState(5)
 t = 0.02
-for label, lo, hi in (("local", 0, 30000), ("scattered", 0, nm - 200)):
+for label, lo, hi in (("first_edit_local", 0, 30000), ("local", 200000, 230000), ("local_again", 400000, 430000), ("scattered", 0, nm - 200)):
     a = rng.randint(lo, hi, 1000).astype(np.int32)
     w0 = time.perf_counter()
     s0 = eng.add_springs(a, a + 1 + rng.randint(0, 100, 1000).astype(np.int32))

@@ -109,6 +109,59 @@ def test_deleted_masses_freeze_and_their_springs_vanish(flags, monkeypatch):
     assert same_bits(st["pos"][gone], o.pos[gone])           # frozen where they were
 
 
+@pytest.mark.parametrize("flags", [tb.MATH_STRICT, tb.MATH_FAST], ids=["strict", "fast"])
+def test_a_series_of_edits_goes_into_the_room_left_in_the_tables(flags, monkeypatch):
+    """Five edits in a row, the layout brought up to date after each (tb_run_async of zero steps): the first one re-allocates
+    the per-spring / per-mass arrays with room, the later ones fill that room -- arrays and tile tables alike -- and nothing is
+    re-uploaded.  The result equals a fresh upload of the final system bit for bit."""
+    monkeypatch.setenv("TB_TPM", "1")
+    monkeypatch.setenv("TB_RESIDENT", "0")
+    sc = scenes.c2_lattice(24)
+    rng = np.random.RandomState(11)
+    A = tb.Engine(0, flags)
+    scenes.upload(A, sc)
+    A.run(30, 0.0)
+    t = 0.0
+    for _ in range(30):
+        t += sc.dt
+    st = A.get_mass_state(first=0, count=sc.nm, fields=("pos", "vel"))
+    left, right, k, rest, damping = [sc.left], [sc.right], [sc.k], [sc.rest], [sc.damping]
+    pos, vel = [st["pos"]], [st["vel"]]
+    nm, ns = sc.nm, sc.ns
+    uploads = A.info()["layout_uploads"]
+    for edit in range(5):
+        n_s = 25
+        a = rng.randint(0, 400, n_s).astype(np.int32)              # local edits: a dozen tiles each
+        b = ((a + rng.randint(1, 60, n_s)) % sc.nm).astype(np.int32)
+        assert A.add_springs(a, b) == ns
+        kk, rr = np.full(n_s, 500.0 + 10 * edit), 0.05 + 0.01 * rng.rand(n_s)
+        A.set_spring_params(first=ns, count=n_s, k=kk, rest=rr, damping=np.zeros(n_s))
+        ns += n_s
+        n_m = 40
+        assert A.add_masses(n_m) == nm
+        anchor = rng.randint(0, 400, n_m)
+        pn = st["pos"][anchor] + np.array([0.0, 0.0, 0.04]) + 0.01 * rng.rand(n_m, 3)
+        A.set_mass_state(first=nm, count=n_m, pos=pn, vel=np.zeros((n_m, 3)), m=np.full(n_m, 0.1))
+        l2, r2 = anchor.astype(np.int32), (nm + np.arange(n_m)).astype(np.int32)
+        assert A.add_springs(l2, r2) == ns
+        A.set_spring_params(first=ns, count=n_m, k=np.full(n_m, 300.0), rest=np.full(n_m, 0.06), damping=np.zeros(n_m))
+        ns += n_m; nm += n_m
+        left += [a, l2]; right += [b, r2]; k += [kk, np.full(n_m, 300.0)]; rest += [rr, np.full(n_m, 0.06)]
+        damping += [np.zeros(n_s), np.zeros(n_m)]; pos.append(pn); vel.append(np.zeros((n_m, 3)))
+        A.run_async(0, t); A.sync()
+    assert A.info()["layout_uploads"] == uploads and A.info()["layout_patches"] == 5     # the tile tables were never re-uploaded
+    A.run(50, t)
+    got = A.get_mass_state(fields=("pos", "vel"))
+    assert A.info()["kernel"] == 1 and A.info()["nm"] == nm and A.info()["ns"] == ns
+    A.close()
+    B = fresh_engine(flags, sc, np.vstack(pos), np.vstack(vel), np.concatenate(left).astype(np.int32), np.concatenate(right).astype(np.int32),
+                     np.concatenate(k), np.concatenate(rest), np.concatenate(damping), nm)
+    B.run(50, t)
+    want = B.get_mass_state(fields=("pos", "vel"))
+    B.close()
+    assert same_bits(got["pos"], want["pos"]) and same_bits(got["vel"], want["vel"])
+
+
 def test_edit_cost_on_a_large_lattice():
     """60^3 lattice (216,000 masses, 2.7 M springs): 1,000 springs + 100 masses added in one region, then the layout brought up
     to date: only the tiles holding an endpoint are rebuilt (the full build runs on all host cores and is the yardstick)."""

@@ -51,7 +51,8 @@ class Info(C.Structure):
                 ("sm_count", C.c_int32), ("graph_steps", C.c_int32), ("threads_per_mass", C.c_int32),
                 ("grid", C.c_int32), ("smem_bytes", C.c_int32), ("ell_unique_tiles", C.c_int32),
                 ("tiled_bytes_per_step", C.c_int64), ("ns_removed", C.c_int64),
-                ("dict_records", C.c_int32), ("dict_split_k", C.c_int32)]
+                ("dict_records", C.c_int32), ("dict_split_k", C.c_int32),
+                ("layout_uploads", C.c_int32), ("layout_patches", C.c_int32)]
 
 
 class TitanError(RuntimeError):

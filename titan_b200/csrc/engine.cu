@@ -216,9 +216,10 @@ template <class T> static int down_scalar(Engine *e, T *dst_host, const T *src, 
 
 static void free_all(Engine *e) {
     auto F = [&](auto *&p, size_t bytes) { dev_free(e, (void *)p, bytes); p = nullptr; };
-    size_t m3 = (size_t)e->nm * 24, m1 = (size_t)e->nm * 8, s1 = (size_t)e->ns * 8, s4 = (size_t)e->ns * 4;
+    const size_t ma = (size_t)e->m_alloc(), sa = (size_t)e->s_alloc();
+    size_t m3 = ma * 24, m1 = ma * 8, s1 = sa * 8, s4 = sa * 4;
     F(e->pos[0], m3); F(e->pos[1], m3); F(e->vel[0], m3); F(e->vel[1], m3); F(e->acc, m3); F(e->ext, m3); F(e->rk2_bvel, m3);
-    F(e->m, m1); F(e->mflags, (size_t)e->nm); F(e->drag, (size_t)e->nm * 4);
+    F(e->m, m1); F(e->mflags, ma); F(e->drag, ma * 4); F(e->m_scratch, m3);
     F(e->left, s4); F(e->right, s4); F(e->type, s4);
     F(e->k, s1); F(e->rest, s1); F(e->damping, s1); F(e->omega, s1); F(e->l_max, s1); F(e->l_min, s1); F(e->rate, s1);
     F(e->row_ptr, (size_t)e->row_ptr_cap * 4); F(e->adj, (size_t)e->adj_cap * 4); e->row_ptr_cap = e->adj_cap = 0;
@@ -226,7 +227,8 @@ static void free_all(Engine *e) {
     e->patch_needs_layout = e->removed_unpatched = e->compact_requested = false;
     F(e->export_f32, (size_t)e->nm * 12);
     F(e->export_idx, (size_t)e->ns * 8);
-    F(e->removed_dev, (size_t)e->ns);
+    F(e->removed_dev, sa);
+    e->cap_s = e->cap_m = 0;
     F(e->act_idx, (size_t)e->n_act * 4); e->n_act = 0; e->act_dirty = true; e->h_act.clear();
     magnet_free(e);
     e->h_removed.clear(); e->n_removed = 0;
@@ -239,7 +241,7 @@ static void free_all(Engine *e) {
 
 template <class T> static int ensure_spring_array(Engine *e, T **p, T init) {
     if (*p) return TB_OK;
-    TB_TRY(dev_alloc(e, p, (size_t)e->ns));
+    TB_TRY(dev_alloc(e, p, (size_t)e->s_alloc()));
     return fill<T>(e, *p, init, e->ns);
 }
 
@@ -409,7 +411,7 @@ int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
     if (extern_force) {
         bool nz = any_nonzero(extern_force, count * 3);
         if (nz && !e->ext) {
-            TB_TRY(dev_alloc(e, &e->ext, (size_t)e->nm * 3));
+            TB_TRY(dev_alloc(e, &e->ext, (size_t)e->m_alloc() * 3));
             TB_CUDA(e, cudaMemsetAsync(e->ext, 0, (size_t)e->nm * 24, e->stream));
         }
         if (e->ext) TB_TRY(up_vec3(e, e->ext, extern_force, idx, first, count));
@@ -419,7 +421,7 @@ int tb_set_mass_state(tb_engine *e, int64_t first, int64_t count, const int32_t 
         bool nz = false;
         for (int64_t j = 0; j < count; j++) nz |= drag[j] != 0;
         if (nz && !e->drag) {
-            TB_TRY(dev_alloc(e, &e->drag, (size_t)e->nm));
+            TB_TRY(dev_alloc(e, &e->drag, (size_t)e->m_alloc()));
             TB_CUDA(e, cudaMemsetAsync(e->drag, 0, (size_t)e->nm * 4, e->stream));
         }
         if (e->drag) TB_TRY(up_scalar<int32_t>(e, e->drag, drag, idx, first, count));
@@ -606,7 +608,7 @@ int tb_remove_springs(tb_engine *e, int64_t n, const int32_t *idx) {
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
     if (e->h_removed.empty()) {
         e->h_removed.assign((size_t)e->ns, 0);
-        TB_TRY(dev_alloc(e, &e->removed_dev, (size_t)e->ns));
+        TB_TRY(dev_alloc(e, &e->removed_dev, (size_t)e->s_alloc()));
         TB_CUDA(e, cudaMemsetAsync(e->removed_dev, 0, (size_t)e->ns, e->stream));
     }
     std::vector<uint8_t> ones((size_t)n, 1);
@@ -647,23 +649,39 @@ template <class T> __global__ void regrow_kernel(T *dst, const T *src, int64_t n
     const int64_t c = q / n_new, i = q % n_new;
     dst[q] = i < n_old ? src[c * n_old + i] : value;
 }
-template <class T> static int regrow(Engine *e, T **p, int64_t n_old, int64_t n_new, int planes, T value) {
+// a_old / a_new: elements allocated per plane before / after.  Enough room: planes == 1 -> the new entries are filled in place;
+// planes == 3 -> the planes move apart inside a buffer of the same size, through *scratch, which takes over as the array (the old
+// buffer becomes the scratch of the next array).  Not enough room: a new buffer of a_new elements per plane.
+template <class T> static int regrow(Engine *e, T **p, int64_t n_old, int64_t n_new, int planes, T value, int64_t a_old, int64_t a_new, T **scratch = nullptr) {
     if (!*p) return TB_OK;             // optional array that was never allocated: stays that way
+    if (a_new == a_old && planes == 1) {
+        fill_kernel<T><<<blocks_for(n_new - n_old), 256, 0, e->stream>>>(*p + n_old, value, n_new - n_old);
+        TB_CUDA(e, cudaGetLastError());
+        return TB_OK;
+    }
+    if (a_new == a_old && scratch && *scratch) {
+        regrow_kernel<T><<<blocks_for(n_new * planes), 256, 0, e->stream>>>(*scratch, *p, n_old, n_new, planes, value);
+        TB_CUDA(e, cudaGetLastError());
+        std::swap(*p, *scratch);
+        return TB_OK;
+    }
     T *bigger = nullptr;
-    TB_TRY(dev_alloc(e, &bigger, (size_t)(n_new * planes)));
+    TB_TRY(dev_alloc(e, &bigger, (size_t)(a_new * planes)));
     regrow_kernel<T><<<blocks_for(n_new * planes), 256, 0, e->stream>>>(bigger, *p, n_old, n_new, planes, value);
     TB_CUDA(e, cudaGetLastError());
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
-    dev_free(e, (void *)*p, (size_t)(n_old * planes) * sizeof(T));
+    dev_free(e, (void *)*p, (size_t)(a_old * planes) * sizeof(T));
     *p = bigger;
     return TB_OK;
 }
+static int64_t with_room(int64_t n) { return n + n / 8 + 4096; }
 }  // namespace tb
 
 extern "C" {
 
 int tb_add_masses(tb_engine *e, int64_t n) {
     E_CHECK(e);
+    TimeScope ts("tb_add_masses");
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_add_masses before tb_set_topology");
     if (n < 0 || e->nm + n >= (int64_t)1 << 31) return fail(e, TB_ERR_INVALID, "tb_add_masses: bad count");
     if (n == 0) return TB_OK;
@@ -672,12 +690,20 @@ int tb_add_masses(tb_engine *e, int64_t n) {
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
     if (e->canon_stale) TB_TRY(tiled_to_canonical(e));     // the canonical arrays are about to move
     const int64_t n0 = e->nm, n1 = e->nm + n;
-    for (int p = 0; p < 2; p++) { TB_TRY(regrow<double>(e, &e->pos[p], n0, n1, 3, 0.0)); TB_TRY(regrow<double>(e, &e->vel[p], n0, n1, 3, 0.0)); }
-    TB_TRY(regrow<double>(e, &e->acc, n0, n1, 3, 0.0));
-    TB_TRY(regrow<double>(e, &e->ext, n0, n1, 3, 0.0));
-    TB_TRY(regrow<double>(e, &e->m, n0, n1, 1, 0.1));                    // Mass default, include/Titan/mass.h:18
-    TB_TRY(regrow<uint8_t>(e, &e->mflags, n0, n1, 1, (uint8_t)F_VALID));
-    TB_TRY(regrow<int32_t>(e, &e->drag, n0, n1, 1, 0));
+    const int64_t a0 = e->m_alloc(), a1 = n1 <= a0 ? a0 : with_room(n1);
+    if (a1 != a0) { dev_free(e, (void *)e->m_scratch, (size_t)a0 * 24); e->m_scratch = nullptr; }
+    else if (!e->m_scratch) TB_TRY(dev_alloc(e, &e->m_scratch, (size_t)a0 * 3));
+    for (int p = 0; p < 2; p++) {
+        TB_TRY(regrow<double>(e, &e->pos[p], n0, n1, 3, 0.0, a0, a1, &e->m_scratch));
+        TB_TRY(regrow<double>(e, &e->vel[p], n0, n1, 3, 0.0, a0, a1, &e->m_scratch));
+    }
+    TB_TRY(regrow<double>(e, &e->acc, n0, n1, 3, 0.0, a0, a1, &e->m_scratch));
+    TB_TRY(regrow<double>(e, &e->ext, n0, n1, 3, 0.0, a0, a1, &e->m_scratch));
+    if (e->rk2_bvel) TB_TRY(regrow<double>(e, &e->rk2_bvel, n0, n1, 3, 0.0, a0, a1, &e->m_scratch));
+    TB_TRY(regrow<double>(e, &e->m, n0, n1, 1, 0.1, a0, a1));                    // Mass default, include/Titan/mass.h:18
+    TB_TRY(regrow<uint8_t>(e, &e->mflags, n0, n1, 1, (uint8_t)F_VALID, a0, a1));
+    TB_TRY(regrow<int32_t>(e, &e->drag, n0, n1, 1, 0, a0, a1));
+    e->cap_m = a1;
     dev_free(e, (void *)e->export_f32, (size_t)n0 * 12); e->export_f32 = nullptr;
     e->h_flags.resize((size_t)n1, F_VALID);
     e->h_T0.resize((size_t)n1, 0.0);
@@ -697,6 +723,7 @@ int tb_add_masses(tb_engine *e, int64_t n) {
 
 int tb_add_springs(tb_engine *e, int64_t n, const int32_t *left, const int32_t *right) {
     E_CHECK(e);
+    TimeScope ts("tb_add_springs");
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_add_springs before tb_set_topology");
     if (n < 0 || (n > 0 && (!left || !right)) || e->ns + n >= (int64_t)1 << 30) return fail(e, TB_ERR_INVALID, "tb_add_springs: bad arguments");
     if (n == 0) return TB_OK;
@@ -705,20 +732,22 @@ int tb_add_springs(tb_engine *e, int64_t n, const int32_t *left, const int32_t *
     if (tiled_halo_connected(e)) return fail(e, TB_ERR_UNSUPPORTED, "tb_add_springs: not on a connected engine of a partition (re-upload the topology)");
     TB_CUDA(e, cudaStreamSynchronize(e->stream));
     const int64_t n0 = e->ns, n1 = e->ns + n;
+    const int64_t a0 = e->s_alloc(), a1 = (n0 > 0 && n1 <= a0) ? a0 : with_room(n1);
     if (n0 == 0) {       // a system that had no spring at all: the arrays were allocated with one placeholder element
         dev_free(e, (void *)e->left, 4); dev_free(e, (void *)e->right, 4); dev_free(e, (void *)e->k, 8); dev_free(e, (void *)e->rest, 8);
-        TB_TRY(dev_alloc(e, &e->left, (size_t)n1)); TB_TRY(dev_alloc(e, &e->right, (size_t)n1)); TB_TRY(dev_alloc(e, &e->k, (size_t)n1)); TB_TRY(dev_alloc(e, &e->rest, (size_t)n1));
+        TB_TRY(dev_alloc(e, &e->left, (size_t)a1)); TB_TRY(dev_alloc(e, &e->right, (size_t)a1)); TB_TRY(dev_alloc(e, &e->k, (size_t)a1)); TB_TRY(dev_alloc(e, &e->rest, (size_t)a1));
         TB_TRY(fill<double>(e, e->k, 10000.0, n1)); TB_TRY(fill<double>(e, e->rest, 1.0, n1));
     } else {
-        TB_TRY(regrow<int32_t>(e, &e->left, n0, n1, 1, -1)); TB_TRY(regrow<int32_t>(e, &e->right, n0, n1, 1, -1));
-        TB_TRY(regrow<double>(e, &e->k, n0, n1, 1, 10000.0));               // Spring default, include/Titan/spring.h:25
-        TB_TRY(regrow<double>(e, &e->rest, n0, n1, 1, 1.0));
+        TB_TRY(regrow<int32_t>(e, &e->left, n0, n1, 1, -1, a0, a1)); TB_TRY(regrow<int32_t>(e, &e->right, n0, n1, 1, -1, a0, a1));
+        TB_TRY(regrow<double>(e, &e->k, n0, n1, 1, 10000.0, a0, a1));               // Spring default, include/Titan/spring.h:25
+        TB_TRY(regrow<double>(e, &e->rest, n0, n1, 1, 1.0, a0, a1));
     }
-    TB_TRY(regrow<int32_t>(e, &e->type, n0, n1, 1, 0));
-    TB_TRY(regrow<double>(e, &e->damping, n0, n1, 1, 0.0)); TB_TRY(regrow<double>(e, &e->omega, n0, n1, 1, 0.0));
-    TB_TRY(regrow<double>(e, &e->l_max, n0, n1, 1, 0.0)); TB_TRY(regrow<double>(e, &e->l_min, n0, n1, 1, 0.0));
-    TB_TRY(regrow<double>(e, &e->rate, n0, n1, 1, 0.0));
-    TB_TRY(regrow<uint8_t>(e, &e->removed_dev, n0, n1, 1, (uint8_t)0));
+    TB_TRY(regrow<int32_t>(e, &e->type, n0, n1, 1, 0, a0, a1));
+    TB_TRY(regrow<double>(e, &e->damping, n0, n1, 1, 0.0, a0, a1)); TB_TRY(regrow<double>(e, &e->omega, n0, n1, 1, 0.0, a0, a1));
+    TB_TRY(regrow<double>(e, &e->l_max, n0, n1, 1, 0.0, a0, a1)); TB_TRY(regrow<double>(e, &e->l_min, n0, n1, 1, 0.0, a0, a1));
+    TB_TRY(regrow<double>(e, &e->rate, n0, n1, 1, 0.0, a0, a1));
+    TB_TRY(regrow<uint8_t>(e, &e->removed_dev, n0, n1, 1, (uint8_t)0, a0, a1));
+    e->cap_s = a1;
     dev_free(e, (void *)e->export_idx, (size_t)n0 * 8); e->export_idx = nullptr;
     TB_CUDA(e, cudaMemcpy(e->left + n0, left, (size_t)n * 4, cudaMemcpyHostToDevice));
     TB_CUDA(e, cudaMemcpy(e->right + n0, right, (size_t)n * 4, cudaMemcpyHostToDevice));
@@ -990,7 +1019,7 @@ int tb_run_async(tb_engine *e, int64_t nsteps, double t0) {
     E_CHECK(e);
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "No masses have been added. Please add masses before starting the simulation.");  // src/sim.cu:1552-1554
     if (nsteps < 0) return fail(e, TB_ERR_INVALID, "tb_run_async: negative step count");
-    if ((e->flags & TB_INTEGRATOR_RK2) && e->any_local && !e->rk2_bvel) TB_TRY(dev_alloc(e, &e->rk2_bvel, (size_t)e->nm * 3));
+    if ((e->flags & TB_INTEGRATOR_RK2) && e->any_local && !e->rk2_bvel) TB_TRY(dev_alloc(e, &e->rk2_bvel, (size_t)e->m_alloc() * 3));
     if (e->any_actuated) {
         if (!e->l_max || !e->l_min || !e->rate) return fail(e, TB_ERR_INVALID, "actuated springs need l_max, l_min and rate");
         TB_TRY(prepare_actuated(e));   // before tiled_prepare: the tile builder records where their rest lengths live

@@ -12,7 +12,10 @@
 // (include/Titan/mass.h:89-126, spring.h:77-97, src/sim.cu:940-1025).
 #pragma once
 
+#include <chrono>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -92,6 +95,13 @@ struct Engine {
     // the CSR covers masses [0, csr_nm) and springs [0, csr_ns); incidences of springs added since (tb_add_springs) wait in
     // extra_adj (mass -> 2*spring+side, ascending) until ensure_csr folds them in
     int64_t csr_nm = 0, csr_ns = 0, row_ptr_cap = 0, adj_cap = 0;
+    // elements allocated per per-spring array / per plane of a per-mass array (0 = exactly ns / nm): tb_add_springs and
+    // tb_add_masses leave room, so that the next edit re-allocates nothing.  [3][nm] arrays keep their plane stride nm inside
+    // a buffer of 3 * cap_m elements; a changed nm re-strides them through m_scratch (buffers swap roles, nothing is allocated)
+    int64_t cap_s = 0, cap_m = 0;
+    double *m_scratch = nullptr;
+    int64_t s_alloc() const { return cap_s ? cap_s : ns; }
+    int64_t m_alloc() const { return cap_m ? cap_m : nm; }
     std::vector<int32_t> patch_masses, patch_springs;        // added / removed since the tiled layout was last brought up to date (TS_PATCH)
     bool patch_needs_layout = false;      // ... and some of them are additions: if the tiles cannot be patched, everything is rebuilt
     bool compact_requested = false;       // tb_compact: the next full build leaves the incidence words of removed springs out
@@ -134,6 +144,14 @@ int fail(Engine *e, int status, const char *fmt, ...);
             return tb::fail((e), TB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_err), \
                             __FILE__, __LINE__);                                                 \
     } while (0)
+
+// TB_TIMING=1: wall time of the host-side phases (edits, layout builds), one line each on stderr
+struct TimeScope {
+    const char *what; std::chrono::steady_clock::time_point t0; bool on;
+    explicit TimeScope(const char *w) : what(w), on(timing_on()) { if (on) t0 = std::chrono::steady_clock::now(); }
+    ~TimeScope() { if (on) fprintf(stderr, "[tb timing] %s: %.2f ms\n", what, std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count()); }
+    static bool timing_on() { static const bool v = getenv("TB_TIMING") != nullptr; return v; }
+};
 
 #ifndef TB_TRY
 #define TB_TRY(x) do { int _rc = (x); if (_rc != TB_OK) return _rc; } while (0)

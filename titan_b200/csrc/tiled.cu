@@ -131,8 +131,15 @@ struct HostTables {
     size_t blob_total = 0;
 };
 
+// elements allocated for the device tables (>= what is in use: the ends are room for in-place edits)
+struct TableCaps { int64_t tiles = 0, st_tiles = 0, halo = 0, ell = 0, rec = 0, rec_map = 0, krec = 0, cls = 0; size_t blob = 0; };
+
 struct TiledState {
     HostTables H;
+    TableCaps cap;
+    int64_t n_halo_up = 0, n_ell_up = 0, n_rec_map_up = 0;   // host entries already on the device (halo / ell / rec_map carry a tail)
+    uint32_t ell_pad = 0;                 // the padding word the free end of the ELL table is filled with
+    int n_uploads = 0, n_patches = 0;     // whole uploads of the tables / edits written into their free ends
     int build_mode = 1;                   // record mode of the last build (1 full dictionary, 2 split, 0 plain)
     int64_t n_tiles = 0, n_slots = 0, n_rec = 0, n_ell = 0, n_halo = 0;
     size_t blob_bytes = 0;
@@ -327,21 +334,25 @@ template <class T> static int upload_vec(Engine *e, T **dst, const std::vector<T
 template <class T> static void release(Engine *e, T *&p, size_t count) { dev_free(e, (void *)p, count * sizeof(T)); p = nullptr; }
 
 static void free_structure(Engine *e, TiledState *S, bool keep_state = false) {
-    if (!keep_state) for (int p = 0; p < 2; p++) release(e, S->st[p], (size_t)S->n_tiles * STATE_BLOCK);
-    release(e, S->class_rep, (size_t)S->n_class_rep); S->n_class_rep = 0; release(e, S->rec_map, (size_t)S->n_rec_map);
+    TableCaps &C = S->cap;
+    if (!keep_state) { for (int p = 0; p < 2; p++) release(e, S->st[p], (size_t)C.st_tiles * STATE_BLOCK); C.st_tiles = 0; }
+    release(e, S->class_rep, (size_t)C.cls); S->n_class_rep = 0; release(e, S->rec_map, (size_t)C.rec_map);
     S->n_rec_map = 0; S->dict = false; S->dict_split = false;
-    release(e, S->krec_spring, (size_t)S->n_krec); S->n_krec = 0;
+    release(e, S->krec_spring, (size_t)C.krec); S->n_krec = 0;
     if (S->act_tile_off) { cudaFree(S->act_tile_off); S->act_tile_off = nullptr; }
     if (S->act_rec) { cudaFree(S->act_rec); S->act_rec = nullptr; }
     S->n_act_rec = 0;
     if (S->krec_off) { cudaFree(S->krec_off); S->krec_off = nullptr; }
-    release(e, S->blob, S->blob_bytes);
-    release(e, S->slot_to_api, (size_t)S->n_slots); release(e, S->halo, (size_t)S->n_halo);
+    release(e, S->blob, C.blob);
+    release(e, S->slot_to_api, (size_t)C.tiles * TM); release(e, S->halo, (size_t)C.halo);
     release(e, S->api_to_slot, S->n_api); S->n_api = 0;
-    release(e, S->rec_spring, (size_t)S->n_rec); release(e, S->ell, (size_t)S->n_ell);
+    release(e, S->rec_spring, (size_t)C.rec); release(e, S->ell, (size_t)C.ell);
     if (S->meta) { cudaFree(S->meta); S->meta = nullptr; }
     S->n_tiles = S->n_slots = S->n_rec = S->n_ell = S->n_halo = 0;
+    S->n_halo_up = S->n_ell_up = S->n_rec_map_up = 0;
     S->blob_bytes = 0;
+    const int64_t st_tiles = C.st_tiles;
+    C = TableCaps(); C.st_tiles = st_tiles;
 }
 
 // n_rec records (k | rest | damping | omega arrays of n_rec slots each, rounded up to even), then the byte map of the
@@ -449,15 +460,51 @@ struct BuildCfg {
     const std::vector<int32_t> *class_of = nullptr, *rep_of = nullptr;
 };
 
+// int32 key (>= 0) -> int32 value, open addressing; clear() undoes only what was inserted (the tables are per-thread and reused)
+struct SmallMap {
+    std::vector<int32_t> key, val;
+    std::vector<uint32_t> used;
+    uint32_t mask;
+    explicit SmallMap(int bits) : key((size_t)1 << bits, -1), val((size_t)1 << bits, 0), mask((1u << bits) - 1) {}
+    void clear() { for (uint32_t q : used) key[q] = -1; used.clear(); }
+    int32_t *find(int32_t k) {
+        for (uint32_t q = ((uint32_t)k * 2654435761u >> 7) & mask;; q = (q + 1) & mask) {
+            if (key[q] == k) return &val[q];
+            if (key[q] < 0) return nullptr;
+        }
+    }
+    int32_t *insert(int32_t k, int32_t v) {            // k must not be present; the tables are sized for twice a tile's worst case
+        uint32_t q = ((uint32_t)k * 2654435761u >> 7) & mask;
+        while (key[q] >= 0) q = (q + 1) & mask;
+        key[q] = k; val[q] = v; used.push_back(q);
+        return &val[q];
+    }
+};
+struct Half { int32_t s, o, os; uint8_t side; };      // spring, the other endpoint, that mass's slot, which end this mass is
+struct TileScratch {
+    std::vector<Half> rows = std::vector<Half>((size_t)TM * MAX_DEG);
+    int cnt[TM];
+    SmallMap halo_local{13}, rec_local{13}, cls_local{10};   // <= TM * MAX_DEG = 4096 foreign masses / springs, <= 256 classes
+    std::vector<int32_t> slot_spring;
+};
+
 static void build_tile(const Engine *e, const TiledState *S, int64_t T, const BuildCfg &cfg, TileOut &o) {
-    struct Half { int32_t s; int32_t o; uint8_t side; };
-    std::vector<Half> rows[TM];
-    std::vector<Half> aligned;
+    static thread_local TileScratch *scratch = nullptr;
+    if (!scratch) scratch = new TileScratch();             // lives as long as its thread
+    TileScratch &W = *scratch;
+    Half *const rows = W.rows.data();
+    int *const cnt = W.cnt;
+    auto row = [&](int t) { return rows + (size_t)t * MAX_DEG; };
+    Half aligned[MAX_DEG];
     const std::vector<int32_t> &rp = e->h_row_ptr, &adj = e->h_adj;
+    const bool any_removed = cfg.drop_removed && !e->h_removed.empty();
     int deg = 0;
+    bool overflow = false;
     for (int t = 0; t < TM; t++) {
+        cnt[t] = 0;
         int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
         if (i < 0 || !(e->h_flags[(size_t)i] & F_VALID) || (e->h_flags[(size_t)i] & F_GHOST)) continue;   // ghosts are updated by their owner
+        Half *r = row(t);
         auto take = [&](int32_t a) {
             const int32_t s = a >> 1;
             const uint8_t side = (uint8_t)(a & 1);
@@ -466,18 +513,19 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
             // a tombstone (tb_remove_springs) keeps its incidence word (it reads k = 0) unless this build compacts: dropping the
             // words of scattered removals makes every tile's block unique, and the content dedupe that keeps the blocks of a
             // lattice L2-resident is worth far more than 0.1 % of dead words (C5: 168 -> 151 G spring-steps/s when dropped)
-            if (cfg.drop_removed && !e->h_removed.empty() && e->h_removed[(size_t)s]) return;
-            rows[t].push_back({s, other, side});
+            if (any_removed && e->h_removed[(size_t)s]) return;
+            if (cnt[t] == MAX_DEG) { overflow = true; return; }
+            r[cnt[t]++] = Half{s, other, S->h_api_to_slot[(size_t)other], side};
         };
         if ((int64_t)i < e->csr_nm) for (int32_t q = rp[(size_t)i]; q < rp[(size_t)i + 1]; q++) take(adj[(size_t)q]);
         if (!e->extra_adj.empty()) {        // springs added since the CSR was built: higher indices, so they come last
             auto it = e->extra_adj.find(i);
             if (it != e->extra_adj.end()) for (int32_t a : it->second) take(a);
         }
-        deg = std::max(deg, (int)rows[t].size());
+        deg = std::max(deg, cnt[t]);
     }
-    o.deg = deg;
-    if (deg > MAX_DEG) { o.why_not = "a mass has more incident springs than the ELL format holds"; return; }
+    o.deg = overflow ? MAX_DEG + 1 : deg;
+    if (overflow) { o.why_not = "a mass has more incident springs than the ELL format holds"; return; }
     // Row alignment: a mass with fewer springs than the tile's fullest one (a lattice surface) gets HOLES so that its
     // springs sit in the rows of the same springs of a full mass -- "same" = same offset in API index, which on a
     // lattice is the direction.  Order per mass is unchanged (ascending spring index), only padding moves; every row
@@ -485,24 +533,26 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
     // A mass whose offsets are no subsequence of the template's keeps its compact rows.
     if (deg > 1 && cfg.align_rows) {
         int tmpl = -1;
-        for (int t = 0; t < TM && tmpl < 0; t++) if ((int)rows[t].size() == deg) tmpl = t;
+        for (int t = 0; t < TM && tmpl < 0; t++) if (cnt[t] == deg) tmpl = t;
         const int32_t i_tmpl = S->h_slot_to_api[(size_t)(T * TM + tmpl)];
+        const Half *rt = row(tmpl);
         for (int t = 0; t < TM; t++) {
-            const int d = (int)rows[t].size();
+            const int d = cnt[t];
             if (d == 0 || d == deg) continue;
             const int32_t i = S->h_slot_to_api[(size_t)(T * TM + t)];
-            aligned.assign((size_t)deg, Half{-1, 0, 0});
+            Half *r = row(t);
+            for (int q = 0; q < deg; q++) aligned[q] = Half{-1, 0, 0, 0};
             int p = 0;
             bool ok = true;
             for (int q = 0; q < d && ok; q++) {
-                const int32_t key = rows[t][(size_t)q].o - i;
-                while (p < deg && rows[tmpl][(size_t)p].o - i_tmpl != key) p++;
-                if (p == deg) ok = false; else aligned[(size_t)p++] = rows[t][(size_t)q];
+                const int32_t key = r[q].o - i;
+                while (p < deg && rt[p].o - i_tmpl != key) p++;
+                if (p == deg) ok = false; else aligned[p++] = r[q];
             }
-            if (ok) rows[t] = aligned;
+            if (ok) { for (int q = 0; q < deg; q++) r[q] = aligned[q]; cnt[t] = deg; }
         }
     }
-    auto has = [&](int t, int j) { return j < (int)rows[t].size() && rows[t][(size_t)j].s >= 0; };
+    auto has = [&](int t, int j) { return j < cnt[t] && row(t)[j].s >= 0; };
     o.block.assign((size_t)ell_chunks(deg) * ELL_CHUNK * TM, 0u);   // zero rows pad the last chunk
     // Halo slots are chosen so that the 16 lanes of a half-warp reading row j hit 16 different shared-memory
     // bank pairs (an LDS.64 conflict costs a replay).  Own neighbours sit at local index t + c_j (c_j = the
@@ -512,13 +562,14 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
     // free slot whose residue no lane of the half-warp uses.  Unused slots (holes) are not gathered.
     std::vector<int32_t> &th = o.th;
     th.clear();
-    std::unordered_map<int32_t, int32_t> halo_local;      // foreign mass -> its halo slot in this tile
+    SmallMap &halo_local = W.halo_local;                  // foreign mass -> its halo slot in this tile
+    halo_local.clear();
     int cjs[MAX_DEG];
     for (int j = 0; j < deg; j++) {
         int votes[16] = {0}, cj = -1, best = 0;
         for (int t = 0; t < TM; t++) {
             if (!has(t, j)) continue;
-            int32_t oslot = S->h_api_to_slot[(size_t)rows[t][(size_t)j].o];
+            const int32_t oslot = row(t)[j].os;
             if (oslot / TM == T) votes[((oslot % TM) - t) & 15]++;
         }
         for (int r = 0; r < 16; r++) if (votes[r] > best) { best = votes[r]; cj = r; }
@@ -527,16 +578,15 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
             uint32_t used = 0;
             for (int t = hw * 16; t < hw * 16 + 16; t++) {
                 if (!has(t, j)) continue;
-                const Half &h = rows[t][(size_t)j];
-                int32_t oslot = S->h_api_to_slot[(size_t)h.o];
-                if (oslot / TM == T) used |= 1u << (oslot % 16);
-                else { auto it = halo_local.find(h.o); if (it != halo_local.end()) used |= 1u << (it->second % 16); }
+                const Half &h = row(t)[j];
+                if (h.os / TM == T) used |= 1u << (h.os % 16);
+                else if (const int32_t *v = halo_local.find(h.o)) used |= 1u << (*v % 16);
             }
             for (int t = hw * 16; t < hw * 16 + 16; t++) {
                 if (!has(t, j)) continue;
-                const Half &h = rows[t][(size_t)j];
-                int32_t oslot = S->h_api_to_slot[(size_t)h.o];
-                if (oslot / TM == T || halo_local.count(h.o)) continue;
+                const Half &h = row(t)[j];
+                const int32_t oslot = h.os;
+                if (oslot / TM == T || halo_local.find(h.o)) continue;
                 int pick = -1;
                 if (cj >= 0) {
                     // preferred residue first, but never at the price of a halo list that no longer fits the
@@ -553,7 +603,7 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
                 }
                 if (pick >= (int)th.size()) th.resize((size_t)pick + 1, -1);
                 th[(size_t)pick] = (int32_t)((int64_t)(oslot / TM) * STATE_BLOCK + oslot % TM);
-                halo_local[h.o] = pick;
+                halo_local.insert(h.o, pick);
                 used |= 1u << (pick % 16);
             }
         }
@@ -563,19 +613,22 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
         const int j = (int)(w / TM), t = (int)(w % TM);
         o.block[w] = (PAD_NB + (uint32_t)((t + ((j < deg && cjs[j] >= 0) ? cjs[j] : 0)) & 15)) << ELL_NB_SHIFT;
     }
-    std::vector<int32_t> slot_spring(1, -1);              // record slot -> spring; slot 0: k = 0, read by padding words
-    std::unordered_map<int32_t, int32_t> rec_local;       // spring -> its record slot in this tile
+    std::vector<int32_t> &slot_spring = W.slot_spring;    // record slot -> spring; slot 0: k = 0, read by padding words
+    slot_spring.assign(1, -1);
+    SmallMap &rec_local = W.rec_local;                    // spring -> its record slot in this tile
+    rec_local.clear();
+    const bool typed = !e->h_type.empty();
     for (int j = 0; j < deg; j++) for (int t = 0; t < TM; t++) {   // j-major walk: record slots of one row are consecutive
         if (!has(t, j)) continue;
-        const Half &h = rows[t][(size_t)j];
-        int32_t oslot = S->h_api_to_slot[(size_t)h.o];
-        const int nb = (oslot / TM == T) ? oslot % TM : TM + halo_local[h.o];
-        auto it = rec_local.find(h.s);
-        if (it == rec_local.end()) { it = rec_local.emplace(h.s, (int32_t)slot_spring.size()).first; slot_spring.push_back(h.s); }
-        const int rec = it->second;
+        const Half &h = row(t)[j];
+        const int32_t oslot = h.os;
+        const int nb = (oslot / TM == T) ? oslot % TM : TM + *halo_local.find(h.o);
+        int32_t *it = rec_local.find(h.s);
+        if (!it) { it = rec_local.insert(h.s, (int32_t)slot_spring.size()); slot_spring.push_back(h.s); }
+        const int rec = *it;
         if (nb >= MAX_LOCAL - N_DUMMY || rec >= MAX_REC) { o.why_not = "a tile reaches too many foreign masses or springs"; return; }
         uint32_t ty = 0;
-        if (!e->h_type.empty()) { uint8_t x = e->h_type[(size_t)h.s]; ty = (x == 2) ? 1u : (x == 3) ? 2u : 0u; }
+        if (typed) { uint8_t x = e->h_type[(size_t)h.s]; ty = (x == 2) ? 1u : (x == 3) ? 2u : 0u; }
         o.block[(size_t)j * TM + (size_t)t] =
             ((uint32_t)nb << ELL_NB_SHIFT) | ((uint32_t)rec << ELL_REC_SHIFT) | (h.side ? ELL_SIDE : 0u) | (ty << ELL_TYPE_SHIFT) | ELL_VALID;
     }
@@ -590,18 +643,20 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
         return;
     }
     // dictionary modes: record slots -> the tile's distinct records; slot 0 (padding) -> record 0 (k = 0)
-    std::unordered_map<int32_t, int32_t> cls_local;       // parameter class -> its record in this tile
+    SmallMap &cls_local = W.cls_local;                    // parameter class -> its record in this tile
+    cls_local.clear();
     o.recs.assign(1, -1);
     o.map.assign(1, 0);
+    o.map.reserve((size_t)n_rec);
     for (int r = 1; r < n_rec; r++) {
         const int32_t sp = slot_spring[(size_t)r], c = (*cfg.class_of)[(size_t)sp];
-        auto it = cls_local.find(c);
-        if (it == cls_local.end()) {
+        int32_t *it = cls_local.find(c);
+        if (!it) {
             if ((int)o.recs.size() >= DICT_MAX_TILE) { o.dict_overflow = true; return; }
-            it = cls_local.emplace(c, (int32_t)o.recs.size()).first;
+            it = cls_local.insert(c, (int32_t)o.recs.size());
             o.recs.push_back((*cfg.rep_of)[(size_t)sp]);
         }
-        o.map.push_back((uint8_t)it->second);
+        o.map.push_back((uint8_t)*it);
     }
     o.n_final = (int)o.recs.size();
     for (int r = 1; r < o.n_final && actuated; r++)
@@ -679,7 +734,7 @@ static const char *merge_tile(Engine *e, TiledState *S, int64_t T, TileOut &o, b
 
 // maxima, shared-memory plan, cluster grouping, then every table to the device.  The state buffers survive (and grow with
 // the tile count); the blobs are re-allocated, so the caller refreshes parameters and flags afterwards.
-static int finalize_and_upload(Engine *e, TiledState *S, int64_t old_tiles) {
+static int finalize_and_upload(Engine *e, TiledState *S, int64_t old_tiles, bool incremental = false) {
     HostTables &H = S->H;
     const int64_t n_tiles = (int64_t)S->h_meta.size();
     int max_halo = 0, max_rec = 0, max_deg = 0, max_dict = 0;
@@ -731,57 +786,107 @@ static int finalize_and_upload(Engine *e, TiledState *S, int64_t old_tiles) {
         }
         act_tile_off.push_back((uint32_t)act_rec.size());
     }
-    const bool dict_mode = S->dict, split_mode = S->dict_split;
-    free_structure(e, S, /*keep_state=*/true);       // device tables only; the host tables above stay
-    S->dict = dict_mode; S->dict_split = split_mode;
     const int64_t n_slots = (int64_t)S->h_slot_to_api.size();
-    S->n_tiles = n_tiles; S->n_slots = n_slots;
+    const size_t ell_tail = (size_t)(MAX_DEG + 2 * ELL_CHUNK) * TM;      // the kernel prefetches whole register sets past a block
+    const uint32_t ell_pad = (uint32_t)(S->cs - N_DUMMY) << ELL_NB_SHIFT;
+    TableCaps &C = S->cap;
+    const bool dict_mode = S->dict, split_mode = S->dict_split;
+    if (!incremental) {                              // the host tables were rebuilt from nothing: every device table goes
+        free_structure(e, S, /*keep_state=*/true);   // (device tables only; the host tables above stay)
+        S->dict = dict_mode; S->dict_split = split_mode;
+    }
+    if (S->ell && S->ell_pad != ell_pad) { release(e, S->ell, (size_t)C.ell); C.ell = 0; }
+    auto room = [](size_t used, size_t least) { return (int64_t)(used + used / 8 + least); };
+    bool moved = false;                              // a table was (re-)allocated
+    // Each table on its own: the host copy only grew at its end since the last call (merge_tile appends) -> when the device
+    // table has room, the new end is copied behind what is already there; otherwise the table moves to a larger allocation
+    // (room of an eighth for the next edits) and is uploaded whole.  `tail` elements of `fill` must follow the used part.
+    auto put = [&](auto *&dst, int64_t &cap, int64_t &up, const auto &src, size_t tail, auto fill, size_t least) -> int {
+        typedef typename std::decay<decltype(src)>::type Vec;
+        if (dst && (int64_t)(src.size() + tail) <= cap) {
+            if ((int64_t)src.size() > up) TB_CUDA(e, cudaMemcpy(dst + up, src.data() + up, (src.size() - (size_t)up) * sizeof(src[0]), cudaMemcpyHostToDevice));
+        } else {
+            release(e, dst, (size_t)cap);
+            cap = room(src.size() + tail, least);
+            Vec padded(src);
+            padded.resize((size_t)cap, (typename Vec::value_type)fill);
+            TB_TRY(upload_vec(e, &dst, padded));
+            moved = true;
+        }
+        up = (int64_t)src.size();
+        return TB_OK;
+    };
     S->max_halo = max_halo; S->max_rec = max_rec; S->max_deg = max_deg; S->max_dict = max_dict;
-    S->max_blob = (int)max_blob; S->blob_bytes = H.blob_total; S->ell_unique_tiles = H.unique_blocks;
-    if (old_tiles != n_tiles) {                      // first build, or tiles appended for new masses: the state moves to larger buffers
+    S->max_blob = (int)max_blob; S->ell_unique_tiles = H.unique_blocks;
+    // state buffers and the per-tile tables (tile table, slots, split-dictionary offsets) share one capacity in tiles
+    if (n_tiles > C.st_tiles || !S->st[0]) {         // first build, or tiles appended for new masses beyond the room
+        const int64_t want = room((size_t)n_tiles, 64);
+        if (want * (int64_t)STATE_BLOCK >= ((int64_t)1 << 31)) { S->why_not = "state exceeds int32 halo indices"; S->supported = false; return TB_OK; }
         for (int p = 0; p < 2; p++) {
             double *bigger = nullptr;
-            TB_TRY(dev_alloc(e, &bigger, (size_t)n_tiles * STATE_BLOCK));
-            TB_CUDA(e, cudaMemset(bigger, 0, (size_t)n_tiles * STATE_BLOCK * 8));
+            TB_TRY(dev_alloc(e, &bigger, (size_t)want * STATE_BLOCK));
+            TB_CUDA(e, cudaMemset(bigger, 0, (size_t)want * STATE_BLOCK * 8));
             if (S->st[p] && old_tiles > 0) TB_CUDA(e, cudaMemcpy(bigger, S->st[p], (size_t)std::min(old_tiles, n_tiles) * STATE_BLOCK * 8, cudaMemcpyDeviceToDevice));
-            release(e, S->st[p], (size_t)old_tiles * STATE_BLOCK);
+            release(e, S->st[p], (size_t)C.st_tiles * STATE_BLOCK);
             S->st[p] = bigger;
         }
+        C.st_tiles = want;
+        moved = true;
     }
-    std::vector<int32_t> halo(H.halo);
-    while (halo.size() % 4) halo.push_back(0);
-    halo.resize(halo.size() + 4, 0);   // the last list may be copied rounded up to 16 bytes
-    std::vector<uint32_t> ell(H.ell);
-    ell.resize(ell.size() + (size_t)(MAX_DEG + 2 * ELL_CHUNK) * TM, (uint32_t)(S->cs - N_DUMMY) << ELL_NB_SHIFT);   // the kernel prefetches whole register sets
-    S->n_halo = (int64_t)halo.size(); S->n_ell = (int64_t)ell.size(); S->n_rec = (int64_t)H.rec_spring.size();
-    if (S->dict && S->dict_split) {
-        S->n_krec = (int64_t)H.kslot_spring.size();
-        TB_TRY(upload_vec(e, &S->krec_spring, H.kslot_spring));
-        TB_CUDA(e, cudaMalloc((void **)&S->krec_off, H.krec_off.size() * sizeof(uint32_t)));
-        TB_CUDA(e, cudaMemcpy(S->krec_off, H.krec_off.data(), H.krec_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
-    }
-    if (S->dict) {
-        std::vector<uint8_t> rec_map(H.rec_map);
-        while (rec_map.size() % 16) rec_map.push_back(0);
-        rec_map.resize(rec_map.size() + 16, 0);
-        S->n_rec_map = (int64_t)rec_map.size(); S->n_class_rep = (int64_t)H.rep_of.size();
-        TB_TRY(upload_vec(e, &S->rec_map, rec_map)); TB_TRY(upload_vec(e, &S->class_rep, H.rep_of));
-        if (!S->dict_bad) TB_CUDA(e, cudaMalloc((void **)&S->dict_bad, sizeof(int)));
-    }
-    if (!act_rec.empty()) {
-        S->n_act_rec = (int64_t)act_rec.size();
-        TB_CUDA(e, cudaMalloc((void **)&S->act_tile_off, act_tile_off.size() * sizeof(uint32_t)));
-        TB_CUDA(e, cudaMemcpy(S->act_tile_off, act_tile_off.data(), act_tile_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
-        TB_CUDA(e, cudaMalloc((void **)&S->act_rec, act_rec.size() * sizeof(int4)));
-        TB_CUDA(e, cudaMemcpy(S->act_rec, act_rec.data(), act_rec.size() * sizeof(int4), cudaMemcpyHostToDevice));
-    }
-    TB_TRY(dev_alloc(e, &S->blob, H.blob_total));
-    TB_CUDA(e, cudaMemset(S->blob, 0, H.blob_total));
-    TB_TRY(upload_vec(e, &S->slot_to_api, S->h_slot_to_api));
-    TB_TRY(upload_vec(e, &S->halo, halo)); TB_TRY(upload_vec(e, &S->rec_spring, H.rec_spring)); TB_TRY(upload_vec(e, &S->ell, ell));
-    TB_CUDA(e, cudaMalloc((void **)&S->meta, (size_t)n_tiles * sizeof(TileMeta)));
+    if (!S->meta || C.tiles < n_tiles) {
+        if (S->meta) { cudaFree(S->meta); S->meta = nullptr; }
+        if (S->krec_off) { cudaFree(S->krec_off); S->krec_off = nullptr; }
+        release(e, S->slot_to_api, (size_t)C.tiles * TM);
+        C.tiles = C.st_tiles; S->n_slots = 0;
+        TB_CUDA(e, cudaMalloc((void **)&S->meta, (size_t)C.tiles * sizeof(TileMeta)));
+        std::vector<int32_t> slots(S->h_slot_to_api);
+        slots.resize((size_t)C.tiles * TM, -1);
+        TB_TRY(upload_vec(e, &S->slot_to_api, slots));
+        moved = true;
+    } else if (n_slots > S->n_slots)
+        TB_CUDA(e, cudaMemcpy(S->slot_to_api + S->n_slots, S->h_slot_to_api.data() + S->n_slots, (size_t)(n_slots - S->n_slots) * 4, cudaMemcpyHostToDevice));
     TB_CUDA(e, cudaMemcpy(S->meta, S->h_meta.data(), (size_t)n_tiles * sizeof(TileMeta), cudaMemcpyHostToDevice));
+    int64_t up_rec = S->n_rec, up_krec = S->n_krec, up_cls = S->n_class_rep;
+    TB_TRY(put(S->halo, C.halo, S->n_halo_up, H.halo, 8, 0, (size_t)1 << 16));
+    TB_TRY(put(S->ell, C.ell, S->n_ell_up, H.ell, ell_tail, ell_pad, (size_t)(n_tiles / 8 + 64) * MAX_DEG * TM));   // (a lattice shares its blocks: room by tiles)
+    TB_TRY(put(S->rec_spring, C.rec, up_rec, H.rec_spring, 0, -1, (size_t)1 << 18));
+    S->ell_pad = ell_pad;
+    S->n_halo = S->n_halo_up + 4; S->n_ell = S->n_ell_up + (int64_t)ell_tail; S->n_rec = up_rec;
+    if (S->dict) {
+        TB_TRY(put(S->rec_map, C.rec_map, S->n_rec_map_up, H.rec_map, 32, 0, (size_t)1 << 18));
+        TB_TRY(put(S->class_rep, C.cls, up_cls, H.rep_of, 0, 0, (size_t)1 << 16));
+        S->n_class_rep = up_cls;
+        if (!S->dict_bad) TB_CUDA(e, cudaMalloc((void **)&S->dict_bad, sizeof(int)));
+        if (S->dict_split) {
+            TB_TRY(put(S->krec_spring, C.krec, up_krec, H.kslot_spring, 0, -1, (size_t)1 << 18));
+            S->n_krec = up_krec;
+            if (!S->krec_off) TB_CUDA(e, cudaMalloc((void **)&S->krec_off, 2 * (size_t)C.tiles * sizeof(uint32_t)));
+            TB_CUDA(e, cudaMemcpy(S->krec_off, H.krec_off.data(), H.krec_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+        }
+    }
+    {   // actuated records: small, rebuilt every time
+        if (S->act_tile_off) { cudaFree(S->act_tile_off); S->act_tile_off = nullptr; }
+        if (S->act_rec) { cudaFree(S->act_rec); S->act_rec = nullptr; }
+        S->n_act_rec = 0;
+        if (!act_rec.empty()) {
+            S->n_act_rec = (int64_t)act_rec.size();
+            TB_CUDA(e, cudaMalloc((void **)&S->act_tile_off, act_tile_off.size() * sizeof(uint32_t)));
+            TB_CUDA(e, cudaMemcpy(S->act_tile_off, act_tile_off.data(), act_tile_off.size() * sizeof(uint32_t), cudaMemcpyHostToDevice));
+            TB_CUDA(e, cudaMalloc((void **)&S->act_rec, act_rec.size() * sizeof(int4)));
+            TB_CUDA(e, cudaMemcpy(S->act_rec, act_rec.data(), act_rec.size() * sizeof(int4), cudaMemcpyHostToDevice));
+        }
+    }
+    // the blobs: rebuilt tiles got fresh places at the end (zeroed room); the caller refreshes masses, flags and parameters
+    if (!S->blob || H.blob_total > C.blob) {
+        release(e, S->blob, C.blob);
+        C.blob = (size_t)room(H.blob_total, 4u << 20);
+        TB_TRY(dev_alloc(e, &S->blob, C.blob));
+        TB_CUDA(e, cudaMemset(S->blob, 0, C.blob));
+        moved = true;
+    }
+    S->n_tiles = n_tiles; S->n_slots = n_slots; S->blob_bytes = H.blob_total;
     S->supported = true;
+    if (moved) S->n_uploads++; else S->n_patches++;
     return TB_OK;
 }
 
@@ -909,8 +1014,10 @@ static int patch_structure(Engine *e, TiledState *S, bool *done) {
     cfg.align_rows = !(getenv("TB_ALIGN_ROWS") && atoi(getenv("TB_ALIGN_ROWS")) == 0);
     cfg.class_of = &H.class_of; cfg.rep_of = &H.rep_of;
     cfg.drop_removed = true;
+    const auto wa = std::chrono::steady_clock::now();
     std::vector<TileOut> outs(touched.size());
     parallel_tiles((int64_t)touched.size(), [&](int64_t q) { build_tile(e, S, touched[(size_t)q], cfg, outs[(size_t)q]); });
+    const auto wb = std::chrono::steady_clock::now();
     for (size_t q = 0; q < touched.size(); q++)
         if (outs[q].why_not || outs[q].dict_overflow || TM + (int)outs[q].th.size() + N_DUMMY > S->cs) return TB_OK;
     S->h_meta.resize((size_t)n_tiles, TileMeta());
@@ -923,10 +1030,11 @@ static int patch_structure(Engine *e, TiledState *S, bool *done) {
         if (why) return TB_OK;
     }
     const auto w1 = std::chrono::steady_clock::now();
-    TB_TRY(finalize_and_upload(e, S, old_tiles));
+    TB_TRY(finalize_and_upload(e, S, old_tiles, /*incremental=*/true));
     if (getenv("TB_TIMING"))
-        fprintf(stderr, "[tb timing]   %zu tiles rebuilt in %.2f ms, tables re-uploaded in %.2f ms\n", touched.size(),
-                std::chrono::duration<double, std::milli>(w1 - w0).count(), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w1).count());
+        fprintf(stderr, "[tb timing]   %zu tiles: classes %.2f ms, built %.2f ms, merged %.2f ms, device tables %.2f ms\n", touched.size(),
+                std::chrono::duration<double, std::milli>(wa - w0).count(), std::chrono::duration<double, std::milli>(wb - wa).count(),
+                std::chrono::duration<double, std::milli>(w1 - wb).count(), std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - w1).count());
     *done = S->supported;
     return TB_OK;
 }
@@ -1721,6 +1829,7 @@ static void halo_release(Engine *e, TiledState *S);
 static unsigned long long *g_prof_dev = nullptr;
 static long long g_prof_launches = 0;
 int tiled_prepare(Engine *e) {
+    TimeScope ts("tiled_prepare");
     if (getenv("TB_PROFILE") && !g_prof_dev) { cudaMalloc((void **)&g_prof_dev, 16 * 8); cudaMemset(g_prof_dev, 0, 16 * 8); }
     if (!e->tiled) e->tiled = new TiledState();
     TiledState *S = e->tiled;
@@ -2501,6 +2610,7 @@ int tiled_info(const Engine *e, tb_info *info) {
     info->ell_unique_tiles = (int32_t)S->ell_unique_tiles;
     info->dict_records = S->dict ? S->max_dict : 0;
     info->dict_split_k = (S->dict && S->dict_split) ? 1 : 0;
+    info->layout_uploads = S->n_uploads; info->layout_patches = S->n_patches;
     // read: blob + own state + halo gathers + halo lists + ELL words + meta; written: own state
     info->tiled_bytes_per_step = (int64_t)S->blob_bytes + 2 * S->n_tiles * STATE_BLOCK * 8 + S->n_halo * (4 + (S->stage_vel ? 48 : 24)) +
                                  S->n_tiles * (int64_t)sizeof(TileMeta) + S->n_ell * 4;
