@@ -360,6 +360,7 @@ int tb_set_topology(tb_engine *e, int64_t nm, int64_t ns, const int32_t *left, c
         TB_CUDA(e, cudaMemcpyAsync(e->left, left, (size_t)ns * 4, cudaMemcpyHostToDevice, e->stream));
         TB_CUDA(e, cudaMemcpyAsync(e->right, right, (size_t)ns * 4, cudaMemcpyHostToDevice, e->stream));
     }
+    e->h_left.reserve((size_t)(ns + ns / 8 + 4096)); e->h_right.reserve((size_t)(ns + ns / 8 + 4096));   // tb_add_springs appends without a copy
     e->h_left.assign(left, left + ns); e->h_right.assign(right, right + ns);
     e->csr_nm = e->csr_ns = 0; e->extra_adj.clear();
     TB_TRY(ensure_csr(e));

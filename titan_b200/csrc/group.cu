@@ -16,6 +16,7 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <thread>
 #include <vector>
 
 struct tb_group {
@@ -54,6 +55,21 @@ int efail(tb_group *g, size_t r, int rc) {
     return rc;
 }
 #define G_TRY(g, r, call) do { int _rc = (call); if (_rc != TB_OK) return efail((g), (r), _rc); } while (0)
+
+// one host thread per engine (each talks to its own device), or chunks of a loop over all host cores
+template <class F> void per_engine(size_t W, F f) {
+    if (W == 1) { f((size_t)0); return; }
+    std::vector<std::thread> th;
+    for (size_t r = 0; r < W; r++) th.emplace_back([&f, r] { f(r); });
+    for (std::thread &t : th) t.join();
+}
+template <class F> void par_chunks(size_t n, F f) {
+    const size_t nt = n < ((size_t)1 << 16) ? 1 : std::min<size_t>(16, std::max(1u, std::thread::hardware_concurrency()));
+    if (nt == 1) { f((size_t)0, n); return; }
+    std::vector<std::thread> th;
+    for (size_t t = 0; t < nt; t++) th.emplace_back([&f, t, nt, n] { f(n * t / nt, n * (t + 1) / nt); });
+    for (std::thread &t : th) t.join();
+}
 
 inline int32_t local_of(const tb_group::Part &p, int64_t gid) {
     auto it = std::lower_bound(p.mass_gid.begin(), p.mass_gid.end(), gid);
@@ -228,6 +244,7 @@ tb_engine *tb_group_engine(tb_group *g, int32_t r) { return (g && r >= 0 && (siz
 
 int tb_group_set_topology(tb_group *g, int64_t nm, int64_t ns, const int32_t *left, const int32_t *right, const int32_t *owner) {
     if (!g) return TB_ERR_INVALID;
+    tb::TimeScope ts("tb_group_set_topology");
     const size_t W = g->eng.size();
     if (nm <= 0 || ns < 0 || (ns > 0 && (!left || !right))) return gfail(g, TB_ERR_INVALID, "tb_group_set_topology: bad sizes/pointers");
     g->nm = nm; g->ns = ns;
@@ -254,23 +271,24 @@ int tb_group_set_topology(tb_group *g, int64_t nm, int64_t ns, const int32_t *le
     }
     // per engine: springs with an own endpoint (global order), masses touched by them plus own masses without springs
     g->any_cut = false;
-    std::vector<int32_t> g2l((size_t)nm);
-    for (size_t r = 0; r < W; r++) {
+    std::vector<std::vector<int32_t>> LL(W), RR(W);
+    std::vector<uint8_t> cut(W, 0);
+    per_engine(W, [&](size_t r) {            // host work only, one thread per engine
         tb_group::Part &p = g->part[r];
         p = tb_group::Part();
-        std::vector<uint8_t> touched((size_t)nm, 0);
-        for (int64_t i = 0; i < nm; i++) if ((size_t)g->owner[(size_t)i] == r) touched[(size_t)i] = 1;
+        std::vector<int32_t> g2l((size_t)nm, -1);            // -1 untouched, then the local index
+        for (int64_t i = 0; i < nm; i++) if ((size_t)g->owner[(size_t)i] == r) g2l[(size_t)i] = 0;
         for (int64_t s = 0; s < ns; s++) {
             const int32_t a = left[s], b = right[s];
             const bool mine = (a >= 0 && (size_t)g->owner[(size_t)a] == r) || (b >= 0 && (size_t)g->owner[(size_t)b] == r);
             if (!mine) continue;
             p.spring_gid.push_back(s);
-            if (a >= 0) touched[(size_t)a] = 1;
-            if (b >= 0) touched[(size_t)b] = 1;
+            if (a >= 0) g2l[(size_t)a] = 0;
+            if (b >= 0) g2l[(size_t)b] = 0;
         }
-        for (int64_t i = 0; i < nm; i++) if (touched[(size_t)i]) { g2l[(size_t)i] = (int32_t)p.mass_gid.size(); p.mass_gid.push_back(i); }
-        if (p.mass_gid.empty()) return gfail(g, TB_ERR_INVALID, "tb_group_set_topology: engine %zu owns no mass (fewer masses than engines?)", r);
-        std::vector<int32_t> ll(p.spring_gid.size()), rr(p.spring_gid.size());
+        for (int64_t i = 0; i < nm; i++) if (g2l[(size_t)i] == 0) { g2l[(size_t)i] = (int32_t)p.mass_gid.size(); p.mass_gid.push_back(i); }
+        std::vector<int32_t> &ll = LL[r], &rr = RR[r];
+        ll.resize(p.spring_gid.size()); rr.resize(p.spring_gid.size());
         for (size_t q = 0; q < p.spring_gid.size(); q++) {
             const int64_t s = p.spring_gid[q];
             ll[q] = left[s] >= 0 ? g2l[(size_t)left[s]] : -1;
@@ -279,11 +297,21 @@ int tb_group_set_topology(tb_group *g, int64_t nm, int64_t ns, const int32_t *le
         for (size_t l = 0; l < p.mass_gid.size(); l++) {
             const int32_t o = g->owner[(size_t)p.mass_gid[l]];
             if ((size_t)o == r) p.own_local.push_back((int32_t)l);
-            else { p.ghost_local.push_back((int32_t)l); p.ghost_owner.push_back(o); g->any_cut = true; }
+            else { p.ghost_local.push_back((int32_t)l); p.ghost_owner.push_back(o); cut[r] = 1; }
         }
-        G_TRY(g, r, tb_set_topology(g->eng[r], (int64_t)p.mass_gid.size(), (int64_t)p.spring_gid.size(), ll.data(), rr.data()));
-        G_TRY(g, r, tb_halo_set_ghosts(g->eng[r], (int64_t)p.ghost_local.size(), p.ghost_local.empty() ? nullptr : p.ghost_local.data()));
+    });
+    for (size_t r = 0; r < W; r++) {
+        tb_group::Part &p = g->part[r];
+        if (cut[r]) g->any_cut = true;
+        if (p.mass_gid.empty()) return gfail(g, TB_ERR_INVALID, "tb_group_set_topology: engine %zu owns no mass (fewer masses than engines?)", r);
     }
+    std::vector<int> rcs(W, TB_OK);
+    per_engine(W, [&](size_t r) {
+        tb_group::Part &p = g->part[r];
+        rcs[r] = tb_set_topology(g->eng[r], (int64_t)p.mass_gid.size(), (int64_t)p.spring_gid.size(), LL[r].data(), RR[r].data());
+        if (rcs[r] == TB_OK) rcs[r] = tb_halo_set_ghosts(g->eng[r], (int64_t)p.ghost_local.size(), p.ghost_local.empty() ? nullptr : p.ghost_local.data());
+    });
+    for (size_t r = 0; r < W; r++) if (rcs[r] != TB_OK) return efail(g, r, rcs[r]);
     g->connected = false; g->need_push = true;
     return TB_OK;
 }
@@ -392,8 +420,39 @@ int tb_group_set_spring_params(tb_group *g, int64_t first, int64_t count, const 
                                const double *damping, const int32_t *type, const double *omega, const double *l_max,
                                const double *l_min, const double *rate) {
     if (!g || g->nm == 0) return TB_ERR_INVALID;
+    tb::TimeScope ts("tb_group_set_spring_params");
     if (count < 0 || (!idx && (first < 0 || first + count > g->ns))) return gfail(g, TB_ERR_INVALID, "tb_group_set_spring_params: range outside [0,%lld)", (long long)g->ns);
     if (idx) for (int64_t j = 0; j < count; j++) if (idx[j] < 0 || idx[j] >= g->ns) return gfail(g, TB_ERR_INVALID, "tb_group_set_spring_params: index %d out of range", idx[j]);
+    if (!idx) {
+        // a range of global springs is a range of every engine's local springs (ascending global order on both sides): gather
+        // the values on all host cores and upload them as a range -- no index lists (43 M springs: 3.2 s -> a fraction)
+        std::vector<double> tmp[7];
+        std::vector<int32_t> ty;
+        for (size_t r = 0; r < g->eng.size(); r++) {
+            const tb_group::Part &p = g->part[r];
+            const size_t lo = (size_t)(std::lower_bound(p.spring_gid.begin(), p.spring_gid.end(), first) - p.spring_gid.begin());
+            const size_t hi = (size_t)(std::lower_bound(p.spring_gid.begin(), p.spring_gid.end(), first + count) - p.spring_gid.begin());
+            if (hi <= lo) continue;
+            const double *src[7] = {k, rest, damping, omega, l_max, l_min, rate};
+            const double *use[7];
+            for (int a = 0; a < 7; a++) {
+                use[a] = nullptr;
+                if (!src[a]) continue;
+                tmp[a].resize(hi - lo);
+                double *dst = tmp[a].data(); const double *from = src[a];
+                par_chunks(hi - lo, [&](size_t q0, size_t q1) { for (size_t q = q0; q < q1; q++) dst[q] = from[p.spring_gid[lo + q] - first]; });
+                use[a] = dst;
+            }
+            if (type) {
+                ty.resize(hi - lo);
+                par_chunks(hi - lo, [&](size_t q0, size_t q1) { for (size_t q = q0; q < q1; q++) ty[q] = type[p.spring_gid[lo + q] - first]; });
+            }
+            G_TRY(g, r, tb_set_spring_params(g->eng[r], (int64_t)lo, (int64_t)(hi - lo), nullptr, use[0], use[1], use[2], type ? ty.data() : nullptr,
+                                             use[3], use[4], use[5], use[6]));
+        }
+        if (type || damping) g->connected = false;
+        return TB_OK;
+    }
     std::vector<Route> rt;
     route_springs(g, first, count, idx, rt);
     std::vector<double> a, b, c, d, e2, f, h;
@@ -452,9 +511,14 @@ int tb_group_set_globals(tb_group *g, const double gravity[3], double dt) {
 int tb_group_run_async(tb_group *g, int64_t nsteps, double t0) {
     if (!g || g->nm == 0) return TB_ERR_INVALID;
     // layouts first (a tile build allocates, which waits for its whole device), then the handshake, then the boundary state
-    for (size_t r = 0; r < g->eng.size(); r++) G_TRY(g, r, tb_run_async(g->eng[r], 0, t0));
-    if (!g->connected) { int rc = group_connect(g); if (rc != TB_OK) return rc; }
-    if (g->need_push) { int rc = group_push(g); if (rc != TB_OK) return rc; }
+    {   tb::TimeScope ts("group layouts");
+        // (each engine builds its layout on its own host thread: the builds are host work, a second or more per million masses)
+        std::vector<int> rcs(g->eng.size(), TB_OK);
+        per_engine(g->eng.size(), [&](size_t r) { rcs[r] = tb_run_async(g->eng[r], 0, t0); });
+        for (size_t r = 0; r < g->eng.size(); r++) if (rcs[r] != TB_OK) return efail(g, r, rcs[r]);
+    }
+    if (!g->connected) { tb::TimeScope ts("group_connect"); int rc = group_connect(g); if (rc != TB_OK) return rc; }
+    if (g->need_push) { tb::TimeScope ts("group_push"); int rc = group_push(g); if (rc != TB_OK) return rc; }
     if (nsteps == 0) return TB_OK;
     for (size_t r = 0; r < g->eng.size(); r++) G_TRY(g, r, tb_run_async(g->eng[r], nsteps, t0));
     return TB_OK;

@@ -140,6 +140,7 @@ struct TiledState {
     int64_t n_halo_up = 0, n_ell_up = 0, n_rec_map_up = 0;   // host entries already on the device (halo / ell / rec_map carry a tail)
     uint32_t ell_pad = 0;                 // the padding word the free end of the ELL table is filled with
     int n_uploads = 0, n_patches = 0;     // whole uploads of the tables / edits written into their free ends
+    bool exports_set = false;             // the tile table carries export fields (tb_halo_set_exports) since its last full build
     int build_mode = 1;                   // record mode of the last build (1 full dictionary, 2 split, 0 plain)
     int64_t n_tiles = 0, n_slots = 0, n_rec = 0, n_ell = 0, n_halo = 0;
     size_t blob_bytes = 0;
@@ -398,6 +399,7 @@ static int param_classes(Engine *e, bool with_k, bool damping, bool active, Host
     }
     const bool typed = active && e->h_type.size() == ns;    // the actuation type is part of a record (sine-table mode scales per record)
     if (s0 == 0) { H.class_seen.clear(); H.class_first.clear(); }
+    if (H.class_of.capacity() < ns) { H.class_of.reserve(ns + ns / 8 + 4096); H.rep_of.reserve(ns + ns / 8 + 4096); }   // springs added later: no copy
     H.class_of.resize(ns); H.rep_of.resize(ns);
     ClassKey last = {0, 0, 0, 0, 0}; int32_t last_class = -1;
     auto bits = [](double x) { uint64_t u; memcpy(&u, &x, 8); return u; };
@@ -453,6 +455,7 @@ struct TileOut {
     std::vector<std::pair<int32_t, int>> act;   // (ACTUATED_* spring, its final record)
     const char *why_not = nullptr;        // the tile does not fit the tiled format
     bool dict_overflow = false;           // more distinct records than a tile's byte map addresses: try the next record mode
+    uint64_t hash = 0;                    // content hash of `block` once its dummy indices are final (seal_tile)
 };
 struct BuildCfg {
     bool dict = false, split = false, align_rows = true;
@@ -668,25 +671,32 @@ static void build_tile(const Engine *e, const TiledState *S, int64_t T, const Bu
 // Host copies of the tables the tiled kernel reads (TiledState::H), kept so that single tiles can be rebuilt later: a rebuilt
 // tile's lists are appended and its TileMeta redirected (the old entries stay behind until the next full build).
 
-// appends tile T's contribution; the dummy indices of its padding words are rebased to stride cs first
+// Once the shared-memory stride cs is known (it depends on the longest halo list of all tiles): the provisional dummy index of
+// the padding words becomes the stride's own dummies [cs - N_DUMMY, cs), and the block gets its content hash (FNV-1a over the
+// words).  Per tile, so it runs on all cores like build_tile.
+static void seal_tile(TileOut &o, int cs) {
+    const uint32_t base = (uint32_t)(cs - N_DUMMY);
+    uint64_t hsh = 1469598103934665603ull ^ (uint64_t)o.deg;
+    for (uint32_t &w : o.block) {
+        if (!(w & ELL_VALID)) { const uint32_t nb = (w >> ELL_NB_SHIFT) & 0x1ffu; w = (base + (nb >= PAD_NB ? nb - PAD_NB : 0u)) << ELL_NB_SHIFT; }
+        hsh ^= w; hsh *= 1099511628211ull;
+    }
+    o.hash = hsh;
+}
+
+// appends tile T's contribution (sealed: seal_tile)
 static const char *merge_tile(Engine *e, TiledState *S, int64_t T, TileOut &o, bool keep_exchange) {
     HostTables &H = S->H;
     TileMeta &M = S->h_meta[(size_t)T];
     const TileMeta old = M;
     const bool dict = S->dict, split = S->dict_split;
-    {   // padding words: provisional dummy index -> the stride's own dummies [cs - N_DUMMY, cs)
-        const uint32_t base = (uint32_t)(S->cs - N_DUMMY);
-        for (uint32_t &w : o.block)
-            if (!(w & ELL_VALID)) { const uint32_t nb = (w >> ELL_NB_SHIFT) & 0x1ffu; w = (base + (nb >= PAD_NB ? nb - PAD_NB : 0u)) << ELL_NB_SHIFT; }
-    }
     M.deg = (uint32_t)o.deg;
     while (H.halo.size() % 4) H.halo.push_back(0);               // 16-byte aligned halo lists (bulk copy)
     M.halo_off = (uint32_t)H.halo.size();
     M.n_halo = (uint32_t)o.th.size();
     H.halo.insert(H.halo.end(), o.th.begin(), o.th.end());      // -1 = hole, skipped by the gather
-    // content dedupe of the ELL block (FNV-1a over the words, verified by comparison)
-    uint64_t hsh = 1469598103934665603ull ^ (uint64_t)o.deg;
-    for (uint32_t w : o.block) { hsh ^= w; hsh *= 1099511628211ull; }
+    // content dedupe of the ELL block (hash from seal_tile, verified by comparison)
+    const uint64_t hsh = o.hash;
     bool found = false;
     std::vector<uint32_t> &cands = H.ell_index[hsh];
     for (uint32_t off : cands)
@@ -963,9 +973,10 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
     }
     if (TM + max_halo + N_DUMMY > CS_BIG) { S->why_not = "a tile reaches too many foreign masses"; return TB_OK; }
     S->cs = choose_cs(max_halo, (e->flags & TB_MATH_STRICT) != 0);
+    parallel_tiles(n_tiles, [&](int64_t T) { seal_tile(outs[(size_t)T], S->cs); });
     S->dict = dict; S->dict_split = split; S->build_mode = mode;
     S->h_meta.resize((size_t)n_tiles);            // keep_slots: the old entries hand over their exchange fields
-    if (!keep_slots) std::fill(S->h_meta.begin(), S->h_meta.end(), TileMeta());
+    if (!keep_slots) { std::fill(S->h_meta.begin(), S->h_meta.end(), TileMeta()); S->exports_set = false; }
     H.act.assign((size_t)n_tiles, {});
     H.tile_slots.assign((size_t)n_tiles, 1);
     H.krec_off.assign(split ? 2 * (size_t)n_tiles : 0, 0u);
@@ -1016,7 +1027,7 @@ static int patch_structure(Engine *e, TiledState *S, bool *done) {
     cfg.drop_removed = true;
     const auto wa = std::chrono::steady_clock::now();
     std::vector<TileOut> outs(touched.size());
-    parallel_tiles((int64_t)touched.size(), [&](int64_t q) { build_tile(e, S, touched[(size_t)q], cfg, outs[(size_t)q]); });
+    parallel_tiles((int64_t)touched.size(), [&](int64_t q) { build_tile(e, S, touched[(size_t)q], cfg, outs[(size_t)q]); seal_tile(outs[(size_t)q], S->cs); });
     const auto wb = std::chrono::steady_clock::now();
     for (size_t q = 0; q < touched.size(); q++)
         if (outs[q].why_not || outs[q].dict_overflow || TM + (int)outs[q].th.size() + N_DUMMY > S->cs) return TB_OK;
@@ -2452,7 +2463,9 @@ int tb_halo_prepare(tb_engine *e, tb_halo_handle *out) {
     cudaSetDevice(e->device);
     if (e->nm == 0) return fail(e, TB_ERR_INVALID, "tb_halo_prepare before tb_set_topology");
     if (e->tiled) halo_release(e, e->tiled);
-    e->tiled_stale |= TS_STRUCT;
+    // a layout whose tile table still carries the export fields of an earlier connection is built afresh; one that is current
+    // and never exchanged (tb_run_async of zero steps built it just now) is taken as it is
+    if (!e->tiled || e->tiled->exports_set || !e->tiled->supported || e->tiled->n_tiles == 0) e->tiled_stale |= TS_STRUCT;
     int rc = tiled_prepare(e);
     if (rc != TB_OK) return rc;
     TiledState *S = e->tiled;
@@ -2543,6 +2556,7 @@ int tb_halo_set_exports(tb_engine *e, int64_t n, const int32_t *mass_idx, const 
     std::vector<std::vector<std::pair<int32_t, int32_t>>> per_slot;   // only for slots of tiles that export
     std::vector<int> rows((size_t)S->n_tiles, 0);
     std::vector<int4> flat((size_t)n);
+    S->exports_set = true;
     std::map<int64_t, std::vector<std::pair<int32_t, int32_t>>> by_slot;
     for (int64_t j = 0; j < n; j++) {
         if (mass_idx[j] < 0 || mass_idx[j] >= e->nm || peer_idx[j] < 0 || peer_idx[j] >= S->n_peers || remote_offset[j] < 0 ||

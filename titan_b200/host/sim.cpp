@@ -749,15 +749,19 @@ void Simulation::upload_local_constraints() {
 // Topology + every field, from the host objects (toArray, src/sim.cu:940-1041).
 void Simulation::upload_everything() {
     const int64_t nm = (int64_t)masses.size(), ns = (int64_t)springs.size();
-    for (int64_t i = 0; i < nm; i++) masses[(size_t)i]->slot = (int32_t)i;
+    PhaseTimer pt_topo("start");
+    parallel_for((size_t)nm, [&](size_t lo, size_t hi) { for (size_t i = lo; i < hi; i++) masses[i]->slot = (int32_t)i; });
     std::vector<int32_t> left((size_t)ns), right((size_t)ns);
-    for (int64_t s = 0; s < ns; s++) {
-        Spring *sp = springs[(size_t)s];
-        sp->slot = (int32_t)s;
-        // nullptr or deleted endpoint -> -1: the spring is skipped by the step (src/sim.cu:1163)
-        left[(size_t)s] = (sp->_left && sp->_left->valid) ? sp->_left->slot : -1;
-        right[(size_t)s] = (sp->_right && sp->_right->valid) ? sp->_right->slot : -1;
-    }
+    parallel_for((size_t)ns, [&](size_t lo, size_t hi) {          // pointer chasing over every Spring and its two Masses: all cores
+        for (size_t s = lo; s < hi; s++) {
+            Spring *sp = springs[s];
+            sp->slot = (int32_t)s;
+            // nullptr or deleted endpoint -> -1: the spring is skipped by the step (src/sim.cu:1163)
+            left[s] = (sp->_left && sp->_left->valid) ? sp->_left->slot : -1;
+            right[s] = (sp->_right && sp->_right->valid) ? sp->_right->slot : -1;
+        }
+    });
+    pt_topo.lap("topology from the host objects");
     // ---- several GPUs: who owns which mass -----------------------------------------------------------------------
     // (a) one grid container holding every mass (createLattice): i-slabs, whole planes per GPU, each slab with its own bricks;
     // (b) bodies no spring connects (every mass in exactly one container): whole containers to the GPUs in turn, balanced by
@@ -827,7 +831,9 @@ void Simulation::upload_everything() {
             }
         }
     }
+    pt_topo.lap("owners and tile hints");
     engine_check(dv_set_topology(dev(), nm, ns, left.data(), right.data(), owner.empty() ? nullptr : owner.data()), "tb_set_topology");
+    pt_topo.lap("tb_set_topology");
     dev_nm = nm; dev_ns = ns;
     if (hs) { hs->mass_valid = hs->spring_valid = hs->ext_uploaded_nonzero = false; }   // the device is back at its defaults
     if (covered && nm > 0) engine_check(dv_set_tile_hint(dev(), hint.data()), "tb_set_tile_hint");
