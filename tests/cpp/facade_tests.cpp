@@ -285,6 +285,37 @@ static void gpu_tests() {
         CHECK(a->vel[1] == vay && sim.masses.size() == 2);
         sim.stop();
     }
+    section("deleteContainer while paused: tombstones and frozen masses on the device, the other body is undisturbed");
+    {
+        // reference: Simulation::deleteContainer src/sim.cu:478-564
+        auto run = [&](bool with_b, std::vector<double> &out) {
+            Simulation sim;
+            Lattice *a = sim.createLattice(Vec(0, 0, 0.3), Vec(0.4, 0.4, 0.4), 5, 5, 5);
+            Lattice *b = with_b ? sim.createLattice(Vec(2, 0, 0.3), Vec(0.4, 0.4, 0.4), 5, 5, 5) : nullptr;
+            sim.createPlane(Vec(0, 0, 1), 0, 0.5, 0.6);
+            sim.start();
+            sim.pause(0.01);
+            if (b) sim.deleteContainer(b);
+            CHECK(sim.masses.size() == 125 && sim.springs.size() == 1036 && sim.containers.size() == 1);
+            sim.resume();
+            sim.pause(0.03);
+            sim.getAll();
+            for (Mass *q : a->masses) for (int c = 0; c < 3; c++) { out.push_back(q->pos[c]); out.push_back(q->vel[c]); }
+            Mass *extra = sim.createMass(Vec(0, 0, 2));           // the object lists and the device slots no longer line up: still consistent
+            sim.resume();
+            sim.pause(0.031);
+            sim.get(extra);
+            CHECK(extra->pos[2] < 2.0 && extra->pos[2] > 1.99);
+            sim.stop();
+        };
+        std::vector<double> alone, after_delete;
+        run(false, alone);
+        run(true, after_delete);
+        double worst = 0;
+        for (size_t q = 0; q < alone.size() && q < after_delete.size(); q++) worst = std::max(worst, std::fabs(alone[q] - after_delete[q]));
+        std::printf("  max |never there - deleted| = %.3e\n", worst);
+        CHECK(alone.size() == after_delete.size() && worst <= 1e-12);
+    }
     section("RobotLink: magnetic connectors pull each other (occupancy-grid + magnet pass)");
     {
         // reference: createRobotLink src/sim.cu:2201-2222, RobotLink src/object.cu:368-384, magnet pass :1223-1281

@@ -166,7 +166,13 @@ void Simulation::deleteContainer(Container *c) {   // src/sim.cu:478-564
     std::vector<Spring *> doomed;
     for (Spring *s : springs) if (dead_springs.count(s)) doomed.push_back(s);
     springs.erase(std::remove_if(springs.begin(), springs.end(), [&](Spring *s) { return dead_springs.count(s) != 0; }), springs.end());
+    // Once started, on one GPU: the container's springs become tombstones and its masses freeze in place on the device, like
+    // deleteSpring / deleteMass one by one (no re-upload; the device slots of the survivors do not move).  Objects that were
+    // created while paused and never uploaded (slot < 0), a pending re-upload, or several GPUs: the full re-upload.
+    bool in_place = STARTED && !topology_dirty && !group && engine;
+    std::vector<int32_t> spring_slots, mass_slots;
     for (Spring *s : doomed) {
+        if (s->slot >= 0) spring_slots.push_back(s->slot); else if (STARTED) in_place = false;
         for (Mass *end : {s->_left, s->_right}) {
             if (!end) continue;
             if (!end->valid && end->ref_count == 1) zombies.erase(std::remove(zombies.begin(), zombies.end(), end), zombies.end());
@@ -179,6 +185,7 @@ void Simulation::deleteContainer(Container *c) {   // src/sim.cu:478-564
     for (Mass *m : masses) if (dead_masses.count(m)) gone.push_back(m);
     masses.erase(std::remove_if(masses.begin(), masses.end(), [&](Mass *m) { return dead_masses.count(m) != 0; }), masses.end());
     for (Mass *m : gone) {
+        if (m->slot >= 0) mass_slots.push_back(m->slot); else if (STARTED) in_place = false;
         m->valid = false;
         m->slot = -1;
         if (m->ref_count > 1) zombies.push_back(m);
@@ -186,8 +193,15 @@ void Simulation::deleteContainer(Container *c) {   // src/sim.cu:478-564
     }
     containers.erase(std::remove(containers.begin(), containers.end(), c), containers.end());
     delete c;
-    if (STARTED) topology_dirty = true;
-}
+    if (!STARTED) return;
+    if (!in_place) { topology_dirty = true; return; }
+    if (!spring_slots.empty()) engine_check(tb_remove_springs(engine, (int64_t)spring_slots.size(), spring_slots.data()), "tb_remove_springs");
+    if (!mass_slots.empty()) {
+        const std::vector<uint8_t> zero(mass_slots.size(), 0);
+        engine_check(tb_set_mass_state(engine, 0, (int64_t)mass_slots.size(), mass_slots.data(), nullptr, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                       nullptr, zero.data()), "tb_set_mass_state");
+    }
+}   // (the whole-array transfers check for themselves that the object lists still line up with the device slots)
 
 Spring *Simulation::getSpringByIndex(int i) { assert(i >= 0 && (size_t)i < springs.size()); return springs[i]; }
 Mass *Simulation::getMassByIndex(int i) { assert(i >= 0 && (size_t)i < masses.size()); return masses[i]; }
