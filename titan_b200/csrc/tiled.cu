@@ -1325,22 +1325,23 @@ __device__ __noinline__ void advance_actuated_records(const ARGS &A, double dt, 
 // before stage 1, which still sits in the slot this thread is about to overwrite (ping-pong buffers; nobody else reads it).
 // A mass with local constraints keeps its velocity backup in a side array: the constraints project the velocity in place before
 // the backup is taken (MassExtras::rk2_bvel).
-// Out of line AND by value: a reference parameter of a function that is not inlined makes the caller keep `force`, `pos` and
-// `vel` in local memory for the whole tile loop (their addresses escape) -- measured: C2 196 -> 157 G for every integrator.
-struct Rk2Out { V3 pos, vel, acc; };
+// The integrators other than the default Euler step, out of line AND by value: a reference parameter of a function that is
+// not inlined makes the caller keep `force`, `pos` and `vel` in local memory for the whole tile loop (their addresses escape)
+// -- measured: C2 196 -> 157 G for every integrator.  stage 0 = Verlet (acc = the previous acceleration), 1 / 2 = RK2.
+struct TailOut { V3 pos, vel, acc; };
 template <class P>
-__device__ __noinline__ Rk2Out rk2_tail(int stage, double dt, double mass, V3 force, const double *ob, V3 pos, V3 vel, double *bvel,
-                                        int64_t i_api, int64_t nm) {
-    Rk2Out o;
-    if (stage == 1) {
+__device__ __noinline__ TailOut other_integrators(int stage, double dt, double mass, V3 force, const double *ob, V3 pos, V3 vel, V3 acc,
+                                                  double *bvel, int64_t i_api, int64_t nm) {
+    if (stage == 0) {
+        verlet_tail<P>(dt, mass, force, pos, vel, acc);
+    } else if (stage == 1) {
         if (bvel) { bvel[i_api] = vel.x; bvel[nm + i_api] = vel.y; bvel[2 * nm + i_api] = vel.z; }
-        rk2_stage1_tail<P>(dt, mass, force, pos, vel, o.acc);
+        rk2_stage1_tail<P>(dt, mass, force, pos, vel, acc);
     } else {
         const V3 bv = bvel ? V3{bvel[i_api], bvel[nm + i_api], bvel[2 * nm + i_api]} : V3{ob[3 * TM], ob[4 * TM], ob[5 * TM]};
-        rk2_stage2_tail<P>(dt, mass, force, V3{ob[0], ob[TM], ob[2 * TM]}, bv, pos, vel, o.acc);
+        rk2_stage2_tail<P>(dt, mass, force, V3{ob[0], ob[TM], ob[2 * TM]}, bv, pos, vel, acc);
     }
-    o.pos = pos; o.vel = vel;
-    return o;
+    return TailOut{pos, vel, acc};
 }
 
 // A consumer warp has finished `pending` boundary tiles: make its peer stores visible, count them, and -- as the
@@ -1715,11 +1716,12 @@ __global__ void __launch_bounds__(TM * TPM + 32, (TPM <= 2 ? (DICT ? DICT_CTAS :
                 const int64_t i_api = extras ? A.slot_to_api[tile * TM + t] : 0;
                 V3 acc;
                 force = mass_forces<P>(G, X, i_api, fl & F_LOCAL, mass, pos, vel, force);
-                if (A.write_acc == 2) {     // the reference's VERLET build: the previous acceleration is state, kept in the
-                    acc = V3{A.acc[i_api], A.acc[X.nm + i_api], A.acc[2 * X.nm + i_api]};   // canonical array by this thread
-                    verlet_tail<P>(G.dt, mass, force, pos, vel, acc);
-                } else if (A.rk2_stage) {   // the reference's RK2 build: two launches per step (out of line, rare)
-                    const Rk2Out o = rk2_tail<P>(A.rk2_stage, G.dt, mass, force, ob, pos, vel, (fl & F_LOCAL) ? X.rk2_bvel : nullptr, i_api, X.nm);
+                if (A.write_acc == 2 || A.rk2_stage) {   // the reference's VERLET / RK2 builds: rare, out of line
+                    // Verlet: the previous acceleration is state, kept in the canonical array by this thread
+                    V3 prev = {0.0, 0.0, 0.0};
+                    if (A.write_acc == 2) prev = V3{A.acc[i_api], A.acc[X.nm + i_api], A.acc[2 * X.nm + i_api]};
+                    const TailOut o = other_integrators<P>(A.rk2_stage, G.dt, mass, force, ob, pos, vel, prev,
+                                                           (fl & F_LOCAL) ? X.rk2_bvel : nullptr, i_api, X.nm);
                     pos = o.pos; vel = o.vel; acc = o.acc;
                 } else {
                     euler_tail<P>(G.dt, mass, force, pos, vel, acc);
