@@ -33,6 +33,7 @@
 #include <atomic>
 #include <chrono>
 #include <map>
+#include <memory>
 #include <mutex>
 #include <numeric>
 #include <thread>
@@ -129,6 +130,7 @@ struct HostTables {
     std::vector<std::vector<int4>> act;                          // per tile: actuated records
     std::vector<int32_t> tile_slots;                             // per tile: record slots
     size_t blob_total = 0;
+    size_t base_ell = 0, base_halo = 0, base_rec = 0, base_map = 0, base_blob = 0;   // sizes right after the last full build
 };
 
 // elements allocated for the device tables (>= what is in use: the ends are room for in-place edits)
@@ -492,8 +494,8 @@ struct TileScratch {
 };
 
 static void build_tile(const Engine *e, const TiledState *S, int64_t T, const BuildCfg &cfg, TileOut &o) {
-    static thread_local TileScratch *scratch = nullptr;
-    if (!scratch) scratch = new TileScratch();             // lives as long as its thread
+    static thread_local std::unique_ptr<TileScratch> scratch;
+    if (!scratch) scratch.reset(new TileScratch());        // lives as long as its thread (the builder's threads are short-lived)
     TileScratch &W = *scratch;
     Half *const rows = W.rows.data();
     int *const cnt = W.cnt;
@@ -986,6 +988,7 @@ static int build_structure(Engine *e, TiledState *S, bool keep_slots = false, in
         TileOut().block.swap(outs[(size_t)T].block);      // release as we go
     }
     e->compact_requested = false;
+    H.base_ell = H.ell.size(); H.base_halo = H.halo.size(); H.base_rec = H.rec_spring.size(); H.base_map = H.rec_map.size(); H.base_blob = H.blob_total;
     return finalize_and_upload(e, S, old_tiles);
 }
 
@@ -998,6 +1001,12 @@ static int patch_structure(Engine *e, TiledState *S, bool *done) {
     if ((int64_t)S->h_meta.size() != S->n_tiles || (int64_t)S->H.tile_slots.size() != S->n_tiles) return TB_OK;
     HostTables &H = S->H;
     const int64_t old_tiles = S->n_tiles;
+    // The lists of rebuilt tiles are appended and the old ones left behind: once that garbage is about one system's worth,
+    // build everything afresh (half a second per million masses) instead of letting host and device tables grow for ever.
+    if (H.ell.size() > 2 * H.base_ell + (size_t)old_tiles * MAX_DEG * TM || H.blob_total > 2 * H.base_blob + ((size_t)64 << 20) ||
+        H.halo.size() > 2 * H.base_halo + ((size_t)1 << 22) || H.rec_spring.size() > 2 * H.base_rec + ((size_t)1 << 22) ||
+        H.rec_map.size() > 2 * H.base_map + ((size_t)1 << 24))
+        return TB_OK;
     const auto w0 = std::chrono::steady_clock::now();
     // new masses: tiles of their own, in index order
     std::vector<int64_t> touched;
