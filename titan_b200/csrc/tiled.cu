@@ -1881,7 +1881,7 @@ int tiled_prepare(Engine *e) {
             e->graph_dirty = true;
             stale |= TS_PARAMS | TS_STATE | TS_FLAGS;       // the blobs were re-allocated; new tiles want their state
             if (S->api_to_slot) { release(e, S->api_to_slot, S->n_api); S->n_api = 0; }
-        } else if (e->patch_needs_layout) stale |= TS_STRUCT;   // the layout cannot absorb the additions: build it afresh
+        } else if (e->patch_needs_layout || !S->supported) stale |= TS_STRUCT;   // the layout cannot absorb the edit: build it afresh
         else e->removed_unpatched = true;                       // removals only: they stay in place with k = 0
     }
     e->patch_masses.clear(); e->patch_springs.clear(); e->patch_needs_layout = false;
